@@ -1,0 +1,732 @@
+// qre_api.cu — the C ABI of libqre_b200.so (declared in include/qre_b200.h): handle
+// lifetime, host<->device staging, TMA descriptor set-up and the launch sequences.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "qre_common.cuh"
+
+using namespace qre;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define QRE_CUDA(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t e__ = (expr);                                                                   \
+    if (e__ != cudaSuccess)                                                                     \
+      return fail(QRE_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// The driver API is reached through the runtime so the library has no link-time dependency
+// on libcuda.so (it must load, and export its symbols, on a machine without a driver).
+int get_encode_fn(EncodeTiledFn* fn) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  QRE_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+  if (p == nullptr || qres != cudaDriverEntryPointSuccess)
+    return fail(QRE_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  *fn = reinterpret_cast<EncodeTiledFn>(p);
+  return QRE_OK;
+}
+
+int make_tmap_bf16(EncodeTiledFn enc, CUtensorMap* map, void* base, uint64_t inner, uint64_t rows,
+                   uint32_t box_inner, uint32_t box_rows) {
+  cuuint64_t dims[2] = {inner, rows};
+  cuuint64_t strides[1] = {inner * 2};
+  cuuint32_t box[2] = {box_inner, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(QRE_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return QRE_OK;
+}
+
+struct Section {
+  size_t off = 0, bytes = 0;
+};
+
+// Device-side result block (one allocation, one D2H copy).
+struct ResultLayout {
+  Section hit_slot, hit_sim, hit_pred_dev, hit_pred_conf, hit_shard, cand, centroid_sim, tok_dev, tok_conf,
+      sem_dev, sem_conf, sem_method, dev, conf, score, flags, ovf;
+  size_t total = 0;
+  void plan(int m, int K, int D) {
+    size_t o = 0;
+    auto add = [&](Section& s, size_t bytes) {
+      s.off = o;
+      s.bytes = bytes;
+      o = align_up(o + bytes, 256);
+    };
+    add(hit_slot, sizeof(int64_t) * m);
+    add(hit_sim, sizeof(float) * m);
+    add(hit_pred_dev, m);
+    add(hit_pred_conf, sizeof(double) * m);
+    add(hit_shard, sizeof(uint32_t) * m);
+    add(cand, sizeof(qre_candidate_t) * m * QRE_TOPK);
+    add(centroid_sim, sizeof(float) * m * (K > 0 ? K : 1));
+    add(tok_dev, m);
+    add(tok_conf, sizeof(double) * m);
+    add(sem_dev, m);
+    add(sem_conf, sizeof(double) * m);
+    add(sem_method, m);
+    add(dev, m);
+    add(conf, sizeof(double) * m);
+    add(score, sizeof(double) * m * D);
+    add(flags, m);
+    add(ovf, sizeof(int32_t));
+    total = o;
+  }
+  qre_result_t view(uint8_t* base) const {
+    qre_result_t r;
+    r.hit_slot = reinterpret_cast<int64_t*>(base + hit_slot.off);
+    r.hit_sim = reinterpret_cast<float*>(base + hit_sim.off);
+    r.hit_pred_dev = base + hit_pred_dev.off;
+    r.hit_pred_conf = reinterpret_cast<double*>(base + hit_pred_conf.off);
+    r.hit_shard = reinterpret_cast<uint32_t*>(base + hit_shard.off);
+    r.cand = reinterpret_cast<qre_candidate_t*>(base + cand.off);
+    r.centroid_sim = reinterpret_cast<float*>(base + centroid_sim.off);
+    r.tok_dev = base + tok_dev.off;
+    r.tok_conf = reinterpret_cast<double*>(base + tok_conf.off);
+    r.sem_dev = base + sem_dev.off;
+    r.sem_conf = reinterpret_cast<double*>(base + sem_conf.off);
+    r.sem_method = base + sem_method.off;
+    r.dev = base + dev.off;
+    r.conf = reinterpret_cast<double*>(base + conf.off);
+    r.score = reinterpret_cast<double*>(base + score.off);
+    r.flags = base + flags.off;
+    return r;
+  }
+};
+
+constexpr size_t kStageBytes = 64u << 20;   // device staging for host-side append/update
+
+}  // namespace
+
+struct qre_cache {
+  DeviceState s;
+  long long hwm = 0, live = 0;
+  std::vector<int64_t> free_slots;
+  std::vector<uint8_t> slot_live;
+  uint8_t* d_stage = nullptr;          // kStageBytes
+  uint8_t* d_in = nullptr;             // lookup inputs (H2D target)
+  uint8_t* h_in = nullptr;             // pinned
+  size_t in_bytes = 0;
+  uint8_t* d_res = nullptr;            // result block
+  uint8_t* h_res = nullptr;            // pinned
+  size_t res_bytes = 0;
+  qre_candidate_t* d_cand = nullptr;   // [max_batch, QRE_TOPK]
+  uint64_t* d_q_ctx = nullptr;         // [max_batch] copy of the last batch's contexts
+  float* d_dump = nullptr;
+  size_t dump_bytes = 0;
+  int64_t launches = 0;
+  int last_m = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+size_t input_bytes(int m, int dim) {
+  return align_up(sizeof(float) * (size_t)m * dim, 256) + align_up(sizeof(uint64_t) * (size_t)m, 256) +
+         align_up(sizeof(int32_t) * (size_t)m, 256) + align_up((size_t)m, 256) +
+         align_up(sizeof(double) * (size_t)m, 256);
+}
+
+int validate_params(const qre_cache_t* h, const qre_params_t* p) {
+  if (p == nullptr) return fail(QRE_ERR_INVALID, "params is NULL");
+  if (p->scan_mode != QRE_SCAN_TENSOR && p->scan_mode != QRE_SCAN_EXACT)
+    return fail(QRE_ERR_INVALID, "unknown scan_mode %d", p->scan_mode);
+  if (p->do_route) {
+    if (p->n_devices < 1 || p->n_devices > QRE_MAX_DEVICES)
+      return fail(QRE_ERR_INVALID, "n_devices %d out of range [1, %d]", p->n_devices, QRE_MAX_DEVICES);
+    if (h->s.n_centroids < 1) return fail(QRE_ERR_INVALID, "do_route set but no centroids uploaded");
+  }
+  return QRE_OK;
+}
+
+// queries -> this shard's candidates (device pointers, enqueue only)
+int scan_enqueue(qre_cache_t* h, int m, const float* q_dev, const uint64_t* q_ctx_dev, const qre_params_t& p,
+                 int shard, qre_candidate_t* cand, cudaStream_t st) {
+  DeviceState& s = h->s;
+  QRE_CUDA(cudaMemcpyAsync(h->d_q_ctx, q_ctx_dev, sizeof(uint64_t) * m, cudaMemcpyDeviceToDevice, st));
+  QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), st));
+  h->launches += launch_prep_queries(s, m, q_dev, st);
+  h->last_m = m;
+  if (p.scan_mode == QRE_SCAN_TENSOR && h->hwm > 0) {
+    h->launches += launch_gemm_topk(s, m, h->hwm, h->d_q_ctx, p, nullptr, 0, 0, 0, st);
+    h->launches += launch_rescore(s, m, h->hwm, p, shard, cand, st);
+  } else {
+    h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, nullptr, m, false, p, shard, cand, st);
+  }
+  QRE_CUDA(cudaGetLastError());
+  return QRE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int qre_abi_version(void) { return QRE_ABI_VERSION; }
+
+const char* qre_last_error(void) { return g_err.c_str(); }
+
+int qre_device_count(int* count) {
+  if (count == nullptr) return fail(QRE_ERR_INVALID, "count is NULL");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    *count = 0;
+    return fail(QRE_ERR_NO_DEVICE, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+  }
+  *count = n;
+  return QRE_OK;
+}
+
+int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_cache_t** out) {
+  if (out == nullptr) return fail(QRE_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  if (dim < 8 || dim % 8 != 0) return fail(QRE_ERR_INVALID, "dim must be a positive multiple of 8 (got %d)", dim);
+  if (capacity < 1 || capacity > 0xFFFFFFF0ll) return fail(QRE_ERR_INVALID, "capacity out of range");
+  if (max_batch < 1 || max_batch > (1 << 20)) return fail(QRE_ERR_INVALID, "max_batch out of range");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+    return fail(QRE_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(QRE_ERR_INVALID, "device %d out of range (have %d)", device, ndev);
+  cudaDeviceProp prop;
+  QRE_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(QRE_ERR_NO_DEVICE, "device %d is sm_%d%d; libqre_b200 is built for sm_100a only", device,
+                prop.major, prop.minor);
+  const int dim_pad = (int)align_up(dim, kBK);
+  if (dim_pad / kBK > kMaxKB)
+    return fail(QRE_ERR_INVALID, "dim %d not supported by the resident-query scan (max %d)", dim, kMaxKB * kBK);
+  DeviceGuard guard(device);
+  qre_cache_t* h = new (std::nothrow) qre_cache_t();
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "out of host memory");
+  DeviceState& s = h->s;
+  s.device = device;
+  s.num_sms = prop.multiProcessorCount;
+  s.dim = dim;
+  s.dim_pad = dim_pad;
+  s.max_batch = max_batch;
+  s.mb_pad = (int)align_up(max_batch, kBM);
+  s.capacity = capacity;
+  s.cap_pad = (long long)align_up((size_t)capacity, kBN);
+#define QRE_TRY(expr)                 \
+  do {                                \
+    int rc__ = (expr);                \
+    if (rc__ != QRE_OK) {             \
+      std::string keep = g_err;       \
+      qre_cache_destroy(h);           \
+      g_err = keep;                   \
+      return rc__;                    \
+    }                                 \
+  } while (0)
+#define QRE_ALLOC(ptr, bytes) QRE_TRY([&]() -> int { QRE_CUDA(cudaMalloc((void**)&(ptr), (bytes))); return QRE_OK; }())
+  QRE_TRY([&]() -> int { QRE_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)); return QRE_OK; }());
+  QRE_ALLOC(s.rows_f32, sizeof(float) * (size_t)capacity * dim_pad);
+  QRE_ALLOC(s.rows_bf16, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad);
+  QRE_ALLOC(s.row_norm, sizeof(float) * (size_t)capacity);
+  QRE_ALLOC(s.meta, sizeof(RowMeta) * (size_t)capacity);
+  QRE_ALLOC(s.lru, sizeof(uint64_t) * (size_t)capacity);
+  QRE_ALLOC(s.pred_dev, (size_t)capacity);
+  QRE_ALLOC(s.pred_conf, sizeof(double) * (size_t)capacity);
+  QRE_ALLOC(s.q_f32, sizeof(float) * (size_t)s.mb_pad * dim_pad);
+  QRE_ALLOC(s.q_bf16, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad);
+  QRE_ALLOC(s.q_norm, sizeof(float) * (size_t)s.mb_pad);
+  // scratch of the fused top-k: [mblocks*128][S][8] entries; S*mblocks <= 8 waves of SMs + slack
+  {
+    long long worst = 0;
+    for (int mb = 1; mb <= s.mb_pad / kBM; ++mb) {
+      const ScanGeometry g = plan_scan(mb * kBM, s.cap_pad, s.num_sms);
+      worst = std::max(worst, (long long)g.mblocks * kBM * g.splits * kTopK);
+      if (mb > 64) mb += 7;   // the product is ~constant beyond one wave; sample sparsely
+    }
+    const ScanGeometry g = plan_scan(s.mb_pad, s.cap_pad, s.num_sms);
+    worst = std::max(worst, (long long)g.mblocks * kBM * g.splits * kTopK);
+    s.partial_entries = worst + (long long)kBM * kTopK * (s.num_sms + 8);
+  }
+  QRE_ALLOC(s.partial, sizeof(PartialEntry) * (size_t)s.partial_entries);
+  s.exact_grid = s.num_sms * 2;
+  QRE_ALLOC(s.exact_partial, sizeof(ExactBest) * (size_t)kExactGroup * s.exact_grid);
+  QRE_ALLOC(s.ovf_count, sizeof(int32_t));
+  QRE_ALLOC(s.ovf_list, sizeof(int32_t) * (size_t)max_batch);
+  QRE_ALLOC(s.q_flags, (size_t)max_batch);
+  QRE_ALLOC(s.centroids, sizeof(float) * (size_t)QRE_MAX_CENTROIDS * dim_pad);
+  QRE_ALLOC(s.cent_norm, sizeof(float) * QRE_MAX_CENTROIDS);
+  QRE_ALLOC(s.cent_owner, QRE_MAX_CENTROIDS);
+  QRE_ALLOC(s.perf_health, sizeof(double) * QRE_MAX_DEVICES);
+  QRE_ALLOC(h->d_stage, kStageBytes);
+  h->in_bytes = input_bytes(max_batch, dim);
+  QRE_ALLOC(h->d_in, h->in_bytes);
+  {
+    ResultLayout L;
+    L.plan(max_batch, QRE_MAX_CENTROIDS, QRE_MAX_DEVICES);
+    h->res_bytes = L.total;
+  }
+  QRE_ALLOC(h->d_res, h->res_bytes);
+  QRE_ALLOC(h->d_cand, sizeof(qre_candidate_t) * (size_t)max_batch * QRE_TOPK);
+  QRE_ALLOC(h->d_q_ctx, sizeof(uint64_t) * (size_t)max_batch);
+  QRE_TRY([&]() -> int {
+    QRE_CUDA(cudaMallocHost((void**)&h->h_in, h->in_bytes));
+    QRE_CUDA(cudaMallocHost((void**)&h->h_res, h->res_bytes));
+    QRE_CUDA(cudaMemsetAsync(s.rows_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.meta, 0xFF, sizeof(RowMeta) * (size_t)capacity, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.q_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.perf_health, 0, sizeof(double) * QRE_MAX_DEVICES, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.q_flags, 0, (size_t)max_batch, s.stream));
+    QRE_CUDA(gemm_topk_init());
+    EncodeTiledFn enc = nullptr;
+    int rc = get_encode_fn(&enc);
+    if (rc != QRE_OK) return rc;
+    rc = make_tmap_bf16(enc, &s.tmap_e, s.rows_bf16, (uint64_t)dim_pad, (uint64_t)s.cap_pad, kBK, kBN);
+    if (rc != QRE_OK) return rc;
+    rc = make_tmap_bf16(enc, &s.tmap_q, s.q_bf16, (uint64_t)dim_pad, (uint64_t)s.mb_pad, kBK, kBM);
+    if (rc != QRE_OK) return rc;
+    QRE_CUDA(cudaStreamSynchronize(s.stream));
+    return QRE_OK;
+  }());
+#undef QRE_ALLOC
+#undef QRE_TRY
+  h->slot_live.assign((size_t)capacity, 0);
+  *out = h;
+  return QRE_OK;
+}
+
+int qre_cache_destroy(qre_cache_t* h) {
+  if (h == nullptr) return QRE_OK;
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  if (s.stream) cudaStreamSynchronize(s.stream);
+  void* dev_ptrs[] = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf, s.q_f32,
+                      s.q_bf16, s.q_norm, s.partial, s.exact_partial, s.ovf_count, s.ovf_list, s.q_flags,
+                      s.centroids, s.cent_norm, s.cent_owner, s.perf_health, h->d_stage, h->d_in, h->d_res,
+                      h->d_cand, h->d_q_ctx, h->d_dump};
+  for (void* p : dev_ptrs)
+    if (p) cudaFree(p);
+  if (h->h_in) cudaFreeHost(h->h_in);
+  if (h->h_res) cudaFreeHost(h->h_res);
+  if (s.stream) cudaStreamDestroy(s.stream);
+  delete h;
+  return QRE_OK;
+}
+
+int qre_cache_info(const qre_cache_t* h, int64_t* capacity, int64_t* high_water, int64_t* live, int* dim,
+                   int* max_batch, int* device) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (capacity) *capacity = h->s.capacity;
+  if (high_water) *high_water = h->hwm;
+  if (live) *live = h->live;
+  if (dim) *dim = h->s.dim;
+  if (max_batch) *max_batch = h->s.max_batch;
+  if (device) *device = h->s.device;
+  return QRE_OK;
+}
+
+int qre_cache_stream(const qre_cache_t* h, void** stream) {
+  if (h == nullptr || stream == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  *stream = (void*)h->s.stream;
+  return QRE_OK;
+}
+
+int qre_launch_count(const qre_cache_t* h, int64_t* count) {
+  if (h == nullptr || count == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  *count = h->launches;
+  return QRE_OK;
+}
+
+// Choose n slots: tombstoned ones first (LIFO), then fresh ones past the high-water mark.
+static int take_slots(qre_cache_t* h, int64_t n, int64_t* slot_out) {
+  const long long avail = (long long)h->free_slots.size() + (h->s.capacity - h->hwm);
+  if (n > avail) return fail(QRE_ERR_CAPACITY, "cache shard full: need %lld slots, %lld free", (long long)n, avail);
+  for (int64_t i = 0; i < n; ++i) {
+    int64_t sl;
+    if (!h->free_slots.empty()) {
+      sl = h->free_slots.back();
+      h->free_slots.pop_back();
+    } else {
+      sl = h->hwm++;
+    }
+    h->slot_live[(size_t)sl] = 1;
+    slot_out[i] = sl;
+  }
+  h->live += n;
+  return QRE_OK;
+}
+
+// One staged chunk: copy host arrays (any may be NULL) into d_stage and launch write_rows.
+static int staged_write(qre_cache_t* h, int64_t n, const int64_t* slot, const float* rows, const uint64_t* ctx,
+                        const int64_t* ts, const uint64_t* lru, const uint8_t* pdev, const double* pconf) {
+  DeviceState& s = h->s;
+  const size_t per_row = sizeof(float) * s.dim + 8 + 8 + 8 + 8 + 1 + 8;
+  const int64_t chunk = std::max<int64_t>(1, (int64_t)((kStageBytes - 8 * 256) / per_row));
+  for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+    const int64_t c = std::min<int64_t>(chunk, n - i0);
+    size_t o = 0;
+    auto put = [&](const void* src, size_t bytes, void** dst) -> cudaError_t {
+      *dst = nullptr;
+      if (src == nullptr) return cudaSuccess;
+      *dst = h->d_stage + o;
+      o = align_up(o + bytes, 256);
+      return cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, s.stream);
+    };
+    void *d_slot, *d_rows, *d_ctx, *d_ts, *d_lru, *d_pdev, *d_pconf;
+    QRE_CUDA(put(slot + i0, sizeof(int64_t) * c, &d_slot));
+    QRE_CUDA(put(rows ? rows + i0 * s.dim : nullptr, sizeof(float) * c * s.dim, &d_rows));
+    QRE_CUDA(put(ctx ? ctx + i0 : nullptr, sizeof(uint64_t) * c, &d_ctx));
+    QRE_CUDA(put(ts ? ts + i0 : nullptr, sizeof(int64_t) * c, &d_ts));
+    QRE_CUDA(put(lru ? lru + i0 : nullptr, sizeof(uint64_t) * c, &d_lru));
+    QRE_CUDA(put(pdev ? pdev + i0 : nullptr, (size_t)c, &d_pdev));
+    QRE_CUDA(put(pconf ? pconf + i0 : nullptr, sizeof(double) * c, &d_pconf));
+    h->launches += launch_append(s, c, (const float*)d_rows, s.dim, (const int64_t*)d_slot, (const uint64_t*)d_ctx,
+                                 (const int64_t*)d_ts, (const uint64_t*)d_lru, (const uint8_t*)d_pdev,
+                                 (const double*)d_pconf, s.stream);
+    QRE_CUDA(cudaGetLastError());
+    // pageable sources: the copies above have consumed the host data before returning, and the
+    // next chunk's copies are stream-ordered after this kernel, so d_stage can be reused.
+  }
+  QRE_CUDA(cudaStreamSynchronize(s.stream));
+  return QRE_OK;
+}
+
+int qre_cache_append(qre_cache_t* h, int64_t n, const float* rows, const uint64_t* ctx, const int64_t* ts_us,
+                     const uint64_t* lru_seq, const uint8_t* pred_dev, const double* pred_conf,
+                     int64_t* slot_out) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n < 0 || (n > 0 && (!rows || !ctx || !ts_us || !lru_seq || !pred_dev || !pred_conf || !slot_out)))
+    return fail(QRE_ERR_INVALID, "append needs every array");
+  if (n == 0) return QRE_OK;
+  DeviceGuard guard(h->s.device);
+  int rc = take_slots(h, n, slot_out);
+  if (rc != QRE_OK) return rc;
+  return staged_write(h, n, slot_out, rows, ctx, ts_us, lru_seq, pred_dev, pred_conf);
+}
+
+int qre_cache_append_dev(qre_cache_t* h, int64_t n, const float* rows, const uint64_t* ctx, const int64_t* ts_us,
+                         const uint64_t* lru_seq, const uint8_t* pred_dev, const double* pred_conf,
+                         int64_t* slot_out_host, void* stream) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n < 0 || (n > 0 && (!rows || !ctx || !ts_us || !lru_seq || !pred_dev || !pred_conf)))
+    return fail(QRE_ERR_INVALID, "append_dev needs every array");
+  if (n == 0) return QRE_OK;
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  cudaStream_t st = stream ? (cudaStream_t)stream : s.stream;
+  std::vector<int64_t> slots((size_t)n);
+  int rc = take_slots(h, n, slots.data());
+  if (rc != QRE_OK) return rc;
+  if (slot_out_host) memcpy(slot_out_host, slots.data(), sizeof(int64_t) * (size_t)n);
+  const int64_t chunk = (int64_t)(kStageBytes / sizeof(int64_t));
+  for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+    const int64_t c = std::min<int64_t>(chunk, n - i0);
+    QRE_CUDA(cudaMemcpyAsync(h->d_stage, slots.data() + i0, sizeof(int64_t) * c, cudaMemcpyHostToDevice, st));
+    h->launches += launch_append(s, c, rows + i0 * s.dim, s.dim, (const int64_t*)h->d_stage, ctx + i0, ts_us + i0,
+                                 lru_seq + i0, pred_dev + i0, pred_conf + i0, st);
+    QRE_CUDA(cudaGetLastError());
+    QRE_CUDA(cudaStreamSynchronize(st));   // `slots` is pageable and d_stage is reused
+  }
+  return QRE_OK;
+}
+
+static int check_slots(const qre_cache_t* h, int64_t n, const int64_t* slot) {
+  for (int64_t i = 0; i < n; ++i)
+    if (slot[i] < 0 || slot[i] >= h->hwm || !h->slot_live[(size_t)slot[i]])
+      return fail(QRE_ERR_INVALID, "slot %lld is not a live row", (long long)slot[i]);
+  return QRE_OK;
+}
+
+int qre_cache_update(qre_cache_t* h, int64_t n, const int64_t* slot, const float* rows, const uint64_t* ctx,
+                     const int64_t* ts_us, const uint64_t* lru_seq, const uint8_t* pred_dev,
+                     const double* pred_conf) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n < 0 || (n > 0 && !slot)) return fail(QRE_ERR_INVALID, "slot is NULL");
+  if (n == 0) return QRE_OK;
+  int rc = check_slots(h, n, slot);
+  if (rc != QRE_OK) return rc;
+  DeviceGuard guard(h->s.device);
+  return staged_write(h, n, slot, rows, ctx, ts_us, lru_seq, pred_dev, pred_conf);
+}
+
+int qre_cache_tombstone(qre_cache_t* h, int64_t n, const int64_t* slot) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n < 0 || (n > 0 && !slot)) return fail(QRE_ERR_INVALID, "slot is NULL");
+  if (n == 0) return QRE_OK;
+  int rc = check_slots(h, n, slot);
+  if (rc != QRE_OK) return rc;
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  const int64_t chunk = (int64_t)(kStageBytes / sizeof(int64_t));
+  for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+    const int64_t c = std::min<int64_t>(chunk, n - i0);
+    QRE_CUDA(cudaMemcpyAsync(h->d_stage, slot + i0, sizeof(int64_t) * c, cudaMemcpyHostToDevice, s.stream));
+    h->launches += launch_tombstone(s, c, (const int64_t*)h->d_stage, s.stream);
+    QRE_CUDA(cudaGetLastError());
+  }
+  QRE_CUDA(cudaStreamSynchronize(s.stream));
+  for (int64_t i = 0; i < n; ++i) {
+    if (h->slot_live[(size_t)slot[i]]) {      // a slot listed twice is freed once
+      h->slot_live[(size_t)slot[i]] = 0;
+      h->free_slots.push_back(slot[i]);
+      --h->live;
+    }
+  }
+  return QRE_OK;
+}
+
+int qre_cache_clear(qre_cache_t* h) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  QRE_CUDA(cudaMemsetAsync(s.rows_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * s.dim_pad, s.stream));
+  QRE_CUDA(cudaMemsetAsync(s.meta, 0xFF, sizeof(RowMeta) * (size_t)s.capacity, s.stream));
+  QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)s.capacity, s.stream));
+  QRE_CUDA(cudaStreamSynchronize(s.stream));
+  h->hwm = 0;
+  h->live = 0;
+  h->free_slots.clear();
+  std::fill(h->slot_live.begin(), h->slot_live.end(), 0);
+  return QRE_OK;
+}
+
+int qre_cache_read_rows(qre_cache_t* h, int64_t n, const int64_t* slot, float* rows_out) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n < 0 || (n > 0 && (!slot || !rows_out))) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (n == 0) return QRE_OK;
+  int rc = check_slots(h, n, slot);
+  if (rc != QRE_OK) return rc;
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  const size_t per_row = sizeof(int64_t) + sizeof(float) * s.dim;
+  const int64_t chunk = std::max<int64_t>(1, (int64_t)((kStageBytes - 512) / per_row));
+  for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+    const int64_t c = std::min<int64_t>(chunk, n - i0);
+    int64_t* d_slot = (int64_t*)h->d_stage;
+    float* d_out = (float*)(h->d_stage + align_up(sizeof(int64_t) * c, 256));
+    QRE_CUDA(cudaMemcpyAsync(d_slot, slot + i0, sizeof(int64_t) * c, cudaMemcpyHostToDevice, s.stream));
+    h->launches += launch_gather_rows(s, c, d_slot, d_out, s.stream);
+    QRE_CUDA(cudaGetLastError());
+    QRE_CUDA(cudaMemcpyAsync(rows_out + i0 * s.dim, d_out, sizeof(float) * c * s.dim, cudaMemcpyDeviceToHost,
+                             s.stream));
+    QRE_CUDA(cudaStreamSynchronize(s.stream));
+  }
+  return QRE_OK;
+}
+
+int qre_set_centroids(qre_cache_t* h, int n_centroids, const float* centroids, const uint8_t* owner_device) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n_centroids < 1 || n_centroids > QRE_MAX_CENTROIDS || !centroids || !owner_device)
+    return fail(QRE_ERR_INVALID, "n_centroids out of range [1, %d] or NULL array", QRE_MAX_CENTROIDS);
+  for (int k = 0; k < n_centroids; ++k)
+    if (owner_device[k] >= QRE_MAX_DEVICES) return fail(QRE_ERR_INVALID, "centroid %d: owner out of range", k);
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  QRE_CUDA(cudaMemsetAsync(s.centroids, 0, sizeof(float) * (size_t)n_centroids * s.dim_pad, s.stream));
+  QRE_CUDA(cudaMemcpy2DAsync(s.centroids, sizeof(float) * s.dim_pad, centroids, sizeof(float) * s.dim,
+                             sizeof(float) * s.dim, n_centroids, cudaMemcpyHostToDevice, s.stream));
+  QRE_CUDA(cudaMemcpyAsync(s.cent_owner, owner_device, n_centroids, cudaMemcpyHostToDevice, s.stream));
+  s.n_centroids = n_centroids;
+  h->launches += launch_prep_centroids(s, n_centroids, s.stream);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaStreamSynchronize(s.stream));
+  return QRE_OK;
+}
+
+int qre_set_perf_health(qre_cache_t* h, int n_devices, const double* health) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (n_devices < 1 || n_devices > QRE_MAX_DEVICES || !health) return fail(QRE_ERR_INVALID, "bad n_devices");
+  DeviceGuard guard(h->s.device);
+  QRE_CUDA(cudaMemcpyAsync(h->s.perf_health, health, sizeof(double) * n_devices, cudaMemcpyHostToDevice,
+                           h->s.stream));
+  QRE_CUDA(cudaStreamSynchronize(h->s.stream));
+  return QRE_OK;
+}
+
+int qre_scan_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx, const qre_params_t* params,
+                 int shard, qre_candidate_t* cand_out, int32_t* overflow_count, void* stream) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
+  if (!queries || !q_ctx || !cand_out) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (params == nullptr) return fail(QRE_ERR_INVALID, "params is NULL");
+  if (params->scan_mode != QRE_SCAN_TENSOR && params->scan_mode != QRE_SCAN_EXACT)
+    return fail(QRE_ERR_INVALID, "unknown scan_mode %d", params->scan_mode);
+  DeviceGuard guard(h->s.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  int rc = scan_enqueue(h, m, queries, q_ctx, *params, shard, cand_out, st);
+  if (rc != QRE_OK) return rc;
+  if (overflow_count)
+    QRE_CUDA(cudaMemcpyAsync(overflow_count, h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  return QRE_OK;
+}
+
+int qre_resolve_overflow_dev(qre_cache_t* h, int m, const qre_params_t* params, int shard,
+                             qre_candidate_t* cand_inout, void* stream) {
+  if (h == nullptr || params == nullptr || cand_inout == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (m != h->last_m) return fail(QRE_ERR_INVALID, "m=%d does not match the last scan (%d)", m, h->last_m);
+  DeviceGuard guard(h->s.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  int32_t n_ovf = 0;
+  QRE_CUDA(cudaMemcpyAsync(&n_ovf, h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  QRE_CUDA(cudaStreamSynchronize(st));
+  if (n_ovf <= 0) return QRE_OK;
+  h->launches += launch_exact_scan(h->s, m, h->hwm, h->d_q_ctx, h->s.ovf_list, n_ovf, true, *params, shard,
+                                   cand_inout, st);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaMemsetAsync(h->s.ovf_count, 0, sizeof(int32_t), st));
+  return QRE_OK;
+}
+
+int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
+                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
+                        qre_result_t* out_dev, void* stream) {
+  if (h == nullptr || cand_all == nullptr || out_dev == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
+  if (m != h->last_m) return fail(QRE_ERR_INVALID, "m=%d does not match the last scan (%d)", m, h->last_m);
+  if (n_shards < 1 || n_shards * QRE_TOPK > 128) return fail(QRE_ERR_INVALID, "n_shards out of range [1, 16]");
+  int rc = validate_params(h, params);
+  if (rc != QRE_OK) return rc;
+  if (params->do_route && (!tok || !heur_dev || !heur_conf))
+    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
+  DeviceGuard guard(h->s.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  h->launches += launch_merge_route(h->s, m, n_shards, cand_all, tok, heur_dev, heur_conf, *params, *out_dev, st);
+  QRE_CUDA(cudaGetLastError());
+  return QRE_OK;
+}
+
+int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx, const int32_t* tok,
+                     const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
+                     qre_result_t* out) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
+  if (!queries || !q_ctx || !out) return fail(QRE_ERR_INVALID, "NULL argument");
+  int rc = validate_params(h, params);
+  if (rc != QRE_OK) return rc;
+  const qre_params_t& p = *params;
+  if (p.do_route && (!tok || !heur_dev || !heur_conf))
+    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  cudaStream_t st = s.stream;
+  // ---- stage inputs (pinned) and copy once ----
+  size_t o = 0;
+  auto put = [&](const void* src, size_t bytes) -> uint8_t* {
+    uint8_t* d = h->d_in + o;
+    if (src) memcpy(h->h_in + o, src, bytes);
+    o = align_up(o + bytes, 256);
+    return d;
+  };
+  const float* d_q = (const float*)put(queries, sizeof(float) * (size_t)m * s.dim);
+  const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t) * (size_t)m);
+  const int32_t* d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m);
+  const uint8_t* d_hd = put(heur_dev, (size_t)m);
+  const double* d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m);
+  QRE_CUDA(cudaMemcpyAsync(h->d_in, h->h_in, o, cudaMemcpyHostToDevice, st));
+  rc = scan_enqueue(h, m, d_q, d_ctx, p, 0, h->d_cand, st);
+  if (rc != QRE_OK) return rc;
+  ResultLayout L;
+  const int K = p.do_route ? s.n_centroids : 0;
+  const int D = p.do_route ? p.n_devices : 1;
+  L.plan(m, K, D);
+  const qre_result_t dres = L.view(h->d_res);
+  for (int pass = 0; pass < 2; ++pass) {
+    h->launches += launch_merge_route(s, m, 1, h->d_cand, d_tok, d_hd, d_hc, p, dres, st);
+    QRE_CUDA(cudaGetLastError());
+    QRE_CUDA(cudaMemcpyAsync(h->d_res + L.ovf.off, s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    QRE_CUDA(cudaMemcpyAsync(h->h_res, h->d_res, L.total, cudaMemcpyDeviceToHost, st));
+    QRE_CUDA(cudaStreamSynchronize(st));
+    const int32_t n_ovf = *reinterpret_cast<const int32_t*>(h->h_res + L.ovf.off);
+    if (n_ovf <= 0 || pass == 1) break;
+    // rare: some query had more than QRE_TOPK contenders inside the bf16 error window of one
+    // row range; settle those queries with the exact fp32 scan and merge again.
+    h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, s.ovf_list, n_ovf, true, p, 0, h->d_cand, st);
+    QRE_CUDA(cudaGetLastError());
+    QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), st));
+  }
+  const qre_result_t hres = L.view(h->h_res);
+#define QRE_OUT(field, bytes) \
+  if (out->field) memcpy(out->field, hres.field, (bytes))
+  QRE_OUT(hit_slot, sizeof(int64_t) * m);
+  QRE_OUT(hit_sim, sizeof(float) * m);
+  QRE_OUT(hit_pred_dev, (size_t)m);
+  QRE_OUT(hit_pred_conf, sizeof(double) * m);
+  QRE_OUT(hit_shard, sizeof(uint32_t) * m);
+  QRE_OUT(cand, sizeof(qre_candidate_t) * m * QRE_TOPK);
+  QRE_OUT(flags, (size_t)m);
+  if (p.do_route) {
+    QRE_OUT(centroid_sim, sizeof(float) * (size_t)m * K);
+    QRE_OUT(tok_dev, (size_t)m);
+    QRE_OUT(tok_conf, sizeof(double) * m);
+    QRE_OUT(sem_dev, (size_t)m);
+    QRE_OUT(sem_conf, sizeof(double) * m);
+    QRE_OUT(sem_method, (size_t)m);
+    QRE_OUT(dev, (size_t)m);
+    QRE_OUT(conf, sizeof(double) * m);
+    QRE_OUT(score, sizeof(double) * (size_t)m * D);
+  }
+#undef QRE_OUT
+  return QRE_OK;
+}
+
+int qre_debug_gemm(qre_cache_t* h, int m, int64_t row0, int n, float* out) {
+  if (h == nullptr || out == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (m < 1 || m != h->last_m) return fail(QRE_ERR_INVALID, "run a scan with the same m first");
+  if (n < 1 || row0 < 0 || row0 + n > h->hwm) return fail(QRE_ERR_INVALID, "row range outside the cache");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  const size_t bytes = sizeof(float) * (size_t)m * n;
+  if (bytes > h->dump_bytes) {
+    if (h->d_dump) cudaFree(h->d_dump);
+    h->d_dump = nullptr;
+    h->dump_bytes = 0;
+    QRE_CUDA(cudaMalloc((void**)&h->d_dump, bytes));
+    h->dump_bytes = bytes;
+  }
+  QRE_CUDA(cudaMemsetAsync(h->d_dump, 0, bytes, s.stream));
+  qre_params_t p;
+  memset(&p, 0, sizeof(p));
+  p.similarity_threshold = 2.0;   // floor above any cosine: the candidate path stays idle
+  p.ttl_us = 1;
+  h->launches += launch_gemm_topk(s, m, h->hwm, h->d_q_ctx, p, h->d_dump, n, row0, n, s.stream);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaMemcpyAsync(out, h->d_dump, bytes, cudaMemcpyDeviceToHost, s.stream));
+  QRE_CUDA(cudaStreamSynchronize(s.stream));
+  return QRE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,124 @@
+// Shared definitions of libqre_b200: device data layout, kernel argument blocks, launch
+// wrappers.  See DESIGN.md for the layout rationale.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#include "../../include/qre_b200.h"
+
+namespace qre {
+
+constexpr int kBM = 128;          // queries per tile (UMMA M, one TMEM lane per query)
+constexpr int kBN = 256;          // cache rows per tile (UMMA N)
+constexpr int kBK = 64;           // bf16 elements per k-block (= one 128-byte swizzle row)
+constexpr int kStages = 4;        // B-tile pipeline depth (4 x 32 KB)
+constexpr int kMaxKB = 6;         // resident-A variant: dim_pad <= 384
+constexpr int kTopK = QRE_TOPK;
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+constexpr float kNormEps = 1e-9f;                 // src/cache.py:284,289 ; qre:136
+
+// |approx - cosine| bound of the bf16 tensor-core score: two bf16 roundings (2^-9 each)
+// under Cauchy-Schwarz = 2^-8, plus fp32 accumulation / normalisation slack.
+constexpr float kApproxEps = 0.00390625f + 0.000244140625f;
+
+struct __align__(16) RowMeta {    // per cache row, read only on the (rare) candidate path
+  uint64_t ctx;                   // context id; QRE_CTX_TOMBSTONE = deleted
+  int64_t ts_us;                  // insert/refresh time, microseconds
+};
+
+struct __align__(8) PartialEntry {  // approximate candidate kept by the fused top-k
+  float v;                          // bf16 tensor-core cosine
+  uint32_t row;                     // slot, kNoRow = empty
+};
+
+struct ExactBest {                  // per-(CTA, query) winner of the brute-force scan
+  float sim;
+  uint32_t row;
+  uint64_t lru;
+};
+
+// Arguments of the tensor-core scan kernel.
+struct GemmArgs {
+  int m;                    // queries in the batch
+  int mblocks;              // ceil(m / 128)
+  int tiles_n;              // ceil(n_rows / 256)
+  int splits;               // S: row ranges per M-block; work units = S * mblocks
+  int num_kb;               // dim_pad / 64
+  long long n_rows;         // high-water mark of the shard
+  float floor_v;            // max(threshold, 0) - eps: nothing below can be a hit
+  long long now_us, ttl_us;
+  const uint64_t* q_ctx;    // [m]
+  const RowMeta* meta;      // [capacity]
+  PartialEntry* partial;    // [mblocks*128][S][kTopK]   (scratch)
+  float* dump;              // debug: raw accumulators out[q * dump_ld + (row - dump_row0)]
+  long long dump_ld, dump_row0;
+};
+
+struct ScanGeometry {
+  int mblocks, tiles_n, splits, grid;
+};
+ScanGeometry plan_scan(int m, long long n_rows, int num_sms);
+cudaError_t gemm_topk_init();
+
+// All device state of one cache shard.
+struct DeviceState {
+  int device = 0, num_sms = 0;
+  int dim = 0, dim_pad = 0, max_batch = 0, mb_pad = 0;
+  long long capacity = 0, cap_pad = 0;
+  cudaStream_t stream = nullptr;
+  // cache rows
+  float* rows_f32 = nullptr;          // [capacity, dim_pad]  fp32 master (zero padded)
+  __nv_bfloat16* rows_bf16 = nullptr; // [cap_pad, dim_pad]   L2-normalised, bf16
+  float* row_norm = nullptr;          // [capacity]           |e| in fp32
+  RowMeta* meta = nullptr;            // [capacity]
+  uint64_t* lru = nullptr;            // [capacity]
+  uint8_t* pred_dev = nullptr;        // [capacity]
+  double* pred_conf = nullptr;        // [capacity]
+  // per-batch query state
+  float* q_f32 = nullptr;             // [mb_pad, dim_pad]
+  __nv_bfloat16* q_bf16 = nullptr;    // [mb_pad, dim_pad]
+  float* q_norm = nullptr;            // [mb_pad]
+  // scratch
+  PartialEntry* partial = nullptr;    // [partial_entries]
+  long long partial_entries = 0;
+  ExactBest* exact_partial = nullptr; // [kExactGroup * exact_grid]
+  int exact_grid = 0;
+  int32_t* ovf_count = nullptr;       // [1]
+  int32_t* ovf_list = nullptr;        // [max_batch]
+  uint8_t* q_flags = nullptr;         // [max_batch]  QRE_FLAG_* of the current batch
+  // router state
+  float* centroids = nullptr;         // [K, dim_pad]
+  float* cent_norm = nullptr;         // [K]
+  uint8_t* cent_owner = nullptr;      // [K]
+  int n_centroids = 0;
+  double* perf_health = nullptr;      // [QRE_MAX_DEVICES]
+  CUtensorMap tmap_q, tmap_e;
+};
+
+constexpr int kExactGroup = 8;        // queries per brute-force pass
+
+// ---- launch wrappers (qre_kernels.cu / qre_gemm_topk.cu); each returns #launches --------
+int launch_append(DeviceState& s, long long n, const float* rows_dev, long long rows_ld, const int64_t* slot_dev,
+                  const uint64_t* ctx, const int64_t* ts, const uint64_t* lru, const uint8_t* pdev,
+                  const double* pconf, cudaStream_t st);
+int launch_update_meta(DeviceState& s, long long n, const int64_t* slot_dev, const uint64_t* ctx,
+                       const int64_t* ts, const uint64_t* lru, const uint8_t* pdev, const double* pconf,
+                       cudaStream_t st);
+int launch_tombstone(DeviceState& s, long long n, const int64_t* slot_dev, cudaStream_t st);
+int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, float* out, cudaStream_t st);
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, cudaStream_t st);
+int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st);
+int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+                     float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st);
+int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& p, int shard,
+                   qre_candidate_t* cand, cudaStream_t st);
+int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const int32_t* qlist_dev,
+                      int nq_total, bool use_ovf_list, const qre_params_t& p, int shard, qre_candidate_t* cand,
+                      cudaStream_t st);
+int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
+                       const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
+                       const qre_result_t& out, cudaStream_t st);
+
+}  // namespace qre

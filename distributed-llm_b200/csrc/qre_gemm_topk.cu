@@ -1,0 +1,296 @@
+// qre_gemm_topk.cu — the dominant kernel of the routing-cache lookup.
+//
+// Replaces the reference's per-entry cosine loop (src/cache.py:287-293) for a whole batch:
+// approx[q, row] = <bf16(q/|q|), bf16(e/|e|)> on the 5th-gen tensor cores, fused with a
+// per-query running top-k so the [m x N] score matrix never leaves the SM.
+//
+//   * one CTA per SM, persistent over work units (row range s, query block mb);
+//   * the 128-query A block (128 x dim bf16 <= 96 KB) is loaded ONCE per unit by TMA and
+//     stays resident in shared memory; only cache-row tiles (256 rows x 64 k, 32 KB) stream
+//     through a 4-stage TMA/mbarrier ring;
+//   * a single elected thread issues tcgen05.mma (M=128, N=256, K=16, bf16 -> fp32) into one
+//     of two 256-column TMEM accumulators, so the epilogue of tile t overlaps the MMAs of t+1;
+//   * four epilogue warps read their 32 TMEM lanes with tcgen05.ld (one lane = one query),
+//     reduce each 64-column chunk to its max and compare with the query's current k-th best
+//     (initialised to the hit floor thr-eps): only chunks that can still matter take the slow
+//     path (context / TTL mask from RowMeta, insertion into the top-k).
+//
+// Units are ordered row-range-major (u = s * mblocks + mb) and dealt round-robin, so at any
+// moment the resident CTAs sweep the SAME rows for different query blocks and the 32 re-reads
+// of each cache-row tile are served by L2, not HBM.
+#include <stdio.h>
+
+#include "qre_common.cuh"
+#include "qre_ptx.cuh"
+
+namespace qre {
+
+constexpr int kThreads = 192;                       // warps 0-3 epilogue, 4 TMA, 5 MMA
+constexpr int kABytesPerKB = kBM * kBK * 2;         // 16 KB
+constexpr int kBBytes = kBN * kBK * 2;              // 32 KB
+constexpr int kSmemA = kMaxKB * kABytesPerKB;       // 96 KB
+constexpr int kSmemB = kStages * kBBytes;           // 128 KB
+constexpr int kSmemBar = 256;
+constexpr int kSmemTotal = kSmemA + kSmemB + kSmemBar + 1024;   // + alignment slack
+constexpr uint32_t kTmemCols = 512;
+
+struct TopK {              // per-thread candidate list; lives in local memory (rare path only)
+  float v[kTopK];
+  uint32_t r[kTopK];
+};
+
+// Candidate path: mask (row bound, context, TTL — src/cache.py:274-276) then insert.
+// Returns the new k-th best.  Deliberately not inlined: the fast path must stay tiny.
+__device__ __noinline__ float consider(TopK* tk, float v, long long row, long long n_rows,
+                                       const RowMeta* __restrict__ meta, uint64_t myctx, long long now_us,
+                                       long long ttl_us) {
+  if (row >= n_rows) return tk->v[kTopK - 1];
+  const int4 raw = __ldg(reinterpret_cast<const int4*>(meta + row));
+  const uint64_t ctx = (static_cast<uint64_t>(static_cast<uint32_t>(raw.y)) << 32) | static_cast<uint32_t>(raw.x);
+  const long long ts = static_cast<long long>((static_cast<uint64_t>(static_cast<uint32_t>(raw.w)) << 32) |
+                                              static_cast<uint32_t>(raw.z));
+  if (ctx != myctx || (now_us - ts) > ttl_us) return tk->v[kTopK - 1];
+  int i = kTopK - 1;
+  while (i > 0 && v > tk->v[i - 1]) {      // strict: equal scores keep the earlier row first
+    tk->v[i] = tk->v[i - 1];
+    tk->r[i] = tk->r[i - 1];
+    --i;
+  }
+  tk->v[i] = v;
+  tk->r[i] = static_cast<uint32_t>(row);
+  return tk->v[kTopK - 1];
+}
+
+template <bool kDump>
+__global__ void __launch_bounds__(kThreads, 1)
+qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_e,
+                     const GemmArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kSmemA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA + kSmemB);
+  uint64_t* full = bars;                    // [kStages]  TMA -> MMA
+  uint64_t* empty = bars + kStages;         // [kStages]  MMA -> TMA
+  uint64_t* a_full = bars + 2 * kStages;    // TMA -> MMA (resident A block landed)
+  uint64_t* a_empty = a_full + 1;           // MMA -> TMA (all MMAs reading A retired)
+  uint64_t* t_full = a_full + 2;            // [2] MMA -> epilogue
+  uint64_t* t_empty = a_full + 4;           // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 6);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_e);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(a_full, 1);
+    mbar_init(a_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&t_full[i], 1);
+      mbar_init(&t_empty[i], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 5) {
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int U = a.splits * a.mblocks;
+  const long long T = a.tiles_n;
+
+  if (warp == 4) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0, a_iter = 0;
+      for (int u = blockIdx.x; u < U; u += gridDim.x) {
+        const int s = u / a.mblocks, mb = u - s * a.mblocks;
+        const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        mbar_wait(a_empty, (a_iter & 1) ^ 1);
+        mbar_arrive_expect_tx(a_full, static_cast<uint32_t>(a.num_kb) * kABytesPerKB);
+        for (int kb = 0; kb < a.num_kb; ++kb)
+          tma_load_2d(sA + kb * kABytesPerKB, &tmap_q, a_full, kb * kBK, mb * kBM);
+        ++a_iter;
+        for (int t = t0; t < t1; ++t) {
+          for (int kb = 0; kb < a.num_kb; ++kb) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full[stage], kBBytes);
+            tma_load_2d(sB + stage * kBBytes, &tmap_e, &full[stage], kb * kBK, t * kBN);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ================= MMA issuer (one thread) =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, kBN);
+      uint32_t stage = 0, phase = 0, a_iter = 0, tile_iter = 0;
+      const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+      for (int u = blockIdx.x; u < U; u += gridDim.x) {
+        const int s = u / a.mblocks;
+        const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        mbar_wait(a_full, a_iter & 1);
+        for (int t = t0; t < t1; ++t) {
+          const uint32_t acc = tile_iter & 1;
+          mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * kBN;
+          for (int kb = 0; kb < a.num_kb; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            const uint64_t adesc = umma_desc_sw128(sA_addr + kb * kABytesPerKB);
+            const uint64_t bdesc = umma_desc_sw128(sB_addr + stage * kBBytes);
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in (addr>>4)
+              umma_bf16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(&empty[stage]);          // stage free once these MMAs retire
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+          umma_commit(&t_full[acc]);             // accumulator complete -> epilogue
+          ++tile_iter;
+        }
+        umma_commit(a_empty);                    // resident A no longer read
+        ++a_iter;
+      }
+    }
+  } else {
+    // ================= epilogue: fused per-query top-k =================
+    uint32_t tile_iter = 0;
+    TopK tk;
+    for (int u = blockIdx.x; u < U; u += gridDim.x) {
+      const int s = u / a.mblocks, mb = u - s * a.mblocks;
+      const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+      const int q = mb * kBM + warp * 32 + lane;
+      const bool active = q < a.m;
+      const uint64_t myctx = active ? a.q_ctx[q] : 0ull;
+#pragma unroll
+      for (int i = 0; i < kTopK; ++i) { tk.v[i] = a.floor_v; tk.r[i] = kNoRow; }
+      float kth = active ? a.floor_v : __int_as_float(0x7f800000);
+      for (int t = t0; t < t1; ++t) {
+        const uint32_t acc = tile_iter & 1;
+        mbar_wait(&t_full[acc], (tile_iter >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + acc * kBN;
+        const long long row_base = static_cast<long long>(t) * kBN;
+#pragma unroll 1
+        for (int c = 0; c < kBN / 64; ++c) {
+          float v[64];
+          tmem_ld_32x32(taddr + c * 64, v);
+          tmem_ld_32x32(taddr + c * 64 + 32, v + 32);
+          tmem_ld_wait();
+          if (kDump) {
+            if (active && a.dump != nullptr) {
+#pragma unroll
+              for (int i = 0; i < 64; ++i) {
+                const long long row = row_base + c * 64 + i;
+                if (row >= a.dump_row0 && row < a.dump_row0 + a.dump_ld && row < a.n_rows)
+                  a.dump[static_cast<long long>(q) * a.dump_ld + (row - a.dump_row0)] = v[i];
+              }
+            }
+          }
+          float m0 = fmaxf(v[0], v[1]), m1 = fmaxf(v[2], v[3]), m2 = fmaxf(v[4], v[5]), m3 = fmaxf(v[6], v[7]);
+#pragma unroll
+          for (int i = 8; i < 64; i += 8) {
+            m0 = fmaxf(m0, fmaxf(v[i], v[i + 1]));
+            m1 = fmaxf(m1, fmaxf(v[i + 2], v[i + 3]));
+            m2 = fmaxf(m2, fmaxf(v[i + 4], v[i + 5]));
+            m3 = fmaxf(m3, fmaxf(v[i + 6], v[i + 7]));
+          }
+          const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+          if (mx > kth) {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) {
+              if (v[i] > kth)
+                kth = consider(&tk, v[i], row_base + c * 64 + i, a.n_rows, a.meta, myctx, a.now_us, a.ttl_us);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&t_empty[acc]);
+        ++tile_iter;
+      }
+      if (active) {
+        PartialEntry* out = a.partial + (static_cast<long long>(q) * a.splits + s) * kTopK;
+#pragma unroll
+        for (int i = 0; i < kTopK; ++i) out[i] = PartialEntry{tk.v[i], tk.r[i]};
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// Work decomposition: S row ranges per M-block so that S*mblocks is about `waves` full waves
+// of the SM count, with units of >= 16 tiles where the problem allows it.
+ScanGeometry plan_scan(int m, long long n_rows, int num_sms) {
+  ScanGeometry g;
+  g.mblocks = (m + kBM - 1) / kBM;
+  g.tiles_n = static_cast<int>((n_rows + kBN - 1) / kBN);
+  if (g.mblocks < 1) g.mblocks = 1;
+  if (g.tiles_n < 1) g.tiles_n = 1;
+  long long waves = (static_cast<long long>(g.tiles_n) * g.mblocks) / (16LL * num_sms);
+  if (waves < 1) waves = 1;
+  if (waves > 8) waves = 8;
+  long long S = (waves * num_sms + g.mblocks / 2) / g.mblocks;
+  if (S < 1) S = 1;
+  if (S > g.tiles_n) S = g.tiles_n;
+  g.splits = static_cast<int>(S);
+  const long long U = S * g.mblocks;
+  g.grid = static_cast<int>(U < num_sms ? U : num_sms);
+  return g;
+}
+
+// Per-device set-up (called by qre_cache_create with the device current): opt in to the
+// 225 KB dynamic shared memory the scan kernel needs.
+cudaError_t gemm_topk_init() {
+  cudaError_t e = cudaFuncSetAttribute(qre_gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kSmemTotal);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(qre_gemm_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              kSmemTotal);
+}
+
+int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+                     float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st) {
+  (void)dump_n;
+  const ScanGeometry g = plan_scan(m, n_rows, s.num_sms);
+  GemmArgs a;
+  a.m = m;
+  a.mblocks = g.mblocks;
+  a.tiles_n = g.tiles_n;
+  a.splits = g.splits;
+  a.num_kb = s.dim_pad / kBK;
+  a.n_rows = n_rows;
+  const double thr = p.similarity_threshold > 0.0 ? p.similarity_threshold : 0.0;
+  a.floor_v = static_cast<float>(thr) - kApproxEps;
+  a.now_us = p.now_us;
+  a.ttl_us = p.ttl_us;
+  a.q_ctx = q_ctx;
+  a.meta = s.meta;
+  a.partial = s.partial;
+  a.dump = dump;
+  a.dump_ld = dump_ld;
+  a.dump_row0 = dump_row0;
+  if (dump != nullptr) {
+    qre_gemm_topk_kernel<true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+  } else {
+    qre_gemm_topk_kernel<false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+  }
+  return 1;
+}
+
+}  // namespace qre

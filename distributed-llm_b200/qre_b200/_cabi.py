@@ -1,0 +1,280 @@
+"""ctypes binding of libqre_b200.so (include/qre_b200.h).
+
+This is the only place the Python host code touches native code.  There is no CPU fallback:
+if the library cannot be loaded, or no sm_100 GPU is present, constructing a `Shard` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+from typing import Optional
+
+import numpy as np
+
+TOPK = 8
+MAX_DEVICES = 32
+MAX_CENTROIDS = 256
+CTX_TOMBSTONE = 0xFFFFFFFFFFFFFFFF
+SCAN_TENSOR, SCAN_EXACT = 0, 1
+FLAG_ZERO_NORM, FLAG_OVERFLOW = 1, 2
+SEM_METHOD_NAMES = ("semantic", "semantic_fallback_irrelevant", "semantic_fallback_ambiguous")
+
+CAND_DTYPE = np.dtype([("sim", "<f4"), ("shard", "<u4"), ("slot", "<i8"), ("lru_seq", "<u8"),
+                       ("pred_conf", "<f8")])
+assert CAND_DTYPE.itemsize == 32
+
+EXPORTS = (
+    "qre_abi_version", "qre_last_error", "qre_device_count", "qre_cache_create", "qre_cache_destroy",
+    "qre_cache_info", "qre_cache_stream", "qre_cache_append", "qre_cache_append_dev", "qre_cache_update",
+    "qre_cache_tombstone", "qre_cache_clear", "qre_cache_read_rows", "qre_set_centroids",
+    "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
+    "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm",
+)
+
+
+class QreError(RuntimeError):
+    pass
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("similarity_threshold", C.c_double), ("now_us", C.c_int64), ("ttl_us", C.c_int64),
+        ("scan_mode", C.c_int32), ("do_route", C.c_int32), ("n_devices", C.c_int32),
+        ("token_threshold", C.c_int32), ("w_token", C.c_double), ("w_semantic", C.c_double),
+        ("w_heuristic", C.c_double), ("w_perf", C.c_double), ("sem_min_similarity", C.c_double),
+        ("sem_margin_threshold", C.c_double),
+    ]
+
+
+RESULT_FIELDS = ("hit_slot", "hit_sim", "hit_pred_dev", "hit_pred_conf", "hit_shard", "cand",
+                 "centroid_sim", "tok_dev", "tok_conf", "sem_dev", "sem_conf", "sem_method", "dev",
+                 "conf", "score", "flags")
+
+
+class Result(C.Structure):
+    _fields_ = [(f, C.c_void_p) for f in RESULT_FIELDS]
+
+
+def lib_path() -> str:
+    return os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib",
+                        "libqre_b200.so")
+
+
+_LIB = None
+
+
+def load() -> C.CDLL:
+    """Load the shared library (building nothing: see qre_b200.build / __graft_entry__.build)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = os.environ.get("QRE_B200_LIB", lib_path())
+    if not os.path.isfile(path):
+        raise QreError(f"{path} not found: build it with `python distributed-llm_b200/qre_b200/build.py` "
+                       "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.qre_last_error.restype = C.c_char_p
+    for name in EXPORTS:
+        getattr(lib, name)
+    _LIB = lib
+    return lib
+
+
+def _check(lib, rc: int) -> None:
+    if rc != 0:
+        raise QreError(f"libqre_b200 error {rc}: {lib.qre_last_error().decode()}")
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _arr(x, dtype, shape=None) -> np.ndarray:
+    a = np.ascontiguousarray(x, dtype=dtype)
+    if shape is not None and tuple(a.shape) != tuple(shape):
+        raise ValueError(f"expected shape {shape}, got {a.shape}")
+    return a
+
+
+@dataclass
+class RouteConfig:
+    """Knobs of one lookup+route pass; defaults = the reference's shipped configs
+    (query_router_engine.py:704-731)."""
+    similarity_threshold: float = 0.85
+    ttl_us: int = 3600 * 1_000_000
+    n_devices: int = 2
+    token_threshold: int = 1000
+    w_token: float = 0.25
+    w_semantic: float = 0.45
+    w_heuristic: float = 0.30
+    w_perf: float = 0.0
+    sem_min_similarity: float = 0.05
+    sem_margin_threshold: float = 0.03
+    scan_mode: int = SCAN_TENSOR
+
+    def to_c(self, now_us: int, do_route: bool) -> Params:
+        return Params(self.similarity_threshold, int(now_us), int(self.ttl_us), self.scan_mode,
+                      1 if do_route else 0, self.n_devices, self.token_threshold, self.w_token,
+                      self.w_semantic, self.w_heuristic, self.w_perf, self.sem_min_similarity,
+                      self.sem_margin_threshold)
+
+
+class Shard:
+    """One GPU's slice of the routing cache (a `qre_cache_t` handle)."""
+
+    def __init__(self, dim: int, capacity: int, max_batch: int = 4096, device: int = 0):
+        self.lib = load()
+        self.dim, self.capacity, self.max_batch, self.device = int(dim), int(capacity), int(max_batch), int(device)
+        h = C.c_void_p()
+        _check(self.lib, self.lib.qre_cache_create(C.c_int(device), C.c_int(dim), C.c_int64(capacity),
+                                                   C.c_int(max_batch), C.byref(h)))
+        self.h = h
+        self.n_centroids = 0
+
+    def close(self) -> None:
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.qre_cache_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- info ----
+    def info(self) -> dict:
+        cap, hwm, live = C.c_int64(), C.c_int64(), C.c_int64()
+        dim, mb, dev = C.c_int(), C.c_int(), C.c_int()
+        _check(self.lib, self.lib.qre_cache_info(self.h, C.byref(cap), C.byref(hwm), C.byref(live),
+                                                 C.byref(dim), C.byref(mb), C.byref(dev)))
+        return dict(capacity=cap.value, high_water=hwm.value, live=live.value, dim=dim.value,
+                    max_batch=mb.value, device=dev.value)
+
+    @property
+    def stream(self) -> int:
+        s = C.c_void_p()
+        _check(self.lib, self.lib.qre_cache_stream(self.h, C.byref(s)))
+        return s.value or 0
+
+    def launch_count(self) -> int:
+        n = C.c_int64()
+        _check(self.lib, self.lib.qre_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    # ---- rows ----
+    def append(self, rows, ctx, ts_us, lru_seq, pred_dev, pred_conf) -> np.ndarray:
+        rows = _arr(rows, np.float32)
+        n = rows.shape[0]
+        if rows.ndim != 2 or rows.shape[1] != self.dim:
+            raise ValueError(f"rows must be [n, {self.dim}]")
+        ctx, ts_us = _arr(ctx, np.uint64, (n,)), _arr(ts_us, np.int64, (n,))
+        lru_seq, pred_dev = _arr(lru_seq, np.uint64, (n,)), _arr(pred_dev, np.uint8, (n,))
+        pred_conf = _arr(pred_conf, np.float64, (n,))
+        slots = np.empty(n, np.int64)
+        _check(self.lib, self.lib.qre_cache_append(self.h, C.c_int64(n), _ptr(rows), _ptr(ctx), _ptr(ts_us),
+                                                   _ptr(lru_seq), _ptr(pred_dev), _ptr(pred_conf), _ptr(slots)))
+        return slots
+
+    def append_dev(self, n, rows_ptr, ctx_ptr, ts_ptr, lru_ptr, pdev_ptr, pconf_ptr, stream=0) -> np.ndarray:
+        slots = np.empty(n, np.int64)
+        _check(self.lib, self.lib.qre_cache_append_dev(
+            self.h, C.c_int64(n), C.c_void_p(rows_ptr), C.c_void_p(ctx_ptr), C.c_void_p(ts_ptr),
+            C.c_void_p(lru_ptr), C.c_void_p(pdev_ptr), C.c_void_p(pconf_ptr), _ptr(slots), C.c_void_p(stream)))
+        return slots
+
+    def update(self, slots, rows=None, ctx=None, ts_us=None, lru_seq=None, pred_dev=None, pred_conf=None):
+        slots = _arr(slots, np.int64)
+        n = slots.shape[0]
+        rows = None if rows is None else _arr(rows, np.float32, (n, self.dim))
+        ctx = None if ctx is None else _arr(ctx, np.uint64, (n,))
+        ts_us = None if ts_us is None else _arr(ts_us, np.int64, (n,))
+        lru_seq = None if lru_seq is None else _arr(lru_seq, np.uint64, (n,))
+        pred_dev = None if pred_dev is None else _arr(pred_dev, np.uint8, (n,))
+        pred_conf = None if pred_conf is None else _arr(pred_conf, np.float64, (n,))
+        _check(self.lib, self.lib.qre_cache_update(self.h, C.c_int64(n), _ptr(slots), _ptr(rows), _ptr(ctx),
+                                                   _ptr(ts_us), _ptr(lru_seq), _ptr(pred_dev), _ptr(pred_conf)))
+
+    def tombstone(self, slots) -> None:
+        slots = _arr(slots, np.int64)
+        _check(self.lib, self.lib.qre_cache_tombstone(self.h, C.c_int64(slots.shape[0]), _ptr(slots)))
+
+    def clear(self) -> None:
+        _check(self.lib, self.lib.qre_cache_clear(self.h))
+
+    def read_rows(self, slots) -> np.ndarray:
+        slots = _arr(slots, np.int64)
+        out = np.empty((slots.shape[0], self.dim), np.float32)
+        _check(self.lib, self.lib.qre_cache_read_rows(self.h, C.c_int64(slots.shape[0]), _ptr(slots), _ptr(out)))
+        return out
+
+    # ---- router state ----
+    def set_centroids(self, centroids, owner) -> None:
+        c = _arr(centroids, np.float32)
+        if c.ndim != 2 or c.shape[1] != self.dim:
+            raise ValueError(f"centroids must be [K, {self.dim}]")
+        o = _arr(owner, np.uint8, (c.shape[0],))
+        _check(self.lib, self.lib.qre_set_centroids(self.h, C.c_int(c.shape[0]), _ptr(c), _ptr(o)))
+        self.n_centroids = c.shape[0]
+
+    def set_perf_health(self, health) -> None:
+        hlt = _arr(health, np.float64)
+        _check(self.lib, self.lib.qre_set_perf_health(self.h, C.c_int(hlt.shape[0]), _ptr(hlt)))
+
+    # ---- the hot path, host buffers ----
+    def lookup_route(self, queries, q_ctx, cfg: RouteConfig, now_us: int, tok=None, heur_dev=None,
+                     heur_conf=None, want_cand: bool = False) -> dict:
+        q = _arr(queries, np.float32)
+        m = q.shape[0]
+        if q.ndim != 2 or q.shape[1] != self.dim:
+            raise ValueError(f"queries must be [m, {self.dim}]")
+        q_ctx = _arr(q_ctx, np.uint64, (m,))
+        do_route = tok is not None
+        D, K = cfg.n_devices, self.n_centroids
+        out = dict(hit_slot=np.empty(m, np.int64), hit_sim=np.empty(m, np.float32),
+                   hit_pred_dev=np.empty(m, np.uint8), hit_pred_conf=np.empty(m, np.float64),
+                   hit_shard=np.empty(m, np.uint32), flags=np.empty(m, np.uint8))
+        if want_cand:
+            out["cand"] = np.empty((m, TOPK), CAND_DTYPE)
+        if do_route:
+            tok = _arr(tok, np.int32, (m,))
+            heur_dev = _arr(heur_dev, np.uint8, (m,))
+            heur_conf = _arr(heur_conf, np.float64, (m,))
+            out.update(centroid_sim=np.empty((m, K), np.float32), tok_dev=np.empty(m, np.uint8),
+                       tok_conf=np.empty(m, np.float64), sem_dev=np.empty(m, np.uint8),
+                       sem_conf=np.empty(m, np.float64), sem_method=np.empty(m, np.uint8),
+                       dev=np.empty(m, np.uint8), conf=np.empty(m, np.float64),
+                       score=np.empty((m, D), np.float64))
+        res = Result(**{f: _ptr(out.get(f)) for f in RESULT_FIELDS})
+        p = cfg.to_c(now_us, do_route)
+        _check(self.lib, self.lib.qre_lookup_route(self.h, C.c_int(m), _ptr(q), _ptr(q_ctx), _ptr(tok),
+                                                   _ptr(heur_dev), _ptr(heur_conf), C.byref(p), C.byref(res)))
+        return out
+
+    # ---- the hot path, device pointers (integers from torch .data_ptr()) ----
+    def scan_dev(self, m, q_ptr, q_ctx_ptr, cfg: RouteConfig, now_us, shard, cand_ptr, ovf_ptr=0, stream=0):
+        p = cfg.to_c(now_us, False)
+        _check(self.lib, self.lib.qre_scan_dev(self.h, C.c_int(m), C.c_void_p(q_ptr), C.c_void_p(q_ctx_ptr),
+                                               C.byref(p), C.c_int(shard), C.c_void_p(cand_ptr),
+                                               C.c_void_p(ovf_ptr), C.c_void_p(stream)))
+
+    def resolve_overflow_dev(self, m, cfg: RouteConfig, now_us, shard, cand_ptr, stream=0):
+        p = cfg.to_c(now_us, False)
+        _check(self.lib, self.lib.qre_resolve_overflow_dev(self.h, C.c_int(m), C.byref(p), C.c_int(shard),
+                                                           C.c_void_p(cand_ptr), C.c_void_p(stream)))
+
+    def merge_route_dev(self, m, n_shards, cand_all_ptr, cfg: RouteConfig, now_us, out_ptrs: dict,
+                        tok_ptr=0, heur_dev_ptr=0, heur_conf_ptr=0, stream=0):
+        do_route = bool(tok_ptr)
+        p = cfg.to_c(now_us, do_route)
+        res = Result(**{f: C.c_void_p(out_ptrs.get(f, 0) or None) for f in RESULT_FIELDS})
+        _check(self.lib, self.lib.qre_merge_route_dev(
+            self.h, C.c_int(m), C.c_int(n_shards), C.c_void_p(cand_all_ptr), C.c_void_p(tok_ptr or None),
+            C.c_void_p(heur_dev_ptr or None), C.c_void_p(heur_conf_ptr or None), C.byref(p), C.byref(res),
+            C.c_void_p(stream)))
+
+    def debug_gemm(self, m: int, row0: int, n: int) -> np.ndarray:
+        out = np.empty((m, n), np.float32)
+        _check(self.lib, self.lib.qre_debug_gemm(self.h, C.c_int(m), C.c_int64(row0), C.c_int(n), _ptr(out)))
+        return out

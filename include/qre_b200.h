@@ -1,0 +1,192 @@
+/* qre_b200.h — C ABI of libqre_b200.so: the B200 (sm_100a) routing-cache hot path.
+ *
+ * The reference (clumpygum/distributed-llm) has no FFI: its boundary for this path is the
+ * Python class API (`QueryCache` in src/cache.py, `SemanticRouter` / `HybridRouter` /
+ * `QueryRouter` in src/query_router_engine.py).  Each entry point below names the reference
+ * code it replaces (file:line relative to /root/reference/).  The Python mirror in
+ * `distributed-llm_b200/` binds these with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions: plain pointers and sizes only; every function returns an int status
+ * (QRE_OK = 0); no exceptions cross the ABI; `qre_last_error()` gives the message of the
+ * calling thread's last failure.  Functions without the `_dev` suffix take HOST buffers and
+ * are synchronous (copies in, kernels, copies out).  `_dev` functions take DEVICE pointers
+ * (on the handle's GPU), enqueue on `stream` (NULL = the handle's own stream) and return
+ * without synchronising.  A handle is not thread-safe: serialise calls per handle (the
+ * reference holds one RLock around its store, src/cache.py:225).
+ *
+ * There is no CPU fallback: `qre_cache_create` fails with QRE_ERR_NO_DEVICE when no sm_100
+ * GPU is present.
+ */
+#ifndef QRE_B200_H
+#define QRE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QRE_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define QRE_API __attribute__((visibility("default")))
+#else
+#define QRE_API
+#endif
+
+enum {
+  QRE_OK = 0,
+  QRE_ERR_INVALID = 1,     /* bad argument */
+  QRE_ERR_CUDA = 2,        /* a CUDA call failed; see qre_last_error() */
+  QRE_ERR_CAPACITY = 3,    /* cache full / batch larger than max_batch */
+  QRE_ERR_NO_DEVICE = 4,   /* no usable sm_100 device */
+  QRE_ERR_OVERFLOW = 5     /* candidate window overflow could not be resolved */
+};
+
+#define QRE_TOPK 8                 /* candidates kept per query (per shard) */
+#define QRE_MAX_DEVICES 32         /* D: routing targets */
+#define QRE_MAX_CENTROIDS 256      /* K: topic centroids */
+#define QRE_CTX_TOMBSTONE 0xFFFFFFFFFFFFFFFFull
+
+/* scan_mode */
+#define QRE_SCAN_TENSOR 0          /* tcgen05 bf16 GEMM + fused top-k, exact fp32 re-score */
+#define QRE_SCAN_EXACT  1          /* brute-force fp32 scan (fallback / cross-check) */
+
+/* semantic method codes (src/query_router_engine.py:190,201,210) */
+#define QRE_SEM_SEMANTIC   0
+#define QRE_SEM_IRRELEVANT 1
+#define QRE_SEM_AMBIGUOUS  2
+
+/* result flags (per query) */
+#define QRE_FLAG_ZERO_NORM   1     /* ||q|| < 1e-9: lookup returns miss (src/cache.py:284) */
+#define QRE_FLAG_OVERFLOW    2     /* candidate window overflowed; resolved by the exact scan */
+
+typedef struct qre_cache qre_cache_t;
+
+/* One exactly re-scored candidate; also the unit of the multi-GPU all-gather (32 bytes). */
+typedef struct {
+  float    sim;        /* fl32(sdot32(q,e) / fl32(|q|*|e|))  — src/cache.py:291 */
+  uint32_t shard;      /* rank that owns the row */
+  int64_t  slot;       /* row slot within that shard; -1 = empty */
+  uint64_t lru_seq;    /* OrderedDict position: smaller = earlier (tie-break, src/cache.py:292) */
+  double   pred_conf;  /* stored predict_device() confidence — src/cache.py:106-140 */
+} qre_candidate_t;
+/* pred_dev travels in the top byte of `shard` (shard = rank | pred_dev << 24). */
+
+/* Parameters of one lookup+route pass.  Defaults in comments = the shipped configs
+ * (src/query_router_engine.py:704-731). */
+typedef struct {
+  double  similarity_threshold;     /* 0.85  — src/cache.py:214, compared in double (cache.py:292) */
+  int64_t now_us;                   /* one `now` per batch, microseconds (src/cache.py:524) */
+  int64_t ttl_us;                   /* ttl_seconds * 1e6 */
+  int32_t scan_mode;                /* QRE_SCAN_* */
+  int32_t do_route;                 /* 0 = lookup only (QueryCache.lookup), 1 = also route */
+  int32_t n_devices;                /* D; reference = 2 (0 = nano, 1 = orin) */
+  int32_t token_threshold;          /* 1000 — qre:87 */
+  double  w_token, w_semantic, w_heuristic;  /* 0.25 / 0.45 / 0.30 — qre:539,715 */
+  double  w_perf;                   /* 0 in the reference; added term w_perf * H[dev] */
+  double  sem_min_similarity;       /* 0.05 — qre:129 */
+  double  sem_margin_threshold;     /* 0.03 — qre:128 */
+} qre_params_t;
+
+/* Per-query outputs, struct-of-arrays.  Any pointer may be NULL (not wanted).
+ * Host pointers for qre_lookup_route, device pointers for the _dev functions. */
+typedef struct {
+  int64_t* hit_slot;        /* [m]      -1 = miss           — src/cache.py:293-296 */
+  float*   hit_sim;         /* [m]      0 on a miss */
+  uint8_t* hit_pred_dev;    /* [m]      stored prediction of the hit row — cache.py:311 */
+  double*  hit_pred_conf;   /* [m] */
+  uint32_t* hit_shard;      /* [m]      owning rank of the hit row */
+  qre_candidate_t* cand;    /* [m, QRE_TOPK] merged candidates, best first */
+  float*   centroid_sim;    /* [m, K]   qre:133-138 */
+  uint8_t* tok_dev;         /* [m]      qre:98 */
+  double*  tok_conf;        /* [m]      qre:99 */
+  uint8_t* sem_dev;         /* [m]      qre:180-213 */
+  double*  sem_conf;        /* [m] */
+  uint8_t* sem_method;      /* [m]      QRE_SEM_* */
+  uint8_t* dev;             /* [m]      hybrid winner — qre:401-404 */
+  double*  conf;            /* [m]      qre:406-407 */
+  double*  score;           /* [m, D]   S[dev] — qre:389-398 */
+  uint8_t* flags;           /* [m]      QRE_FLAG_* */
+} qre_result_t;
+
+/* ---- library ------------------------------------------------------------------------- */
+QRE_API int qre_abi_version(void);
+QRE_API const char* qre_last_error(void);
+QRE_API int qre_device_count(int* count);
+
+/* ---- cache object: replaces QueryCache's store (src/cache.py:224) ---------------------
+ * dim: embedding dimension (multiple of 8); capacity: max rows on this GPU (QueryCache
+ * max_size / number of shards, src/cache.py:212); max_batch: largest m a lookup may pass. */
+QRE_API int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_cache_t** out);
+QRE_API int qre_cache_destroy(qre_cache_t* h);
+QRE_API int qre_cache_info(const qre_cache_t* h, int64_t* capacity, int64_t* high_water, int64_t* live,
+                   int* dim, int* max_batch, int* device);
+/* The handle's CUDA stream (a cudaStream_t) for interop. */
+QRE_API int qre_cache_stream(const qre_cache_t* h, void** stream);
+
+/* Insert n new rows (QueryCache.insert new-hash branch, src/cache.py:356-370): copies the
+ * fp32 rows, stores |e|, the L2-normalised bf16 copy and the row metadata; returns the
+ * slots chosen (tombstoned slots are reused first). */
+QRE_API int qre_cache_append(qre_cache_t* h, int64_t n, const float* rows, const uint64_t* ctx,
+                     const int64_t* ts_us, const uint64_t* lru_seq, const uint8_t* pred_dev,
+                     const double* pred_conf, int64_t* slot_out);
+QRE_API int qre_cache_append_dev(qre_cache_t* h, int64_t n, const float* rows, const uint64_t* ctx,
+                         const int64_t* ts_us, const uint64_t* lru_seq, const uint8_t* pred_dev,
+                         const double* pred_conf, int64_t* slot_out_host, void* stream);
+/* Refresh-in-place (src/cache.py:345-354) and LRU promotion (cache.py:261,303): overwrite
+ * row data and/or metadata of existing slots.  NULL arrays are left unchanged. */
+QRE_API int qre_cache_update(qre_cache_t* h, int64_t n, const int64_t* slot, const float* rows,
+                     const uint64_t* ctx, const int64_t* ts_us, const uint64_t* lru_seq,
+                     const uint8_t* pred_dev, const double* pred_conf);
+/* Delete rows (src/cache.py:526-530 _delete_entry; eviction cache.py:532-554). */
+QRE_API int qre_cache_tombstone(qre_cache_t* h, int64_t n, const int64_t* slot);
+QRE_API int qre_cache_clear(qre_cache_t* h);                          /* src/cache.py:502-512 */
+/* Read back fp32 rows (for QueryCache.save, src/cache.py:426-432). */
+QRE_API int qre_cache_read_rows(qre_cache_t* h, int64_t n, const int64_t* slot, float* rows_out);
+
+/* ---- router state: replaces SemanticRouter centroids (qre:131,140-178) ---------------- */
+QRE_API int qre_set_centroids(qre_cache_t* h, int n_centroids, const float* centroids,
+                      const uint8_t* owner_device);
+QRE_API int qre_set_perf_health(qre_cache_t* h, int n_devices, const double* health);
+
+/* ---- the hot path ---------------------------------------------------------------------
+ * QueryCache.lookup semantic scan (src/cache.py:267-305) for m queries against one snapshot
+ * of the cache, fused with SemanticRouter.route (qre:180-213), TokenBasedRouter.route
+ * (qre:98-99) and HybridRouter.route (qre:382-414).  `tok`, `heur_dev`, `heur_conf` are the
+ * host-computed per-query features (token count; HeuristicRouter result, qre:323-364); they
+ * may be NULL when params->do_route == 0.  shard/n_shards describe this handle's place in a
+ * row-sharded cache (0/1 for a single GPU). */
+QRE_API int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
+                     const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
+                     const qre_params_t* params, qre_result_t* out);
+
+/* Device-pointer pipeline, one stage per call (all enqueue on `stream`):
+ *   qre_scan_dev   : queries -> this shard's exactly re-scored candidates cand[m, QRE_TOPK]
+ *   (multi-GPU: all-gather cand over NCCL, e.g. torch.distributed.all_gather_into_tensor)
+ *   qre_merge_route_dev : n_shards candidate lists -> hit decision + routing outputs.
+ * qre_scan_dev also writes *overflow_count (device int32): number of queries whose candidate
+ * window overflowed and were NOT resolved on the device; if it is non-zero the caller must
+ * call qre_resolve_overflow_dev before merging. */
+QRE_API int qre_scan_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
+                 const qre_params_t* params, int shard, qre_candidate_t* cand_out,
+                 int32_t* overflow_count, void* stream);
+QRE_API int qre_resolve_overflow_dev(qre_cache_t* h, int m, const qre_params_t* params, int shard,
+                             qre_candidate_t* cand_inout, void* stream);
+QRE_API int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_candidate_t* cand_all,
+                        const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
+                        const qre_params_t* params, qre_result_t* out_dev, void* stream);
+
+/* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
+QRE_API int qre_launch_count(const qre_cache_t* h, int64_t* count);
+
+/* ---- bring-up / test hooks ------------------------------------------------------------
+ * Raw bf16 tensor-core product of the resident queries (from the last scan) with cache rows
+ * [row0, row0+n): out[m, n] fp32, host buffer.  Used by tests to check the tcgen05/TMA
+ * descriptors independently of the top-k logic. */
+QRE_API int qre_debug_gemm(qre_cache_t* h, int m, int64_t row0, int n, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QRE_B200_H */

@@ -1,0 +1,50 @@
+"""CPU-only checks of the drop-in boundary: the shared library loads without a GPU driver and
+exports every symbol include/qre_b200.h declares; with no device the product fails loudly."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from qre_b200 import _cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "qre_b200.h")).read()
+    return sorted(set(re.findall(r"QRE_API\s+(?:const\s+char\s*\*|int)\s+(qre_\w+)\s*\(", text)))
+
+
+def test_header_symbols_all_exported():
+    lib = _cabi.load()
+    names = _declared()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), n
+    assert sorted(_cabi.EXPORTS) == names
+    assert lib.qre_abi_version() == 1
+
+
+def test_struct_layout_matches_header():
+    assert _cabi.CAND_DTYPE.itemsize == 32
+    assert ctypes.sizeof(_cabi.Params) == 8 * 3 + 4 * 4 + 8 * 6
+    assert ctypes.sizeof(_cabi.Result) == 8 * len(_cabi.RESULT_FIELDS)
+
+
+def test_no_device_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(_cabi.QreError, match="no CUDA device|CPU fallback|cudaGetDeviceCount"):
+        _cabi.Shard(dim=384, capacity=1024, max_batch=8)
+
+
+def test_bad_arguments_rejected_before_any_cuda_call():
+    lib = _cabi.load()
+    h = ctypes.c_void_p()
+    assert lib.qre_cache_create(0, 100, ctypes.c_int64(10), 4, ctypes.byref(h)) == 1   # dim % 8
+    assert b"multiple of 8" in lib.qre_last_error()
+    assert lib.qre_cache_create(0, 384, ctypes.c_int64(0), 4, ctypes.byref(h)) == 1
+    assert lib.qre_cache_destroy(None) == 0

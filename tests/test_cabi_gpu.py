@@ -1,0 +1,223 @@
+"""GPU parity of the C-ABI hot path against the CPU oracle (seeded inputs, oracle-sized)."""
+import numpy as np
+import pytest
+
+from oracle import qre_oracle as O
+from qre_b200 import _cabi, synth
+
+pytestmark = pytest.mark.gpu
+REL = 1e-5          # north_star: scores within 1e-5 relative
+
+
+def _load(w, max_batch=None, n_rows=None):
+    n = w.rows.shape[0] if n_rows is None else n_rows
+    sh = _cabi.Shard(dim=w.rows.shape[1], capacity=n + 64, max_batch=max_batch or w.queries.shape[0])
+    slots = sh.append(w.rows[:n], w.row_ctx[:n], w.row_ts_us[:n], w.row_lru[:n], w.row_pred_dev[:n],
+                      w.row_pred_conf[:n])
+    assert np.array_equal(slots, np.arange(n))
+    sh.set_centroids(w.centroids, w.owner)
+    sh.set_perf_health(w.perf_health)
+    return sh
+
+
+def _oracle_scan(w, thr=0.85, n_rows=None):
+    n = w.rows.shape[0] if n_rows is None else n_rows
+    img = O.CacheImage(w.rows[:n], w.row_ctx[:n], w.row_ts_us[:n], w.row_lru[:n])
+    return O.scan_batch(w.queries, w.q_ctx, img, w.now_us, w.ttl_us, thr)
+
+
+def _check_lookup(out, exp_row, exp_sim):
+    got = out["hit_slot"]
+    bad = np.nonzero(got != exp_row)[0]
+    assert bad.size == 0, (bad[:10], got[bad[:10]], exp_row[bad[:10]])
+    hit = exp_row >= 0
+    np.testing.assert_allclose(out["hit_sim"][hit], exp_sim[hit], rtol=REL)
+    assert np.all(out["hit_sim"][~hit] == 0)
+
+
+@pytest.fixture(scope="module")
+def small():
+    return synth.make_workload(6000, 300, 384, n_centroids=8, seed=3, frac_near=0.08, frac_dup=0.03)
+
+
+def test_exact_scan_matches_oracle(small):
+    w = small
+    sh = _load(w)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us, scan_mode=_cabi.SCAN_EXACT)
+    out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us)
+    exp_row, exp_sim = _oracle_scan(w)
+    _check_lookup(out, exp_row, exp_sim)
+    assert (exp_row >= 0).sum() > 100 and (exp_row < 0).sum() > 100
+    hit = exp_row >= 0
+    assert np.array_equal(out["hit_pred_dev"][hit], w.row_pred_dev[exp_row[hit]])
+    assert np.array_equal(out["hit_pred_conf"][hit], w.row_pred_conf[exp_row[hit]])
+    zero = ~np.any(w.queries != 0, axis=1)
+    assert np.all(out["flags"][zero] & _cabi.FLAG_ZERO_NORM) and np.all(out["hit_slot"][zero] == -1)
+    sh.close()
+
+
+def test_tensor_gemm_raw_products(small):
+    """tcgen05/TMA descriptor check: raw bf16 products against a CPU bf16 emulation."""
+    import torch
+    w = small
+    sh = _load(w)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us)
+    m, n = w.queries.shape[0], 1500
+    for row0 in (0, 4400):
+        got = sh.debug_gemm(m, row0, n)
+        qn = torch.from_numpy(w.queries / np.maximum(np.linalg.norm(w.queries, axis=1, keepdims=True), 1e-30))
+        en = torch.from_numpy(w.rows[row0:row0 + n] /
+                              np.maximum(np.linalg.norm(w.rows[row0:row0 + n], axis=1, keepdims=True), 1e-30))
+        ref = (qn.bfloat16().float() @ en.bfloat16().float().T).numpy()
+        # 1-ulp differences in the fp32 normalisation can flip a bf16 rounding: allow 2 bf16 ulps of slack
+        np.testing.assert_allclose(got, ref, atol=3e-4, rtol=0)
+        true = (qn.double() @ en.double().T).numpy()
+        assert np.abs(got - true).max() < 2e-3        # well inside the eps the candidate window assumes
+    sh.close()
+
+
+def test_tensor_scan_matches_oracle(small):
+    w = small
+    sh = _load(w)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us, want_cand=True)
+    exp_row, exp_sim = _oracle_scan(w)
+    _check_lookup(out, exp_row, exp_sim)
+    cfg_e = _cabi.RouteConfig(ttl_us=w.ttl_us, scan_mode=_cabi.SCAN_EXACT)
+    out_e = sh.lookup_route(w.queries, w.q_ctx, cfg_e, w.now_us)
+    assert np.array_equal(out["hit_slot"], out_e["hit_slot"])
+    assert np.array_equal(out["hit_sim"], out_e["hit_sim"])          # same summation order: bit-equal
+    assert np.array_equal(out["cand"]["slot"][:, 0], out["hit_slot"])
+    sh.close()
+
+
+@pytest.mark.parametrize("m", [1, 7, 64, 129])
+def test_tensor_scan_ragged_batches(small, m):
+    w = small
+    sh = _load(w, max_batch=256)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    out = sh.lookup_route(w.queries[:m], w.q_ctx[:m], cfg, w.now_us)
+    exp_row, exp_sim = _oracle_scan(w)
+    _check_lookup(out, exp_row[:m], exp_sim[:m])
+    sh.close()
+
+
+def test_route_matches_oracle(small):
+    w = small
+    sh = _load(w)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us, tok=w.tok, heur_dev=w.heur_dev,
+                          heur_conf=w.heur_conf)
+    p = O.RouteParams()
+    r = O.route_batch(w.queries, w.tok, w.heur_dev, w.heur_conf, w.centroids, w.owner, p)
+    np.testing.assert_allclose(out["centroid_sim"], r["sims"], rtol=REL, atol=1e-7)
+    assert np.array_equal(out["tok_dev"], r["tok_dev"]) and np.array_equal(out["tok_conf"], r["tok_conf"])
+    # a decision may legitimately differ only where a margin sits within fp32 summation noise of a rule
+    sims = np.sort(r["sims"].astype(np.float64).reshape(len(w.tok), -1, 1).max(axis=2), axis=1)
+    dsim = np.full((len(w.tok), 2), -np.inf)
+    for k in range(w.centroids.shape[0]):
+        dsim[:, w.owner[k]] = np.maximum(dsim[:, w.owner[k]], r["sims"][:, k])
+    margin = np.abs(dsim[:, 1] - dsim[:, 0])
+    band = (np.abs(margin - 0.03) < 2e-6) | (np.abs(dsim.max(1) - 0.05) < 2e-6) | (margin < 2e-6)
+    assert band.sum() <= 3
+    ok = ~band
+    assert np.array_equal(out["sem_method"][ok], r["sem_method"][ok])
+    assert np.array_equal(out["sem_dev"][ok], r["sem_dev"][ok])
+    assert np.array_equal(out["dev"][ok], r["dev"][ok])
+    np.testing.assert_allclose(out["sem_conf"][ok], r["sem_conf"][ok], rtol=REL, atol=2e-6)
+    np.testing.assert_allclose(out["conf"][ok], r["conf"][ok], rtol=REL, atol=4e-6)
+    np.testing.assert_allclose(out["score"][ok], r["S"][ok], rtol=REL, atol=2e-6)
+    assert set(np.unique(r["sem_method"])) == {0, 1, 2}
+    del sims
+    sh.close()
+
+
+def test_update_tombstone_and_reuse(small):
+    w = small
+    n = 2000
+    sh = _load(w, n_rows=n)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    exp_row, _ = _oracle_scan(w, n_rows=n)
+    hits = np.nonzero(exp_row >= 0)[0]
+    assert hits.size > 20
+    victims = np.unique(exp_row[hits[:10]])
+    sh.tombstone(victims)
+    ctx2 = w.row_ctx[:n].copy(); ctx2[victims] = O.CTX_TOMBSTONE
+    img = O.CacheImage(w.rows[:n], ctx2, w.row_ts_us[:n], w.row_lru[:n])
+    exp2, sim2 = O.scan_batch(w.queries, w.q_ctx, img, w.now_us, w.ttl_us, 0.85)
+    out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us)
+    _check_lookup(out, exp2, sim2)
+    # freed slots are reused (LIFO) and the new rows are found
+    new_rows = w.rows[victims] * np.float32(0.5)
+    slots = sh.append(new_rows, w.row_ctx[victims], w.row_ts_us[victims], w.row_lru[victims],
+                      w.row_pred_dev[victims], w.row_pred_conf[victims])
+    assert sorted(slots.tolist()) == sorted(victims.tolist())
+    assert sh.info()["live"] == n
+    rows3 = w.rows[:n].copy(); rows3[slots] = new_rows
+    ctx3 = w.row_ctx[:n].copy(); ctx3[slots] = w.row_ctx[victims]
+    ts3 = w.row_ts_us[:n].copy(); ts3[slots] = w.row_ts_us[victims]
+    lru3 = w.row_lru[:n].copy(); lru3[slots] = w.row_lru[victims]
+    img3 = O.CacheImage(rows3, ctx3, ts3, lru3)
+    exp3, sim3 = O.scan_batch(w.queries, w.q_ctx, img3, w.now_us, w.ttl_us, 0.85)
+    out3 = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us)
+    _check_lookup(out3, exp3, sim3)
+    # LRU promotion of one of two identical rows flips the winner (cache.py:292,303)
+    np.testing.assert_array_equal(sh.read_rows(slots), new_rows)
+    sh.close()
+
+
+def test_lru_tie_break_and_ttl():
+    d = 384
+    rs = np.random.Generator(np.random.PCG64(9))
+    base = rs.standard_normal((4, d)).astype(np.float32)
+    rows = np.stack([base[0], base[0], base[1], base[2]])
+    ctx = np.array([5, 5, 5, 6], np.uint64)
+    ts = np.array([1000, 1000, 0, 1000], np.int64)
+    lru = np.array([20, 10, 30, 40], np.uint64)
+    sh = _cabi.Shard(dim=d, capacity=16, max_batch=8)
+    sh.append(rows, ctx, ts, lru, np.zeros(4, np.uint8), np.ones(4))
+    q = np.stack([base[0] * 3, base[1], base[2], base[2]])
+    qc = np.array([5, 5, 6, 5], np.uint64)
+    for mode in (_cabi.SCAN_TENSOR, _cabi.SCAN_EXACT):
+        cfg = _cabi.RouteConfig(ttl_us=500, scan_mode=mode)
+        out = sh.lookup_route(q, qc, cfg, now_us=1200)
+        # twin rows: smaller lru_seq wins; row 2 expired (age 1200 > 500); ctx mismatch misses
+        assert out["hit_slot"].tolist() == [1, -1, 3, -1], mode
+        sh.update(np.array([1]), lru_seq=np.array([50], np.uint64))       # move_to_end
+        out = sh.lookup_route(q, qc, cfg, now_us=1200)
+        assert out["hit_slot"].tolist() == [0, -1, 3, -1], mode
+        sh.update(np.array([1]), lru_seq=np.array([10], np.uint64))
+        out = sh.lookup_route(q, qc, cfg, now_us=1500)                    # age == ttl is still valid
+        assert out["hit_slot"].tolist() == [1, -1, 3, -1], mode
+        out = sh.lookup_route(q, qc, cfg, now_us=1501)
+        assert out["hit_slot"].tolist() == [-1, -1, -1, -1], mode
+    sh.close()
+
+
+def test_overflow_falls_back_to_exact_scan():
+    """More than QRE_TOPK near-identical contenders in one row range: the bf16 window cannot
+    separate them, the exact fp32 scan must settle it (and pick the LRU-earliest of the best)."""
+    d = 384
+    rs = np.random.Generator(np.random.PCG64(10))
+    e = rs.standard_normal(d).astype(np.float32)
+    n = 40
+    rows = np.stack([e * np.float32(1 + 0.01 * i) for i in range(n)])
+    noise = rs.standard_normal((n, d)).astype(np.float32) * np.float32(1e-4)
+    rows[5:] += noise[5:]
+    ctx = np.full(n, 7, np.uint64)
+    lru = np.arange(100, 100 + n, dtype=np.uint64)[::-1].copy()
+    sh = _cabi.Shard(dim=d, capacity=64, max_batch=8)
+    sh.append(rows, ctx, np.zeros(n, np.int64), lru, np.zeros(n, np.uint8), np.ones(n))
+    q = e[None, :].copy()
+    cfg = _cabi.RouteConfig(ttl_us=10**9)
+    out = sh.lookup_route(q, np.array([7], np.uint64), cfg, now_us=1)
+    img = O.CacheImage(rows, ctx, np.zeros(n, np.int64), lru)
+    exp_row, exp_sim = O.scan_batch(q, np.array([7], np.uint64), img, 1, 10**9, 0.85)
+    cfg_e = _cabi.RouteConfig(ttl_us=10**9, scan_mode=_cabi.SCAN_EXACT)
+    out_e = sh.lookup_route(q, np.array([7], np.uint64), cfg_e, now_us=1)
+    assert out["flags"][0] & _cabi.FLAG_OVERFLOW
+    assert out["hit_slot"][0] == out_e["hit_slot"][0]
+    assert out["hit_sim"][0] == out_e["hit_sim"][0]
+    np.testing.assert_allclose(out["hit_sim"][0], exp_sim[0], rtol=REL)
+    sh.close()
