@@ -1,0 +1,526 @@
+"""cache.py — drop-in for the reference's `src/cache.py` with the store on a B200.
+
+Same import surface (`from cache import CacheEntry, CacheLookupResult, QueryCache`,
+reference query_router_engine.py:26) and the same observable behaviour; what changes is
+where the work happens:
+
+  * the embeddings live in a device-resident matrix (fp32 master rows + L2-normalised bf16
+    rows, appended / refreshed / tombstoned in place) owned by `qre_b200.engine.Engine`;
+  * the semantic scan of reference cache.py:267-305 is one call into libqre_b200.so
+    (tcgen05 bf16 GEMM + fused top-k, exact fp32 re-score, see include/qre_b200.h);
+  * the host keeps what is string- or history-shaped: the md5 exact-match index
+    (cache.py:518-521), LRU order, TTL bookkeeping, routing history and its weighted vote
+    (cache.py:94-140), regex invalidation, JSON persistence and stats.
+
+Host-side complexity also drops: TTL expiry uses a heap instead of the reference's O(N) scan
+per lookup (cache.py:250, 532-538), with identical eviction counts.
+
+There is NO CPU fallback: without libqre_b200.so and an sm_100 GPU the first operation that
+needs the device raises `qre_b200._cabi.QreError`.
+"""
+from __future__ import annotations
+
+import hashlib
+import heapq
+import json
+import logging
+import re
+import threading
+from collections import OrderedDict
+from dataclasses import dataclass, field
+from datetime import datetime, timedelta
+from pathlib import Path
+from typing import Any, Dict, List, Optional, Tuple
+
+import numpy as np
+
+from qre_b200 import _cabi
+from qre_b200.engine import Engine
+
+logger = logging.getLogger(__name__)
+
+PREDICTION_CONFIDENCE_THRESHOLD = 0.60      # reference cache.py:42
+RECENCY_DECAY = 0.85                        # reference cache.py:46
+DEVICE_NAMES: List[str] = ["nano", "orin"]  # index = device id on the GPU side
+
+_EPOCH = datetime(1970, 1, 1)
+_ONE_US = timedelta(microseconds=1)
+
+
+def _to_us(t: datetime) -> int:
+    """Exact microseconds since the epoch (naive datetimes, like the reference's now())."""
+    return (t - _EPOCH) // _ONE_US
+
+
+def device_index(name: str) -> int:
+    """Anything that is not a known device counts as device 0, as the reference's vote treats
+    every non-"orin" record as "nano" (cache.py:124-127)."""
+    try:
+        return DEVICE_NAMES.index(name)
+    except ValueError:
+        return 0
+
+
+@dataclass
+class RoutingRecord:
+    """One routing decision remembered for a cached query (reference cache.py:53-76)."""
+    device: str
+    confidence: float
+    method: str
+    timestamp: str
+
+    def to_dict(self) -> Dict[str, Any]:
+        return dict(device=self.device, confidence=self.confidence, method=self.method,
+                    timestamp=self.timestamp)
+
+    @classmethod
+    def from_dict(cls, d: Dict[str, Any]) -> "RoutingRecord":
+        return cls(d["device"], float(d["confidence"]), d.get("method", "unknown"),
+                   d.get("timestamp", datetime.now().isoformat()))
+
+
+@dataclass
+class CacheEntry:
+    """Same fields as the reference (cache.py:79-92); `_slot`/`_seq`/`_ts_us` are the row's
+    place in the device matrix, its LRU sequence number and its timestamp in microseconds."""
+    query: str
+    query_hash: str
+    context_key: str
+    embedding: Optional[np.ndarray]
+    timestamp: datetime
+    device_used: str
+    response_time: Optional[float] = None
+    hit_count: int = 0
+    routing_history: List[RoutingRecord] = field(default_factory=list)
+    _slot: Optional[int] = field(default=None, repr=False, compare=False)
+    _seq: int = field(default=0, repr=False, compare=False)
+
+    MAX_HISTORY = 20
+
+    def record_routing(self, device: str, confidence: float, method: str) -> None:
+        self.routing_history.append(RoutingRecord(device, confidence, method, datetime.now().isoformat()))
+        del self.routing_history[:-self.MAX_HISTORY]
+        self.device_used = device
+
+    def predict_device(self) -> Tuple[str, float]:
+        """Recency-weighted vote (reference cache.py:106-140): newest record weighs
+        confidence, the i-th newest 0.85**i * confidence; the winner's share of the total is
+        the confidence; equal scores go to the HIGHER device index ("orin" >= "nano");
+        no history or ~zero weight -> (device_used, 0.5)."""
+        if not self.routing_history:
+            return self.device_used, 0.5
+        score = [0.0] * len(DEVICE_NAMES)
+        total = 0.0
+        for age, rec in enumerate(reversed(self.routing_history)):
+            w = (RECENCY_DECAY ** age) * rec.confidence
+            score[device_index(rec.device)] += w
+            total += w
+        if total < 1e-9:
+            return self.device_used, 0.5
+        best = 0
+        for d in range(1, len(score)):
+            if score[d] >= score[best]:
+                best = d
+        return DEVICE_NAMES[best], float(min(score[best] / total, 1.0))
+
+    def to_dict(self) -> Dict[str, Any]:
+        return {
+            "query": self.query, "query_hash": self.query_hash, "context_key": self.context_key,
+            "embedding": None if self.embedding is None else self.embedding.tolist(),
+            "timestamp": self.timestamp.isoformat(), "device_used": self.device_used,
+            "response_time": self.response_time, "hit_count": self.hit_count,
+            "routing_history": [r.to_dict() for r in self.routing_history],
+        }
+
+    @classmethod
+    def from_dict(cls, d: Dict[str, Any]) -> "CacheEntry":
+        emb = np.array(d["embedding"], dtype=np.float32) if d.get("embedding") else None
+        return cls(query=d["query"], query_hash=d["query_hash"], context_key=d["context_key"],
+                   embedding=emb, timestamp=datetime.fromisoformat(d["timestamp"]),
+                   device_used=d["device_used"], response_time=d.get("response_time"),
+                   hit_count=d.get("hit_count", 0),
+                   routing_history=[RoutingRecord.from_dict(r) for r in d.get("routing_history", [])])
+
+
+@dataclass
+class CacheLookupResult:
+    """What `lookup` returns on a hit (reference cache.py:179-192)."""
+    entry: CacheEntry
+    predicted_device: str
+    predicted_confidence: float
+    use_hybrid_fallback: bool
+
+
+class QueryCache:
+    """LRU + TTL routing cache with the semantic scan on the GPU.
+
+    Constructor and method signatures are the reference's (cache.py:210-217, 236, 328, 372,
+    398, 426, 434, 471, 502).  Keyword-only extras: `engine` (share a device store with the
+    router so lookup and routing fuse into one launch sequence), `device` (GPU index),
+    `max_batch` (largest `lookup_batch`)."""
+
+    def __init__(self, max_size: int = 100, ttl_seconds: int = 300, similarity_threshold: float = 0.85,
+                 use_semantic: bool = True,
+                 prediction_confidence_threshold: float = PREDICTION_CONFIDENCE_THRESHOLD, *,
+                 engine: Optional[Any] = None, device: int = 0, max_batch: int = 64):
+        self.max_size = max_size
+        self.ttl_seconds = ttl_seconds
+        self.similarity_threshold = similarity_threshold
+        self.use_semantic = use_semantic
+        self.prediction_confidence_threshold = prediction_confidence_threshold
+
+        self._store: "OrderedDict[str, CacheEntry]" = OrderedDict()
+        self._lock = threading.RLock()
+        self._engine = engine if engine is not None else Engine(capacity=max(max_size, 1), device=device,
+                                                                max_batch=max_batch)
+        self._slot_key: Dict[int, str] = {}          # device slot -> query_hash
+        self._ctx_ids: Dict[str, int] = {}           # context_key -> u64 id the device compares
+        self._seq = 0                                # LRU clock: larger = more recently used
+        self._exp_heap: List[Tuple[int, str]] = []   # (ts_us, hash), lazy deletion
+        self._stale_heap: List[Tuple[int, str, int]] = []   # (seq, hash, ts_us) of expired entries
+
+        self._hits = 0
+        self._attempts = 0
+        self._evictions = 0
+        self._hybrid_fallbacks = 0
+
+    # ------------------------------------------------------------------ helpers
+    @staticmethod
+    def _make_hash(query: str, context_key: str) -> str:
+        """md5 of "<ctx>||<query lowered and stripped>" (reference cache.py:518-521)."""
+        return hashlib.md5(f"{context_key}||{query.lower().strip()}".encode("utf-8")).hexdigest()
+
+    def _ttl_us(self) -> int:
+        return int(self.ttl_seconds * 1_000_000)
+
+    def _is_valid(self, entry: CacheEntry, now: Optional[datetime] = None) -> bool:
+        now = datetime.now() if now is None else now
+        return (now - entry.timestamp).total_seconds() <= self.ttl_seconds
+
+    def _ctx_id(self, context_key: str) -> int:
+        cid = self._ctx_ids.get(context_key)
+        if cid is None:
+            cid = len(self._ctx_ids) + 1             # never the tombstone value
+            self._ctx_ids[context_key] = cid
+        return cid
+
+    def _cfg(self) -> _cabi.RouteConfig:
+        return _cabi.RouteConfig(similarity_threshold=float(self.similarity_threshold), ttl_us=self._ttl_us())
+
+    def _touch(self, key: str, entry: CacheEntry) -> None:
+        """move_to_end + the matching lru_seq on the device row."""
+        self._store.move_to_end(key)
+        self._seq += 1
+        entry._seq = self._seq
+
+    def _stamp(self, key: str, entry: CacheEntry, now: datetime) -> None:
+        entry.timestamp = now
+        heapq.heappush(self._exp_heap, (_to_us(now), key))
+
+    def _delete_entry(self, key: str) -> None:
+        entry = self._store.pop(key, None)
+        if entry is None:
+            return
+        if entry._slot is not None:
+            self._slot_key.pop(entry._slot, None)
+            self._engine.tombstone([entry._slot])
+            entry._slot = None
+        entry.embedding = None
+
+    def _collect_stale(self, now_us: int) -> None:
+        limit = now_us - self._ttl_us()
+        while self._exp_heap and self._exp_heap[0][0] < limit:
+            ts, key = heapq.heappop(self._exp_heap)
+            e = self._store.get(key)
+            if e is not None and _to_us(e.timestamp) == ts:
+                heapq.heappush(self._stale_heap, (e._seq, key, ts))
+
+    def _pop_stale(self, now_us: int) -> Optional[str]:
+        """Earliest-in-LRU-order entry that is expired right now, or None."""
+        limit = now_us - self._ttl_us()
+        while self._stale_heap:
+            seq, key, ts = heapq.heappop(self._stale_heap)
+            e = self._store.get(key)
+            if e is not None and e._seq == seq and _to_us(e.timestamp) == ts and ts < limit:
+                return key
+        return None
+
+    def _evict_expired(self, now: Optional[datetime] = None) -> None:
+        """Drop every TTL-expired entry, counting each (reference cache.py:532-538)."""
+        with self._lock:
+            now_us = _to_us(datetime.now() if now is None else now)
+            self._collect_stale(now_us)
+            while True:
+                key = self._pop_stale(now_us)
+                if key is None:
+                    break
+                self._delete_entry(key)
+                self._evictions += 1
+
+    def _evict_one(self, now: datetime) -> None:
+        """At capacity: first expired entry in LRU order, else the LRU front
+        (reference cache.py:540-554)."""
+        now_us = _to_us(now)
+        self._collect_stale(now_us)
+        key = self._pop_stale(now_us)
+        if key is None and self._store:
+            key = next(iter(self._store))
+        if key is not None:
+            self._delete_entry(key)
+            self._evictions += 1
+
+    def _sync_row(self, entry: CacheEntry, row_changed: bool) -> None:
+        """Mirror an entry's scan-relevant state into its device row."""
+        if entry.embedding is None:
+            return
+        pdev, pconf = entry.predict_device()
+        ts_us = _to_us(entry.timestamp)
+        if entry._slot is None:
+            entry._slot = self._engine.append(entry.embedding, self._ctx_id(entry.context_key), ts_us,
+                                              entry._seq, device_index(pdev), pconf)
+            self._slot_key[entry._slot] = entry.query_hash
+        else:
+            self._engine.update(entry._slot, row=entry.embedding if row_changed else None, ts_us=ts_us,
+                                lru=entry._seq, pdev=device_index(pdev), pconf=pconf)
+
+    # ------------------------------------------------------------------ public API
+    def lookup(self, query: str, context_key: str,
+               q_emb: Optional[np.ndarray] = None) -> Optional[CacheLookupResult]:
+        """Exact-hash match first, then the semantic scan (reference cache.py:236-326).
+        Returns None on a miss."""
+        return self._lookup_and_route(query, context_key, q_emb, None)[0]
+
+    def _lookup_and_route(self, query: str, context_key: str, q_emb: Optional[np.ndarray],
+                          route_in: Optional[dict], route_cfg: Optional[_cabi.RouteConfig] = None):
+        """lookup() plus, when `route_in` is given, the routing epilogue in the same device
+        pass.  Returns (CacheLookupResult | None, device outputs | None)."""
+        with self._lock:
+            self._attempts += 1
+            now = datetime.now()
+            self._evict_expired(now)
+            key = self._make_hash(query, context_key)
+            entry: Optional[CacheEntry] = None
+            exact = self._store.get(key)
+            if exact is not None and exact.context_key == context_key:
+                if self._is_valid(exact, now):
+                    entry = exact
+                else:
+                    self._delete_entry(key)
+            want_scan = entry is None and self.use_semantic and q_emb is not None
+            dev_out = None
+            if q_emb is not None and (want_scan or route_in is not None):
+                cfg = route_cfg if route_cfg is not None else self._cfg()
+                cfg.similarity_threshold = float(self.similarity_threshold)
+                cfg.ttl_us = self._ttl_us()
+                dev_out = self._engine.scan(q_emb, np.array([self._ctx_id(context_key)], np.uint64),
+                                            _to_us(now), cfg, route_in)
+            if entry is None:
+                if not want_scan:
+                    return None, dev_out
+                slot = int(dev_out["hit_slot"][0])
+                if slot < 0:
+                    return None, dev_out
+                found = self._store.get(self._slot_key.get(slot, ""))
+                if found is None or not self._is_valid(found, now):
+                    return None, dev_out
+                entry, key = found, found.query_hash
+            entry.hit_count += 1
+            self._touch(key, entry)
+            if entry._slot is not None:
+                self._engine.update(entry._slot, lru=entry._seq)
+            self._hits += 1
+            pdev, pconf = entry.predict_device()
+            fallback = pconf < self.prediction_confidence_threshold
+            if fallback:
+                self._hybrid_fallbacks += 1
+                logger.debug("cache hit with weak prediction %.2f for %r", pconf, query[:60])
+            return CacheLookupResult(entry, pdev, pconf, fallback), dev_out
+
+    def lookup_batch(self, queries: List[str], context_keys: List[str],
+                     q_embs: np.ndarray) -> List[Optional[CacheLookupResult]]:
+        """Additive batch form: every query is scored against ONE snapshot of the cache (a
+        single device pass), then hits are applied in order.  Equals a loop of `lookup` unless
+        an earlier hit's LRU promotion would change a later tie-break."""
+        with self._lock:
+            now = datetime.now()
+            self._evict_expired(now)
+            q_embs = np.ascontiguousarray(q_embs, np.float32)
+            ctx = np.array([self._ctx_id(c) for c in context_keys], np.uint64)
+            out = self._engine.scan(q_embs, ctx, _to_us(now), self._cfg())
+            results: List[Optional[CacheLookupResult]] = []
+            for i, (q, c) in enumerate(zip(queries, context_keys)):
+                self._attempts += 1
+                key = self._make_hash(q, c)
+                entry = self._store.get(key)
+                if entry is None or entry.context_key != c or not self._is_valid(entry, now):
+                    entry = None
+                    slot = int(out["hit_slot"][i]) if self.use_semantic else -1
+                    if slot >= 0:
+                        entry = self._store.get(self._slot_key.get(slot, ""))
+                        if entry is not None and not self._is_valid(entry, now):
+                            entry = None
+                if entry is None:
+                    results.append(None)
+                    continue
+                entry.hit_count += 1
+                self._touch(entry.query_hash, entry)
+                if entry._slot is not None:
+                    self._engine.update(entry._slot, lru=entry._seq)
+                self._hits += 1
+                pdev, pconf = entry.predict_device()
+                fb = pconf < self.prediction_confidence_threshold
+                self._hybrid_fallbacks += int(fb)
+                results.append(CacheLookupResult(entry, pdev, pconf, fb))
+            return results
+
+    def insert(self, query: str, context_key: str, device: str, confidence: float = 1.0,
+               method: str = "unknown", q_emb: Optional[np.ndarray] = None,
+               response_time: Optional[float] = None) -> None:
+        """Insert, or refresh in place when the hash exists (reference cache.py:328-370)."""
+        key = self._make_hash(query, context_key)
+        with self._lock:
+            now = datetime.now()
+            entry = self._store.get(key)
+            if entry is not None:
+                self._stamp(key, entry, now)
+                entry.record_routing(device, confidence, method)
+                if q_emb is not None:
+                    entry.embedding = np.array(q_emb, dtype=np.float32, copy=True)
+                if response_time is not None:
+                    entry.response_time = response_time
+                self._touch(key, entry)
+                self._sync_row(entry, row_changed=q_emb is not None)
+                return
+            if len(self._store) >= self.max_size:
+                self._evict_one(now)
+            entry = CacheEntry(query=query, query_hash=key, context_key=context_key,
+                               embedding=None if q_emb is None else np.array(q_emb, dtype=np.float32, copy=True),
+                               timestamp=now, device_used=device, response_time=response_time)
+            entry.record_routing(device, confidence, method)
+            self._store[key] = entry
+            self._stamp(key, entry, now)
+            self._touch(key, entry)
+            self._sync_row(entry, row_changed=True)
+
+    def invalidate(self, context_key: Optional[str] = None, query_pattern: Optional[str] = None) -> int:
+        """Remove entries by context and/or case-insensitive regex on the query text; neither
+        means everything (reference cache.py:372-396).  Returns the number removed."""
+        rx = re.compile(query_pattern, re.IGNORECASE) if query_pattern else None
+        with self._lock:
+            doomed = [k for k, e in self._store.items()
+                      if (context_key is None or e.context_key == context_key)
+                      and (rx is None or rx.search(e.query))]
+            for k in doomed:
+                self._delete_entry(k)
+        logger.debug("invalidate removed %d entries", len(doomed))
+        return len(doomed)
+
+    def warm_up(self, pairs: List[Tuple[str, str, str]], embedder: Any = None) -> None:
+        """Pre-populate from (query, context_key, device) triples (reference cache.py:398-420)."""
+        vecs: List[Optional[np.ndarray]] = [None] * len(pairs)
+        if embedder is not None:
+            try:
+                vecs = list(embedder.encode([q for q, _, _ in pairs]))
+            except Exception as exc:
+                logger.warning("warm_up: embedding failed, inserting without vectors: %s", exc)
+        for (q, ctx, dev), v in zip(pairs, vecs):
+            self.insert(q, ctx, dev, q_emb=v)
+        logger.info("cache warmed up with %d entries", len(pairs))
+
+    # ------------------------------------------------------------------ persistence
+    def save(self, path: str) -> None:
+        """JSON list of the non-expired entries, same schema as the reference
+        (cache.py:426-432, 146-157), so files move between the two implementations."""
+        self._evict_expired()
+        with self._lock:
+            data = [e.to_dict() for e in self._store.values()]
+        Path(path).write_text(json.dumps(data, indent=2), encoding="utf-8")
+        logger.info("cache saved %d entries -> %s", len(data), path)
+
+    def load(self, path: str) -> int:
+        """Restore entries; expired or malformed ones are skipped; returns the count loaded
+        (reference cache.py:434-465; like the reference, max_size is not enforced here)."""
+        p = Path(path)
+        if not p.exists():
+            logger.warning("cache load: %s not found", path)
+            return 0
+        try:
+            raw = json.loads(p.read_text(encoding="utf-8"))
+        except json.JSONDecodeError as exc:
+            logger.error("cache load: bad JSON: %s", exc)
+            return 0
+        loaded = 0
+        with self._lock:
+            now = datetime.now()
+            for d in raw:
+                try:
+                    entry = CacheEntry.from_dict(d)
+                except Exception as exc:
+                    logger.warning("cache load: skipping malformed entry: %s", exc)
+                    continue
+                if not self._is_valid(entry, now):
+                    continue
+                old = self._store.get(entry.query_hash)
+                if old is not None:                   # same key: replaced in place, position kept
+                    entry._seq = old._seq
+                    if old._slot is not None:
+                        self._slot_key.pop(old._slot, None)
+                        self._engine.tombstone([old._slot])
+                    self._store[entry.query_hash] = entry
+                else:
+                    self._store[entry.query_hash] = entry
+                    self._seq += 1
+                    entry._seq = self._seq
+                heapq.heappush(self._exp_heap, (_to_us(entry.timestamp), entry.query_hash))
+                self._ensure_capacity(len(self._store))
+                self._sync_row(entry, row_changed=True)
+                loaded += 1
+        logger.info("cache loaded %d entries from %s", loaded, path)
+        return loaded
+
+    def _ensure_capacity(self, need: int) -> None:
+        """`load` may exceed max_size (reference quirk); rebuild the device store larger."""
+        eng = self._engine
+        if need <= eng.capacity:
+            return
+        new_cap = max(need, eng.capacity * 2)
+        if eng.shard is not None:
+            eng.close()
+        eng.capacity = new_cap
+        self._slot_key.clear()
+        for e in self._store.values():
+            e._slot = None
+        for e in self._store.values():
+            self._sync_row(e, row_changed=True)
+
+    # ------------------------------------------------------------------ stats
+    def stats(self) -> Dict[str, Any]:
+        """Same keys as the reference (cache.py:471-500)."""
+        with self._lock:
+            now = datetime.now()
+            valid = sum(1 for e in self._store.values() if self._is_valid(e, now))
+            hot = sorted(self._store.values(), key=lambda e: e.hit_count, reverse=True)[:5]
+            size = len(self._store)
+        return {
+            "size": size, "max_size": self.max_size, "valid": valid, "stale": size - valid,
+            "hits": self._hits, "attempts": self._attempts,
+            "hit_rate": round(self._hits / max(self._attempts, 1), 4),
+            "evictions": self._evictions, "hybrid_fallbacks": self._hybrid_fallbacks,
+            "top_queries": [{"query": e.query[:60], "hits": e.hit_count,
+                             "predicted_device": e.predict_device()[0],
+                             "predicted_confidence": round(e.predict_device()[1], 3),
+                             "history_len": len(e.routing_history)} for e in hot],
+        }
+
+    def clear(self) -> None:
+        """Wipe the cache and reset the counters (reference cache.py:502-512)."""
+        with self._lock:
+            for e in self._store.values():
+                e.embedding = None
+                e._slot = None
+            self._store.clear()
+            self._slot_key.clear()
+            self._exp_heap.clear()
+            self._stale_heap.clear()
+            self._engine.clear()
+            self._hits = self._attempts = self._evictions = self._hybrid_fallbacks = 0

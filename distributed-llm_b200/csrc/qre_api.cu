@@ -342,6 +342,10 @@ int qre_cache_destroy(qre_cache_t* h) {
     if (p) cudaFree(p);
   if (h->h_in) cudaFreeHost(h->h_in);
   if (h->h_res) cudaFreeHost(h->h_res);
+  if (s.prof_ev) {
+    for (int i = 0; i < 2 * kProfMax; ++i) cudaEventDestroy(s.prof_ev[i]);
+    delete[] s.prof_ev;
+  }
   if (s.stream) cudaStreamDestroy(s.stream);
   delete h;
   return QRE_OK;
@@ -700,6 +704,37 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
     QRE_OUT(score, sizeof(double) * (size_t)m * D);
   }
 #undef QRE_OUT
+  return QRE_OK;
+}
+
+int qre_profile(qre_cache_t* h, int enable) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  if (enable && s.prof_ev == nullptr) {
+    s.prof_ev = new (std::nothrow) cudaEvent_t[2 * kProfMax];
+    if (s.prof_ev == nullptr) return fail(QRE_ERR_INVALID, "out of host memory");
+    for (int i = 0; i < 2 * kProfMax; ++i) QRE_CUDA(cudaEventCreate(&s.prof_ev[i]));
+  }
+  s.prof_on = enable != 0;
+  s.prof_used = 0;
+  return QRE_OK;
+}
+
+int qre_profile_read(qre_cache_t* h, double* scan_ms_total, int* n_launches) {
+  if (h == nullptr || scan_ms_total == nullptr || n_launches == nullptr)
+    return fail(QRE_ERR_INVALID, "NULL argument");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  double total = 0.0;
+  for (int i = 0; i < s.prof_used; ++i) {
+    float ms = 0.f;
+    QRE_CUDA(cudaEventSynchronize(s.prof_ev[2 * i + 1]));
+    QRE_CUDA(cudaEventElapsedTime(&ms, s.prof_ev[2 * i], s.prof_ev[2 * i + 1]));
+    total += ms;
+  }
+  *scan_ms_total = total;
+  *n_launches = s.prof_used;
   return QRE_OK;
 }
 

@@ -95,7 +95,12 @@ struct DeviceState {
   int n_centroids = 0;
   double* perf_health = nullptr;      // [QRE_MAX_DEVICES]
   CUtensorMap tmap_q, tmap_e;
+  // optional CUDA-event bracket around every scan-kernel launch (bench.py's live roofline)
+  bool prof_on = false;
+  cudaEvent_t* prof_ev = nullptr;     // [2 * kProfMax]
+  int prof_used = 0;
 };
+constexpr int kProfMax = 2048;
 
 constexpr int kExactGroup = 8;        // queries per brute-force pass
 

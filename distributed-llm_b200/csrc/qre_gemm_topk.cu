@@ -285,10 +285,16 @@ int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_
   a.dump = dump;
   a.dump_ld = dump_ld;
   a.dump_row0 = dump_row0;
+  const bool prof = s.prof_on && s.prof_ev != nullptr && s.prof_used < kProfMax && dump == nullptr;
+  if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
   if (dump != nullptr) {
     qre_gemm_topk_kernel<true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
   } else {
     qre_gemm_topk_kernel<false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+  }
+  if (prof) {
+    cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);
+    ++s.prof_used;
   }
   return 1;
 }

@@ -29,7 +29,7 @@ EXPORTS = (
     "qre_cache_info", "qre_cache_stream", "qre_cache_append", "qre_cache_append_dev", "qre_cache_update",
     "qre_cache_tombstone", "qre_cache_clear", "qre_cache_read_rows", "qre_set_centroids",
     "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
-    "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm",
+    "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
 )
 
 
@@ -273,6 +273,14 @@ class Shard:
             self.h, C.c_int(m), C.c_int(n_shards), C.c_void_p(cand_all_ptr), C.c_void_p(tok_ptr or None),
             C.c_void_p(heur_dev_ptr or None), C.c_void_p(heur_conf_ptr or None), C.byref(p), C.byref(res),
             C.c_void_p(stream)))
+
+    def profile(self, enable: bool) -> None:
+        _check(self.lib, self.lib.qre_profile(self.h, C.c_int(1 if enable else 0)))
+
+    def profile_read(self):
+        ms, n = C.c_double(), C.c_int()
+        _check(self.lib, self.lib.qre_profile_read(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def debug_gemm(self, m: int, row0: int, n: int) -> np.ndarray:
         out = np.empty((m, n), np.float32)

@@ -1,0 +1,107 @@
+"""Engine — the device side of one routing cache + its router state, behind the small store
+interface the host classes (`cache.QueryCache`, `query_router_engine.SemanticRouter`) use.
+
+The Shard is created lazily, once the embedding dimension is known (the reference learns it
+from the first embedding it sees, src/cache.py:363).  There is no CPU fallback: creating the
+Shard without an sm_100 GPU raises `QreError`.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+
+from . import _cabi
+
+
+class Engine:
+    def __init__(self, capacity: int = 512, device: int = 0, max_batch: int = 64,
+                 dim: Optional[int] = None, scan_mode: int = _cabi.SCAN_TENSOR):
+        self.capacity = max(int(capacity), 1)
+        self.device, self.max_batch, self.scan_mode = int(device), int(max_batch), int(scan_mode)
+        self.shard: Optional[_cabi.Shard] = None
+        self._centroids: Optional[np.ndarray] = None
+        self._owner: Optional[np.ndarray] = None
+        self._health: Optional[np.ndarray] = None
+        if dim is not None:
+            self.ensure(dim)
+
+    # ---- lifetime ----
+    def ensure(self, dim: int) -> _cabi.Shard:
+        if self.shard is None:
+            self.shard = _cabi.Shard(dim=int(dim), capacity=self.capacity, max_batch=self.max_batch,
+                                     device=self.device)
+            if self._centroids is not None:
+                self.shard.set_centroids(self._centroids, self._owner)
+            if self._health is not None:
+                self.shard.set_perf_health(self._health)
+        elif self.shard.dim != int(dim):
+            raise ValueError(f"embedding dimension changed: cache holds {self.shard.dim}-d rows, got {dim}")
+        return self.shard
+
+    def close(self) -> None:
+        if self.shard is not None:
+            self.shard.close()
+            self.shard = None
+
+    # ---- router state ----
+    def set_centroids(self, centroids: np.ndarray, owner: Sequence[int]) -> None:
+        self._centroids = np.ascontiguousarray(centroids, np.float32)
+        self._owner = np.ascontiguousarray(owner, np.uint8)
+        if self.shard is None:
+            self.ensure(self._centroids.shape[1])
+        else:
+            self.shard.set_centroids(self._centroids, self._owner)
+
+    def set_perf_health(self, health: Sequence[float]) -> None:
+        self._health = np.ascontiguousarray(health, np.float64)
+        if self.shard is not None:
+            self.shard.set_perf_health(self._health)
+
+    @property
+    def n_centroids(self) -> int:
+        return 0 if self._centroids is None else int(self._centroids.shape[0])
+
+    # ---- store interface used by QueryCache ----
+    def append(self, row, ctx: int, ts_us: int, lru: int, pdev: int, pconf: float) -> int:
+        row = np.ascontiguousarray(row, np.float32).reshape(1, -1)
+        sh = self.ensure(row.shape[1])
+        return int(sh.append(row, [ctx], [ts_us], [lru], [pdev], [pconf])[0])
+
+    def append_many(self, rows, ctx, ts_us, lru, pdev, pconf) -> np.ndarray:
+        rows = np.ascontiguousarray(rows, np.float32)
+        return self.ensure(rows.shape[1]).append(rows, ctx, ts_us, lru, pdev, pconf)
+
+    def update(self, slot: int, row=None, ts_us=None, lru=None, pdev=None, pconf=None) -> None:
+        one = lambda v, dt: None if v is None else np.array([v], dt)   # noqa: E731
+        self.shard.update(np.array([slot], np.int64),
+                          rows=None if row is None else np.ascontiguousarray(row, np.float32).reshape(1, -1),
+                          ts_us=one(ts_us, np.int64), lru_seq=one(lru, np.uint64),
+                          pred_dev=one(pdev, np.uint8), pred_conf=one(pconf, np.float64))
+
+    def tombstone(self, slots) -> None:
+        slots = np.asarray(list(slots), np.int64)
+        if slots.size and self.shard is not None:
+            self.shard.tombstone(slots)
+
+    def clear(self) -> None:
+        if self.shard is not None:
+            self.shard.clear()
+
+    def read_rows(self, slots) -> np.ndarray:
+        return self.shard.read_rows(np.asarray(list(slots), np.int64))
+
+    def scan(self, q, q_ctx, now_us: int, cfg: _cabi.RouteConfig, route_in: Optional[dict] = None) -> dict:
+        """One fused device pass for a batch: lookup (always) + route (when route_in is given:
+        dict(tok, heur_dev, heur_conf))."""
+        q = np.ascontiguousarray(q, np.float32)
+        if q.ndim == 1:
+            q = q.reshape(1, -1)
+        sh = self.ensure(q.shape[1])
+        if q.shape[0] > sh.max_batch:
+            raise _cabi.QreError(f"batch of {q.shape[0]} exceeds max_batch={sh.max_batch}")
+        cfg.scan_mode = self.scan_mode
+        if route_in is None:
+            return sh.lookup_route(q, q_ctx, cfg, now_us)
+        return sh.lookup_route(q, q_ctx, cfg, now_us, tok=route_in["tok"], heur_dev=route_in["heur_dev"],
+                               heur_conf=route_in["heur_conf"])

@@ -1,0 +1,92 @@
+"""Row-sharded lookup+route over the GPUs of one box.
+
+One process per GPU.  Each rank owns a `Shard` holding rows {r : r % world == rank} or any
+other disjoint subset; queries and per-query features are replicated.  Per batch:
+
+    scan_dev (local tcgen05 scan + exact re-score)  ->  cand[m, 8]  (32-byte records)
+    all_gather_into_tensor over NCCL / NVLink       ->  cand_all[world, m, 8]
+    merge_route_dev (comparator (sim desc, lru_seq asc) + routing epilogue) on every rank
+
+torch is plumbing here: device buffers, streams and the NCCL collective.  With world == 1 the
+collective is skipped.  CPU tests drive `merge_candidates_host` over gloo instead.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+
+from . import _cabi
+
+RESULT_SPECS = {            # field -> (torch dtype name, trailing shape symbol)
+    "hit_slot": ("int64", ()), "hit_sim": ("float32", ()), "hit_pred_dev": ("uint8", ()),
+    "hit_pred_conf": ("float64", ()), "hit_shard": ("int32", ()), "centroid_sim": ("float32", ("K",)),
+    "tok_dev": ("uint8", ()), "tok_conf": ("float64", ()), "sem_dev": ("uint8", ()),
+    "sem_conf": ("float64", ()), "sem_method": ("uint8", ()), "dev": ("uint8", ()),
+    "conf": ("float64", ()), "score": ("float64", ("D",)), "flags": ("uint8", ()),
+}
+
+
+def merge_candidates_host(cand_all: np.ndarray) -> np.ndarray:
+    """Host restatement of the merge comparator, for CPU (gloo) tests of the N>1 plumbing.
+    cand_all: structured [world, m, 8] -> merged [m, 8], best first; (sim desc, lru_seq asc)."""
+    world, m, k = cand_all.shape
+    out = np.empty((m, k), _cabi.CAND_DTYPE)
+    flat = np.transpose(cand_all, (1, 0, 2)).reshape(m, world * k)
+    for q in range(m):
+        c = flat[q]
+        valid = c["slot"] >= 0
+        order = np.lexsort((np.arange(c.size), c["lru_seq"], -c["sim"].astype(np.float64), ~valid))
+        out[q] = c[order[:k]]
+    return out
+
+
+class ShardedLookup:
+    def __init__(self, shard: _cabi.Shard, cfg: _cabi.RouteConfig, rank: int = 0, world: int = 1,
+                 group=None):
+        import torch
+        self.torch = torch
+        self.shard, self.cfg, self.rank, self.world, self.group = shard, cfg, rank, world, group
+        self.dev = torch.device("cuda", shard.device)
+        mb = shard.max_batch
+        self.cand = torch.empty(mb * _cabi.TOPK * 32, dtype=torch.uint8, device=self.dev)
+        self.cand_all = (torch.empty(world * mb * _cabi.TOPK * 32, dtype=torch.uint8, device=self.dev)
+                         if world > 1 else self.cand)
+        self.ovf = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self.out = None
+
+    def _alloc_out(self, m: int):
+        torch = self.torch
+        K, D = max(1, self.shard.n_centroids), self.cfg.n_devices
+        out = {}
+        for f, (dt, tail) in RESULT_SPECS.items():
+            shape = (m,) + tuple({"K": K, "D": D}[t] for t in tail)
+            out[f] = torch.empty(shape, dtype=getattr(torch, dt), device=self.dev)
+        self.out = out
+
+    def step(self, q, q_ctx, now_us: int, tok=None, heur_dev=None, heur_conf=None, check_overflow=False):
+        """q: float32 [m, dim] cuda tensor; q_ctx: int64 view of the u64 ids.  Enqueues on the
+        current torch stream and returns the dict of result tensors (no synchronisation)."""
+        torch = self.torch
+        m = q.shape[0]
+        if self.out is None or self.out["hit_slot"].shape[0] != m:
+            self._alloc_out(m)
+        # torch's default stream has handle 0, which the C ABI reads as "the handle's own
+        # stream": name the legacy default stream explicitly (cudaStreamLegacy == 0x1).
+        st = torch.cuda.current_stream(self.dev).cuda_stream or 1
+        nbytes = m * _cabi.TOPK * 32
+        self.shard.scan_dev(m, q.data_ptr(), q_ctx.data_ptr(), self.cfg, now_us, self.rank,
+                            self.cand.data_ptr(), self.ovf.data_ptr(), st)
+        if check_overflow and int(self.ovf.item()) > 0:
+            self.shard.resolve_overflow_dev(m, self.cfg, now_us, self.rank, self.cand.data_ptr(), st)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self.cand_all[: self.world * nbytes], self.cand[:nbytes],
+                                        group=self.group)
+        ptrs = {f: t.data_ptr() for f, t in self.out.items()}
+        self.shard.merge_route_dev(
+            m, self.world, self.cand_all.data_ptr(), self.cfg, now_us, ptrs,
+            tok_ptr=0 if tok is None else tok.data_ptr(),
+            heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
+            heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=st)
+        return self.out

@@ -10,8 +10,8 @@
  * (QRE_OK = 0); no exceptions cross the ABI; `qre_last_error()` gives the message of the
  * calling thread's last failure.  Functions without the `_dev` suffix take HOST buffers and
  * are synchronous (copies in, kernels, copies out).  `_dev` functions take DEVICE pointers
- * (on the handle's GPU), enqueue on `stream` (NULL = the handle's own stream) and return
- * without synchronising.  A handle is not thread-safe: serialise calls per handle (the
+ * (on the handle's GPU), enqueue on `stream` (a cudaStream_t; NULL = the handle's own stream,
+ * so pass cudaStreamLegacy to name the default stream) and return without synchronising.  A handle is not thread-safe: serialise calls per handle (the
  * reference holds one RLock around its store, src/cache.py:225).
  *
  * There is no CPU fallback: `qre_cache_create` fails with QRE_ERR_NO_DEVICE when no sm_100
@@ -179,6 +179,12 @@ QRE_API int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_c
 
 /* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 QRE_API int qre_launch_count(const qre_cache_t* h, int64_t* count);
+
+/* Bracket every tensor-core scan launch with CUDA events on its own stream (enable != 0
+ * resets the counters); qre_profile_read waits for the recorded launches and returns their
+ * summed device time.  bench.py uses this for the live roofline of the dominant kernel. */
+QRE_API int qre_profile(qre_cache_t* h, int enable);
+QRE_API int qre_profile_read(qre_cache_t* h, double* scan_ms_total, int* n_launches);
 
 /* ---- bring-up / test hooks ------------------------------------------------------------
  * Raw bf16 tensor-core product of the resident queries (from the last scan) with cache rows

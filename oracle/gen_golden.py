@@ -365,9 +365,11 @@ def gen_router_replay():
         call(q, long_ctx, "ctx0")
     for _, q, _ in queries[:6]:
         call(q, None, None)
-    allq = sorted(table)
+    allq = sorted({s_["query"] for s_ in steps})
+    sem = qr.router.routers["semantic"]
     np.savez_compressed(os.path.join(GOLD, "router_replay_table.npz"),
-                        texts=np.array(allq), vecs=np.stack([table[t] for t in allq]))
+                        texts=np.array(allq), vecs=np.stack([table[t] for t in allq]),
+                        centroids=np.stack([sem.nano_center, sem.orin_center]).astype(np.float32))
     json.dump({"steps": steps, "stats": {k: v for k, v in qr.get_cache_stats().items()
                                          if k != "top_queries"},
                "short_ctx": short_ctx, "long_ctx": long_ctx},

@@ -1,0 +1,85 @@
+"""GPU: the drop-in classes (cache.QueryCache, query_router_engine.*) on the real libqre_b200
+engine against outputs recorded from the reference's own code (tests/golden)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_harness
+from tests import replay_common as R
+
+pytestmark = pytest.mark.gpu
+
+
+def test_cache_ops_replay_gpu():
+    clock = ref_harness.FakeClock()
+    cache_mod, _, _ = R.load_modules(clock)
+    qc = R.replay_cache_ops(cache_mod, clock)
+    assert type(qc._engine).__module__ == "qre_b200.engine"
+
+
+def test_router_replay_gpu():
+    clock = ref_harness.FakeClock()
+    _, qre_mod, st = R.load_modules(clock)
+    qr = R.replay_router(qre_mod, st, clock)
+    assert qr._engine.shard is not None and qr._engine.shard.launch_count() > 300
+
+
+def test_route_arith_gpu():
+    _, qre_mod, st = R.load_modules(None)
+    R.check_route_arith(qre_mod, st)
+
+
+def test_golden_cache_scan_through_query_cache():
+    """The recorded reference run of cache_scan.npz replayed through OUR QueryCache on the GPU:
+    same inserts, same refreshes, same lookups at the same (fake) times."""
+    g = np.load(os.path.join(R.GOLDEN, "cache_scan.npz"))
+    clock = ref_harness.FakeClock()
+    cache_mod, _, _ = R.load_modules(clock)
+    from datetime import datetime, timedelta
+    epoch = datetime(1970, 1, 1)
+
+    def set_time(us):
+        clock.t = epoch + timedelta(microseconds=int(us))
+
+    N, M = g["rows"].shape[0], g["queries"].shape[0]
+    qc = cache_mod.QueryCache(max_size=N + 8, ttl_seconds=int(g["ttl_s"]), similarity_threshold=0.85,
+                              prediction_confidence_threshold=0.70)
+    names = {int(c): f"{int(c):016x}" for c in np.unique(np.concatenate([g["row_ctx"], g["q_ctx"]]))}
+    for j in range(N):
+        set_time(g["insert_time_us"][j])
+        qc.insert(f"entry {j}", names[int(g["row_ctx"][j])], "nano" if j % 3 else "orin",
+                  confidence=0.5 + 0.5 * ((j * 37) % 100) / 100.0, method="hybrid", q_emb=g["rows"][j])
+    for (j, dev, t), conf in zip(g["hist_ops"], g["hist_conf"]):
+        set_time(t)
+        qc.insert(f"entry {j}", names[int(g["row_ctx"][j])], "orin" if dev else "nano", confidence=float(conf),
+                  method="hybrid", q_emb=g["rows"][j])
+    for m in range(M):
+        set_time(g["now_us"][m])
+        r = qc.lookup(f"query {m}", names[int(g["q_ctx"][m])], g["queries"][m])
+        exp = int(g["exp_row"][m])
+        assert (r is None) == (exp < 0), m
+        if r is not None:
+            assert r.entry.query == f"entry {exp}", (m, r.entry.query, exp)
+            assert ["nano", "orin"].index(r.predicted_device) == int(g["exp_pred_dev"][m])
+            assert r.predicted_confidence == float(g["exp_pred_conf"][m])
+            assert r.use_hybrid_fallback == bool(g["exp_fallback"][m])
+    s = qc.stats()
+    assert s["hits"] == int(g["stats_hits"]) and s["evictions"] == int(g["stats_evictions"])
+    assert s["size"] == int(g["stats_size"]) and s["hybrid_fallbacks"] == int(g["stats_fallbacks"])
+
+
+def test_lookup_batch_equals_sequential_snapshot():
+    cache_mod, _, _ = R.load_modules(None)
+    from qre_b200 import synth
+    w = synth.make_workload(400, 60, 384, n_centroids=2, seed=21, n_ctx=3, frac_expired=0.0, frac_dup=0.0)
+    names = {int(synth.ctx_id(i)): f"ctx{i}" for i in range(3)}
+    a = cache_mod.QueryCache(max_size=500, ttl_seconds=10**6)
+    b = cache_mod.QueryCache(max_size=500, ttl_seconds=10**6)
+    for qc in (a, b):
+        for j in range(400):
+            qc.insert(f"e{j}", names[int(w.row_ctx[j])], "orin" if j % 2 else "nano", q_emb=w.rows[j])
+    seq = [a.lookup(f"q{m}", names[int(w.q_ctx[m])], w.queries[m]) for m in range(60)]
+    bat = b.lookup_batch([f"q{m}" for m in range(60)], [names[int(c)] for c in w.q_ctx], w.queries)
+    assert [None if r is None else r.entry.query for r in seq] == [None if r is None else r.entry.query for r in bat]
+    assert sum(r is not None for r in seq) > 10
