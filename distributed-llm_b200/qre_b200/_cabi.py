@@ -30,6 +30,7 @@ EXPORTS = (
     "qre_cache_tombstone", "qre_cache_clear", "qre_cache_read_rows", "qre_set_centroids",
     "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
+    "qre_exact_lookup_noalloc",
 )
 
 
@@ -286,3 +287,23 @@ class Shard:
         out = np.empty((m, n), np.float32)
         _check(self.lib, self.lib.qre_debug_gemm(self.h, C.c_int(m), C.c_int64(row0), C.c_int(n), _ptr(out)))
         return out
+
+
+NOALLOC_MAX_QUERIES, NOALLOC_MAX_DIM = 8, 1024
+
+
+def exact_lookup_noalloc(device: int, n_rows: int, dim: int, rows_ptr: int, row_ctx_ptr: int, row_ts_ptr: int,
+                         row_lru_ptr: int, m: int, q_ptr: int, q_ctx_ptr: int, threshold: float, now_us: int,
+                         ttl_us: int, hit_row_ptr: int, hit_sim_ptr: int, stream: int = 0) -> None:
+    """Thin call of qre_exact_lookup_noalloc (include/qre_b200.h): every array is a DEVICE pointer
+    the caller owns; nothing is allocated on the way.  Raises QreError with the library's message
+    when a size limit is exceeded or a CUDA call fails."""
+    lib = load()
+    err = C.create_string_buffer(256)
+    rc = lib.qre_exact_lookup_noalloc(
+        C.c_int(device), C.c_int64(n_rows), C.c_int(dim), C.c_void_p(rows_ptr), C.c_void_p(row_ctx_ptr),
+        C.c_void_p(row_ts_ptr), C.c_void_p(row_lru_ptr), C.c_int(m), C.c_void_p(q_ptr), C.c_void_p(q_ctx_ptr),
+        C.c_double(threshold), C.c_int64(now_us), C.c_int64(ttl_us), C.c_void_p(hit_row_ptr),
+        C.c_void_p(hit_sim_ptr), C.c_void_p(stream or None), err, C.c_size_t(len(err)))
+    if rc != 0:
+        raise QreError(f"libqre_b200 error {rc}: {err.value.decode()}")

@@ -20,6 +20,7 @@
 #ifndef QRE_B200_H
 #define QRE_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -185,6 +186,40 @@ QRE_API int qre_launch_count(const qre_cache_t* h, int64_t* count);
  * summed device time.  bench.py uses this for the live roofline of the dominant kernel. */
 QRE_API int qre_profile(qre_cache_t* h, int enable);
 QRE_API int qre_profile_read(qre_cache_t* h, double* scan_ms_total, int* n_launches);
+
+/* ---- lookup without any allocation --------------------------------------------------------
+ * No counterpart in the reference (its cache is a Python dict; it never manages device memory).
+ *
+ * For callers that are not allowed to allocate GPU memory at lookup time: a process that gave
+ * all of HBM to its own pool at start-up, a request thread that cannot take the device-wide
+ * stall cudaMalloc/cudaFree cause, a plugin whose host forbids allocations outside the host's
+ * allocator.  This is the brute-force exact lookup (same masks, same fp32 rounding sequence
+ * and therefore the same hit row and score as QRE_SCAN_EXACT) over arrays the CALLER owns,
+ * all DEVICE pointers on `device`:
+ *   rows[n_rows, dim] fp32 (16-byte aligned, dim % 4 == 0), row_ctx / row_ts_us / row_lru [n_rows]
+ *   (ctx == QRE_CTX_TOMBSTONE marks a deleted row), queries[m, dim], q_ctx[m];
+ *   outputs hit_row[m] (-1 = miss) and hit_sim[m] (0 on a miss).
+ * It calls no cudaMalloc / cudaFree / allocating library routine.  Its only scratch (per-CTA
+ * partial winners and a completion ticket) is a 197,120-byte static __device__ array inside
+ * the library, which therefore occupies that much memory on every GPU that loads the library
+ * until the process exits.  Limits: m <= QRE_NOALLOC_MAX_QUERIES, dim <= QRE_NOALLOC_MAX_DIM,
+ * n_rows <= QRE_NOALLOC_MAX_ROWS; anything larger is rejected with QRE_ERR_CAPACITY and a
+ * message in `err` (caller's buffer of err_len bytes, may be NULL).
+ * All calls on a device share the array and it keeps the previous call's contents (the part
+ * that must be zero is cleared at the start of each call), so calls that overlap on the same
+ * GPU race with each other: issue them one after another.  The first call on each device
+ * resolves the array's device address (cudaGetSymbolAddress); make that first call before
+ * starting any stream capture.  Asynchronous: work is enqueued on `stream` (a cudaStream_t;
+ * NULL = the default stream) and the outputs are valid once the stream has caught up. */
+#define QRE_NOALLOC_MAX_QUERIES 8
+#define QRE_NOALLOC_MAX_DIM 1024
+#define QRE_NOALLOC_MAX_ROWS 2147483647ll
+QRE_API int qre_exact_lookup_noalloc(int device, int64_t n_rows, int dim, const float* rows,
+                                     const uint64_t* row_ctx, const int64_t* row_ts_us,
+                                     const uint64_t* row_lru, int m, const float* queries,
+                                     const uint64_t* q_ctx, double similarity_threshold, int64_t now_us,
+                                     int64_t ttl_us, int64_t* hit_row, float* hit_sim, void* stream,
+                                     char* err, size_t err_len);
 
 /* ---- bring-up / test hooks ------------------------------------------------------------
  * Raw bf16 tensor-core product of the resident queries (from the last scan) with cache rows
