@@ -1,0 +1,66 @@
+"""GPU x2 (NCCL): row-sharded scan -> all-gather -> merge+route equals the unsharded oracle.
+Skipped on a single-GPU box."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, ret):
+    import torch
+    import torch.distributed as dist
+    from oracle import qre_oracle as O
+    from qre_b200 import _cabi, synth
+    from qre_b200.sharded import ShardedLookup
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    w = synth.make_workload(30000, 300, 384, n_centroids=8, seed=44, frac_dup=0.03, frac_near=0.05)
+    w.rows[1::2][:60] = w.rows[0::2][:60]                 # cross-shard duplicates: tie-break via lru
+    w.row_ctx[1::2][:60] = w.row_ctx[0::2][:60]
+    idx = np.arange(rank, w.rows.shape[0], world)
+    sh = _cabi.Shard(dim=384, capacity=idx.size, max_batch=300, device=rank)
+    sh.append(w.rows[idx], w.row_ctx[idx], w.row_ts_us[idx], w.row_lru[idx], w.row_pred_dev[idx],
+              w.row_pred_conf[idx])
+    sh.set_centroids(w.centroids, w.owner)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    look = ShardedLookup(sh, cfg, rank, world)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)   # noqa: E731
+    out = look.step(t(w.queries), t(w.q_ctx.view(np.int64)), w.now_us, t(w.tok), t(w.heur_dev), t(w.heur_conf),
+                    check_overflow=True)
+    torch.cuda.synchronize()
+    slot, shard = out["hit_slot"].cpu().numpy(), out["hit_shard"].cpu().numpy()
+    glob = np.where(slot >= 0, slot * world + shard, -1)
+    img = O.CacheImage(w.rows, w.row_ctx, w.row_ts_us, w.row_lru)
+    exp_row, exp_sim = O.scan_batch(w.queries, w.q_ctx, img, w.now_us, w.ttl_us, 0.85)
+    hit = exp_row >= 0
+    r = O.route_batch(w.queries, w.tok, w.heur_dev, w.heur_conf, w.centroids, w.owner, O.RouteParams())
+    ok = (np.array_equal(glob, exp_row)
+          and np.allclose(out["hit_sim"].cpu().numpy()[hit], exp_sim[hit], rtol=1e-5)
+          and np.array_equal(out["hit_pred_dev"].cpu().numpy()[hit], w.row_pred_dev[exp_row[hit]])
+          and float(np.mean(out["dev"].cpu().numpy() == r["dev"])) > 0.995)
+    ret[rank] = (bool(ok), int(hit.sum()))
+    dist.barrier()
+    dist.destroy_process_group()
+    sh.close()
+
+
+def test_two_gpu_sharded_lookup_equals_oracle():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    world, port = 2, _free_port()
+    with mp.Manager() as man:
+        ret = man.dict()
+        mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert all(ret[r][0] for r in range(world)), dict(ret)
+        assert ret[0][1] > 50
