@@ -233,8 +233,8 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     return fail(QRE_ERR_NO_DEVICE, "device %d is sm_%d%d; libqre_b200 is built for sm_100a only", device,
                 prop.major, prop.minor);
   const int dim_pad = (int)align_up(dim, kBK);
-  if (dim_pad / kBK > kMaxKB)
-    return fail(QRE_ERR_INVALID, "dim %d not supported by the resident-query scan (max %d)", dim, kMaxKB * kBK);
+  if (dim_pad / kBK > kMaxKBStream)
+    return fail(QRE_ERR_INVALID, "dim %d not supported (max %d)", dim, kMaxKBStream * kBK);
   DeviceGuard guard(device);
   qre_cache_t* h = new (std::nothrow) qre_cache_t();
   if (h == nullptr) return fail(QRE_ERR_INVALID, "out of host memory");

@@ -15,6 +15,7 @@ constexpr int kBN = 256;          // cache rows per tile (UMMA N)
 constexpr int kBK = 64;           // bf16 elements per k-block (= one 128-byte swizzle row)
 constexpr int kStages = 4;        // B-tile pipeline depth (4 x 32 KB)
 constexpr int kMaxKB = 6;         // resident-A variant: dim_pad <= 384
+constexpr int kMaxKBStream = 16;  // streaming-A variant: dim_pad <= 1024
 constexpr int kTopK = QRE_TOPK;
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr float kNormEps = 1e-9f;                 // src/cache.py:284,289 ; qre:136

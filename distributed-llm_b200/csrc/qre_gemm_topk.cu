@@ -5,8 +5,8 @@
 // per-query running top-k so the [m x N] score matrix never leaves the SM.
 //
 //   * one CTA per SM, persistent over work units (row range s, query block mb);
-//   * the 128-query A block (128 x dim bf16 <= 96 KB) is loaded ONCE per unit by TMA and
-//     stays resident in shared memory; only cache-row tiles (256 rows x 64 k, 32 KB) stream
+//   * for dim <= 384 the 128-query A block (128 x dim bf16 <= 96 KB) is loaded ONCE per unit by
+//     TMA and stays resident in shared memory (for larger dims A k-blocks ride with B); only cache-row tiles (256 rows x 64 k, 32 KB) stream
 //     through a 4-stage TMA/mbarrier ring;
 //   * a single elected thread issues tcgen05.mma (M=128, N=256, K=16, bf16 -> fp32) into one
 //     of two 256-column TMEM accumulators, so the epilogue of tile t overlaps the MMAs of t+1;
@@ -61,15 +61,20 @@ __device__ __noinline__ float consider(TopK* tk, float v, long long row, long lo
   return tk->v[kTopK - 1];
 }
 
-template <bool kDump>
+// kResident: the 128-query A block fits in shared memory next to the B ring (dim_pad <= 384)
+// and is loaded once per work unit.  Otherwise (dim_pad up to 1024, e.g. 768-d embeddings) each
+// pipeline stage carries the A k-block (16 KB) together with the B k-block (32 KB).
+template <bool kDump, bool kResident>
 __global__ void __launch_bounds__(kThreads, 1)
 qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_e,
                      const GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // resident: [A: 6 x 16 KB][B ring: 4 x 32 KB]; streaming: ring of 4 x (A 16 KB + B 32 KB)
+  constexpr int kStageBytes = kResident ? kBBytes : (kABytesPerKB + kBBytes);
   uint8_t* sA = smem;
-  uint8_t* sB = smem + kSmemA;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA + kSmemB);
+  uint8_t* sB = kResident ? smem + kSmemA : smem + kABytesPerKB;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (kResident ? kSmemA + kSmemB : kStages * kStageBytes));
   uint64_t* full = bars;                    // [kStages]  TMA -> MMA
   uint64_t* empty = bars + kStages;         // [kStages]  MMA -> TMA
   uint64_t* a_full = bars + 2 * kStages;    // TMA -> MMA (resident A block landed)
@@ -115,16 +120,19 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       for (int u = blockIdx.x; u < U; u += gridDim.x) {
         const int s = u / a.mblocks, mb = u - s * a.mblocks;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        mbar_wait(a_empty, (a_iter & 1) ^ 1);
-        mbar_arrive_expect_tx(a_full, static_cast<uint32_t>(a.num_kb) * kABytesPerKB);
-        for (int kb = 0; kb < a.num_kb; ++kb)
-          tma_load_2d(sA + kb * kABytesPerKB, &tmap_q, a_full, kb * kBK, mb * kBM);
-        ++a_iter;
+        if (kResident) {
+          mbar_wait(a_empty, (a_iter & 1) ^ 1);
+          mbar_arrive_expect_tx(a_full, static_cast<uint32_t>(a.num_kb) * kABytesPerKB);
+          for (int kb = 0; kb < a.num_kb; ++kb)
+            tma_load_2d(sA + kb * kABytesPerKB, &tmap_q, a_full, kb * kBK, mb * kBM);
+          ++a_iter;
+        }
         for (int t = t0; t < t1; ++t) {
           for (int kb = 0; kb < a.num_kb; ++kb) {
             mbar_wait(&empty[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full[stage], kBBytes);
-            tma_load_2d(sB + stage * kBBytes, &tmap_e, &full[stage], kb * kBK, t * kBN);
+            mbar_arrive_expect_tx(&full[stage], kStageBytes);
+            if (!kResident) tma_load_2d(sA + stage * kStageBytes, &tmap_q, &full[stage], kb * kBK, mb * kBM);
+            tma_load_2d(sB + stage * kStageBytes, &tmap_e, &full[stage], kb * kBK, t * kBN);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -139,7 +147,7 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       for (int u = blockIdx.x; u < U; u += gridDim.x) {
         const int s = u / a.mblocks;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        mbar_wait(a_full, a_iter & 1);
+        if (kResident) mbar_wait(a_full, a_iter & 1);
         for (int t = t0; t < t1; ++t) {
           const uint32_t acc = tile_iter & 1;
           mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
@@ -148,8 +156,8 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
           for (int kb = 0; kb < a.num_kb; ++kb) {
             mbar_wait(&full[stage], phase);
             tc_fence_after();
-            const uint64_t adesc = umma_desc_sw128(sA_addr + kb * kABytesPerKB);
-            const uint64_t bdesc = umma_desc_sw128(sB_addr + stage * kBBytes);
+            const uint64_t adesc = umma_desc_sw128(sA_addr + (kResident ? kb * kABytesPerKB : stage * kStageBytes));
+            const uint64_t bdesc = umma_desc_sw128(sB_addr + stage * kStageBytes);
 #pragma unroll
             for (int k = 0; k < kBK / 16; ++k) {
               // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in (addr>>4)
@@ -161,8 +169,10 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
           umma_commit(&t_full[acc]);             // accumulator complete -> epilogue
           ++tile_iter;
         }
-        umma_commit(a_empty);                    // resident A no longer read
-        ++a_iter;
+        if (kResident) {
+          umma_commit(a_empty);                  // resident A no longer read
+          ++a_iter;
+        }
       }
     }
   } else {
@@ -256,12 +266,17 @@ ScanGeometry plan_scan(int m, long long n_rows, int num_sms) {
 
 // Per-device set-up (called by qre_cache_create with the device current): opt in to the
 // 225 KB dynamic shared memory the scan kernel needs.
-cudaError_t gemm_topk_init() {
-  cudaError_t e = cudaFuncSetAttribute(qre_gemm_topk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       kSmemTotal);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(qre_gemm_topk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <bool kDump, bool kResident>
+static cudaError_t set_smem_attr() {
+  return cudaFuncSetAttribute(qre_gemm_topk_kernel<kDump, kResident>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               kSmemTotal);
+}
+cudaError_t gemm_topk_init() {
+  cudaError_t e = set_smem_attr<true, true>();
+  if (e == cudaSuccess) e = set_smem_attr<false, true>();
+  if (e == cudaSuccess) e = set_smem_attr<true, false>();
+  if (e == cudaSuccess) e = set_smem_attr<false, false>();
+  return e;
 }
 
 int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
@@ -287,10 +302,13 @@ int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_
   a.dump_row0 = dump_row0;
   const bool prof = s.prof_on && s.prof_ev != nullptr && s.prof_used < kProfMax && dump == nullptr;
   if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
+  const bool resident = a.num_kb <= kMaxKB;
   if (dump != nullptr) {
-    qre_gemm_topk_kernel<true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+    if (resident) qre_gemm_topk_kernel<true, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+    else qre_gemm_topk_kernel<true, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
   } else {
-    qre_gemm_topk_kernel<false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+    if (resident) qre_gemm_topk_kernel<false, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+    else qre_gemm_topk_kernel<false, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
   }
   if (prof) {
     cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);

@@ -221,3 +221,40 @@ def test_overflow_falls_back_to_exact_scan():
     assert out["hit_sim"][0] == out_e["hit_sim"][0]
     np.testing.assert_allclose(out["hit_sim"][0], exp_sim[0], rtol=REL)
     sh.close()
+
+
+def test_config4_768d_64_centroids_16_devices_perf_term():
+    """BASELINE config 4 at oracle size: 768-d rows (streaming-A scan variant), 64 centroids owned
+    by 16 devices, perf health vector in the hybrid score."""
+    w = synth.make_workload(12000, 260, 768, n_centroids=64, n_devices=16, seed=8, frac_near=0.06, frac_dup=0.03)
+    sh = _load(w)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us, n_devices=16, w_perf=0.1)
+    out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us, tok=w.tok, heur_dev=w.heur_dev,
+                          heur_conf=w.heur_conf)
+    exp_row, exp_sim = _oracle_scan(w)
+    _check_lookup(out, exp_row, exp_sim)
+    assert (exp_row >= 0).sum() > 80
+    got = sh.debug_gemm(260, 256, 512)
+    qn = w.queries / np.maximum(np.linalg.norm(w.queries, axis=1, keepdims=True), 1e-30)
+    en = w.rows[256:768] / np.maximum(np.linalg.norm(w.rows[256:768], axis=1, keepdims=True), 1e-30)
+    assert np.abs(got - qn.astype(np.float64) @ en.astype(np.float64).T).max() < 2e-3
+    p = O.RouteParams(n_devices=16, w_perf=0.1)
+    r = O.route_batch(w.queries, w.tok, w.heur_dev, w.heur_conf, w.centroids, w.owner, p, w.perf_health)
+    np.testing.assert_allclose(out["centroid_sim"], r["sims"], rtol=REL, atol=1e-7)
+    dsim = np.full((260, 16), -np.inf)
+    for k in range(64):
+        dsim[:, w.owner[k]] = np.maximum(dsim[:, w.owner[k]], r["sims"][:, k])
+    top2 = np.sort(dsim, axis=1)[:, -2:]
+    margin = top2[:, 1] - top2[:, 0]
+    S2 = np.sort(r["S"], axis=1)[:, -2:]
+    band = (np.abs(margin - 0.03) < 2e-6) | (np.abs(top2[:, 1] - 0.05) < 2e-6) | (margin < 2e-6) \
+        | (np.abs(S2[:, 1] - S2[:, 0]) < 1e-6)
+    ok = ~band
+    assert band.sum() <= 4
+    assert np.array_equal(out["sem_method"][ok], r["sem_method"][ok])
+    assert np.array_equal(out["sem_dev"][ok], r["sem_dev"][ok])
+    assert np.array_equal(out["dev"][ok], r["dev"][ok])
+    np.testing.assert_allclose(out["score"][ok], r["S"][ok], rtol=REL, atol=2e-6)
+    np.testing.assert_allclose(out["conf"][ok], r["conf"][ok], rtol=REL, atol=4e-6)
+    assert len(np.unique(r["dev"])) > 3
+    sh.close()
