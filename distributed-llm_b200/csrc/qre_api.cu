@@ -183,9 +183,8 @@ int validate_params(const qre_cache_t* h, const qre_params_t* p) {
 int scan_enqueue(qre_cache_t* h, int m, const float* q_dev, const uint64_t* q_ctx_dev, const qre_params_t& p,
                  int shard, qre_candidate_t* cand, cudaStream_t st) {
   DeviceState& s = h->s;
-  QRE_CUDA(cudaMemcpyAsync(h->d_q_ctx, q_ctx_dev, sizeof(uint64_t) * m, cudaMemcpyDeviceToDevice, st));
-  QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), st));
-  h->launches += launch_prep_queries(s, m, q_dev, st);
+  s.slot = p.pipeline_slot & 1;
+  h->launches += launch_prep_queries(s, m, q_dev, q_ctx_dev, h->d_q_ctx, st);
   h->last_m = m;
   if (p.scan_mode == QRE_SCAN_TENSOR && h->hwm > 0) {
     h->launches += launch_gemm_topk(s, m, h->hwm, h->d_q_ctx, p, nullptr, 0, 0, 0, st);
@@ -266,9 +265,12 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
   QRE_ALLOC(s.lru, sizeof(uint64_t) * (size_t)capacity);
   QRE_ALLOC(s.pred_dev, (size_t)capacity);
   QRE_ALLOC(s.pred_conf, sizeof(double) * (size_t)capacity);
-  QRE_ALLOC(s.q_f32, sizeof(float) * (size_t)s.mb_pad * dim_pad);
+  for (int b = 0; b < 2; ++b) {
+    QRE_ALLOC(s.q_f32[b], sizeof(float) * (size_t)s.mb_pad * dim_pad);
+    QRE_ALLOC(s.q_norm[b], sizeof(float) * (size_t)s.mb_pad);
+    QRE_ALLOC(s.q_flags[b], (size_t)max_batch);
+  }
   QRE_ALLOC(s.q_bf16, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad);
-  QRE_ALLOC(s.q_norm, sizeof(float) * (size_t)s.mb_pad);
   // scratch of the fused top-k: [mblocks*128][S][8] entries; S*mblocks <= 8 waves of SMs + slack
   {
     long long worst = 0;
@@ -279,14 +281,14 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     }
     const ScanGeometry g = plan_scan(s.mb_pad, s.cap_pad, s.num_sms);
     worst = std::max(worst, (long long)g.mblocks * kBM * g.splits * kTopK);
-    s.partial_entries = worst + (long long)kBM * kTopK * (s.num_sms + 8);
+    // head-room: the split search may pick a different S when SMs are reserved for other kernels
+    s.partial_entries = 2 * worst + (long long)kBM * kTopK * (s.num_sms + 8);
   }
   QRE_ALLOC(s.partial, sizeof(PartialEntry) * (size_t)s.partial_entries);
   s.exact_grid = s.num_sms * 2;
   QRE_ALLOC(s.exact_partial, sizeof(ExactBest) * (size_t)kExactGroup * s.exact_grid);
   QRE_ALLOC(s.ovf_count, sizeof(int32_t));
   QRE_ALLOC(s.ovf_list, sizeof(int32_t) * (size_t)max_batch);
-  QRE_ALLOC(s.q_flags, (size_t)max_batch);
   QRE_ALLOC(s.centroids, sizeof(float) * (size_t)QRE_MAX_CENTROIDS * dim_pad);
   QRE_ALLOC(s.cent_norm, sizeof(float) * QRE_MAX_CENTROIDS);
   QRE_ALLOC(s.cent_owner, QRE_MAX_CENTROIDS);
@@ -310,7 +312,7 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.q_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.perf_health, 0, sizeof(double) * QRE_MAX_DEVICES, s.stream));
-    QRE_CUDA(cudaMemsetAsync(s.q_flags, 0, (size_t)max_batch, s.stream));
+    for (int b = 0; b < 2; ++b) QRE_CUDA(cudaMemsetAsync(s.q_flags[b], 0, (size_t)max_batch, s.stream));
     QRE_CUDA(gemm_topk_init());
     EncodeTiledFn enc = nullptr;
     int rc = get_encode_fn(&enc);
@@ -334,8 +336,9 @@ int qre_cache_destroy(qre_cache_t* h) {
   DeviceGuard guard(h->s.device);
   DeviceState& s = h->s;
   if (s.stream) cudaStreamSynchronize(s.stream);
-  void* dev_ptrs[] = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf, s.q_f32,
-                      s.q_bf16, s.q_norm, s.partial, s.exact_partial, s.ovf_count, s.ovf_list, s.q_flags,
+  void* dev_ptrs[] = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf, s.q_f32[0],
+                      s.q_f32[1], s.q_bf16, s.q_norm[0], s.q_norm[1], s.partial, s.exact_partial, s.ovf_count,
+                      s.ovf_list, s.q_flags[0], s.q_flags[1],
                       s.centroids, s.cent_norm, s.cent_owner, s.perf_health, h->d_stage, h->d_in, h->d_res,
                       h->d_cand, h->d_q_ctx, h->d_dump};
   for (void* p : dev_ptrs)
@@ -608,6 +611,7 @@ int qre_resolve_overflow_dev(qre_cache_t* h, int m, const qre_params_t* params, 
   QRE_CUDA(cudaMemcpyAsync(&n_ovf, h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   QRE_CUDA(cudaStreamSynchronize(st));
   if (n_ovf <= 0) return QRE_OK;
+  h->s.slot = params->pipeline_slot & 1;
   h->launches += launch_exact_scan(h->s, m, h->hwm, h->d_q_ctx, h->s.ovf_list, n_ovf, true, *params, shard,
                                    cand_inout, st);
   QRE_CUDA(cudaGetLastError());
@@ -620,7 +624,6 @@ int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_candidate
                         qre_result_t* out_dev, void* stream) {
   if (h == nullptr || cand_all == nullptr || out_dev == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
   if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
-  if (m != h->last_m) return fail(QRE_ERR_INVALID, "m=%d does not match the last scan (%d)", m, h->last_m);
   if (n_shards < 1 || n_shards * QRE_TOPK > 128) return fail(QRE_ERR_INVALID, "n_shards out of range [1, 16]");
   int rc = validate_params(h, params);
   if (rc != QRE_OK) return rc;
@@ -628,6 +631,7 @@ int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_candidate
     return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
   DeviceGuard guard(h->s.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  h->s.slot = params->pipeline_slot & 1;
   h->launches += launch_merge_route(h->s, m, n_shards, cand_all, tok, heur_dev, heur_conf, *params, *out_dev, st);
   QRE_CUDA(cudaGetLastError());
   return QRE_OK;

@@ -62,6 +62,8 @@ struct ScanGeometry {
 };
 ScanGeometry plan_scan(int m, long long n_rows, int num_sms);
 cudaError_t gemm_topk_init();
+struct DeviceState;
+int scan_sms(const DeviceState& s, const qre_params_t& p);
 
 // All device state of one cache shard.
 struct DeviceState {
@@ -78,9 +80,12 @@ struct DeviceState {
   uint8_t* pred_dev = nullptr;        // [capacity]
   double* pred_conf = nullptr;        // [capacity]
   // per-batch query state
-  float* q_f32 = nullptr;             // [mb_pad, dim_pad]
-  __nv_bfloat16* q_bf16 = nullptr;    // [mb_pad, dim_pad]
-  float* q_norm = nullptr;            // [mb_pad]
+  // q_f32 / q_norm / q_flags are double-buffered ("pipeline slots"): merge_route of batch i may
+  // still read slot i&1 on another stream while the scan of batch i+1 fills the other slot.
+  int slot = 0;
+  float* q_f32[2] = {nullptr, nullptr};     // [mb_pad, dim_pad]
+  __nv_bfloat16* q_bf16 = nullptr;          // [mb_pad, dim_pad]  (scan only: single buffer)
+  float* q_norm[2] = {nullptr, nullptr};    // [mb_pad]
   // scratch
   PartialEntry* partial = nullptr;    // [partial_entries]
   long long partial_entries = 0;
@@ -88,7 +93,7 @@ struct DeviceState {
   int exact_grid = 0;
   int32_t* ovf_count = nullptr;       // [1]
   int32_t* ovf_list = nullptr;        // [max_batch]
-  uint8_t* q_flags = nullptr;         // [max_batch]  QRE_FLAG_* of the current batch
+  uint8_t* q_flags[2] = {nullptr, nullptr};  // [max_batch]  QRE_FLAG_* of the batch in each slot
   // router state
   float* centroids = nullptr;         // [K, dim_pad]
   float* cent_norm = nullptr;         // [K]
@@ -114,7 +119,8 @@ int launch_update_meta(DeviceState& s, long long n, const int64_t* slot_dev, con
                        cudaStream_t st);
 int launch_tombstone(DeviceState& s, long long n, const int64_t* slot_dev, cudaStream_t st);
 int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, float* out, cudaStream_t st);
-int launch_prep_queries(DeviceState& s, int m, const float* q_dev, cudaStream_t st);
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src,
+                        uint64_t* q_ctx_dst, cudaStream_t st);
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st);
 int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
                      float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st);

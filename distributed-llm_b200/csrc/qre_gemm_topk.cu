@@ -20,6 +20,9 @@
 // of each cache-row tile are served by L2, not HBM.
 #include <stdio.h>
 
+#include <algorithm>
+#include <cmath>
+
 #include "qre_common.cuh"
 #include "qre_ptx.cuh"
 
@@ -252,16 +255,34 @@ ScanGeometry plan_scan(int m, long long n_rows, int num_sms) {
   g.tiles_n = static_cast<int>((n_rows + kBN - 1) / kBN);
   if (g.mblocks < 1) g.mblocks = 1;
   if (g.tiles_n < 1) g.tiles_n = 1;
-  long long waves = (static_cast<long long>(g.tiles_n) * g.mblocks) / (16LL * num_sms);
-  if (waves < 1) waves = 1;
-  if (waves > 8) waves = 8;
-  long long S = (waves * num_sms + g.mblocks / 2) / g.mblocks;
-  if (S < 1) S = 1;
-  if (S > g.tiles_n) S = g.tiles_n;
+  // Units are equal-sized, so a launch takes ceil(U / G) rounds of T / S tiles; every unit also
+  // pays ~1.6 tile-times of pipeline fill (A load, first B stages).  Pick the S that maximises
+  //   (U / G) / ceil(U / G)  *  L / (L + 1.6),   L = T / S,  U = S * mblocks,
+  // among S giving at most 8 rounds.
+  long long S = 1;
+  double best = -1.0;
+  const long long s_max = std::min<long long>(g.tiles_n, (8LL * num_sms) / g.mblocks + 1);
+  for (long long c = 1; c <= s_max; ++c) {
+    const double U = static_cast<double>(c) * g.mblocks;
+    const double rounds = std::ceil(U / num_sms);
+    if (rounds > 8.0) break;
+    const double L = static_cast<double>(g.tiles_n) / c;
+    const double score = (U / num_sms) / rounds * L / (L + 1.6);
+    if (score > best + 1e-12) { best = score; S = c; }
+  }
   g.splits = static_cast<int>(S);
   const long long U = S * g.mblocks;
   g.grid = static_cast<int>(U < num_sms ? U : num_sms);
   return g;
+}
+
+// SMs the scan may occupy: all of them minus what the caller reserves for kernels that should
+// run beside it (NCCL all-gather + merge of the previous batch in the pipelined multi-GPU path).
+int scan_sms(const DeviceState& s, const qre_params_t& p) {
+  int r = p.reserve_sms;
+  if (r < 0) r = 0;
+  if (r > s.num_sms / 2) r = s.num_sms / 2;
+  return s.num_sms - r;
 }
 
 // Per-device set-up (called by qre_cache_create with the device current): opt in to the
@@ -282,7 +303,7 @@ cudaError_t gemm_topk_init() {
 int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
                      float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st) {
   (void)dump_n;
-  const ScanGeometry g = plan_scan(m, n_rows, s.num_sms);
+  const ScanGeometry g = plan_scan(m, n_rows, scan_sms(s, p));
   GemmArgs a;
   a.m = m;
   a.mblocks = g.mblocks;

@@ -146,10 +146,13 @@ __global__ void gather_rows_kernel(long long n, const int64_t* slot, const float
 
 // Queries: fp32 copy (zero padded), |q|, and the L2-normalised bf16 operand of the scan.
 __global__ void prep_queries_kernel(int m, int rows_total, const float* q, int dim, int dim_pad, float* q_f32,
-                                    __nv_bfloat16* q_bf16, float* q_norm) {
+                                    __nv_bfloat16* q_bf16, float* q_norm, const uint64_t* q_ctx_src,
+                                    uint64_t* q_ctx_dst, int32_t* ovf_count) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *ovf_count = 0;     // per-batch overflow counter
   if (w >= rows_total) return;
+  if (lane == 0 && w < m) q_ctx_dst[w] = q_ctx_src[w];          // private copy for the scan
   float* dst = q_f32 + static_cast<long long>(w) * dim_pad;
   __nv_bfloat16* bdst = q_bf16 + static_cast<long long>(w) * dim_pad;
   float acc = 0.f;
@@ -653,10 +656,12 @@ int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, flo
   gather_rows_kernel<<<blocks_for_warps(n, 256), 256, 0, st>>>(n, slot_dev, s.rows_f32, s.dim, s.dim_pad, out);
   return 1;
 }
-int launch_prep_queries(DeviceState& s, int m, const float* q_dev, cudaStream_t st) {
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src,
+                        uint64_t* q_ctx_dst, cudaStream_t st) {
   const int rows_total = ((m + kBM - 1) / kBM) * kBM;
-  prep_queries_kernel<<<blocks_for_warps(rows_total, 256), 256, 0, st>>>(m, rows_total, q_dev, s.dim, s.dim_pad,
-                                                                        s.q_f32, s.q_bf16, s.q_norm);
+  prep_queries_kernel<<<blocks_for_warps(rows_total, 256), 256, 0, st>>>(
+      m, rows_total, q_dev, s.dim, s.dim_pad, s.q_f32[s.slot], s.q_bf16, s.q_norm[s.slot], q_ctx_src, q_ctx_dst,
+      s.ovf_count);
   return 1;
 }
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st) {
@@ -666,15 +671,15 @@ int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st) {
 
 int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& p, int shard,
                    qre_candidate_t* cand, cudaStream_t st) {
-  const ScanGeometry g = plan_scan(m, n_rows, s.num_sms);
+  const ScanGeometry g = plan_scan(m, n_rows, scan_sms(s, p));
   RescoreArgs a;
   a.m = m; a.splits = g.splits; a.dim_pad = s.dim_pad; a.shard = shard;
   const double thr = p.similarity_threshold > 0.0 ? p.similarity_threshold : 0.0;
   a.floor_v = static_cast<float>(thr) - kApproxEps;
   a.thr = p.similarity_threshold;
-  a.partial = s.partial; a.q_f32 = s.q_f32; a.q_norm = s.q_norm; a.rows_f32 = s.rows_f32;
+  a.partial = s.partial; a.q_f32 = s.q_f32[s.slot]; a.q_norm = s.q_norm[s.slot]; a.rows_f32 = s.rows_f32;
   a.row_norm = s.row_norm; a.lru = s.lru; a.pdev = s.pred_dev; a.pconf = s.pred_conf; a.cand = cand;
-  a.q_flags = s.q_flags;
+  a.q_flags = s.q_flags[s.slot];
   a.ovf_count = s.ovf_count; a.ovf_list = s.ovf_list;
   rescore_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
   return 1;
@@ -686,17 +691,17 @@ int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q
   (void)m;
   const size_t smem = static_cast<size_t>(kExactGroup) * s.dim_pad * sizeof(float);   // <= 12 KB
   int launches = 0;
-  uint8_t* q_flags = s.q_flags;
+  uint8_t* q_flags = s.q_flags[s.slot];
   for (int g0 = 0; g0 < nq_total; g0 += kExactGroup) {
     ExactArgs a;
     a.nq = nq_total - g0 < kExactGroup ? nq_total - g0 : kExactGroup;
     a.q_first = g0; a.qlist = qlist_dev; a.n_rows = n_rows; a.dim_pad = s.dim_pad;
-    a.thr = p.similarity_threshold; a.now_us = p.now_us; a.ttl_us = p.ttl_us; a.q_f32 = s.q_f32;
-    a.q_norm = s.q_norm; a.q_ctx = q_ctx; a.rows_f32 = s.rows_f32; a.row_norm = s.row_norm; a.meta = s.meta;
+    a.thr = p.similarity_threshold; a.now_us = p.now_us; a.ttl_us = p.ttl_us; a.q_f32 = s.q_f32[s.slot];
+    a.q_norm = s.q_norm[s.slot]; a.q_ctx = q_ctx; a.rows_f32 = s.rows_f32; a.row_norm = s.row_norm; a.meta = s.meta;
     a.lru = s.lru; a.partial = s.exact_partial;
     exact_scan_kernel<<<s.exact_grid, kExactWarps * 32, smem, st>>>(a);
     exact_reduce_kernel<<<1, kExactGroup * 32, 0, st>>>(a.nq, g0, qlist_dev, s.exact_grid, s.exact_partial, shard,
-                                                       s.pred_dev, s.pred_conf, s.q_norm, cand, q_flags,
+                                                       s.pred_dev, s.pred_conf, s.q_norm[s.slot], cand, q_flags,
                                                        mark_overflow ? QRE_FLAG_OVERFLOW : 0);
     launches += 2;
   }
@@ -708,8 +713,8 @@ int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_
                        const qre_result_t& out, cudaStream_t st) {
   MergeArgs a;
   a.m = m; a.n_shards = n_shards; a.dim_pad = s.dim_pad; a.n_centroids = s.n_centroids;
-  a.do_route = p.do_route; a.cand_all = cand_all; a.q_f32 = s.q_f32; a.q_norm = s.q_norm;
-  a.q_flags = s.q_flags;
+  a.do_route = p.do_route; a.cand_all = cand_all; a.q_f32 = s.q_f32[s.slot]; a.q_norm = s.q_norm[s.slot];
+  a.q_flags = s.q_flags[s.slot];
   a.centroids = s.centroids; a.cent_norm = s.cent_norm; a.cent_owner = s.cent_owner;
   a.perf_health = s.perf_health; a.tok = tok; a.heur_dev = heur_dev; a.heur_conf = heur_conf; a.p = p;
   a.out = out;

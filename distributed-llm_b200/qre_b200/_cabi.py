@@ -44,7 +44,7 @@ class Params(C.Structure):
         ("scan_mode", C.c_int32), ("do_route", C.c_int32), ("n_devices", C.c_int32),
         ("token_threshold", C.c_int32), ("w_token", C.c_double), ("w_semantic", C.c_double),
         ("w_heuristic", C.c_double), ("w_perf", C.c_double), ("sem_min_similarity", C.c_double),
-        ("sem_margin_threshold", C.c_double),
+        ("sem_margin_threshold", C.c_double), ("pipeline_slot", C.c_int32), ("reserve_sms", C.c_int32),
     ]
 
 
@@ -113,12 +113,14 @@ class RouteConfig:
     sem_min_similarity: float = 0.05
     sem_margin_threshold: float = 0.03
     scan_mode: int = SCAN_TENSOR
+    pipeline_slot: int = 0
+    reserve_sms: int = 0
 
     def to_c(self, now_us: int, do_route: bool) -> Params:
         return Params(self.similarity_threshold, int(now_us), int(self.ttl_us), self.scan_mode,
                       1 if do_route else 0, self.n_devices, self.token_threshold, self.w_token,
                       self.w_semantic, self.w_heuristic, self.w_perf, self.sem_min_similarity,
-                      self.sem_margin_threshold)
+                      self.sem_margin_threshold, self.pipeline_slot, self.reserve_sms)
 
 
 class Shard:

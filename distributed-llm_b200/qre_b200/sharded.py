@@ -9,6 +9,12 @@ other disjoint subset; queries and per-query features are replicated.  Per batch
 
 torch is plumbing here: device buffers, streams and the NCCL collective.  With world == 1 the
 collective is skipped.  CPU tests drive `merge_candidates_host` over gloo instead.
+
+`step_pipelined` overlaps the exchange with compute: the all-gather + merge of batch i run on a
+side stream while the scan of batch i+1 runs on the main stream.  The scan kernel is persistent
+(one CTA per SM, all shared memory), so it leaves `reserve_sms` SMs free for the side stream's
+kernels; candidate buffers, outputs and the handle's per-batch query state are double-buffered
+(`pipeline_slot`).
 """
 from __future__ import annotations
 
@@ -43,26 +49,87 @@ def merge_candidates_host(cand_all: np.ndarray) -> np.ndarray:
 
 class ShardedLookup:
     def __init__(self, shard: _cabi.Shard, cfg: _cabi.RouteConfig, rank: int = 0, world: int = 1,
-                 group=None):
+                 group=None, reserve_sms: int = 8):
+        import copy
         import torch
         self.torch = torch
         self.shard, self.cfg, self.rank, self.world, self.group = shard, cfg, rank, world, group
         self.dev = torch.device("cuda", shard.device)
         mb = shard.max_batch
-        self.cand = torch.empty(mb * _cabi.TOPK * 32, dtype=torch.uint8, device=self.dev)
-        self.cand_all = (torch.empty(world * mb * _cabi.TOPK * 32, dtype=torch.uint8, device=self.dev)
-                         if world > 1 else self.cand)
+        nb = mb * _cabi.TOPK * 32
+        self.cand2 = [torch.empty(nb, dtype=torch.uint8, device=self.dev) for _ in range(2)]
+        self.cand_all2 = ([torch.empty(world * nb, dtype=torch.uint8, device=self.dev) for _ in range(2)]
+                          if world > 1 else self.cand2)
+        self.cand, self.cand_all = self.cand2[0], self.cand_all2[0]
         self.ovf = torch.zeros(1, dtype=torch.int32, device=self.dev)
         self.out = None
+        # pipelined mode
+        self.out2 = [None, None]
+        self.cfg2 = []
+        for b in range(2):
+            c = copy.copy(cfg)
+            c.pipeline_slot, c.reserve_sms = b, reserve_sms
+            self.cfg2.append(c)
+        self.side = None
+        self.done = [None, None]
+        self.iter = 0
 
-    def _alloc_out(self, m: int):
+    def _new_out(self, m: int):
         torch = self.torch
         K, D = max(1, self.shard.n_centroids), self.cfg.n_devices
         out = {}
         for f, (dt, tail) in RESULT_SPECS.items():
             shape = (m,) + tuple({"K": K, "D": D}[t] for t in tail)
             out[f] = torch.empty(shape, dtype=getattr(torch, dt), device=self.dev)
-        self.out = out
+        return out
+
+    def _alloc_out(self, m: int):
+        self.out = self._new_out(m)
+
+    def step_pipelined(self, q, q_ctx, now_us: int, tok=None, heur_dev=None, heur_conf=None):
+        """Like `step`, but the exchange + merge of this batch are queued on a side stream so the
+        NEXT call's scan overlaps them.  Returns (outputs, event): the outputs are valid once
+        `event` has completed (`event.synchronize()` or `stream.wait_event(event)`)."""
+        torch = self.torch
+        m = q.shape[0]
+        b = self.iter & 1
+        self.iter += 1
+        if self.side is None:
+            self.side = torch.cuda.Stream(device=self.dev)
+        if self.out2[b] is None or self.out2[b]["hit_slot"].shape[0] != m:
+            self.out2[b] = self._new_out(m)
+        main = torch.cuda.current_stream(self.dev)
+        if self.done[b] is not None:
+            main.wait_event(self.done[b])            # slot b (batch i-2) fully consumed
+        cfg = self.cfg2[b]
+        nbytes = m * _cabi.TOPK * 32
+        self.shard.scan_dev(m, q.data_ptr(), q_ctx.data_ptr(), cfg, now_us, self.rank,
+                            self.cand2[b].data_ptr(), 0, main.cuda_stream or 1)
+        scanned = torch.cuda.Event()
+        scanned.record(main)
+        self.side.wait_event(scanned)
+        with torch.cuda.stream(self.side):
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.all_gather_into_tensor(self.cand_all2[b][: self.world * nbytes], self.cand2[b][:nbytes],
+                                            group=self.group)
+            out = self.out2[b]
+            self.shard.merge_route_dev(
+                m, self.world, self.cand_all2[b].data_ptr(), cfg, now_us, {f: t.data_ptr() for f, t in out.items()},
+                tok_ptr=0 if tok is None else tok.data_ptr(),
+                heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
+                heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=self.side.cuda_stream)
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+        self.done[b] = ev
+        return out, ev
+
+    def drain(self):
+        """Make the current stream wait for every pipelined batch issued so far."""
+        main = self.torch.cuda.current_stream(self.dev)
+        for ev in self.done:
+            if ev is not None:
+                main.wait_event(ev)
 
     def step(self, q, q_ctx, now_us: int, tok=None, heur_dev=None, heur_conf=None, check_overflow=False):
         """q: float32 [m, dim] cuda tensor; q_ctx: int64 view of the u64 ids.  Enqueues on the

@@ -88,6 +88,11 @@ typedef struct {
   double  w_perf;                   /* 0 in the reference; added term w_perf * H[dev] */
   double  sem_min_similarity;       /* 0.05 — qre:129 */
   double  sem_margin_threshold;     /* 0.03 — qre:128 */
+  int32_t pipeline_slot;            /* 0 or 1: which copy of the per-batch query state this call uses.
+                                       qre_scan_dev(slot) and the qre_merge_route_dev(slot) of the SAME batch
+                                       pass the same value; alternate it between batches to overlap the merge of
+                                       batch i (another stream) with the scan of batch i+1.  0 otherwise. */
+  int32_t reserve_sms;              /* SMs the scan leaves free for kernels running beside it (0 = none) */
 } qre_params_t;
 
 /* Per-query outputs, struct-of-arrays.  Any pointer may be NULL (not wanted).

@@ -29,7 +29,7 @@ def test_header_symbols_all_exported():
 
 def test_struct_layout_matches_header():
     assert _cabi.CAND_DTYPE.itemsize == 32
-    assert ctypes.sizeof(_cabi.Params) == 8 * 3 + 4 * 4 + 8 * 6
+    assert ctypes.sizeof(_cabi.Params) == 8 * 3 + 4 * 4 + 8 * 6 + 4 * 2
     assert ctypes.sizeof(_cabi.Result) == 8 * len(_cabi.RESULT_FIELDS)
 
 

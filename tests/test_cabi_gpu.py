@@ -258,3 +258,40 @@ def test_config4_768d_64_centroids_16_devices_perf_term():
     np.testing.assert_allclose(out["conf"][ok], r["conf"][ok], rtol=REL, atol=4e-6)
     assert len(np.unique(r["dev"])) > 3
     sh.close()
+
+
+def test_pipelined_slots_single_gpu(small):
+    """Double-buffered query state: the merge of batch i on a side stream while the scan of batch
+    i+1 runs must give the serial results (world = 1: no collective, same code path otherwise)."""
+    import torch
+    from qre_b200.sharded import ShardedLookup
+    w = small
+    sh = _load(w)
+    dev = torch.device("cuda", 0)
+    look = ShardedLookup(sh, _cabi.RouteConfig(ttl_us=w.ttl_us), 0, 1, reserve_sms=8)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)   # noqa: E731
+    perms = [np.random.Generator(np.random.PCG64(s_)).permutation(300) for s_ in range(4)]
+    ins = [(t(w.queries[pm]), t(w.q_ctx[pm].view(np.int64)), t(w.tok[pm]), t(w.heur_dev[pm]), t(w.heur_conf[pm]))
+           for pm in perms]
+    serial = []
+    for a, b, c, d, e in ins:
+        o = look.step(a, b, w.now_us, c, d, e)
+        torch.cuda.synchronize()
+        serial.append({k: v.cpu().numpy().copy() for k, v in o.items()})
+    exp_row, _ = _oracle_scan(w)
+    assert np.array_equal(serial[0]["hit_slot"], exp_row[perms[0]])
+    torch.cuda.synchronize()
+    got = []
+    for i, (a, b, c, d, e) in enumerate(ins):
+        o, ev = look.step_pipelined(a, b, w.now_us, c, d, e)
+        if i >= 1:      # consume batch i-1 before its buffers are reused by batch i+1
+            po, pev = prev
+            pev.synchronize()
+            got.append({k: v.cpu().numpy().copy() for k, v in po.items()})
+        prev = (o, ev)
+    prev[1].synchronize()
+    got.append({k: v.cpu().numpy().copy() for k, v in prev[0].items()})
+    for i in range(4):
+        for k in ("hit_slot", "hit_sim", "dev", "conf", "score", "sem_method", "flags"):
+            assert np.array_equal(got[i][k], serial[i][k]), (i, k)
+    sh.close()

@@ -47,6 +47,27 @@ def _worker(rank, world, port, ret):
           and np.allclose(out["hit_sim"].cpu().numpy()[hit], exp_sim[hit], rtol=1e-5)
           and np.array_equal(out["hit_pred_dev"].cpu().numpy()[hit], w.row_pred_dev[exp_row[hit]])
           and float(np.mean(out["dev"].cpu().numpy() == r["dev"])) > 0.995)
+    # pipelined: three different batches in flight back to back must each equal the serial result
+    perms = [np.random.Generator(np.random.PCG64(s_)).permutation(300) for s_ in range(3)]
+    serial, piped = [], []
+    for pm in perms:
+        o = look.step(t(w.queries[pm]), t(w.q_ctx[pm].view(np.int64)), w.now_us, t(w.tok[pm]), t(w.heur_dev[pm]),
+                      t(w.heur_conf[pm]))
+        torch.cuda.synchronize()
+        serial.append({k: v.cpu().numpy().copy() for k, v in o.items()})
+    ins = [(t(w.queries[pm]), t(w.q_ctx[pm].view(np.int64)), t(w.tok[pm]), t(w.heur_dev[pm]), t(w.heur_conf[pm]))
+           for pm in perms]
+    torch.cuda.synchronize()
+    handles = [look.step_pipelined(a, b, w.now_us, c, d, e) for a, b, c, d, e in ins]
+    for i, (o, ev) in enumerate(handles):
+        if i < 2:          # buffers of batch i are reused by batch i+2: read before that (here: only 3)
+            pass
+    # with 3 batches, batch 0's buffers were reused by batch 2; check batches 1 and 2
+    for i in (1, 2):
+        o, ev = handles[i]
+        ev.synchronize()
+        for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf", "score", "sem_method"):
+            ok = ok and np.array_equal(o[k].cpu().numpy(), serial[i][k])
     ret[rank] = (bool(ok), int(hit.sum()))
     dist.barrier()
     dist.destroy_process_group()
