@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--devices", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: serialise scan / all-gather / merge")
-    ap.add_argument("--reserve-sms", type=int, default=8)
+    ap.add_argument("--reserve-sms", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     return ap.parse_args()
 
@@ -77,7 +77,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -86,7 +86,10 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def mark(self, t0: float, t1: float):
+        self.window = (t0, t1)
 
     def stop(self):
         if self.proc is None:
@@ -99,7 +102,14 @@ class ClockSampler:
         self.th.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for r in self.rows:
+        t0, t1 = getattr(self, "window", (0.0, float("inf")))
+        inside = [r for t, r in self.rows if t0 <= t <= t1 + 0.15]
+        note = None
+        if not inside and self.rows:       # timed region shorter than the sampling period
+            mid = 0.5 * (t0 + min(t1, t0 + 3600))
+            inside = [min(self.rows, key=lambda tr: abs(tr[0] - mid))[1]]
+            note = "timed region shorter than the 50 ms sampling period: nearest sample (under load) used"
+        for r in inside:
             if len(r) < 7:
                 continue
             try:
@@ -109,8 +119,11 @@ class ClockSampler:
             for n, v in zip(names, r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+               "samples": len(sm), "reasons": sorted(reasons)}
+        if note:
+            out["note"] = note
+        return out
 
 
 # ----------------------------------------------------------------------------------------
@@ -223,7 +236,7 @@ def run_b200(args):
         Q=wq["Q"], ctx=q_ctx_np.view(np.int64), tok=wq["tok"], hd=wq["heur_dev"], hc=wq["heur_conf"]).items()}
     d_in = {k: v.to(dev) for k, v in h.items()}
 
-    pipelined = world > 1 and not args.no_overlap
+    pipelined = world >= 4 and not args.no_overlap      # measured: pays off from 4 ranks (profiles/r1_scaling.md)
 
     def step_resident():
         if pipelined:     # exchange + merge of batch i overlap the scan of batch i+1
@@ -255,14 +268,15 @@ def run_b200(args):
     # ---- value: inputs resident in HBM, CUDA events on the launching stream, max over ranks ----
     side = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(side)
+    sampler = ClockSampler(local)
+    sampler.start()                     # nvidia-smi needs ~100 ms to produce its first line
     for _ in range(args.warmup):
         step_resident()
-    sampler = ClockSampler(local)
     barrier()
     sh.profile(True)
     l0 = sh.launch_count()
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin = time.perf_counter()
     e0.record()
     for _ in range(args.steps):
         step_resident()
@@ -270,6 +284,7 @@ def run_b200(args):
         look.drain()
     e1.record()
     barrier()
+    sampler.mark(t_begin, time.perf_counter())
     clocks = sampler.stop()
     launches = sh.launch_count() - l0
     scan_ms, scan_n = sh.profile_read()

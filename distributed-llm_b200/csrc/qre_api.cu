@@ -189,7 +189,9 @@ int scan_enqueue(qre_cache_t* h, int m, const float* q_dev, const uint64_t* q_ct
   if (p.scan_mode == QRE_SCAN_TENSOR && h->hwm > 0) {
     h->launches += launch_gemm_topk(s, m, h->hwm, h->d_q_ctx, p, nullptr, 0, 0, 0, st);
     h->launches += launch_rescore(s, m, h->hwm, p, shard, cand, st);
+    h->launches += launch_overflow_settle(s, h->hwm, h->d_q_ctx, p, shard, cand, st);
   } else {
+    QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
     h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, nullptr, m, false, p, shard, cand, st);
   }
   QRE_CUDA(cudaGetLastError());
@@ -288,6 +290,9 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
   s.exact_grid = s.num_sms * 2;
   QRE_ALLOC(s.exact_partial, sizeof(ExactBest) * (size_t)kExactGroup * s.exact_grid);
   QRE_ALLOC(s.ovf_count, sizeof(int32_t));
+  QRE_ALLOC(s.ovf_unresolved, sizeof(int32_t));
+  QRE_ALLOC(s.settle_tickets, sizeof(unsigned) * kSettleMaxGroups);
+  QRE_ALLOC(s.settle_partial, sizeof(ExactBest) * (size_t)kSettleMaxGroups * kExactGroup * s.exact_grid);
   QRE_ALLOC(s.ovf_list, sizeof(int32_t) * (size_t)max_batch);
   QRE_ALLOC(s.centroids, sizeof(float) * (size_t)QRE_MAX_CENTROIDS * dim_pad);
   QRE_ALLOC(s.cent_norm, sizeof(float) * QRE_MAX_CENTROIDS);
@@ -312,6 +317,9 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.q_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.perf_health, 0, sizeof(double) * QRE_MAX_DEVICES, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.settle_tickets, 0, sizeof(unsigned) * kSettleMaxGroups, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), s.stream));
     for (int b = 0; b < 2; ++b) QRE_CUDA(cudaMemsetAsync(s.q_flags[b], 0, (size_t)max_batch, s.stream));
     QRE_CUDA(gemm_topk_init());
     EncodeTiledFn enc = nullptr;
@@ -337,7 +345,7 @@ int qre_cache_destroy(qre_cache_t* h) {
   DeviceState& s = h->s;
   if (s.stream) cudaStreamSynchronize(s.stream);
   void* dev_ptrs[] = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf, s.q_f32[0],
-                      s.q_f32[1], s.q_bf16, s.q_norm[0], s.q_norm[1], s.partial, s.exact_partial, s.ovf_count,
+                      s.q_f32[1], s.q_bf16, s.q_norm[0], s.q_norm[1], s.partial, s.exact_partial, s.ovf_count, s.ovf_unresolved, s.settle_tickets, s.settle_partial,
                       s.ovf_list, s.q_flags[0], s.q_flags[1],
                       s.centroids, s.cent_norm, s.cent_owner, s.perf_health, h->d_stage, h->d_in, h->d_res,
                       h->d_cand, h->d_q_ctx, h->d_dump};
@@ -597,7 +605,7 @@ int qre_scan_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_
   int rc = scan_enqueue(h, m, queries, q_ctx, *params, shard, cand_out, st);
   if (rc != QRE_OK) return rc;
   if (overflow_count)
-    QRE_CUDA(cudaMemcpyAsync(overflow_count, h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    QRE_CUDA(cudaMemcpyAsync(overflow_count, h->s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   return QRE_OK;
 }
 
@@ -607,15 +615,17 @@ int qre_resolve_overflow_dev(qre_cache_t* h, int m, const qre_params_t* params, 
   if (m != h->last_m) return fail(QRE_ERR_INVALID, "m=%d does not match the last scan (%d)", m, h->last_m);
   DeviceGuard guard(h->s.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
-  int32_t n_ovf = 0;
-  QRE_CUDA(cudaMemcpyAsync(&n_ovf, h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  int32_t cnt[2] = {0, 0};
+  QRE_CUDA(cudaMemcpyAsync(&cnt[0], h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  QRE_CUDA(cudaMemcpyAsync(&cnt[1], h->s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   QRE_CUDA(cudaStreamSynchronize(st));
-  if (n_ovf <= 0) return QRE_OK;
+  const int32_t n_ovf = cnt[0];
+  if (cnt[1] <= 0 || n_ovf <= 0) return QRE_OK;
   h->s.slot = params->pipeline_slot & 1;
   h->launches += launch_exact_scan(h->s, m, h->hwm, h->d_q_ctx, h->s.ovf_list, n_ovf, true, *params, shard,
                                    cand_inout, st);
   QRE_CUDA(cudaGetLastError());
-  QRE_CUDA(cudaMemsetAsync(h->s.ovf_count, 0, sizeof(int32_t), st));
+  QRE_CUDA(cudaMemsetAsync(h->s.ovf_unresolved, 0, sizeof(int32_t), st));
   return QRE_OK;
 }
 
@@ -675,16 +685,18 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
   for (int pass = 0; pass < 2; ++pass) {
     h->launches += launch_merge_route(s, m, 1, h->d_cand, d_tok, d_hd, d_hc, p, dres, st);
     QRE_CUDA(cudaGetLastError());
-    QRE_CUDA(cudaMemcpyAsync(h->d_res + L.ovf.off, s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    QRE_CUDA(cudaMemcpyAsync(h->d_res + L.ovf.off, s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
     QRE_CUDA(cudaMemcpyAsync(h->h_res, h->d_res, L.total, cudaMemcpyDeviceToHost, st));
     QRE_CUDA(cudaStreamSynchronize(st));
-    const int32_t n_ovf = *reinterpret_cast<const int32_t*>(h->h_res + L.ovf.off);
-    if (n_ovf <= 0 || pass == 1) break;
-    // rare: some query had more than QRE_TOPK contenders inside the bf16 error window of one
-    // row range; settle those queries with the exact fp32 scan and merge again.
+    const int32_t n_left = *reinterpret_cast<const int32_t*>(h->h_res + L.ovf.off);
+    if (n_left <= 0 || pass == 1) break;
+    // very rare: more overflowed queries than the device-side fallback settles per batch (512).
+    // Settle all of them with host-driven brute-force passes and merge again.
+    int32_t n_ovf = 0;
+    QRE_CUDA(cudaMemcpy(&n_ovf, s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost));
     h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, s.ovf_list, n_ovf, true, p, 0, h->d_cand, st);
     QRE_CUDA(cudaGetLastError());
-    QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), st));
+    QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
   }
   const qre_result_t hres = L.view(h->h_res);
 #define QRE_OUT(field, bytes) \

@@ -18,6 +18,8 @@ constexpr int kMaxKB = 6;         // resident-A variant: dim_pad <= 384
 constexpr int kMaxKBStream = 16;  // streaming-A variant: dim_pad <= 1024
 constexpr int kTopK = QRE_TOPK;
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+constexpr int kExactGroup = 8;        // queries per brute-force pass
+constexpr int kSettleMaxGroups = 64;  // overflowed queries settled on the device per batch: 512
 constexpr float kNormEps = 1e-9f;                 // src/cache.py:284,289 ; qre:136
 
 // |approx - cosine| bound of the bf16 tensor-core score: two bf16 roundings (2^-9 each)
@@ -91,7 +93,10 @@ struct DeviceState {
   long long partial_entries = 0;
   ExactBest* exact_partial = nullptr; // [kExactGroup * exact_grid]
   int exact_grid = 0;
-  int32_t* ovf_count = nullptr;       // [1]
+  int32_t* ovf_count = nullptr;       // [1]  queries whose candidate window overflowed (this batch)
+  int32_t* ovf_unresolved = nullptr;  // [1]  of those, not settled by the device-side fallback
+  unsigned* settle_tickets = nullptr; // [kSettleMaxGroups]
+  ExactBest* settle_partial = nullptr;  // [kSettleMaxGroups][kExactGroup][exact_grid]
   int32_t* ovf_list = nullptr;        // [max_batch]
   uint8_t* q_flags[2] = {nullptr, nullptr};  // [max_batch]  QRE_FLAG_* of the batch in each slot
   // router state
@@ -108,7 +113,6 @@ struct DeviceState {
 };
 constexpr int kProfMax = 2048;
 
-constexpr int kExactGroup = 8;        // queries per brute-force pass
 
 // ---- launch wrappers (qre_kernels.cu / qre_gemm_topk.cu); each returns #launches --------
 int launch_append(DeviceState& s, long long n, const float* rows_dev, long long rows_ld, const int64_t* slot_dev,
@@ -129,6 +133,8 @@ int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& 
 int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const int32_t* qlist_dev,
                       int nq_total, bool use_ovf_list, const qre_params_t& p, int shard, qre_candidate_t* cand,
                       cudaStream_t st);
+int launch_overflow_settle(DeviceState& s, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p, int shard,
+                           qre_candidate_t* cand, cudaStream_t st);
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
                        const qre_result_t& out, cudaStream_t st);

@@ -334,11 +334,18 @@ struct ExactArgs {
 constexpr int kExactWarps = 8;
 constexpr int kExactMaxIt = 8;  // dim_pad <= 1024
 
-__global__ void __launch_bounds__(kExactWarps * 32) exact_scan_kernel(const ExactArgs a) {
-  extern __shared__ float qs[];                     // [kExactGroup, dim_pad]
-  __shared__ float s_nq[kExactGroup];
-  __shared__ uint64_t s_ctx[kExactGroup];
-  __shared__ ExactBest s_best[kExactWarps][kExactGroup];
+struct ExactSmem {
+  float nq[kExactGroup];
+  uint64_t ctx[kExactGroup];
+  ExactBest best[kExactWarps][kExactGroup];
+};
+
+// One CTA's share of a brute-force pass: stage the group's queries, scan rows [r0, r1) of this
+// CTA's slice, leave the per-query winners in a.partial[query][blockIdx.x].
+__device__ __forceinline__ void exact_scan_body(const ExactArgs& a, float* qs, ExactSmem& sm) {
+  float* s_nq = sm.nq;
+  uint64_t* s_ctx = sm.ctx;
+  ExactBest (*s_best)[kExactGroup] = sm.best;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int j = 0; j < a.nq; ++j) {
     const int q = a.qlist ? a.qlist[a.q_first + j] : a.q_first + j;
@@ -406,15 +413,27 @@ __global__ void __launch_bounds__(kExactWarps * 32) exact_scan_kernel(const Exac
   }
 }
 
-__global__ void exact_reduce_kernel(int nq, int q_first, const int32_t* qlist, int grid, const ExactBest* partial,
-                                    int shard, const uint8_t* pdev, const double* pconf, const float* q_norm,
-                                    qre_candidate_t* cand, uint8_t* q_flags, uint8_t extra_flag) {
+__global__ void __launch_bounds__(kExactWarps * 32) exact_scan_kernel(const ExactArgs a) {
+  extern __shared__ float qs[];                     // [kExactGroup, dim_pad]
+  __shared__ ExactSmem sm;
+  exact_scan_body(a, qs, sm);
+}
+
+// Cross-CTA reduction of one group's partial winners -> cand[q][0] (warp j handles query j).
+__device__ __forceinline__ void exact_reduce_body(int nq, int q_first, const int32_t* qlist, int grid,
+                                                  const ExactBest* partial, int shard, const uint8_t* pdev,
+                                                  const double* pconf, const float* q_norm,
+                                                  qre_candidate_t* cand, uint8_t* q_flags, uint8_t extra_flag) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp >= nq) return;
   const int q = qlist ? qlist[q_first + warp] : q_first + warp;
   ExactBest b{-INFINITY, kNoRow, ~0ull};
   for (int i = lane; i < grid; i += 32) {
-    const ExactBest c = partial[static_cast<long long>(warp) * grid + i];
+    const ExactBest* pp = &partial[static_cast<long long>(warp) * grid + i];
+    ExactBest c;                                    // may have been written by another CTA of this launch
+    c.sim = __ldcg(&pp->sim);
+    c.row = __ldcg(&pp->row);
+    c.lru = __ldcg(&pp->lru);
     if (c.row != kNoRow && (b.row == kNoRow || cand_better(c.sim, c.lru, b.sim, b.lru))) b = c;
   }
 #pragma unroll
@@ -437,6 +456,66 @@ __global__ void exact_reduce_kernel(int nq, int q_first, const int32_t* qlist, i
     cand[static_cast<long long>(q) * kTopK + lane] = c;
   }
   if (lane == 0) q_flags[q] = extra_flag | (q_norm[q] < kNormEps ? QRE_FLAG_ZERO_NORM : 0);
+}
+
+__global__ void exact_reduce_kernel(int nq, int q_first, const int32_t* qlist, int grid, const ExactBest* partial,
+                                    int shard, const uint8_t* pdev, const double* pconf, const float* q_norm,
+                                    qre_candidate_t* cand, uint8_t* q_flags, uint8_t extra_flag) {
+  exact_reduce_body(nq, q_first, qlist, grid, partial, shard, pdev, pconf, q_norm, cand, q_flags, extra_flag);
+}
+
+// Device-driven overflow settlement: ONE launch after rescore_kernel, no host round trip.  Reads
+// the overflow counter the re-score pass left on the device; exits at once when it is zero (the
+// normal case); otherwise runs the brute-force pass for up to kSettleMaxGroups groups of 8
+// overflowed queries, the last CTA of each group (ticket counter) doing the reduction.
+// *unresolved = overflowed queries beyond that capacity (the host API settles those).
+struct SettleArgs {
+  ExactArgs base;                 // nq / q_first / partial filled per group
+  const int32_t* ovf_count;
+  const int32_t* ovf_list;
+  int32_t* unresolved;
+  unsigned* tickets;              // [kSettleMaxGroups], zero between launches
+  ExactBest* partial;             // [kSettleMaxGroups][kExactGroup][gridDim.x]
+  int shard;
+  const uint8_t* pdev;
+  const double* pconf;
+  qre_candidate_t* cand;
+  uint8_t* q_flags;
+};
+
+__global__ void __launch_bounds__(kExactWarps * 32) overflow_settle_kernel(const SettleArgs sa) {
+  extern __shared__ float qs[];
+  __shared__ ExactSmem sm;
+  __shared__ unsigned s_ticket;
+  const int n_ovf = *sa.ovf_count;
+  if (n_ovf <= 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *sa.unresolved = 0;
+    return;
+  }
+  const int groups_all = (n_ovf + kExactGroup - 1) / kExactGroup;
+  const int groups = groups_all < kSettleMaxGroups ? groups_all : kSettleMaxGroups;
+  for (int g = 0; g < groups; ++g) {
+    ExactArgs a = sa.base;
+    a.q_first = g * kExactGroup;
+    a.nq = n_ovf - a.q_first < kExactGroup ? n_ovf - a.q_first : kExactGroup;
+    a.qlist = sa.ovf_list;
+    a.partial = sa.partial + static_cast<long long>(g) * kExactGroup * gridDim.x;
+    __syncthreads();
+    exact_scan_body(a, qs, sm);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_ticket = atomicAdd(&sa.tickets[g], 1u);
+    __syncthreads();
+    if (s_ticket == gridDim.x - 1) {          // last CTA of this group: all partials are visible
+      __threadfence();
+      exact_reduce_body(a.nq, a.q_first, a.qlist, gridDim.x, a.partial, sa.shard, sa.pdev, sa.pconf, a.q_norm,
+                        sa.cand, sa.q_flags, QRE_FLAG_OVERFLOW);
+      if (threadIdx.x == 0) {
+        sa.tickets[g] = 0u;
+        if (g == groups - 1) *sa.unresolved = n_ovf - groups * kExactGroup > 0 ? n_ovf - groups * kExactGroup : 0;
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -706,6 +785,22 @@ int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q
     launches += 2;
   }
   return launches;
+}
+
+int launch_overflow_settle(DeviceState& s, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p, int shard,
+                           qre_candidate_t* cand, cudaStream_t st) {
+  SettleArgs sa;
+  ExactArgs& a = sa.base;
+  a.nq = 0; a.q_first = 0; a.qlist = s.ovf_list; a.n_rows = n_rows; a.dim_pad = s.dim_pad;
+  a.thr = p.similarity_threshold; a.now_us = p.now_us; a.ttl_us = p.ttl_us; a.q_f32 = s.q_f32[s.slot];
+  a.q_norm = s.q_norm[s.slot]; a.q_ctx = q_ctx; a.rows_f32 = s.rows_f32; a.row_norm = s.row_norm; a.meta = s.meta;
+  a.lru = s.lru; a.partial = nullptr;
+  sa.ovf_count = s.ovf_count; sa.ovf_list = s.ovf_list; sa.unresolved = s.ovf_unresolved;
+  sa.tickets = s.settle_tickets; sa.partial = s.settle_partial; sa.shard = shard; sa.pdev = s.pred_dev;
+  sa.pconf = s.pred_conf; sa.cand = cand; sa.q_flags = s.q_flags[s.slot];
+  const size_t smem = static_cast<size_t>(kExactGroup) * s.dim_pad * sizeof(float);
+  overflow_settle_kernel<<<s.exact_grid, kExactWarps * 32, smem, st>>>(sa);
+  return 1;
 }
 
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
