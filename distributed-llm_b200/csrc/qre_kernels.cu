@@ -557,7 +557,17 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   }
   __syncwarp();
   qre_candidate_t best0 = empty_cand();
-  for (int k = 0; k < kTopK; ++k) {
+  // Most queries have zero or one live candidate, and callers that do not ask for the merged
+  // list only need the winner: run only as many selection rounds as can produce something.
+  int n_valid = 0;
+  for (int i = lane; i < n_cand; i += 32) n_valid += sc[i].slot >= 0 ? 1 : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_xor_sync(kFull, n_valid, o);
+  const int want = a.out.cand != nullptr ? kTopK : 1;
+  const int rounds = n_valid < want ? n_valid : want;
+  if (a.out.cand != nullptr && lane >= rounds && lane < kTopK)
+    a.out.cand[static_cast<long long>(q) * kTopK + lane] = empty_cand();
+  for (int k = 0; k < rounds; ++k) {
     int bi = -1;
     float bs = -INFINITY;
     uint64_t bl = ~0ull;

@@ -295,3 +295,36 @@ def test_pipelined_slots_single_gpu(small):
         for k in ("hit_slot", "hit_sim", "dev", "conf", "score", "sem_method", "flags"):
             assert np.array_equal(got[i][k], serial[i][k]), (i, k)
     sh.close()
+
+
+def test_many_overflowed_queries_settled_on_device():
+    """20 queries, each facing 12 near-identical rows: three groups of the device-side fallback;
+    the async device pipeline (no host check) must return the exact-scan answers on its own."""
+    import torch
+    from qre_b200.sharded import ShardedLookup
+    d, nq, per = 384, 20, 12
+    rs = np.random.Generator(np.random.PCG64(12))
+    base = rs.standard_normal((nq, d)).astype(np.float32)
+    rows = np.repeat(base, per, axis=0) + rs.standard_normal((nq * per, d)).astype(np.float32) * np.float32(2e-4)
+    filler = rs.standard_normal((3000, d)).astype(np.float32)
+    rows = np.concatenate([rows, filler])
+    n = rows.shape[0]
+    ctx = np.full(n, 3, np.uint64)
+    lru = rs.permutation(n).astype(np.uint64) + np.uint64(1)
+    sh = _cabi.Shard(dim=d, capacity=n, max_batch=32)
+    sh.append(rows, ctx, np.zeros(n, np.int64), lru, np.zeros(n, np.uint8), np.ones(n))
+    q = np.concatenate([base, rs.standard_normal((4, d)).astype(np.float32)])       # 4 plain misses
+    qc = np.full(q.shape[0], 3, np.uint64)
+    out_e = sh.lookup_route(q, qc, _cabi.RouteConfig(ttl_us=10**9, scan_mode=_cabi.SCAN_EXACT), now_us=1)
+    out_t = sh.lookup_route(q, qc, _cabi.RouteConfig(ttl_us=10**9), now_us=1)
+    assert np.all(out_t["flags"][:nq] & _cabi.FLAG_OVERFLOW) and not np.any(out_t["flags"][nq:] & _cabi.FLAG_OVERFLOW)
+    assert np.array_equal(out_t["hit_slot"], out_e["hit_slot"]) and np.array_equal(out_t["hit_sim"], out_e["hit_sim"])
+    assert np.all(out_e["hit_slot"][:nq] >= 0) and np.all(out_e["hit_slot"][nq:] == -1)
+    dev = torch.device("cuda", 0)
+    look = ShardedLookup(sh, _cabi.RouteConfig(ttl_us=10**9), 0, 1)
+    o = look.step(torch.from_numpy(q).to(dev), torch.from_numpy(qc.view(np.int64)).to(dev), 1)
+    torch.cuda.synchronize()
+    assert np.array_equal(o["hit_slot"].cpu().numpy(), out_e["hit_slot"])
+    assert np.array_equal(o["hit_sim"].cpu().numpy(), out_e["hit_sim"])
+    assert int(look.ovf.item()) == 0            # nothing left for the host to settle
+    sh.close()
