@@ -341,12 +341,27 @@ class QueryCache:
         """Additive batch form: every query is scored against ONE snapshot of the cache (a
         single device pass), then hits are applied in order.  Equals a loop of `lookup` unless
         an earlier hit's LRU promotion would change a later tie-break."""
+        return self._batch_pass(queries, context_keys, q_embs, None, None)[0]
+
+    def _batch_pass(self, queries: List[str], context_keys: List[str], q_embs: np.ndarray,
+                    route_in: Optional[dict], route_cfg: Optional[_cabi.RouteConfig]):
+        """Snapshot lookup of a whole batch (+ routing epilogue when `route_in` is given) in one
+        device pass per `max_batch` chunk.  Returns (results, device outputs)."""
         with self._lock:
             now = datetime.now()
             self._evict_expired(now)
             q_embs = np.ascontiguousarray(q_embs, np.float32)
             ctx = np.array([self._ctx_id(c) for c in context_keys], np.uint64)
-            out = self._engine.scan(q_embs, ctx, _to_us(now), self._cfg())
+            cfg = route_cfg if route_cfg is not None else self._cfg()
+            cfg.similarity_threshold = float(self.similarity_threshold)
+            cfg.ttl_us = self._ttl_us()
+            step = max(1, int(getattr(self._engine, "max_batch", 64)))
+            outs = []
+            for i0 in range(0, len(queries), step):
+                sl = slice(i0, min(len(queries), i0 + step))
+                ri = None if route_in is None else {k: v[sl] for k, v in route_in.items()}
+                outs.append(self._engine.scan(q_embs[sl], ctx[sl], _to_us(now), cfg, ri))
+            out = {k: np.concatenate([o[k] for o in outs]) for k in outs[0]} if outs else {}
             results: List[Optional[CacheLookupResult]] = []
             for i, (q, c) in enumerate(zip(queries, context_keys)):
                 self._attempts += 1
@@ -371,7 +386,7 @@ class QueryCache:
                 fb = pconf < self.prediction_confidence_threshold
                 self._hybrid_fallbacks += int(fb)
                 results.append(CacheLookupResult(entry, pdev, pconf, fb))
-            return results
+            return results, out
 
     def insert(self, query: str, context_key: str, device: str, confidence: float = 1.0,
                method: str = "unknown", q_emb: Optional[np.ndarray] = None,
@@ -477,6 +492,65 @@ class QueryCache:
                 loaded += 1
         logger.info("cache loaded %d entries from %s", loaded, path)
         return loaded
+
+    def save_snapshot(self, path: str) -> None:
+        """Binary companion of `save` for large caches: the device rows and row
+        metadata go to `<path>.rows` through qre_cache_snapshot_save (no float -> text), the
+        host-side state (queries, hashes, histories, LRU order, slots) to `<path>` as JSON
+        without embeddings."""
+        self._evict_expired()
+        with self._lock:
+            if self._engine.shard is None:
+                raise _cabi.QreError("nothing on the device to snapshot")
+            self._engine.shard.snapshot_save(path + ".rows")
+            entries = []
+            for e in self._store.values():
+                d = e.to_dict()
+                d["embedding"] = None
+                d["_slot"], d["_seq"] = e._slot, e._seq
+                entries.append(d)
+            meta = {"version": 1, "ctx_ids": self._ctx_ids, "seq": self._seq, "entries": entries,
+                    "dim": self._engine.shard.dim}
+        Path(path).write_text(json.dumps(meta), encoding="utf-8")
+
+    def load_snapshot(self, path: str) -> int:
+        """Restore a `save_snapshot` pair into an EMPTY cache; expired entries are dropped.
+        Returns the number of entries loaded."""
+        meta = json.loads(Path(path).read_text(encoding="utf-8"))
+        with self._lock:
+            if self._store:
+                raise ValueError("load_snapshot needs an empty cache")
+            eng = self._engine
+            need = max([(d["_slot"] or 0) + 1 for d in meta["entries"]] + [1])
+            if need > eng.capacity:
+                eng.close()
+                eng.capacity = need
+            sh = eng.ensure(int(meta["dim"]))
+            sh.clear()
+            sh.snapshot_load(path + ".rows")
+            self._ctx_ids = {k: int(v) for k, v in meta["ctx_ids"].items()}
+            self._seq = int(meta["seq"])
+            now = datetime.now()
+            stale = []
+            for d in meta["entries"]:
+                entry = CacheEntry.from_dict(d)
+                entry._slot, entry._seq = d["_slot"], int(d["_seq"])
+                if not self._is_valid(entry, now):
+                    if entry._slot is not None:
+                        stale.append(entry._slot)
+                    continue
+                self._store[entry.query_hash] = entry
+                if entry._slot is not None:
+                    self._slot_key[entry._slot] = entry.query_hash
+                heapq.heappush(self._exp_heap, (_to_us(entry.timestamp), entry.query_hash))
+            if stale:
+                eng.tombstone(stale)
+            live = [e for e in self._store.values() if e._slot is not None]
+            if live:
+                rows = eng.read_rows([e._slot for e in live])
+                for e, r in zip(live, rows):
+                    e.embedding = r.copy()
+            return len(self._store)
 
     def _ensure_capacity(self, need: int) -> None:
         """`load` may exceed max_size (reference quirk); rebuild the device store larger."""

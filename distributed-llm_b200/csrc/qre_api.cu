@@ -723,6 +723,127 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
   return QRE_OK;
 }
 
+// ---- binary snapshot -----------------------------------------------------
+// Layout: header | slot_live[hwm] | RowMeta[hwm] | lru[hwm] | pred_dev[hwm] | pred_conf[hwm] |
+// rows_f32[hwm][dim] (unpadded).  Dead slots are stored too (their contents are ignored on load).
+namespace {
+struct SnapHeader {
+  char magic[8];
+  int32_t version, dim;
+  int64_t hwm, live;
+};
+}  // namespace
+
+int qre_cache_snapshot_save(qre_cache_t* h, const char* path) {
+  if (h == nullptr || path == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  FILE* f = fopen(path, "wb");
+  if (f == nullptr) return fail(QRE_ERR_INVALID, "cannot open %s for writing", path);
+  SnapHeader hd;
+  memcpy(hd.magic, "QRESNAP1", 8);
+  hd.version = 1; hd.dim = s.dim; hd.hwm = h->hwm; hd.live = h->live;
+  const size_t n = (size_t)h->hwm;
+  bool ok = fwrite(&hd, sizeof(hd), 1, f) == 1;
+  if (n) ok = ok && fwrite(h->slot_live.data(), 1, n, f) == n;
+  int rc = QRE_OK;
+  auto dump = [&](const void* dev, size_t bytes) -> int {
+    std::vector<uint8_t> buf(bytes);
+    QRE_CUDA(cudaMemcpyAsync(buf.data(), dev, bytes, cudaMemcpyDeviceToHost, s.stream));
+    QRE_CUDA(cudaStreamSynchronize(s.stream));
+    ok = ok && (bytes == 0 || fwrite(buf.data(), 1, bytes, f) == bytes);
+    return QRE_OK;
+  };
+  if (n) {
+    if (rc == QRE_OK) rc = dump(s.meta, sizeof(RowMeta) * n);
+    if (rc == QRE_OK) rc = dump(s.lru, sizeof(uint64_t) * n);
+    if (rc == QRE_OK) rc = dump(s.pred_dev, n);
+    if (rc == QRE_OK) rc = dump(s.pred_conf, sizeof(double) * n);
+    const size_t chunk = std::max<size_t>(1, (32u << 20) / (sizeof(float) * s.dim));
+    std::vector<float> buf(chunk * s.dim);
+    for (size_t r0 = 0; r0 < n && rc == QRE_OK && ok; r0 += chunk) {
+      const size_t c = std::min(chunk, n - r0);
+      cudaError_t e = cudaMemcpy2DAsync(buf.data(), sizeof(float) * s.dim, s.rows_f32 + r0 * s.dim_pad,
+                                        sizeof(float) * s.dim_pad, sizeof(float) * s.dim, c,
+                                        cudaMemcpyDeviceToHost, s.stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+      if (e != cudaSuccess) { rc = fail(QRE_ERR_CUDA, "snapshot copy failed: %s", cudaGetErrorString(e)); break; }
+      ok = ok && fwrite(buf.data(), sizeof(float) * s.dim, c, f) == c;
+    }
+  }
+  ok = (fclose(f) == 0) && ok;
+  if (rc != QRE_OK) return rc;
+  if (!ok) return fail(QRE_ERR_INVALID, "short write to %s", path);
+  return QRE_OK;
+}
+
+int qre_cache_snapshot_load(qre_cache_t* h, const char* path) {
+  if (h == nullptr || path == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (h->hwm != 0) return fail(QRE_ERR_INVALID, "snapshot_load needs an empty cache (call qre_cache_clear)");
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  FILE* f = fopen(path, "rb");
+  if (f == nullptr) return fail(QRE_ERR_INVALID, "cannot open %s", path);
+  SnapHeader hd;
+  int rc = QRE_OK;
+  if (fread(&hd, sizeof(hd), 1, f) != 1 || memcmp(hd.magic, "QRESNAP1", 8) != 0 || hd.version != 1)
+    rc = fail(QRE_ERR_INVALID, "%s is not a qre snapshot", path);
+  else if (hd.dim != s.dim) rc = fail(QRE_ERR_INVALID, "snapshot dim %d != cache dim %d", hd.dim, s.dim);
+  else if (hd.hwm < 0 || hd.hwm > s.capacity)
+    rc = fail(QRE_ERR_CAPACITY, "snapshot holds %lld slots, capacity is %lld", (long long)hd.hwm, s.capacity);
+  if (rc != QRE_OK) { fclose(f); return rc; }
+  const size_t n = (size_t)hd.hwm;
+  std::vector<uint8_t> live(n);
+  std::vector<RowMeta> meta(n);
+  std::vector<uint64_t> lru(n);
+  std::vector<uint8_t> pdev(n);
+  std::vector<double> pconf(n);
+  bool ok = true;
+  if (n) {
+    ok = fread(live.data(), 1, n, f) == n && fread(meta.data(), sizeof(RowMeta), n, f) == n &&
+         fread(lru.data(), sizeof(uint64_t), n, f) == n && fread(pdev.data(), 1, n, f) == n &&
+         fread(pconf.data(), sizeof(double), n, f) == n;
+  }
+  const size_t chunk = std::max<size_t>(1, (32u << 20) / (sizeof(float) * s.dim));
+  std::vector<float> rows(chunk * s.dim), rows_c(chunk * s.dim);
+  std::vector<int64_t> slot;
+  std::vector<uint64_t> ctx_c, lru_c;
+  std::vector<int64_t> ts_c;
+  std::vector<uint8_t> pdev_c;
+  std::vector<double> pconf_c;
+  long long n_live = 0;
+  for (size_t r0 = 0; r0 < n && ok && rc == QRE_OK; r0 += chunk) {
+    const size_t c = std::min(chunk, n - r0);
+    ok = fread(rows.data(), sizeof(float) * s.dim, c, f) == c;
+    if (!ok) break;
+    slot.clear(); ctx_c.clear(); lru_c.clear(); ts_c.clear(); pdev_c.clear(); pconf_c.clear();
+    size_t k = 0;
+    for (size_t i = 0; i < c; ++i) {
+      const size_t g = r0 + i;
+      if (!live[g]) continue;
+      memcpy(rows_c.data() + k * s.dim, rows.data() + i * s.dim, sizeof(float) * s.dim);
+      slot.push_back((int64_t)g); ctx_c.push_back(meta[g].ctx); ts_c.push_back(meta[g].ts_us);
+      lru_c.push_back(lru[g]); pdev_c.push_back(pdev[g]); pconf_c.push_back(pconf[g]);
+      ++k;
+    }
+    if (k)
+      rc = staged_write(h, (int64_t)k, slot.data(), rows_c.data(), ctx_c.data(), ts_c.data(), lru_c.data(),
+                        pdev_c.data(), pconf_c.data());
+    n_live += (long long)k;
+  }
+  fclose(f);
+  if (rc != QRE_OK) return rc;
+  if (!ok) { qre_cache_clear(h); return fail(QRE_ERR_INVALID, "%s is truncated", path); }
+  h->hwm = hd.hwm;
+  h->live = n_live;
+  h->free_slots.clear();
+  for (size_t g = n; g-- > 0;) {
+    h->slot_live[g] = live[g];
+    if (!live[g]) h->free_slots.push_back((int64_t)g);
+  }
+  return QRE_OK;
+}
+
 int qre_profile(qre_cache_t* h, int enable) {
   if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
   DeviceGuard guard(h->s.device);

@@ -612,14 +612,43 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   __syncwarp();
   const float nq = a.q_norm[q];
   const float* qv = a.q_f32 + static_cast<long long>(q) * a.dim_pad;
-  for (int k = 0; k < a.n_centroids; ++k) {
-    const float dot = warp_dot(qv, a.centroids + static_cast<long long>(k) * a.dim_pad, a.dim_pad, lane);
+  // The query row stays in registers (dim_pad <= 1024 -> at most 8 float4 per lane) and the
+  // centroid loop is unrolled by 4 so the loads of independent centroids overlap; the summation
+  // order per centroid is warp_dot's (every exact score in the library uses it).
+  float4 qr[8];
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int i = lane * 4 + it * 128;
+    qr[it] = i < a.dim_pad ? *reinterpret_cast<const float4*>(qv + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int k0 = 0; k0 < a.n_centroids; k0 += 4) {
+    float dot[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float acc = 0.f;
+      if (k0 + u < a.n_centroids) {
+        const float* cv = a.centroids + static_cast<long long>(k0 + u) * a.dim_pad;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int i = lane * 4 + it * 128;
+          if (i < a.dim_pad) acc = lane_fma4(qr[it], __ldg(reinterpret_cast<const float4*>(cv + i)), acc);
+        }
+      }
+      dot[u] = acc;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) dot[u] = warp_sum(dot[u]);
     if (lane == 0) {
-      const float nc = a.cent_norm[k];
-      const float sim = (nq < kNormEps || nc < kNormEps) ? 0.f : exact_sim(dot, nq, nc);   // qre:135-138
-      if (a.out.centroid_sim) a.out.centroid_sim[static_cast<long long>(q) * a.n_centroids + k] = sim;
-      const int o = a.cent_owner[k];
-      if (sim > s_dsim[warp][o]) s_dsim[warp][o] = sim;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + u;
+        if (k >= a.n_centroids) break;
+        const float nc = a.cent_norm[k];
+        const float sim = (nq < kNormEps || nc < kNormEps) ? 0.f : exact_sim(dot[u], nq, nc);   // qre:135-138
+        if (a.out.centroid_sim) a.out.centroid_sim[static_cast<long long>(q) * a.n_centroids + k] = sim;
+        const int o = a.cent_owner[k];
+        if (sim > s_dsim[warp][o]) s_dsim[warp][o] = sim;
+      }
     }
   }
   if (lane != 0) return;

@@ -30,7 +30,7 @@ EXPORTS = (
     "qre_cache_tombstone", "qre_cache_clear", "qre_cache_read_rows", "qre_set_centroids",
     "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
-    "qre_exact_lookup_noalloc",
+    "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
 )
 
 
@@ -211,6 +211,12 @@ class Shard:
         out = np.empty((slots.shape[0], self.dim), np.float32)
         _check(self.lib, self.lib.qre_cache_read_rows(self.h, C.c_int64(slots.shape[0]), _ptr(slots), _ptr(out)))
         return out
+
+    def snapshot_save(self, path: str) -> None:
+        _check(self.lib, self.lib.qre_cache_snapshot_save(self.h, C.c_char_p(os.fsencode(path))))
+
+    def snapshot_load(self, path: str) -> None:
+        _check(self.lib, self.lib.qre_cache_snapshot_load(self.h, C.c_char_p(os.fsencode(path))))
 
     # ---- router state ----
     def set_centroids(self, centroids, owner) -> None:

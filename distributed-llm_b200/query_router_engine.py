@@ -516,6 +516,59 @@ class QueryRouter:
                                method=decision.method, q_emb=q_emb)
         return decision
 
+    def route_queries(self, queries: Sequence[str], contexts: Optional[Sequence[Optional[str]]] = None,
+                      context_keys: Optional[Sequence[Optional[str]]] = None,
+                      q_embs: Optional[np.ndarray] = None) -> List[RoutingDecision]:
+        """Additive batch entry point (the reference routes one query per call, qre:559): every
+        query of the batch is looked up against ONE snapshot of the cache and routed in a single
+        fused device pass; the hit / override / insert control flow of `route_query` is then
+        applied per query, in order, with all inserts after all lookups.  Equal to a loop of
+        `route_query` whenever no query of the batch would hit an entry inserted by an earlier
+        query of the same batch."""
+        n = len(queries)
+        contexts = list(contexts) if contexts is not None else [None] * n
+        ctxks = [(k or "default") for k in (context_keys if context_keys is not None else [None] * n)]
+        if not (self.cache_enabled and self._fusable()) or (q_embs is None and self.cache_embedder is None):
+            return [self.route_query(q, c, k) for q, c, k in zip(queries, contexts, ctxks)]
+        if q_embs is None:
+            q_embs = np.asarray(self.cache_embedder.encode(list(queries)), np.float32)
+        r = self.router
+        hybrid = isinstance(r, HybridRouter)
+        sem = r.routers["semantic"] if hybrid else r
+        feats = [r.features(q, c) if hybrid else (r._token_fallback.route(q, c), (0, 0.0, "", "", None))
+                 for q, c in zip(queries, contexts)]
+        route_in = dict(tok=np.array([int(t.complexity_score) for t, _ in feats], np.int32),
+                        heur_dev=np.array([h[0] for _, h in feats], np.uint8),
+                        heur_conf=np.array([h[1] for _, h in feats], np.float64))
+        results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg())
+        decisions: List[RoutingDecision] = []
+        threshold = int(self.config.get("heuristic_context_chars", 800))
+        for i, (q, c, k) in enumerate(zip(queries, contexts, ctxks)):
+            tok_d, heur = feats[i]
+            routed = r._decision(out, i, tok_d, heur) if hybrid else r._decision(out, i, tok_d)
+            res = results[i]
+            if res is not None:
+                context_len = len(c) if c else 0
+                heavy_ctx = context_len >= threshold and res.predicted_device == DEVICE_NAMES[0]
+                if not (heavy_ctx or res.use_hybrid_fallback):
+                    age = int((datetime.now() - res.entry.timestamp).total_seconds())
+                    decisions.append(RoutingDecision(
+                        device=res.predicted_device, confidence=res.predicted_confidence,
+                        method=f"{self.strategy_name}_cached",
+                        reasoning=(f"cache hit age={age}s hits={res.entry.hit_count} "
+                                   f"predicted={res.predicted_device} conf={res.predicted_confidence:.2f} "
+                                   f"context_len={context_len} history={len(res.entry.routing_history)}"),
+                        cache_hit=True))
+                    continue
+                reason = (f"context_len={context_len}>={threshold} overrides cached nano" if heavy_ctx
+                          else f"low prediction confidence={res.predicted_confidence:.2f}")
+                routed.reasoning = f"cache hit (hybrid re-route: {reason}) | " + routed.reasoning
+                routed.cache_hit = True
+            self._cache.insert(q, k, device=routed.device, confidence=routed.confidence, method=routed.method,
+                               q_emb=q_embs[i])
+            decisions.append(routed)
+        return decisions
+
     def _route(self, query: str, context: Optional[str], q_emb: Optional[np.ndarray]) -> RoutingDecision:
         if isinstance(self.router, HybridRouter) and q_emb is not None:
             return self.router.route(query, context, q_emb=q_emb)

@@ -151,6 +151,12 @@ QRE_API int qre_cache_clear(qre_cache_t* h);                          /* src/cac
 /* Read back fp32 rows (for QueryCache.save, src/cache.py:426-432). */
 QRE_API int qre_cache_read_rows(qre_cache_t* h, int64_t n, const int64_t* slot, float* rows_out);
 
+/* Binary snapshot of the device-resident rows and row metadata, beside the JSON save/load the
+ * reference offers (src/cache.py:426-465; 1M x 384 floats are ~8 GB of JSON text).  Load needs an
+ * empty cache of the same dim and enough capacity; slots keep their numbers. */
+QRE_API int qre_cache_snapshot_save(qre_cache_t* h, const char* path);
+QRE_API int qre_cache_snapshot_load(qre_cache_t* h, const char* path);
+
 /* ---- router state: replaces SemanticRouter centroids (qre:131,140-178) ---------------- */
 QRE_API int qre_set_centroids(qre_cache_t* h, int n_centroids, const float* centroids,
                       const uint8_t* owner_device);

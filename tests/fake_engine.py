@@ -13,6 +13,7 @@ class OracleEngine:
     def __init__(self, capacity=512, device=0, max_batch=64, dim=384, scan_mode=0):
         self.capacity = capacity
         self.dim = dim
+        self.max_batch = max_batch
         self.shard = None
         self.rows = np.zeros((capacity, dim), np.float32)
         self.ctx = np.full(capacity, O.CTX_TOMBSTONE, np.uint64)

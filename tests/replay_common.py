@@ -127,3 +127,30 @@ def check_route_arith(qre_mod, st_mod, rel=1e-5):
         assert abs(d.confidence - float(g["conf"][m])) <= 4e-6 + rel * abs(float(g["conf"][m])), (m, d)
         n_checked += 1
     assert n_checked > 300
+
+
+def check_route_queries_batch(qre_mod, st_mod, clock):
+    """`route_queries` (one fused device pass per batch) against a twin router driven one query at
+    a time, on batches without intra-batch interactions: identical decisions, methods, strings."""
+    g = json.load(open(os.path.join(GOLDEN, "router_replay.json")))
+    t = np.load(os.path.join(GOLDEN, "router_replay_table.npz"))
+    st_mod.set_table({str(k): v for k, v in zip(t["texts"], t["vecs"])}, dim=t["vecs"].shape[1])
+    cfg = dict(qre_mod.PRODUCTION_CFG)
+    cfg["centroids"], cfg["centroid_owner"] = t["centroids"], [0, 1]
+    a, b = qre_mod.QueryRouter("hybrid", cfg), qre_mod.QueryRouter("hybrid", cfg)
+    steps = g["steps"]
+    first = [s for s in steps[:32]]                       # pass 1 of the fixture: distinct queries
+    qs = [s["query"] for s in first]
+    ctxs = {len(g["short_ctx"]): g["short_ctx"], len(g["long_ctx"]): g["long_ctx"], -1: None}
+    for rnd, context in enumerate((g["short_ctx"], g["short_ctx"], g["long_ctx"])):
+        clock.advance(5.0)
+        seq = [a.route_query(q, context=context, context_key="ctx0") for q in qs]
+        bat = b.route_queries(qs, [context] * len(qs), ["ctx0"] * len(qs))
+        for x, y in zip(seq, bat):
+            assert (x.device, x.method, x.cache_hit, x.reasoning) == (y.device, y.method, y.cache_hit, y.reasoning), \
+                (rnd, x, y)
+            assert x.confidence == y.confidence
+    sa, sb = a.get_cache_stats(), b.get_cache_stats()
+    for k in ("size", "hits", "attempts", "evictions", "hybrid_fallbacks"):
+        assert sa[k] == sb[k], (k, sa[k], sb[k])
+    assert {d.method for d in bat} == {"hybrid", "hybrid_cached"}

@@ -30,6 +30,12 @@ def test_route_arith_gpu():
     R.check_route_arith(qre_mod, st)
 
 
+def test_route_queries_batch_gpu():
+    clock = ref_harness.FakeClock()
+    _, qre_mod, st = R.load_modules(clock)
+    R.check_route_queries_batch(qre_mod, st, clock)
+
+
 def test_golden_cache_scan_through_query_cache():
     """The recorded reference run of cache_scan.npz replayed through OUR QueryCache on the GPU:
     same inserts, same refreshes, same lookups at the same (fake) times."""
@@ -83,3 +89,31 @@ def test_lookup_batch_equals_sequential_snapshot():
     bat = b.lookup_batch([f"q{m}" for m in range(60)], [names[int(c)] for c in w.q_ctx], w.queries)
     assert [None if r is None else r.entry.query for r in seq] == [None if r is None else r.entry.query for r in bat]
     assert sum(r is not None for r in seq) > 10
+
+
+def test_binary_snapshot_roundtrip(tmp_path):
+    clock = ref_harness.FakeClock()
+    cache_mod, _, _ = R.load_modules(clock)
+    from qre_b200 import synth
+    w = synth.make_workload(600, 80, 384, n_centroids=2, seed=23, n_ctx=3, frac_expired=0.0, frac_dup=0.0)
+    names = {int(synth.ctx_id(i)): f"ctx{i}" for i in range(3)}
+    a = cache_mod.QueryCache(max_size=700, ttl_seconds=1000)
+    for j in range(600):
+        a.insert(f"e{j}", names[int(w.row_ctx[j])], "orin" if j % 2 else "nano", confidence=0.9, q_emb=w.rows[j])
+        if j == 299:
+            clock.advance(600)                      # the first 300 will be expired at load time
+    a.invalidate(query_pattern=r"^e3[0-4]\d$")       # tombstoned slots travel through the snapshot
+    p = str(tmp_path / "snap.json")
+    a.save_snapshot(p)
+    clock.advance(500)
+    b = cache_mod.QueryCache(max_size=700, ttl_seconds=1000)
+    n = b.load_snapshot(p)
+    assert n == 250 and b.stats()["size"] == 250
+    ra = [a.lookup(f"q{m}", names[int(w.q_ctx[m])], w.queries[m]) for m in range(80)]
+    rb = [b.lookup(f"q{m}", names[int(w.q_ctx[m])], w.queries[m]) for m in range(80)]
+    assert [None if r is None else r.entry.query for r in ra] == [None if r is None else r.entry.query for r in rb]
+    assert sum(r is not None for r in rb) > 5
+    e = next(iter(b._store.values()))
+    assert np.array_equal(e.embedding, w.rows[int(e.query[1:])])
+    b.insert("fresh", "ctx0", "nano", q_emb=w.rows[0] * 2)      # freed slots are reusable after load
+    assert b.lookup("probe", "ctx0", w.rows[0]).entry.query == "fresh"

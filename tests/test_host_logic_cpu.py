@@ -30,6 +30,12 @@ def test_route_arith_through_hybrid_router():
     R.check_route_arith(qre_mod, st)
 
 
+def test_route_queries_batch_equals_sequential():
+    clock = ref_harness.FakeClock()
+    _, qre_mod, st = R.load_modules(clock, OracleEngine)
+    R.check_route_queries_batch(qre_mod, st, clock)
+
+
 def test_save_load_roundtrip_and_reference_schema(tmp_path):
     clock = ref_harness.FakeClock()
     cache_mod, _, _ = R.load_modules(clock, OracleEngine)
