@@ -132,11 +132,23 @@ struct qre_cache {
   std::vector<int64_t> free_slots;
   std::vector<uint8_t> slot_live;
   uint8_t* d_stage = nullptr;          // kStageBytes
-  uint8_t* d_in = nullptr;             // lookup inputs (H2D target)
-  uint8_t* h_in = nullptr;             // pinned
+  // Two host-API slots: batch i+1's inputs can be copied in while batch i is being scanned.
+  struct HostSlot {
+    uint8_t* d_in = nullptr;           // lookup inputs (H2D target)
+    uint8_t* h_in = nullptr;           // pinned staging
+    uint8_t* d_res = nullptr;          // result block
+    uint8_t* h_res = nullptr;          // pinned
+    cudaEvent_t e_in = nullptr, e_mid = nullptr, e_done = nullptr;
+    bool pending = false;
+    int m = 0;
+    qre_params_t p;
+    ResultLayout L;
+    const int32_t* d_tok = nullptr;
+    const uint8_t* d_hd = nullptr;
+    const double* d_hc = nullptr;
+  } hs[2];
+  cudaStream_t h2d = nullptr, d2h = nullptr;
   size_t in_bytes = 0;
-  uint8_t* d_res = nullptr;            // result block
-  uint8_t* h_res = nullptr;            // pinned
   size_t res_bytes = 0;
   qre_candidate_t* d_cand = nullptr;   // [max_batch, QRE_TOPK]
   uint64_t* d_q_ctx = nullptr;         // [max_batch] copy of the last batch's contexts
@@ -300,18 +312,27 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
   QRE_ALLOC(s.perf_health, sizeof(double) * QRE_MAX_DEVICES);
   QRE_ALLOC(h->d_stage, kStageBytes);
   h->in_bytes = input_bytes(max_batch, dim);
-  QRE_ALLOC(h->d_in, h->in_bytes);
   {
     ResultLayout L;
     L.plan(max_batch, QRE_MAX_CENTROIDS, QRE_MAX_DEVICES);
     h->res_bytes = L.total;
   }
-  QRE_ALLOC(h->d_res, h->res_bytes);
+  for (int b = 0; b < 2; ++b) {
+    QRE_ALLOC(h->hs[b].d_in, h->in_bytes);
+    QRE_ALLOC(h->hs[b].d_res, h->res_bytes);
+  }
   QRE_ALLOC(h->d_cand, sizeof(qre_candidate_t) * (size_t)max_batch * QRE_TOPK);
   QRE_ALLOC(h->d_q_ctx, sizeof(uint64_t) * (size_t)max_batch);
   QRE_TRY([&]() -> int {
-    QRE_CUDA(cudaMallocHost((void**)&h->h_in, h->in_bytes));
-    QRE_CUDA(cudaMallocHost((void**)&h->h_res, h->res_bytes));
+    for (int b = 0; b < 2; ++b) {
+      QRE_CUDA(cudaMallocHost((void**)&h->hs[b].h_in, h->in_bytes));
+      QRE_CUDA(cudaMallocHost((void**)&h->hs[b].h_res, h->res_bytes));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_in, cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_mid, cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_done, cudaEventDisableTiming));
+    }
+    QRE_CUDA(cudaStreamCreateWithFlags(&h->h2d, cudaStreamNonBlocking));
+    QRE_CUDA(cudaStreamCreateWithFlags(&h->d2h, cudaStreamNonBlocking));
     QRE_CUDA(cudaMemsetAsync(s.rows_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.meta, 0xFF, sizeof(RowMeta) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
@@ -347,12 +368,19 @@ int qre_cache_destroy(qre_cache_t* h) {
   void* dev_ptrs[] = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf, s.q_f32[0],
                       s.q_f32[1], s.q_bf16, s.q_norm[0], s.q_norm[1], s.partial, s.exact_partial, s.ovf_count, s.ovf_unresolved, s.settle_tickets, s.settle_partial,
                       s.ovf_list, s.q_flags[0], s.q_flags[1],
-                      s.centroids, s.cent_norm, s.cent_owner, s.perf_health, h->d_stage, h->d_in, h->d_res,
-                      h->d_cand, h->d_q_ctx, h->d_dump};
+                      s.centroids, s.cent_norm, s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in,
+                      h->hs[1].d_in, h->hs[0].d_res, h->hs[1].d_res, h->d_cand, h->d_q_ctx, h->d_dump};
   for (void* p : dev_ptrs)
     if (p) cudaFree(p);
-  if (h->h_in) cudaFreeHost(h->h_in);
-  if (h->h_res) cudaFreeHost(h->h_res);
+  for (int b = 0; b < 2; ++b) {
+    if (h->hs[b].h_in) cudaFreeHost(h->hs[b].h_in);
+    if (h->hs[b].h_res) cudaFreeHost(h->hs[b].h_res);
+    if (h->hs[b].e_in) cudaEventDestroy(h->hs[b].e_in);
+    if (h->hs[b].e_mid) cudaEventDestroy(h->hs[b].e_mid);
+    if (h->hs[b].e_done) cudaEventDestroy(h->hs[b].e_done);
+  }
+  if (h->h2d) cudaStreamDestroy(h->h2d);
+  if (h->d2h) cudaStreamDestroy(h->d2h);
   if (s.prof_ev) {
     for (int i = 0; i < 2 * kProfMax; ++i) cudaEventDestroy(s.prof_ev[i]);
     delete[] s.prof_ev;
@@ -647,58 +675,18 @@ int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_candidate
   return QRE_OK;
 }
 
-int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx, const int32_t* tok,
-                     const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
-                     qre_result_t* out) {
-  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
-  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
-  if (!queries || !q_ctx || !out) return fail(QRE_ERR_INVALID, "NULL argument");
-  int rc = validate_params(h, params);
-  if (rc != QRE_OK) return rc;
-  const qre_params_t& p = *params;
-  if (p.do_route && (!tok || !heur_dev || !heur_conf))
-    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
-  DeviceGuard guard(h->s.device);
-  DeviceState& s = h->s;
-  cudaStream_t st = s.stream;
-  // ---- stage inputs (pinned) and copy once ----
-  size_t o = 0;
-  auto put = [&](const void* src, size_t bytes) -> uint8_t* {
-    uint8_t* d = h->d_in + o;
-    if (src) memcpy(h->h_in + o, src, bytes);
-    o = align_up(o + bytes, 256);
-    return d;
-  };
-  const float* d_q = (const float*)put(queries, sizeof(float) * (size_t)m * s.dim);
-  const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t) * (size_t)m);
-  const int32_t* d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m);
-  const uint8_t* d_hd = put(heur_dev, (size_t)m);
-  const double* d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m);
-  QRE_CUDA(cudaMemcpyAsync(h->d_in, h->h_in, o, cudaMemcpyHostToDevice, st));
-  rc = scan_enqueue(h, m, d_q, d_ctx, p, 0, h->d_cand, st);
-  if (rc != QRE_OK) return rc;
-  ResultLayout L;
-  const int K = p.do_route ? s.n_centroids : 0;
-  const int D = p.do_route ? p.n_devices : 1;
-  L.plan(m, K, D);
-  const qre_result_t dres = L.view(h->d_res);
-  for (int pass = 0; pass < 2; ++pass) {
-    h->launches += launch_merge_route(s, m, 1, h->d_cand, d_tok, d_hd, d_hc, p, dres, st);
-    QRE_CUDA(cudaGetLastError());
-    QRE_CUDA(cudaMemcpyAsync(h->d_res + L.ovf.off, s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-    QRE_CUDA(cudaMemcpyAsync(h->h_res, h->d_res, L.total, cudaMemcpyDeviceToHost, st));
-    QRE_CUDA(cudaStreamSynchronize(st));
-    const int32_t n_left = *reinterpret_cast<const int32_t*>(h->h_res + L.ovf.off);
-    if (n_left <= 0 || pass == 1) break;
-    // very rare: more overflowed queries than the device-side fallback settles per batch (512).
-    // Settle all of them with host-driven brute-force passes and merge again.
-    int32_t n_ovf = 0;
-    QRE_CUDA(cudaMemcpy(&n_ovf, s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost));
-    h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, s.ovf_list, n_ovf, true, p, 0, h->d_cand, st);
-    QRE_CUDA(cudaGetLastError());
-    QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
+static bool is_pinned_host(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
   }
-  const qre_result_t hres = L.view(h->h_res);
+  return at.type == cudaMemoryTypeHost;
+}
+
+static void scatter_results(const qre_cache_t::HostSlot& S, int K, int D, qre_result_t* out) {
+  const int m = S.m;
+  const qre_result_t hres = S.L.view(S.h_res);
 #define QRE_OUT(field, bytes) \
   if (out->field) memcpy(out->field, hres.field, (bytes))
   QRE_OUT(hit_slot, sizeof(int64_t) * m);
@@ -708,7 +696,7 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
   QRE_OUT(hit_shard, sizeof(uint32_t) * m);
   QRE_OUT(cand, sizeof(qre_candidate_t) * m * QRE_TOPK);
   QRE_OUT(flags, (size_t)m);
-  if (p.do_route) {
+  if (S.p.do_route) {
     QRE_OUT(centroid_sim, sizeof(float) * (size_t)m * K);
     QRE_OUT(tok_dev, (size_t)m);
     QRE_OUT(tok_conf, sizeof(double) * m);
@@ -720,6 +708,114 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
     QRE_OUT(score, sizeof(double) * (size_t)m * D);
   }
 #undef QRE_OUT
+}
+
+int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries, const uint64_t* q_ctx,
+                           const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
+                           const qre_params_t* params) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
+  if (!queries || !q_ctx) return fail(QRE_ERR_INVALID, "NULL argument");
+  int rc = validate_params(h, params);
+  if (rc != QRE_OK) return rc;
+  if (params->do_route && (!tok || !heur_dev || !heur_conf))
+    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
+  qre_cache_t::HostSlot& S = h->hs[slot];
+  if (S.pending) return fail(QRE_ERR_INVALID, "slot %d still has a batch in flight: call qre_lookup_route_end", slot);
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  S.m = m;
+  S.p = *params;
+  S.p.pipeline_slot = 0;       // one compute stream: scan(i+1) is ordered after merge(i)
+  // ---- inputs: small arrays through pinned staging; the query matrix straight from the caller's
+  // buffer when that is already page-locked (no extra host copy), else staged too ----
+  const bool direct = is_pinned_host(queries);
+  size_t o = 0;
+  auto put = [&](const void* src, size_t bytes, bool copy) -> uint8_t* {
+    uint8_t* d = S.d_in + o;
+    if (src && copy) memcpy(S.h_in + o, src, bytes);
+    o = align_up(o + bytes, 256);
+    return d;
+  };
+  const size_t q_bytes = sizeof(float) * (size_t)m * s.dim;
+  const float* d_q = (const float*)put(queries, q_bytes, !direct);
+  const size_t small_off = o;
+  const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t) * (size_t)m, true);
+  S.d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m, true);
+  S.d_hd = put(heur_dev, (size_t)m, true);
+  S.d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m, true);
+  if (direct) {
+    QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, h->h2d));
+    QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice, h->h2d));
+  } else {
+    QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, h->h2d));
+  }
+  QRE_CUDA(cudaEventRecord(S.e_in, h->h2d));
+  cudaStream_t st = s.stream;
+  QRE_CUDA(cudaStreamWaitEvent(st, S.e_in, 0));
+  rc = scan_enqueue(h, m, d_q, d_ctx, S.p, 0, h->d_cand, st);
+  if (rc != QRE_OK) return rc;
+  const int K = S.p.do_route ? s.n_centroids : 0;
+  const int D = S.p.do_route ? S.p.n_devices : 1;
+  S.L.plan(m, K, D);
+  const qre_result_t dres = S.L.view(S.d_res);
+  h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p, dres, st);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaMemcpyAsync(S.d_res + S.L.ovf.off, s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  QRE_CUDA(cudaEventRecord(S.e_mid, st));
+  QRE_CUDA(cudaStreamWaitEvent(h->d2h, S.e_mid, 0));
+  QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, h->d2h));
+  QRE_CUDA(cudaEventRecord(S.e_done, h->d2h));
+  S.pending = true;
+  return QRE_OK;
+}
+
+int qre_lookup_route_end(qre_cache_t* h, int slot, qre_result_t* out) {
+  if (h == nullptr || out == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  qre_cache_t::HostSlot& S = h->hs[slot];
+  if (!S.pending) return fail(QRE_ERR_INVALID, "slot %d has no batch in flight", slot);
+  DeviceGuard guard(h->s.device);
+  QRE_CUDA(cudaEventSynchronize(S.e_done));
+  S.pending = false;
+  const int32_t n_left = *reinterpret_cast<const int32_t*>(S.h_res + S.L.ovf.off);
+  if (n_left > 0)
+    return fail(QRE_ERR_OVERFLOW, "%d overflowed queries beyond the device-side fallback's capacity; "
+                "re-run this batch with qre_lookup_route", (int)n_left);
+  const int K = S.p.do_route ? h->s.n_centroids : 0;
+  const int D = S.p.do_route ? S.p.n_devices : 1;
+  scatter_results(S, K, D, out);
+  return QRE_OK;
+}
+
+int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx, const int32_t* tok,
+                     const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
+                     qre_result_t* out) {
+  if (out == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (h != nullptr && (h->hs[0].pending || h->hs[1].pending))
+    return fail(QRE_ERR_INVALID, "asynchronous batches in flight: finish them with qre_lookup_route_end first");
+  int rc = qre_lookup_route_begin(h, 0, m, queries, q_ctx, tok, heur_dev, heur_conf, params);
+  if (rc != QRE_OK) return rc;
+  rc = qre_lookup_route_end(h, 0, out);
+  if (rc != QRE_ERR_OVERFLOW) return rc;
+  // very rare: more overflowed queries than the device-side fallback settles per batch (512).
+  // The handle still holds this batch's state: settle all of them with host-driven brute-force
+  // passes, merge again and read the results back.
+  DeviceGuard guard(h->s.device);
+  DeviceState& s = h->s;
+  qre_cache_t::HostSlot& S = h->hs[0];
+  cudaStream_t st = s.stream;
+  int32_t n_ovf = 0;
+  QRE_CUDA(cudaMemcpy(&n_ovf, s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, s.ovf_list, n_ovf, true, S.p, 0, h->d_cand, st);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
+  h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p, S.L.view(S.d_res), st);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, st));
+  QRE_CUDA(cudaStreamSynchronize(st));
+  scatter_results(S, S.p.do_route ? s.n_centroids : 0, S.p.do_route ? S.p.n_devices : 1, out);
   return QRE_OK;
 }
 

@@ -31,6 +31,7 @@ EXPORTS = (
     "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
+    "qre_lookup_route_begin", "qre_lookup_route_end",
 )
 
 
@@ -232,6 +233,49 @@ class Shard:
         _check(self.lib, self.lib.qre_set_perf_health(self.h, C.c_int(hlt.shape[0]), _ptr(hlt)))
 
     # ---- the hot path, host buffers ----
+    def _host_outputs(self, m: int, do_route: bool, D: int, want_cand: bool) -> dict:
+        K = self.n_centroids
+        out = dict(hit_slot=np.empty(m, np.int64), hit_sim=np.empty(m, np.float32),
+                   hit_pred_dev=np.empty(m, np.uint8), hit_pred_conf=np.empty(m, np.float64),
+                   hit_shard=np.empty(m, np.uint32), flags=np.empty(m, np.uint8))
+        if want_cand:
+            out["cand"] = np.empty((m, TOPK), CAND_DTYPE)
+        if do_route:
+            out.update(centroid_sim=np.empty((m, K), np.float32), tok_dev=np.empty(m, np.uint8),
+                       tok_conf=np.empty(m, np.float64), sem_dev=np.empty(m, np.uint8),
+                       sem_conf=np.empty(m, np.float64), sem_method=np.empty(m, np.uint8),
+                       dev=np.empty(m, np.uint8), conf=np.empty(m, np.float64),
+                       score=np.empty((m, D), np.float64))
+        return out
+
+    def lookup_route_begin(self, slot: int, queries, q_ctx, cfg: RouteConfig, now_us: int, tok=None,
+                           heur_dev=None, heur_conf=None, want_cand: bool = False) -> None:
+        """Enqueue one batch on host slot 0/1 and return; pair with `lookup_route_end(slot)`.
+        The arrays must stay alive and unchanged until then (they are kept referenced here)."""
+        q = _arr(queries, np.float32)
+        m = q.shape[0]
+        if q.ndim != 2 or q.shape[1] != self.dim:
+            raise ValueError(f"queries must be [m, {self.dim}]")
+        q_ctx = _arr(q_ctx, np.uint64, (m,))
+        do_route = tok is not None
+        if do_route:
+            tok = _arr(tok, np.int32, (m,))
+            heur_dev = _arr(heur_dev, np.uint8, (m,))
+            heur_conf = _arr(heur_conf, np.float64, (m,))
+        p = cfg.to_c(now_us, do_route)
+        _check(self.lib, self.lib.qre_lookup_route_begin(self.h, C.c_int(slot), C.c_int(m), _ptr(q), _ptr(q_ctx),
+                                                         _ptr(tok), _ptr(heur_dev), _ptr(heur_conf), C.byref(p)))
+        if not hasattr(self, "_inflight"):
+            self._inflight = {}
+        self._inflight[slot] = (m, do_route, cfg.n_devices, want_cand, (q, q_ctx, tok, heur_dev, heur_conf))
+
+    def lookup_route_end(self, slot: int) -> dict:
+        m, do_route, D, want_cand, _keep = self._inflight.pop(slot)
+        out = self._host_outputs(m, do_route, D, want_cand)
+        res = Result(**{f: _ptr(out.get(f)) for f in RESULT_FIELDS})
+        _check(self.lib, self.lib.qre_lookup_route_end(self.h, C.c_int(slot), C.byref(res)))
+        return out
+
     def lookup_route(self, queries, q_ctx, cfg: RouteConfig, now_us: int, tok=None, heur_dev=None,
                      heur_conf=None, want_cand: bool = False) -> dict:
         q = _arr(queries, np.float32)
@@ -240,21 +284,11 @@ class Shard:
             raise ValueError(f"queries must be [m, {self.dim}]")
         q_ctx = _arr(q_ctx, np.uint64, (m,))
         do_route = tok is not None
-        D, K = cfg.n_devices, self.n_centroids
-        out = dict(hit_slot=np.empty(m, np.int64), hit_sim=np.empty(m, np.float32),
-                   hit_pred_dev=np.empty(m, np.uint8), hit_pred_conf=np.empty(m, np.float64),
-                   hit_shard=np.empty(m, np.uint32), flags=np.empty(m, np.uint8))
-        if want_cand:
-            out["cand"] = np.empty((m, TOPK), CAND_DTYPE)
         if do_route:
             tok = _arr(tok, np.int32, (m,))
             heur_dev = _arr(heur_dev, np.uint8, (m,))
             heur_conf = _arr(heur_conf, np.float64, (m,))
-            out.update(centroid_sim=np.empty((m, K), np.float32), tok_dev=np.empty(m, np.uint8),
-                       tok_conf=np.empty(m, np.float64), sem_dev=np.empty(m, np.uint8),
-                       sem_conf=np.empty(m, np.float64), sem_method=np.empty(m, np.uint8),
-                       dev=np.empty(m, np.uint8), conf=np.empty(m, np.float64),
-                       score=np.empty((m, D), np.float64))
+        out = self._host_outputs(m, do_route, cfg.n_devices, want_cand)
         res = Result(**{f: _ptr(out.get(f)) for f in RESULT_FIELDS})
         p = cfg.to_c(now_us, do_route)
         _check(self.lib, self.lib.qre_lookup_route(self.h, C.c_int(m), _ptr(q), _ptr(q_ctx), _ptr(tok),

@@ -173,6 +173,17 @@ QRE_API int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const 
                      const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
                      const qre_params_t* params, qre_result_t* out);
 
+/* The same call split in two so that consecutive batches overlap: `begin` enqueues the H2D
+ * copy of the inputs (own copy stream), the kernels and the D2H copy of the results (own copy
+ * stream) and returns; `end` waits for that batch and fills `out`.  Two slots (0 / 1): begin
+ * batch i+1 on the other slot before ending batch i and its input copy runs under batch i's
+ * scan.  The inputs must stay unchanged until `end`; if `queries` is page-locked memory it is
+ * copied straight from the caller's buffer.  qre_lookup_route == begin(0) + end(0). */
+QRE_API int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries,
+                                   const uint64_t* q_ctx, const int32_t* tok, const uint8_t* heur_dev,
+                                   const double* heur_conf, const qre_params_t* params);
+QRE_API int qre_lookup_route_end(qre_cache_t* h, int slot, qre_result_t* out);
+
 /* Device-pointer pipeline, one stage per call (all enqueue on `stream`):
  *   qre_scan_dev   : queries -> this shard's exactly re-scored candidates cand[m, QRE_TOPK]
  *   (multi-GPU: all-gather cand over NCCL, e.g. torch.distributed.all_gather_into_tensor)

@@ -328,3 +328,30 @@ def test_many_overflowed_queries_settled_on_device():
     assert np.array_equal(o["hit_sim"].cpu().numpy(), out_e["hit_sim"])
     assert int(look.ovf.item()) == 0            # nothing left for the host to settle
     sh.close()
+
+
+def test_begin_end_slots_overlap_and_pinned_inputs(small):
+    """Two batches in flight on the two host slots, one from page-locked and one from pageable
+    memory: each equals the synchronous call."""
+    import torch
+    w = small
+    sh = _load(w)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    parts = [slice(0, 150), slice(150, 300)]
+    sync = [sh.lookup_route(w.queries[p], w.q_ctx[p], cfg, w.now_us, tok=w.tok[p], heur_dev=w.heur_dev[p],
+                            heur_conf=w.heur_conf[p]) for p in parts]
+    pinned_q = torch.from_numpy(np.ascontiguousarray(w.queries[parts[0]])).pin_memory().numpy()
+    sh.lookup_route_begin(0, pinned_q, w.q_ctx[parts[0]], cfg, w.now_us, tok=w.tok[parts[0]],
+                          heur_dev=w.heur_dev[parts[0]], heur_conf=w.heur_conf[parts[0]])
+    sh.lookup_route_begin(1, w.queries[parts[1]], w.q_ctx[parts[1]], cfg, w.now_us, tok=w.tok[parts[1]],
+                          heur_dev=w.heur_dev[parts[1]], heur_conf=w.heur_conf[parts[1]])
+    with pytest.raises(_cabi.QreError, match="still has a batch in flight"):
+        sh.lookup_route_begin(1, w.queries[parts[1]], w.q_ctx[parts[1]], cfg, w.now_us)
+    got = [sh.lookup_route_end(0), sh.lookup_route_end(1)]
+    for g, s_ in zip(got, sync):
+        for k in s_:
+            assert np.array_equal(g[k], s_[k]), k
+    with pytest.raises(_cabi.QreError, match="no batch in flight"):
+        sh.lib.qre_lookup_route_end.restype = None
+        _cabi._check(sh.lib, sh.lib.qre_lookup_route_end(sh.h, 0, __import__("ctypes").byref(_cabi.Result())) or 0)
+    sh.close()
