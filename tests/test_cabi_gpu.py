@@ -351,7 +351,7 @@ def test_begin_end_slots_overlap_and_pinned_inputs(small):
     for g, s_ in zip(got, sync):
         for k in s_:
             assert np.array_equal(g[k], s_[k]), k
-    with pytest.raises(_cabi.QreError, match="no batch in flight"):
-        sh.lib.qre_lookup_route_end.restype = None
-        _cabi._check(sh.lib, sh.lib.qre_lookup_route_end(sh.h, 0, __import__("ctypes").byref(_cabi.Result())) or 0)
+    import ctypes
+    assert sh.lib.qre_lookup_route_end(sh.h, 0, ctypes.byref(_cabi.Result())) == 1
+    assert b"no batch in flight" in sh.lib.qre_last_error()
     sh.close()
