@@ -82,7 +82,7 @@ def make_workload(n_rows: int, n_queries: int, dim: int = 384, n_centroids: int 
     row_lru = rs.permutation(n_rows).astype(np.uint64) + np.uint64(1)
     row_pred_dev = rs.integers(0, n_devices, n_rows).astype(np.uint8)
     row_pred_conf = rs.uniform(0.5, 1.0, n_rows)
-    if n_zero_rows:
+    if n_zero_rows and n_rows > n_zero_rows:
         zr = rs.choice(n_rows, n_zero_rows, replace=False)
         rows[zr] = 0.0
 

@@ -1,0 +1,107 @@
+"""GPU parity sweep over shapes and thresholds: ragged / tiny / boundary sizes, every dim class
+(resident-A up to 384, streaming-A up to 1024, dims that need padding), low / zero / negative
+thresholds (the candidate path carries the load), empty cache, NaN queries."""
+import numpy as np
+import pytest
+
+from oracle import qre_oracle as O
+from qre_b200 import _cabi, synth
+
+pytestmark = pytest.mark.gpu
+REL = 1e-5
+
+
+def _run(w, thr, max_batch=None, scan_mode=_cabi.SCAN_TENSOR):
+    n = w.rows.shape[0]
+    sh = _cabi.Shard(dim=w.rows.shape[1], capacity=max(n, 1), max_batch=max_batch or max(w.queries.shape[0], 1))
+    if n:
+        sh.append(w.rows, w.row_ctx, w.row_ts_us, w.row_lru, w.row_pred_dev, w.row_pred_conf)
+    cfg = _cabi.RouteConfig(similarity_threshold=thr, ttl_us=w.ttl_us, scan_mode=scan_mode)
+    out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us)
+    sh.close()
+    return out
+
+
+def _oracle(w, thr):
+    img = O.CacheImage(w.rows, w.row_ctx, w.row_ts_us, w.row_lru)
+    return O.scan_batch(w.queries, w.q_ctx, img, w.now_us, w.ttl_us, thr)
+
+
+def _compare(out, exp_row, exp_sim, w, thr):
+    """Decisions must match except where the winning score sits within fp32 summation noise of
+    the threshold or of a rival (the 'ambiguity band'); count and bound those."""
+    got = out["hit_slot"]
+    diff = np.nonzero(got != exp_row)[0]
+    band = 0
+    for m in diff:
+        img_rows = [r for r in (got[m], exp_row[m]) if r >= 0]
+        sims = [O.cache_similarity(w.queries[m], w.rows[r]) for r in img_rows]
+        near_thr = any(abs(s - thr) < 4e-6 for s in sims)
+        near_tie = len(sims) == 2 and abs(sims[0] - sims[1]) < 4e-6 * max(1.0, abs(sims[0]))
+        assert near_thr or near_tie, (m, got[m], exp_row[m], sims)
+        band += 1
+    assert band <= 2
+    same = (got == exp_row) & (exp_row >= 0)
+    np.testing.assert_allclose(out["hit_sim"][same], exp_sim[same], rtol=REL)
+
+
+@pytest.mark.parametrize("dim,n,m", [
+    (64, 1, 1), (64, 255, 5), (128, 256, 128), (200, 257, 129), (384, 1000, 256), (384, 3333, 257),
+    (392, 700, 33), (512, 900, 130), (768, 2049, 64), (1024, 1500, 77),
+])
+def test_shape_sweep(dim, n, m):
+    w = synth.make_workload(n, m, dim, n_centroids=2, seed=dim + n + m, frac_planted=0.6, frac_near=0.1,
+                            frac_dup=0.05, n_zero_q=1 if m > 2 else 0, n_zero_rows=1 if n > 4 else 0, n_ctx=3)
+    out = _run(w, 0.85)
+    exp_row, exp_sim = _oracle(w, 0.85)
+    _compare(out, exp_row, exp_sim, w, 0.85)
+    if n > 100 and m > 30:
+        assert (exp_row >= 0).sum() > 3
+
+
+@pytest.mark.parametrize("thr", [0.5, 0.2, 0.05, 0.0, -0.5])
+def test_low_thresholds_load_the_candidate_path(thr):
+    """Random rows (cosine ~ N(0, 0.05)): at low thresholds almost every query has live
+    candidates in every row range, overflow is common, and sims <= 0 must still never hit."""
+    w = synth.make_workload(5000, 150, 384, n_centroids=2, seed=77, frac_planted=0.3, frac_near=0.0,
+                            frac_dup=0.02, n_ctx=2)
+    out = _run(w, thr)
+    exp_row, exp_sim = _oracle(w, thr)
+    _compare(out, exp_row, exp_sim, w, thr)
+    out_e = _run(w, thr, scan_mode=_cabi.SCAN_EXACT)
+    assert np.array_equal(out["hit_slot"], out_e["hit_slot"]) and np.array_equal(out["hit_sim"], out_e["hit_sim"])
+    assert np.all(out["hit_sim"][out["hit_slot"] >= 0] > 0)
+    if thr <= 0.2:
+        assert (exp_row >= 0).mean() > 0.9
+
+
+def test_empty_cache_and_nan_queries():
+    w = synth.make_workload(300, 16, 384, n_centroids=2, seed=5, n_ctx=1, frac_planted=0.9, n_zero_q=0)
+    empty = synth.make_workload(0, 16, 384, n_centroids=2, seed=5, rows=np.zeros((0, 384), np.float32))
+    out = _run(empty, 0.85)
+    assert np.all(out["hit_slot"] == -1) and np.all(out["hit_sim"] == 0)
+    w.queries[3, 7] = np.nan
+    w.queries[4, 0] = np.inf
+    out = _run(w, 0.85)
+    exp_row, exp_sim = _oracle(w, 0.85)
+    assert out["hit_slot"][3] == -1 and out["hit_slot"][4] == -1       # NaN / inf never compare >= thr
+    ok = np.ones(16, bool); ok[[3, 4]] = False
+    assert np.array_equal(out["hit_slot"][ok], exp_row[ok])
+
+
+def test_capacity_and_batch_limits_are_errors():
+    sh = _cabi.Shard(dim=64, capacity=4, max_batch=2)
+    z = np.zeros(5)
+    rows = np.ones((5, 64), np.float32)
+    with pytest.raises(_cabi.QreError, match="full"):
+        sh.append(rows, z, z, z, z, z)
+    sh.append(rows[:4], z[:4], z[:4], z[:4], z[:4], z[:4])
+    with pytest.raises(_cabi.QreError, match="max_batch"):
+        sh.lookup_route(rows[:3], z[:3], _cabi.RouteConfig(), 0)
+    with pytest.raises(_cabi.QreError, match="not a live row"):
+        sh.tombstone(np.array([7]))
+    sh.tombstone(np.array([1, 1]))                                       # listed twice: freed once
+    assert sh.info()["live"] == 3
+    with pytest.raises(_cabi.QreError, match="no centroids"):
+        sh.lookup_route(rows[:2], z[:2], _cabi.RouteConfig(), 0, tok=[1, 2], heur_dev=[0, 0], heur_conf=[.5, .5])
+    sh.close()
