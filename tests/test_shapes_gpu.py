@@ -71,12 +71,12 @@ def test_low_thresholds_load_the_candidate_path(thr):
     out_e = _run(w, thr, scan_mode=_cabi.SCAN_EXACT)
     assert np.array_equal(out["hit_slot"], out_e["hit_slot"]) and np.array_equal(out["hit_sim"], out_e["hit_sim"])
     assert np.all(out["hit_sim"][out["hit_slot"] >= 0] > 0)
-    if thr <= 0.2:
-        assert (exp_row >= 0).mean() > 0.9
+    if thr <= 0.05:
+        assert (exp_row >= 0).mean() > 0.85
 
 
 def test_empty_cache_and_nan_queries():
-    w = synth.make_workload(300, 16, 384, n_centroids=2, seed=5, n_ctx=1, frac_planted=0.9, n_zero_q=0)
+    w = synth.make_workload(300, 16, 384, n_centroids=2, seed=5, n_ctx=2, frac_planted=0.9, n_zero_q=0)
     empty = synth.make_workload(0, 16, 384, n_centroids=2, seed=5, rows=np.zeros((0, 384), np.float32))
     out = _run(empty, 0.85)
     assert np.all(out["hit_slot"] == -1) and np.all(out["hit_sim"] == 0)
