@@ -2,6 +2,7 @@
 // lifetime, host<->device staging, TMA descriptor set-up and the launch sequences.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -257,7 +258,7 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
   s.dim = dim;
   s.dim_pad = dim_pad;
   s.max_batch = max_batch;
-  s.mb_pad = (int)align_up(max_batch, kBM);
+  s.mb_pad = (int)align_up(max_batch, 2 * kBM);     // CTA pairs work on two 128-query blocks
   s.capacity = capacity;
   s.cap_pad = (long long)align_up((size_t)capacity, kBN);
 #define QRE_TRY(expr)                 \
@@ -291,6 +292,8 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     for (int mb = 1; mb <= s.mb_pad / kBM; ++mb) {
       const ScanGeometry g = plan_scan(mb * kBM, s.cap_pad, s.num_sms);
       worst = std::max(worst, (long long)g.mblocks * kBM * g.splits * kTopK);
+      const ScanGeometry g2 = plan_scan_pair(mb * kBM, s.cap_pad, s.num_sms);
+      worst = std::max(worst, (long long)(g2.mblocks + 1) * kBM * g2.splits * kTopK);
       if (mb > 64) mb += 7;   // the product is ~constant beyond one wave; sample sparsely
     }
     const ScanGeometry g = plan_scan(s.mb_pad, s.cap_pad, s.num_sms);
@@ -343,10 +346,17 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), s.stream));
     for (int b = 0; b < 2; ++b) QRE_CUDA(cudaMemsetAsync(s.q_flags[b], 0, (size_t)max_batch, s.stream));
     QRE_CUDA(gemm_topk_init());
+    QRE_CUDA(gemm_topk_pair_init());
+    {
+      const char* e = getenv("QRE_SCAN_SINGLE_CTA");
+      s.allow_pair = !(e != nullptr && e[0] == '1');
+    }
     EncodeTiledFn enc = nullptr;
     int rc = get_encode_fn(&enc);
     if (rc != QRE_OK) return rc;
     rc = make_tmap_bf16(enc, &s.tmap_e, s.rows_bf16, (uint64_t)dim_pad, (uint64_t)s.cap_pad, kBK, kBN);
+    if (rc != QRE_OK) return rc;
+    rc = make_tmap_bf16(enc, &s.tmap_eh, s.rows_bf16, (uint64_t)dim_pad, (uint64_t)s.cap_pad, kBK, kBN / 2);
     if (rc != QRE_OK) return rc;
     rc = make_tmap_bf16(enc, &s.tmap_q, s.q_bf16, (uint64_t)dim_pad, (uint64_t)s.mb_pad, kBK, kBM);
     if (rc != QRE_OK) return rc;

@@ -61,11 +61,16 @@ struct GemmArgs {
 
 struct ScanGeometry {
   int mblocks, tiles_n, splits, grid;
+  bool pair = false;        // CTA-pair (cta_group::2) kernel chosen
 };
 ScanGeometry plan_scan(int m, long long n_rows, int num_sms);
 cudaError_t gemm_topk_init();
+cudaError_t gemm_topk_pair_init();
+ScanGeometry plan_scan_pair(int m, long long n_rows, int num_sms);
 struct DeviceState;
 int scan_sms(const DeviceState& s, const qre_params_t& p);
+// The geometry (and kernel variant) one scan launch will use; rescore must ask the same question.
+ScanGeometry plan_for(const DeviceState& s, int m, long long n_rows, const qre_params_t& p);
 
 // All device state of one cache shard.
 struct DeviceState {
@@ -105,7 +110,8 @@ struct DeviceState {
   uint8_t* cent_owner = nullptr;      // [K]
   int n_centroids = 0;
   double* perf_health = nullptr;      // [QRE_MAX_DEVICES]
-  CUtensorMap tmap_q, tmap_e;
+  CUtensorMap tmap_q, tmap_e, tmap_eh;   // queries (128-row box), cache rows (256-row box / 128-row half box)
+  bool allow_pair = true;               // QRE_SCAN_SINGLE_CTA=1 forces the single-CTA kernel
   // optional CUDA-event bracket around every scan-kernel launch (bench.py's live roofline)
   bool prof_on = false;
   cudaEvent_t* prof_ev = nullptr;     // [2 * kProfMax]
@@ -128,6 +134,8 @@ int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st);
 int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
                      float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st);
+int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+                          float* dump, long long dump_ld, long long dump_row0, cudaStream_t st);
 int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& p, int shard,
                    qre_candidate_t* cand, cudaStream_t st);
 int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const int32_t* qlist_dev,

@@ -285,6 +285,17 @@ int scan_sms(const DeviceState& s, const qre_params_t& p) {
   return s.num_sms - r;
 }
 
+ScanGeometry plan_for(const DeviceState& s, int m, long long n_rows, const qre_params_t& p) {
+  const int sms = scan_sms(s, p);
+  const int mblocks = (m + kBM - 1) / kBM;
+  if (s.allow_pair && s.dim_pad / kBK <= kMaxKB && mblocks >= 2 && sms >= 2) {
+    ScanGeometry g = plan_scan_pair(m, n_rows, sms);
+    g.pair = true;
+    return g;
+  }
+  return plan_scan(m, n_rows, sms);
+}
+
 // Per-device set-up (called by qre_cache_create with the device current): opt in to the
 // 225 KB dynamic shared memory the scan kernel needs.
 template <bool kDump, bool kResident>
@@ -303,7 +314,8 @@ cudaError_t gemm_topk_init() {
 int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
                      float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st) {
   (void)dump_n;
-  const ScanGeometry g = plan_scan(m, n_rows, scan_sms(s, p));
+  const ScanGeometry g = plan_for(s, m, n_rows, p);
+  if (g.pair) return launch_gemm_topk_pair(s, m, n_rows, q_ctx, p, dump, dump_ld, dump_row0, st);
   GemmArgs a;
   a.m = m;
   a.mblocks = g.mblocks;

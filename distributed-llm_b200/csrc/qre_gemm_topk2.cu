@@ -1,0 +1,377 @@
+// qre_gemm_topk2.cu — CTA-pair (cta_group::2) variant of the scan kernel.
+//
+// Same contract as qre_gemm_topk_kernel (qre_gemm_topk.cu): approx[q, row] on the tensor cores,
+// fused per-query top-k, results in the `partial` scratch.  What changes is the data movement:
+// a cluster of two CTAs (one TPC) works on 256 queries x 256 cache rows per tile with ONE
+// tcgen05.mma.cta_group::2 (M = 256), each CTA keeping its own 128-query A block resident and
+// loading only HALF of every cache-row tile (128 rows x 64 k = 16 KB per stage).  Per SM that
+// halves the L2->SM traffic and the shared-memory reads of the B operand — the resources the
+// single-CTA kernel saturates (profiles/r1_summary.md: 12.6 TB/s L2->SM) — and leaves room for
+// an 8-deep B ring.
+//
+// Protocol (barrier objects live at the same shared-memory offset in both CTAs):
+//   full[s], a_full   leader (rank 0) only, count 2: both CTAs' producers arrive (the leader
+//                     with expect_tx for both halves); both CTAs' TMA loads complete_tx there.
+//   empty[s], a_empty, t_full[acc]   in each CTA, signalled by the leader's MMA thread with a
+//                     multicast tcgen05.commit (mask 0b11).
+//   t_empty[acc]      leader only, count 256: the epilogue threads of both CTAs arrive remotely.
+// Only the leader issues MMAs; both CTAs run a TMA producer and four epilogue warps over their
+// own 128 TMEM lanes.
+#include <stdio.h>
+
+#include <algorithm>
+#include <cmath>
+
+#include "qre_common.cuh"
+#include "qre_ptx.cuh"
+
+namespace qre {
+
+namespace {
+
+constexpr int kThreads2 = 192;
+constexpr int kStages2 = 8;
+constexpr int kABytesPerKB2 = kBM * kBK * 2;          // 16 KB
+constexpr int kBHalfRows = kBN / 2;                   // 128 cache rows per CTA per tile
+constexpr int kBHalfBytes = kBHalfRows * kBK * 2;     // 16 KB
+constexpr int kSmemA2 = kMaxKB * kABytesPerKB2;       // 96 KB
+constexpr int kSmemB2 = kStages2 * kBHalfBytes;       // 128 KB
+constexpr int kSmemTotal2 = kSmemA2 + kSmemB2 + 512 + 1024;
+constexpr uint32_t kTmemCols2 = 512;
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;           // shared::cluster address of the even CTA of a pair
+
+struct TopK2 {
+  float v[kTopK];
+  uint32_t r[kTopK];
+};
+
+__device__ __noinline__ float consider2(TopK2* tk, float v, long long row, long long n_rows,
+                                        const RowMeta* __restrict__ meta, uint64_t myctx, long long now_us,
+                                        long long ttl_us) {
+  if (row >= n_rows) return tk->v[kTopK - 1];
+  const int4 raw = __ldg(reinterpret_cast<const int4*>(meta + row));
+  const uint64_t ctx = (static_cast<uint64_t>(static_cast<uint32_t>(raw.y)) << 32) | static_cast<uint32_t>(raw.x);
+  const long long ts = static_cast<long long>((static_cast<uint64_t>(static_cast<uint32_t>(raw.w)) << 32) |
+                                              static_cast<uint32_t>(raw.z));
+  if (ctx != myctx || (now_us - ts) > ttl_us) return tk->v[kTopK - 1];
+  int i = kTopK - 1;
+  while (i > 0 && v > tk->v[i - 1]) {
+    tk->v[i] = tk->v[i - 1];
+    tk->r[i] = tk->r[i - 1];
+    --i;
+  }
+  tk->v[i] = v;
+  tk->r[i] = static_cast<uint32_t>(row);
+  return tk->v[kTopK - 1];
+}
+
+// ---- cluster / cta_group::2 PTX ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive (count 1, no tx) on the barrier at the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+      :
+      : "r"(smem_u32(bar)), "r"(rank)
+      : "memory");
+}
+// TMA load into THIS CTA's shared memory, completion bytes credited to the pair leader's barrier
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int32_t c0,
+                                                 int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerMask), "r"(c0),
+        "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      :
+      : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this offset in BOTH CTAs once all MMAs issued so far have retired
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      :
+      : "r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+
+}  // namespace
+
+template <bool kDump>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
+qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_eh,
+                          const GemmArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kSmemA2;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA2 + kSmemB2);
+  uint64_t* full = bars;                       // [kStages2]
+  uint64_t* empty = bars + kStages2;           // [kStages2]
+  uint64_t* a_full = bars + 2 * kStages2;
+  uint64_t* a_empty = a_full + 1;
+  uint64_t* t_full = a_full + 2;               // [2]
+  uint64_t* t_empty = a_full + 4;              // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 6);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int n_clusters = gridDim.x >> 1;
+
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_eh);
+    for (int i = 0; i < kStages2; ++i) {
+      mbar_init(&full[i], 2);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(a_full, 2);
+    mbar_init(a_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&t_full[i], 1);
+      mbar_init(&t_empty[i], 256);
+    }
+    fence_barrier_init();
+  }
+  cluster_sync_all();                          // barriers of both CTAs are initialised
+  if (warp == 5) {
+    tmem_alloc2(tmem_slot, kTmemCols2);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int npairs = (a.mblocks + 1) >> 1;
+  const int U = a.splits * npairs;
+  const long long T = a.tiles_n;
+
+  if (warp == 4) {
+    // ================= TMA producer (one per CTA) =================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0, a_iter = 0;
+      for (int u = cluster_id; u < U; u += n_clusters) {
+        const int s = u / npairs, pr = u - s * npairs;
+        const int mb = 2 * pr + static_cast<int>(rank);
+        const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        mbar_wait(a_empty, (a_iter & 1) ^ 1);
+        if (leader) mbar_arrive_expect_tx(a_full, 2u * static_cast<uint32_t>(a.num_kb) * kABytesPerKB2);
+        else mbar_arrive_remote(a_full, 0);
+        for (int kb = 0; kb < a.num_kb; ++kb)
+          tma_load_2d_pair(sA + kb * kABytesPerKB2, &tmap_q, a_full, kb * kBK, mb * kBM);
+        ++a_iter;
+        for (int t = t0; t < t1; ++t) {
+          for (int kb = 0; kb < a.num_kb; ++kb) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            if (leader) mbar_arrive_expect_tx(&full[stage], 2u * kBHalfBytes);
+            else mbar_arrive_remote(&full[stage], 0);
+            tma_load_2d_pair(sB + stage * kBHalfBytes, &tmap_eh, &full[stage], kb * kBK,
+                             t * kBN + static_cast<int>(rank) * kBHalfRows);
+            if (++stage == kStages2) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ================= MMA issuer: one thread of the leader CTA =================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * kBM, kBN);      // M = 256 across the pair
+      uint32_t stage = 0, phase = 0, a_iter = 0, tile_iter = 0;
+      const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+      for (int u = cluster_id; u < U; u += n_clusters) {
+        const int s = u / npairs;
+        const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        mbar_wait(a_full, a_iter & 1);
+        for (int t = t0; t < t1; ++t) {
+          const uint32_t acc = tile_iter & 1;
+          mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * kBN;
+          for (int kb = 0; kb < a.num_kb; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            const uint64_t adesc = umma_desc_sw128(sA_addr + kb * kABytesPerKB2);
+            const uint64_t bdesc = umma_desc_sw128(sB_addr + stage * kBHalfBytes);
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k)
+              umma_bf16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit_pair(&empty[stage]);
+            if (++stage == kStages2) { stage = 0; phase ^= 1; }
+          }
+          umma_commit_pair(&t_full[acc]);
+          ++tile_iter;
+        }
+        umma_commit_pair(a_empty);
+        ++a_iter;
+      }
+    }
+  } else {
+    // ================= epilogue (both CTAs): fused per-query top-k =================
+    uint32_t tile_iter = 0;
+    TopK2 tk;
+    for (int u = cluster_id; u < U; u += n_clusters) {
+      const int s = u / npairs, pr = u - s * npairs;
+      const int mb = 2 * pr + static_cast<int>(rank);
+      const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+      const int q = mb * kBM + warp * 32 + lane;
+      const bool active = q < a.m;
+      const uint64_t myctx = active ? a.q_ctx[q] : 0ull;
+#pragma unroll
+      for (int i = 0; i < kTopK; ++i) { tk.v[i] = a.floor_v; tk.r[i] = kNoRow; }
+      float kth = active ? a.floor_v : __int_as_float(0x7f800000);
+      for (int t = t0; t < t1; ++t) {
+        const uint32_t acc = tile_iter & 1;
+        mbar_wait(&t_full[acc], (tile_iter >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + acc * kBN;
+        const long long row_base = static_cast<long long>(t) * kBN;
+#pragma unroll 1
+        for (int c = 0; c < kBN / 64; ++c) {
+          float v[64];
+          tmem_ld_32x32(taddr + c * 64, v);
+          tmem_ld_32x32(taddr + c * 64 + 32, v + 32);
+          tmem_ld_wait();
+          if (kDump) {
+            if (active && a.dump != nullptr) {
+#pragma unroll
+              for (int i = 0; i < 64; ++i) {
+                const long long row = row_base + c * 64 + i;
+                if (row >= a.dump_row0 && row < a.dump_row0 + a.dump_ld && row < a.n_rows)
+                  a.dump[static_cast<long long>(q) * a.dump_ld + (row - a.dump_row0)] = v[i];
+              }
+            }
+          }
+          float m0 = fmaxf(v[0], v[1]), m1 = fmaxf(v[2], v[3]), m2 = fmaxf(v[4], v[5]), m3 = fmaxf(v[6], v[7]);
+#pragma unroll
+          for (int i = 8; i < 64; i += 8) {
+            m0 = fmaxf(m0, fmaxf(v[i], v[i + 1]));
+            m1 = fmaxf(m1, fmaxf(v[i + 2], v[i + 3]));
+            m2 = fmaxf(m2, fmaxf(v[i + 4], v[i + 5]));
+            m3 = fmaxf(m3, fmaxf(v[i + 6], v[i + 7]));
+          }
+          const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+          if (mx > kth) {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) {
+              if (v[i] > kth)
+                kth = consider2(&tk, v[i], row_base + c * 64 + i, a.n_rows, a.meta, myctx, a.now_us, a.ttl_us);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive_remote(&t_empty[acc], 0);      // the leader's MMA thread owns the accumulator hand-off
+        ++tile_iter;
+      }
+      if (active) {
+        PartialEntry* out = a.partial + (static_cast<long long>(q) * a.splits + s) * kTopK;
+#pragma unroll
+        for (int i = 0; i < kTopK; ++i) out[i] = PartialEntry{tk.v[i], tk.r[i]};
+      }
+    }
+  }
+
+  __syncwarp();                                // the single-lane roles rejoin their warps
+  tc_fence_before();
+  cluster_sync_all();                          // nobody frees TMEM / exits while the peer still uses it
+  if (warp == 5) tmem_dealloc2(tmem_base, kTmemCols2);
+}
+
+cudaError_t gemm_topk_pair_init() {
+  cudaError_t e = cudaFuncSetAttribute(qre_gemm_topk_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kSmemTotal2);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(qre_gemm_topk_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              kSmemTotal2);
+}
+
+// Same search as plan_scan, over query-block PAIRS and CTA-pair clusters.
+ScanGeometry plan_scan_pair(int m, long long n_rows, int num_sms) {
+  ScanGeometry g = plan_scan(m, n_rows, num_sms);
+  const int npairs = (g.mblocks + 1) / 2;
+  const int clusters = num_sms / 2;
+  long long S = 1;
+  double best = -1.0;
+  const long long s_max = std::min<long long>(g.tiles_n, (8LL * clusters) / npairs + 1);
+  for (long long c = 1; c <= s_max; ++c) {
+    const double U = static_cast<double>(c) * npairs;
+    const double rounds = std::ceil(U / clusters);
+    if (rounds > 8.0) break;
+    const double L = static_cast<double>(g.tiles_n) / c;
+    const double score = (U / clusters) / rounds * L / (L + 1.6);
+    if (score > best + 1e-12) { best = score; S = c; }
+  }
+  g.splits = static_cast<int>(S);
+  const long long U = S * npairs;
+  g.grid = 2 * static_cast<int>(U < clusters ? U : clusters);
+  return g;
+}
+
+int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+                          float* dump, long long dump_ld, long long dump_row0, cudaStream_t st) {
+  const ScanGeometry g = plan_scan_pair(m, n_rows, scan_sms(s, p));
+  GemmArgs a;
+  a.m = m;
+  a.mblocks = g.mblocks;
+  a.tiles_n = g.tiles_n;
+  a.splits = g.splits;
+  a.num_kb = s.dim_pad / kBK;
+  a.n_rows = n_rows;
+  const double thr = p.similarity_threshold > 0.0 ? p.similarity_threshold : 0.0;
+  a.floor_v = static_cast<float>(thr) - kApproxEps;
+  a.now_us = p.now_us;
+  a.ttl_us = p.ttl_us;
+  a.q_ctx = q_ctx;
+  a.meta = s.meta;
+  a.partial = s.partial;
+  a.dump = dump;
+  a.dump_ld = dump_ld;
+  a.dump_row0 = dump_row0;
+  const bool prof = s.prof_on && s.prof_ev != nullptr && s.prof_used < kProfMax && dump == nullptr;
+  if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
+  if (dump != nullptr)
+    qre_gemm_topk_pair_kernel<true><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.tmap_q, s.tmap_eh, a);
+  else
+    qre_gemm_topk_pair_kernel<false><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.tmap_q, s.tmap_eh, a);
+  if (prof) {
+    cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);
+    ++s.prof_used;
+  }
+  return 1;
+}
+
+}  // namespace qre

@@ -789,7 +789,7 @@ int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st) {
 
 int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& p, int shard,
                    qre_candidate_t* cand, cudaStream_t st) {
-  const ScanGeometry g = plan_scan(m, n_rows, scan_sms(s, p));
+  const ScanGeometry g = plan_for(s, m, n_rows, p);
   RescoreArgs a;
   a.m = m; a.splits = g.splits; a.dim_pad = s.dim_pad; a.shard = shard;
   const double thr = p.similarity_threshold > 0.0 ? p.similarity_threshold : 0.0;
