@@ -49,6 +49,11 @@ class OracleEngine:
             self.capacity = len(self.ctx)
 
     def append(self, row, ctx, ts_us, lru, pdev, pconf):
+        row = np.asarray(row, np.float32)
+        if row.shape[0] != self.rows.shape[1]:          # dimension is learnt from the first row
+            assert self.hwm == 0
+            self.dim = row.shape[0]
+            self.rows = np.zeros((len(self.ctx), self.dim), np.float32)
         if self.free:
             s = self.free.pop()
         else:

@@ -1,0 +1,87 @@
+"""CPU: randomized operation sequences run side by side on the LIVE reference QueryCache
+(/root/reference, build container only) and on the drop-in QueryCache with the oracle-backed
+engine: every observable (lookup result, order, hit counts, history lengths, stats) must agree
+after every step.  Exercises the host bookkeeping far beyond the scripted golden sequence:
+capacity eviction with and without stale entries, TTL expiry, refresh-in-place, exact-hash
+hits, invalidate by context / pattern, clear, save/load."""
+import numpy as np
+import pytest
+
+from oracle import ref_harness
+from tests import replay_common as R
+from tests.fake_engine import OracleEngine
+
+pytestmark = pytest.mark.skipif(not ref_harness.available(), reason="reference tree not mounted")
+
+
+def _snap(qc):
+    s = qc.stats()
+    return ([e.query for e in qc._store.values()], [e.hit_count for e in qc._store.values()],
+            [len(e.routing_history) for e in qc._store.values()],
+            [e.device_used for e in qc._store.values()],
+            {k: s[k] for k in ("size", "valid", "stale", "hits", "attempts", "evictions", "hybrid_fallbacks")},
+            s["top_queries"])
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_random_ops_match_live_reference(seed, tmp_path):
+    clock = ref_harness.FakeClock()
+    ref_cache, _, _ = ref_harness.load_reference(clock)
+    cache_mod, _, _ = R.load_modules(clock, OracleEngine)
+    rs = np.random.Generator(np.random.PCG64(seed))
+    d = 64
+    base = rs.standard_normal((24, d)).astype(np.float32)
+    kw = dict(max_size=int(rs.integers(4, 12)), ttl_seconds=int(rs.integers(20, 80)),
+              similarity_threshold=float(rs.choice([0.85, 0.6])), prediction_confidence_threshold=0.7)
+    a, b = ref_cache.QueryCache(**kw), cache_mod.QueryCache(**kw)
+    ctxs = ["A", "B", "C"]
+    n_hits = n_miss = 0
+
+    def vec(i, noise):
+        return (base[i] * np.float32(rs.uniform(0.5, 2.0)) + noise * rs.standard_normal(d).astype(np.float32))
+
+    for step in range(400):
+        op = rs.choice(["insert", "insert", "lookup", "lookup", "lookup", "advance", "exact", "noemb",
+                        "invalidate", "saveload", "clear"], p=[.2, .15, .2, .15, .08, .1, .05, .03, .02, .015, .005])
+        if op == "insert":
+            i = int(rs.integers(0, 24))
+            args = (f"Query {i}", str(rs.choice(ctxs)), str(rs.choice(["nano", "orin"])))
+            kwargs = dict(confidence=float(rs.uniform(0.1, 1.0)), method="hybrid", q_emb=vec(i, 0.05))
+            a.insert(*args, **kwargs); b.insert(*args, **kwargs)
+        elif op == "noemb":
+            args = (f"Bare {int(rs.integers(0, 5))}", str(rs.choice(ctxs)), "orin")
+            a.insert(*args); b.insert(*args)
+        elif op in ("lookup", "exact"):
+            i = int(rs.integers(0, 24))
+            q = f"query {i} " if op == "exact" else f"probe {step}"
+            ctx = str(rs.choice(ctxs))
+            v = vec(i, float(rs.choice([0.02, 0.05, 0.3, 1.0])))
+            if rs.random() < 0.05:
+                v = None
+            ra, rb = a.lookup(q, ctx, v), b.lookup(q, ctx, v)
+            assert (ra is None) == (rb is None), (step, op, q)
+            n_hits += ra is not None
+            n_miss += ra is None
+            if ra is not None:
+                assert (ra.entry.query, ra.predicted_device, ra.predicted_confidence, ra.use_hybrid_fallback) == \
+                       (rb.entry.query, rb.predicted_device, rb.predicted_confidence, rb.use_hybrid_fallback), step
+        elif op == "advance":
+            clock.advance(float(rs.choice([0.5, 5.0, 30.0, 90.0])))
+        elif op == "invalidate":
+            if rs.random() < 0.5:
+                k = dict(context_key=str(rs.choice(ctxs)))
+            else:
+                k = dict(query_pattern=rf"query {int(rs.integers(0, 3))}\d?$")
+            assert a.invalidate(**k) == b.invalidate(**k)
+        elif op == "saveload":
+            pa, pb = str(tmp_path / f"a{step}.json"), str(tmp_path / f"b{step}.json")
+            a.save(pa); b.save(pb)
+            a2, b2 = ref_cache.QueryCache(**kw), cache_mod.QueryCache(**kw)
+            # each implementation loads the OTHER one's file: the schema is interchangeable
+            assert a2.load(pb) == b2.load(pa)
+            assert _snap(a2)[:4] == _snap(b2)[:4]
+        elif op == "clear":
+            a.clear(); b.clear()
+        sa, sb = _snap(a), _snap(b)
+        assert sa == sb, (step, op, sa, sb)
+    assert n_hits > 5 and n_miss > 5
