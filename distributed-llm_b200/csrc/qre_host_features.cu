@@ -1,0 +1,290 @@
+// qre_host_features.cu — host-side per-query features for a whole batch, in C++ threads
+// (SURVEY §8f-2).  No device code: it lives in libqre_b200.so so that one binding serves both.
+//
+// Restates, for ASCII input, the reference's HeuristicRouter.route (src/query_router_engine.py:
+// 323-364) — its ordered rule list and the regular expressions of qre:231-294 — and the
+// no-tokenizer token estimate of TokenBasedRouter (qre:91,96: max(1, len(text)//4)).  The
+// Python `re` patterns are compiled by hand into "segments": sets of literal alternatives with
+// \b conditions at either end, joined by `.*` (which, as in Python, does not cross a newline).
+// Queries containing non-ASCII bytes are NOT classified here (rule = -1): \b, \w and len()
+// are Unicode-aware in Python, so the caller keeps those on its own path.
+#include <stdint.h>
+#include <string.h>
+
+#include <string>
+#include <thread>
+#include <utility>
+#include <vector>
+
+#include "../../include/qre_b200.h"
+
+namespace {
+
+inline bool is_word(unsigned char c) {
+  return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z') || (c >= '0' && c <= '9') || c == '_';
+}
+inline bool is_space(unsigned char c) {          // str.isspace() / \s for code points < 128
+  return c == 0x20 || (c >= 0x09 && c <= 0x0D) || (c >= 0x1C && c <= 0x1F);
+}
+inline bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
+
+struct View {
+  const char* p;
+  int n;
+  unsigned char at(int i) const { return (i >= 0 && i < n) ? static_cast<unsigned char>(p[i]) : 0; }
+  bool boundary(int i) const {                   // \b between positions i-1 and i
+    const bool a = i > 0 && is_word(at(i - 1));
+    const bool b = i < n && is_word(at(i));
+    return a != b;
+  }
+};
+
+struct Seg {
+  bool wb_start, wb_end;
+  std::vector<std::string> alts;
+};
+struct Pat {
+  std::vector<Seg> segs;      // joined by .*
+  int special = 0;            // 1: a* ; 2: tiny math ; 3: "what is" tiny math
+};
+
+// all (start, end) matches of one segment
+void seg_matches(const View& s, const Seg& g, std::vector<std::pair<int, int>>& out) {
+  out.clear();
+  for (const std::string& a : g.alts) {
+    const int L = static_cast<int>(a.size());
+    for (int i = 0; i + L <= s.n; ++i) {
+      if (memcmp(s.p + i, a.data(), L) != 0) continue;
+      if (g.wb_start && !s.boundary(i)) continue;
+      if (g.wb_end && !s.boundary(i + L)) continue;
+      out.emplace_back(i, i + L);
+    }
+  }
+}
+
+bool match_math(const View& s, bool with_what_is) {
+  // ^\s*(what is\s+)?\d+\s*[\+\-\*/]\s*\d+\s*\??\s*$
+  int i = 0;
+  while (i < s.n && is_space(s.at(i))) ++i;
+  if (with_what_is) {
+    if (i + 7 > s.n || memcmp(s.p + i, "what is", 7) != 0) return false;
+    i += 7;
+    if (i >= s.n || !is_space(s.at(i))) return false;
+    while (i < s.n && is_space(s.at(i))) ++i;
+  }
+  int d0 = i;
+  while (i < s.n && is_digit(s.at(i))) ++i;
+  if (i == d0) return false;
+  while (i < s.n && is_space(s.at(i))) ++i;
+  const unsigned char op = s.at(i);
+  if (!(op == '+' || op == '-' || op == '*' || op == '/')) return false;
+  ++i;
+  while (i < s.n && is_space(s.at(i))) ++i;
+  d0 = i;
+  while (i < s.n && is_digit(s.at(i))) ++i;
+  if (i == d0) return false;
+  while (i < s.n && is_space(s.at(i))) ++i;
+  if (i < s.n && s.at(i) == '?') ++i;
+  while (i < s.n && is_space(s.at(i))) ++i;
+  return i == s.n;
+}
+
+bool pat_search(const View& s, const Pat& p) {
+  if (p.special == 1) {                          // (?:\b|^)a\*(?:\s|$|\W)
+    for (int i = 0; i + 2 <= s.n; ++i)
+      if (s.at(i) == 'a' && s.at(i + 1) == '*' && (i == 0 || !is_word(s.at(i - 1))) &&
+          (i + 2 == s.n || !is_word(s.at(i + 2))))
+        return true;
+    return false;
+  }
+  if (p.special == 2) return match_math(s, false);
+  if (p.special == 3) return match_math(s, true);
+  std::vector<std::pair<int, int>> cur, nxt, reach;
+  seg_matches(s, p.segs[0], cur);
+  if (cur.empty()) return false;
+  for (size_t k = 1; k < p.segs.size(); ++k) {
+    seg_matches(s, p.segs[k], nxt);
+    reach.clear();
+    for (const auto& m2 : nxt) {
+      bool ok = false;
+      for (const auto& m1 : cur) {
+        if (m2.first < m1.second) continue;
+        bool nl = false;                          // `.` does not match '\n'
+        for (int j = m1.second; j < m2.first && !nl; ++j) nl = s.at(j) == '\n';
+        if (!nl) { ok = true; break; }
+      }
+      if (ok) reach.push_back(m2);
+    }
+    cur.swap(reach);
+    if (cur.empty()) return false;
+  }
+  return true;
+}
+
+Pat words(std::vector<std::string> alts, bool wb_start = true, bool wb_end = true) {
+  Pat p;
+  p.segs.push_back(Seg{wb_start, wb_end, std::move(alts)});
+  return p;
+}
+Pat gap(std::vector<std::string> a, std::vector<std::string> b) {
+  Pat p;
+  p.segs.push_back(Seg{true, true, std::move(a)});
+  p.segs.push_back(Seg{true, true, std::move(b)});
+  return p;
+}
+Pat special(int k) {
+  Pat p;
+  p.special = k;
+  return p;
+}
+
+struct Tables {
+  std::vector<std::vector<Pat>> complex_cats, simple_cats;   // in the reference's dict order
+  std::vector<std::string> code_markers;
+  Tables() {
+    complex_cats = {
+        // code_build_debug
+        {words({"write", "implement", "code", "program", "script", "build", "refactor", "debug", "fix"}),
+         words({"traceback", "exception", "error", "segfault", "timeout", "hanging"}),
+         words({"api", "flask", "fastapi", "docker", "kubernetes", "ssh", "tunnel", "nginx"}),
+         words({"system design", "architecture", "distributed", "scalability", "load balanc"})},
+        // math_cs_theory
+        {words({"prove", "lemma", "theorem", "corollary", "derivative", "integral", "gradient"}),
+         words({"time complexity", "space complexity", "big-o", "big o"}),
+         words({"dynamic programming", "dp", "graph", "dijkstra", "bfs", "dfs"}), special(1)},
+        // reasoning_comparison
+        {words({"compare", "contrast", "difference between", "pros and cons", "vs.", "vs", "versus"}),
+         words({"evaluate", "assess", "critique", "analyze"})},
+        // long_form_generation
+        {words({"essay", "report", "proposal", "research paper", "literature review", "methodology"}),
+         words({"comprehensive", "in-depth", "step-by-step", "step by step", "step-by step", "step by-step",
+                "detailed"}),
+         gap({"summarize", "synthesis"}, {"everything", "all", "so far", "entire"}),
+         words({"transcript", "debate", "dialogue", "format as json", "markdown table"})},
+        // data_engineering
+        {words({"etl", "pipeline", "spark", "hadoop", "presto", "sql", "csv", "excel", "dataframe", "dataset"}),
+         words({"deduplicate", "normalize", "clean", "transform", "parse", "extract"})},
+        // medical_analysis
+        {words({"symptom", "diagnosis", "treatment", "therapy", "prognosis", "chronic", "severe"}),
+         words({"pain", "migraine", "dizziness", "fatigue", "nausea", "inflammation", "anxiety", "depression"}),
+         gap({"dietary", "meal", "training", "exercise", "recovery"}, {"plan", "schedule", "regimen"}),
+         words({"mental health", "psycholog", "counseling", "therapist", "physician", "hospital"})},
+        // context_heavy
+        {words({"using all context", "using all history", "using all above", "using the context",
+                "using the history", "using the above", "based on the conversation", "based on the context",
+                "based on our conversation", "based on our context"}),
+         gap({"continue", "expand", "build on", "follow up"}, {"previous", "earlier", "above"})},
+    };
+    simple_cats = {
+        // greeting
+        {words({"hi", "hello", "hey", "yo", "sup"}), words({"good morning", "good afternoon", "good evening"}),
+         words({"thanks", "thank you"})},
+        // general_knowledge
+        {words({"what is", "who is", "where is", "when is", "when did", "how many", "capital of"}),
+         words({"tell me a joke", "fun fact", "random fact"}), words({"how to", "how do i", "can you tell me"})},
+        // wellness_tips
+        {words({"benefit of", "benefits of", "tip for", "tips for", "advice on"}),
+         words({"daily intake", "how often", "how much"}),
+         gap({"healthy", "good"}, {"habit", "routine", "lifestyle"})},
+        // short_definition
+        {words({"define", "meaning of", "definition of"}), gap({"what does"}, {"mean"})},
+        // tiny_math
+        {special(2), special(3)},
+    };
+    code_markers = {"```", "def ", "class ", "import ", "Traceback", "Exception", "ModuleNotFoundError",
+                    "SELECT ", "WITH ", "FROM ", "JOIN ", ";", "{", "}", "->", "::", "==", "!="};
+  }
+};
+
+const Tables& tables() {
+  static const Tables t;
+  return t;
+}
+
+bool contains(const View& s, const std::string& m) {
+  const int L = static_cast<int>(m.size());
+  for (int i = 0; i + L <= s.n; ++i)
+    if (memcmp(s.p + i, m.data(), L) == 0) return true;
+  return false;
+}
+
+void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_heur_params_t& hp,
+                  int32_t* tok, uint8_t* dev, double* conf, int32_t* rule, int32_t* cat) {
+  const Tables& T = tables();
+  const bool has_ctx = ctx_len > 0;               // `if context` — an empty string is falsy
+  // token estimate over f"{context}\n{query}" (qre:91,96); the ORIGINAL query, not the stripped one
+  const int64_t full_len = has_ctx ? ctx_len + 1 + q_len : q_len;
+  const int64_t t = full_len / 4 > 1 ? full_len / 4 : 1;
+  *tok = static_cast<int32_t>(t > 0x7fffffff ? 0x7fffffff : t);
+  for (int64_t i = 0; i < q_len; ++i)
+    if (static_cast<unsigned char>(q_raw[i]) >= 0x80) { *rule = -1; *cat = -1; *dev = 0; *conf = 0.0; return; }
+  // q = query.strip(); ql = q.lower()
+  int64_t b = 0, e = q_len;
+  while (b < e && is_space(static_cast<unsigned char>(q_raw[b]))) ++b;
+  while (e > b && is_space(static_cast<unsigned char>(q_raw[e - 1]))) --e;
+  const View q{q_raw + b, static_cast<int>(e - b)};
+  std::string low(q.p, q.n);
+  for (char& c : low)
+    if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
+  const View ql{low.data(), q.n};
+  const uint8_t heavy = static_cast<uint8_t>(hp.n_devices - 1), light = 0;
+  *cat = -1;
+  for (size_t c = 0; c < T.complex_cats.size(); ++c)
+    for (const Pat& p : T.complex_cats[c])
+      if (pat_search(ql, p)) { *rule = 0; *cat = static_cast<int32_t>(c); *dev = heavy; *conf = 0.92; return; }
+  if (q.n >= hp.long_chars) { *rule = 1; *dev = heavy; *conf = 0.80; return; }
+  int qm = 0;
+  for (int i = 0; i < q.n; ++i) qm += q.p[i] == '?';
+  if (qm >= hp.multi_qmarks) { *rule = 2; *cat = qm; *dev = heavy; *conf = 0.80; return; }
+  int marks = 0;
+  for (const std::string& m : T.code_markers) marks += contains(q, m) ? 1 : 0;
+  if (marks >= hp.code_markers_needed) { *rule = 3; *dev = heavy; *conf = 0.88; return; }
+  if (has_ctx && ctx_len >= hp.context_chars) { *rule = 4; *dev = heavy; *conf = 0.75; return; }
+  for (size_t c = 0; c < T.simple_cats.size(); ++c)
+    for (const Pat& p : T.simple_cats[c])
+      if (pat_search(ql, p)) { *rule = 5; *cat = static_cast<int32_t>(c); *dev = light; *conf = 0.90; return; }
+  int words_n = 0;
+  for (int i = 0; i < ql.n;) {
+    while (i < ql.n && is_space(ql.at(i))) ++i;
+    if (i < ql.n) ++words_n;
+    while (i < ql.n && !is_space(ql.at(i))) ++i;
+  }
+  if (words_n <= 15 && q.n <= 100) { *rule = 6; *dev = light; *conf = 0.75; return; }
+  // no rule fired: token router's device, half its confidence (qre:357-364)
+  const int thr = hp.token_threshold;
+  const int64_t diff = t > thr ? t - thr : thr - t;
+  double c = static_cast<double>(diff) / static_cast<double>(thr > 1 ? thr : 1);
+  if (c > 1.0) c = 1.0;
+  *rule = 7;
+  *dev = t > thr ? 1 : 0;
+  *conf = c * 0.5;
+}
+
+}  // namespace
+
+extern "C" QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64_t* query_len,
+                                         const int64_t* context_len, const qre_heur_params_t* hp, int n_threads,
+                                         int32_t* tok, uint8_t* heur_dev, double* heur_conf, int32_t* heur_rule,
+                                         int32_t* heur_cat) {
+  if (n < 0 || hp == nullptr || (n > 0 && (!queries || !query_len || !tok || !heur_dev || !heur_conf ||
+                                           !heur_rule || !heur_cat)))
+    return QRE_ERR_INVALID;
+  if (hp->n_devices < 1) return QRE_ERR_INVALID;
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 256) n_threads = 256;
+  if (n < 64) n_threads = 1;
+  tables();                                       // build the tables before any thread needs them
+  auto work = [&](int64_t i0, int64_t i1) {
+    for (int64_t i = i0; i < i1; ++i)
+      classify_one(queries[i] ? queries[i] : "", queries[i] ? query_len[i] : 0, context_len ? context_len[i] : 0,
+                   *hp, &tok[i], &heur_dev[i], &heur_conf[i], &heur_rule[i], &heur_cat[i]);
+  };
+  if (n_threads == 1) {
+    work(0, n);
+    return QRE_OK;
+  }
+  std::vector<std::thread> th;
+  for (int t = 0; t < n_threads; ++t) th.emplace_back(work, n * t / n_threads, n * (t + 1) / n_threads);
+  for (auto& x : th) x.join();
+  return QRE_OK;
+}

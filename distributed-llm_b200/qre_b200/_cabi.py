@@ -31,7 +31,7 @@ EXPORTS = (
     "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
-    "qre_lookup_route_begin", "qre_lookup_route_end",
+    "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
 )
 
 
@@ -349,3 +349,29 @@ def exact_lookup_noalloc(device: int, n_rows: int, dim: int, rows_ptr: int, row_
         C.c_void_p(hit_sim_ptr), C.c_void_p(stream or None), err, C.c_size_t(len(err)))
     if rc != 0:
         raise QreError(f"libqre_b200 error {rc}: {err.value.decode()}")
+
+
+class HeurParams(C.Structure):
+    _fields_ = [("long_chars", C.c_int32), ("multi_qmarks", C.c_int32), ("code_markers_needed", C.c_int32),
+                ("context_chars", C.c_int32), ("token_threshold", C.c_int32), ("n_devices", C.c_int32)]
+
+
+def host_features(queries, context_lens, hp: HeurParams, n_threads: int = 0) -> dict:
+    """qre_host_features for a list of str: token estimate + heuristic rule per query, computed on
+    C++ threads (no GIL).  rule == -1 marks queries the caller must classify itself (non-ASCII)."""
+    lib = load()
+    n = len(queries)
+    enc = [q.encode("utf-8") for q in queries]
+    ptrs = (C.c_char_p * n)(*enc)
+    qlen = np.array([len(b) for b in enc], np.int64)
+    clen = np.ascontiguousarray(context_lens, np.int64)
+    out = dict(tok=np.empty(n, np.int32), heur_dev=np.empty(n, np.uint8), heur_conf=np.empty(n, np.float64),
+               rule=np.empty(n, np.int32), cat=np.empty(n, np.int32))
+    if n_threads <= 0:
+        n_threads = min(32, os.cpu_count() or 1)
+    rc = lib.qre_host_features(C.c_int64(n), ptrs, _ptr(qlen), _ptr(clen), C.byref(hp), C.c_int(n_threads),
+                               _ptr(out["tok"]), _ptr(out["heur_dev"]), _ptr(out["heur_conf"]), _ptr(out["rule"]),
+                               _ptr(out["cat"]))
+    if rc != 0:
+        raise QreError(f"qre_host_features failed with {rc}")
+    return out

@@ -305,6 +305,50 @@ class HeuristicRouter(BaseRouter):
         return RoutingDecision(device=self._names[dev], confidence=conf, method=method, reasoning=why,
                                complexity_score=score)
 
+    def classify_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
+        """`classify` for a whole batch on C++ threads (libqre_b200 qre_host_features); the few
+        queries with non-ASCII characters, and every query when a real tokenizer is installed,
+        go through `classify`.  Returns (list of classify() tuples, token counts)."""
+        n = len(queries)
+        if LITELLM_AVAILABLE:
+            feats = [self.classify(q, c) for q, c in zip(queries, contexts)]
+            return feats, [self._token_fallback.count(q, c) for q, c in zip(queries, contexts)]
+        hp = _cabi.HeurParams(self.long_text_threshold, self.multi_question_threshold, self.code_markers_needed,
+                              self.context_chars_threshold, self._token_fallback.threshold, len(self._names))
+        safe_q = [(q or "") for q in queries]
+        r = _cabi.host_features(safe_q, [len(c) if c else 0 for c in contexts], hp)
+        ccat, scat = list(self.COMPLEX), list(self.SIMPLE)
+        feats, toks = [], []
+        for i in range(n):
+            rule = int(r["rule"][i])
+            if rule < 0:
+                feats.append(self.classify(queries[i], contexts[i]))
+                toks.append(self._token_fallback.count(queries[i], contexts[i]))
+                continue
+            dev, conf, tok = int(r["heur_dev"][i]), float(r["heur_conf"][i]), int(r["tok"][i])
+            q = safe_q[i].strip()
+            method, score = "heuristic", None
+            if rule == 0:
+                why = f"complex pattern={ccat[int(r['cat'][i])]}"
+            elif rule == 1:
+                why = f"long query chars={len(q)}"
+            elif rule == 2:
+                why = f"multi-question count={int(r['cat'][i])}"
+            elif rule == 3:
+                why = "code/debug markers detected"
+            elif rule == 4:
+                why = f"large context chars={len(contexts[i])}"
+            elif rule == 5:
+                why = f"simple pattern={scat[int(r['cat'][i])]}"
+            elif rule == 6:
+                why = "short everyday query"
+            else:
+                method, score = "heuristic_fallback", float(tok)
+                why = f"no heuristic match -> tokens={tok} threshold={self._token_fallback.threshold}"
+            feats.append((dev, conf, method, why, score))
+            toks.append(tok)
+        return feats, toks
+
 
 # ----------------------------------------------------------------------------- hybrid
 class HybridRouter(BaseRouter):
@@ -535,8 +579,12 @@ class QueryRouter:
         r = self.router
         hybrid = isinstance(r, HybridRouter)
         sem = r.routers["semantic"] if hybrid else r
-        feats = [r.features(q, c) if hybrid else (r._token_fallback.route(q, c), (0, 0.0, "", "", None))
-                 for q, c in zip(queries, contexts)]
+        if hybrid:        # heuristic rules + token estimate for the whole batch on C++ threads
+            hfeats, toks = r.routers["heuristic"].classify_batch(list(queries), contexts)
+            tr = r.routers["token"]
+            feats = [(tr._decision(t, *tr.decide(t)), h) for t, h in zip(toks, hfeats)]
+        else:
+            feats = [(r._token_fallback.route(q, c), (0, 0.0, "", "", None)) for q, c in zip(queries, contexts)]
         route_in = dict(tok=np.array([int(t.complexity_score) for t, _ in feats], np.int32),
                         heur_dev=np.array([h[0] for _, h in feats], np.uint8),
                         heur_conf=np.array([h[1] for _, h in feats], np.float64))

@@ -200,6 +200,28 @@ QRE_API int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_c
                         const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
                         const qre_params_t* params, qre_result_t* out_dev, void* stream);
 
+/* ---- host-side per-query features for a batch (no GPU involved) -----------------------------
+ * HeuristicRouter.route (qre:323-364, patterns qre:231-294) and the no-tokenizer token estimate
+ * of TokenBasedRouter (qre:91,96) for n queries on `n_threads` C++ threads.  `queries[i]` are
+ * UTF-8 bytes of length query_len[i]; context_len[i] is len(context) in characters (<= 0: no
+ * context).  Outputs: tok[i]; heur_dev/heur_conf[i]; heur_rule[i] = which rule fired
+ * (0 complex pattern, 1 long query, 2 multi-question, 3 code markers, 4 large context,
+ * 5 simple pattern, 6 short everyday query, 7 token fallback; -1 = the query has non-ASCII
+ * characters and must be classified by the caller's Unicode-aware code); heur_cat[i] = pattern
+ * category index for rules 0 / 5 (the '?' count for rule 2). */
+typedef struct {
+  int32_t long_chars;            /* heuristic_long_chars          (qre:225) */
+  int32_t multi_qmarks;          /* heuristic_multi_qmarks        (qre:226) */
+  int32_t code_markers_needed;   /* heuristic_code_markers_needed (qre:227) */
+  int32_t context_chars;         /* heuristic_context_chars       (qre:228) */
+  int32_t token_threshold;       /* token_threshold               (qre:87)  */
+  int32_t n_devices;
+} qre_heur_params_t;
+QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64_t* query_len,
+                              const int64_t* context_len, const qre_heur_params_t* hp, int n_threads,
+                              int32_t* tok, uint8_t* heur_dev, double* heur_conf, int32_t* heur_rule,
+                              int32_t* heur_cat);
+
 /* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 QRE_API int qre_launch_count(const qre_cache_t* h, int64_t* count);
 

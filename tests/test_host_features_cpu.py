@@ -1,0 +1,102 @@
+"""CPU: qre_host_features (C++ threads) against HeuristicRouter.classify (Python `re`) on a large
+generated ASCII corpus that stresses every pattern, word-boundary quirk and rule order; and, when
+the reference tree is mounted, against the reference's own HeuristicRouter."""
+import numpy as np
+import pytest
+
+from oracle import ref_harness
+from qre_b200 import _cabi
+from tests import replay_common as R
+from tests.fake_engine import OracleEngine
+
+VOCAB = """write implement code program script build refactor debug fix traceback exception error segfault timeout
+hanging api flask fastapi docker kubernetes ssh tunnel nginx system design architecture distributed scalability
+load balanc balancing prove lemma theorem corollary derivative integral gradient time space complexity big-o big o
+dynamic programming dp graph dijkstra bfs dfs a* a*b compare contrast difference between pros and cons vs vs. versus
+evaluate assess critique analyze essay report proposal research paper literature review methodology comprehensive
+in-depth step-by-step step by step detailed summarize synthesis everything all so far entire transcript debate
+dialogue format as json markdown table etl pipeline spark hadoop presto sql csv excel dataframe dataset deduplicate
+normalize clean transform parse extract symptom diagnosis treatment therapy prognosis chronic severe pain migraine
+dizziness fatigue nausea inflammation anxiety depression dietary meal training exercise recovery plan schedule
+regimen mental health psycholog psychology counseling therapist physician hospital using the context history above
+based on our conversation continue expand build on follow up previous earlier hi hello hey yo sup good morning
+afternoon evening thanks thank you what is who is where is when did how many capital of tell me a joke fun fact
+random how to how do i can you tell me benefit benefits of tip tips for advice on daily intake how often how much
+healthy habit routine lifestyle define meaning of definition what does mean 2+2 12 * 3 ? what is 7/8? the of a an
+cat dog blue apple_pie under_score x9 versus. fixes prefix codex apis hi5 thanksgiving report's""".split()
+FILLERS = ["the", "of", "quick", "brown", "fox", "zzz", "lorem", "ipsum", "42", "ok", "maybe", "really"]
+PUNCT = [" ", " ", " ", ", ", ". ", "? ", "! ", "\n", "\t", " - ", "; ", " {", "} ", "==", "->", "::", "```", "."]
+MARKERS = ["def ", "class ", "import ", "Traceback", "Exception", "SELECT ", "FROM ", "JOIN ", "WITH ", "!="]
+
+
+def _corpus(n, seed):
+    rs = np.random.Generator(np.random.PCG64(seed))
+    out = []
+    for i in range(n):
+        k = int(rs.choice([1, 2, 3, 5, 8, 14, 18, 30, 120]))
+        parts = []
+        plain = rs.random() < 0.2              # fillers only: reaches the length / word-count / fallback rules
+        for _ in range(k):
+            u = 0.5 + 0.4 * rs.random() if plain else rs.random()
+            w = str(rs.choice(VOCAB)) if u < 0.45 else (str(rs.choice(FILLERS)) if u < 0.9 else str(rs.choice(MARKERS)))
+            if rs.random() < 0.15:
+                w = w.upper() if rs.random() < 0.5 else w.capitalize()
+            parts.append(w)
+            parts.append(" " if plain else str(rs.choice(PUNCT)))
+        q = "".join(parts)
+        if rs.random() < 0.2:
+            q = " \t" + q + "  \n"
+        if rs.random() < 0.03:
+            q = f"{rs.integers(0, 99)} {rs.choice(list('+-*/'))} {rs.integers(0, 99)}{rs.choice(['', '?', ' ?'])}"
+        if rs.random() < 0.02:
+            q = "what is " + f"{rs.integers(0, 99)}{rs.choice(list('+-*/'))}{rs.integers(0, 99)}?"
+        if rs.random() < 0.02:
+            q = ""
+        if rs.random() < 0.03:
+            q += " café naïve"            # non-ASCII: must be handed back (rule -1)
+        ctx_len = int(rs.choice([0, 0, 5, 799, 800, 3199, 3200, 9000]))
+        out.append((q, None if ctx_len == 0 else "c" * ctx_len))
+    return out
+
+
+CFGS = [dict(), dict(heuristic_long_chars=800, heuristic_multi_qmarks=2, heuristic_code_markers_needed=2,
+                     heuristic_context_chars=3200, token_threshold=1000),
+        dict(heuristic_long_chars=40, heuristic_multi_qmarks=1, heuristic_code_markers_needed=1,
+             heuristic_context_chars=5, token_threshold=3)]
+
+
+@pytest.mark.parametrize("ci", range(len(CFGS)))
+def test_cpp_features_equal_python_classifier(ci):
+    _, qre_mod, _ = R.load_modules(None, OracleEngine)
+    hr = qre_mod.HeuristicRouter(CFGS[ci])
+    corpus = _corpus(6000, 10 + ci)
+    qs, cs = [q for q, _ in corpus], [c for _, c in corpus]
+    feats, toks = hr.classify_batch(qs, cs)
+    prefix = {"complex pattern": 0, "long query chars": 1, "multi-question count": 2,
+              "code/debug markers detected": 3, "large context chars": 4, "simple pattern": 5,
+              "short everyday query": 6, "no heuristic match": 7}
+    exp_rule = []
+    for (q, c), f, t in zip(corpus, feats, toks):
+        exp = hr.classify(q, c)
+        assert f == exp, (q, c and len(c), f, exp)
+        assert t == hr._token_fallback.count(q, c)
+        exp_rule.append(-1 if not q.isascii() else prefix[exp[3].split("=")[0].split(" ->")[0]])
+    hp = _cabi.HeurParams(hr.long_text_threshold, hr.multi_question_threshold, hr.code_markers_needed,
+                          hr.context_chars_threshold, hr._token_fallback.threshold, 2)
+    r = _cabi.host_features(qs, [len(c) if c else 0 for c in cs], hp, n_threads=4)
+    assert np.array_equal(r["rule"], np.array(exp_rule, np.int32))
+    if ci == 0:      # with the default thresholds the corpus reaches every rule
+        assert set(exp_rule) == {-1, 0, 1, 2, 3, 4, 5, 6, 7}
+
+
+@pytest.mark.skipif(not ref_harness.available(), reason="reference tree not mounted")
+def test_cpp_features_equal_live_reference():
+    _, ref_qre, _ = ref_harness.load_reference()
+    _, qre_mod, _ = R.load_modules(None, OracleEngine)
+    cfg = dict(ref_qre.PRODUCTION_CFG)
+    a, b = ref_qre.HeuristicRouter(cfg), qre_mod.HeuristicRouter(cfg)
+    corpus = _corpus(4000, 99)
+    feats, _ = b.classify_batch([q for q, _ in corpus], [c for _, c in corpus])
+    for (q, c), f in zip(corpus, feats):
+        d = a.route(q, c)
+        assert (["nano", "orin"].index(d.device), d.confidence, d.method, d.reasoning, d.complexity_score) == f, (q, f, d)

@@ -85,3 +85,68 @@ def test_random_ops_match_live_reference(seed, tmp_path):
         sa, sb = _snap(a), _snap(b)
         assert sa == sb, (step, op, sa, sb)
     assert n_hits > 5 and n_miss > 5
+
+
+@pytest.mark.parametrize("seed,strategy", [(0, "hybrid"), (1, "hybrid"), (2, "semantic"), (3, "token"),
+                                           (4, "heuristic"), (5, "perf")])
+def test_random_route_query_matches_live_reference(seed, strategy):
+    """QueryRouter.route_query driven with random queries / contexts / clock on both
+    implementations: same device, method, cache_hit flag, confidence and reasoning text."""
+    import zlib
+    clock = ref_harness.FakeClock()
+    _, ref_qre, ref_st = ref_harness.load_reference(clock)
+    _, qre_mod, st = R.load_modules(clock, OracleEngine)
+    rs = np.random.Generator(np.random.PCG64(100 + seed))
+    d = 384
+    u = rs.standard_normal((2, d))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    cents = np.stack([u[0] + 0.3 * u[1], u[1] + 0.3 * u[0]]).astype(np.float32)
+    topics = ["hello there", "what is the capital of France", "implement a red black tree in python",
+              "compare TCP and UDP? which is faster? why?", "tell me a joke", "summarize everything so far",
+              "x == y != z;", "lorem ipsum dolor sit amet consectetur " * 4, "explain " + "very " * 60 + "long",
+              "2+2?", "how often should I exercise"]
+    table = {}
+    pool = []
+    for t in topics:
+        base = rs.uniform(-0.3, 1.0) * u[0] + rs.uniform(-0.3, 1.0) * u[1] + 0.7 * rs.standard_normal(d) / np.sqrt(d)
+        for v in range(3):
+            text = t if v == 0 else f"{t} (variant {v})"
+            table[text] = (base + (0.0 if v == 0 else rs.choice([0.03, 0.4])) * rs.standard_normal(d) / np.sqrt(d)
+                           ).astype(np.float32)
+            pool.append(text)
+    for mod in (ref_st, st):
+        mod.set_table(table, dim=d)
+    cfg = dict(ref_qre.PRODUCTION_CFG)
+    cfg["cache_max_size"] = 12
+    cfg["cache_ttl_seconds"] = 60
+    ours_cfg = dict(cfg)
+    ours_cfg["centroids"], ours_cfg["centroid_owner"] = cents, [0, 1]
+    a = ref_qre.QueryRouter(strategy=strategy, config=cfg)
+    b = qre_mod.QueryRouter(strategy=strategy, config=ours_cfg)
+    # give the reference the same centroids (its own come from the label file through the stub)
+    sem_a = a.router if strategy == "semantic" else (a.router.routers["semantic"] if strategy == "hybrid" else None)
+    if sem_a is not None:
+        sem_a.nano_center, sem_a.orin_center = cents[0], cents[1]
+    ctx_pool = [None, "user: hi", "u: " + "earlier turn. " * 100, "u: " + "long history " * 300]
+    kinds = set()
+    for step in range(250):
+        if rs.random() < 0.15:
+            clock.advance(float(rs.choice([1.0, 20.0, 70.0])))
+        if strategy == "perf" and rs.random() < 0.3:
+            args = (str(rs.choice(["nano", "orin"])), float(rs.uniform(50, 900)), int(rs.integers(0, 200)),
+                    bool(rs.random() < 0.8))
+            a.update_perf(*args); b.update_perf(*args)
+        q = str(rs.choice(pool))
+        context = ctx_pool[int(rs.integers(0, len(ctx_pool)))]
+        key = str(rs.choice(["k1", "k2"])) if rs.random() < 0.9 else None
+        da = a.route_query(q, context=context, context_key=key)
+        db = b.route_query(q, context=context, context_key=key)
+        assert (da.device, da.method, da.cache_hit, da.reasoning) == (db.device, db.method, db.cache_hit, db.reasoning), \
+            (step, q, da, db)
+        assert da.confidence == db.confidence and da.complexity_score == db.complexity_score, (step, da, db)
+        kinds.add((da.method, da.cache_hit))
+        sa, sb = a.get_cache_stats(), b.get_cache_stats()
+        for k in ("size", "hits", "attempts", "evictions", "hybrid_fallbacks"):
+            assert sa[k] == sb[k], (step, k, sa[k], sb[k])
+    assert any(m.endswith("_cached") for m, _ in kinds) and any(not c for _, c in kinds)
+    del zlib
