@@ -346,6 +346,10 @@ def run_b200(args):
         t_e2e = float(t.item())
     e2e_value = M * args.steps / t_e2e
 
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     pk = peaks()

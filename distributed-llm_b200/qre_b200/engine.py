@@ -7,11 +7,24 @@ Shard without an sm_100 GPU raises `QreError`.
 """
 from __future__ import annotations
 
+import functools
+import threading
 from typing import Dict, Optional, Sequence
 
 import numpy as np
 
 from . import _cabi
+
+
+def _locked(fn):
+    """A qre_cache_t handle is not thread-safe (include/qre_b200.h): the cache and the routers
+    that share one Engine may be called from different request threads, so every native call
+    goes through the engine's lock."""
+    @functools.wraps(fn)
+    def wrapper(self, *a, **k):
+        with self._lock:
+            return fn(self, *a, **k)
+    return wrapper
 
 
 class Engine:
@@ -23,10 +36,12 @@ class Engine:
         self._centroids: Optional[np.ndarray] = None
         self._owner: Optional[np.ndarray] = None
         self._health: Optional[np.ndarray] = None
+        self._lock = threading.RLock()
         if dim is not None:
             self.ensure(dim)
 
     # ---- lifetime ----
+    @_locked
     def ensure(self, dim: int) -> _cabi.Shard:
         if self.shard is None:
             self.shard = _cabi.Shard(dim=int(dim), capacity=self.capacity, max_batch=self.max_batch,
@@ -39,12 +54,14 @@ class Engine:
             raise ValueError(f"embedding dimension changed: cache holds {self.shard.dim}-d rows, got {dim}")
         return self.shard
 
+    @_locked
     def close(self) -> None:
         if self.shard is not None:
             self.shard.close()
             self.shard = None
 
     # ---- router state ----
+    @_locked
     def set_centroids(self, centroids: np.ndarray, owner: Sequence[int]) -> None:
         self._centroids = np.ascontiguousarray(centroids, np.float32)
         self._owner = np.ascontiguousarray(owner, np.uint8)
@@ -53,6 +70,7 @@ class Engine:
         else:
             self.shard.set_centroids(self._centroids, self._owner)
 
+    @_locked
     def set_perf_health(self, health: Sequence[float]) -> None:
         self._health = np.ascontiguousarray(health, np.float64)
         if self.shard is not None:
@@ -63,15 +81,18 @@ class Engine:
         return 0 if self._centroids is None else int(self._centroids.shape[0])
 
     # ---- store interface used by QueryCache ----
+    @_locked
     def append(self, row, ctx: int, ts_us: int, lru: int, pdev: int, pconf: float) -> int:
         row = np.ascontiguousarray(row, np.float32).reshape(1, -1)
         sh = self.ensure(row.shape[1])
         return int(sh.append(row, [ctx], [ts_us], [lru], [pdev], [pconf])[0])
 
+    @_locked
     def append_many(self, rows, ctx, ts_us, lru, pdev, pconf) -> np.ndarray:
         rows = np.ascontiguousarray(rows, np.float32)
         return self.ensure(rows.shape[1]).append(rows, ctx, ts_us, lru, pdev, pconf)
 
+    @_locked
     def update(self, slot: int, row=None, ts_us=None, lru=None, pdev=None, pconf=None) -> None:
         one = lambda v, dt: None if v is None else np.array([v], dt)   # noqa: E731
         self.shard.update(np.array([slot], np.int64),
@@ -79,18 +100,22 @@ class Engine:
                           ts_us=one(ts_us, np.int64), lru_seq=one(lru, np.uint64),
                           pred_dev=one(pdev, np.uint8), pred_conf=one(pconf, np.float64))
 
+    @_locked
     def tombstone(self, slots) -> None:
         slots = np.asarray(list(slots), np.int64)
         if slots.size and self.shard is not None:
             self.shard.tombstone(slots)
 
+    @_locked
     def clear(self) -> None:
         if self.shard is not None:
             self.shard.clear()
 
+    @_locked
     def read_rows(self, slots) -> np.ndarray:
         return self.shard.read_rows(np.asarray(list(slots), np.int64))
 
+    @_locked
     def scan(self, q, q_ctx, now_us: int, cfg: _cabi.RouteConfig, route_in: Optional[dict] = None) -> dict:
         """One fused device pass for a batch: lookup (always) + route (when route_in is given:
         dict(tok, heur_dev, heur_conf))."""
