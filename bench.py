@@ -344,16 +344,18 @@ def run_b200(args):
                 main.wait_event(ev_in[b])
                 dq = d_buf[b]
                 if pipelined:
-                    o, ev = look.step_pipelined(dq["Q"], dq["ctx"], NOW_US, dq["tok"], dq["hd"], dq["hc"])
-                    main.wait_event(ev)
+                    o, _ = look.step_pipelined(dq["Q"], dq["ctx"], NOW_US, dq["tok"], dq["hd"], dq["hc"])
+                    out_st = look.side            # the read-back follows the merge on the side stream
                 else:
                     o = look.step(dq["Q"], dq["ctx"], NOW_US, dq["tok"], dq["hd"], dq["hc"])
+                    out_st = main
                 if h_out[b] is None:
                     h_out[b] = {k: torch.empty(o[k].shape, dtype=o[k].dtype).pin_memory() for k in keys}
-                for k in keys:
-                    h_out[b][k].copy_(o[k], non_blocking=True)
-                ev_out[b] = torch.cuda.Event()
-                ev_out[b].record(main)
+                with torch.cuda.stream(out_st):
+                    for k in keys:
+                        h_out[b][k].copy_(o[k], non_blocking=True)
+                    ev_out[b] = torch.cuda.Event()
+                    ev_out[b].record(out_st)
             for e in ev_out:
                 if e is not None:
                     e.synchronize()
