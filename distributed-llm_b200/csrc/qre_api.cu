@@ -157,6 +157,15 @@ struct qre_cache {
   size_t dump_bytes = 0;
   int64_t launches = 0;
   int last_m = 0;
+  // peer exchange (qre_xchg_*): [2 slots][world][max_batch * QRE_TOPK] records, then
+  // [2][world][32] uint32 flags; mapped into every peer process with CUDA IPC
+  uint8_t* xchg = nullptr;
+  size_t xchg_flags_off = 0;
+  int xchg_world = 0, xchg_rank = 0;
+  uint8_t* xchg_peer[16] = {};
+  bool xchg_open[16] = {};
+  uint32_t xchg_pub_epoch = 0, xchg_merge_epoch = 0;
+  unsigned* xchg_ticket = nullptr;
 };
 
 namespace {
@@ -389,6 +398,10 @@ int qre_cache_destroy(qre_cache_t* h) {
     if (h->hs[b].e_mid) cudaEventDestroy(h->hs[b].e_mid);
     if (h->hs[b].e_done) cudaEventDestroy(h->hs[b].e_done);
   }
+  for (int pr = 0; pr < 16; ++pr)
+    if (h->xchg_open[pr] && h->xchg_peer[pr]) cudaIpcCloseMemHandle(h->xchg_peer[pr]);
+  if (h->xchg) cudaFree(h->xchg);
+  if (h->xchg_ticket) cudaFree(h->xchg_ticket);
   if (h->h2d) cudaStreamDestroy(h->h2d);
   if (h->d2h) cudaStreamDestroy(h->d2h);
   if (s.prof_ev) {
@@ -718,6 +731,98 @@ static void scatter_results(const qre_cache_t::HostSlot& S, int K, int D, qre_re
     QRE_OUT(score, sizeof(double) * (size_t)m * D);
   }
 #undef QRE_OUT
+}
+
+// ---- peer exchange of candidate lists (replaces the NCCL all-gather) ------------------------
+static size_t xchg_list_records(const qre_cache_t* h) { return (size_t)h->s.max_batch * QRE_TOPK; }
+
+int qre_xchg_init(qre_cache_t* h, int world, int rank, uint8_t* handle_out) {
+  if (h == nullptr || handle_out == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (world < 1 || world > 16 || rank < 0 || rank >= world) return fail(QRE_ERR_INVALID, "bad world/rank");
+  if (h->xchg != nullptr) return fail(QRE_ERR_INVALID, "exchange already initialised");
+  static_assert(sizeof(cudaIpcMemHandle_t) == QRE_IPC_HANDLE_BYTES, "handle size");
+  DeviceGuard guard(h->s.device);
+  const size_t lists = sizeof(qre_candidate_t) * 2 * (size_t)world * xchg_list_records(h);
+  h->xchg_flags_off = align_up(lists, 256);
+  const size_t total = h->xchg_flags_off + sizeof(uint32_t) * 2 * (size_t)world * 32;
+  QRE_CUDA(cudaMalloc((void**)&h->xchg, total));
+  QRE_CUDA(cudaMemset(h->xchg, 0, total));
+  QRE_CUDA(cudaMalloc((void**)&h->xchg_ticket, sizeof(unsigned)));
+  QRE_CUDA(cudaMemset(h->xchg_ticket, 0, sizeof(unsigned)));
+  cudaIpcMemHandle_t ipc;
+  QRE_CUDA(cudaIpcGetMemHandle(&ipc, h->xchg));
+  memcpy(handle_out, &ipc, sizeof(ipc));
+  h->xchg_world = world;
+  h->xchg_rank = rank;
+  h->xchg_peer[rank] = h->xchg;
+  h->xchg_pub_epoch = h->xchg_merge_epoch = 0;
+  return QRE_OK;
+}
+
+int qre_xchg_connect(qre_cache_t* h, int peer, const uint8_t* handle) {
+  if (h == nullptr || handle == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "call qre_xchg_init first");
+  if (peer < 0 || peer >= h->xchg_world || peer == h->xchg_rank) return fail(QRE_ERR_INVALID, "bad peer %d", peer);
+  DeviceGuard guard(h->s.device);
+  cudaIpcMemHandle_t ipc;
+  memcpy(&ipc, handle, sizeof(ipc));
+  void* p = nullptr;
+  QRE_CUDA(cudaIpcOpenMemHandle(&p, ipc, cudaIpcMemLazyEnablePeerAccess));
+  h->xchg_peer[peer] = (uint8_t*)p;
+  h->xchg_open[peer] = true;
+  return QRE_OK;
+}
+
+int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
+                         const qre_params_t* params, int32_t* overflow_count, void* stream) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "call qre_xchg_init / qre_xchg_connect first");
+  for (int pr = 0; pr < h->xchg_world; ++pr)
+    if (h->xchg_peer[pr] == nullptr) return fail(QRE_ERR_INVALID, "peer %d is not connected", pr);
+  if (h->xchg_pub_epoch - h->xchg_merge_epoch >= 2)
+    return fail(QRE_ERR_INVALID, "two batches already published and not merged (the exchange has two slots)");
+  int rc = qre_scan_dev(h, m, queries, q_ctx, params, h->xchg_rank, h->d_cand, overflow_count, stream);
+  if (rc != QRE_OK) return rc;
+  DeviceGuard guard(h->s.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  const uint32_t epoch = ++h->xchg_pub_epoch;
+  const int slot = (int)(epoch & 1u);
+  qre_candidate_t* dst[16];
+  uint32_t* flag[16];
+  for (int pr = 0; pr < h->xchg_world; ++pr) {
+    const size_t idx = (size_t)slot * h->xchg_world + h->xchg_rank;
+    dst[pr] = reinterpret_cast<qre_candidate_t*>(h->xchg_peer[pr]) + idx * xchg_list_records(h);
+    flag[pr] = reinterpret_cast<uint32_t*>(h->xchg_peer[pr] + h->xchg_flags_off) + idx * 32;
+  }
+  h->launches += launch_publish(m, h->xchg_world, h->d_cand, dst, flag, epoch, h->xchg_ticket, st);
+  QRE_CUDA(cudaGetLastError());
+  return QRE_OK;
+}
+
+int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,
+                             const double* heur_conf, const qre_params_t* params, qre_result_t* out_dev,
+                             void* stream) {
+  if (h == nullptr || out_dev == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "exchange not initialised");
+  if (h->xchg_merge_epoch >= h->xchg_pub_epoch) return fail(QRE_ERR_INVALID, "nothing published to merge");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
+  int rc = validate_params(h, params);
+  if (rc != QRE_OK) return rc;
+  if (params->do_route && (!tok || !heur_dev || !heur_conf))
+    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
+  DeviceGuard guard(h->s.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  const uint32_t epoch = ++h->xchg_merge_epoch;
+  const int slot = (int)(epoch & 1u);
+  const qre_candidate_t* lists =
+      reinterpret_cast<const qre_candidate_t*>(h->xchg) + (size_t)slot * h->xchg_world * xchg_list_records(h);
+  const uint32_t* flags = reinterpret_cast<const uint32_t*>(h->xchg + h->xchg_flags_off) +
+                          (size_t)slot * h->xchg_world * 32;
+  h->s.slot = params->pipeline_slot & 1;
+  h->launches += launch_merge_route(h->s, m, h->xchg_world, lists, tok, heur_dev, heur_conf, *params, *out_dev, st,
+                                    (long long)xchg_list_records(h), flags, epoch);
+  QRE_CUDA(cudaGetLastError());
+  return QRE_OK;
 }
 
 int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries, const uint64_t* q_ctx,

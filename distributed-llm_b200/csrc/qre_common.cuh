@@ -145,6 +145,9 @@ int launch_overflow_settle(DeviceState& s, long long n_rows, const uint64_t* q_c
                            qre_candidate_t* cand, cudaStream_t st);
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
-                       const qre_result_t& out, cudaStream_t st);
+                       const qre_result_t& out, cudaStream_t st, long long shard_stride = 0,
+                       const uint32_t* wait_flags = nullptr, uint32_t wait_epoch = 0);
+int launch_publish(int m, int world, const qre_candidate_t* cand, qre_candidate_t* const* dst, uint32_t* const* flag,
+                   uint32_t epoch, unsigned* ticket, cudaStream_t st);
 
 }  // namespace qre

@@ -536,6 +536,9 @@ struct MergeArgs {
   const double* heur_conf;
   qre_params_t p;
   qre_result_t out;
+  long long shard_stride;            // records between consecutive shards' lists in cand_all
+  const uint32_t* wait_flags;        // peer exchange: flags[shard * 32] must equal wait_epoch first
+  uint32_t wait_epoch;
 };
 
 constexpr int kMergeMax = 128;     // n_shards * kTopK <= 128 (up to 16 shards)
@@ -546,6 +549,24 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = blockIdx.x * kWarpsPerBlock + warp;
+  if (a.wait_flags != nullptr) {
+    // Peer exchange: every rank's publish kernel stores its candidates into THIS GPU's buffer over
+    // NVLink and then raises its flag to the batch's epoch.  The publishers run on other GPUs, so
+    // this wait never depends on work queued behind it on this GPU.  Bounded: a dead peer must
+    // abort the job, not hang the box.
+    if (threadIdx.x < a.n_shards) {
+      const volatile uint32_t* f = a.wait_flags + threadIdx.x * 32;
+      const long long t0 = clock64();
+      while (*f != a.wait_epoch) {
+        if (clock64() - t0 > 8000000000LL) {
+          printf("qre: peer %d never published epoch %u (saw %u)\n", threadIdx.x, a.wait_epoch, *f);
+          __trap();
+        }
+      }
+      __threadfence_system();
+    }
+    __syncthreads();
+  }
   if (q >= a.m) return;
 
   // ---- merge: n_shards * kTopK candidates, comparator (sim desc, lru asc) ----
@@ -553,7 +574,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   const int n_cand = a.n_shards * kTopK;
   for (int i = lane; i < n_cand; i += 32) {
     const int r = i / kTopK, k = i - r * kTopK;
-    sc[i] = a.cand_all[(static_cast<long long>(r) * a.m + q) * kTopK + k];
+    const int4* src = reinterpret_cast<const int4*>(a.cand_all + static_cast<long long>(r) * a.shard_stride +
+                                                    static_cast<long long>(q) * kTopK + k);
+    int4* dst = reinterpret_cast<int4*>(sc + i);     // read through L2: peers may have written it
+    dst[0] = __ldcg(src);
+    dst[1] = __ldcg(src + 1);
   }
   __syncwarp();
   qre_candidate_t best0 = empty_cand();
@@ -844,7 +869,8 @@ int launch_overflow_settle(DeviceState& s, long long n_rows, const uint64_t* q_c
 
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
-                       const qre_result_t& out, cudaStream_t st) {
+                       const qre_result_t& out, cudaStream_t st, long long shard_stride, const uint32_t* wait_flags,
+                       uint32_t wait_epoch) {
   MergeArgs a;
   a.m = m; a.n_shards = n_shards; a.dim_pad = s.dim_pad; a.n_centroids = s.n_centroids;
   a.do_route = p.do_route; a.cand_all = cand_all; a.q_f32 = s.q_f32[s.slot]; a.q_norm = s.q_norm[s.slot];
@@ -852,7 +878,52 @@ int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_
   a.centroids = s.centroids; a.cent_norm = s.cent_norm; a.cent_owner = s.cent_owner;
   a.perf_health = s.perf_health; a.tok = tok; a.heur_dev = heur_dev; a.heur_conf = heur_conf; a.p = p;
   a.out = out;
+  a.shard_stride = shard_stride > 0 ? shard_stride : static_cast<long long>(m) * kTopK;
+  a.wait_flags = wait_flags;
+  a.wait_epoch = wait_epoch;
   merge_route_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
+  return 1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Peer exchange: write this rank's candidate lists straight into every rank's exchange buffer
+// (NVLink stores through IPC-mapped pointers), then raise this rank's flag on each of them.
+// ---------------------------------------------------------------------------------------
+struct PublishArgs {
+  int m, world;
+  const qre_candidate_t* cand;
+  qre_candidate_t* dst[16];      // per peer: start of [slot][my rank] in that peer's buffer
+  uint32_t* flag[16];            // per peer: my flag for this slot in that peer's buffer
+  uint32_t epoch;
+  unsigned* ticket;
+};
+
+__global__ void __launch_bounds__(256) publish_kernel(const PublishArgs a) {
+  __shared__ unsigned s_ticket;
+  const long long n16 = static_cast<long long>(a.m) * kTopK * 2;      // int4 words per list
+  const int4* src = reinterpret_cast<const int4*>(a.cand);
+  for (int p = 0; p < a.world; ++p) {
+    int4* d = reinterpret_cast<int4*>(a.dst[p]);
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16;
+         i += static_cast<long long>(gridDim.x) * blockDim.x)
+      d[i] = src[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_ticket = atomicAdd(a.ticket, 1u);
+  __syncthreads();
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence_system();                      // every CTA's stores are ordered before the flags
+  if (threadIdx.x < a.world) *reinterpret_cast<volatile uint32_t*>(a.flag[threadIdx.x]) = a.epoch;
+  if (threadIdx.x == 0) *a.ticket = 0u;
+}
+
+int launch_publish(int m, int world, const qre_candidate_t* cand, qre_candidate_t* const* dst, uint32_t* const* flag,
+                   uint32_t epoch, unsigned* ticket, cudaStream_t st) {
+  PublishArgs a;
+  a.m = m; a.world = world; a.cand = cand; a.epoch = epoch; a.ticket = ticket;
+  for (int p = 0; p < world; ++p) { a.dst[p] = dst[p]; a.flag[p] = flag[p]; }
+  publish_kernel<<<16, 256, 0, st>>>(a);
   return 1;
 }
 

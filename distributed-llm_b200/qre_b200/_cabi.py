@@ -32,6 +32,7 @@ EXPORTS = (
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
     "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
+    "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev",
 )
 
 
@@ -324,6 +325,28 @@ class Shard:
         ms, n = C.c_double(), C.c_int()
         _check(self.lib, self.lib.qre_profile_read(self.h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    # ---- peer exchange ----
+    def xchg_init(self, world: int, rank: int) -> bytes:
+        buf = C.create_string_buffer(64)
+        _check(self.lib, self.lib.qre_xchg_init(self.h, C.c_int(world), C.c_int(rank), buf))
+        return buf.raw
+
+    def xchg_connect(self, peer: int, handle: bytes) -> None:
+        _check(self.lib, self.lib.qre_xchg_connect(self.h, C.c_int(peer), C.c_char_p(handle)))
+
+    def scan_publish_dev(self, m, q_ptr, q_ctx_ptr, cfg: RouteConfig, now_us, ovf_ptr=0, stream=0):
+        p = cfg.to_c(now_us, False)
+        _check(self.lib, self.lib.qre_scan_publish_dev(self.h, C.c_int(m), C.c_void_p(q_ptr), C.c_void_p(q_ctx_ptr),
+                                                       C.byref(p), C.c_void_p(ovf_ptr or None), C.c_void_p(stream)))
+
+    def merge_route_xchg_dev(self, m, cfg: RouteConfig, now_us, out_ptrs: dict, tok_ptr=0, heur_dev_ptr=0,
+                             heur_conf_ptr=0, stream=0):
+        p = cfg.to_c(now_us, bool(tok_ptr))
+        res = Result(**{f: C.c_void_p(out_ptrs.get(f, 0) or None) for f in RESULT_FIELDS})
+        _check(self.lib, self.lib.qre_merge_route_xchg_dev(
+            self.h, C.c_int(m), C.c_void_p(tok_ptr or None), C.c_void_p(heur_dev_ptr or None),
+            C.c_void_p(heur_conf_ptr or None), C.byref(p), C.byref(res), C.c_void_p(stream)))
 
     def debug_gemm(self, m: int, row0: int, n: int) -> np.ndarray:
         out = np.empty((m, n), np.float32)

@@ -49,7 +49,7 @@ def merge_candidates_host(cand_all: np.ndarray) -> np.ndarray:
 
 class ShardedLookup:
     def __init__(self, shard: _cabi.Shard, cfg: _cabi.RouteConfig, rank: int = 0, world: int = 1,
-                 group=None, reserve_sms: int = 8):
+                 group=None, reserve_sms: int = 8, exchange: str = "nccl"):
         import copy
         import torch
         self.torch = torch
@@ -73,6 +73,18 @@ class ShardedLookup:
         self.side = None
         self.done = [None, None]
         self.iter = 0
+        # exchange = "p2p": candidates are stored straight into every peer's buffer by a publish
+        # kernel (CUDA IPC over NVLink) instead of an NCCL all-gather; handles travel once, here.
+        self.exchange = exchange if world > 1 else "nccl"
+        if self.exchange == "p2p":
+            import torch.distributed as dist
+            mine = shard.xchg_init(world, rank)
+            handles = [None] * world
+            dist.all_gather_object(handles, mine, group=group)
+            for peer, hnd in enumerate(handles):
+                if peer != rank:
+                    shard.xchg_connect(peer, hnd)
+            dist.barrier(group=group)
 
     def _new_out(self, m: int):
         torch = self.torch
@@ -142,6 +154,14 @@ class ShardedLookup:
         # stream": name the legacy default stream explicitly (cudaStreamLegacy == 0x1).
         st = torch.cuda.current_stream(self.dev).cuda_stream or 1
         nbytes = m * _cabi.TOPK * 32
+        if self.exchange == "p2p":
+            self.shard.scan_publish_dev(m, q.data_ptr(), q_ctx.data_ptr(), self.cfg, now_us, self.ovf.data_ptr(), st)
+            self.shard.merge_route_xchg_dev(
+                m, self.cfg, now_us, {f: t.data_ptr() for f, t in self.out.items()},
+                tok_ptr=0 if tok is None else tok.data_ptr(),
+                heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
+                heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=st)
+            return self.out
         self.shard.scan_dev(m, q.data_ptr(), q_ctx.data_ptr(), self.cfg, now_us, self.rank,
                             self.cand.data_ptr(), self.ovf.data_ptr(), st)
         if check_overflow and int(self.ovf.item()) > 0:

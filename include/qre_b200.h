@@ -222,6 +222,27 @@ QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64
                               int32_t* tok, uint8_t* heur_dev, double* heur_conf, int32_t* heur_rule,
                               int32_t* heur_cat);
 
+/* ---- peer exchange: the all-gather written as stores into peer memory ------------------------
+ * For a row-sharded cache with one process per GPU on one NVLink/NVSwitch box.  Instead of
+ * handing cand[m, QRE_TOPK] to an NCCL all-gather, each rank's publish kernel writes its lists
+ * directly into every rank's exchange buffer (CUDA-IPC-mapped peer pointers) and then raises a
+ * per-rank flag there; the merge kernel of each rank waits for all flags of the batch before it
+ * reads its local buffer.  Set-up: every rank calls qre_xchg_init (allocates its buffer, returns
+ * a 64-byte IPC handle), the ranks exchange handles out of band (e.g. all_gather_object) and call
+ * qre_xchg_connect once per peer.  Per batch: qre_scan_publish_dev then
+ * qre_merge_route_xchg_dev, in that order, the same number of times on every rank; at most two
+ * published batches may be waiting for their merge (two slots).  A peer that never publishes
+ * makes the merge kernel trap after a few seconds instead of hanging.  Before destroying a
+ * handle, synchronise all ranks (peers write into its buffer). */
+#define QRE_IPC_HANDLE_BYTES 64
+QRE_API int qre_xchg_init(qre_cache_t* h, int world, int rank, uint8_t* handle_out);
+QRE_API int qre_xchg_connect(qre_cache_t* h, int peer, const uint8_t* handle);
+QRE_API int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
+                                 const qre_params_t* params, int32_t* overflow_count, void* stream);
+QRE_API int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,
+                                     const double* heur_conf, const qre_params_t* params,
+                                     qre_result_t* out_dev, void* stream);
+
 /* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
 QRE_API int qre_launch_count(const qre_cache_t* h, int64_t* count);
 

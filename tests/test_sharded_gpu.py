@@ -68,6 +68,21 @@ def _worker(rank, world, port, ret):
         ev.synchronize()
         for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf", "score", "sem_method"):
             ok = ok and np.array_equal(o[k].cpu().numpy(), serial[i][k])
+    # peer-memory exchange instead of the NCCL all-gather: same answers, several batches in a row
+    look_p = ShardedLookup(sh, cfg, rank, world, exchange="p2p")
+    for i, pm in enumerate(perms + perms):
+        a, b, c, d, e = ins[i % 3]
+        o = look_p.step(a, b, w.now_us, c, d, e)
+        torch.cuda.synchronize()
+        for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf", "score", "sem_method", "hit_pred_dev"):
+            ok = ok and np.array_equal(o[k].cpu().numpy(), serial[i % 3][k])
+    # back to back without host synchronisation (the two-slot protocol must hold up)
+    for i in range(12):
+        a, b, c, d, e = ins[i % 3]
+        o = look_p.step(a, b, w.now_us, c, d, e)
+    torch.cuda.synchronize()
+    for k in ("hit_slot", "hit_sim", "dev"):
+        ok = ok and np.array_equal(o[k].cpu().numpy(), serial[11 % 3][k])
     ret[rank] = (bool(ok), int(hit.sum()))
     dist.barrier()
     dist.destroy_process_group()
