@@ -238,7 +238,7 @@ def run_b200(args):
         Q=wq["Q"], ctx=q_ctx_np.view(np.int64), tok=wq["tok"], hd=wq["heur_dev"], hc=wq["heur_conf"]).items()}
     d_in = {k: v.to(dev) for k, v in h.items()}
 
-    pipelined = world >= 4 and not args.no_overlap and args.exchange == "nccl"      # measured: pays off from 4 ranks (profiles/r1_scaling.md)
+    pipelined = world >= 4 and not args.no_overlap      # measured: pays off from 4 ranks (profiles/r1_scaling.md)
 
     def step_resident():
         if pipelined:     # exchange + merge of batch i overlap the scan of batch i+1
@@ -400,8 +400,9 @@ def run_b200(args):
             "queries_per_batch": M, "cache_entries": args.entries, "dim": args.dim,
             "parallelism": (f"row-sharded x{world}, all-gather+merge of batch i overlapped with scan of "
                             f"batch i+1 ({args.reserve_sms} SMs reserved)" if pipelined else
-                            f"row-sharded x{world}, candidates exchanged by stores into peer memory" if world > 1
-                            and args.exchange == "p2p" else f"row-sharded x{world}" if world > 1 else "single GPU"),
+                            f"row-sharded x{world}" if world > 1 else "single GPU") +
+                           (", candidates exchanged by stores into peer memory (CUDA IPC)" if world > 1
+                            and args.exchange == "p2p" else ", NCCL all-gather" if world > 1 else ""),
             "l2": "inputs larger than L2 (768 MB bf16 rows + 1.5 GB fp32 rows vs 126 MB L2)",
             "parity_gate": {"planted_checked": int(sure.sum()), "missed": n_bad, "false_hits": n_false,
                             "max_abs_sim_err_vs_planted_cos": sim_err},

@@ -773,16 +773,14 @@ int qre_xchg_connect(qre_cache_t* h, int peer, const uint8_t* handle) {
   return QRE_OK;
 }
 
-int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
-                         const qre_params_t* params, int32_t* overflow_count, void* stream) {
-  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+int qre_publish_dev(qre_cache_t* h, int m, const qre_candidate_t* cand, void* stream) {
+  if (h == nullptr || cand == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
   if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "call qre_xchg_init / qre_xchg_connect first");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
   for (int pr = 0; pr < h->xchg_world; ++pr)
     if (h->xchg_peer[pr] == nullptr) return fail(QRE_ERR_INVALID, "peer %d is not connected", pr);
   if (h->xchg_pub_epoch - h->xchg_merge_epoch >= 2)
     return fail(QRE_ERR_INVALID, "two batches already published and not merged (the exchange has two slots)");
-  int rc = qre_scan_dev(h, m, queries, q_ctx, params, h->xchg_rank, h->d_cand, overflow_count, stream);
-  if (rc != QRE_OK) return rc;
   DeviceGuard guard(h->s.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
   const uint32_t epoch = ++h->xchg_pub_epoch;
@@ -794,9 +792,18 @@ int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint
     dst[pr] = reinterpret_cast<qre_candidate_t*>(h->xchg_peer[pr]) + idx * xchg_list_records(h);
     flag[pr] = reinterpret_cast<uint32_t*>(h->xchg_peer[pr] + h->xchg_flags_off) + idx * 32;
   }
-  h->launches += launch_publish(m, h->xchg_world, h->d_cand, dst, flag, epoch, h->xchg_ticket, st);
+  h->launches += launch_publish(m, h->xchg_world, cand, dst, flag, epoch, h->xchg_ticket, st);
   QRE_CUDA(cudaGetLastError());
   return QRE_OK;
+}
+
+int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
+                         const qre_params_t* params, int32_t* overflow_count, void* stream) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "call qre_xchg_init / qre_xchg_connect first");
+  int rc = qre_scan_dev(h, m, queries, q_ctx, params, h->xchg_rank, h->d_cand, overflow_count, stream);
+  if (rc != QRE_OK) return rc;
+  return qre_publish_dev(h, m, h->d_cand, stream);
 }
 
 int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,

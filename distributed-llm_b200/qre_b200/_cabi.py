@@ -32,7 +32,7 @@ EXPORTS = (
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
     "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
-    "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev",
+    "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
 )
 
 
@@ -334,6 +334,9 @@ class Shard:
 
     def xchg_connect(self, peer: int, handle: bytes) -> None:
         _check(self.lib, self.lib.qre_xchg_connect(self.h, C.c_int(peer), C.c_char_p(handle)))
+
+    def publish_dev(self, m, cand_ptr, stream=0):
+        _check(self.lib, self.lib.qre_publish_dev(self.h, C.c_int(m), C.c_void_p(cand_ptr), C.c_void_p(stream)))
 
     def scan_publish_dev(self, m, q_ptr, q_ctx_ptr, cfg: RouteConfig, now_us, ovf_ptr=0, stream=0):
         p = cfg.to_c(now_us, False)

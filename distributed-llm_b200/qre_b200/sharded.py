@@ -121,16 +121,20 @@ class ShardedLookup:
         scanned.record(main)
         self.side.wait_event(scanned)
         with torch.cuda.stream(self.side):
-            if self.world > 1:
-                import torch.distributed as dist
-                dist.all_gather_into_tensor(self.cand_all2[b][: self.world * nbytes], self.cand2[b][:nbytes],
-                                            group=self.group)
             out = self.out2[b]
-            self.shard.merge_route_dev(
-                m, self.world, self.cand_all2[b].data_ptr(), cfg, now_us, {f: t.data_ptr() for f, t in out.items()},
-                tok_ptr=0 if tok is None else tok.data_ptr(),
-                heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
-                heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=self.side.cuda_stream)
+            ptrs = {f: t.data_ptr() for f, t in out.items()}
+            extra = dict(tok_ptr=0 if tok is None else tok.data_ptr(),
+                         heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
+                         heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=self.side.cuda_stream)
+            if self.exchange == "p2p":
+                self.shard.publish_dev(m, self.cand2[b].data_ptr(), self.side.cuda_stream)
+                self.shard.merge_route_xchg_dev(m, cfg, now_us, ptrs, **extra)
+            else:
+                if self.world > 1:
+                    import torch.distributed as dist
+                    dist.all_gather_into_tensor(self.cand_all2[b][: self.world * nbytes], self.cand2[b][:nbytes],
+                                                group=self.group)
+                self.shard.merge_route_dev(m, self.world, self.cand_all2[b].data_ptr(), cfg, now_us, ptrs, **extra)
             ev = torch.cuda.Event()
             ev.record(self.side)
         self.done[b] = ev

@@ -237,6 +237,9 @@ QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64
 #define QRE_IPC_HANDLE_BYTES 64
 QRE_API int qre_xchg_init(qre_cache_t* h, int world, int rank, uint8_t* handle_out);
 QRE_API int qre_xchg_connect(qre_cache_t* h, int peer, const uint8_t* handle);
+/* qre_publish_dev alone publishes lists a previous qre_scan_dev left in `cand` (DEVICE pointer), so
+ * the exchange can sit on another stream than the scan; qre_scan_publish_dev = scan + publish. */
+QRE_API int qre_publish_dev(qre_cache_t* h, int m, const qre_candidate_t* cand, void* stream);
 QRE_API int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_ctx,
                                  const qre_params_t* params, int32_t* overflow_count, void* stream);
 QRE_API int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,

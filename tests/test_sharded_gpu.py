@@ -49,7 +49,7 @@ def _worker(rank, world, port, ret):
           and float(np.mean(out["dev"].cpu().numpy() == r["dev"])) > 0.995)
     # pipelined: three different batches in flight back to back must each equal the serial result
     perms = [np.random.Generator(np.random.PCG64(s_)).permutation(300) for s_ in range(3)]
-    serial, piped = [], []
+    serial = []
     for pm in perms:
         o = look.step(t(w.queries[pm]), t(w.q_ctx[pm].view(np.int64)), w.now_us, t(w.tok[pm]), t(w.heur_dev[pm]),
                       t(w.heur_conf[pm]))
@@ -59,9 +59,6 @@ def _worker(rank, world, port, ret):
            for pm in perms]
     torch.cuda.synchronize()
     handles = [look.step_pipelined(a, b, w.now_us, c, d, e) for a, b, c, d, e in ins]
-    for i, (o, ev) in enumerate(handles):
-        if i < 2:          # buffers of batch i are reused by batch i+2: read before that (here: only 3)
-            pass
     # with 3 batches, batch 0's buffers were reused by batch 2; check batches 1 and 2
     for i in (1, 2):
         o, ev = handles[i]
@@ -83,6 +80,14 @@ def _worker(rank, world, port, ret):
     torch.cuda.synchronize()
     for k in ("hit_slot", "hit_sim", "dev"):
         ok = ok and np.array_equal(o[k].cpu().numpy(), serial[11 % 3][k])
+    # pipelined + peer exchange: publish and merge on the side stream under the next scan
+    handles = [look_p.step_pipelined(a, b, w.now_us, c, d, e) for a, b, c, d, e in ins]
+    for i in (1, 2):
+        o, ev = handles[i]
+        ev.synchronize()
+        for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf"):
+            ok = ok and np.array_equal(o[k].cpu().numpy(), serial[i][k])
+    torch.cuda.synchronize()
     ret[rank] = (bool(ok), int(hit.sum()))
     dist.barrier()
     dist.destroy_process_group()
