@@ -52,7 +52,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: serialise scan / all-gather / merge")
     ap.add_argument("--reserve-sms", type=int, default=4)
-    ap.add_argument("--exchange", default="nccl", choices=["nccl", "p2p"],
+    ap.add_argument("--exchange", default="auto", choices=["auto", "nccl", "p2p"],
                     help="N>1: NCCL all-gather of the candidates, or stores into peer memory (CUDA IPC)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     return ap.parse_args()
@@ -230,7 +230,10 @@ def run_b200(args):
     wq = make_queries(args)
     sh, kept = build_shard(args, wq, rank, world, torch)
     cfg = _cabi.RouteConfig(ttl_us=TTL_US, n_devices=args.devices)
+    if args.exchange == "auto":        # measured (profiles/r1_scaling.md): peer stores win from 4 ranks
+        args.exchange = "p2p" if world >= 4 else "nccl"
     look = ShardedLookup(sh, cfg, rank, world, reserve_sms=args.reserve_sms, exchange=args.exchange)
+    args.exchange = look.exchange
     M = args.queries
     q_ctx_np = wq["ctx_tab"][wq["q_ci"]]
     # pinned host copies (e2e) and resident device copies (value)

@@ -78,13 +78,26 @@ class ShardedLookup:
         self.exchange = exchange if world > 1 else "nccl"
         if self.exchange == "p2p":
             import torch.distributed as dist
-            mine = shard.xchg_init(world, rank)
+            ok, mine = 1, b""
+            try:
+                mine = shard.xchg_init(world, rank)
+            except _cabi.QreError:
+                ok = 0
             handles = [None] * world
-            dist.all_gather_object(handles, mine, group=group)
-            for peer, hnd in enumerate(handles):
-                if peer != rank:
-                    shard.xchg_connect(peer, hnd)
-            dist.barrier(group=group)
+            dist.all_gather_object(handles, (ok, mine), group=group)
+            if all(o for o, _ in handles):
+                try:
+                    for peer, (_, hnd) in enumerate(handles):
+                        if peer != rank:
+                            shard.xchg_connect(peer, hnd)
+                except _cabi.QreError:
+                    ok = 0
+            else:
+                ok = 0
+            flag = torch.tensor([ok], device=self.dev, dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)     # every rank takes the same path
+            if int(flag.item()) == 0:
+                self.exchange = "nccl"
 
     def _new_out(self, m: int):
         torch = self.torch
