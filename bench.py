@@ -274,7 +274,10 @@ def run_b200(args):
     side = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(side)
     sampler = ClockSampler(local)
-    sampler.start()                     # nvidia-smi needs ~100 ms to produce its first line
+    sampler.start()                     # nvidia-smi needs a moment to produce its first line
+    t_wait = time.perf_counter()
+    while rank == 0 and sampler.proc is not None and not sampler.rows and time.perf_counter() - t_wait < 5.0:
+        time.sleep(0.02)
     for _ in range(args.warmup):
         step_resident()
     barrier()
