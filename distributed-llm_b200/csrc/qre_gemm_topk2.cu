@@ -24,6 +24,7 @@
 
 #include "qre_common.cuh"
 #include "qre_ptx.cuh"
+#include "qre_scan_epilogue.cuh"
 
 namespace qre {
 
@@ -39,31 +40,6 @@ constexpr int kSmemB2 = kStages2 * kBHalfBytes;       // 128 KB
 constexpr int kSmemTotal2 = kSmemA2 + kSmemB2 + 512 + 1024;
 constexpr uint32_t kTmemCols2 = 512;
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;           // shared::cluster address of the even CTA of a pair
-
-struct TopK2 {
-  float v[kTopK];
-  uint32_t r[kTopK];
-};
-
-__device__ __noinline__ float consider2(TopK2* tk, float v, long long row, long long n_rows,
-                                        const RowMeta* __restrict__ meta, uint64_t myctx, long long now_us,
-                                        long long ttl_us) {
-  if (row >= n_rows) return tk->v[kTopK - 1];
-  const int4 raw = __ldg(reinterpret_cast<const int4*>(meta + row));
-  const uint64_t ctx = (static_cast<uint64_t>(static_cast<uint32_t>(raw.y)) << 32) | static_cast<uint32_t>(raw.x);
-  const long long ts = static_cast<long long>((static_cast<uint64_t>(static_cast<uint32_t>(raw.w)) << 32) |
-                                              static_cast<uint32_t>(raw.z));
-  if (ctx != myctx || (now_us - ts) > ttl_us) return tk->v[kTopK - 1];
-  int i = kTopK - 1;
-  while (i > 0 && v > tk->v[i - 1]) {
-    tk->v[i] = tk->v[i - 1];
-    tk->r[i] = tk->r[i - 1];
-    --i;
-  }
-  tk->v[i] = v;
-  tk->r[i] = static_cast<uint32_t>(row);
-  return tk->v[kTopK - 1];
-}
 
 // ---- cluster / cta_group::2 PTX ----
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -243,7 +219,7 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   } else {
     // ================= epilogue (both CTAs): fused per-query top-k =================
     uint32_t tile_iter = 0;
-    TopK2 tk;
+    TopK tk;
     for (int u = cluster_id; u < U; u += n_clusters) {
       const int s = u / npairs, pr = u - s * npairs;
       const int mb = 2 * pr + static_cast<int>(rank);
@@ -251,57 +227,19 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       const int q = mb * kBM + warp * 32 + lane;
       const bool active = q < a.m;
       const uint64_t myctx = active ? a.q_ctx[q] : 0ull;
-#pragma unroll
-      for (int i = 0; i < kTopK; ++i) { tk.v[i] = a.floor_v; tk.r[i] = kNoRow; }
+      topk_reset(tk, a.floor_v);
       float kth = active ? a.floor_v : __int_as_float(0x7f800000);
       for (int t = t0; t < t1; ++t) {
         const uint32_t acc = tile_iter & 1;
         mbar_wait(&t_full[acc], (tile_iter >> 1) & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + acc * kBN;
-        const long long row_base = static_cast<long long>(t) * kBN;
-#pragma unroll 1
-        for (int c = 0; c < kBN / 64; ++c) {
-          float v[64];
-          tmem_ld_32x32(taddr + c * 64, v);
-          tmem_ld_32x32(taddr + c * 64 + 32, v + 32);
-          tmem_ld_wait();
-          if (kDump) {
-            if (active && a.dump != nullptr) {
-#pragma unroll
-              for (int i = 0; i < 64; ++i) {
-                const long long row = row_base + c * 64 + i;
-                if (row >= a.dump_row0 && row < a.dump_row0 + a.dump_ld && row < a.n_rows)
-                  a.dump[static_cast<long long>(q) * a.dump_ld + (row - a.dump_row0)] = v[i];
-              }
-            }
-          }
-          float m0 = fmaxf(v[0], v[1]), m1 = fmaxf(v[2], v[3]), m2 = fmaxf(v[4], v[5]), m3 = fmaxf(v[6], v[7]);
-#pragma unroll
-          for (int i = 8; i < 64; i += 8) {
-            m0 = fmaxf(m0, fmaxf(v[i], v[i + 1]));
-            m1 = fmaxf(m1, fmaxf(v[i + 2], v[i + 3]));
-            m2 = fmaxf(m2, fmaxf(v[i + 4], v[i + 5]));
-            m3 = fmaxf(m3, fmaxf(v[i + 6], v[i + 7]));
-          }
-          const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-          if (mx > kth) {
-#pragma unroll
-            for (int i = 0; i < 64; ++i) {
-              if (v[i] > kth)
-                kth = consider2(&tk, v[i], row_base + c * 64 + i, a.n_rows, a.meta, myctx, a.now_us, a.ttl_us);
-            }
-          }
-        }
+        kth = scan_tile<kDump>(taddr, static_cast<long long>(t) * kBN, q, active, kth, tk, myctx, a);
         tc_fence_before();
         mbar_arrive_remote(&t_empty[acc], 0);      // the leader's MMA thread owns the accumulator hand-off
         ++tile_iter;
       }
-      if (active) {
-        PartialEntry* out = a.partial + (static_cast<long long>(q) * a.splits + s) * kTopK;
-#pragma unroll
-        for (int i = 0; i < kTopK; ++i) out[i] = PartialEntry{tk.v[i], tk.r[i]};
-      }
+      if (active) topk_store(tk, a.partial + (static_cast<long long>(q) * a.splits + s) * kTopK);
     }
   }
 

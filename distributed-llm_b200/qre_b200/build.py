@@ -11,7 +11,7 @@ LIB_DIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIB_DIR, "libqre_b200.so")
 SOURCES = ["qre_api.cu", "qre_kernels.cu", "qre_gemm_topk.cu", "qre_gemm_topk2.cu", "qre_noalloc.cu",
            "qre_host_features.cu"]
-HEADERS = ["qre_common.cuh", "qre_ptx.cuh", os.path.join("..", "..", "include", "qre_b200.h")]
+HEADERS = ["qre_common.cuh", "qre_ptx.cuh", "qre_scan_epilogue.cuh", os.path.join("..", "..", "include", "qre_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
