@@ -25,6 +25,7 @@ import heapq
 import json
 import logging
 import re
+import contextlib
 import threading
 from collections import OrderedDict
 from dataclasses import dataclass, field
@@ -183,6 +184,62 @@ class QueryCache:
         self._attempts = 0
         self._evictions = 0
         self._hybrid_fallbacks = 0
+        self._defer: Optional[dict] = None           # batched device sync in progress (see _deferred)
+
+    # ------------------------------------------------------------------ batched device sync
+    @contextlib.contextmanager
+    def _deferred(self):
+        """Inside this block the device mirror of host-side changes is queued and written at
+        the end with a handful of batched C-ABI calls (one tombstone, one append, one or two
+        updates) instead of one synchronous call per entry.  Only the batch entry points use it:
+        they look everything up against a snapshot first, so nothing reads the device rows before
+        the flush."""
+        with self._lock:
+            if self._defer is not None:              # nested: the outer block flushes
+                yield
+                return
+            self._defer = {"dirty": OrderedDict(), "tomb": [], "lru": {}}
+            try:
+                yield
+            finally:
+                q, self._defer = self._defer, None
+                self._flush(q)
+
+    def _flush(self, q: dict) -> None:
+        eng = self._engine
+        if q["tomb"]:
+            eng.tombstone(q["tomb"])
+        new = [(e, rc) for e, rc in q["dirty"].values() if e._slot is None and e.embedding is not None]
+        old = [(e, rc) for e, rc in q["dirty"].values() if e._slot is not None and e.embedding is not None]
+        if new:
+            pred = [e.predict_device() for e, _ in new]
+            slots = eng.append_many(np.stack([e.embedding for e, _ in new]),
+                                    [self._ctx_id(e.context_key) for e, _ in new],
+                                    [_to_us(e.timestamp) for e, _ in new], [e._seq for e, _ in new],
+                                    [device_index(d) for d, _ in pred], [c for _, c in pred])
+            for (e, _), sl in zip(new, slots):
+                e._slot = int(sl)
+                self._slot_key[e._slot] = e.query_hash
+        for changed in (True, False):
+            grp = [e for e, rc in old if rc == changed]
+            if not grp:
+                continue
+            pred = [e.predict_device() for e in grp]
+            eng.update_many([e._slot for e in grp], rows=np.stack([e.embedding for e in grp]) if changed else None,
+                            ts_us=[_to_us(e.timestamp) for e in grp], lru=[e._seq for e in grp],
+                            pdev=[device_index(d) for d, _ in pred], pconf=[c for _, c in pred])
+        touched = {e._slot for e, _ in q["dirty"].values() if e._slot is not None}
+        lru = {s_: v for s_, v in q["lru"].items() if s_ not in touched and s_ in self._slot_key}
+        if lru:
+            eng.update_many(list(lru), lru=list(lru.values()))
+
+    def _bump_lru(self, entry: CacheEntry) -> None:
+        if entry._slot is None:
+            return
+        if self._defer is not None:
+            self._defer["lru"][entry._slot] = entry._seq
+        else:
+            self._engine.update(entry._slot, lru=entry._seq)
 
     # ------------------------------------------------------------------ helpers
     @staticmethod
@@ -221,9 +278,15 @@ class QueryCache:
         entry = self._store.pop(key, None)
         if entry is None:
             return
+        if self._defer is not None:
+            self._defer["dirty"].pop(key, None)
         if entry._slot is not None:
             self._slot_key.pop(entry._slot, None)
-            self._engine.tombstone([entry._slot])
+            if self._defer is not None:
+                self._defer["tomb"].append(entry._slot)
+                self._defer["lru"].pop(entry._slot, None)
+            else:
+                self._engine.tombstone([entry._slot])
             entry._slot = None
         entry.embedding = None
 
@@ -272,6 +335,10 @@ class QueryCache:
     def _sync_row(self, entry: CacheEntry, row_changed: bool) -> None:
         """Mirror an entry's scan-relevant state into its device row."""
         if entry.embedding is None:
+            return
+        if self._defer is not None:
+            prev = self._defer["dirty"].get(entry.query_hash)
+            self._defer["dirty"][entry.query_hash] = (entry, row_changed or (prev is not None and prev[1]))
             return
         pdev, pconf = entry.predict_device()
         ts_us = _to_us(entry.timestamp)
@@ -326,8 +393,7 @@ class QueryCache:
                 entry, key = found, found.query_hash
             entry.hit_count += 1
             self._touch(key, entry)
-            if entry._slot is not None:
-                self._engine.update(entry._slot, lru=entry._seq)
+            self._bump_lru(entry)
             self._hits += 1
             pdev, pconf = entry.predict_device()
             fallback = pconf < self.prediction_confidence_threshold
@@ -363,30 +429,34 @@ class QueryCache:
                 outs.append(self._engine.scan(q_embs[sl], ctx[sl], _to_us(now), cfg, ri))
             out = {k: np.concatenate([o[k] for o in outs]) for k in outs[0]} if outs else {}
             results: List[Optional[CacheLookupResult]] = []
-            for i, (q, c) in enumerate(zip(queries, context_keys)):
-                self._attempts += 1
-                key = self._make_hash(q, c)
-                entry = self._store.get(key)
-                if entry is None or entry.context_key != c or not self._is_valid(entry, now):
-                    entry = None
-                    slot = int(out["hit_slot"][i]) if self.use_semantic else -1
-                    if slot >= 0:
-                        entry = self._store.get(self._slot_key.get(slot, ""))
-                        if entry is not None and not self._is_valid(entry, now):
-                            entry = None
-                if entry is None:
-                    results.append(None)
-                    continue
-                entry.hit_count += 1
-                self._touch(entry.query_hash, entry)
-                if entry._slot is not None:
-                    self._engine.update(entry._slot, lru=entry._seq)
-                self._hits += 1
-                pdev, pconf = entry.predict_device()
-                fb = pconf < self.prediction_confidence_threshold
-                self._hybrid_fallbacks += int(fb)
-                results.append(CacheLookupResult(entry, pdev, pconf, fb))
+            with self._deferred():
+                self._apply_batch_hits(queries, context_keys, out, now, results)
             return results, out
+
+    def _apply_batch_hits(self, queries, context_keys, out, now, results) -> None:
+        """Host bookkeeping of a batch's hits, in order (exact-hash match first, then the device
+        scan's row), as `lookup` does for one query."""
+        for i, (q, c) in enumerate(zip(queries, context_keys)):
+            self._attempts += 1
+            entry = self._store.get(self._make_hash(q, c))
+            if entry is None or entry.context_key != c or not self._is_valid(entry, now):
+                entry = None
+                slot = int(out["hit_slot"][i]) if self.use_semantic else -1
+                if slot >= 0:
+                    entry = self._store.get(self._slot_key.get(slot, ""))
+                    if entry is not None and not self._is_valid(entry, now):
+                        entry = None
+            if entry is None:
+                results.append(None)
+                continue
+            entry.hit_count += 1
+            self._touch(entry.query_hash, entry)
+            self._bump_lru(entry)
+            self._hits += 1
+            pdev, pconf = entry.predict_device()
+            fb = pconf < self.prediction_confidence_threshold
+            self._hybrid_fallbacks += int(fb)
+            results.append(CacheLookupResult(entry, pdev, pconf, fb))
 
     def insert(self, query: str, context_key: str, device: str, confidence: float = 1.0,
                method: str = "unknown", q_emb: Optional[np.ndarray] = None,

@@ -101,6 +101,14 @@ class Engine:
                           pred_dev=one(pdev, np.uint8), pred_conf=one(pconf, np.float64))
 
     @_locked
+    def update_many(self, slots, rows=None, ts_us=None, lru=None, pdev=None, pconf=None) -> None:
+        arr = lambda v, dt: None if v is None else np.asarray(v, dt)   # noqa: E731
+        self.shard.update(np.asarray(slots, np.int64),
+                          rows=None if rows is None else np.ascontiguousarray(rows, np.float32),
+                          ts_us=arr(ts_us, np.int64), lru_seq=arr(lru, np.uint64), pred_dev=arr(pdev, np.uint8),
+                          pred_conf=arr(pconf, np.float64))
+
+    @_locked
     def tombstone(self, slots) -> None:
         slots = np.asarray(list(slots), np.int64)
         if slots.size and self.shard is not None:

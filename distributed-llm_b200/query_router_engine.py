@@ -589,6 +589,11 @@ class QueryRouter:
                         heur_dev=np.array([h[0] for _, h in feats], np.uint8),
                         heur_conf=np.array([h[1] for _, h in feats], np.float64))
         results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg())
+        with self._cache._deferred():        # all inserts of the batch reach the device in a few calls
+            return self._finish_batch(queries, contexts, ctxks, q_embs, feats, results, out, hybrid)
+
+    def _finish_batch(self, queries, contexts, ctxks, q_embs, feats, results, out, hybrid) -> List[RoutingDecision]:
+        r = self.router
         decisions: List[RoutingDecision] = []
         threshold = int(self.config.get("heuristic_context_chars", 800))
         for i, (q, c, k) in enumerate(zip(queries, contexts, ctxks)):

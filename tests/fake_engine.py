@@ -71,6 +71,15 @@ class OracleEngine:
         if pdev is not None: self.pdev[slot] = pdev
         if pconf is not None: self.pconf[slot] = pconf
 
+    def append_many(self, rows, ctx, ts_us, lru, pdev, pconf):
+        return np.array([self.append(*a) for a in zip(rows, ctx, ts_us, lru, pdev, pconf)], np.int64)
+
+    def update_many(self, slots, rows=None, ts_us=None, lru=None, pdev=None, pconf=None):
+        for i, s_ in enumerate(slots):
+            self.update(int(s_), None if rows is None else rows[i], None if ts_us is None else ts_us[i],
+                        None if lru is None else lru[i], None if pdev is None else pdev[i],
+                        None if pconf is None else pconf[i])
+
     def tombstone(self, slots):
         for s in slots:
             self.ctx[s] = O.CTX_TOMBSTONE
