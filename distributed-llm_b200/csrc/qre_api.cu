@@ -244,7 +244,8 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
   if (out == nullptr) return fail(QRE_ERR_INVALID, "out is NULL");
   *out = nullptr;
   if (dim < 8 || dim % 8 != 0) return fail(QRE_ERR_INVALID, "dim must be a positive multiple of 8 (got %d)", dim);
-  if (capacity < 1 || capacity > 0xFFFFFFF0ll) return fail(QRE_ERR_INVALID, "capacity out of range");
+  // row numbers travel as int32 TMA coordinates and u32 candidate slots
+  if (capacity < 1 || capacity > 2147483000ll) return fail(QRE_ERR_INVALID, "capacity out of range [1, 2^31)");
   if (max_batch < 1 || max_batch > (1 << 20)) return fail(QRE_ERR_INVALID, "max_batch out of range");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
