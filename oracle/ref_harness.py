@@ -69,3 +69,39 @@ def load_reference(clock: FakeClock | None = None):
     for name in ("cache", "query_router_engine"):
         sys.modules.pop(name, None)
     return cache, qre, st
+
+
+def load_reference_router(dropin_dir: str | None, clock: FakeClock | None = None):
+    """Import the reference's ORCHESTRATOR (`src/router.py`, unmodified) together with its
+    device clients, either on top of the reference's own `cache` / `query_router_engine`
+    (dropin_dir=None) or on top of the drop-in modules found in `dropin_dir` — the claim of
+    INTEGRATION.md §1.  Returns (router_module, cache_module, qre_module, stub_st_module)."""
+    if not available():
+        raise RuntimeError("reference not present at " + REFERENCE_SRC)
+    sys.dont_write_bytecode = True
+    names = ("router", "cache", "query_router_engine", "token_counter", "models", "models.nano", "models.orin",
+             "models.server_manager", "sentence_transformers", "litellm", "pexpect")
+    for name in names:
+        sys.modules.pop(name, None)
+    saved = list(sys.path)
+    sys.path.insert(0, REFERENCE_SRC)
+    if dropin_dir is not None:
+        sys.path.insert(0, dropin_dir)          # shadows cache.py / query_router_engine.py only
+    sys.path.insert(0, STUBS)
+    try:
+        st = importlib.import_module("sentence_transformers")
+        router = importlib.import_module("router")
+        cache = sys.modules["cache"]
+        qre = sys.modules["query_router_engine"]
+        assert router.__file__.startswith(REFERENCE_SRC), router.__file__
+        want = dropin_dir if dropin_dir is not None else REFERENCE_SRC
+        assert cache.__file__.startswith(want) and qre.__file__.startswith(want), (cache.__file__, qre.__file__)
+    finally:
+        sys.path[:] = saved
+    if clock is not None:
+        dt = clock.make_datetime_class()
+        cache.datetime = dt
+        qre.datetime = dt
+    for name in names:
+        sys.modules.pop(name, None)
+    return router, cache, qre, st
