@@ -37,7 +37,7 @@ except ImportError as _e:   # pragma: no cover
     raise ImportError("query_router_engine needs the B200 cache.py next to it on sys.path "
                       f"(distributed-llm_b200/): {_e}") from _e
 
-from qre_b200 import _cabi
+from qre_b200 import _cabi, heuristic_tables
 from qre_b200.engine import Engine
 
 logger = logging.getLogger(__name__)
@@ -210,50 +210,9 @@ class HeuristicRouter(BaseRouter):
     reference's (they ARE the behaviour); the fixed confidences are 0.92 / 0.80 / 0.88 / 0.75
     for the heavy device and 0.90 / 0.75 for the light one."""
 
-    COMPLEX = {
-        "code_build_debug": [
-            r"\b(write|implement|code|program|script|build|refactor|debug|fix)\b",
-            r"\b(traceback|exception|error|segfault|timeout|hanging)\b",
-            r"\b(api|flask|fastapi|docker|kubernetes|ssh|tunnel|nginx)\b",
-            r"\b(system design|architecture|distributed|scalability|load balanc)\b"],
-        "math_cs_theory": [
-            r"\b(prove|lemma|theorem|corollary|derivative|integral|gradient)\b",
-            r"\b(time complexity|space complexity|big[- ]o)\b",
-            r"\b(dynamic programming|dp|graph|dijkstra|bfs|dfs)\b",
-            r"(?:\b|^)a\*(?:\s|$|\W)"],
-        "reasoning_comparison": [
-            r"\b(compare|contrast|difference between|pros and cons|vs\.?|versus)\b",
-            r"\b(evaluate|assess|critique|analyze)\b"],
-        "long_form_generation": [
-            r"\b(essay|report|proposal|research paper|literature review|methodology)\b",
-            r"\b(comprehensive|in-depth|step[- ]by[- ]step|detailed)\b",
-            r"\b(summarize|synthesis)\b.*\b(everything|all|so far|entire)\b",
-            r"\b(transcript|debate|dialogue|format as json|markdown table)\b"],
-        "data_engineering": [
-            r"\b(etl|pipeline|spark|hadoop|presto|sql|csv|excel|dataframe|dataset)\b",
-            r"\b(deduplicate|normalize|clean|transform|parse|extract)\b"],
-        "medical_analysis": [
-            r"\b(symptom|diagnosis|treatment|therapy|prognosis|chronic|severe)\b",
-            r"\b(pain|migraine|dizziness|fatigue|nausea|inflammation|anxiety|depression)\b",
-            r"\b(dietary|meal|training|exercise|recovery)\b.*\b(plan|schedule|regimen)\b",
-            r"\b(mental health|psycholog|counseling|therapist|physician|hospital)\b"],
-        "context_heavy": [
-            r"\b(using (all|the) (context|history|above)|based on (the|our) (conversation|context))\b",
-            r"\b(continue|expand|build on|follow up)\b.*\b(previous|earlier|above)\b"],
-    }
-    SIMPLE = {
-        "greeting": [r"\b(hi|hello|hey|yo|sup)\b", r"\bgood (morning|afternoon|evening)\b",
-                     r"\b(thanks|thank you)\b"],
-        "general_knowledge": [
-            r"\b(what is|who is|where is|when is|when did|how many|capital of)\b",
-            r"\b(tell me a joke|fun fact|random fact)\b", r"\b(how to|how do i|can you tell me)\b"],
-        "wellness_tips": [r"\b(benefits? of|tips? for|advice on)\b", r"\b(daily intake|how often|how much)\b",
-                          r"\b(healthy|good)\b.*\b(habit|routine|lifestyle)\b"],
-        "short_definition": [r"\b(define|meaning of|definition of)\b", r"\bwhat does\b.*\bmean\b"],
-        "tiny_math": [r"^\s*\d+\s*[\+\-\*/]\s*\d+\s*\??\s*$", r"^\s*what is\s+\d+\s*[\+\-\*/]\s*\d+\s*\??\s*$"],
-    }
-    CODE_MARKERS = ("```", "def ", "class ", "import ", "Traceback", "Exception", "ModuleNotFoundError",
-                    "SELECT ", "WITH ", "FROM ", "JOIN ", ";", "{", "}", "->", "::", "==", "!=")
+    COMPLEX = {name: list(pats) for name, pats in heuristic_tables.COMPLEX_CATEGORIES}
+    SIMPLE = {name: list(pats) for name, pats in heuristic_tables.SIMPLE_CATEGORIES}
+    CODE_MARKERS = heuristic_tables.CODE_MARKERS
 
     def __init__(self, config: Dict[str, Any]):
         super().__init__(config)
@@ -673,30 +632,17 @@ class QueryRouter:
 
 
 # Shared configs (reference qre:704-731): same keys and values.
-BENCHMARK_CFG = {
-    "token_threshold": 1000,
-    "model": "meta-llama/Llama-2-7b-hf",
-    "embedding_model": "all-MiniLM-L6-v2",
-    "semantic_label_path": "src/tests/semantic_labels.json",
-    "semantic_margin_threshold": 0.03,
-    "semantic_min_similarity": 0.05,
-    "heuristic_long_chars": 800,
-    "heuristic_multi_qmarks": 2,
-    "heuristic_code_markers_needed": 2,
-    "heuristic_context_chars": 3200,
-    "weights": {"token": 0.25, "semantic": 0.45, "heuristic": 0.30},
-    "cache_enabled": False,
-    "perf_window": 30,
-    "perf_fail_penalty": 3000.0,
-}
+BENCHMARK_CFG = dict(
+    token_threshold=1000, model="meta-llama/Llama-2-7b-hf", embedding_model="all-MiniLM-L6-v2",
+    semantic_label_path="src/tests/semantic_labels.json", semantic_margin_threshold=0.03,
+    semantic_min_similarity=0.05, heuristic_long_chars=800, heuristic_multi_qmarks=2,
+    heuristic_code_markers_needed=2, heuristic_context_chars=3200,
+    weights=dict(token=0.25, semantic=0.45, heuristic=0.30), cache_enabled=False, perf_window=30,
+    perf_fail_penalty=3000.0,
+)
 
-PRODUCTION_CFG = {
-    **BENCHMARK_CFG,
-    "cache_enabled": True,
-    "cache_ttl_seconds": 3600,
-    "cache_max_size": 500,
-    "cache_similarity_threshold": 0.85,
-    "use_semantic_cache": True,
-    "prediction_confidence_threshold": 0.70,
-    "enable_response_cache": True,
-}
+PRODUCTION_CFG = dict(
+    BENCHMARK_CFG, cache_enabled=True, cache_ttl_seconds=3600, cache_max_size=500,
+    cache_similarity_threshold=0.85, use_semantic_cache=True, prediction_confidence_threshold=0.70,
+    enable_response_cache=True,
+)
