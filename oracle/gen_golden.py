@@ -378,9 +378,90 @@ def gen_router_replay():
     print("router_replay:", len(steps), "steps", Counter(s["method"] for s in steps))
 
 
+
+
+# ----------------------------------------------------------------------------------------
+def config1_inputs():
+    """Seeded inputs of BASELINE.json configs[0] (1k queries x 10k cache entries x 384-d fp32, hybrid
+    strategy + semantic cache).  Shared by the generator and the GPU test: only the reference's
+    OUTPUTS are committed, the inputs are regenerated from the seed (and checksummed)."""
+    w = synth.make_workload(10_000, 1_000, 384, n_centroids=2, seed=101, frac_planted=0.45, frac_near=0.03,
+                            frac_dup=0.01, n_zero_q=2, n_zero_rows=2, frac_expired=0.0, n_ctx=6)
+    rs = np.random.Generator(np.random.PCG64(102))
+    templates = ["note {i}", "what is item {i}", "implement step {i}", "item {i}? really? sure?",
+                 "item {i} " + "lorem ipsum dolor sit amet " * 8]
+    q_text = [templates[int(rs.integers(0, len(templates)))].format(i=m) for m in range(1000)]
+    ctx_len = np.where(rs.random(1000) < 0.25, rs.integers(3200, 9000, 1000),
+                       np.where(rs.random(1000) < 0.5, rs.integers(1, 600, 1000), 0))
+    row_dev = rs.integers(0, 2, 10_000)
+    row_conf = rs.uniform(0.3, 1.0, 10_000)
+    # a second routing record on 30 % of the rows so predictions are not all unanimous
+    second = rs.random(10_000) < 0.3
+    second_dev = rs.integers(0, 2, 10_000)
+    second_conf = rs.uniform(0.3, 1.0, 10_000)
+    checksum = float(np.float64(w.rows.astype(np.float64).sum() + w.queries.astype(np.float64).sum()))
+    return dict(w=w, q_text=q_text, ctx_len=ctx_len, row_dev=row_dev, row_conf=row_conf, second=second,
+                second_dev=second_dev, second_conf=second_conf, checksum=checksum)
+
+
+def run_config1(qre_mod, st_mod, clock, patch_centroids):
+    """Drive one implementation (reference or drop-in) through config 1; returns the decisions."""
+    I = config1_inputs()
+    w = I["w"]
+    names = ["nano", "orin"]
+    table = {f"entry {j}": w.rows[j] for j in range(10_000)}
+    table.update({I["q_text"][m]: w.queries[m] for m in range(1_000)})
+    st_mod.set_table(table, dim=384)
+    cfg = dict(qre_mod.PRODUCTION_CFG, cache_max_size=20_000, cache_ttl_seconds=10**6)
+    cfg.update(patch_centroids(cfg))
+    qr = qre_mod.QueryRouter(strategy="hybrid", config=cfg)
+    patch_centroids(cfg, qr)
+    ctx_key = {int(synth.ctx_id(i)): f"{int(synth.ctx_id(i)):016x}" for i in range(6)}
+    for j in range(10_000):
+        qr._cache.insert(f"entry {j}", ctx_key[int(w.row_ctx[j])], names[int(I["row_dev"][j])],
+                         confidence=float(I["row_conf"][j]), method="hybrid", q_emb=w.rows[j])
+        if I["second"][j]:
+            qr._cache.insert(f"entry {j}", ctx_key[int(w.row_ctx[j])], names[int(I["second_dev"][j])],
+                             confidence=float(I["second_conf"][j]), method="hybrid", q_emb=w.rows[j])
+    out = []
+    for m in range(1_000):
+        clock.advance(0.5)
+        n = int(I["ctx_len"][m])
+        d = qr.route_query(I["q_text"][m], context=("c" * n) if n else None, context_key=ctx_key[int(w.q_ctx[m])])
+        out.append(dict(device=d.device, confidence=d.confidence, method=d.method, cache_hit=d.cache_hit))
+    st = {k: v for k, v in qr.get_cache_stats().items() if k != "top_queries"}
+    return out, st, I["checksum"]
+
+
+def gen_config1():
+    clock = ref_harness.FakeClock()
+    _, qre, st = ref_harness.load_reference(clock)
+    rs = np.random.Generator(np.random.PCG64(103))
+    u = synth._unit(rs.standard_normal((2, 384)))
+    cents = np.stack([u[0] + 0.3 * u[1], u[1] + 0.3 * u[0]]).astype(np.float32)
+
+    def patch(cfg, qr=None):
+        if qr is not None:          # the reference builds centroids from the label file: overwrite them
+            sem = qr.router.routers["semantic"]
+            sem.nano_center, sem.orin_center = cents[0], cents[1]
+        return {"semantic_label_path": os.path.join(ref_harness.REFERENCE_SRC, "tests", "semantic_labels.json")}
+
+    import time
+    t0 = time.time()
+    out, stats, checksum = run_config1(qre, st, clock, patch)
+    np.save(os.path.join(GOLD, "config1_centroids.npy"), cents)
+    json.dump({"decisions": out, "stats": stats, "input_checksum": checksum,
+               "reference_seconds": round(time.time() - t0, 1)},
+              open(os.path.join(GOLD, "config1_replay.json"), "w"))
+    from collections import Counter
+    print("config1:", Counter((o["method"], o["cache_hit"]) for o in out), stats, f"{time.time() - t0:.0f}s")
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    gen_cache_scan()
-    gen_route_arith()
-    gen_cache_ops()
-    gen_router_replay()
+    only = sys.argv[1:] 
+    gens = dict(cache_scan=gen_cache_scan, route_arith=gen_route_arith, cache_ops=gen_cache_ops,
+                router_replay=gen_router_replay, config1=gen_config1)
+    for name, fn in gens.items():
+        if not only or name in only:
+            fn()

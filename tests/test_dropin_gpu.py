@@ -117,3 +117,35 @@ def test_binary_snapshot_roundtrip(tmp_path):
     assert np.array_equal(e.embedding, w.rows[int(e.query[1:])])
     b.insert("fresh", "ctx0", "nano", q_emb=w.rows[0] * 2)      # freed slots are reusable after load
     assert b.lookup("probe", "ctx0", w.rows[0]).entry.query == "fresh"
+
+
+def test_config1_sequential_replay_matches_reference_run():
+    """BASELINE.json configs[0] — the reference's own CPU-runnable case: hybrid strategy + semantic
+    cache, 10,000 pre-inserted entries, 1,000 queries routed ONE AT A TIME through
+    QueryRouter.route_query (so query i can hit what query i-1 inserted), 384-d fp32.  The
+    decisions recorded from the reference's own code (82 s on the build host) must be reproduced
+    by the drop-in classes on the GPU: device, method and cache_hit identical, confidence within
+    the score tolerance."""
+    import json
+    import time
+    from oracle import gen_golden as G
+    g = json.load(open(os.path.join(R.GOLDEN, "config1_replay.json")))
+    cents = np.load(os.path.join(R.GOLDEN, "config1_centroids.npy"))
+    clock = ref_harness.FakeClock()
+    _, qre_mod, st = R.load_modules(clock)
+
+    def patch(cfg, qr=None):
+        return {"centroids": cents, "centroid_owner": [0, 1]}
+
+    t0 = time.time()
+    out, stats, checksum = G.run_config1(qre_mod, st, clock, patch)
+    ours_s = time.time() - t0
+    assert checksum == g["input_checksum"], "seeded inputs differ from the ones the fixture was recorded on"
+    bad = [i for i, (a, b) in enumerate(zip(out, g["decisions"]))
+           if (a["device"], a["method"], a["cache_hit"]) != (b["device"], b["method"], b["cache_hit"])]
+    assert not bad, (bad[:5], [(out[i], g["decisions"][i]) for i in bad[:3]])
+    for a, b in zip(out, g["decisions"]):
+        assert abs(a["confidence"] - b["confidence"]) <= 4e-6 + 1e-5 * abs(b["confidence"]), (a, b)
+    for k, v in g["stats"].items():
+        assert stats[k] == v, (k, stats[k], v)
+    print(f"config 1: reference {g['reference_seconds']} s, drop-in on GPU {ours_s:.1f} s")
