@@ -410,7 +410,7 @@ def run_b200(args):
                         f"threshold 0.85, {args.devices} devices, {args.centroids} centroids "
                         "(BASELINE.json configs[1])",
             "queries_per_batch": M, "cache_entries": args.entries, "dim": args.dim,
-            "parallelism": (f"row-sharded x{world}, all-gather+merge of batch i overlapped with scan of "
+            "parallelism": (f"row-sharded x{world}, exchange+merge of batch i overlapped with scan of "
                             f"batch i+1 ({args.reserve_sms} SMs reserved)" if pipelined else
                             f"row-sharded x{world}" if world > 1 else "single GPU") +
                            (", candidates exchanged by stores into peer memory (CUDA IPC)" if world > 1
