@@ -149,3 +149,64 @@ def test_config1_sequential_replay_matches_reference_run():
     for k, v in g["stats"].items():
         assert stats[k] == v, (k, stats[k], v)
     print(f"config 1: reference {g['reference_seconds']} s, drop-in on GPU {ours_s:.1f} s")
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_random_ops_device_engine_vs_oracle_engine(seed, tmp_path):
+    """Differential test of the device store under realistic interleavings: the same random
+    sequence of inserts / refreshes / lookups / evictions / invalidations / snapshot round trips is
+    applied to two QueryCache objects, one on the real libqre_b200 engine and one on the
+    oracle-backed engine; every lookup result and the store order must agree at every step."""
+    from tests.fake_engine import OracleEngine
+    clock = ref_harness.FakeClock()
+    cache_mod, _, _ = R.load_modules(clock)
+    rs = np.random.Generator(np.random.PCG64(500 + seed))
+    d = 384
+    base = rs.standard_normal((40, d)).astype(np.float32)
+    kw = dict(max_size=int(rs.integers(8, 20)), ttl_seconds=int(rs.integers(30, 90)), similarity_threshold=0.85,
+              prediction_confidence_threshold=0.7)
+    gpu = cache_mod.QueryCache(**kw)
+    cpu = cache_mod.QueryCache(**kw, engine=OracleEngine(capacity=64, dim=d))
+    ctxs = ["A", "B"]
+    hits = 0
+    for step in range(350):
+        op = rs.choice(["insert", "lookup", "batch", "advance", "invalidate", "snapshot"],
+                       p=[.35, .35, .1, .12, .05, .03])
+        if op == "insert":
+            i = int(rs.integers(0, 40))
+            v = base[i] * np.float32(rs.uniform(0.5, 2)) + np.float32(0.03) * rs.standard_normal(d).astype(np.float32)
+            args = (f"Item {i}", str(rs.choice(ctxs)), str(rs.choice(["nano", "orin"])))
+            k = dict(confidence=float(rs.uniform(0.2, 1)), method="hybrid", q_emb=v)
+            gpu.insert(*args, **k); cpu.insert(*args, **k)
+        elif op == "lookup":
+            i = int(rs.integers(0, 40))
+            v = base[i] + np.float32(rs.choice([0.02, 0.2, 0.8])) * rs.standard_normal(d).astype(np.float32)
+            ctx = str(rs.choice(ctxs))
+            a, b = gpu.lookup(f"probe {step}", ctx, v), cpu.lookup(f"probe {step}", ctx, v)
+            assert (a is None) == (b is None), step
+            if a is not None:
+                hits += 1
+                assert (a.entry.query, a.predicted_device, a.predicted_confidence) == \
+                       (b.entry.query, b.predicted_device, b.predicted_confidence), step
+        elif op == "batch":
+            idx = rs.integers(0, 40, 6)
+            V = base[idx] + np.float32(0.05) * rs.standard_normal((6, d)).astype(np.float32)
+            qs, cs = [f"bq {step}-{j}" for j in range(6)], [str(rs.choice(ctxs)) for _ in range(6)]
+            a, b = gpu.lookup_batch(qs, cs, V), cpu.lookup_batch(qs, cs, V)
+            assert [None if x is None else x.entry.query for x in a] == [None if x is None else x.entry.query for x in b]
+        elif op == "advance":
+            clock.advance(float(rs.choice([1.0, 10.0, 40.0])))
+        elif op == "invalidate":
+            pat = rf"item {int(rs.integers(0, 4))}\d?$"
+            assert gpu.invalidate(query_pattern=pat) == cpu.invalidate(query_pattern=pat)
+        elif op == "snapshot" and gpu._engine.shard is not None:
+            p = str(tmp_path / f"s{step}.json")
+            gpu.save_snapshot(p)
+            fresh = cache_mod.QueryCache(**kw)
+            fresh.load_snapshot(p)
+            assert [e.query for e in fresh._store.values()] == [e.query for e in gpu._store.values()]
+            gpu = fresh                                 # carry on with the restored cache
+        assert [e.query for e in gpu._store.values()] == [e.query for e in cpu._store.values()], (step, op)
+        sa, sb = gpu.stats(), cpu.stats()
+        assert (sa["size"], sa["valid"]) == (sb["size"], sb["valid"]), (step, op)
+    assert hits > 20
