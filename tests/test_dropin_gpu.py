@@ -202,6 +202,7 @@ def test_random_ops_device_engine_vs_oracle_engine(seed, tmp_path):
         elif op == "snapshot" and gpu._engine.shard is not None:
             p = str(tmp_path / f"s{step}.json")
             gpu.save_snapshot(p)
+            cpu._evict_expired()                        # save_snapshot drops expired entries first, like save()
             fresh = cache_mod.QueryCache(**kw)
             fresh.load_snapshot(p)
             assert [e.query for e in fresh._store.values()] == [e.query for e in gpu._store.values()]
