@@ -179,9 +179,12 @@ def test_random_ops_device_engine_vs_oracle_engine(seed, tmp_path):
             k = dict(confidence=float(rs.uniform(0.2, 1)), method="hybrid", q_emb=v)
             gpu.insert(*args, **k); cpu.insert(*args, **k)
         elif op == "lookup":
-            i = int(rs.integers(0, 40))
+            i, ctx = int(rs.integers(0, 40)), str(rs.choice(ctxs))
+            live = list(cpu._store.values())
+            if live and rs.random() < 0.7:              # aim at something that is in the cache
+                e = live[int(rs.integers(0, len(live)))]
+                i, ctx = int(e.query.split()[1]), e.context_key
             v = base[i] + np.float32(rs.choice([0.02, 0.2, 0.8])) * rs.standard_normal(d).astype(np.float32)
-            ctx = str(rs.choice(ctxs))
             a, b = gpu.lookup(f"probe {step}", ctx, v), cpu.lookup(f"probe {step}", ctx, v)
             assert (a is None) == (b is None), step
             if a is not None:
