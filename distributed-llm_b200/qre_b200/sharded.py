@@ -100,12 +100,21 @@ class ShardedLookup:
                 self.exchange = "nccl"
 
     def _new_out(self, m: int):
+        """Result tensors as views of ONE device buffer (`out["_blob"]`), so a caller that wants
+        everything on the host needs a single device-to-host copy."""
         torch = self.torch
         K, D = max(1, self.shard.n_centroids), self.cfg.n_devices
-        out = {}
+        specs, off = [], 0
         for f, (dt, tail) in RESULT_SPECS.items():
             shape = (m,) + tuple({"K": K, "D": D}[t] for t in tail)
-            out[f] = torch.empty(shape, dtype=getattr(torch, dt), device=self.dev)
+            dtype = getattr(torch, dt)
+            nbytes = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+            specs.append((f, dtype, shape, off, nbytes))
+            off = (off + nbytes + 255) // 256 * 256
+        blob = torch.empty(off, dtype=torch.uint8, device=self.dev)
+        out = {f: blob[o:o + nb].view(dtype).view(shape) for f, dtype, shape, o, nb in specs}
+        out["_blob"] = blob
+        self.layout = specs          # (field, dtype, shape, offset, nbytes) within the blob
         return out
 
     def _alloc_out(self, m: int):
@@ -135,7 +144,7 @@ class ShardedLookup:
         self.side.wait_event(scanned)
         with torch.cuda.stream(self.side):
             out = self.out2[b]
-            ptrs = {f: t.data_ptr() for f, t in out.items()}
+            ptrs = {f: t.data_ptr() for f, t in out.items() if not f.startswith("_")}
             extra = dict(tok_ptr=0 if tok is None else tok.data_ptr(),
                          heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
                          heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=self.side.cuda_stream)
@@ -174,7 +183,7 @@ class ShardedLookup:
         if self.exchange == "p2p":
             self.shard.scan_publish_dev(m, q.data_ptr(), q_ctx.data_ptr(), self.cfg, now_us, self.ovf.data_ptr(), st)
             self.shard.merge_route_xchg_dev(
-                m, self.cfg, now_us, {f: t.data_ptr() for f, t in self.out.items()},
+                m, self.cfg, now_us, {f: t.data_ptr() for f, t in self.out.items() if not f.startswith("_")},
                 tok_ptr=0 if tok is None else tok.data_ptr(),
                 heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
                 heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=st)
@@ -187,7 +196,7 @@ class ShardedLookup:
             import torch.distributed as dist
             dist.all_gather_into_tensor(self.cand_all[: self.world * nbytes], self.cand[:nbytes],
                                         group=self.group)
-        ptrs = {f: t.data_ptr() for f, t in self.out.items()}
+        ptrs = {f: t.data_ptr() for f, t in self.out.items() if not f.startswith("_")}
         self.shard.merge_route_dev(
             m, self.world, self.cand_all.data_ptr(), self.cfg, now_us, ptrs,
             tok_ptr=0 if tok is None else tok.data_ptr(),
