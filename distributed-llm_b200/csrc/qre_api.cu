@@ -868,15 +868,22 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   S.d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m, true);
   S.d_hd = put(heur_dev, (size_t)m, true);
   S.d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m, true);
-  if (direct) {
-    QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, h->h2d));
-    QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice, h->h2d));
-  } else {
-    QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, h->h2d));
-  }
-  QRE_CUDA(cudaEventRecord(S.e_in, h->h2d));
+  // Small batches are latency-bound (one query block, ~120 us of scan): keep everything on the
+  // compute stream and skip the cross-stream events; large batches use the copy streams so that
+  // batch i+1's input copy runs under batch i's scan.
   cudaStream_t st = s.stream;
-  QRE_CUDA(cudaStreamWaitEvent(st, S.e_in, 0));
+  const bool one_stream = m <= kBM;
+  cudaStream_t in_st = one_stream ? st : h->h2d;
+  if (direct) {
+    QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, in_st));
+    QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice, in_st));
+  } else {
+    QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, in_st));
+  }
+  if (!one_stream) {
+    QRE_CUDA(cudaEventRecord(S.e_in, h->h2d));
+    QRE_CUDA(cudaStreamWaitEvent(st, S.e_in, 0));
+  }
   rc = scan_enqueue(h, m, d_q, d_ctx, S.p, 0, h->d_cand, st);
   if (rc != QRE_OK) return rc;
   const int K = S.p.do_route ? s.n_centroids : 0;
@@ -886,10 +893,15 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p, dres, st);
   QRE_CUDA(cudaGetLastError());
   QRE_CUDA(cudaMemcpyAsync(S.d_res + S.L.ovf.off, s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-  QRE_CUDA(cudaEventRecord(S.e_mid, st));
-  QRE_CUDA(cudaStreamWaitEvent(h->d2h, S.e_mid, 0));
-  QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, h->d2h));
-  QRE_CUDA(cudaEventRecord(S.e_done, h->d2h));
+  if (one_stream) {
+    QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, st));
+    QRE_CUDA(cudaEventRecord(S.e_done, st));
+  } else {
+    QRE_CUDA(cudaEventRecord(S.e_mid, st));
+    QRE_CUDA(cudaStreamWaitEvent(h->d2h, S.e_mid, 0));
+    QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, h->d2h));
+    QRE_CUDA(cudaEventRecord(S.e_done, h->d2h));
+  }
   S.pending = true;
   return QRE_OK;
 }
