@@ -851,36 +851,39 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   S.m = m;
   S.p = *params;
   S.p.pipeline_slot = 0;       // one compute stream: scan(i+1) is ordered after merge(i)
-  // ---- inputs: small arrays through pinned staging; the query matrix straight from the caller's
-  // buffer when that is already page-locked (no extra host copy), else staged too ----
+  // ---- inputs ----
+  // Large batches: small arrays through pinned staging, the query matrix straight from the caller's
+  // buffer when that is already page-locked, one H2D copy on the copy stream (it runs under the
+  // previous batch's scan) and one D2H copy of the result block on the other copy stream.
+  // Small batches (one query block, ~120 us of scan) are latency-bound: no copies at all — the
+  // kernels read the inputs from, and write the results to, page-locked host memory directly.
+  const bool zero_copy = m <= kBM;
   const bool direct = is_pinned_host(queries);
+  uint8_t* in_base = zero_copy ? S.h_in : S.d_in;      // pinned host memory is device-accessible (UVA)
   size_t o = 0;
   auto put = [&](const void* src, size_t bytes, bool copy) -> uint8_t* {
-    uint8_t* d = S.d_in + o;
+    uint8_t* d = in_base + o;
     if (src && copy) memcpy(S.h_in + o, src, bytes);
     o = align_up(o + bytes, 256);
     return d;
   };
   const size_t q_bytes = sizeof(float) * (size_t)m * s.dim;
   const float* d_q = (const float*)put(queries, q_bytes, !direct);
+  if (zero_copy && direct) d_q = queries;
   const size_t small_off = o;
   const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t) * (size_t)m, true);
   S.d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m, true);
   S.d_hd = put(heur_dev, (size_t)m, true);
   S.d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m, true);
-  // Small batches are latency-bound (one query block, ~120 us of scan): keep everything on the
-  // compute stream and skip the cross-stream events; large batches use the copy streams so that
-  // batch i+1's input copy runs under batch i's scan.
   cudaStream_t st = s.stream;
-  const bool one_stream = m <= kBM;
-  cudaStream_t in_st = one_stream ? st : h->h2d;
-  if (direct) {
-    QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, in_st));
-    QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice, in_st));
-  } else {
-    QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, in_st));
-  }
-  if (!one_stream) {
+  if (!zero_copy) {
+    if (direct) {
+      QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, h->h2d));
+      QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice,
+                               h->h2d));
+    } else {
+      QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, h->h2d));
+    }
     QRE_CUDA(cudaEventRecord(S.e_in, h->h2d));
     QRE_CUDA(cudaStreamWaitEvent(st, S.e_in, 0));
   }
@@ -889,12 +892,13 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   const int K = S.p.do_route ? s.n_centroids : 0;
   const int D = S.p.do_route ? S.p.n_devices : 1;
   S.L.plan(m, K, D);
-  const qre_result_t dres = S.L.view(S.d_res);
+  uint8_t* res_base = zero_copy ? S.h_res : S.d_res;
+  const qre_result_t dres = S.L.view(res_base);
   h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p, dres, st);
   QRE_CUDA(cudaGetLastError());
-  QRE_CUDA(cudaMemcpyAsync(S.d_res + S.L.ovf.off, s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-  if (one_stream) {
-    QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, st));
+  QRE_CUDA(cudaMemcpyAsync(res_base + S.L.ovf.off, s.ovf_unresolved, sizeof(int32_t),
+                           zero_copy ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+  if (zero_copy) {
     QRE_CUDA(cudaEventRecord(S.e_done, st));
   } else {
     QRE_CUDA(cudaEventRecord(S.e_mid, st));
@@ -946,9 +950,11 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
   h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, s.ovf_list, n_ovf, true, S.p, 0, h->d_cand, st);
   QRE_CUDA(cudaGetLastError());
   QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
-  h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p, S.L.view(S.d_res), st);
+  const bool zero_copy = m <= kBM;                  // same rule as qre_lookup_route_begin
+  h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p,
+                                    S.L.view(zero_copy ? S.h_res : S.d_res), st);
   QRE_CUDA(cudaGetLastError());
-  QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, st));
+  if (!zero_copy) QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, st));
   QRE_CUDA(cudaStreamSynchronize(st));
   scatter_results(S, S.p.do_route ? s.n_centroids : 0, S.p.do_route ? S.p.n_devices : 1, out);
   return QRE_OK;
