@@ -60,7 +60,8 @@ enum {
 
 /* result flags (per query) */
 #define QRE_FLAG_ZERO_NORM   1     /* ||q|| < 1e-9: lookup returns miss (src/cache.py:284) */
-#define QRE_FLAG_OVERFLOW    2     /* candidate window overflowed; resolved by the exact scan */
+#define QRE_FLAG_OVERFLOW    2     /* candidate window overflowed; settled by the brute-force fp32 pass:
+                                      the winner is exact, but cand[] then lists the winner only */
 
 typedef struct qre_cache qre_cache_t;
 
