@@ -224,6 +224,7 @@ QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64
                               int32_t* heur_cat);
 
 /* ---- peer exchange: the all-gather written as stores into peer memory ------------------------
+ * No counterpart in the reference (it never shards its cache; SURVEY §8e defines this exchange).
  * For a row-sharded cache with one process per GPU on one NVLink/NVSwitch box.  Instead of
  * handing cand[m, QRE_TOPK] to an NCCL all-gather, each rank's publish kernel writes its lists
  * directly into every rank's exchange buffer (CUDA-IPC-mapped peer pointers) and then raises a
@@ -247,10 +248,12 @@ QRE_API int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, 
                                      const double* heur_conf, const qre_params_t* params,
                                      qre_result_t* out_dev, void* stream);
 
-/* Kernel launches issued by this handle since creation (bench.py's gpu_launches). */
+/* Kernel launches issued by this handle since creation (bench.py's gpu_launches).  Measurement
+ * tooling: no counterpart in the reference. */
 QRE_API int qre_launch_count(const qre_cache_t* h, int64_t* count);
 
-/* Bracket every tensor-core scan launch with CUDA events on its own stream (enable != 0
+/* Measurement tooling, no counterpart in the reference.
+ * Bracket every tensor-core scan launch with CUDA events on its own stream (enable != 0
  * resets the counters); qre_profile_read waits for the recorded launches and returns their
  * summed device time.  bench.py uses this for the live roofline of the dominant kernel. */
 QRE_API int qre_profile(qre_cache_t* h, int enable);
@@ -290,7 +293,7 @@ QRE_API int qre_exact_lookup_noalloc(int device, int64_t n_rows, int dim, const 
                                      int64_t ttl_us, int64_t* hit_row, float* hit_sim, void* stream,
                                      char* err, size_t err_len);
 
-/* ---- bring-up / test hooks ------------------------------------------------------------
+/* ---- bring-up / test hooks (no counterpart in the reference) --------------------------------
  * Raw bf16 tensor-core product of the resident queries (from the last scan) with cache rows
  * [row0, row0+n): out[m, n] fp32, host buffer.  Used by tests to check the tcgen05/TMA
  * descriptors independently of the top-k logic. */
