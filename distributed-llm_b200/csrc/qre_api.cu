@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "qre_common.cuh"
+#include "qre_encoder.cuh"
 
 using namespace qre;
 
@@ -126,6 +127,26 @@ struct ResultLayout {
 constexpr size_t kStageBytes = 64u << 20;   // device staging for host-side append/update
 
 }  // namespace
+
+// Helpers shared with the other translation units of the library (qre_encoder.cuh).
+namespace qre {
+int set_error(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+int make_tensor_map_bf16(CUtensorMap* map, void* base, uint64_t inner, uint64_t rows, uint32_t box_inner,
+                         uint32_t box_rows) {
+  EncodeTiledFn enc = nullptr;
+  int rc = get_encode_fn(&enc);
+  if (rc != QRE_OK) return rc;
+  return make_tmap_bf16(enc, map, base, inner, rows, box_inner, box_rows);
+}
+}  // namespace qre
 
 struct qre_cache {
   DeviceState s;

@@ -1,0 +1,745 @@
+// qre_encoder.cu — the on-GPU query embedder behind include/qre_encoder_b200.h:
+// what SentenceTransformer("all-MiniLM-L6-v2").encode does between "token ids" and "fp32
+// embedding" (src/query_router_engine.py:181, 571; src/cache.py:412), restated in
+// oracle/minilm_oracle.py.  This file holds the non-GEMM kernels (embedding gather + LayerNorm,
+// attention, LayerNorm, mean pool + normalise), the weight/activation layout and the launch
+// sequence; the linear layers are in qre_enc_gemm.cu.
+//
+// Activations for one batch (T packed tokens, hidden H, FFN F), all bf16, rows padded to 128:
+//   x   [T, H]   layer input / residual stream          (A operand of QKV and FFN-up)
+//   qkv [T, 3H]  Q | K | V column blocks                (one fused projection)
+//   ctx [T, H]   attention output                       (A operand of the output projection)
+//   y   [T, H]   projection + residual, before LayerNorm
+//   h   [T, F]   GELU(FFN-up)                           (A operand of FFN-down)
+// LayerNorm statistics, softmax and pooling are fp32.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "qre_encoder.cuh"
+
+using namespace qre;
+
+namespace {
+
+constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int kMaxHidden = 1024;
+constexpr int kMaxInter = 4096;
+constexpr int kMaxSeq = 512;
+
+#define ENC_CUDA(expr)                                                                              \
+  do {                                                                                              \
+    cudaError_t e__ = (expr);                                                                       \
+    if (e__ != cudaSuccess)                                                                         \
+      return set_error(QRE_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  return v;
+}
+
+// One warp normalises one token row held as pairs: lane owns elements 64*i + 2*lane + {0,1}.
+template <int kMaxPairs>
+__device__ __forceinline__ void warp_layernorm_store(float (&v)[kMaxPairs][2], int pairs, int H, const float* g,
+                                                     const float* b, float eps, __nv_bfloat16* out, int lane) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxPairs; ++i)
+    if (i < pairs) s += v[i][0] + v[i][1];
+  const float mu = warp_sum(s) / static_cast<float>(H);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxPairs; ++i)
+    if (i < pairs) {
+      const float d0 = v[i][0] - mu, d1 = v[i][1] - mu;
+      q += d0 * d0 + d1 * d1;
+    }
+  const float rstd = rsqrtf(warp_sum(q) / static_cast<float>(H) + eps);
+#pragma unroll
+  for (int i = 0; i < kMaxPairs; ++i)
+    if (i < pairs) {
+      const int c = 64 * i + 2 * lane;
+      const float2 gg = *reinterpret_cast<const float2*>(g + c);
+      const float2 bb = *reinterpret_cast<const float2*>(b + c);
+      *reinterpret_cast<__nv_bfloat162*>(out + c) =
+          __floats2bfloat162_rn((v[i][0] - mu) * rstd * gg.x + bb.x, (v[i][1] - mu) * rstd * gg.y + bb.y);
+    }
+}
+
+constexpr int kPairsMax = kMaxHidden / 64;   // 16
+
+// x[t] = LayerNorm(word[id[t]] + position[t - seq start] + token_type[0]); one CTA per sequence,
+// warps stride over its tokens.  (BertEmbeddings; token_type_ids are all zero for one-segment input.)
+__global__ void __launch_bounds__(256)
+enc_embed_ln_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ offsets, const float* __restrict__ word,
+                    const float* __restrict__ pos, const float* __restrict__ type0, const float* __restrict__ g,
+                    const float* __restrict__ b, float eps, int H, int vocab, __nv_bfloat16* __restrict__ x) {
+  const int seq = blockIdx.x;
+  const int t0 = offsets[seq], L = offsets[seq + 1] - t0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int pairs = H / 64;
+  for (int p = warp; p < L; p += nw) {
+    int id = ids[t0 + p];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    const float* wr = word + static_cast<long long>(id) * H;
+    const float* pr = pos + static_cast<long long>(p) * H;
+    float v[kPairsMax][2];
+#pragma unroll
+    for (int i = 0; i < kPairsMax; ++i)
+      if (i < pairs) {
+        const int c = 64 * i + 2 * lane;
+        const float2 a = *reinterpret_cast<const float2*>(wr + c);
+        const float2 q = *reinterpret_cast<const float2*>(pr + c);
+        const float2 t = *reinterpret_cast<const float2*>(type0 + c);
+        v[i][0] = a.x + q.x + t.x;
+        v[i][1] = a.y + q.y + t.y;
+      }
+    warp_layernorm_store<kPairsMax>(v, pairs, H, g, b, eps, x + static_cast<long long>(t0 + p) * H, lane);
+  }
+}
+
+// x[t] = LayerNorm(y[t]); y already holds projection + bias + residual.  One warp per token.
+__global__ void __launch_bounds__(256)
+enc_layernorm_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
+                     float eps, int H, long long T, __nv_bfloat16* __restrict__ x) {
+  const long long t = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (t >= T) return;
+  const int lane = threadIdx.x & 31, pairs = H / 64;
+  const __nv_bfloat16* yr = y + t * H;
+  float v[kPairsMax][2];
+#pragma unroll
+  for (int i = 0; i < kPairsMax; ++i)
+    if (i < pairs) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(yr + 64 * i + 2 * lane));
+      v[i][0] = f.x;
+      v[i][1] = f.y;
+    }
+  warp_layernorm_store<kPairsMax>(v, pairs, H, g, b, eps, x + t * H, lane);
+}
+
+// ---- attention --------------------------------------------------------------------------------
+__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// softmax(Q K^T / sqrt(HD)) V for one (sequence, head): the L keys and values are staged in
+// shared memory (K as [key][dim], V transposed to [dim][key], both padded against bank
+// conflicts); each warp owns 16 query rows at a time and walks the keys 16 at a time with an
+// online softmax, scores and probabilities never leaving registers (the accumulator layout of
+// one m16n8k16 product is the A-operand layout of the next).
+template <int HD>
+__global__ void __launch_bounds__(128)
+enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
+                     __nv_bfloat16* __restrict__ ctx, int H, int Lp, float scale_log2e) {
+  constexpr int KS = HD + 8;                 // Ks row stride (elements)
+  const int VS = Lp + 8;                     // Vt row stride (elements)
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);
+  __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
+
+  const int seq = blockIdx.x, head = blockIdx.y;
+  const int t0 = offsets[seq];
+  const int L = min(offsets[seq + 1] - t0, Lp);
+  if (L <= 0) return;
+  const int Lk = (L + 15) & ~15;
+  const long long ld = 3LL * H;
+  const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
+
+  for (int idx = threadIdx.x; idx < Lk * (HD / 8); idx += blockDim.x) {
+    const int key = idx / (HD / 8), part = idx - key * (HD / 8);
+    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+    if (key < L) {
+      kv = *reinterpret_cast<const uint4*>(base + key * ld + H + part * 8);
+      vv = *reinterpret_cast<const uint4*>(base + key * ld + 2 * H + part * 8);
+    }
+    *reinterpret_cast<uint4*>(Ks + key * KS + part * 8) = kv;
+    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) Vt[(part * 8 + j) * VS + key] = ve[j];
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const float ninf = __int_as_float(0xff800000);
+
+  for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5) {
+    const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
+    uint32_t qa[HD / 16][4];
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+      const int c = kk * 16 + 2 * t;
+      qa[kk][0] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c) : 0u;
+      qa[kk][1] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c) : 0u;
+      qa[kk][2] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c + 8) : 0u;
+      qa[kk][3] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c + 8) : 0u;
+    }
+    float o[HD / 8][4];
+#pragma unroll
+    for (int nd = 0; nd < HD / 8; ++nd) o[nd][0] = o[nd][1] = o[nd][2] = o[nd][3] = 0.f;
+    float m_lo = ninf, m_hi = ninf, l_lo = 0.f, l_hi = 0.f;
+
+    for (int k0 = 0; k0 < Lk; k0 += 16) {
+      float s[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+        const __nv_bfloat16* kr = Ks + (k0 + j * 8 + g) * KS + 2 * t;
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          mma_16816(s[j], qa[kk], *reinterpret_cast<const uint32_t*>(kr + kk * 16),
+                    *reinterpret_cast<const uint32_t*>(kr + kk * 16 + 8));
+      }
+      // scale into the log2 domain and mask the padded keys
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int key = k0 + j * 8 + 2 * t;
+        s[j][0] = key < L ? s[j][0] * scale_log2e : ninf;
+        s[j][2] = key < L ? s[j][2] * scale_log2e : ninf;
+        s[j][1] = key + 1 < L ? s[j][1] * scale_log2e : ninf;
+        s[j][3] = key + 1 < L ? s[j][3] * scale_log2e : ninf;
+      }
+      float bm_lo = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+      float bm_hi = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+      bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 1));
+      bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 2));
+      bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 1));
+      bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 2));
+      const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);   // finite: key k0 < L is in every block
+      const float c_lo = exp2f(m_lo - mn_lo), c_hi = exp2f(m_hi - mn_hi);
+      m_lo = mn_lo;
+      m_hi = mn_hi;
+      float p[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        p[j][0] = exp2f(s[j][0] - mn_lo);
+        p[j][1] = exp2f(s[j][1] - mn_lo);
+        p[j][2] = exp2f(s[j][2] - mn_hi);
+        p[j][3] = exp2f(s[j][3] - mn_hi);
+      }
+      l_lo = l_lo * c_lo + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
+      l_hi = l_hi * c_hi + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
+      const uint32_t pa[4] = {pack_bf16(p[0][0], p[0][1]), pack_bf16(p[0][2], p[0][3]), pack_bf16(p[1][0], p[1][1]),
+                              pack_bf16(p[1][2], p[1][3])};
+#pragma unroll
+      for (int nd = 0; nd < HD / 8; ++nd) {
+        o[nd][0] *= c_lo;
+        o[nd][1] *= c_lo;
+        o[nd][2] *= c_hi;
+        o[nd][3] *= c_hi;
+        const __nv_bfloat16* vr = Vt + (nd * 8 + g) * VS + k0 + 2 * t;
+        mma_16816(o[nd], pa, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
+      }
+    }
+    l_lo += __shfl_xor_sync(kFull, l_lo, 1);
+    l_lo += __shfl_xor_sync(kFull, l_lo, 2);
+    l_hi += __shfl_xor_sync(kFull, l_hi, 1);
+    l_hi += __shfl_xor_sync(kFull, l_hi, 2);
+    const float i_lo = 1.f / l_lo, i_hi = 1.f / l_hi;
+    __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD + 2 * t;
+#pragma unroll
+    for (int nd = 0; nd < HD / 8; ++nd) {
+      if (r_lo < L)
+        *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_lo) * H + nd * 8) =
+            __floats2bfloat162_rn(o[nd][0] * i_lo, o[nd][1] * i_lo);
+      if (r_hi < L)
+        *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_hi) * H + nd * 8) =
+            __floats2bfloat162_rn(o[nd][2] * i_hi, o[nd][3] * i_hi);
+    }
+  }
+}
+
+// Pooling(mean over the sequence's tokens) + Normalize (x / max(|x|, 1e-12)); one CTA per sequence.
+__global__ void __launch_bounds__(128)
+enc_pool_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ offsets, int H, int normalize,
+                float* __restrict__ out) {
+  __shared__ float red[4];
+  const int seq = blockIdx.x;
+  const int t0 = offsets[seq], L = offsets[seq + 1] - t0;
+  const int pairs = H / 2;                       // thread owns column pairs tid, tid + 128, ...
+  float2 acc[kMaxHidden / 256];
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxHidden / 256; ++i) {
+    acc[i] = make_float2(0.f, 0.f);
+    const int pc = threadIdx.x + i * 128;
+    if (pc < pairs) {
+      for (int p = 0; p < L; ++p) {
+        const float2 f =
+            __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + static_cast<long long>(t0 + p) * H + 2 * pc));
+        acc[i].x += f.x;
+        acc[i].y += f.y;
+      }
+      const float inv = 1.f / fmaxf(static_cast<float>(L), 1e-9f);
+      acc[i].x *= inv;
+      acc[i].y *= inv;
+      sq += acc[i].x * acc[i].x + acc[i].y * acc[i].y;
+    }
+  }
+  sq = warp_sum(sq);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
+  __syncthreads();
+  const float nrm = sqrtf(red[0] + red[1] + red[2] + red[3]);
+  const float sc = normalize ? 1.f / fmaxf(nrm, 1e-12f) : 1.f;
+#pragma unroll
+  for (int i = 0; i < kMaxHidden / 256; ++i) {
+    const int pc = threadIdx.x + i * 128;
+    if (pc < pairs)
+      *reinterpret_cast<float2*>(out + static_cast<long long>(seq) * H + 2 * pc) = make_float2(acc[i].x * sc, acc[i].y * sc);
+  }
+}
+
+size_t attention_smem(int hd, int Lp) {
+  return static_cast<size_t>(Lp) * (hd + 8) * 2 + static_cast<size_t>(hd) * (Lp + 8) * 2;
+}
+
+struct Linear {
+  __nv_bfloat16* w = nullptr;   // [n, k] bf16
+  float* b = nullptr;           // [n]
+  CUtensorMap map;
+  int n = 0, k = 0;
+};
+
+struct Layer {
+  Linear qkv, out, up, down;
+  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+};
+
+inline size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+struct qre_encoder {
+  qre_encoder_config_t cfg;
+  int device = 0, num_sms = 0, hd = 0;
+  int64_t max_tokens = 0, tok_pad = 0;
+  int max_seqs = 0;
+  cudaStream_t stream = nullptr;
+  float *word = nullptr, *pos = nullptr, *type = nullptr, *eln_g = nullptr, *eln_b = nullptr;
+  std::vector<Layer> layers;
+  __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *h = nullptr;
+  CUtensorMap map_x, map_ctx, map_h;
+  int32_t *d_ids = nullptr, *d_off = nullptr;
+  float* d_out = nullptr;
+  int32_t *h_ids = nullptr, *h_off = nullptr;     // pinned staging of the host entry point
+  float* h_out = nullptr;
+  int64_t launches = 0;
+  bool have_emb = false;
+  std::vector<char> have_layer;
+};
+
+namespace {
+
+int upload_f32(float** dst, const float* src, size_t n) {
+  if (src == nullptr) return set_error(QRE_ERR_INVALID, "null weight pointer");
+  if (*dst == nullptr) ENC_CUDA(cudaMalloc(dst, n * sizeof(float)));
+  ENC_CUDA(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
+  return QRE_OK;
+}
+
+// fp32 [n, k] host blocks stacked along n -> one bf16 [n_total, k] device matrix + its tensor map.
+int upload_linear(Linear& L, std::initializer_list<const float*> ws, std::initializer_list<const float*> bs, int n_each,
+                  int k) {
+  const int parts = static_cast<int>(ws.size());
+  const int n = n_each * parts;
+  for (const float* p : ws)
+    if (p == nullptr) return set_error(QRE_ERR_INVALID, "null weight pointer");
+  for (const float* p : bs)
+    if (p == nullptr) return set_error(QRE_ERR_INVALID, "null bias pointer");
+  std::vector<__nv_bfloat16> wb(static_cast<size_t>(n) * k);
+  std::vector<float> bb(n);
+  int part = 0;
+  for (const float* p : ws) {
+    for (size_t i = 0; i < static_cast<size_t>(n_each) * k; ++i)
+      wb[static_cast<size_t>(part) * n_each * k + i] = __float2bfloat16(p[i]);
+    ++part;
+  }
+  part = 0;
+  for (const float* p : bs) {
+    memcpy(bb.data() + static_cast<size_t>(part) * n_each, p, sizeof(float) * n_each);
+    ++part;
+  }
+  if (L.w == nullptr) {
+    // rows padded to the 192-row TMA box so the last feature tile never reads past the allocation
+    const size_t rows_pad = round_up(n, kEncBN);
+    ENC_CUDA(cudaMalloc(&L.w, rows_pad * k * sizeof(__nv_bfloat16)));
+    ENC_CUDA(cudaMemset(L.w, 0, rows_pad * k * sizeof(__nv_bfloat16)));
+    ENC_CUDA(cudaMalloc(&L.b, round_up(n, kEncBN) * sizeof(float)));
+    ENC_CUDA(cudaMemset(L.b, 0, round_up(n, kEncBN) * sizeof(float)));
+    int rc = make_tensor_map_bf16(&L.map, L.w, static_cast<uint64_t>(k), rows_pad, kEncBK, kEncBN);
+    if (rc != QRE_OK) return rc;
+  }
+  ENC_CUDA(cudaMemcpy(L.w, wb.data(), wb.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+  ENC_CUDA(cudaMemcpy(L.b, bb.data(), bb.size() * sizeof(float), cudaMemcpyHostToDevice));
+  L.n = n;
+  L.k = k;
+  return QRE_OK;
+}
+
+void free_linear(Linear& L) {
+  cudaFree(L.w);
+  cudaFree(L.b);
+  L.w = nullptr;
+  L.b = nullptr;
+}
+
+int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_t T, const __nv_bfloat16* residual,
+               __nv_bfloat16* out, int epi, cudaStream_t st) {
+  EncGemmArgs a;
+  a.rows = static_cast<int>(T);
+  a.n = L.n;
+  a.num_kb = L.k / kEncBK;
+  a.tiles_m = static_cast<int>((T + kEncBM - 1) / kEncBM);
+  a.tiles_n = (L.n + kEncBN - 1) / kEncBN;
+  a.bias = L.b;
+  a.residual = residual;
+  a.out = out;
+  return launch_enc_gemm(map_a, L.map, a, epi, e->num_sms, st);
+}
+
+int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len, cudaStream_t st) {
+  const int Lp = (max_len + 15) & ~15;
+  const int H = e->cfg.hidden;
+  const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(e->hd));
+  const dim3 grid(m, e->cfg.heads);
+  const size_t smem = attention_smem(e->hd, Lp);
+  if (e->hd == 32)
+    enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, scale_log2e);
+  else
+    enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, scale_log2e);
+  return 1;
+}
+
+// The whole forward pass for m packed sequences already on the device.
+int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* offsets, int64_t T, int max_len,
+                     int normalize, float* out, cudaStream_t st) {
+  const qre_encoder_config_t& c = e->cfg;
+  const int H = c.hidden;
+  if (T > 0) {
+    enc_embed_ln_kernel<<<m, 256, 0, st>>>(ids, offsets, e->word, e->pos, e->type, e->eln_g, e->eln_b, c.ln_eps, H,
+                                           c.vocab_size, e->x);
+    ++e->launches;
+    const int ln_grid = static_cast<int>((T + 7) / 8);
+    for (int l = 0; l < c.layers; ++l) {
+      Layer& L = e->layers[l];
+      e->launches += run_linear(e, e->map_x, L.qkv, T, nullptr, e->qkv, kEpiBias, st);
+      e->launches += launch_attention(e, m, offsets, max_len, st);
+      e->launches += run_linear(e, e->map_ctx, L.out, T, e->x, e->y, kEpiResidual, st);
+      enc_layernorm_kernel<<<ln_grid, 256, 0, st>>>(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x);
+      e->launches += run_linear(e, e->map_x, L.up, T, nullptr, e->h, kEpiGelu, st);
+      e->launches += run_linear(e, e->map_h, L.down, T, e->x, e->y, kEpiResidual, st);
+      enc_layernorm_kernel<<<ln_grid, 256, 0, st>>>(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x);
+      e->launches += 2;
+    }
+  }
+  enc_pool_kernel<<<m, 128, 0, st>>>(e->x, offsets, H, normalize, out);
+  ++e->launches;
+  ENC_CUDA(cudaGetLastError());
+  return QRE_OK;
+}
+
+int check_ready(const qre_encoder* e) {
+  if (e == nullptr) return set_error(QRE_ERR_INVALID, "null encoder handle");
+  if (!e->have_emb) return set_error(QRE_ERR_INVALID, "encoder: embeddings not set (qre_encoder_set_embeddings)");
+  for (size_t l = 0; l < e->have_layer.size(); ++l)
+    if (!e->have_layer[l]) return set_error(QRE_ERR_INVALID, "encoder: layer %d not set (qre_encoder_set_layer)", (int)l);
+  return QRE_OK;
+}
+
+void destroy(qre_encoder* e) {
+  if (e == nullptr) return;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (float* p : {e->word, e->pos, e->type, e->eln_g, e->eln_b, e->d_out}) cudaFree(p);
+  for (Layer& L : e->layers) {
+    free_linear(L.qkv);
+    free_linear(L.out);
+    free_linear(L.up);
+    free_linear(L.down);
+    for (float* p : {L.ln1_g, L.ln1_b, L.ln2_g, L.ln2_b}) cudaFree(p);
+  }
+  for (__nv_bfloat16* p : {e->x, e->qkv, e->ctx, e->y, e->h}) cudaFree(p);
+  cudaFree(e->d_ids);
+  cudaFree(e->d_off);
+  cudaFreeHost(e->h_ids);
+  cudaFreeHost(e->h_off);
+  cudaFreeHost(e->h_out);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+}  // namespace
+
+extern "C" {
+
+int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_tokens, int max_seqs,
+                       qre_encoder_t** out) {
+  if (cfg == nullptr || out == nullptr) return set_error(QRE_ERR_INVALID, "null argument");
+  *out = nullptr;
+  const qre_encoder_config_t& c = *cfg;
+  if (c.hidden <= 0 || c.hidden % 64 != 0 || c.hidden > kMaxHidden)
+    return set_error(QRE_ERR_INVALID, "encoder: hidden must be a multiple of 64 and <= %d (got %d)", kMaxHidden, c.hidden);
+  if (c.intermediate <= 0 || c.intermediate % 64 != 0 || c.intermediate > kMaxInter)
+    return set_error(QRE_ERR_INVALID, "encoder: intermediate must be a multiple of 64 and <= %d (got %d)", kMaxInter,
+                     c.intermediate);
+  if (c.heads <= 0 || c.hidden % c.heads != 0 || (c.hidden / c.heads != 32 && c.hidden / c.heads != 64))
+    return set_error(QRE_ERR_INVALID, "encoder: hidden / heads must be 32 or 64 (got %d / %d)", c.hidden, c.heads);
+  if (c.layers <= 0 || c.layers > 48 || c.vocab_size <= 0 || c.type_vocab <= 0)
+    return set_error(QRE_ERR_INVALID, "encoder: bad layers / vocab_size / type_vocab");
+  if (c.max_seq_len <= 0 || c.max_seq_len > kMaxSeq || c.max_seq_len > c.max_positions)
+    return set_error(QRE_ERR_INVALID, "encoder: max_seq_len must be in [1, min(%d, max_positions)]", kMaxSeq);
+  if (!(c.ln_eps >= 0.f)) return set_error(QRE_ERR_INVALID, "encoder: bad ln_eps");
+  if (max_tokens <= 0 || max_seqs <= 0 || max_tokens > (1LL << 30))
+    return set_error(QRE_ERR_INVALID, "encoder: bad max_tokens / max_seqs");
+  int n_dev = 0;
+  ENC_CUDA(cudaGetDeviceCount(&n_dev));
+  if (device < 0 || device >= n_dev) return set_error(QRE_ERR_NO_DEVICE, "encoder: no CUDA device %d", device);
+  ENC_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  ENC_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return set_error(QRE_ERR_NO_DEVICE, "encoder: device %d is sm_%d%d; this library is built for sm_100a only", device,
+                     prop.major, prop.minor);
+  qre_encoder* e = new (std::nothrow) qre_encoder();
+  if (e == nullptr) return set_error(QRE_ERR_CUDA, "out of host memory");
+  e->cfg = c;
+  e->device = device;
+  e->num_sms = prop.multiProcessorCount;
+  e->hd = c.hidden / c.heads;
+  e->max_tokens = max_tokens;
+  e->tok_pad = static_cast<int64_t>(round_up(static_cast<size_t>(max_tokens), kEncBM));
+  e->max_seqs = max_seqs;
+  e->layers.resize(c.layers);
+  e->have_layer.assign(c.layers, 0);
+  auto fail_free = [&](int rc) {
+    destroy(e);
+    return rc;
+  };
+#define ENC_TRY(expr)                                                                                \
+  do {                                                                                               \
+    cudaError_t e__ = (expr);                                                                        \
+    if (e__ != cudaSuccess)                                                                          \
+      return fail_free(set_error(e__ == cudaErrorMemoryAllocation ? QRE_ERR_CUDA : QRE_ERR_CUDA,    \
+                                 "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__)); \
+  } while (0)
+  ENC_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  ENC_TRY(enc_gemm_init());
+  const size_t att = attention_smem(e->hd, (c.max_seq_len + 15) & ~15);
+  if (att > 48 * 1024) {
+    if (e->hd == 32)
+      ENC_TRY(cudaFuncSetAttribute(enc_attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att));
+    else
+      ENC_TRY(cudaFuncSetAttribute(enc_attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att));
+  }
+  const size_t T = static_cast<size_t>(e->tok_pad), H = c.hidden, F = c.intermediate;
+  ENC_TRY(cudaMalloc(&e->x, T * H * 2));
+  ENC_TRY(cudaMalloc(&e->qkv, T * 3 * H * 2));
+  ENC_TRY(cudaMalloc(&e->ctx, T * H * 2));
+  ENC_TRY(cudaMalloc(&e->y, T * H * 2));
+  ENC_TRY(cudaMalloc(&e->h, T * F * 2));
+  // rows past the batch's token count are read by the last TMA box of a GEMM (never stored):
+  // keep them finite
+  ENC_TRY(cudaMemset(e->x, 0, T * H * 2));
+  ENC_TRY(cudaMemset(e->ctx, 0, T * H * 2));
+  ENC_TRY(cudaMemset(e->h, 0, T * F * 2));
+  ENC_TRY(cudaMalloc(&e->d_ids, sizeof(int32_t) * max_tokens));
+  ENC_TRY(cudaMalloc(&e->d_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
+  ENC_TRY(cudaMalloc(&e->d_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
+  ENC_TRY(cudaMallocHost(&e->h_ids, sizeof(int32_t) * max_tokens));
+  ENC_TRY(cudaMallocHost(&e->h_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
+  ENC_TRY(cudaMallocHost(&e->h_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
+#undef ENC_TRY
+  int rc = make_tensor_map_bf16(&e->map_x, e->x, H, T, kEncBK, kEncBM);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->map_ctx, e->ctx, H, T, kEncBK, kEncBM);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->map_h, e->h, F, T, kEncBK, kEncBM);
+  if (rc != QRE_OK) return fail_free(rc);
+  *out = e;
+  return QRE_OK;
+}
+
+int qre_encoder_destroy(qre_encoder_t* e) {
+  destroy(e);
+  return QRE_OK;
+}
+
+int qre_encoder_set_embeddings(qre_encoder_t* e, const float* word, const float* position, const float* token_type,
+                               const float* ln_g, const float* ln_b) {
+  if (e == nullptr) return set_error(QRE_ERR_INVALID, "null encoder handle");
+  ENC_CUDA(cudaSetDevice(e->device));
+  ENC_CUDA(cudaStreamSynchronize(e->stream));
+  const size_t H = e->cfg.hidden;
+  int rc = upload_f32(&e->word, word, static_cast<size_t>(e->cfg.vocab_size) * H);
+  if (rc == QRE_OK) rc = upload_f32(&e->pos, position, static_cast<size_t>(e->cfg.max_positions) * H);
+  if (rc == QRE_OK) rc = upload_f32(&e->type, token_type, static_cast<size_t>(e->cfg.type_vocab) * H);
+  if (rc == QRE_OK) rc = upload_f32(&e->eln_g, ln_g, H);
+  if (rc == QRE_OK) rc = upload_f32(&e->eln_b, ln_b, H);
+  if (rc == QRE_OK) e->have_emb = true;
+  return rc;
+}
+
+int qre_encoder_set_layer(qre_encoder_t* e, int layer, const qre_encoder_layer_t* w) {
+  if (e == nullptr || w == nullptr) return set_error(QRE_ERR_INVALID, "null argument");
+  if (layer < 0 || layer >= e->cfg.layers) return set_error(QRE_ERR_INVALID, "encoder: layer %d out of range", layer);
+  ENC_CUDA(cudaSetDevice(e->device));
+  ENC_CUDA(cudaStreamSynchronize(e->stream));
+  Layer& L = e->layers[layer];
+  const int H = e->cfg.hidden, F = e->cfg.intermediate;
+  int rc = upload_linear(L.qkv, {w->wq, w->wk, w->wv}, {w->bq, w->bk, w->bv}, H, H);
+  if (rc == QRE_OK) rc = upload_linear(L.out, {w->wo}, {w->bo}, H, H);
+  if (rc == QRE_OK) rc = upload_linear(L.up, {w->w1}, {w->b1}, F, H);
+  if (rc == QRE_OK) rc = upload_linear(L.down, {w->w2}, {w->b2}, H, F);
+  if (rc == QRE_OK) rc = upload_f32(&L.ln1_g, w->ln1_g, H);
+  if (rc == QRE_OK) rc = upload_f32(&L.ln1_b, w->ln1_b, H);
+  if (rc == QRE_OK) rc = upload_f32(&L.ln2_g, w->ln2_g, H);
+  if (rc == QRE_OK) rc = upload_f32(&L.ln2_b, w->ln2_b, H);
+  if (rc == QRE_OK) e->have_layer[layer] = 1;
+  return rc;
+}
+
+int qre_encode_dev(qre_encoder_t* e, int m, const int32_t* ids, const int32_t* offsets, int64_t n_tokens, int max_len,
+                   int normalize, float* out, void* stream) {
+  int rc = check_ready(e);
+  if (rc != QRE_OK) return rc;
+  if (m == 0) return QRE_OK;
+  if (m < 0 || m > e->max_seqs) return set_error(QRE_ERR_CAPACITY, "encoder: %d sequences, capacity %d", m, e->max_seqs);
+  if (n_tokens < 0 || n_tokens > e->max_tokens)
+    return set_error(QRE_ERR_CAPACITY, "encoder: %lld tokens, capacity %lld", (long long)n_tokens, (long long)e->max_tokens);
+  if (max_len < 0 || max_len > e->cfg.max_seq_len)
+    return set_error(QRE_ERR_INVALID, "encoder: max_len %d exceeds max_seq_len %d", max_len, e->cfg.max_seq_len);
+  if (offsets == nullptr || out == nullptr || (n_tokens > 0 && ids == nullptr))
+    return set_error(QRE_ERR_INVALID, "null argument");
+  ENC_CUDA(cudaSetDevice(e->device));
+  cudaStream_t st = stream != nullptr ? static_cast<cudaStream_t>(stream) : e->stream;
+  return encode_on_device(e, m, ids, offsets, n_tokens, max_len, normalize, out, st);
+}
+
+int qre_encode(qre_encoder_t* e, int m, const int32_t* ids, const int32_t* offsets, int normalize, float* out) {
+  int rc = check_ready(e);
+  if (rc != QRE_OK) return rc;
+  if (m == 0) return QRE_OK;
+  if (m < 0 || m > e->max_seqs) return set_error(QRE_ERR_CAPACITY, "encoder: %d sequences, capacity %d", m, e->max_seqs);
+  if (offsets == nullptr || out == nullptr) return set_error(QRE_ERR_INVALID, "null argument");
+  if (offsets[0] != 0) return set_error(QRE_ERR_INVALID, "encoder: offsets[0] must be 0");
+  // pack with truncation into the pinned staging buffers
+  int64_t T = 0;
+  int max_len = 0;
+  e->h_off[0] = 0;
+  for (int i = 0; i < m; ++i) {
+    const int64_t len_in = static_cast<int64_t>(offsets[i + 1]) - offsets[i];
+    if (len_in < 0) return set_error(QRE_ERR_INVALID, "encoder: offsets must be non-decreasing (sequence %d)", i);
+    const int len = static_cast<int>(len_in < e->cfg.max_seq_len ? len_in : e->cfg.max_seq_len);
+    if (T + len > e->max_tokens)
+      return set_error(QRE_ERR_CAPACITY, "encoder: more than %lld tokens in the batch", (long long)e->max_tokens);
+    if (len > 0) {
+      if (ids == nullptr) return set_error(QRE_ERR_INVALID, "null ids");
+      memcpy(e->h_ids + T, ids + offsets[i], sizeof(int32_t) * len);
+    }
+    T += len;
+    e->h_off[i + 1] = static_cast<int32_t>(T);
+    if (len > max_len) max_len = len;
+  }
+  ENC_CUDA(cudaSetDevice(e->device));
+  cudaStream_t st = e->stream;
+  if (T > 0) ENC_CUDA(cudaMemcpyAsync(e->d_ids, e->h_ids, sizeof(int32_t) * T, cudaMemcpyHostToDevice, st));
+  ENC_CUDA(cudaMemcpyAsync(e->d_off, e->h_off, sizeof(int32_t) * (m + 1), cudaMemcpyHostToDevice, st));
+  rc = encode_on_device(e, m, e->d_ids, e->d_off, T, max_len, normalize, e->d_out, st);
+  if (rc != QRE_OK) return rc;
+  const size_t bytes = sizeof(float) * static_cast<size_t>(m) * e->cfg.hidden;
+  ENC_CUDA(cudaMemcpyAsync(e->h_out, e->d_out, bytes, cudaMemcpyDeviceToHost, st));
+  ENC_CUDA(cudaStreamSynchronize(st));
+  memcpy(out, e->h_out, bytes);
+  return QRE_OK;
+}
+
+int qre_encoder_launch_count(const qre_encoder_t* e, int64_t* count) {
+  if (e == nullptr || count == nullptr) return set_error(QRE_ERR_INVALID, "null argument");
+  *count = e->launches;
+  return QRE_OK;
+}
+
+int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, const float* w, const float* bias,
+                           const float* residual, int epilogue, float* c) {
+  if (rows <= 0 || n <= 0 || k <= 0 || n % 32 != 0 || k % 64 != 0)
+    return set_error(QRE_ERR_INVALID, "debug_gemm: need rows > 0, n %% 32 == 0, k %% 64 == 0");
+  if (a == nullptr || w == nullptr || bias == nullptr || c == nullptr || (epilogue == kEpiResidual && residual == nullptr))
+    return set_error(QRE_ERR_INVALID, "null argument");
+  if (epilogue < 0 || epilogue > 2) return set_error(QRE_ERR_INVALID, "debug_gemm: epilogue must be 0, 1 or 2");
+  ENC_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  ENC_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return set_error(QRE_ERR_NO_DEVICE, "debug_gemm: sm_100a only");
+  ENC_CUDA(enc_gemm_init());
+  const size_t rows_pad = round_up(rows, kEncBM), n_pad = round_up(n, kEncBN);
+  std::vector<__nv_bfloat16> ab(rows_pad * k, __float2bfloat16(0.f)), wb(n_pad * k, __float2bfloat16(0.f)),
+      rb(static_cast<size_t>(rows) * n), cb(static_cast<size_t>(rows) * n);
+  for (size_t i = 0; i < static_cast<size_t>(rows) * k; ++i) ab[i] = __float2bfloat16(a[i]);
+  for (size_t i = 0; i < static_cast<size_t>(n) * k; ++i) wb[i] = __float2bfloat16(w[i]);
+  if (residual != nullptr)
+    for (size_t i = 0; i < rb.size(); ++i) rb[i] = __float2bfloat16(residual[i]);
+  __nv_bfloat16 *da = nullptr, *dw = nullptr, *dr = nullptr, *dc = nullptr;
+  float* db = nullptr;
+  int rc = QRE_OK;
+  auto cleanup = [&]() {
+    cudaFree(da);
+    cudaFree(dw);
+    cudaFree(dr);
+    cudaFree(dc);
+    cudaFree(db);
+  };
+#define DBG_TRY(expr)                                                                              \
+  do {                                                                                             \
+    cudaError_t e__ = (expr);                                                                      \
+    if (e__ != cudaSuccess) {                                                                      \
+      cleanup();                                                                                   \
+      return set_error(QRE_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    }                                                                                              \
+  } while (0)
+  DBG_TRY(cudaMalloc(&da, ab.size() * 2));
+  DBG_TRY(cudaMalloc(&dw, wb.size() * 2));
+  DBG_TRY(cudaMalloc(&dr, rb.size() * 2));
+  DBG_TRY(cudaMalloc(&dc, cb.size() * 2));
+  DBG_TRY(cudaMalloc(&db, n_pad * sizeof(float)));
+  DBG_TRY(cudaMemset(db, 0, n_pad * sizeof(float)));
+  DBG_TRY(cudaMemcpy(da, ab.data(), ab.size() * 2, cudaMemcpyHostToDevice));
+  DBG_TRY(cudaMemcpy(dw, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
+  DBG_TRY(cudaMemcpy(dr, rb.data(), rb.size() * 2, cudaMemcpyHostToDevice));
+  DBG_TRY(cudaMemcpy(db, bias, n * sizeof(float), cudaMemcpyHostToDevice));
+  CUtensorMap ma, mw;
+  rc = make_tensor_map_bf16(&ma, da, k, rows_pad, kEncBK, kEncBM);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&mw, dw, k, n_pad, kEncBK, kEncBN);
+  if (rc != QRE_OK) {
+    cleanup();
+    return rc;
+  }
+  EncGemmArgs g;
+  g.rows = rows;
+  g.n = n;
+  g.num_kb = k / kEncBK;
+  g.tiles_m = static_cast<int>(rows_pad / kEncBM);
+  g.tiles_n = static_cast<int>(n_pad / kEncBN);
+  g.bias = db;
+  g.residual = dr;
+  g.out = dc;
+  launch_enc_gemm(ma, mw, g, epilogue, prop.multiProcessorCount, nullptr);
+  DBG_TRY(cudaGetLastError());
+  DBG_TRY(cudaDeviceSynchronize());
+  DBG_TRY(cudaMemcpy(cb.data(), dc, cb.size() * 2, cudaMemcpyDeviceToHost));
+#undef DBG_TRY
+  cleanup();
+  for (size_t i = 0; i < cb.size(); ++i) c[i] = __bfloat162float(cb[i]);
+  return QRE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,43 @@
+// Shared declarations of the on-GPU query embedder (include/qre_encoder_b200.h).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/qre_encoder_b200.h"
+
+namespace qre {
+
+// Tile of the encoder GEMM: 128 tokens (one TMEM lane each) x 192 output features.  192 divides
+// every feature count of the MiniLM / BERT-base family (384, 768, 1152, 1536, 2304, 3072), and
+// two fp32 accumulators of 192 columns fit the 512 TMEM columns for epilogue/MMA overlap.
+constexpr int kEncBM = 128;
+constexpr int kEncBN = 192;
+constexpr int kEncBK = 64;
+constexpr int kEncStages = 5;
+
+enum EncEpilogue { kEpiBias = 0, kEpiGelu = 1, kEpiResidual = 2 };
+
+struct EncGemmArgs {
+  int rows;                      // tokens
+  int n;                         // output features (multiple of 32)
+  int num_kb;                    // input features / 64
+  int tiles_m, tiles_n;
+  const float* bias;             // [n]
+  const __nv_bfloat16* residual; // [rows, n] or null
+  __nv_bfloat16* out;            // [rows, n]
+};
+
+cudaError_t enc_gemm_init();
+// Returns the number of kernel launches (1).
+int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const EncGemmArgs& a, int epilogue,
+                    int num_sms, cudaStream_t st);
+
+// Sets the thread's last-error string (qre_last_error) and returns `code`.
+int set_error(int code, const char* fmt, ...);
+// bf16 2-D K-major tensor map with the 128-byte swizzle the UMMA descriptors assume.
+int make_tensor_map_bf16(CUtensorMap* map, void* base, uint64_t inner, uint64_t rows, uint32_t box_inner,
+                         uint32_t box_rows);
+
+}  // namespace qre

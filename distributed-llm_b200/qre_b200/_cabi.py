@@ -33,6 +33,10 @@ EXPORTS = (
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
     "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
     "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
+    # include/qre_encoder_b200.h
+    "qre_encoder_create", "qre_encoder_destroy", "qre_encoder_set_embeddings", "qre_encoder_set_layer",
+    "qre_encode", "qre_encode_dev", "qre_encoder_launch_count", "qre_encoder_debug_gemm",
+    "qre_wordpiece_create", "qre_wordpiece_destroy", "qre_wordpiece_encode",
 )
 
 
@@ -403,3 +407,147 @@ def host_features(queries, context_lens, hp: HeurParams, n_threads: int = 0) -> 
     if rc != 0:
         raise QreError(f"qre_host_features failed with {rc}")
     return out
+
+
+# ---- include/qre_encoder_b200.h -----------------------------------------------------------------
+class EncoderConfig(C.Structure):
+    """qre_encoder_config_t; the defaults are all-MiniLM-L6-v2 (qre:125, 510)."""
+    _fields_ = [("vocab_size", C.c_int32), ("hidden", C.c_int32), ("layers", C.c_int32), ("heads", C.c_int32),
+                ("intermediate", C.c_int32), ("max_positions", C.c_int32), ("type_vocab", C.c_int32),
+                ("ln_eps", C.c_float), ("max_seq_len", C.c_int32), ("reserved", C.c_int32)]
+
+    def __init__(self, vocab_size=30522, hidden=384, layers=6, heads=12, intermediate=1536, max_positions=512,
+                 type_vocab=2, ln_eps=1e-12, max_seq_len=256):
+        super().__init__(vocab_size, hidden, layers, heads, intermediate, max_positions, type_vocab, ln_eps,
+                         max_seq_len, 0)
+
+
+_LAYER_FIELDS = ("wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo", "ln1_g", "ln1_b", "w1", "b1", "w2", "b2",
+                 "ln2_g", "ln2_b")
+_LAYER_KEYS = ("attention.self.query.weight", "attention.self.query.bias", "attention.self.key.weight",
+               "attention.self.key.bias", "attention.self.value.weight", "attention.self.value.bias",
+               "attention.output.dense.weight", "attention.output.dense.bias", "attention.output.LayerNorm.weight",
+               "attention.output.LayerNorm.bias", "intermediate.dense.weight", "intermediate.dense.bias",
+               "output.dense.weight", "output.dense.bias", "output.LayerNorm.weight", "output.LayerNorm.bias")
+
+
+class EncoderLayer(C.Structure):
+    _fields_ = [(f, C.c_void_p) for f in _LAYER_FIELDS]
+
+
+class Encoder:
+    """One on-GPU query embedder (qre_encoder_t).  Weights: a dict of float32 arrays under
+    transformers' `BertModel.state_dict()` names."""
+
+    def __init__(self, cfg: EncoderConfig, weights: dict, max_tokens: int = 1 << 18, max_seqs: int = 4096,
+                 device: int = 0):
+        self._lib = load()
+        self._h = C.c_void_p()
+        self.cfg, self.device, self.max_tokens, self.max_seqs = cfg, device, int(max_tokens), int(max_seqs)
+        _check(self._lib, self._lib.qre_encoder_create(C.c_int(device), C.byref(cfg), C.c_int64(max_tokens),
+                                                       C.c_int(max_seqs), C.byref(self._h)))
+        try:
+            self.set_weights(weights)
+        except Exception:
+            self.close()
+            raise
+
+    def set_weights(self, w: dict) -> None:
+        c, H, F = self.cfg, self.cfg.hidden, self.cfg.intermediate
+        g = lambda k, shape: _arr(w[k], np.float32, shape)   # noqa: E731
+        emb = [g("embeddings.word_embeddings.weight", (c.vocab_size, H)),
+               g("embeddings.position_embeddings.weight", (c.max_positions, H)),
+               g("embeddings.token_type_embeddings.weight", (c.type_vocab, H)),
+               g("embeddings.LayerNorm.weight", (H,)), g("embeddings.LayerNorm.bias", (H,))]
+        _check(self._lib, self._lib.qre_encoder_set_embeddings(self._h, *[_ptr(a) for a in emb]))
+        shapes = ((H, H), (H,), (H, H), (H,), (H, H), (H,), (H, H), (H,), (H,), (H,), (F, H), (F,), (H, F), (H,),
+                  (H,), (H,))
+        for l in range(c.layers):
+            arrs = [g(f"encoder.layer.{l}.{k}", sh) for k, sh in zip(_LAYER_KEYS, shapes)]
+            lay = EncoderLayer(*[a.__array_interface__["data"][0] for a in arrs])
+            _check(self._lib, self._lib.qre_encoder_set_layer(self._h, C.c_int(l), C.byref(lay)))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.qre_encoder_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def encode_ids(self, seqs, normalize: bool = True) -> np.ndarray:
+        """seqs: list of int id arrays -> float32 [m, hidden] (host in, host out)."""
+        m = len(seqs)
+        lens = np.fromiter((len(s) for s in seqs), np.int64, m)
+        off = np.zeros(m + 1, np.int32)
+        np.cumsum(lens, out=off[1:])
+        ids = (np.concatenate([np.asarray(s, np.int32) for s in seqs]) if m and off[-1] else np.zeros(0, np.int32))
+        return self.encode_packed(ids, off, normalize)
+
+    def encode_packed(self, ids: np.ndarray, offsets: np.ndarray, normalize: bool = True) -> np.ndarray:
+        ids, offsets = _arr(ids, np.int32), _arr(offsets, np.int32)
+        m = offsets.shape[0] - 1
+        out = np.empty((m, self.cfg.hidden), np.float32)
+        _check(self._lib, self._lib.qre_encode(self._h, C.c_int(m), _ptr(ids) if ids.size else None, _ptr(offsets),
+                                               C.c_int(int(normalize)), _ptr(out)))
+        return out
+
+    def encode_dev(self, m: int, ids_ptr: int, offsets_ptr: int, n_tokens: int, max_len: int, out_ptr: int,
+                   normalize: bool = True, stream: int = 0) -> None:
+        _check(self._lib, self._lib.qre_encode_dev(self._h, C.c_int(m), C.c_void_p(ids_ptr), C.c_void_p(offsets_ptr),
+                                                   C.c_int64(n_tokens), C.c_int(max_len), C.c_int(int(normalize)),
+                                                   C.c_void_p(out_ptr), C.c_void_p(stream)))
+
+    def launch_count(self) -> int:
+        n = C.c_int64()
+        _check(self._lib, self._lib.qre_encoder_launch_count(self._h, C.byref(n)))
+        return n.value
+
+
+def encoder_debug_gemm(a, w, bias, residual=None, epilogue: int = 0, device: int = 0) -> np.ndarray:
+    a, w, bias = _arr(a, np.float32), _arr(w, np.float32), _arr(bias, np.float32)
+    rows, k = a.shape
+    n = w.shape[0]
+    res = None if residual is None else _arr(residual, np.float32, (rows, n))
+    out = np.empty((rows, n), np.float32)
+    lib = load()
+    _check(lib, lib.qre_encoder_debug_gemm(C.c_int(device), C.c_int(rows), C.c_int(n), C.c_int(k), _ptr(a), _ptr(w),
+                                           _ptr(bias), _ptr(res), C.c_int(epilogue), _ptr(out)))
+    return out
+
+
+class WordPiece:
+    """Host-thread WordPiece (qre_wordpiece_t): ASCII texts only; others come back as None."""
+
+    def __init__(self, vocab_path: str, do_lower_case: bool = True):
+        self._lib = load()
+        self._h = C.c_void_p()
+        _check(self._lib, self._lib.qre_wordpiece_create(vocab_path.encode(), C.c_int(int(do_lower_case)),
+                                                         C.byref(self._h)))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.qre_wordpiece_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def encode(self, texts, max_len: int = 256, n_threads: int = 0):
+        """-> (ids int32 [total], lens int32 [n]); lens[i] == -1 marks a text this tokenizer declined."""
+        n = len(texts)
+        raw = [t.encode("utf-8") for t in texts]
+        arr = (C.c_char_p * n)(*raw)
+        tl = np.fromiter((len(b) for b in raw), np.int64, n)
+        cap = int(np.minimum(tl + 2, max_len).sum()) if n else 0
+        ids = np.empty(max(cap, 1), np.int32)
+        lens = np.empty(n, np.int32)
+        _check(self._lib, self._lib.qre_wordpiece_encode(self._h, C.c_int64(n), arr, _ptr(tl), C.c_int(max_len),
+                                                         _ptr(ids), C.c_int64(cap), _ptr(lens), C.c_int(n_threads)))
+        return ids[: int(lens[lens > 0].sum())], lens

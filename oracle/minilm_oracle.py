@@ -55,7 +55,10 @@ def _ln(x: np.ndarray, g: np.ndarray, b: np.ndarray, eps: float) -> np.ndarray:
     return ((x - mu) / np.sqrt(var + np.float32(eps))) * g + b
 
 
-_erf = np.vectorize(math.erf, otypes=[np.float64])
+try:                                   # scipy is only a faster erf; the values are the same
+    from scipy.special import erf as _erf
+except Exception:                      # pragma: no cover
+    _erf = np.vectorize(math.erf, otypes=[np.float64])
 
 
 def _gelu(x: np.ndarray) -> np.ndarray:

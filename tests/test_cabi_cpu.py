@@ -1,5 +1,5 @@
 """CPU-only checks of the drop-in boundary: the shared library loads without a GPU driver and
-exports every symbol include/qre_b200.h declares; with no device the product fails loudly."""
+exports every symbol include/*.h declares; with no device the product fails loudly."""
 import ctypes
 import os
 import re
@@ -13,7 +13,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _declared():
-    text = open(os.path.join(ROOT, "include", "qre_b200.h")).read()
+    inc = os.path.join(ROOT, "include")
+    text = "".join(open(os.path.join(inc, f)).read() for f in sorted(os.listdir(inc)) if f.endswith(".h"))
     return sorted(set(re.findall(r"QRE_API\s+(?:const\s+char\s*\*|int)\s+(qre_\w+)\s*\(", text)))
 
 
@@ -31,6 +32,28 @@ def test_struct_layout_matches_header():
     assert _cabi.CAND_DTYPE.itemsize == 32
     assert ctypes.sizeof(_cabi.Params) == 8 * 3 + 4 * 4 + 8 * 6 + 4 * 2
     assert ctypes.sizeof(_cabi.Result) == 8 * len(_cabi.RESULT_FIELDS)
+
+
+def test_encoder_structs_and_arguments():
+    assert ctypes.sizeof(_cabi.EncoderConfig) == 40
+    assert ctypes.sizeof(_cabi.EncoderLayer) == 16 * 8
+    lib = _cabi.load()
+    h = ctypes.c_void_p()
+    bad = _cabi.EncoderConfig(hidden=100)
+    assert lib.qre_encoder_create(0, ctypes.byref(bad), ctypes.c_int64(128), 4, ctypes.byref(h)) == 1
+    assert b"multiple of 64" in lib.qre_last_error()
+    bad = _cabi.EncoderConfig(heads=5)
+    assert lib.qre_encoder_create(0, ctypes.byref(bad), ctypes.c_int64(128), 4, ctypes.byref(h)) == 1
+    assert lib.qre_encoder_destroy(None) == 0
+    assert lib.qre_encoder_debug_gemm(0, 4, 30, 64, None, None, None, None, 0, None) == 1
+
+
+def test_encoder_without_device_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(_cabi.QreError, match="no CUDA device|cudaGetDeviceCount"):
+        _cabi.Encoder(_cabi.EncoderConfig(), {}, max_tokens=128, max_seqs=4)
 
 
 def test_no_device_fails_loudly():

@@ -72,22 +72,7 @@ def test_truncation_and_empty():
     assert not z.any()
 
 
-VOCAB = ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]", "hello", "world", "##s", "what", "is", "the", "un",
-         "##believ", "##able", "!", "?", ",", ".", "a", "b", "c", "##a", "##b", "##c", "cafe", "e", "##e",
-         "explain", "how", "to", "write", "code", "in", "python", "##ic", "-", "'", "don", "t", "1", "##2", "##3",
-         "(", ")", "new", "york", "##er", "x", "##x", "中", "文", "$", "def", "_", "foo", "##_", "##foo"]
-
-TEXTS = [
-    "Hello worlds! What is the unbelievable cafe abc?",
-    "  explain   how to write\tpythonic code\n in python... ",
-    "don't (new-yorker) 123 xxx $x",
-    "Café ÉE 中文abc",
-    "",
-    "zzzz unknownword hello",
-    "def foo_foo(a, b): x_x",
-    "a" * 120 + " hello",
-    "hello " * 40,
-]
+from tests.wordpiece_cases import TEXTS, VOCAB  # noqa: E402
 
 
 def test_wordpiece_restatement_equals_berttokenizer(tmp_path):

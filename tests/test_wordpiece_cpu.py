@@ -1,0 +1,84 @@
+"""The C++ host WordPiece (qre_wordpiece_encode) against the oracle restatement, which is itself pinned
+against transformers' BertTokenizer (tests/test_minilm_oracle_cpu.py).  No GPU involved."""
+import os
+import random
+
+import numpy as np
+
+from oracle import minilm_oracle as MO
+from qre_b200 import _cabi
+from tests.wordpiece_cases import TEXTS, VOCAB
+
+
+def _vocab_file(tmp_path):
+    vp = os.path.join(tmp_path, "vocab.txt")
+    with open(vp, "w", encoding="utf-8") as f:
+        f.write("\n".join(VOCAB) + "\n")
+    return vp, {t: i for i, t in enumerate(VOCAB)}
+
+
+def _split(ids, lens):
+    out, o = [], 0
+    for n in lens:
+        if n < 0:
+            out.append(None)
+        else:
+            out.append(ids[o:o + n].tolist())
+            o += n
+    assert o == ids.size
+    return out
+
+
+def test_fixed_texts(tmp_path):
+    vp, vocab = _vocab_file(tmp_path)
+    wp = _cabi.WordPiece(vp)
+    for max_len in (256, 16, 3, 2):
+        ids, lens = wp.encode(TEXTS, max_len=max_len)
+        got = _split(ids, lens)
+        for text, g in zip(TEXTS, got):
+            if any(ord(c) > 127 for c in text):
+                assert g is None
+            else:
+                assert g == MO.tokenize_ids(text, vocab, max_len).tolist(), (text, max_len)
+
+
+def test_random_ascii_texts_threaded(tmp_path):
+    vp, vocab = _vocab_file(tmp_path)
+    wp = _cabi.WordPiece(vp)
+    rnd = random.Random(7)
+    words = [v for v in VOCAB if v.isascii() and not v.startswith("[") and not v.startswith("##")]
+    glue = [" ", "  ", "\t", "", "-", "'", ", ", ". ", "\n", "\x01", "_"]
+    texts = []
+    for _ in range(3000):
+        n = rnd.randint(0, 30)
+        s = "".join(rnd.choice(words).upper() if rnd.random() < 0.2 else rnd.choice(words) + rnd.choice(glue)
+                    for _ in range(n))
+        if rnd.random() < 0.1:
+            s += rnd.choice(["zzz", "q" * 150, "helloworlds", "abcabc", "123", "x" * 99])
+        texts.append(s)
+    for threads in (1, 4):
+        ids, lens = wp.encode(texts, max_len=24, n_threads=threads)
+        got = _split(ids, lens)
+        for text, g in zip(texts, got):
+            assert g == MO.tokenize_ids(text, vocab, 24).tolist(), repr(text)
+    assert (lens >= 2).all()
+
+
+def test_errors(tmp_path):
+    import ctypes
+    import pytest
+    lib = _cabi.load()
+    with pytest.raises(_cabi.QreError, match="cannot open"):
+        _cabi.WordPiece(os.path.join(tmp_path, "missing.txt"))
+    bad = os.path.join(tmp_path, "bad.txt")
+    open(bad, "w").write("a\nb\n")
+    with pytest.raises(_cabi.QreError, match="lacks"):
+        _cabi.WordPiece(bad)
+    vp, _ = _vocab_file(tmp_path)
+    wp = _cabi.WordPiece(vp)
+    texts = (ctypes.c_char_p * 1)(b"hello world hello world")
+    lens = np.zeros(1, np.int32)
+    ids = np.zeros(2, np.int32)
+    rc = lib.qre_wordpiece_encode(wp._h, ctypes.c_int64(1), texts, None, 256, ids.ctypes.data_as(ctypes.c_void_p),
+                                  ctypes.c_int64(2), lens.ctypes.data_as(ctypes.c_void_p), 1)
+    assert rc == 3 and b"capacity" in lib.qre_last_error()
