@@ -122,6 +122,76 @@ enc_layernorm_kernel(const __nv_bfloat16* __restrict__ y, const float* __restric
   warp_layernorm_store<kPairsMax>(v, pairs, H, g, b, eps, x + t * H, lane);
 }
 
+// Same, for the common widths (H = 64 * kChunks): 8 lanes per token, four tokens per warp, 16-byte
+// loads and stores, so that enough bytes are in flight per SM to run at HBM speed.
+template <int kChunks>
+__global__ void __launch_bounds__(256)
+enc_layernorm_wide_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
+                          float eps, long long T, __nv_bfloat16* __restrict__ x) {
+  constexpr int H = 64 * kChunks;
+  const int lane = threadIdx.x & 31, gl = lane & 7;
+  const long long t = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4 + (lane >> 3);
+  const bool ok = t < T;
+  const __nv_bfloat16* yr = y + (ok ? t : 0) * H;
+  float v[kChunks][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i) {
+    const uint4 u = *reinterpret_cast<const uint4*>(yr + (i * 8 + gl) * 8);
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
+      v[i][2 * e] = f.x;
+      v[i][2 * e + 1] = f.y;
+      s += f.x + f.y;
+    }
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) s += __shfl_xor_sync(kFull, s, o);
+  const float mu = s / static_cast<float>(H);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float d = v[i][e] - mu;
+      q += d * d;
+    }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) q += __shfl_xor_sync(kFull, q, o);
+  const float rstd = rsqrtf(q / static_cast<float>(H) + eps);
+  if (!ok) return;
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i) {
+    const int c = (i * 8 + gl) * 8;
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(g + c)), g1 = __ldg(reinterpret_cast<const float4*>(g + c + 4));
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(b + c)), b1 = __ldg(reinterpret_cast<const float4*>(b + c + 4));
+    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    uint32_t w[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn((v[i][2 * e] - mu) * rstd * gg[2 * e] + bb[2 * e],
+                                                     (v[i][2 * e + 1] - mu) * rstd * gg[2 * e + 1] + bb[2 * e + 1]);
+      w[e] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(x + t * H + c) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+int launch_layernorm(const __nv_bfloat16* y, const float* g, const float* b, float eps, int H, long long T,
+                     __nv_bfloat16* x, cudaStream_t st) {
+  const int wide_grid = static_cast<int>((T + 31) / 32);      // 8 warps x 4 tokens per CTA
+  if (H == 384)
+    enc_layernorm_wide_kernel<6><<<wide_grid, 256, 0, st>>>(y, g, b, eps, T, x);
+  else if (H == 768)
+    enc_layernorm_wide_kernel<12><<<wide_grid, 256, 0, st>>>(y, g, b, eps, T, x);
+  else
+    enc_layernorm_kernel<<<static_cast<int>((T + 7) / 8), 256, 0, st>>>(y, g, b, eps, H, T, x);
+  return 1;
+}
+
 // ---- attention --------------------------------------------------------------------------------
 __device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -134,30 +204,17 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-// softmax(Q K^T / sqrt(HD)) V for one (sequence, head): the L keys and values are staged in
-// shared memory (K as [key][dim], V transposed to [dim][key], both padded against bank
-// conflicts); each warp owns 16 query rows at a time and walks the keys 16 at a time with an
-// online softmax, scores and probabilities never leaving registers (the accumulator layout of
-// one m16n8k16 product is the A-operand layout of the next).
+// ---- softmax(Q K^T / sqrt(HD)) V --------------------------------------------------------------
+// The L keys and values of one (sequence, head) are staged in shared memory (K as [key][dim], V
+// transposed to [dim][key], both padded against bank conflicts); a warp owns 16 query rows at a
+// time and walks the keys 16 at a time with an online softmax, scores and probabilities never
+// leaving registers (the accumulator layout of one m16n8k16 product is the A-operand layout of
+// the next).
 template <int HD>
-__global__ void __launch_bounds__(128)
-enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
-                     __nv_bfloat16* __restrict__ ctx, int H, int Lp, float scale_log2e) {
-  constexpr int KS = HD + 8;                 // Ks row stride (elements)
-  const int VS = Lp + 8;                     // Vt row stride (elements)
-  extern __shared__ __align__(16) uint8_t att_smem[];
-  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);
-  __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
-
-  const int seq = blockIdx.x, head = blockIdx.y;
-  const int t0 = offsets[seq];
-  const int L = min(offsets[seq + 1] - t0, Lp);
-  if (L <= 0) return;
-  const int Lk = (L + 15) & ~15;
-  const long long ld = 3LL * H;
-  const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
-
-  for (int idx = threadIdx.x; idx < Lk * (HD / 8); idx += blockDim.x) {
+__device__ __forceinline__ void stage_kv(__nv_bfloat16* Ks, __nv_bfloat16* Vt, int VS, const __nv_bfloat16* base,
+                                         long long ld, int H, int L, int Lk, int tid, int nthreads) {
+  constexpr int KS = HD + 8;
+  for (int idx = tid; idx < Lk * (HD / 8); idx += nthreads) {
     const int key = idx / (HD / 8), part = idx - key * (HD / 8);
     uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
     if (key < L) {
@@ -169,96 +226,155 @@ enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __res
 #pragma unroll
     for (int j = 0; j < 8; ++j) Vt[(part * 8 + j) * VS + key] = ve[j];
   }
-  __syncthreads();
+}
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+// One 16-row query block [16 * qb, +16) of one head; `base` points at the sequence's first token,
+// this head's Q columns; `out` at the same position of the context buffer.
+template <int HD>
+__device__ __forceinline__ void attend_block(const __nv_bfloat16* Ks, const __nv_bfloat16* Vt, int VS,
+                                             const __nv_bfloat16* base, long long ld, int L, int Lk, int qb,
+                                             __nv_bfloat16* out, int H, float scale_log2e, int lane) {
+  constexpr int KS = HD + 8;
   const int g = lane >> 2, t = lane & 3;
   const float ninf = __int_as_float(0xff800000);
+  const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
+  uint32_t qa[HD / 16][4];
+#pragma unroll
+  for (int kk = 0; kk < HD / 16; ++kk) {
+    const int c = kk * 16 + 2 * t;
+    qa[kk][0] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c) : 0u;
+    qa[kk][1] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c) : 0u;
+    qa[kk][2] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c + 8) : 0u;
+    qa[kk][3] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c + 8) : 0u;
+  }
+  float o[HD / 8][4];
+#pragma unroll
+  for (int nd = 0; nd < HD / 8; ++nd) o[nd][0] = o[nd][1] = o[nd][2] = o[nd][3] = 0.f;
+  float m_lo = ninf, m_hi = ninf, l_lo = 0.f, l_hi = 0.f;
 
-  for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5) {
-    const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
-    uint32_t qa[HD / 16][4];
+  for (int k0 = 0; k0 < Lk; k0 += 16) {
+    float s[2][4];
 #pragma unroll
-    for (int kk = 0; kk < HD / 16; ++kk) {
-      const int c = kk * 16 + 2 * t;
-      qa[kk][0] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c) : 0u;
-      qa[kk][1] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c) : 0u;
-      qa[kk][2] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c + 8) : 0u;
-      qa[kk][3] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c + 8) : 0u;
+    for (int j = 0; j < 2; ++j) {
+      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+      const __nv_bfloat16* kr = Ks + (k0 + j * 8 + g) * KS + 2 * t;
+#pragma unroll
+      for (int kk = 0; kk < HD / 16; ++kk)
+        mma_16816(s[j], qa[kk], *reinterpret_cast<const uint32_t*>(kr + kk * 16),
+                  *reinterpret_cast<const uint32_t*>(kr + kk * 16 + 8));
     }
-    float o[HD / 8][4];
+    // scale into the log2 domain and mask the padded keys
 #pragma unroll
-    for (int nd = 0; nd < HD / 8; ++nd) o[nd][0] = o[nd][1] = o[nd][2] = o[nd][3] = 0.f;
-    float m_lo = ninf, m_hi = ninf, l_lo = 0.f, l_hi = 0.f;
-
-    for (int k0 = 0; k0 < Lk; k0 += 16) {
-      float s[2][4];
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
-        const __nv_bfloat16* kr = Ks + (k0 + j * 8 + g) * KS + 2 * t;
-#pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk)
-          mma_16816(s[j], qa[kk], *reinterpret_cast<const uint32_t*>(kr + kk * 16),
-                    *reinterpret_cast<const uint32_t*>(kr + kk * 16 + 8));
-      }
-      // scale into the log2 domain and mask the padded keys
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const int key = k0 + j * 8 + 2 * t;
-        s[j][0] = key < L ? s[j][0] * scale_log2e : ninf;
-        s[j][2] = key < L ? s[j][2] * scale_log2e : ninf;
-        s[j][1] = key + 1 < L ? s[j][1] * scale_log2e : ninf;
-        s[j][3] = key + 1 < L ? s[j][3] * scale_log2e : ninf;
-      }
-      float bm_lo = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
-      float bm_hi = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
-      bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 1));
-      bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 2));
-      bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 1));
-      bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 2));
-      const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);   // finite: key k0 < L is in every block
-      const float c_lo = exp2f(m_lo - mn_lo), c_hi = exp2f(m_hi - mn_hi);
-      m_lo = mn_lo;
-      m_hi = mn_hi;
-      float p[2][4];
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        p[j][0] = exp2f(s[j][0] - mn_lo);
-        p[j][1] = exp2f(s[j][1] - mn_lo);
-        p[j][2] = exp2f(s[j][2] - mn_hi);
-        p[j][3] = exp2f(s[j][3] - mn_hi);
-      }
-      l_lo = l_lo * c_lo + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
-      l_hi = l_hi * c_hi + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
-      const uint32_t pa[4] = {pack_bf16(p[0][0], p[0][1]), pack_bf16(p[0][2], p[0][3]), pack_bf16(p[1][0], p[1][1]),
-                              pack_bf16(p[1][2], p[1][3])};
-#pragma unroll
-      for (int nd = 0; nd < HD / 8; ++nd) {
-        o[nd][0] *= c_lo;
-        o[nd][1] *= c_lo;
-        o[nd][2] *= c_hi;
-        o[nd][3] *= c_hi;
-        const __nv_bfloat16* vr = Vt + (nd * 8 + g) * VS + k0 + 2 * t;
-        mma_16816(o[nd], pa, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
-      }
+    for (int j = 0; j < 2; ++j) {
+      const int key = k0 + j * 8 + 2 * t;
+      s[j][0] = key < L ? s[j][0] * scale_log2e : ninf;
+      s[j][2] = key < L ? s[j][2] * scale_log2e : ninf;
+      s[j][1] = key + 1 < L ? s[j][1] * scale_log2e : ninf;
+      s[j][3] = key + 1 < L ? s[j][3] * scale_log2e : ninf;
     }
-    l_lo += __shfl_xor_sync(kFull, l_lo, 1);
-    l_lo += __shfl_xor_sync(kFull, l_lo, 2);
-    l_hi += __shfl_xor_sync(kFull, l_hi, 1);
-    l_hi += __shfl_xor_sync(kFull, l_hi, 2);
-    const float i_lo = 1.f / l_lo, i_hi = 1.f / l_hi;
-    __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD + 2 * t;
+    float bm_lo = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+    float bm_hi = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+    bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 1));
+    bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 2));
+    bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 1));
+    bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 2));
+    const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);   // finite: key k0 < L is in every block
+    const float c_lo = exp2f(m_lo - mn_lo), c_hi = exp2f(m_hi - mn_hi);
+    m_lo = mn_lo;
+    m_hi = mn_hi;
+    float p[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      p[j][0] = exp2f(s[j][0] - mn_lo);
+      p[j][1] = exp2f(s[j][1] - mn_lo);
+      p[j][2] = exp2f(s[j][2] - mn_hi);
+      p[j][3] = exp2f(s[j][3] - mn_hi);
+    }
+    l_lo = l_lo * c_lo + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
+    l_hi = l_hi * c_hi + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
+    const uint32_t pa[4] = {pack_bf16(p[0][0], p[0][1]), pack_bf16(p[0][2], p[0][3]), pack_bf16(p[1][0], p[1][1]),
+                            pack_bf16(p[1][2], p[1][3])};
 #pragma unroll
     for (int nd = 0; nd < HD / 8; ++nd) {
-      if (r_lo < L)
-        *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_lo) * H + nd * 8) =
-            __floats2bfloat162_rn(o[nd][0] * i_lo, o[nd][1] * i_lo);
-      if (r_hi < L)
-        *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_hi) * H + nd * 8) =
-            __floats2bfloat162_rn(o[nd][2] * i_hi, o[nd][3] * i_hi);
+      o[nd][0] *= c_lo;
+      o[nd][1] *= c_lo;
+      o[nd][2] *= c_hi;
+      o[nd][3] *= c_hi;
+      const __nv_bfloat16* vr = Vt + (nd * 8 + g) * VS + k0 + 2 * t;
+      mma_16816(o[nd], pa, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
     }
   }
+  l_lo += __shfl_xor_sync(kFull, l_lo, 1);
+  l_lo += __shfl_xor_sync(kFull, l_lo, 2);
+  l_hi += __shfl_xor_sync(kFull, l_hi, 1);
+  l_hi += __shfl_xor_sync(kFull, l_hi, 2);
+  const float i_lo = 1.f / l_lo, i_hi = 1.f / l_hi;
+  out += 2 * t;
+#pragma unroll
+  for (int nd = 0; nd < HD / 8; ++nd) {
+    if (r_lo < L)
+      *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_lo) * H + nd * 8) =
+          __floats2bfloat162_rn(o[nd][0] * i_lo, o[nd][1] * i_lo);
+    if (r_hi < L)
+      *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_hi) * H + nd * 8) =
+          __floats2bfloat162_rn(o[nd][2] * i_hi, o[nd][3] * i_hi);
+  }
+}
+
+constexpr int kShortLen = 64;     // sequences up to this long take the warp-per-head kernel
+
+// Long sequences (kShortLen < L): one CTA per (sequence, head), its four warps share the staged
+// K/V and split the query blocks.  `min_len`: sequences of at most this length are skipped (they
+// belong to the short kernel).
+template <int HD>
+__global__ void __launch_bounds__(128)
+enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
+                     __nv_bfloat16* __restrict__ ctx, int H, int Lp, int min_len, float scale_log2e) {
+  constexpr int KS = HD + 8;
+  const int VS = Lp + 8;
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);
+  __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
+  const int seq = blockIdx.x, head = blockIdx.y;
+  const int t0 = offsets[seq];
+  const int L = min(offsets[seq + 1] - t0, Lp);
+  if (L <= min_len) return;
+  const int Lk = (L + 15) & ~15;
+  const long long ld = 3LL * H;
+  const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
+  stage_kv<HD>(Ks, Vt, VS, base, ld, H, L, Lk, threadIdx.x, blockDim.x);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD;
+  for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5)
+    attend_block<HD>(Ks, Vt, VS, base, ld, L, Lk, qb, out, H, scale_log2e, lane);
+}
+
+// Short sequences (0 < L <= kShortLen, the bulk of chat queries): one WARP per (sequence, head),
+// four heads of the same sequence per CTA.  Each warp stages its own head's K/V in a private
+// slice of shared memory and runs all of the head's query blocks; warps never wait for each other.
+template <int HD>
+__global__ void __launch_bounds__(128)
+enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
+                           __nv_bfloat16* __restrict__ ctx, int H, int heads, int Lp, float scale_log2e) {
+  constexpr int KS = HD + 8;
+  const int VS = Lp + 8;
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const size_t per_warp = static_cast<size_t>(Lp) * KS + static_cast<size_t>(HD) * VS;   // elements; a multiple of 8
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem) + warp * per_warp;
+  __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
+  const int seq = blockIdx.x, head = blockIdx.y * 4 + warp;
+  const int t0 = offsets[seq];
+  const int L = offsets[seq + 1] - t0;
+  if (L <= 0 || L > Lp || head >= heads) return;
+  const int Lk = (L + 15) & ~15;
+  const long long ld = 3LL * H;
+  const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
+  stage_kv<HD>(Ks, Vt, VS, base, ld, H, L, Lk, lane, 32);
+  __syncwarp();
+  __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD;
+  for (int qb = 0; qb * 16 < L; ++qb) attend_block<HD>(Ks, Vt, VS, base, ld, L, Lk, qb, out, H, scale_log2e, lane);
 }
 
 // Pooling(mean over the sequence's tokens) + Normalize (x / max(|x|, 1e-12)); one CTA per sequence.
@@ -330,7 +446,8 @@ struct qre_encoder {
   float *word = nullptr, *pos = nullptr, *type = nullptr, *eln_g = nullptr, *eln_b = nullptr;
   std::vector<Layer> layers;
   __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *h = nullptr;
-  CUtensorMap map_x, map_ctx, map_h;
+  CUtensorMap map_x, map_ctx, map_h;                       // A operands (128-token boxes)
+  CUtensorMap box_qkv, box_y, box_h, box_x;                // epilogue boxes: outputs qkv / y / h, residual x
   int32_t *d_ids = nullptr, *d_off = nullptr;
   float* d_out = nullptr;
   int32_t *h_ids = nullptr, *h_off = nullptr;     // pinned staging of the host entry point
@@ -395,31 +512,43 @@ void free_linear(Linear& L) {
   L.b = nullptr;
 }
 
-int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_t T, const __nv_bfloat16* residual,
-               __nv_bfloat16* out, int epi, cudaStream_t st) {
+int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_t T, const CUtensorMap& box_out,
+               const CUtensorMap* box_res, int epi, cudaStream_t st) {
   EncGemmArgs a;
-  a.rows = static_cast<int>(T);
-  a.n = L.n;
   a.num_kb = L.k / kEncBK;
   a.tiles_m = static_cast<int>((T + kEncBM - 1) / kEncBM);
   a.tiles_n = (L.n + kEncBN - 1) / kEncBN;
   a.bias = L.b;
-  a.residual = residual;
-  a.out = out;
-  return launch_enc_gemm(map_a, L.map, a, epi, e->num_sms, st);
+  return launch_enc_gemm(map_a, L.map, box_out, box_res, a, epi, e->num_sms, st);
 }
 
+size_t attention_short_smem(int hd, int Lp) { return 4 * attention_smem(hd, Lp); }
+
 int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len, cudaStream_t st) {
-  const int Lp = (max_len + 15) & ~15;
   const int H = e->cfg.hidden;
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(e->hd));
-  const dim3 grid(m, e->cfg.heads);
-  const size_t smem = attention_smem(e->hd, Lp);
+  int n = 0;
+  // sequences of up to kShortLen tokens: warp per head
+  const int Ls = ((max_len < kShortLen ? max_len : kShortLen) + 15) & ~15;
+  const dim3 grid_s(m, (e->cfg.heads + 3) / 4);
   if (e->hd == 32)
-    enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, scale_log2e);
+    enc_attention_short_kernel<32><<<grid_s, 128, attention_short_smem(32, Ls), st>>>(e->qkv, offsets, e->ctx, H,
+                                                                                      e->cfg.heads, Ls, scale_log2e);
   else
-    enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, scale_log2e);
-  return 1;
+    enc_attention_short_kernel<64><<<grid_s, 128, attention_short_smem(64, Ls), st>>>(e->qkv, offsets, e->ctx, H,
+                                                                                      e->cfg.heads, Ls, scale_log2e);
+  ++n;
+  if (max_len > kShortLen) {   // the batch has longer sequences: CTA per (sequence, head) for those
+    const int Lp = (max_len + 15) & ~15;
+    const dim3 grid(m, e->cfg.heads);
+    const size_t smem = attention_smem(e->hd, Lp);
+    if (e->hd == 32)
+      enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, kShortLen, scale_log2e);
+    else
+      enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, kShortLen, scale_log2e);
+    ++n;
+  }
+  return n;
 }
 
 // The whole forward pass for m packed sequences already on the device.
@@ -431,17 +560,15 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
     enc_embed_ln_kernel<<<m, 256, 0, st>>>(ids, offsets, e->word, e->pos, e->type, e->eln_g, e->eln_b, c.ln_eps, H,
                                            c.vocab_size, e->x);
     ++e->launches;
-    const int ln_grid = static_cast<int>((T + 7) / 8);
     for (int l = 0; l < c.layers; ++l) {
       Layer& L = e->layers[l];
-      e->launches += run_linear(e, e->map_x, L.qkv, T, nullptr, e->qkv, kEpiBias, st);
+      e->launches += run_linear(e, e->map_x, L.qkv, T, e->box_qkv, nullptr, kEpiBias, st);
       e->launches += launch_attention(e, m, offsets, max_len, st);
-      e->launches += run_linear(e, e->map_ctx, L.out, T, e->x, e->y, kEpiResidual, st);
-      enc_layernorm_kernel<<<ln_grid, 256, 0, st>>>(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x);
-      e->launches += run_linear(e, e->map_x, L.up, T, nullptr, e->h, kEpiGelu, st);
-      e->launches += run_linear(e, e->map_h, L.down, T, e->x, e->y, kEpiResidual, st);
-      enc_layernorm_kernel<<<ln_grid, 256, 0, st>>>(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x);
-      e->launches += 2;
+      e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_y, &e->box_x, kEpiResidual, st);
+      e->launches += launch_layernorm(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x, st);
+      e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
+      e->launches += run_linear(e, e->map_h, L.down, T, e->box_y, &e->box_x, kEpiResidual, st);
+      e->launches += launch_layernorm(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x, st);
     }
   }
   enc_pool_kernel<<<m, 128, 0, st>>>(e->x, offsets, H, normalize, out);
@@ -536,6 +663,13 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   } while (0)
   ENC_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   ENC_TRY(enc_gemm_init());
+  const size_t att_s = attention_short_smem(e->hd, kShortLen);
+  if (att_s > 48 * 1024) {
+    if (e->hd == 32)
+      ENC_TRY(cudaFuncSetAttribute(enc_attention_short_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_s));
+    else
+      ENC_TRY(cudaFuncSetAttribute(enc_attention_short_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_s));
+  }
   const size_t att = attention_smem(e->hd, (c.max_seq_len + 15) & ~15);
   if (att > 48 * 1024) {
     if (e->hd == 32)
@@ -564,6 +698,10 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   int rc = make_tensor_map_bf16(&e->map_x, e->x, H, T, kEncBK, kEncBM);
   if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->map_ctx, e->ctx, H, T, kEncBK, kEncBM);
   if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->map_h, e->h, F, T, kEncBK, kEncBM);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->box_qkv, e->qkv, 3 * H, T, kEncBoxCols, kEncBoxRows);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->box_y, e->y, H, T, kEncBoxCols, kEncBoxRows);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->box_h, e->h, F, T, kEncBoxCols, kEncBoxRows);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&e->box_x, e->x, H, T, kEncBoxCols, kEncBoxRows);
   if (rc != QRE_OK) return fail_free(rc);
   *out = e;
   return QRE_OK;
@@ -671,8 +809,8 @@ int qre_encoder_launch_count(const qre_encoder_t* e, int64_t* count) {
 
 int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, const float* w, const float* bias,
                            const float* residual, int epilogue, float* c) {
-  if (rows <= 0 || n <= 0 || k <= 0 || n % 32 != 0 || k % 64 != 0)
-    return set_error(QRE_ERR_INVALID, "debug_gemm: need rows > 0, n %% 32 == 0, k %% 64 == 0");
+  if (rows <= 0 || n <= 0 || k <= 0 || n % 8 != 0 || k % 64 != 0)
+    return set_error(QRE_ERR_INVALID, "debug_gemm: need rows > 0, n %% 8 == 0, k %% 64 == 0");
   if (a == nullptr || w == nullptr || bias == nullptr || c == nullptr || (epilogue == kEpiResidual && residual == nullptr))
     return set_error(QRE_ERR_INVALID, "null argument");
   if (epilogue < 0 || epilogue > 2) return set_error(QRE_ERR_INVALID, "debug_gemm: epilogue must be 0, 1 or 2");
@@ -683,11 +821,11 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   ENC_CUDA(enc_gemm_init());
   const size_t rows_pad = round_up(rows, kEncBM), n_pad = round_up(n, kEncBN);
   std::vector<__nv_bfloat16> ab(rows_pad * k, __float2bfloat16(0.f)), wb(n_pad * k, __float2bfloat16(0.f)),
-      rb(static_cast<size_t>(rows) * n), cb(static_cast<size_t>(rows) * n);
+      rb(rows_pad * n, __float2bfloat16(0.f)), cb(rows_pad * n);
   for (size_t i = 0; i < static_cast<size_t>(rows) * k; ++i) ab[i] = __float2bfloat16(a[i]);
   for (size_t i = 0; i < static_cast<size_t>(n) * k; ++i) wb[i] = __float2bfloat16(w[i]);
   if (residual != nullptr)
-    for (size_t i = 0; i < rb.size(); ++i) rb[i] = __float2bfloat16(residual[i]);
+    for (size_t i = 0; i < static_cast<size_t>(rows) * n; ++i) rb[i] = __float2bfloat16(residual[i]);
   __nv_bfloat16 *da = nullptr, *dw = nullptr, *dr = nullptr, *dc = nullptr;
   float* db = nullptr;
   int rc = QRE_OK;
@@ -716,29 +854,27 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   DBG_TRY(cudaMemcpy(dw, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
   DBG_TRY(cudaMemcpy(dr, rb.data(), rb.size() * 2, cudaMemcpyHostToDevice));
   DBG_TRY(cudaMemcpy(db, bias, n * sizeof(float), cudaMemcpyHostToDevice));
-  CUtensorMap ma, mw;
+  CUtensorMap ma, mw, mo, mr;
   rc = make_tensor_map_bf16(&ma, da, k, rows_pad, kEncBK, kEncBM);
   if (rc == QRE_OK) rc = make_tensor_map_bf16(&mw, dw, k, n_pad, kEncBK, kEncBN);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&mo, dc, n, rows_pad, kEncBoxCols, kEncBoxRows);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&mr, dr, n, rows_pad, kEncBoxCols, kEncBoxRows);
   if (rc != QRE_OK) {
     cleanup();
     return rc;
   }
   EncGemmArgs g;
-  g.rows = rows;
-  g.n = n;
   g.num_kb = k / kEncBK;
   g.tiles_m = static_cast<int>(rows_pad / kEncBM);
   g.tiles_n = static_cast<int>(n_pad / kEncBN);
   g.bias = db;
-  g.residual = dr;
-  g.out = dc;
-  launch_enc_gemm(ma, mw, g, epilogue, prop.multiProcessorCount, nullptr);
+  launch_enc_gemm(ma, mw, mo, &mr, g, epilogue, prop.multiProcessorCount, nullptr);
   DBG_TRY(cudaGetLastError());
   DBG_TRY(cudaDeviceSynchronize());
   DBG_TRY(cudaMemcpy(cb.data(), dc, cb.size() * 2, cudaMemcpyDeviceToHost));
 #undef DBG_TRY
   cleanup();
-  for (size_t i = 0; i < cb.size(); ++i) c[i] = __bfloat162float(cb[i]);
+  for (size_t i = 0; i < static_cast<size_t>(rows) * n; ++i) c[i] = __bfloat162float(cb[i]);
   return QRE_OK;
 }
 

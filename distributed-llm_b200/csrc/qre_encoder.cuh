@@ -15,24 +15,26 @@ namespace qre {
 constexpr int kEncBM = 128;
 constexpr int kEncBN = 192;
 constexpr int kEncBK = 64;
-constexpr int kEncStages = 5;
+constexpr int kEncStages = 4;
 
 enum EncEpilogue { kEpiBias = 0, kEpiGelu = 1, kEpiResidual = 2 };
 
 struct EncGemmArgs {
-  int rows;                      // tokens
-  int n;                         // output features (multiple of 32)
   int num_kb;                    // input features / 64
-  int tiles_m, tiles_n;
-  const float* bias;             // [n]
-  const __nv_bfloat16* residual; // [rows, n] or null
-  __nv_bfloat16* out;            // [rows, n]
+  int tiles_m, tiles_n;          // ceil(tokens / 128), ceil(features / 192)
+  const float* bias;             // [tiles_n * 192], zero padded
 };
+// Output / residual boxes of the GEMM epilogue: 32 tokens x 64 features, 128-byte swizzle.
+constexpr int kEncBoxRows = 32;
+constexpr int kEncBoxCols = 64;
 
 cudaError_t enc_gemm_init();
 // Returns the number of kernel launches (1).
-int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const EncGemmArgs& a, int epilogue,
-                    int num_sms, cudaStream_t st);
+// tmap_out / tmap_res: [tokens padded to 128, features] bf16 with the kEncBox box; tmap_res may be null
+// unless epilogue == kEpiResidual.  Rows past the batch's tokens are computed and stored like any
+// other (the buffers are padded); features past the tensor's width are clipped by the TMA unit.
+int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const CUtensorMap& tmap_out,
+                    const CUtensorMap* tmap_res, const EncGemmArgs& a, int epilogue, int num_sms, cudaStream_t st);
 
 // Sets the thread's last-error string (qre_last_error) and returns `code`.
 int set_error(int code, const char* fmt, ...);

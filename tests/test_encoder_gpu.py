@@ -30,7 +30,8 @@ def _gelu(x):
 
 
 @pytest.mark.parametrize("rows,n,k", [(1, 192, 64), (100, 384, 384), (128, 1152, 384), (300, 1536, 384),
-                                      (257, 384, 1536), (129, 96, 128), (500, 64, 64), (64, 800, 256)])
+                                      (257, 384, 1536), (129, 96, 128), (500, 64, 64), (64, 800, 256),
+                                      (40, 72, 64), (20000, 384, 384)])
 @pytest.mark.parametrize("epi", [0, 1, 2])
 def test_gemm_hook_matches_numpy(rows, n, k, epi):
     from qre_b200 import _cabi
@@ -91,6 +92,17 @@ def test_small_encoder_head_dim_64():
     c = _cabi.EncoderConfig(300, 128, 3, 2, 192, 128, 2, 1e-12, 100)
     lens = [3, 100, 64, 65, 1, 18]
     got, want = _check(o, c, lens, seed=4)
+    _assert_close(got, want, lens)
+
+
+def test_bert_base_width_head_dim_64():
+    """hidden 768 / 12 heads / FFN 3072 (all-mpnet-base / BERT-base widths), two layers."""
+    from qre_b200 import _cabi
+    o = MO.EncoderConfig(vocab_size=1000, hidden=768, layers=2, heads=12, intermediate=3072, max_positions=128,
+                         max_seq_len=128)
+    c = _cabi.EncoderConfig(1000, 768, 2, 12, 3072, 128, 2, 1e-12, 128)
+    lens = [5, 64, 65, 128, 17, 1, 90]
+    got, want = _check(o, c, lens, seed=8)
     _assert_close(got, want, lens)
 
 
