@@ -323,31 +323,45 @@ __device__ __forceinline__ void attend_block(const __nv_bfloat16* Ks, const __nv
 
 constexpr int kShortLen = 64;     // sequences up to this long take the warp-per-head kernel
 
-// Long sequences (kShortLen < L): one CTA per (sequence, head), its four warps share the staged
-// K/V and split the query blocks.  `min_len`: sequences of at most this length are skipped (they
-// belong to the short kernel).
+// Long sequences (kShortLen < L): one CTA per (sequence, head) at a time, its four warps share the
+// staged K/V and split the query blocks.  The sequences come from `long_list` (built once per batch by
+// enc_find_long_kernel; *n_long entries), walked with a grid stride so the launch stays small however
+// few long sequences there are.
 template <int HD>
 __global__ void __launch_bounds__(128)
 enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
-                     __nv_bfloat16* __restrict__ ctx, int H, int Lp, int min_len, float scale_log2e) {
+                     const int32_t* __restrict__ long_list, const int32_t* __restrict__ n_long,
+                     __nv_bfloat16* __restrict__ ctx, int H, int Lp, float scale_log2e) {
   constexpr int KS = HD + 8;
   const int VS = Lp + 8;
   extern __shared__ __align__(16) uint8_t att_smem[];
   __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);
   __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
-  const int seq = blockIdx.x, head = blockIdx.y;
-  const int t0 = offsets[seq];
-  const int L = min(offsets[seq + 1] - t0, Lp);
-  if (L <= min_len) return;
-  const int Lk = (L + 15) & ~15;
-  const long long ld = 3LL * H;
-  const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
-  stage_kv<HD>(Ks, Vt, VS, base, ld, H, L, Lk, threadIdx.x, blockDim.x);
-  __syncthreads();
+  const int head = blockIdx.y, n = *n_long;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD;
-  for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5)
-    attend_block<HD>(Ks, Vt, VS, base, ld, L, Lk, qb, out, H, scale_log2e, lane);
+  const long long ld = 3LL * H;
+  for (int i = blockIdx.x; i < n; i += gridDim.x) {
+    const int seq = long_list[i];
+    const int t0 = offsets[seq];
+    const int L = min(offsets[seq + 1] - t0, Lp);
+    const int Lk = (L + 15) & ~15;
+    const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
+    __syncthreads();                       // previous sequence's K/V no longer read
+    stage_kv<HD>(Ks, Vt, VS, base, ld, H, L, Lk, threadIdx.x, blockDim.x);
+    __syncthreads();
+    __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD;
+    for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5)
+      attend_block<HD>(Ks, Vt, VS, base, ld, L, Lk, qb, out, H, scale_log2e, lane);
+  }
+}
+
+// Appends the indices of sequences longer than `min_len` to long_list (order irrelevant: every
+// sequence is computed independently).  *n_long must be zero on entry.
+__global__ void __launch_bounds__(256)
+enc_find_long_kernel(const int32_t* __restrict__ offsets, int m, int min_len, int32_t* __restrict__ long_list,
+                     int32_t* __restrict__ n_long) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < m && offsets[i + 1] - offsets[i] > min_len) long_list[atomicAdd(n_long, 1)] = i;
 }
 
 // Short sequences (0 < L <= kShortLen, the bulk of chat queries): one WARP per (sequence, head),
@@ -449,6 +463,7 @@ struct qre_encoder {
   CUtensorMap map_x, map_ctx, map_h;                       // A operands (128-token boxes)
   CUtensorMap box_qkv, box_y, box_h, box_x;                // epilogue boxes: outputs qkv / y / h, residual x
   int32_t *d_ids = nullptr, *d_off = nullptr;
+  int32_t *long_list = nullptr, *n_long = nullptr;   // sequences longer than kShortLen in the current batch
   float* d_out = nullptr;
   int32_t *h_ids = nullptr, *h_off = nullptr;     // pinned staging of the host entry point
   float* h_out = nullptr;
@@ -538,14 +553,20 @@ int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len,
     enc_attention_short_kernel<64><<<grid_s, 128, attention_short_smem(64, Ls), st>>>(e->qkv, offsets, e->ctx, H,
                                                                                       e->cfg.heads, Ls, scale_log2e);
   ++n;
-  if (max_len > kShortLen) {   // the batch has longer sequences: CTA per (sequence, head) for those
+  if (max_len > kShortLen) {   // the batch has longer sequences (listed in e->long_list by encode_on_device)
     const int Lp = (max_len + 15) & ~15;
-    const dim3 grid(m, e->cfg.heads);
     const size_t smem = attention_smem(e->hd, Lp);
+    int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
+    per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+    int gx = (e->num_sms * per_sm + e->cfg.heads - 1) / e->cfg.heads;
+    gx = gx < 1 ? 1 : (gx > m ? m : gx);
+    const dim3 grid(gx, e->cfg.heads);
     if (e->hd == 32)
-      enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, kShortLen, scale_log2e);
+      enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, e->long_list, e->n_long, e->ctx, H, Lp,
+                                                        scale_log2e);
     else
-      enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, e->ctx, H, Lp, kShortLen, scale_log2e);
+      enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, e->long_list, e->n_long, e->ctx, H, Lp,
+                                                        scale_log2e);
     ++n;
   }
   return n;
@@ -557,6 +578,11 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
   const qre_encoder_config_t& c = e->cfg;
   const int H = c.hidden;
   if (T > 0) {
+    if (max_len > kShortLen) {
+      ENC_CUDA(cudaMemsetAsync(e->n_long, 0, sizeof(int32_t), st));
+      enc_find_long_kernel<<<(m + 255) / 256, 256, 0, st>>>(offsets, m, kShortLen, e->long_list, e->n_long);
+      ++e->launches;
+    }
     enc_embed_ln_kernel<<<m, 256, 0, st>>>(ids, offsets, e->word, e->pos, e->type, e->eln_g, e->eln_b, c.ln_eps, H,
                                            c.vocab_size, e->x);
     ++e->launches;
@@ -600,6 +626,8 @@ void destroy(qre_encoder* e) {
   for (__nv_bfloat16* p : {e->x, e->qkv, e->ctx, e->y, e->h}) cudaFree(p);
   cudaFree(e->d_ids);
   cudaFree(e->d_off);
+  cudaFree(e->long_list);
+  cudaFree(e->n_long);
   cudaFreeHost(e->h_ids);
   cudaFreeHost(e->h_off);
   cudaFreeHost(e->h_out);
@@ -691,6 +719,8 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   ENC_TRY(cudaMalloc(&e->d_ids, sizeof(int32_t) * max_tokens));
   ENC_TRY(cudaMalloc(&e->d_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
   ENC_TRY(cudaMalloc(&e->d_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
+  ENC_TRY(cudaMalloc(&e->long_list, sizeof(int32_t) * static_cast<size_t>(max_seqs)));
+  ENC_TRY(cudaMalloc(&e->n_long, sizeof(int32_t)));
   ENC_TRY(cudaMallocHost(&e->h_ids, sizeof(int32_t) * max_tokens));
   ENC_TRY(cudaMallocHost(&e->h_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
   ENC_TRY(cudaMallocHost(&e->h_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
