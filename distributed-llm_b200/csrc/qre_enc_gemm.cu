@@ -3,20 +3,28 @@
 // for the four projections of a BERT layer (QKV, attention output, FFN up, FFN down), which the
 // reference reaches through SentenceTransformer.encode (src/query_router_engine.py:181, 571).
 //
-//   * tokens are the M operand: 128 per tile, one TMEM lane per token;
+//   * tokens are the M operand, one TMEM lane per token; a cluster of two CTAs (one TPC) works on
+//     256 tokens x 192 features per tile with ONE tcgen05.mma.cta_group::2 (M = 256): each CTA
+//     streams its own 128 tokens of x and only HALF of the weight tile (96 rows).  The single-CTA
+//     form of this kernel ran at the L2->SM limit (ncu: 1.1 GB of L2 reads per QKV projection,
+//     11.5 TB/s), not at the tensor pipe's; pairing removes 30 % of that traffic;
 //   * W is in torch.nn.Linear layout [out, in] = K-major, exactly what the UMMA B operand wants:
 //     no transposition anywhere.  192 output features per tile (see qre_encoder.cuh);
-//   * persistent CTAs, one per SM; a 4-stage TMA/mbarrier ring carries 128x64 of x and 192x64
-//     of W per stage (40 KB); one elected thread issues tcgen05.mma (M=128, N=192, K=16) into one
-//     of two TMEM accumulators, so the epilogue of tile i runs under the MMAs of tile i+1;
-//   * twelve epilogue warps, one per (TMEM lane quarter, 64-column group).  Each owns a 4 KB
-//     staging box in shared memory (32 tokens x 64 features, 128-byte swizzle): the residual rows
-//     arrive in it by TMA while the MMAs run, the warp adds accumulator + bias (+ GELU | + residual)
-//     in place, and one TMA store writes the box out — every byte of global traffic is a full
-//     line moved by the copy engine; the accumulator is handed back to the MMA warp as soon as it
-//     has been read into registers.
+//   * persistent clusters; a 6-stage TMA/mbarrier ring carries 128x64 of x and 96x64 of W per
+//     CTA per stage (28 KB); one elected thread of the leader CTA issues the MMAs into one of two
+//     TMEM accumulators, so the epilogue of tile i runs under the MMAs of tile i+1;
+//   * twelve epilogue warps per CTA, one per (TMEM lane quarter, 64-column group).  Each owns a
+//     4 KB staging box in shared memory (32 tokens x 64 features, 128-byte swizzle): the residual
+//     rows arrive in it by TMA while the MMAs run, the warp adds accumulator + bias (+ GELU |
+//     + residual) in place, and one TMA store writes the box out — every byte of global traffic is
+//     a full line moved by the copy engine.
 //
-// Tiles are walked feature-tile-fastest, so the CTAs resident at any moment share a few token
+// Barrier protocol (objects at the same shared-memory offset in both CTAs), as in
+// qre_gemm_topk2.cu: full[s] on the leader (count 2: both producers arrive, the leader with the
+// expect_tx of both CTAs' bytes); empty[s] and t_full[acc] in each CTA, signalled by a multicast
+// tcgen05.commit; t_empty[acc] on the leader (count 768: the epilogue threads of both CTAs).
+//
+// Tiles are walked feature-tile-fastest, so the clusters resident at any moment share a few token
 // blocks (L2 hits on x) and all of W (<= 1.2 MB, L2-resident).
 #include <stdio.h>
 
@@ -29,36 +37,98 @@ namespace {
 
 constexpr int kEpiWarps = 12;                          // warps 0-11 epilogue, 12 TMA, 13 MMA
 constexpr int kThreads = (kEpiWarps + 2) * 32;
-constexpr int kABytes = kEncBM * kEncBK * 2;           // 16 KB
-constexpr int kBBytes = kEncBN * kEncBK * 2;           // 24 KB
-constexpr int kStageBytes = kABytes + kBBytes;         // 40 KB
+constexpr int kABytes = kEncBM * kEncBK * 2;           // 16 KB: this CTA's 128 tokens
+constexpr int kWHalfRows = kEncBN / 2;                 // 96 weight rows per CTA per tile
+constexpr int kBBytes = kWHalfRows * kEncBK * 2;       // 12 KB
+constexpr int kStageBytes = kABytes + kBBytes;         // 28 KB per CTA
 constexpr int kBoxBytes = 32 * 64 * 2;                 // 4 KB staging box per epilogue warp
 constexpr int kSmemBar = 512;
 constexpr int kSmemTotal = kEncStages * kStageBytes + kEpiWarps * kBoxBytes + kSmemBar + 1024;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kAccStride = 256;                   // TMEM column offset of the second accumulator
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;            // shared::cluster address of the even CTA of a pair
 
-// GELU with the exact (erf) definition, x * Phi(x).  Phi(-a) = exp2(R(a)) for a = |x| in [0, 5.5],
-// R a degree-7 polynomial fitted to log2(0.5 erfc(a / sqrt 2)) (near-minimax, Chebyshev nodes);
-// Phi(a) = 1 - Phi(-a).  Measured against float64 erf over [-12, 12]: |error| <= 6.7e-7 absolute,
-// 4.4e-6 relative — fp32 rounding level, two orders below the bf16 rounding that follows.  Costs
-// one MUFU (ex2) and ~11 ALU instructions per element; erff costs two to three times that and the
-// FFN-up epilogue is ALU-bound.
+// ---- cluster / cta_group::2 PTX (same forms as qre_gemm_topk2.cu) ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+      :
+      : "r"(smem_u32(bar)), "r"(rank)
+      : "memory");
+}
+// TMA load into THIS CTA's shared memory, completion bytes credited to the pair leader's barrier
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int32_t c0,
+                                                 int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerMask), "r"(c0),
+        "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      :
+      : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this offset in BOTH CTAs once all MMAs issued so far have retired
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      :
+      : "r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+
+// GELU with the exact (erf) definition, x * Phi(x).  Phi(-a) = exp2(R(a)) for a = |x| in [0, 5.25],
+// R a degree-6 polynomial fitted to log2(0.5 erfc(a / sqrt 2)) (near-minimax, Chebyshev nodes);
+// Phi(a) = 1 - Phi(-a).  Measured against float64 erf over [-12, 12]: |error| <= 2.8e-6 absolute,
+// 2.1e-5 relative wherever |gelu| > 1e-6 — two orders below the bf16 rounding that follows.  One
+// MUFU (ex2) and ten ALU instructions per element: the FFN-up epilogue is bound by instruction issue
+// (24,576 elements per tile against ~2 us of tensor-core time), erff would cost twice that.
 __device__ __forceinline__ float gelu_erf(float x) {
-  const float a = fminf(fabsf(x), 5.5f);
-  float r = fmaf(a, -1.921234571e-06f, 6.328849850e-05f);
-  r = fmaf(a, r, -9.434208623e-04f);
-  r = fmaf(a, r, 8.556271903e-03f);
-  r = fmaf(a, r, -5.405228212e-02f);
-  r = fmaf(a, r, -4.583817720e-01f);
-  r = fmaf(a, r, -1.151278377e+00f);
-  r = fmaf(a, r, -9.999938607e-01f);
-  const float e = exp2f(r);                                // Phi(-|x|); -30 <= r <= -1, no range issues
+  const float a = fminf(fabsf(x), 5.25f);
+  float r = fmaf(a, 2.802607560e-05f, -6.891732337e-04f);
+  r = fmaf(a, r, 7.647311781e-03f);
+  r = fmaf(a, r, -5.238423496e-02f);
+  r = fmaf(a, r, -4.598393440e-01f);
+  r = fmaf(a, r, -1.150800705e+00f);
+  r = fmaf(a, r, -1.000019431e+00f);
+  float e;                                                 // Phi(-|x|); -28 < r <= -1: no range handling needed
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(r));
   return x * (x < 0.f ? e : 1.0f - e);
 }
 
 template <int kEpi>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                     const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                     const EncGemmArgs a) {
@@ -75,6 +145,10 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int n_clusters = gridDim.x >> 1;
 
   if (warp == kEpiWarps && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -82,49 +156,54 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     tma_prefetch_desc(&tmap_out);
     if (kEpi == kEpiResidual) tma_prefetch_desc(&tmap_res);
     for (int i = 0; i < kEncStages; ++i) {
-      mbar_init(&full[i], 1);
+      mbar_init(&full[i], 2);
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&t_full[i], 1);
-      mbar_init(&t_empty[i], kEpiWarps * 32);
+      mbar_init(&t_empty[i], 2 * kEpiWarps * 32);
     }
     for (int i = 0; i < kEpiWarps; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
+  cluster_sync_all();                          // barriers of both CTAs are initialised
   if (warp == kEpiWarps + 1) {
-    tmem_alloc(tmem_slot, kTmemCols);
-    tmem_relinquish();
+    tmem_alloc2(tmem_slot, kTmemCols);
+    tmem_relinquish2();
   }
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int total = a.tiles_m * a.tiles_n;
+  const int npairs = (a.tiles_m + 1) >> 1;     // pairs of 128-token blocks
+  const int total = npairs * a.tiles_n;
 
   if (warp == kEpiWarps) {
     // ================= TMA producer =================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int mt = tile / a.tiles_n, nt = tile - mt * a.tiles_n;
+      for (int tile = cluster_id; tile < total; tile += n_clusters) {
+        const int pr = tile / a.tiles_n, nt = tile - pr * a.tiles_n;
+        const int mt = 2 * pr + static_cast<int>(rank);
         for (int kb = 0; kb < a.num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full[stage], kStageBytes);
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2u * kStageBytes);
+          else mbar_arrive_remote(&full[stage], 0);
           uint8_t* st = smem + stage * kStageBytes;
-          tma_load_2d(st, &tmap_a, &full[stage], kb * kEncBK, mt * kEncBM);
-          tma_load_2d(st + kABytes, &tmap_w, &full[stage], kb * kEncBK, nt * kEncBN);
+          tma_load_2d_pair(st, &tmap_a, &full[stage], kb * kEncBK, mt * kEncBM);
+          tma_load_2d_pair(st + kABytes, &tmap_w, &full[stage], kb * kEncBK,
+                           nt * kEncBN + static_cast<int>(rank) * kWHalfRows);
           if (++stage == kEncStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == kEpiWarps + 1) {
-    // ================= MMA issuer (one thread) =================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kEncBM, kEncBN);
+    // ================= MMA issuer: one thread of the leader CTA =================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * kEncBM, kEncBN);     // M = 256 across the pair
       uint32_t stage = 0, phase = 0, it = 0;
       const uint32_t s_addr = smem_u32(smem);
-      for (int tile = blockIdx.x; tile < total; tile += gridDim.x, ++it) {
+      for (int tile = cluster_id; tile < total; tile += n_clusters, ++it) {
         const uint32_t acc = it & 1;
         mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -136,11 +215,11 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           const uint64_t bdesc = umma_desc_sw128(s_addr + stage * kStageBytes + kABytes);
 #pragma unroll
           for (int k = 0; k < kEncBK / 16; ++k)
-            umma_bf16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(&empty[stage]);
+            umma_bf16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit_pair(&empty[stage]);
           if (++stage == kEncStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&t_full[acc]);
+        umma_commit_pair(&t_full[acc]);
       }
     }
   } else {
@@ -151,8 +230,9 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint8_t* my_row = box + lane * 128;      // this thread's token: 64 bf16, 16-byte chunks XOR-swizzled by row
     const int sw = lane & 7;
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < total; tile += gridDim.x, ++it) {
-      const int mt = tile / a.tiles_n, nt = tile - mt * a.tiles_n;
+    for (int tile = cluster_id; tile < total; tile += n_clusters, ++it) {
+      const int pr = tile / a.tiles_n, nt = tile - pr * a.tiles_n;
+      const int mt = 2 * pr + static_cast<int>(rank);
       const int row0 = mt * kEncBM + quarter * 32;
       const int col0 = nt * kEncBN + cg * 64;
       const uint32_t acc = it & 1;
@@ -168,15 +248,17 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * kAccStride + cg * 64;
       bool res_ready = kEpi != kEpiResidual;
-#pragma unroll 1
+      // drain this warp's 64 accumulator columns into registers and hand the accumulator back at
+      // once: the MMAs of the tile after next wait for all 24 epilogue warps of the pair
+      float acc_v[2][32];
+      tmem_ld_32x32(taddr, acc_v[0]);
+      tmem_ld_32x32(taddr + 32, acc_v[1]);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive_remote(&t_empty[acc], 0);      // the leader's MMA thread owns the accumulator hand-off
+#pragma unroll
       for (int hlf = 0; hlf < 2; ++hlf) {
-        float v[32];
-        tmem_ld_32x32(taddr + hlf * 32, v);
-        tmem_ld_wait();
-        if (hlf == 1) {                      // accumulator fully read: the MMA warp may overwrite it
-          tc_fence_before();
-          mbar_arrive(&t_empty[acc]);
-        }
+        float(&v)[32] = acc_v[hlf];
         const float4* b4 = reinterpret_cast<const float4*>(a.bias + col0 + hlf * 32);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -232,9 +314,10 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (lane == 0) bulk_wait_all();
   }
 
+  __syncwarp();                                // the single-lane roles rejoin their warps
   tc_fence_before();
-  __syncthreads();
-  if (warp == kEpiWarps + 1) tmem_dealloc(tmem_base, kTmemCols);
+  cluster_sync_all();                          // nobody frees TMEM / exits while the peer still uses it
+  if (warp == kEpiWarps + 1) tmem_dealloc2(tmem_base, kTmemCols);
 }
 
 template <int kEpi>
@@ -253,9 +336,10 @@ cudaError_t enc_gemm_init() {
 
 int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const CUtensorMap& tmap_out,
                     const CUtensorMap* tmap_res, const EncGemmArgs& a, int epilogue, int num_sms, cudaStream_t st) {
-  const int total = a.tiles_m * a.tiles_n;
+  const int total = ((a.tiles_m + 1) / 2) * a.tiles_n;          // tiles of 256 tokens x 192 features
   if (total <= 0) return 0;
-  const int grid = total < num_sms ? total : num_sms;
+  const int clusters = num_sms / 2;
+  const int grid = 2 * (total < clusters ? total : clusters);
   const CUtensorMap& res = tmap_res != nullptr ? *tmap_res : tmap_out;
   switch (epilogue) {
     case kEpiGelu:

@@ -205,48 +205,70 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 
 // ---- softmax(Q K^T / sqrt(HD)) V --------------------------------------------------------------
-// The L keys and values of one (sequence, head) are staged in shared memory (K as [key][dim], V
-// transposed to [dim][key], both padded against bank conflicts); a warp owns 16 query rows at a
-// time and walks the keys 16 at a time with an online softmax, scores and probabilities never
-// leaving registers (the accumulator layout of one m16n8k16 product is the A-operand layout of
-// the next).
+// The L keys and values of one (sequence, head) are staged row-major in shared memory (row stride
+// HD + 8 elements: 16-byte aligned rows that fall into distinct bank groups).  A warp owns 16 query
+// rows at a time and walks the keys 16 at a time with an online softmax; K and V fragments come out
+// of shared memory with ldmatrix (transposed for V), scores and probabilities never leave registers
+// (the accumulator layout of one m16n8k16 product is the A-operand layout of the next).
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* row_ptr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(row_ptr))));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* row_ptr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(row_ptr))));
+}
+
+// Q, K and V rows of one (sequence, head) -> shared memory, 16 bytes per thread per load.
 template <int HD>
-__device__ __forceinline__ void stage_kv(__nv_bfloat16* Ks, __nv_bfloat16* Vt, int VS, const __nv_bfloat16* base,
-                                         long long ld, int H, int L, int Lk, int tid, int nthreads) {
+__device__ __forceinline__ void stage_qkv(__nv_bfloat16* Qs, __nv_bfloat16* Ks, __nv_bfloat16* Vs,
+                                          const __nv_bfloat16* base, long long ld, int H, int L, int Lk, int tid,
+                                          int nthreads) {
   constexpr int KS = HD + 8;
   for (int idx = tid; idx < Lk * (HD / 8); idx += nthreads) {
     const int key = idx / (HD / 8), part = idx - key * (HD / 8);
-    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+    uint4 qv = make_uint4(0, 0, 0, 0), kv = qv, vv = qv;               // padded rows: zeros (keys are masked below)
     if (key < L) {
-      kv = *reinterpret_cast<const uint4*>(base + key * ld + H + part * 8);
-      vv = *reinterpret_cast<const uint4*>(base + key * ld + 2 * H + part * 8);
+      const __nv_bfloat16* p = base + key * ld + part * 8;
+      qv = *reinterpret_cast<const uint4*>(p);
+      kv = *reinterpret_cast<const uint4*>(p + H);
+      vv = *reinterpret_cast<const uint4*>(p + 2 * H);
     }
+    *reinterpret_cast<uint4*>(Qs + key * KS + part * 8) = qv;
     *reinterpret_cast<uint4*>(Ks + key * KS + part * 8) = kv;
-    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) Vt[(part * 8 + j) * VS + key] = ve[j];
+    *reinterpret_cast<uint4*>(Vs + key * KS + part * 8) = vv;
   }
 }
 
-// One 16-row query block [16 * qb, +16) of one head; `base` points at the sequence's first token,
-// this head's Q columns; `out` at the same position of the context buffer.
+// The context rows left in the Q slice by attend_block -> global memory, 16 bytes per thread per store.
 template <int HD>
-__device__ __forceinline__ void attend_block(const __nv_bfloat16* Ks, const __nv_bfloat16* Vt, int VS,
-                                             const __nv_bfloat16* base, long long ld, int L, int Lk, int qb,
-                                             __nv_bfloat16* out, int H, float scale_log2e, int lane) {
+__device__ __forceinline__ void store_ctx(const __nv_bfloat16* Qs, __nv_bfloat16* out, int H, int L, int tid,
+                                          int nthreads) {
+  constexpr int KS = HD + 8;
+  for (int idx = tid; idx < L * (HD / 8); idx += nthreads) {
+    const int row = idx / (HD / 8), part = idx - row * (HD / 8);
+    *reinterpret_cast<uint4*>(out + static_cast<long long>(row) * H + part * 8) =
+        *reinterpret_cast<const uint4*>(Qs + row * KS + part * 8);
+  }
+}
+
+// One 16-row query block of one head against the staged keys/values.  The block's context rows
+// overwrite its query rows in Qs (bf16) once the query fragments are in registers.
+template <int HD>
+__device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloat16* Ks, const __nv_bfloat16* Vs,
+                                             int L, int Lk, int qb, float scale_log2e, int lane) {
   constexpr int KS = HD + 8;
   const int g = lane >> 2, t = lane & 3;
+  const int mi = lane >> 3, mr = lane & 7;          // ldmatrix: this lane addresses row mr of matrix mi
   const float ninf = __int_as_float(0xff800000);
   const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
+  // A fragments: matrices 0..3 = rows [8 (mi & 1), +8) x dims [16 kk + 8 (mi >> 1), +8) of the block
   uint32_t qa[HD / 16][4];
 #pragma unroll
-  for (int kk = 0; kk < HD / 16; ++kk) {
-    const int c = kk * 16 + 2 * t;
-    qa[kk][0] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c) : 0u;
-    qa[kk][1] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c) : 0u;
-    qa[kk][2] = r_lo < L ? *reinterpret_cast<const uint32_t*>(base + r_lo * ld + c + 8) : 0u;
-    qa[kk][3] = r_hi < L ? *reinterpret_cast<const uint32_t*>(base + r_hi * ld + c + 8) : 0u;
-  }
+  for (int kk = 0; kk < HD / 16; ++kk)
+    ldmatrix_x4(qa[kk], Qs + (qb * 16 + (mi & 1) * 8 + mr) * KS + kk * 16 + (mi >> 1) * 8);
   float o[HD / 8][4];
 #pragma unroll
   for (int nd = 0; nd < HD / 8; ++nd) o[nd][0] = o[nd][1] = o[nd][2] = o[nd][3] = 0.f;
@@ -257,11 +279,15 @@ __device__ __forceinline__ void attend_block(const __nv_bfloat16* Ks, const __nv
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
-      const __nv_bfloat16* kr = Ks + (k0 + j * 8 + g) * KS + 2 * t;
+      // matrices 0..3 = keys [k0 + 8j, +8) x dims [32 k2 + 8 mi, +8): b0/b1 of two consecutive k-steps
+      const __nv_bfloat16* kr = Ks + (k0 + j * 8 + mr) * KS + mi * 8;
 #pragma unroll
-      for (int kk = 0; kk < HD / 16; ++kk)
-        mma_16816(s[j], qa[kk], *reinterpret_cast<const uint32_t*>(kr + kk * 16),
-                  *reinterpret_cast<const uint32_t*>(kr + kk * 16 + 8));
+      for (int k2 = 0; k2 < HD / 32; ++k2) {
+        uint32_t kf[4];
+        ldmatrix_x4(kf, kr + k2 * 32);
+        mma_16816(s[j], qa[2 * k2], kf[0], kf[1]);
+        mma_16816(s[j], qa[2 * k2 + 1], kf[2], kf[3]);
+      }
     }
     // scale into the log2 domain and mask the padded keys
 #pragma unroll
@@ -294,14 +320,22 @@ __device__ __forceinline__ void attend_block(const __nv_bfloat16* Ks, const __nv
     l_hi = l_hi * c_hi + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
     const uint32_t pa[4] = {pack_bf16(p[0][0], p[0][1]), pack_bf16(p[0][2], p[0][3]), pack_bf16(p[1][0], p[1][1]),
                             pack_bf16(p[1][2], p[1][3])};
+    // matrices 0..3 = keys [k0 + 8 (mi & 1), +8) x dims [16 n2 + 8 (mi >> 1), +8), transposed on load:
+    // b0/b1 (keys 0-7 / 8-15 of the block) for two consecutive 8-dim output tiles
+    const __nv_bfloat16* vr = Vs + (k0 + (mi & 1) * 8 + mr) * KS + (mi >> 1) * 8;
 #pragma unroll
-    for (int nd = 0; nd < HD / 8; ++nd) {
-      o[nd][0] *= c_lo;
-      o[nd][1] *= c_lo;
-      o[nd][2] *= c_hi;
-      o[nd][3] *= c_hi;
-      const __nv_bfloat16* vr = Vt + (nd * 8 + g) * VS + k0 + 2 * t;
-      mma_16816(o[nd], pa, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
+    for (int n2 = 0; n2 < HD / 16; ++n2) {
+      uint32_t vf[4];
+      ldmatrix_x4_trans(vf, vr + n2 * 16);
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        float(&oo)[4] = o[2 * n2 + h2];
+        oo[0] *= c_lo;
+        oo[1] *= c_lo;
+        oo[2] *= c_hi;
+        oo[3] *= c_hi;
+        mma_16816(oo, pa, vf[2 * h2], vf[2 * h2 + 1]);
+      }
     }
   }
   l_lo += __shfl_xor_sync(kFull, l_lo, 1);
@@ -309,19 +343,17 @@ __device__ __forceinline__ void attend_block(const __nv_bfloat16* Ks, const __nv
   l_hi += __shfl_xor_sync(kFull, l_hi, 1);
   l_hi += __shfl_xor_sync(kFull, l_hi, 2);
   const float i_lo = 1.f / l_lo, i_hi = 1.f / l_hi;
-  out += 2 * t;
+  __syncwarp();                                   // every lane's ldmatrix of this block's Q rows has retired
 #pragma unroll
   for (int nd = 0; nd < HD / 8; ++nd) {
-    if (r_lo < L)
-      *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_lo) * H + nd * 8) =
-          __floats2bfloat162_rn(o[nd][0] * i_lo, o[nd][1] * i_lo);
-    if (r_hi < L)
-      *reinterpret_cast<__nv_bfloat162*>(out + static_cast<long long>(r_hi) * H + nd * 8) =
-          __floats2bfloat162_rn(o[nd][2] * i_hi, o[nd][3] * i_hi);
+    *reinterpret_cast<__nv_bfloat162*>(Qs + r_lo * KS + nd * 8 + 2 * t) =
+        __floats2bfloat162_rn(o[nd][0] * i_lo, o[nd][1] * i_lo);
+    *reinterpret_cast<__nv_bfloat162*>(Qs + r_hi * KS + nd * 8 + 2 * t) =
+        __floats2bfloat162_rn(o[nd][2] * i_hi, o[nd][3] * i_hi);
   }
 }
 
-constexpr int kShortLen = 64;     // sequences up to this long take the warp-per-head kernel
+constexpr int kShortLen = 32;     // sequences up to this long take the warp-per-head kernel
 
 // Long sequences (kShortLen < L): one CTA per (sequence, head) at a time, its four warps share the
 // staged K/V and split the query blocks.  The sequences come from `long_list` (built once per batch by
@@ -333,10 +365,10 @@ enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __res
                      const int32_t* __restrict__ long_list, const int32_t* __restrict__ n_long,
                      __nv_bfloat16* __restrict__ ctx, int H, int Lp, float scale_log2e) {
   constexpr int KS = HD + 8;
-  const int VS = Lp + 8;
   extern __shared__ __align__(16) uint8_t att_smem[];
-  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem);
-  __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
+  __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(att_smem);
+  __nv_bfloat16* Ks = Qs + static_cast<size_t>(Lp) * KS;
+  __nv_bfloat16* Vs = Ks + static_cast<size_t>(Lp) * KS;
   const int head = blockIdx.y, n = *n_long;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long ld = 3LL * H;
@@ -346,12 +378,12 @@ enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __res
     const int L = min(offsets[seq + 1] - t0, Lp);
     const int Lk = (L + 15) & ~15;
     const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
-    __syncthreads();                       // previous sequence's K/V no longer read
-    stage_kv<HD>(Ks, Vt, VS, base, ld, H, L, Lk, threadIdx.x, blockDim.x);
+    __syncthreads();                               // previous sequence's rows fully copied out
+    stage_qkv<HD>(Qs, Ks, Vs, base, ld, H, L, Lk, threadIdx.x, blockDim.x);
     __syncthreads();
-    __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD;
-    for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5)
-      attend_block<HD>(Ks, Vt, VS, base, ld, L, Lk, qb, out, H, scale_log2e, lane);
+    for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5) attend_block<HD>(Qs, Ks, Vs, L, Lk, qb, scale_log2e, lane);
+    __syncthreads();
+    store_ctx<HD>(Qs, ctx + static_cast<long long>(t0) * H + head * HD, H, L, threadIdx.x, blockDim.x);
   }
 }
 
@@ -364,31 +396,33 @@ enc_find_long_kernel(const int32_t* __restrict__ offsets, int m, int min_len, in
   if (i < m && offsets[i + 1] - offsets[i] > min_len) long_list[atomicAdd(n_long, 1)] = i;
 }
 
-// Short sequences (0 < L <= kShortLen, the bulk of chat queries): one WARP per (sequence, head),
-// four heads of the same sequence per CTA.  Each warp stages its own head's K/V in a private
-// slice of shared memory and runs all of the head's query blocks; warps never wait for each other.
+// Short sequences (0 < L <= kShortLen = 32, the bulk of chat queries): one WARP per (sequence, head),
+// four heads of the same sequence per CTA.  Each warp stages its own head's K/V in a private slice
+// of shared memory and runs the head's one or two query blocks; warps never wait for each other.  All
+// global traffic is 16 bytes per thread on 64-byte row segments (Q/K/V in, context rows out).
 template <int HD>
 __global__ void __launch_bounds__(128)
 enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
                            __nv_bfloat16* __restrict__ ctx, int H, int heads, int Lp, float scale_log2e) {
   constexpr int KS = HD + 8;
-  const int VS = Lp + 8;
   extern __shared__ __align__(16) uint8_t att_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const size_t per_warp = static_cast<size_t>(Lp) * KS + static_cast<size_t>(HD) * VS;   // elements; a multiple of 8
-  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(att_smem) + warp * per_warp;
-  __nv_bfloat16* Vt = Ks + static_cast<size_t>(Lp) * KS;
+  const size_t slice = static_cast<size_t>(Lp) * KS;                  // elements per Q / K / V slice
+  __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(att_smem) + warp * 3 * slice;
+  __nv_bfloat16* Ks = Qs + slice;
+  __nv_bfloat16* Vs = Ks + slice;
   const int seq = blockIdx.x, head = blockIdx.y * 4 + warp;
   const int t0 = offsets[seq];
   const int L = offsets[seq + 1] - t0;
   if (L <= 0 || L > Lp || head >= heads) return;
   const int Lk = (L + 15) & ~15;
   const long long ld = 3LL * H;
-  const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
-  stage_kv<HD>(Ks, Vt, VS, base, ld, H, L, Lk, lane, 32);
+  stage_qkv<HD>(Qs, Ks, Vs, qkv + static_cast<long long>(t0) * ld + head * HD, ld, H, L, Lk, lane, 32);
   __syncwarp();
-  __nv_bfloat16* out = ctx + static_cast<long long>(t0) * H + head * HD;
-  for (int qb = 0; qb * 16 < L; ++qb) attend_block<HD>(Ks, Vt, VS, base, ld, L, Lk, qb, out, H, scale_log2e, lane);
+  attend_block<HD>(Qs, Ks, Vs, L, Lk, 0, scale_log2e, lane);
+  if (L > 16) attend_block<HD>(Qs, Ks, Vs, L, Lk, 1, scale_log2e, lane);
+  __syncwarp();
+  store_ctx<HD>(Qs, ctx + static_cast<long long>(t0) * H + head * HD, H, L, lane, 32);
 }
 
 // Pooling(mean over the sequence's tokens) + Normalize (x / max(|x|, 1e-12)); one CTA per sequence.
@@ -431,9 +465,7 @@ enc_pool_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__
   }
 }
 
-size_t attention_smem(int hd, int Lp) {
-  return static_cast<size_t>(Lp) * (hd + 8) * 2 + static_cast<size_t>(hd) * (Lp + 8) * 2;
-}
+size_t attention_smem(int hd, int Lp) { return 3 * static_cast<size_t>(Lp) * (hd + 8) * 2; }   // Q, K, V slices
 
 struct Linear {
   __nv_bfloat16* w = nullptr;   // [n, k] bf16
@@ -510,7 +542,7 @@ int upload_linear(Linear& L, std::initializer_list<const float*> ws, std::initia
     ENC_CUDA(cudaMemset(L.w, 0, rows_pad * k * sizeof(__nv_bfloat16)));
     ENC_CUDA(cudaMalloc(&L.b, round_up(n, kEncBN) * sizeof(float)));
     ENC_CUDA(cudaMemset(L.b, 0, round_up(n, kEncBN) * sizeof(float)));
-    int rc = make_tensor_map_bf16(&L.map, L.w, static_cast<uint64_t>(k), rows_pad, kEncBK, kEncBN);
+    int rc = make_tensor_map_bf16(&L.map, L.w, static_cast<uint64_t>(k), rows_pad, kEncBK, kEncBN / 2);
     if (rc != QRE_OK) return rc;
   }
   ENC_CUDA(cudaMemcpy(L.w, wb.data(), wb.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
@@ -674,7 +706,7 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   e->num_sms = prop.multiProcessorCount;
   e->hd = c.hidden / c.heads;
   e->max_tokens = max_tokens;
-  e->tok_pad = static_cast<int64_t>(round_up(static_cast<size_t>(max_tokens), kEncBM));
+  e->tok_pad = static_cast<int64_t>(round_up(static_cast<size_t>(max_tokens), kEncRowPad));
   e->max_seqs = max_seqs;
   e->layers.resize(c.layers);
   e->have_layer.assign(c.layers, 0);
@@ -849,7 +881,7 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   ENC_CUDA(cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10) return set_error(QRE_ERR_NO_DEVICE, "debug_gemm: sm_100a only");
   ENC_CUDA(enc_gemm_init());
-  const size_t rows_pad = round_up(rows, kEncBM), n_pad = round_up(n, kEncBN);
+  const size_t rows_pad = round_up(rows, kEncRowPad), n_pad = round_up(n, kEncBN);
   std::vector<__nv_bfloat16> ab(rows_pad * k, __float2bfloat16(0.f)), wb(n_pad * k, __float2bfloat16(0.f)),
       rb(rows_pad * n, __float2bfloat16(0.f)), cb(rows_pad * n);
   for (size_t i = 0; i < static_cast<size_t>(rows) * k; ++i) ab[i] = __float2bfloat16(a[i]);
@@ -886,7 +918,7 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   DBG_TRY(cudaMemcpy(db, bias, n * sizeof(float), cudaMemcpyHostToDevice));
   CUtensorMap ma, mw, mo, mr;
   rc = make_tensor_map_bf16(&ma, da, k, rows_pad, kEncBK, kEncBM);
-  if (rc == QRE_OK) rc = make_tensor_map_bf16(&mw, dw, k, n_pad, kEncBK, kEncBN);
+  if (rc == QRE_OK) rc = make_tensor_map_bf16(&mw, dw, k, n_pad, kEncBK, kEncBN / 2);
   if (rc == QRE_OK) rc = make_tensor_map_bf16(&mo, dc, n, rows_pad, kEncBoxCols, kEncBoxRows);
   if (rc == QRE_OK) rc = make_tensor_map_bf16(&mr, dr, n, rows_pad, kEncBoxCols, kEncBoxRows);
   if (rc != QRE_OK) {

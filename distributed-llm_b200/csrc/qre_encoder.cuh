@@ -15,7 +15,8 @@ namespace qre {
 constexpr int kEncBM = 128;
 constexpr int kEncBN = 192;
 constexpr int kEncBK = 64;
-constexpr int kEncStages = 4;
+constexpr int kEncStages = 6;
+constexpr int kEncRowPad = 256;    // activation buffers are padded to whole CTA-pair tiles (2 x 128 tokens)
 
 enum EncEpilogue { kEpiBias = 0, kEpiGelu = 1, kEpiResidual = 2 };
 
