@@ -111,15 +111,28 @@ class TokenBasedRouter(BaseRouter):
         return self._decision(tok, *self.decide(tok))
 
 
+def _make_embedder(config: Dict[str, Any]):
+    """The object whose `.encode(list[str]) -> float32 [n, d]` the routers call (qre:126, 511).
+    `config["embedder"]` (additive key) supplies one directly — e.g. a
+    `qre_b200.embedder.B200SentenceEncoder`, which embeds on the GPU next to the cache; otherwise the
+    reference's SentenceTransformer(model name) when that package is installed, else None."""
+    emb = config.get("embedder")
+    if emb is not None:
+        return emb
+    if SENTENCE_TRANSFORMERS_AVAILABLE:
+        return SentenceTransformer(config.get("embedding_model", "all-MiniLM-L6-v2"))
+    return None
+
+
 # ----------------------------------------------------------------------------- semantic
 class SemanticRouter(BaseRouter):
     """Centroid router (reference qre:114-213); the cosines and the rule run on the GPU."""
 
     def __init__(self, config: Dict[str, Any], engine: Optional[Engine] = None):
         super().__init__(config)
-        if not SENTENCE_TRANSFORMERS_AVAILABLE:
+        self.embedder = _make_embedder(config)
+        if self.embedder is None:
             raise ImportError("sentence-transformers required for SemanticRouter")
-        self.embedder = SentenceTransformer(config.get("embedding_model", "all-MiniLM-L6-v2"))
         self.label_path = config.get("semantic_label_path", "")
         self.margin_threshold = float(config.get("semantic_margin_threshold", 0.03))
         self.min_similarity = float(config.get("semantic_min_similarity", 0.05))
@@ -448,8 +461,8 @@ class QueryRouter:
             engine=self._engine,
         )
         self.cache_embedder = None
-        if SENTENCE_TRANSFORMERS_AVAILABLE and self.config.get("use_semantic_cache", True):
-            self.cache_embedder = SentenceTransformer(self.config.get("embedding_model", "all-MiniLM-L6-v2"))
+        if self.config.get("use_semantic_cache", True):
+            self.cache_embedder = _make_embedder(self.config)
 
     def _make_router(self, strategy: str) -> BaseRouter:
         cls = self.AVAILABLE_STRATEGIES[strategy]
