@@ -25,6 +25,9 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--check", type=int, default=64, help="sequences compared with the fp32 oracle")
+    ap.add_argument("--fused-cache-rows", type=int, default=0,
+                    help="also time token ids -> embedding -> cache lookup + hybrid route against a cache of "
+                         "this many random rows, everything on the device (SURVEY 8f-1 feeding 8a)")
     a = ap.parse_args()
     import torch
     from oracle import minilm_oracle as MO
@@ -84,6 +87,47 @@ def main():
         "peaks": peaks, "dtype": "bf16 x bf16 -> fp32, bf16 activations",
         "vs_fp32_oracle": {"sequences": int(k), "min_cosine": float(cos.min()), "max_abs_diff": float(np.abs(got[sel] - want).max())},
     }
+    if a.fused_cache_rows > 0:
+        from qre_b200.sharded import ShardedLookup
+        n = a.fused_cache_rows
+        sh = _cabi.Shard(dim=cfg_o.hidden, capacity=n + 256, max_batch=m)
+        rr = np.random.Generator(np.random.PCG64(7))
+        for i0 in range(0, n, 1 << 17):
+            k = min(1 << 17, n - i0)
+            rows = rr.standard_normal((k, cfg_o.hidden), dtype=np.float32)
+            sh.append(rows, np.full(k, 2, np.uint64), np.zeros(k, np.int64), np.arange(i0 + 1, i0 + k + 1, dtype=np.uint64),
+                      (np.arange(k) % 2).astype(np.uint8), np.full(k, 0.9))
+        # Random-weight encoders map every text close to one direction (pairwise cosines > 0.85), unlike the
+        # trained model, so each planted embedding is a hit for EVERY query: plant only 4 (a window of at most
+        # 4 candidates per query; more than 8 would push every query through the overflow path).
+        sh.append(got[:4], np.full(4, 2, np.uint64), np.zeros(4, np.int64),
+                  np.arange(n + 1, n + 5, dtype=np.uint64), np.zeros(4, np.uint8), np.full(4, 0.9))
+        sh.set_centroids(got[:8].copy(), (np.arange(8) % 2).astype(np.uint8))
+        look = ShardedLookup(sh, _cabi.RouteConfig(ttl_us=10**15))
+        t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev)   # noqa: E731
+        ctx_d, tok_d = t(np.full(m, 2, np.int64)), t(lens.astype(np.int32))
+        hd_d, hc_d = t(np.zeros(m, np.uint8)), t(np.full(m, 0.8))
+        q_d = torch.empty((m, cfg_o.hidden), dtype=torch.float32, device=dev)
+
+        def fused():
+            enc.encode_dev(m, ids_d.data_ptr(), off_d.data_ptr(), T, max_len, q_d.data_ptr(), stream=side.cuda_stream)
+            return look.step(q_d, ctx_d, 1, tok_d, hd_d, hc_d)
+
+        with torch.cuda.stream(side):
+            for _ in range(a.warmup):
+                out = fused()
+            side.synchronize()
+            e0.record(side)
+            for _ in range(a.steps):
+                out = fused()
+            e1.record(side)
+            side.synchronize()
+        fms = e0.elapsed_time(e1) / a.steps
+        hits = int((out["hit_slot"] >= 0).sum().item())
+        print(json.dumps({"metric": "token ids -> embedded -> looked up + routed, queries/s (one B200, on device)",
+                          "value": m / fms * 1e3, "unit": "queries/s", "ms_per_batch": fms, "queries": m, "tokens": T,
+                          "cache_rows": n, "hits": hits, "embed_ms": ms, "lookup_route_ms": fms - ms}))
+        sh.close()
     print(json.dumps(line))
     enc.close()
 
