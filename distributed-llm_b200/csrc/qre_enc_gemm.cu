@@ -43,7 +43,13 @@ constexpr int kBBytes = kWHalfRows * kEncBK * 2;       // 12 KB
 constexpr int kStageBytes = kABytes + kBBytes;         // 28 KB per CTA
 constexpr int kBoxBytes = 32 * 64 * 2;                 // 4 KB staging box per epilogue warp
 constexpr int kSmemBar = 512;
-constexpr int kSmemTotal = kEncStages * kStageBytes + kEpiWarps * kBoxBytes + kSmemBar + 1024;
+constexpr int kLnStages = 4;                           // the LayerNorm epilogue trades two ring stages for a second box
+constexpr int kLnStatBytes = 2 * kEpiWarps * 32 * 8;   // double-buffered per-row (sum, sum of squares) partials
+constexpr int smem_total(int epi) {
+  return epi == kEpiResidualLN
+             ? kLnStages * kStageBytes + 2 * kEpiWarps * kBoxBytes + kSmemBar + kLnStatBytes + 1024
+             : kEncStages * kStageBytes + kEpiWarps * kBoxBytes + kSmemBar + 1024;
+}
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kAccStride = 256;                   // TMEM column offset of the second accumulator
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;            // shared::cluster address of the even CTA of a pair
@@ -134,11 +140,15 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     const EncGemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* boxes = smem + kEncStages * kStageBytes;                 // [kEpiWarps] x 4 KB, 1024-aligned
-  uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + kEpiWarps * kBoxBytes);
-  uint64_t* full = bars;                        // [kEncStages] TMA -> MMA
-  uint64_t* empty = bars + kEncStages;          // [kEncStages] MMA -> TMA
-  uint64_t* t_full = bars + 2 * kEncStages;     // [2] MMA -> epilogue
+  constexpr bool kLN = kEpi == kEpiResidualLN;
+  constexpr int kStages = kLN ? kLnStages : kEncStages;
+  constexpr int kBoxesPerWarp = kLN ? 2 : 1;
+  uint8_t* boxes = smem + kStages * kStageBytes;                    // [kEpiWarps][kBoxesPerWarp] x 4 KB, 1024-aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(boxes + kEpiWarps * kBoxesPerWarp * kBoxBytes);
+  float2* ln_stats = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(bars) + kSmemBar);   // kLN only
+  uint64_t* full = bars;                        // [kStages] TMA -> MMA
+  uint64_t* empty = bars + kStages;             // [kStages] MMA -> TMA
+  uint64_t* t_full = bars + 2 * kStages;        // [2] MMA -> epilogue
   uint64_t* t_empty = t_full + 2;               // [2] epilogue -> MMA
   uint64_t* res_bar = t_empty + 2;              // [kEpiWarps] residual box landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + kEpiWarps);
@@ -154,8 +164,8 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_w);
     tma_prefetch_desc(&tmap_out);
-    if (kEpi == kEpiResidual) tma_prefetch_desc(&tmap_res);
-    for (int i = 0; i < kEncStages; ++i) {
+    if (kEpi == kEpiResidual || kLN) tma_prefetch_desc(&tmap_res);
+    for (int i = 0; i < kStages; ++i) {
       mbar_init(&full[i], 2);
       mbar_init(&empty[i], 1);
     }
@@ -176,14 +186,30 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int npairs = (a.tiles_m + 1) >> 1;     // pairs of 128-token blocks
-  const int total = npairs * a.tiles_n;
+  // The j-th tile of this cluster.  Default: tiles dealt round-robin, feature tile fastest.  LayerNorm
+  // epilogue: whole 256-token units (both feature tiles, so one CTA sees complete rows), units round-robin.
+  const int n_mine = kLN ? (cluster_id < npairs ? 2 * ((npairs - cluster_id + n_clusters - 1) / n_clusters) : 0)
+                         : (cluster_id < npairs * a.tiles_n
+                                ? (npairs * a.tiles_n - cluster_id + n_clusters - 1) / n_clusters
+                                : 0);
+  auto tile_of = [&](int j, int& pr, int& nt) {
+    if (kLN) {
+      pr = cluster_id + (j >> 1) * n_clusters;
+      nt = j & 1;
+    } else {
+      const int tile = cluster_id + j * n_clusters;
+      pr = tile / a.tiles_n;
+      nt = tile - pr * a.tiles_n;
+    }
+  };
 
   if (warp == kEpiWarps) {
     // ================= TMA producer =================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int tile = cluster_id; tile < total; tile += n_clusters) {
-        const int pr = tile / a.tiles_n, nt = tile - pr * a.tiles_n;
+      for (int j = 0; j < n_mine; ++j) {
+        int pr, nt;
+        tile_of(j, pr, nt);
         const int mt = 2 * pr + static_cast<int>(rank);
         for (int kb = 0; kb < a.num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
@@ -193,7 +219,7 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           tma_load_2d_pair(st, &tmap_a, &full[stage], kb * kEncBK, mt * kEncBM);
           tma_load_2d_pair(st + kABytes, &tmap_w, &full[stage], kb * kEncBK,
                            nt * kEncBN + static_cast<int>(rank) * kWHalfRows);
-          if (++stage == kEncStages) { stage = 0; phase ^= 1; }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -203,7 +229,7 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       constexpr uint32_t idesc = umma_idesc_bf16(2 * kEncBM, kEncBN);     // M = 256 across the pair
       uint32_t stage = 0, phase = 0, it = 0;
       const uint32_t s_addr = smem_u32(smem);
-      for (int tile = cluster_id; tile < total; tile += n_clusters, ++it) {
+      for (int j = 0; j < n_mine; ++j, ++it) {
         const uint32_t acc = it & 1;
         mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -217,21 +243,125 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           for (int k = 0; k < kEncBK / 16; ++k)
             umma_bf16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit_pair(&empty[stage]);
-          if (++stage == kEncStages) { stage = 0; phase ^= 1; }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
         umma_commit_pair(&t_full[acc]);
       }
     }
   } else {
-    // ================= epilogue: bias (+ GELU | + residual) -> bf16 -> TMA store =================
+    // ================= epilogue: bias (+ GELU | + residual [+ LayerNorm]) -> bf16 -> TMA store =================
     const int quarter = warp & 3;            // TMEM lanes [32*quarter, +32): the only ones this warp may read
     const int cg = warp >> 2;                // columns [64*cg, +64) of the tile
-    uint8_t* box = boxes + warp * kBoxBytes;
+    uint8_t* box = boxes + warp * kBoxesPerWarp * kBoxBytes;
     uint8_t* my_row = box + lane * 128;      // this thread's token: 64 bf16, 16-byte chunks XOR-swizzled by row
     const int sw = lane & 7;
     uint32_t it = 0;
-    for (int tile = cluster_id; tile < total; tile += n_clusters, ++it) {
-      const int pr = tile / a.tiles_n, nt = tile - pr * a.tiles_n;
+    if constexpr (kLN) {
+      // One unit = 256 tokens x 384 features = both accumulators.  Pass 1 (per feature tile): accumulator +
+      // bias + residual -> fp32 row sums, bf16 value left in the tile's box.  The three warps that share a
+      // lane quarter exchange their partial sums through shared memory (named barrier 1 + quarter), then
+      // pass 2 normalises the boxes in place and two TMA stores write the rows out — over the residual rows
+      // they came from: the LayerNorm output IS the next residual stream.
+      for (int j = 0; j < n_mine; j += 2) {
+        int pr, nt_unused;
+        tile_of(j, pr, nt_unused);
+        const uint32_t unit = static_cast<uint32_t>(j) >> 1;
+        const int row0 = (2 * pr + static_cast<int>(rank)) * kEncBM + quarter * 32;
+        if (lane == 0) {
+          bulk_wait_read_all();              // the previous unit's stores no longer read the boxes
+          mbar_arrive_expect_tx(&res_bar[warp], 2 * kBoxBytes);
+          tma_load_2d(box, &tmap_res, &res_bar[warp], cg * 64, row0);
+          tma_load_2d(box + kBoxBytes, &tmap_res, &res_bar[warp], kEncBN + cg * 64, row0);
+        }
+        __syncwarp();
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll 1
+        for (int nt = 0; nt < 2; ++nt, ++it) {
+          const uint32_t acc = it & 1;
+          const int col0 = nt * kEncBN + cg * 64;
+          uint8_t* row = my_row + nt * kBoxBytes;
+          mbar_wait(&t_full[acc], (it >> 1) & 1);
+          tc_fence_after();
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * kAccStride + cg * 64;
+          float acc_v[2][32];
+          tmem_ld_32x32(taddr, acc_v[0]);
+          tmem_ld_32x32(taddr + 32, acc_v[1]);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive_remote(&t_empty[acc], 0);
+          if (nt == 0) mbar_wait(&res_bar[warp], unit & 1);
+#pragma unroll
+          for (int hlf = 0; hlf < 2; ++hlf) {
+            float(&v)[32] = acc_v[hlf];
+            const float4* b4 = reinterpret_cast<const float4*>(a.bias + col0 + hlf * 32);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              uint4* slot = reinterpret_cast<uint4*>(row + (((hlf * 4 + c) ^ sw) << 4));
+              const uint4 r = *slot;
+              const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+              const float4 ba = __ldg(b4 + 2 * c), bb = __ldg(b4 + 2 * c + 1);
+              const float bv[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+              uint32_t w[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
+                const float y0 = v[8 * c + 2 * e] + bv[2 * e] + f.x, y1 = v[8 * c + 2 * e + 1] + bv[2 * e + 1] + f.y;
+                s1 += y0 + y1;
+                s2 = fmaf(y0, y0, fmaf(y1, y1, s2));
+                const __nv_bfloat162 h = __floats2bfloat162_rn(y0, y1);
+                w[e] = *reinterpret_cast<const uint32_t*>(&h);
+              }
+              *slot = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+          }
+        }
+        // row statistics over the 384 features: this warp saw 128 of them
+        float2* st = ln_stats + (unit & 1) * (kEpiWarps * 32);
+        st[warp * 32 + lane] = make_float2(s1, s2);
+        asm volatile("bar.sync %0, 96;" ::"r"(1 + quarter) : "memory");
+        const float2 p0 = st[quarter * 32 + lane], p1 = st[(quarter + 4) * 32 + lane], p2 = st[(quarter + 8) * 32 + lane];
+        const float inv_n = 1.0f / static_cast<float>(2 * kEncBN);
+        const float mu = (p0.x + p1.x + p2.x) * inv_n;
+        const float var = fmaxf((p0.y + p1.y + p2.y) * inv_n - mu * mu, 0.f);
+        const float rstd = rsqrtf(var + a.ln_eps);
+#pragma unroll 1
+        for (int nt = 0; nt < 2; ++nt) {
+          const int col0 = nt * kEncBN + cg * 64;
+          uint8_t* row = my_row + nt * kBoxBytes;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4* slot = reinterpret_cast<uint4*>(row + ((c ^ sw) << 4));
+            const uint4 r = *slot;
+            const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+            const float4 ga = __ldg(reinterpret_cast<const float4*>(a.ln_g + col0 + 8 * c)),
+                         gb = __ldg(reinterpret_cast<const float4*>(a.ln_g + col0 + 8 * c + 4));
+            const float4 ba = __ldg(reinterpret_cast<const float4*>(a.ln_b + col0 + 8 * c)),
+                         bb = __ldg(reinterpret_cast<const float4*>(a.ln_b + col0 + 8 * c + 4));
+            const float gv[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+            const float bv[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
+              const __nv_bfloat162 h = __floats2bfloat162_rn((f.x - mu) * rstd * gv[2 * e] + bv[2 * e],
+                                                             (f.y - mu) * rstd * gv[2 * e + 1] + bv[2 * e + 1]);
+              w[e] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            *slot = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmap_out, box, cg * 64, row0);
+          tma_store_2d(&tmap_out, box + kBoxBytes, kEncBN + cg * 64, row0);
+          bulk_commit_group();
+        }
+      }
+    } else {
+    for (int j = 0; j < n_mine; ++j, ++it) {
+      int pr, nt;
+      tile_of(j, pr, nt);
       const int mt = 2 * pr + static_cast<int>(rank);
       const int row0 = mt * kEncBM + quarter * 32;
       const int col0 = nt * kEncBN + cg * 64;
@@ -248,17 +378,30 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * kAccStride + cg * 64;
       bool res_ready = kEpi != kEpiResidual;
-      // drain this warp's 64 accumulator columns into registers and hand the accumulator back at
-      // once: the MMAs of the tile after next wait for all 24 epilogue warps of the pair
+      // Bias / residual epilogues drain all 64 accumulator columns into registers and hand the accumulator
+      // back at once (the MMAs of the tile after next wait for all 24 epilogue warps of the pair).  The GELU
+      // epilogue is bound by instruction issue instead: it keeps only 32 columns live so that the compiler
+      // can interleave more polynomial chains, and releases after the second load.
+      constexpr bool kDrainFirst = kEpi != kEpiGelu;
       float acc_v[2][32];
-      tmem_ld_32x32(taddr, acc_v[0]);
-      tmem_ld_32x32(taddr + 32, acc_v[1]);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive_remote(&t_empty[acc], 0);      // the leader's MMA thread owns the accumulator hand-off
+      if (kDrainFirst) {
+        tmem_ld_32x32(taddr, acc_v[0]);
+        tmem_ld_32x32(taddr + 32, acc_v[1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive_remote(&t_empty[acc], 0);    // the leader's MMA thread owns the accumulator hand-off
+      }
 #pragma unroll
       for (int hlf = 0; hlf < 2; ++hlf) {
         float(&v)[32] = acc_v[hlf];
+        if (!kDrainFirst) {
+          tmem_ld_32x32(taddr + hlf * 32, v);
+          tmem_ld_wait();
+          if (hlf == 1) {
+            tc_fence_before();
+            mbar_arrive_remote(&t_empty[acc], 0);
+          }
+        }
         const float4* b4 = reinterpret_cast<const float4*>(a.bias + col0 + hlf * 32);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -311,6 +454,7 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         bulk_commit_group();
       }
     }
+    }
     if (lane == 0) bulk_wait_all();
   }
 
@@ -322,7 +466,7 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
 template <int kEpi>
 cudaError_t set_attr() {
-  return cudaFuncSetAttribute(qre_enc_gemm_kernel<kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
+  return cudaFuncSetAttribute(qre_enc_gemm_kernel<kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(kEpi));
 }
 
 }  // namespace
@@ -331,6 +475,7 @@ cudaError_t enc_gemm_init() {
   cudaError_t e = set_attr<kEpiBias>();
   if (e == cudaSuccess) e = set_attr<kEpiGelu>();
   if (e == cudaSuccess) e = set_attr<kEpiResidual>();
+  if (e == cudaSuccess) e = set_attr<kEpiResidualLN>();
   return e;
 }
 
@@ -339,17 +484,23 @@ int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const 
   const int total = ((a.tiles_m + 1) / 2) * a.tiles_n;          // tiles of 256 tokens x 192 features
   if (total <= 0) return 0;
   const int clusters = num_sms / 2;
-  const int grid = 2 * (total < clusters ? total : clusters);
+  const int work = epilogue == kEpiResidualLN ? (a.tiles_m + 1) / 2 : total;     // LayerNorm: whole 256-token units
+  const int grid = 2 * (work < clusters ? work : clusters);
   const CUtensorMap& res = tmap_res != nullptr ? *tmap_res : tmap_out;
   switch (epilogue) {
     case kEpiGelu:
-      qre_enc_gemm_kernel<kEpiGelu><<<grid, kThreads, kSmemTotal, st>>>(tmap_a, tmap_w, tmap_out, res, a);
+      qre_enc_gemm_kernel<kEpiGelu><<<grid, kThreads, smem_total(kEpiGelu), st>>>(tmap_a, tmap_w, tmap_out, res, a);
       break;
     case kEpiResidual:
-      qre_enc_gemm_kernel<kEpiResidual><<<grid, kThreads, kSmemTotal, st>>>(tmap_a, tmap_w, tmap_out, res, a);
+      qre_enc_gemm_kernel<kEpiResidual><<<grid, kThreads, smem_total(kEpiResidual), st>>>(tmap_a, tmap_w, tmap_out,
+                                                                                           res, a);
+      break;
+    case kEpiResidualLN:      // caller guarantees tiles_n == 2 (384 features) and ln_g / ln_b set
+      qre_enc_gemm_kernel<kEpiResidualLN><<<grid, kThreads, smem_total(kEpiResidualLN), st>>>(tmap_a, tmap_w, tmap_out,
+                                                                                               res, a);
       break;
     default:
-      qre_enc_gemm_kernel<kEpiBias><<<grid, kThreads, kSmemTotal, st>>>(tmap_a, tmap_w, tmap_out, res, a);
+      qre_enc_gemm_kernel<kEpiBias><<<grid, kThreads, smem_total(kEpiBias), st>>>(tmap_a, tmap_w, tmap_out, res, a);
       break;
   }
   return 1;

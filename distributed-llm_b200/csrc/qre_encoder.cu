@@ -210,6 +210,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // rows at a time and walks the keys 16 at a time with an online softmax; K and V fragments come out
 // of shared memory with ldmatrix (transposed for V), scores and probabilities never leave registers
 // (the accumulator layout of one m16n8k16 product is the A-operand layout of the next).
+// 2^x for x <= 0 or -inf (the online-softmax arguments): the bare MUFU, no range fix-up code
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* row_ptr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
@@ -305,16 +311,16 @@ __device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloa
     bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 1));
     bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 2));
     const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);   // finite: key k0 < L is in every block
-    const float c_lo = exp2f(m_lo - mn_lo), c_hi = exp2f(m_hi - mn_hi);
+    const float c_lo = ex2_fast(m_lo - mn_lo), c_hi = ex2_fast(m_hi - mn_hi);
     m_lo = mn_lo;
     m_hi = mn_hi;
     float p[2][4];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      p[j][0] = exp2f(s[j][0] - mn_lo);
-      p[j][1] = exp2f(s[j][1] - mn_lo);
-      p[j][2] = exp2f(s[j][2] - mn_hi);
-      p[j][3] = exp2f(s[j][3] - mn_hi);
+      p[j][0] = ex2_fast(s[j][0] - mn_lo);
+      p[j][1] = ex2_fast(s[j][1] - mn_lo);
+      p[j][2] = ex2_fast(s[j][2] - mn_hi);
+      p[j][3] = ex2_fast(s[j][3] - mn_hi);
     }
     l_lo = l_lo * c_lo + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
     l_hi = l_hi * c_hi + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
@@ -387,13 +393,18 @@ enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __res
   }
 }
 
-// Appends the indices of sequences longer than `min_len` to long_list (order irrelevant: every
-// sequence is computed independently).  *n_long must be zero on entry.
+constexpr int kMidLen = 64;       // (kShortLen, kMidLen]: CTA-per-head kernel with a small shared-memory footprint
+
+// Sorts the sequences that the warp-per-head kernel does not take into two lists: mid
+// (kShortLen < L <= kMidLen) at list[0 .. n[0]) and long (L > kMidLen) at list[m .. m + n[1]).  Order within a
+// list is irrelevant: every sequence is computed independently.  n[0..1] must be zero on entry.
 __global__ void __launch_bounds__(256)
-enc_find_long_kernel(const int32_t* __restrict__ offsets, int m, int min_len, int32_t* __restrict__ long_list,
-                     int32_t* __restrict__ n_long) {
+enc_find_long_kernel(const int32_t* __restrict__ offsets, int m, int32_t* __restrict__ list, int32_t* __restrict__ n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < m && offsets[i + 1] - offsets[i] > min_len) long_list[atomicAdd(n_long, 1)] = i;
+  if (i >= m) return;
+  const int L = offsets[i + 1] - offsets[i];
+  if (L > kMidLen) list[m + atomicAdd(n + 1, 1)] = i;
+  else if (L > kShortLen) list[atomicAdd(n, 1)] = i;
 }
 
 // Short sequences (0 < L <= kShortLen = 32, the bulk of chat queries): one WARP per (sequence, head),
@@ -495,7 +506,7 @@ struct qre_encoder {
   CUtensorMap map_x, map_ctx, map_h;                       // A operands (128-token boxes)
   CUtensorMap box_qkv, box_y, box_h, box_x;                // epilogue boxes: outputs qkv / y / h, residual x
   int32_t *d_ids = nullptr, *d_off = nullptr;
-  int32_t *long_list = nullptr, *n_long = nullptr;   // sequences longer than kShortLen in the current batch
+  int32_t *long_list = nullptr, *n_long = nullptr;   // sequences longer than kShortLen in the current batch: two buckets
   float* d_out = nullptr;
   int32_t *h_ids = nullptr, *h_off = nullptr;     // pinned staging of the host entry point
   float* h_out = nullptr;
@@ -560,12 +571,16 @@ void free_linear(Linear& L) {
 }
 
 int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_t T, const CUtensorMap& box_out,
-               const CUtensorMap* box_res, int epi, cudaStream_t st) {
+               const CUtensorMap* box_res, int epi, cudaStream_t st, const float* ln_g = nullptr,
+               const float* ln_b = nullptr) {
   EncGemmArgs a;
   a.num_kb = L.k / kEncBK;
   a.tiles_m = static_cast<int>((T + kEncBM - 1) / kEncBM);
   a.tiles_n = (L.n + kEncBN - 1) / kEncBN;
   a.bias = L.b;
+  a.ln_g = ln_g;
+  a.ln_b = ln_b;
+  a.ln_eps = e->cfg.ln_eps;
   return launch_enc_gemm(map_a, L.map, box_out, box_res, a, epi, e->num_sms, st);
 }
 
@@ -585,19 +600,23 @@ int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len,
     enc_attention_short_kernel<64><<<grid_s, 128, attention_short_smem(64, Ls), st>>>(e->qkv, offsets, e->ctx, H,
                                                                                       e->cfg.heads, Ls, scale_log2e);
   ++n;
-  if (max_len > kShortLen) {   // the batch has longer sequences (listed in e->long_list by encode_on_device)
-    const int Lp = (max_len + 15) & ~15;
+  // longer sequences (listed by enc_find_long_kernel): CTA per (sequence, head), once for the mid bucket with
+  // a 64-row footprint (many CTAs per SM) and once, if the batch has any, for the long bucket
+  for (int bucket = 0; bucket < 2; ++bucket) {
+    if (max_len <= (bucket == 0 ? kShortLen : kMidLen)) break;
+    const int Lp = bucket == 0 ? (((max_len < kMidLen ? max_len : kMidLen) + 15) & ~15) : ((max_len + 15) & ~15);
     const size_t smem = attention_smem(e->hd, Lp);
     int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
-    per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+    per_sm = per_sm < 1 ? 1 : (per_sm > 16 ? 16 : per_sm);
     int gx = (e->num_sms * per_sm + e->cfg.heads - 1) / e->cfg.heads;
     gx = gx < 1 ? 1 : (gx > m ? m : gx);
     const dim3 grid(gx, e->cfg.heads);
+    const int32_t* list = e->long_list + (bucket == 0 ? 0 : m);
     if (e->hd == 32)
-      enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, e->long_list, e->n_long, e->ctx, H, Lp,
+      enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, list, e->n_long + bucket, e->ctx, H, Lp,
                                                         scale_log2e);
     else
-      enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, e->long_list, e->n_long, e->ctx, H, Lp,
+      enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, list, e->n_long + bucket, e->ctx, H, Lp,
                                                         scale_log2e);
     ++n;
   }
@@ -611,8 +630,8 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
   const int H = c.hidden;
   if (T > 0) {
     if (max_len > kShortLen) {
-      ENC_CUDA(cudaMemsetAsync(e->n_long, 0, sizeof(int32_t), st));
-      enc_find_long_kernel<<<(m + 255) / 256, 256, 0, st>>>(offsets, m, kShortLen, e->long_list, e->n_long);
+      ENC_CUDA(cudaMemsetAsync(e->n_long, 0, 2 * sizeof(int32_t), st));
+      enc_find_long_kernel<<<(m + 255) / 256, 256, 0, st>>>(offsets, m, e->long_list, e->n_long);
       ++e->launches;
     }
     enc_embed_ln_kernel<<<m, 256, 0, st>>>(ids, offsets, e->word, e->pos, e->type, e->eln_g, e->eln_b, c.ln_eps, H,
@@ -622,11 +641,19 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
       Layer& L = e->layers[l];
       e->launches += run_linear(e, e->map_x, L.qkv, T, e->box_qkv, nullptr, kEpiBias, st);
       e->launches += launch_attention(e, m, offsets, max_len, st);
-      e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_y, &e->box_x, kEpiResidual, st);
-      e->launches += launch_layernorm(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x, st);
-      e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
-      e->launches += run_linear(e, e->map_h, L.down, T, e->box_y, &e->box_x, kEpiResidual, st);
-      e->launches += launch_layernorm(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x, st);
+      if (H == 2 * kEncBN) {
+        // hidden 384 = two feature tiles = the two TMEM accumulators: LayerNorm runs in the projection's
+        // epilogue and the result replaces the residual rows of x it was computed from
+        e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln1_g, L.ln1_b);
+        e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
+        e->launches += run_linear(e, e->map_h, L.down, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln2_g, L.ln2_b);
+      } else {
+        e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_y, &e->box_x, kEpiResidual, st);
+        e->launches += launch_layernorm(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x, st);
+        e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
+        e->launches += run_linear(e, e->map_h, L.down, T, e->box_y, &e->box_x, kEpiResidual, st);
+        e->launches += launch_layernorm(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x, st);
+      }
     }
   }
   enc_pool_kernel<<<m, 128, 0, st>>>(e->x, offsets, H, normalize, out);
@@ -751,8 +778,8 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   ENC_TRY(cudaMalloc(&e->d_ids, sizeof(int32_t) * max_tokens));
   ENC_TRY(cudaMalloc(&e->d_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
   ENC_TRY(cudaMalloc(&e->d_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
-  ENC_TRY(cudaMalloc(&e->long_list, sizeof(int32_t) * static_cast<size_t>(max_seqs)));
-  ENC_TRY(cudaMalloc(&e->n_long, sizeof(int32_t)));
+  ENC_TRY(cudaMalloc(&e->long_list, 2 * sizeof(int32_t) * static_cast<size_t>(max_seqs)));
+  ENC_TRY(cudaMalloc(&e->n_long, 2 * sizeof(int32_t)));
   ENC_TRY(cudaMallocHost(&e->h_ids, sizeof(int32_t) * max_tokens));
   ENC_TRY(cudaMallocHost(&e->h_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
   ENC_TRY(cudaMallocHost(&e->h_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
@@ -870,12 +897,15 @@ int qre_encoder_launch_count(const qre_encoder_t* e, int64_t* count) {
 }
 
 int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, const float* w, const float* bias,
-                           const float* residual, int epilogue, float* c) {
+                           const float* residual, int epilogue, const float* ln_g, const float* ln_b, float ln_eps,
+                           float* c) {
   if (rows <= 0 || n <= 0 || k <= 0 || n % 8 != 0 || k % 64 != 0)
     return set_error(QRE_ERR_INVALID, "debug_gemm: need rows > 0, n %% 8 == 0, k %% 64 == 0");
-  if (a == nullptr || w == nullptr || bias == nullptr || c == nullptr || (epilogue == kEpiResidual && residual == nullptr))
+  if (a == nullptr || w == nullptr || bias == nullptr || c == nullptr || (epilogue >= kEpiResidual && residual == nullptr))
     return set_error(QRE_ERR_INVALID, "null argument");
-  if (epilogue < 0 || epilogue > 2) return set_error(QRE_ERR_INVALID, "debug_gemm: epilogue must be 0, 1 or 2");
+  if (epilogue < 0 || epilogue > 3) return set_error(QRE_ERR_INVALID, "debug_gemm: epilogue must be 0..3");
+  if (epilogue == kEpiResidualLN && (n != 2 * kEncBN || ln_g == nullptr || ln_b == nullptr))
+    return set_error(QRE_ERR_INVALID, "debug_gemm: the LayerNorm epilogue needs n == %d and ln_g / ln_b", 2 * kEncBN);
   ENC_CUDA(cudaSetDevice(device));
   cudaDeviceProp prop;
   ENC_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -889,7 +919,7 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   if (residual != nullptr)
     for (size_t i = 0; i < static_cast<size_t>(rows) * n; ++i) rb[i] = __float2bfloat16(residual[i]);
   __nv_bfloat16 *da = nullptr, *dw = nullptr, *dr = nullptr, *dc = nullptr;
-  float* db = nullptr;
+  float *db = nullptr, *dg = nullptr, *dbeta = nullptr;
   int rc = QRE_OK;
   auto cleanup = [&]() {
     cudaFree(da);
@@ -897,6 +927,8 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
     cudaFree(dr);
     cudaFree(dc);
     cudaFree(db);
+    cudaFree(dg);
+    cudaFree(dbeta);
   };
 #define DBG_TRY(expr)                                                                              \
   do {                                                                                             \
@@ -916,6 +948,12 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   DBG_TRY(cudaMemcpy(dw, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
   DBG_TRY(cudaMemcpy(dr, rb.data(), rb.size() * 2, cudaMemcpyHostToDevice));
   DBG_TRY(cudaMemcpy(db, bias, n * sizeof(float), cudaMemcpyHostToDevice));
+  if (epilogue == kEpiResidualLN) {
+    DBG_TRY(cudaMalloc(&dg, n * sizeof(float)));
+    DBG_TRY(cudaMalloc(&dbeta, n * sizeof(float)));
+    DBG_TRY(cudaMemcpy(dg, ln_g, n * sizeof(float), cudaMemcpyHostToDevice));
+    DBG_TRY(cudaMemcpy(dbeta, ln_b, n * sizeof(float), cudaMemcpyHostToDevice));
+  }
   CUtensorMap ma, mw, mo, mr;
   rc = make_tensor_map_bf16(&ma, da, k, rows_pad, kEncBK, kEncBM);
   if (rc == QRE_OK) rc = make_tensor_map_bf16(&mw, dw, k, n_pad, kEncBK, kEncBN / 2);
@@ -930,6 +968,9 @@ int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, c
   g.tiles_m = static_cast<int>(rows_pad / kEncBM);
   g.tiles_n = static_cast<int>(n_pad / kEncBN);
   g.bias = db;
+  g.ln_g = dg;
+  g.ln_b = dbeta;
+  g.ln_eps = ln_eps;
   launch_enc_gemm(ma, mw, mo, &mr, g, epilogue, prop.multiProcessorCount, nullptr);
   DBG_TRY(cudaGetLastError());
   DBG_TRY(cudaDeviceSynchronize());

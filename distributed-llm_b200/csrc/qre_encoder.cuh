@@ -18,12 +18,16 @@ constexpr int kEncBK = 64;
 constexpr int kEncStages = 6;
 constexpr int kEncRowPad = 256;    // activation buffers are padded to whole CTA-pair tiles (2 x 128 tokens)
 
-enum EncEpilogue { kEpiBias = 0, kEpiGelu = 1, kEpiResidual = 2 };
+enum EncEpilogue { kEpiBias = 0, kEpiGelu = 1, kEpiResidual = 2, kEpiResidualLN = 3 };
 
 struct EncGemmArgs {
   int num_kb;                    // input features / 64
   int tiles_m, tiles_n;          // ceil(tokens / 128), ceil(features / 192)
   const float* bias;             // [tiles_n * 192], zero padded
+  // kEpiResidualLN only (features == 384 = two feature tiles): out = LayerNorm(acc + bias + residual)
+  const float* ln_g = nullptr;   // [384]
+  const float* ln_b = nullptr;   // [384]
+  float ln_eps = 0.f;
 };
 // Output / residual boxes of the GEMM epilogue: 32 tokens x 64 features, 128-byte swizzle.
 constexpr int kEncBoxRows = 32;

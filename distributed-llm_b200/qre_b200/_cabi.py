@@ -507,15 +507,19 @@ class Encoder:
         return n.value
 
 
-def encoder_debug_gemm(a, w, bias, residual=None, epilogue: int = 0, device: int = 0) -> np.ndarray:
+def encoder_debug_gemm(a, w, bias, residual=None, epilogue: int = 0, device: int = 0, ln_g=None, ln_b=None,
+                       ln_eps: float = 0.0) -> np.ndarray:
     a, w, bias = _arr(a, np.float32), _arr(w, np.float32), _arr(bias, np.float32)
     rows, k = a.shape
     n = w.shape[0]
     res = None if residual is None else _arr(residual, np.float32, (rows, n))
     out = np.empty((rows, n), np.float32)
     lib = load()
+    g = None if ln_g is None else _arr(ln_g, np.float32, (n,))
+    b = None if ln_b is None else _arr(ln_b, np.float32, (n,))
     _check(lib, lib.qre_encoder_debug_gemm(C.c_int(device), C.c_int(rows), C.c_int(n), C.c_int(k), _ptr(a), _ptr(w),
-                                           _ptr(bias), _ptr(res), C.c_int(epilogue), _ptr(out)))
+                                           _ptr(bias), _ptr(res), C.c_int(epilogue), _ptr(g), _ptr(b),
+                                           C.c_float(ln_eps), _ptr(out)))
     return out
 
 

@@ -92,9 +92,11 @@ QRE_API int qre_encoder_launch_count(const qre_encoder_t* e, int64_t* count);
 /* ---- bring-up / test hooks (no counterpart in the reference) --------------------------------
  * C[rows, n] = epilogue(A[rows, k] * W[n, k]^T + bias) through the encoder's tcgen05 GEMM kernel,
  * host fp32 in/out (A and W are rounded to bf16 on the way in, C is bf16 rounded on the way
- * out).  epilogue: 0 = bias, 1 = bias + exact GELU, 2 = bias + residual[rows, n]. */
+ * out).  epilogue: 0 = bias, 1 = bias + exact GELU, 2 = bias + residual[rows, n],
+ * 3 = LayerNorm(bias + residual) with ln_g / ln_b / ln_eps (n must be 384; NULL / 0 otherwise). */
 QRE_API int qre_encoder_debug_gemm(int device, int rows, int n, int k, const float* a, const float* w,
-                                   const float* bias, const float* residual, int epilogue, float* c);
+                                   const float* bias, const float* residual, int epilogue, const float* ln_g,
+                                   const float* ln_b, float ln_eps, float* c);
 
 /* ---- WordPiece on host threads --------------------------------------------------------------
  * BERT uncased tokenisation (BasicTokenizer + greedy longest-match-first WordPiece), the step

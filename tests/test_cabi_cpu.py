@@ -45,7 +45,7 @@ def test_encoder_structs_and_arguments():
     bad = _cabi.EncoderConfig(heads=5)
     assert lib.qre_encoder_create(0, ctypes.byref(bad), ctypes.c_int64(128), 4, ctypes.byref(h)) == 1
     assert lib.qre_encoder_destroy(None) == 0
-    assert lib.qre_encoder_debug_gemm(0, 4, 30, 64, None, None, None, None, 0, None) == 1
+    assert lib.qre_encoder_debug_gemm(0, 4, 30, 64, None, None, None, None, 0, None, None, ctypes.c_float(0), None) == 1
 
 
 def test_encoder_without_device_fails_loudly():

@@ -52,6 +52,29 @@ def test_gemm_hook_matches_numpy(rows, n, k, epi):
     assert not bad.any(), (int(bad.sum()), float(np.abs(got - ref).max()))
 
 
+@pytest.mark.parametrize("rows,k", [(1, 384), (300, 384), (1000, 1536), (20000, 384)])
+def test_gemm_hook_layernorm_epilogue(rows, k):
+    """Epilogue 3: LayerNorm(x W^T + bias + residual) over 384 features inside the projection kernel."""
+    from qre_b200 import _cabi
+    rs = np.random.Generator(np.random.PCG64(rows + k))
+    n = 384
+    a = _bf16(rs.standard_normal((rows, k)).astype(np.float32))
+    w = _bf16((rs.standard_normal((n, k)) / np.sqrt(k)).astype(np.float32))
+    bias = rs.standard_normal(n).astype(np.float32)
+    res = _bf16((2.0 * rs.standard_normal((rows, n)) + 0.5).astype(np.float32))
+    g = (1.0 + 0.2 * rs.standard_normal(n)).astype(np.float32)
+    b = rs.standard_normal(n).astype(np.float32)
+    got = _cabi.encoder_debug_gemm(a, w, bias, res, 3, ln_g=g, ln_b=b, ln_eps=1e-12)
+    y = a.astype(np.float64) @ w.astype(np.float64).T + bias + res
+    mu, sd = y.mean(1, keepdims=True), y.std(1, keepdims=True)
+    ref = (y - mu) / sd * g + b
+    # the kernel rounds y to bf16 before normalising (error 2^-9 |y|, i.e. 2^-9 (|ref - b| + |g mu| / sd) after
+    # the scaling) and rounds the result to bf16 again (2^-9 |ref|); factor 2 of slack on both
+    tol = 2.0 ** -8 * np.abs(ref) + 2.0 ** -8 * (np.abs(ref - b) + np.abs(g) * np.abs(mu) / sd) + 2e-3
+    bad = np.abs(got - ref) > tol
+    assert not bad.any(), (int(bad.sum()), float(np.abs(got - ref).max()))
+
+
 def _check(cfg_o, ccfg, lens, seed, normalize=True):
     from qre_b200 import _cabi
     w = MO.random_weights(cfg_o, seed=seed)
