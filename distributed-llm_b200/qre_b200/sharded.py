@@ -162,6 +162,54 @@ class ShardedLookup:
         self.done[b] = ev
         return out, ev
 
+    @staticmethod
+    def split_sequences(m: int, world: int):
+        """Sequence ranges [i0, i1) per rank for data-parallel embedding: equal COUNTS (the all-gather
+        needs equal slices), the last ranks padded with empty sequences when world does not divide m."""
+        per = (m + world - 1) // world
+        return [(min(m, r * per), min(m, (r + 1) * per)) for r in range(world)], per
+
+    def embed_ids(self, enc, ids: np.ndarray, offsets: np.ndarray, normalize: bool = True):
+        """Data-parallel embedding in front of the row-sharded lookup (SURVEY §8f-1 + §8e): the batch's
+        token ids are replicated on the hosts (like the queries of `step` were); rank r embeds the
+        sequences of its slice with the on-GPU encoder `enc` (a `_cabi.Encoder`), and one all-gather of
+        the fp32 rows (m x hidden x 4 bytes, 6 MB at 4096 x 384) gives every rank the full [m, hidden]
+        query matrix `step` takes.  Embeddings do not depend on batch composition, so the result is
+        bit-identical to embedding everything on one GPU.  Returns the device tensor (no sync)."""
+        torch = self.torch
+        m = offsets.shape[0] - 1
+        ranges, per = self.split_sequences(m, self.world)
+        i0, i1 = ranges[self.rank]
+        H = enc.cfg.hidden
+        if getattr(self, "_q_all", None) is None or self._q_all.shape[0] != per * self.world:
+            self._q_all = torch.zeros((per * self.world, H), dtype=torch.float32, device=self.dev)
+            self._ids_pin = torch.empty(enc.max_tokens, dtype=torch.int32).pin_memory()
+            self._off_pin = torch.empty(per + 1, dtype=torch.int32).pin_memory()
+            self._ids_dev = torch.empty(enc.max_tokens, dtype=torch.int32, device=self.dev)
+            self._off_dev = torch.empty(per + 1, dtype=torch.int32, device=self.dev)
+        n = i1 - i0
+        T = int(offsets[i1] - offsets[i0])
+        if n > enc.max_seqs or T > enc.max_tokens:
+            raise _cabi.QreError(f"rank slice of {n} sequences / {T} tokens exceeds the encoder's capacity")
+        st = torch.cuda.current_stream(self.dev)
+        mine = self._q_all[self.rank * per:(self.rank + 1) * per]
+        if n > 0:
+            if getattr(self, "_h2d_done", None) is not None:
+                self._h2d_done.synchronize()        # the previous batch's ids have left the pinned buffers
+            self._ids_pin[:T].copy_(torch.from_numpy(np.ascontiguousarray(ids[offsets[i0]:offsets[i1]], np.int32)))
+            self._off_pin[:n + 1].copy_(torch.from_numpy((offsets[i0:i1 + 1] - offsets[i0]).astype(np.int32)))
+            self._ids_dev[:T].copy_(self._ids_pin[:T], non_blocking=True)
+            self._off_dev[:n + 1].copy_(self._off_pin[:n + 1], non_blocking=True)
+            self._h2d_done = torch.cuda.Event()
+            self._h2d_done.record(st)
+            max_len = int(np.diff(offsets[i0:i1 + 1]).max())
+            enc.encode_dev(n, self._ids_dev.data_ptr(), self._off_dev.data_ptr(), T, max_len, mine.data_ptr(),
+                           normalize=normalize, stream=st.cuda_stream or 1)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self._q_all.view(-1), mine.reshape(-1), group=self.group)
+        return self._q_all[:m]
+
     def drain(self):
         """Make the current stream wait for every pipelined batch issued so far."""
         main = self.torch.cuda.current_stream(self.dev)

@@ -71,3 +71,16 @@ def test_merge_comparator_ties_and_empties():
     m = sharded.merge_candidates_host(c)
     assert m["slot"][0, :3].tolist() == [2, 9, 5] and m["shard"][0, :3].tolist() == [1, 1, 0]
     assert m["slot"][0, 3] == -1
+
+
+def test_split_sequences_covers_the_batch_in_equal_slices():
+    """Partition used by the data-parallel embedder in front of the sharded lookup (ShardedLookup.embed_ids)."""
+    from qre_b200.sharded import ShardedLookup
+    for m in (0, 1, 3, 61, 4096, 4097):
+        for world in (1, 2, 3, 4, 8):
+            ranges, per = ShardedLookup.split_sequences(m, world)
+            assert len(ranges) == world and per * world >= m
+            assert ranges[0][0] == 0 and ranges[-1][1] == m
+            assert all(a1 == b0 for (_, a1), (b0, _) in zip(ranges, ranges[1:]))
+            assert all(0 <= i1 - i0 <= per for i0, i1 in ranges)
+            assert all(i0 == min(m, r * per) for r, (i0, _) in enumerate(ranges))     # slice r starts at r * per

@@ -88,6 +88,26 @@ def _worker(rank, world, port, ret):
         for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf"):
             ok = ok and np.array_equal(o[k].cpu().numpy(), serial[i][k])
     torch.cuda.synchronize()
+    # data-parallel embedding in front of the lookup: each rank embeds half of the sequences, one all-gather,
+    # and the [m, hidden] matrix equals what a single encoder call over the whole batch produces, bit for bit
+    from oracle import minilm_oracle as MO
+    eo = MO.EncoderConfig(vocab_size=500, hidden=384, layers=1, heads=12, intermediate=384, max_positions=64,
+                          max_seq_len=48)
+    enc = _cabi.Encoder(_cabi.EncoderConfig(500, 384, 1, 12, 384, 64, 2, 1e-12, 48), MO.random_weights(eo, seed=9),
+                        max_tokens=4096, max_seqs=64, device=rank)
+    rs = np.random.Generator(np.random.PCG64(12))
+    lens = rs.integers(1, 48, 61)                                    # 61: world does not divide it
+    seqs = [rs.integers(0, 500, n).astype(np.int32) for n in lens]
+    off = np.zeros(62, np.int32)
+    off[1:] = np.cumsum(lens)
+    whole = enc.encode_ids(seqs)
+    for _ in range(2):
+        q_all = look.embed_ids(enc, np.concatenate(seqs), off)
+        torch.cuda.synchronize()
+        ok = ok and np.array_equal(q_all.cpu().numpy(), whole)
+    want = MO.encode_ids(MO.random_weights(eo, seed=9), seqs[:4], eo)
+    ok = ok and float((whole[:4] * want).sum(1).min()) > 0.999
+    enc.close()
     ret[rank] = (bool(ok), int(hit.sum()))
     dist.barrier()
     dist.destroy_process_group()
