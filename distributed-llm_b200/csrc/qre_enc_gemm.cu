@@ -185,6 +185,8 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();                     // the next kernel of the chain may start its own set-up
+  pdl_wait();                                  // everything above overlapped the previous kernel's tail
   const int npairs = (a.tiles_m + 1) >> 1;     // pairs of 128-token blocks
   // The j-th tile of this cluster.  Default: tiles dealt round-robin, feature tile fastest.  LayerNorm
   // epilogue: whole 256-token units (both feature tiles, so one CTA sees complete rows), units round-robin.
@@ -480,27 +482,31 @@ cudaError_t enc_gemm_init() {
 }
 
 int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const CUtensorMap& tmap_out,
-                    const CUtensorMap* tmap_res, const EncGemmArgs& a, int epilogue, int num_sms, cudaStream_t st) {
+                    const CUtensorMap* tmap_res, const EncGemmArgs& a, int epilogue, int num_sms, cudaStream_t st,
+                    bool after_kernel) {
   const int total = ((a.tiles_m + 1) / 2) * a.tiles_n;          // tiles of 256 tokens x 192 features
   if (total <= 0) return 0;
   const int clusters = num_sms / 2;
   const int work = epilogue == kEpiResidualLN ? (a.tiles_m + 1) / 2 : total;     // LayerNorm: whole 256-token units
   const int grid = 2 * (work < clusters ? work : clusters);
   const CUtensorMap& res = tmap_res != nullptr ? *tmap_res : tmap_out;
+  const dim3 g(grid), blk(kThreads);
   switch (epilogue) {
     case kEpiGelu:
-      qre_enc_gemm_kernel<kEpiGelu><<<grid, kThreads, smem_total(kEpiGelu), st>>>(tmap_a, tmap_w, tmap_out, res, a);
+      launch_chain(qre_enc_gemm_kernel<kEpiGelu>, g, blk, smem_total(kEpiGelu), st, after_kernel, tmap_a, tmap_w, tmap_out,
+                   res, a);
       break;
     case kEpiResidual:
-      qre_enc_gemm_kernel<kEpiResidual><<<grid, kThreads, smem_total(kEpiResidual), st>>>(tmap_a, tmap_w, tmap_out,
-                                                                                           res, a);
+      launch_chain(qre_enc_gemm_kernel<kEpiResidual>, g, blk, smem_total(kEpiResidual), st, after_kernel, tmap_a, tmap_w,
+                   tmap_out, res, a);
       break;
     case kEpiResidualLN:      // caller guarantees tiles_n == 2 (384 features) and ln_g / ln_b set
-      qre_enc_gemm_kernel<kEpiResidualLN><<<grid, kThreads, smem_total(kEpiResidualLN), st>>>(tmap_a, tmap_w, tmap_out,
-                                                                                               res, a);
+      launch_chain(qre_enc_gemm_kernel<kEpiResidualLN>, g, blk, smem_total(kEpiResidualLN), st, after_kernel, tmap_a,
+                   tmap_w, tmap_out, res, a);
       break;
     default:
-      qre_enc_gemm_kernel<kEpiBias><<<grid, kThreads, smem_total(kEpiBias), st>>>(tmap_a, tmap_w, tmap_out, res, a);
+      launch_chain(qre_enc_gemm_kernel<kEpiBias>, g, blk, smem_total(kEpiBias), st, after_kernel, tmap_a, tmap_w, tmap_out,
+                   res, a);
       break;
   }
   return 1;

@@ -79,6 +79,8 @@ __global__ void __launch_bounds__(256)
 enc_embed_ln_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ offsets, const float* __restrict__ word,
                     const float* __restrict__ pos, const float* __restrict__ type0, const float* __restrict__ g,
                     const float* __restrict__ b, float eps, int H, int vocab, __nv_bfloat16* __restrict__ x) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int seq = blockIdx.x;
   const int t0 = offsets[seq], L = offsets[seq + 1] - t0;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -107,6 +109,8 @@ enc_embed_ln_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__
 __global__ void __launch_bounds__(256)
 enc_layernorm_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
                      float eps, int H, long long T, __nv_bfloat16* __restrict__ x) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long t = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (t >= T) return;
   const int lane = threadIdx.x & 31, pairs = H / 64;
@@ -128,6 +132,8 @@ template <int kChunks>
 __global__ void __launch_bounds__(256)
 enc_layernorm_wide_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
                           float eps, long long T, __nv_bfloat16* __restrict__ x) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int H = 64 * kChunks;
   const int lane = threadIdx.x & 31, gl = lane & 7;
   const long long t = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4 + (lane >> 3);
@@ -182,13 +188,14 @@ enc_layernorm_wide_kernel(const __nv_bfloat16* __restrict__ y, const float* __re
 
 int launch_layernorm(const __nv_bfloat16* y, const float* g, const float* b, float eps, int H, long long T,
                      __nv_bfloat16* x, cudaStream_t st) {
-  const int wide_grid = static_cast<int>((T + 31) / 32);      // 8 warps x 4 tokens per CTA
+  const dim3 wide_grid(static_cast<unsigned>((T + 31) / 32));      // 8 warps x 4 tokens per CTA
   if (H == 384)
-    enc_layernorm_wide_kernel<6><<<wide_grid, 256, 0, st>>>(y, g, b, eps, T, x);
+    launch_chain(enc_layernorm_wide_kernel<6>, wide_grid, dim3(256), 0, st, true, y, g, b, eps, T, x);
   else if (H == 768)
-    enc_layernorm_wide_kernel<12><<<wide_grid, 256, 0, st>>>(y, g, b, eps, T, x);
+    launch_chain(enc_layernorm_wide_kernel<12>, wide_grid, dim3(256), 0, st, true, y, g, b, eps, T, x);
   else
-    enc_layernorm_kernel<<<static_cast<int>((T + 7) / 8), 256, 0, st>>>(y, g, b, eps, H, T, x);
+    launch_chain(enc_layernorm_kernel, dim3(static_cast<unsigned>((T + 7) / 8)), dim3(256), 0, st, true, y, g, b, eps, H, T,
+                 x);
   return 1;
 }
 
@@ -370,6 +377,8 @@ __global__ void __launch_bounds__(128)
 enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
                      const int32_t* __restrict__ long_list, const int32_t* __restrict__ n_long,
                      __nv_bfloat16* __restrict__ ctx, int H, int Lp, float scale_log2e) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int KS = HD + 8;
   extern __shared__ __align__(16) uint8_t att_smem[];
   __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(att_smem);
@@ -400,6 +409,8 @@ constexpr int kMidLen = 64;       // (kShortLen, kMidLen]: CTA-per-head kernel w
 // list is irrelevant: every sequence is computed independently.  n[0..1] must be zero on entry.
 __global__ void __launch_bounds__(256)
 enc_find_long_kernel(const int32_t* __restrict__ offsets, int m, int32_t* __restrict__ list, int32_t* __restrict__ n) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const int L = offsets[i + 1] - offsets[i];
@@ -415,6 +426,8 @@ template <int HD>
 __global__ void __launch_bounds__(128)
 enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ offsets,
                            __nv_bfloat16* __restrict__ ctx, int H, int heads, int Lp, float scale_log2e) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int KS = HD + 8;
   extern __shared__ __align__(16) uint8_t att_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -440,6 +453,8 @@ enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t*
 __global__ void __launch_bounds__(128)
 enc_pool_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ offsets, int H, int normalize,
                 float* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[4];
   const int seq = blockIdx.x;
   const int t0 = offsets[seq], L = offsets[seq + 1] - t0;
@@ -581,7 +596,7 @@ int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_
   a.ln_g = ln_g;
   a.ln_b = ln_b;
   a.ln_eps = e->cfg.ln_eps;
-  return launch_enc_gemm(map_a, L.map, box_out, box_res, a, epi, e->num_sms, st);
+  return launch_enc_gemm(map_a, L.map, box_out, box_res, a, epi, e->num_sms, st, true);
 }
 
 size_t attention_short_smem(int hd, int Lp) { return 4 * attention_smem(hd, Lp); }
@@ -593,12 +608,13 @@ int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len,
   // sequences of up to kShortLen tokens: warp per head
   const int Ls = ((max_len < kShortLen ? max_len : kShortLen) + 15) & ~15;
   const dim3 grid_s(m, (e->cfg.heads + 3) / 4);
+  const __nv_bfloat16* qkv = e->qkv;
   if (e->hd == 32)
-    enc_attention_short_kernel<32><<<grid_s, 128, attention_short_smem(32, Ls), st>>>(e->qkv, offsets, e->ctx, H,
-                                                                                      e->cfg.heads, Ls, scale_log2e);
+    launch_chain(enc_attention_short_kernel<32>, grid_s, dim3(128), attention_short_smem(32, Ls), st, true, qkv, offsets,
+                 e->ctx, H, e->cfg.heads, Ls, scale_log2e);
   else
-    enc_attention_short_kernel<64><<<grid_s, 128, attention_short_smem(64, Ls), st>>>(e->qkv, offsets, e->ctx, H,
-                                                                                      e->cfg.heads, Ls, scale_log2e);
+    launch_chain(enc_attention_short_kernel<64>, grid_s, dim3(128), attention_short_smem(64, Ls), st, true, qkv, offsets,
+                 e->ctx, H, e->cfg.heads, Ls, scale_log2e);
   ++n;
   // longer sequences (listed by enc_find_long_kernel): CTA per (sequence, head), once for the mid bucket with
   // a 64-row footprint (many CTAs per SM) and once, if the batch has any, for the long bucket
@@ -612,12 +628,13 @@ int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len,
     gx = gx < 1 ? 1 : (gx > m ? m : gx);
     const dim3 grid(gx, e->cfg.heads);
     const int32_t* list = e->long_list + (bucket == 0 ? 0 : m);
+    const int32_t* cnt = e->n_long + bucket;
     if (e->hd == 32)
-      enc_attention_kernel<32><<<grid, 128, smem, st>>>(e->qkv, offsets, list, e->n_long + bucket, e->ctx, H, Lp,
-                                                        scale_log2e);
+      launch_chain(enc_attention_kernel<32>, grid, dim3(128), smem, st, true, qkv, offsets, list, cnt, e->ctx, H, Lp,
+                   scale_log2e);
     else
-      enc_attention_kernel<64><<<grid, 128, smem, st>>>(e->qkv, offsets, list, e->n_long + bucket, e->ctx, H, Lp,
-                                                        scale_log2e);
+      launch_chain(enc_attention_kernel<64>, grid, dim3(128), smem, st, true, qkv, offsets, list, cnt, e->ctx, H, Lp,
+                   scale_log2e);
     ++n;
   }
   return n;
@@ -628,14 +645,18 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
                      int normalize, float* out, cudaStream_t st) {
   const qre_encoder_config_t& c = e->cfg;
   const int H = c.hidden;
+  bool chained = false;                  // has a kernel of this batch been launched yet (see launch_chain)
   if (T > 0) {
     if (max_len > kShortLen) {
       ENC_CUDA(cudaMemsetAsync(e->n_long, 0, 2 * sizeof(int32_t), st));
-      enc_find_long_kernel<<<(m + 255) / 256, 256, 0, st>>>(offsets, m, e->long_list, e->n_long);
+      launch_chain(enc_find_long_kernel, dim3((m + 255) / 256), dim3(256), 0, st, false, offsets, m, e->long_list,
+                   e->n_long);
+      chained = true;
       ++e->launches;
     }
-    enc_embed_ln_kernel<<<m, 256, 0, st>>>(ids, offsets, e->word, e->pos, e->type, e->eln_g, e->eln_b, c.ln_eps, H,
-                                           c.vocab_size, e->x);
+    launch_chain(enc_embed_ln_kernel, dim3(m), dim3(256), 0, st, chained, ids, offsets, e->word, e->pos, e->type,
+                 e->eln_g, e->eln_b, c.ln_eps, H, c.vocab_size, e->x);
+    chained = true;
     ++e->launches;
     for (int l = 0; l < c.layers; ++l) {
       Layer& L = e->layers[l];
@@ -646,7 +667,14 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
         // epilogue and the result replaces the residual rows of x it was computed from
         e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln1_g, L.ln1_b);
         e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
-        e->launches += run_linear(e, e->map_h, L.down, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln2_g, L.ln2_b);
+        if (2 * ((T + 255) / 256) >= e->num_sms / 2) {
+          e->launches += run_linear(e, e->map_h, L.down, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln2_g, L.ln2_b);
+        } else {
+          // few tokens (online batches): the fused form would walk both feature tiles' 24 k-steps each on one
+          // CTA pair, one after the other; separate tiles run side by side on two pairs, LayerNorm after
+          e->launches += run_linear(e, e->map_h, L.down, T, e->box_y, &e->box_x, kEpiResidual, st);
+          e->launches += launch_layernorm(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x, st);
+        }
       } else {
         e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_y, &e->box_x, kEpiResidual, st);
         e->launches += launch_layernorm(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x, st);
@@ -656,7 +684,7 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
       }
     }
   }
-  enc_pool_kernel<<<m, 128, 0, st>>>(e->x, offsets, H, normalize, out);
+  launch_chain(enc_pool_kernel, dim3(m), dim3(128), 0, st, chained, e->x, offsets, H, normalize, out);
   ++e->launches;
   ENC_CUDA(cudaGetLastError());
   return QRE_OK;

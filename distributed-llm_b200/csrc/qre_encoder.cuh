@@ -39,7 +39,37 @@ cudaError_t enc_gemm_init();
 // unless epilogue == kEpiResidual.  Rows past the batch's tokens are computed and stored like any
 // other (the buffers are padded); features past the tensor's width are clipped by the TMA unit.
 int launch_enc_gemm(const CUtensorMap& tmap_a, const CUtensorMap& tmap_w, const CUtensorMap& tmap_out,
-                    const CUtensorMap* tmap_res, const EncGemmArgs& a, int epilogue, int num_sms, cudaStream_t st);
+                    const CUtensorMap* tmap_res, const EncGemmArgs& a, int epilogue, int num_sms, cudaStream_t st,
+                    bool after_kernel = false);
+
+// ---- programmatic dependent launch ------------------------------------------------------------
+// The encoder is a chain of ~45 short kernels on one stream.  Each is launched with the
+// "programmatic stream serialization" attribute: its CTAs may be scheduled (and run their set-up:
+// barrier init, TMEM allocation, descriptor prefetch) while the previous kernel is still draining,
+// and wait in pdl_wait() until that kernel has completed and its writes are visible.  Rules every
+// kernel of the chain follows: pdl_launch_dependents() first, then pdl_wait() before the first global
+// read OR write — every link waits, so completion is transitive along the chain.  Without the launch
+// attribute both instructions do nothing.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                bool after_kernel, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = after_kernel ? 1 : 0;      // the first kernel of a chain follows copies / unrelated work: plain launch
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 // Sets the thread's last-error string (qre_last_error) and returns `code`.
 int set_error(int code, const char* fmt, ...);
