@@ -302,15 +302,15 @@ __device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloa
         mma_16816(s[j], qa[2 * k2 + 1], kf[2], kf[3]);
       }
     }
-    // scale into the log2 domain and mask the padded keys
+    if (k0 + 16 > L) {                    // only the last key block has padded keys to mask
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int key = k0 + j * 8 + 2 * t;
-      s[j][0] = key < L ? s[j][0] * scale_log2e : ninf;
-      s[j][2] = key < L ? s[j][2] * scale_log2e : ninf;
-      s[j][1] = key + 1 < L ? s[j][1] * scale_log2e : ninf;
-      s[j][3] = key + 1 < L ? s[j][3] * scale_log2e : ninf;
+      for (int j = 0; j < 2; ++j) {
+        const int key = k0 + j * 8 + 2 * t;
+        if (key >= L) s[j][0] = s[j][2] = ninf;
+        if (key + 1 >= L) s[j][1] = s[j][3] = ninf;
+      }
     }
+    // online softmax on the raw scores; the 1/sqrt(HD) * log2(e) factor rides in the exp2 argument
     float bm_lo = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
     float bm_hi = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
     bm_lo = fmaxf(bm_lo, __shfl_xor_sync(kFull, bm_lo, 1));
@@ -318,19 +318,33 @@ __device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloa
     bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 1));
     bm_hi = fmaxf(bm_hi, __shfl_xor_sync(kFull, bm_hi, 2));
     const float mn_lo = fmaxf(m_lo, bm_lo), mn_hi = fmaxf(m_hi, bm_hi);   // finite: key k0 < L is in every block
-    const float c_lo = ex2_fast(m_lo - mn_lo), c_hi = ex2_fast(m_hi - mn_hi);
-    m_lo = mn_lo;
-    m_hi = mn_hi;
+    const float ms_lo = -mn_lo * scale_log2e, ms_hi = -mn_hi * scale_log2e;
     float p[2][4];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      p[j][0] = ex2_fast(s[j][0] - mn_lo);
-      p[j][1] = ex2_fast(s[j][1] - mn_lo);
-      p[j][2] = ex2_fast(s[j][2] - mn_hi);
-      p[j][3] = ex2_fast(s[j][3] - mn_hi);
+      p[j][0] = ex2_fast(fmaf(s[j][0], scale_log2e, ms_lo));
+      p[j][1] = ex2_fast(fmaf(s[j][1], scale_log2e, ms_lo));
+      p[j][2] = ex2_fast(fmaf(s[j][2], scale_log2e, ms_hi));
+      p[j][3] = ex2_fast(fmaf(s[j][3], scale_log2e, ms_hi));
     }
-    l_lo = l_lo * c_lo + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
-    l_hi = l_hi * c_hi + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
+    const float ps_lo = p[0][0] + p[0][1] + p[1][0] + p[1][1], ps_hi = p[0][2] + p[0][3] + p[1][2] + p[1][3];
+    if (k0 > 0) {                         // rescale what earlier blocks accumulated (nothing yet in the first)
+      const float c_lo = ex2_fast(fmaf(m_lo, scale_log2e, ms_lo)), c_hi = ex2_fast(fmaf(m_hi, scale_log2e, ms_hi));
+      l_lo = fmaf(l_lo, c_lo, ps_lo);
+      l_hi = fmaf(l_hi, c_hi, ps_hi);
+#pragma unroll
+      for (int nd = 0; nd < HD / 8; ++nd) {
+        o[nd][0] *= c_lo;
+        o[nd][1] *= c_lo;
+        o[nd][2] *= c_hi;
+        o[nd][3] *= c_hi;
+      }
+    } else {
+      l_lo = ps_lo;
+      l_hi = ps_hi;
+    }
+    m_lo = mn_lo;
+    m_hi = mn_hi;
     const uint32_t pa[4] = {pack_bf16(p[0][0], p[0][1]), pack_bf16(p[0][2], p[0][3]), pack_bf16(p[1][0], p[1][1]),
                             pack_bf16(p[1][2], p[1][3])};
     // matrices 0..3 = keys [k0 + 8 (mi & 1), +8) x dims [16 n2 + 8 (mi >> 1), +8), transposed on load:
@@ -340,15 +354,8 @@ __device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloa
     for (int n2 = 0; n2 < HD / 16; ++n2) {
       uint32_t vf[4];
       ldmatrix_x4_trans(vf, vr + n2 * 16);
-#pragma unroll
-      for (int h2 = 0; h2 < 2; ++h2) {
-        float(&oo)[4] = o[2 * n2 + h2];
-        oo[0] *= c_lo;
-        oo[1] *= c_lo;
-        oo[2] *= c_hi;
-        oo[3] *= c_hi;
-        mma_16816(oo, pa, vf[2 * h2], vf[2 * h2 + 1]);
-      }
+      mma_16816(o[2 * n2], pa, vf[0], vf[1]);
+      mma_16816(o[2 * n2 + 1], pa, vf[2], vf[3]);
     }
   }
   l_lo += __shfl_xor_sync(kFull, l_lo, 1);
