@@ -114,23 +114,50 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
       : "memory");
 }
 
-// GELU with the exact (erf) definition, x * Phi(x).  Phi(-a) = exp2(R(a)) for a = |x| in [0, 5.25],
-// R a degree-6 polynomial fitted to log2(0.5 erfc(a / sqrt 2)) (near-minimax, Chebyshev nodes);
-// Phi(a) = 1 - Phi(-a).  Measured against float64 erf over [-12, 12]: |error| <= 2.8e-6 absolute,
-// 2.1e-5 relative wherever |gelu| > 1e-6 — two orders below the bf16 rounding that follows.  One
-// MUFU (ex2) and ten ALU instructions per element: the FFN-up epilogue is bound by instruction issue
-// (24,576 elements per tile against ~2 us of tensor-core time), erff would cost twice that.
-__device__ __forceinline__ float gelu_erf(float x) {
-  const float a = fminf(fabsf(x), 5.25f);
-  float r = fmaf(a, 2.802607560e-05f, -6.891732337e-04f);
-  r = fmaf(a, r, 7.647311781e-03f);
-  r = fmaf(a, r, -5.238423496e-02f);
-  r = fmaf(a, r, -4.598393440e-01f);
-  r = fmaf(a, r, -1.150800705e+00f);
-  r = fmaf(a, r, -1.000019431e+00f);
-  float e;                                                 // Phi(-|x|); -28 < r <= -1: no range handling needed
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(r));
-  return x * (x < 0.f ? e : 1.0f - e);
+// Packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2): two IEEE fp32 operations per issued instruction.
+__device__ __forceinline__ unsigned long long f2_bits(float2 v) { return *reinterpret_cast<unsigned long long*>(&v); }
+__device__ __forceinline__ float2 bits_f2(unsigned long long v) { return *reinterpret_cast<float2*>(&v); }
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(f2_bits(a)), "l"(f2_bits(b)), "l"(f2_bits(c)));
+  return bits_f2(d);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+  return bits_f2(d);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+  return bits_f2(d);
+}
+__device__ __forceinline__ float2 splat(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// GELU with the exact (erf) definition, x * Phi(x), for two values at once.  2 Phi(-a) = exp2(R(a)) for
+// a = |x| in [0, 5.25], R a degree-6 polynomial fitted to 1 + log2(0.5 erfc(a / sqrt 2)) (near-minimax,
+// Chebyshev nodes); then x Phi(x) = h + |h| (1 - 2 Phi(-|x|)) with h = x / 2, which needs no select.
+// Measured against float64 erf over [-12, 12]: |error| <= 2.8e-6 absolute, 2.1e-5 relative wherever
+// |gelu| > 1e-6 — two orders below the bf16 rounding that follows.  Per pair: 9 packed FMA/MUL, 2 MUFU
+// (ex2) and 4 scalar instructions.  The FFN-up epilogue is bound by instruction issue (24,576 elements per
+// tile against ~2 us of tensor-core time); erff would cost four times that.
+__device__ __forceinline__ float2 gelu_erf2(float2 x) {
+  const float2 a = make_float2(fminf(fabsf(x.x), 5.25f), fminf(fabsf(x.y), 5.25f));
+  float2 r = ffma2(a, splat(2.802607560e-05f), splat(-6.891732337e-04f));
+  r = ffma2(a, r, splat(7.647311781e-03f));
+  r = ffma2(a, r, splat(-5.238423496e-02f));
+  r = ffma2(a, r, splat(-4.598393440e-01f));
+  r = ffma2(a, r, splat(-1.150800705e+00f));
+  r = ffma2(a, r, splat(-1.943111420e-05f));               // constant term of R: 1 - 1.000019431
+  const float2 e2 = make_float2(ex2_approx(r.x), ex2_approx(r.y));      // 2 Phi(-|x|); -27 < r <= 0
+  const float2 t = ffma2(e2, splat(-1.0f), splat(1.0f));
+  const float2 h = fmul2(x, splat(0.5f));
+  return ffma2(make_float2(fabsf(h.x), fabsf(h.y)), t, h);
 }
 
 template <int kEpi>
@@ -276,7 +303,7 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           tma_load_2d(box + kBoxBytes, &tmap_res, &res_bar[warp], kEncBN + cg * 64, row0);
         }
         __syncwarp();
-        float s1 = 0.f, s2 = 0.f;
+        float2 s1p = make_float2(0.f, 0.f), s2p = s1p;      // even / odd column partial sums
 #pragma unroll 1
         for (int nt = 0; nt < 2; ++nt, ++it) {
           const uint32_t acc = it & 1;
@@ -307,10 +334,11 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
-                const float y0 = v[8 * c + 2 * e] + bv[2 * e] + f.x, y1 = v[8 * c + 2 * e + 1] + bv[2 * e + 1] + f.y;
-                s1 += y0 + y1;
-                s2 = fmaf(y0, y0, fmaf(y1, y1, s2));
-                const __nv_bfloat162 h = __floats2bfloat162_rn(y0, y1);
+                const float2 y = fadd2(fadd2(make_float2(v[8 * c + 2 * e], v[8 * c + 2 * e + 1]),
+                                             make_float2(bv[2 * e], bv[2 * e + 1])), f);
+                s1p = fadd2(s1p, y);
+                s2p = ffma2(y, y, s2p);
+                const __nv_bfloat162 h = __floats2bfloat162_rn(y.x, y.y);
                 w[e] = *reinterpret_cast<const uint32_t*>(&h);
               }
               *slot = make_uint4(w[0], w[1], w[2], w[3]);
@@ -319,7 +347,7 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         // row statistics over the 384 features: this warp saw 128 of them
         float2* st = ln_stats + (unit & 1) * (kEpiWarps * 32);
-        st[warp * 32 + lane] = make_float2(s1, s2);
+        st[warp * 32 + lane] = make_float2(s1p.x + s1p.y, s2p.x + s2p.y);
         asm volatile("bar.sync %0, 96;" ::"r"(1 + quarter) : "memory");
         const float2 p0 = st[quarter * 32 + lane], p1 = st[(quarter + 4) * 32 + lane], p2 = st[(quarter + 8) * 32 + lane];
         const float inv_n = 1.0f / static_cast<float>(2 * kEncBN);
@@ -344,9 +372,11 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             uint32_t w[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
+              // (f - mu) rstd g + b  =  f (rstd g) + (b - mu rstd g)
               const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
-              const __nv_bfloat162 h = __floats2bfloat162_rn((f.x - mu) * rstd * gv[2 * e] + bv[2 * e],
-                                                             (f.y - mu) * rstd * gv[2 * e + 1] + bv[2 * e + 1]);
+              const float2 rg = fmul2(make_float2(gv[2 * e], gv[2 * e + 1]), splat(rstd));
+              const float2 o = ffma2(f, rg, ffma2(rg, splat(-mu), make_float2(bv[2 * e], bv[2 * e + 1])));
+              const __nv_bfloat162 h = __floats2bfloat162_rn(o.x, o.y);
               w[e] = *reinterpret_cast<const uint32_t*>(&h);
             }
             *slot = make_uint4(w[0], w[1], w[2], w[3]);
@@ -408,14 +438,16 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float4 b = __ldg(b4 + j);
-          v[4 * j + 0] += b.x;
-          v[4 * j + 1] += b.y;
-          v[4 * j + 2] += b.z;
-          v[4 * j + 3] += b.w;
-        }
-        if (kEpi == kEpiGelu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          float2 lo = fadd2(make_float2(v[4 * j + 0], v[4 * j + 1]), make_float2(b.x, b.y));
+          float2 hi = fadd2(make_float2(v[4 * j + 2], v[4 * j + 3]), make_float2(b.z, b.w));
+          if (kEpi == kEpiGelu) {
+            lo = gelu_erf2(lo);
+            hi = gelu_erf2(hi);
+          }
+          v[4 * j + 0] = lo.x;
+          v[4 * j + 1] = lo.y;
+          v[4 * j + 2] = hi.x;
+          v[4 * j + 3] = hi.y;
         }
         if (!res_ready) {
           mbar_wait(&res_bar[warp], it & 1);
@@ -435,9 +467,10 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
-              v[8 * c + 2 * e] += f.x;
-              v[8 * c + 2 * e + 1] += f.y;
+              const float2 f = fadd2(make_float2(v[8 * c + 2 * e], v[8 * c + 2 * e + 1]),
+                                     __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e])));
+              v[8 * c + 2 * e] = f.x;
+              v[8 * c + 2 * e + 1] = f.y;
             }
           }
           uint32_t w[4];
