@@ -73,36 +73,46 @@ __device__ __forceinline__ void warp_layernorm_store(float (&v)[kMaxPairs][2], i
 
 constexpr int kPairsMax = kMaxHidden / 64;   // 16
 
-// x[t] = LayerNorm(word[id[t]] + position[t - seq start] + token_type[0]); one CTA per sequence,
-// warps stride over its tokens.  (BertEmbeddings; token_type_ids are all zero for one-segment input.)
+// pos[t] = index of packed token t inside its sequence; one thread per sequence.
 __global__ void __launch_bounds__(256)
-enc_embed_ln_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ offsets, const float* __restrict__ word,
-                    const float* __restrict__ pos, const float* __restrict__ type0, const float* __restrict__ g,
-                    const float* __restrict__ b, float eps, int H, int vocab, __nv_bfloat16* __restrict__ x) {
+enc_positions_kernel(const int32_t* __restrict__ offsets, int m, int32_t* __restrict__ pos) {
   pdl_launch_dependents();
   pdl_wait();
-  const int seq = blockIdx.x;
-  const int t0 = offsets[seq], L = offsets[seq + 1] - t0;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const int t0 = offsets[i], L = offsets[i + 1] - t0;
+  for (int p = 0; p < L; ++p) pos[t0 + p] = p;
+}
+
+// x[t] = LayerNorm(word[id[t]] + position[pos[t]] + token_type[0]); one warp per packed token, so that
+// the random 1.5 KB row gathers of ~100k tokens are all in flight together.  (BertEmbeddings;
+// token_type_ids are all zero for one-segment input.)
+__global__ void __launch_bounds__(256)
+enc_embed_ln_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ tok_pos, const float* __restrict__ word,
+                    const float* __restrict__ pos, const float* __restrict__ type0, const float* __restrict__ g,
+                    const float* __restrict__ b, float eps, int H, int vocab, long long T, __nv_bfloat16* __restrict__ x) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long t = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (t >= T) return;
+  const int lane = threadIdx.x & 31;
   const int pairs = H / 64;
-  for (int p = warp; p < L; p += nw) {
-    int id = ids[t0 + p];
-    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
-    const float* wr = word + static_cast<long long>(id) * H;
-    const float* pr = pos + static_cast<long long>(p) * H;
-    float v[kPairsMax][2];
+  int id = ids[t];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const float* wr = word + static_cast<long long>(id) * H;
+  const float* pr = pos + static_cast<long long>(tok_pos[t]) * H;
+  float v[kPairsMax][2];
 #pragma unroll
-    for (int i = 0; i < kPairsMax; ++i)
-      if (i < pairs) {
-        const int c = 64 * i + 2 * lane;
-        const float2 a = *reinterpret_cast<const float2*>(wr + c);
-        const float2 q = *reinterpret_cast<const float2*>(pr + c);
-        const float2 t = *reinterpret_cast<const float2*>(type0 + c);
-        v[i][0] = a.x + q.x + t.x;
-        v[i][1] = a.y + q.y + t.y;
-      }
-    warp_layernorm_store<kPairsMax>(v, pairs, H, g, b, eps, x + static_cast<long long>(t0 + p) * H, lane);
-  }
+  for (int i = 0; i < kPairsMax; ++i)
+    if (i < pairs) {
+      const int c = 64 * i + 2 * lane;
+      const float2 a = *reinterpret_cast<const float2*>(wr + c);
+      const float2 q = *reinterpret_cast<const float2*>(pr + c);
+      const float2 ty = *reinterpret_cast<const float2*>(type0 + c);
+      v[i][0] = a.x + q.x + ty.x;
+      v[i][1] = a.y + q.y + ty.y;
+    }
+  warp_layernorm_store<kPairsMax>(v, pairs, H, g, b, eps, x + t * H, lane);
 }
 
 // x[t] = LayerNorm(y[t]); y already holds projection + bias + residual.  One warp per token.
@@ -456,46 +466,45 @@ enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t*
   store_ctx<HD>(Qs, ctx + static_cast<long long>(t0) * H + head * HD, H, L, lane, 32);
 }
 
-// Pooling(mean over the sequence's tokens) + Normalize (x / max(|x|, 1e-12)); one CTA per sequence.
-__global__ void __launch_bounds__(128)
+// Pooling(mean over the sequence's tokens) + Normalize (x / max(|x|, 1e-12)); one CTA per sequence, one
+// thread per pair of columns (blockDim = H / 2), four token rows in flight per thread.
+__global__ void __launch_bounds__(512)
 enc_pool_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ offsets, int H, int normalize,
                 float* __restrict__ out) {
   pdl_launch_dependents();
   pdl_wait();
-  __shared__ float red[4];
+  __shared__ float red[16];
   const int seq = blockIdx.x;
   const int t0 = offsets[seq], L = offsets[seq + 1] - t0;
-  const int pairs = H / 2;                       // thread owns column pairs tid, tid + 128, ...
-  float2 acc[kMaxHidden / 256];
-  float sq = 0.f;
+  const __nv_bfloat16* col = x + static_cast<long long>(t0) * H + 2 * threadIdx.x;
+  float2 acc = make_float2(0.f, 0.f);
+  int p = 0;
+  for (; p + 4 <= L; p += 4) {
+    float2 f[4];
 #pragma unroll
-  for (int i = 0; i < kMaxHidden / 256; ++i) {
-    acc[i] = make_float2(0.f, 0.f);
-    const int pc = threadIdx.x + i * 128;
-    if (pc < pairs) {
-      for (int p = 0; p < L; ++p) {
-        const float2 f =
-            __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + static_cast<long long>(t0 + p) * H + 2 * pc));
-        acc[i].x += f.x;
-        acc[i].y += f.y;
-      }
-      const float inv = 1.f / fmaxf(static_cast<float>(L), 1e-9f);
-      acc[i].x *= inv;
-      acc[i].y *= inv;
-      sq += acc[i].x * acc[i].x + acc[i].y * acc[i].y;
+    for (int u = 0; u < 4; ++u)
+      f[u] = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(col + static_cast<long long>(p + u) * H));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {            // token order, as the sequential sum of the restatement
+      acc.x += f[u].x;
+      acc.y += f[u].y;
     }
   }
-  sq = warp_sum(sq);
+  for (; p < L; ++p) {
+    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(col + static_cast<long long>(p) * H));
+    acc.x += f.x;
+    acc.y += f.y;
+  }
+  const float inv = 1.f / fmaxf(static_cast<float>(L), 1e-9f);
+  acc.x *= inv;
+  acc.y *= inv;
+  float sq = warp_sum(acc.x * acc.x + acc.y * acc.y);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
   __syncthreads();
-  const float nrm = sqrtf(red[0] + red[1] + red[2] + red[3]);
-  const float sc = normalize ? 1.f / fmaxf(nrm, 1e-12f) : 1.f;
-#pragma unroll
-  for (int i = 0; i < kMaxHidden / 256; ++i) {
-    const int pc = threadIdx.x + i * 128;
-    if (pc < pairs)
-      *reinterpret_cast<float2*>(out + static_cast<long long>(seq) * H + 2 * pc) = make_float2(acc[i].x * sc, acc[i].y * sc);
-  }
+  float tot = 0.f;
+  for (int w = 0; w < (blockDim.x >> 5); ++w) tot += red[w];
+  const float sc = normalize ? 1.f / fmaxf(sqrtf(tot), 1e-12f) : 1.f;
+  *reinterpret_cast<float2*>(out + static_cast<long long>(seq) * H + 2 * threadIdx.x) = make_float2(acc.x * sc, acc.y * sc);
 }
 
 size_t attention_smem(int hd, int Lp) { return 3 * static_cast<size_t>(Lp) * (hd + 8) * 2; }   // Q, K, V slices
@@ -528,6 +537,7 @@ struct qre_encoder {
   CUtensorMap map_x, map_ctx, map_h;                       // A operands (128-token boxes)
   CUtensorMap box_qkv, box_y, box_h, box_x;                // epilogue boxes: outputs qkv / y / h, residual x
   int32_t *d_ids = nullptr, *d_off = nullptr;
+  int32_t* tok_pos = nullptr;                        // [max_tokens] position of each packed token in its sequence
   int32_t *long_list = nullptr, *n_long = nullptr;   // sequences longer than kShortLen in the current batch: two buckets
   float* d_out = nullptr;
   int32_t *h_ids = nullptr, *h_off = nullptr;     // pinned staging of the host entry point
@@ -661,8 +671,12 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
       chained = true;
       ++e->launches;
     }
-    launch_chain(enc_embed_ln_kernel, dim3(m), dim3(256), 0, st, chained, ids, offsets, e->word, e->pos, e->type,
-                 e->eln_g, e->eln_b, c.ln_eps, H, c.vocab_size, e->x);
+    launch_chain(enc_positions_kernel, dim3((m + 255) / 256), dim3(256), 0, st, chained, offsets, m, e->tok_pos);
+    launch_chain(enc_embed_ln_kernel, dim3(static_cast<unsigned>((T + 7) / 8)), dim3(256), 0, st, true, ids,
+                 static_cast<const int32_t*>(e->tok_pos), static_cast<const float*>(e->word),
+                 static_cast<const float*>(e->pos), static_cast<const float*>(e->type), static_cast<const float*>(e->eln_g),
+                 static_cast<const float*>(e->eln_b), c.ln_eps, H, c.vocab_size, static_cast<long long>(T), e->x);
+    ++e->launches;
     chained = true;
     ++e->launches;
     for (int l = 0; l < c.layers; ++l) {
@@ -691,7 +705,8 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
       }
     }
   }
-  launch_chain(enc_pool_kernel, dim3(m), dim3(128), 0, st, chained, e->x, offsets, H, normalize, out);
+  launch_chain(enc_pool_kernel, dim3(m), dim3(H / 2), 0, st, chained, static_cast<const __nv_bfloat16*>(e->x), offsets, H,
+               normalize, out);
   ++e->launches;
   ENC_CUDA(cudaGetLastError());
   return QRE_OK;
@@ -720,6 +735,7 @@ void destroy(qre_encoder* e) {
   for (__nv_bfloat16* p : {e->x, e->qkv, e->ctx, e->y, e->h}) cudaFree(p);
   cudaFree(e->d_ids);
   cudaFree(e->d_off);
+  cudaFree(e->tok_pos);
   cudaFree(e->long_list);
   cudaFree(e->n_long);
   cudaFreeHost(e->h_ids);
@@ -813,6 +829,7 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   ENC_TRY(cudaMalloc(&e->d_ids, sizeof(int32_t) * max_tokens));
   ENC_TRY(cudaMalloc(&e->d_off, sizeof(int32_t) * (static_cast<size_t>(max_seqs) + 1)));
   ENC_TRY(cudaMalloc(&e->d_out, sizeof(float) * static_cast<size_t>(max_seqs) * H));
+  ENC_TRY(cudaMalloc(&e->tok_pos, sizeof(int32_t) * static_cast<size_t>(max_tokens)));
   ENC_TRY(cudaMalloc(&e->long_list, 2 * sizeof(int32_t) * static_cast<size_t>(max_seqs)));
   ENC_TRY(cudaMalloc(&e->n_long, 2 * sizeof(int32_t)));
   ENC_TRY(cudaMallocHost(&e->h_ids, sizeof(int32_t) * max_tokens));
