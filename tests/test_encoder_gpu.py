@@ -163,6 +163,30 @@ def test_unnormalised_pool_and_batch_independence():
     enc.close()
 
 
+def test_small_and_large_batches_agree():
+    """hidden 384: FFN-down runs with LayerNorm fused in its epilogue from ~9.5 k tokens up and with the
+    separate LayerNorm kernel below.  The same sequences embedded alone (small) and inside a 12 k-token
+    batch (large) must agree to bf16 noise, and the large batch must itself meet the oracle tolerance."""
+    from qre_b200 import _cabi
+    o = MO.EncoderConfig(vocab_size=800, hidden=384, layers=2, heads=12, intermediate=1536, max_positions=64,
+                         max_seq_len=64)
+    c = _cabi.EncoderConfig(800, 384, 2, 12, 1536, 64, 2, 1e-12, 64)
+    w = MO.random_weights(o, seed=13)
+    rs = np.random.Generator(np.random.PCG64(14))
+    lens = rs.integers(8, 64, 340)
+    seqs = [rs.integers(0, 800, n).astype(np.int32) for n in lens]
+    assert sum(lens) > 10500
+    enc = _cabi.Encoder(c, w, max_tokens=int(sum(lens)) + 64, max_seqs=len(seqs))
+    large = enc.encode_ids(seqs)
+    small = enc.encode_ids(seqs[:6])
+    cos = (large[:6] * small).sum(1)
+    assert cos.min() > 0.9999, float(cos.min())
+    assert np.abs(large[:6] - small).max() < 4e-3
+    want = MO.encode_ids(w, seqs[:24], o)
+    _assert_close(large[:24], want, lens[:24])
+    enc.close()
+
+
 def test_encode_dev_feeds_the_lookup_without_a_host_round_trip():
     """ids -> qre_encode_dev -> qre_cache_append_dev / lookup on device pointers: a text inserted through
     the encoder is found again by the same text (sim ~ 1) and by nothing else."""
