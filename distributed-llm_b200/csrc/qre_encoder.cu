@@ -5,11 +5,12 @@
 // attention, LayerNorm, mean pool + normalise), the weight/activation layout and the launch
 // sequence; the linear layers are in qre_enc_gemm.cu.
 //
-// Activations for one batch (T packed tokens, hidden H, FFN F), all bf16, rows padded to 128:
+// Activations for one batch (T packed tokens, hidden H, FFN F), all bf16, rows padded to 256:
 //   x   [T, H]   layer input / residual stream          (A operand of QKV and FFN-up)
 //   qkv [T, 3H]  Q | K | V column blocks                (one fused projection)
 //   ctx [T, H]   attention output                       (A operand of the output projection)
-//   y   [T, H]   projection + residual, before LayerNorm
+//   y   [T, H]   projection + residual, before LayerNorm (unused when LayerNorm runs in the
+//                projection's epilogue and the result goes straight back into x: hidden 384)
 //   h   [T, F]   GELU(FFN-up)                           (A operand of FFN-down)
 // LayerNorm statistics, softmax and pooling are fp32.
 #include <math.h>
