@@ -163,6 +163,20 @@ def test_unnormalised_pool_and_batch_independence():
     enc.close()
 
 
+@pytest.mark.parametrize("H,heads,F,P,lens", [
+    (1024, 16, 4096, 512, [512, 300, 1, 77]),       # the documented maxima: hidden, FFN, sequence length, 64-wide heads
+    (64, 2, 64, 32, [1, 5, 32, 16, 0, 40]),         # the minima: one 192-feature tile mostly clipped
+    (320, 10, 1280, 96, [96, 33, 64, 65, 7]),       # widths that are not multiples of the 192-feature tile
+])
+def test_extreme_shapes(H, heads, F, P, lens):
+    from qre_b200 import _cabi
+    o = MO.EncoderConfig(vocab_size=300, hidden=H, layers=1, heads=heads, intermediate=F, max_positions=P,
+                         max_seq_len=P)
+    c = _cabi.EncoderConfig(300, H, 1, heads, F, P, 2, 1e-12, P)
+    got, want = _check(o, c, lens, seed=H)
+    _assert_close(got, want, [min(n, P) for n in lens])
+
+
 def test_small_and_large_batches_agree():
     """hidden 384: FFN-down runs with LayerNorm fused in its epilogue from ~9.5 k tokens up and with the
     separate LayerNorm kernel below.  The same sequences embedded alone (small) and inside a 12 k-token
