@@ -120,9 +120,9 @@ int qre_wordpiece_create(const char* vocab_path, int do_lower_case, qre_wordpiec
   int ch;
   auto commit = [&]() {
     while (!line.empty() && (line.back() == '\r' || line.back() == '\n')) line.pop_back();
-    // vocab.txt lines are pieces verbatim; a later duplicate keeps the first id (as a dict load would not,
-    // but published vocabularies have none)
-    t->vocab.emplace(line, id);
+    // vocab.txt lines are pieces verbatim; a duplicated piece takes the id of its LAST line, as the dict the
+    // Python tokenizers load the file into does
+    t->vocab[line] = id;
     t->max_piece = std::max(t->max_piece, line.size());
     ++id;
     line.clear();

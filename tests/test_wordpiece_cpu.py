@@ -82,3 +82,15 @@ def test_errors(tmp_path):
     rc = lib.qre_wordpiece_encode(wp._h, ctypes.c_int64(1), texts, None, 256, ids.ctypes.data_as(ctypes.c_void_p),
                                   ctypes.c_int64(2), lens.ctypes.data_as(ctypes.c_void_p), 1)
     assert rc == 3 and b"capacity" in lib.qre_last_error()
+
+
+def test_duplicate_vocab_lines_take_the_last_id(tmp_path):
+    """A piece listed twice gets the id of its last line — what loading vocab.txt into a dict does."""
+    vp = os.path.join(tmp_path, "dup.txt")
+    pieces = ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "go", "##ing", "x", "##ing", "go"]
+    with open(vp, "w") as f:
+        f.write("\n".join(pieces) + "\n")
+    vocab = {t: i for i, t in enumerate(pieces)}
+    wp = _cabi.WordPiece(vp)
+    ids, lens = wp.encode(["going x"], max_len=16)
+    assert ids.tolist() == MO.tokenize_ids("going x", vocab, 16).tolist() == [2, 8, 7, 6, 3]
