@@ -87,3 +87,33 @@ def test_wordpiece_restatement_equals_berttokenizer(tmp_path):
             want = tok(text, truncation=True, max_length=max_len)["input_ids"]
             got = MO.tokenize_ids(text, vocab, max_len).tolist()
             assert got == want, (text, max_len, got, want)
+
+
+def test_wordpiece_restatement_on_random_texts(tmp_path):
+    """1,500 generated texts (vocab words, ASCII punctuation and control characters, accents, CJK, emoji,
+    odd whitespace): the restatement and BertTokenizer must produce the same ids for each."""
+    import random
+    from transformers import BertTokenizer
+    vp = os.path.join(tmp_path, "vocab.txt")
+    with open(vp, "w", encoding="utf-8") as f:
+        f.write("\n".join(VOCAB) + "\n")
+    tok = BertTokenizer(vp, do_lower_case=True)
+    vocab = {t: i for i, t in enumerate(VOCAB)}
+    rnd = random.Random(11)
+    words = [v for v in VOCAB if not v.startswith("[") and not v.startswith("##")]
+    extra = ["É", "ü", "ñ", "ß", "ø", "中", "文", "日本", "😀", " ", " ", "​", "\x07", "\x7f", "…", "—", "«", "»",
+             "ǅ", "İ", "ﬁ", "²", "½"]
+    glue = [" ", "  ", "\t", "\n", "\r\n", "", "-", "'", ",", ".", "!", "?", "(", ")", "$", "_", "/", "\\", "[", "]", "#", "##"]
+    for i in range(1500):
+        parts = []
+        for _ in range(rnd.randint(0, 14)):
+            r = rnd.random()
+            w = rnd.choice(words) if r < 0.6 else (rnd.choice(extra) if r < 0.8 else
+                                                    "".join(rnd.choice("abcxyzHELLO019") for _ in range(rnd.randint(1, 7))))
+            parts.append(w.upper() if rnd.random() < 0.15 else w)
+            parts.append(rnd.choice(glue))
+        text = "".join(parts)
+        for max_len in (256, 9):
+            want = tok(text, truncation=True, max_length=max_len)["input_ids"]
+            got = MO.tokenize_ids(text, vocab, max_len).tolist()
+            assert got == want, (i, repr(text), max_len, got, want)

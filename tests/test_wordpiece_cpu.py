@@ -94,3 +94,18 @@ def test_duplicate_vocab_lines_take_the_last_id(tmp_path):
     wp = _cabi.WordPiece(vp)
     ids, lens = wp.encode(["going x"], max_len=16)
     assert ids.tolist() == MO.tokenize_ids("going x", vocab, 16).tolist() == [2, 8, 7, 6, 3]
+
+
+def test_product_unicode_fallback_equals_oracle():
+    """qre_b200.embedder.wordpiece_unicode (the Python path for texts the C++ tokenizer declines) against the
+    restatement, on generated texts with accents, CJK, emoji, control characters and odd whitespace."""
+    from qre_b200.embedder import wordpiece_unicode
+    vocab = {t: i for i, t in enumerate(VOCAB)}
+    rnd = random.Random(5)
+    words = [v for v in VOCAB if not v.startswith("[") and not v.startswith("##")]
+    extra = ["É", "ü", "ñ", "ß", "中", "文", "日本", "😀", " ", " ", "​", "\x07", "…", "—", "İ", "ﬁ", "½"]
+    glue = [" ", "\t", "\n", "", "-", "'", ",", ".", "!", "(", ")", "$", "_", "#"]
+    for _ in range(1500):
+        text = "".join(rnd.choice(words + extra) + rnd.choice(glue) for _ in range(rnd.randint(0, 12)))
+        for max_len in (256, 7):
+            assert wordpiece_unicode(text, vocab, max_len) == MO.tokenize_ids(text, vocab, max_len).tolist(), repr(text)
