@@ -72,3 +72,43 @@ def test_router_embeds_on_the_gpu(tmp_path):
     st = router.get_cache_stats()
     assert st["hits"] >= 2 * len(qs) + 1
     enc.close()
+
+
+def test_from_hf_dir_loads_a_saved_bert_checkpoint(tmp_path):
+    """A BertModel saved by transformers (config.json + model.safetensors) plus vocab.txt and a
+    sentence_bert_config.json, as a sentence-transformers cache entry has them: from_hf_dir must reproduce
+    the torch pipeline (BertTokenizer -> BertModel -> mean pool -> normalise) on the same texts."""
+    import json
+    import torch
+    from transformers import BertConfig, BertModel, BertTokenizer
+    from qre_b200.embedder import B200SentenceEncoder
+    d = os.path.join(tmp_path, "model")
+    hc = BertConfig(vocab_size=len(VOCAB), hidden_size=128, num_hidden_layers=2, num_attention_heads=4,
+                    intermediate_size=256, max_position_embeddings=64, hidden_act="gelu", layer_norm_eps=1e-12)
+    torch.manual_seed(3)
+    model = BertModel(hc, add_pooling_layer=False).eval()
+    with torch.no_grad():                         # default init leaves LayerNorm at identity and biases at zero
+        for n_, p_ in model.named_parameters():
+            if "LayerNorm" in n_ or n_.endswith("bias"):
+                p_.add_(0.1 * torch.randn_like(p_))
+            else:
+                p_.mul_(2.5)
+    model.save_pretrained(d)
+    with open(os.path.join(d, "vocab.txt"), "w", encoding="utf-8") as f:
+        f.write("\n".join(VOCAB) + "\n")
+    with open(os.path.join(d, "sentence_bert_config.json"), "w") as f:
+        json.dump({"max_seq_length": 32, "do_lower_case": False}, f)
+    enc = B200SentenceEncoder.from_hf_dir(d, max_batch=16)
+    assert enc.max_seq_length == 32 and enc.config.heads == 4 and enc.config.layers == 2
+    tok = BertTokenizer(os.path.join(d, "vocab.txt"), do_lower_case=True)
+    texts = [t for t in TEXTS if t] + ["hello " * 50]
+    b = tok(texts, truncation=True, max_length=32, padding=True, return_tensors="pt")
+    with torch.no_grad():
+        h = model(input_ids=b["input_ids"], attention_mask=b["attention_mask"]).last_hidden_state
+    mf = b["attention_mask"].unsqueeze(-1).float()
+    want = torch.nn.functional.normalize((h * mf).sum(1) / mf.sum(1).clamp(min=1e-9), p=2, dim=1).numpy()
+    got = enc.encode(texts)
+    cos = (got * want).sum(1)
+    assert cos.min() >= 0.999, float(cos.min())
+    assert np.abs(got - want).max() <= 8e-3
+    enc.close()
