@@ -159,6 +159,10 @@ class B200SentenceEncoder:
         cfg = _cabi.EncoderConfig(c["vocab_size"], c["hidden_size"], c["num_hidden_layers"], c["num_attention_heads"],
                                   c["intermediate_size"], c["max_position_embeddings"], c.get("type_vocab_size", 2),
                                   c.get("layer_norm_eps", 1e-12), min(max_seq, c["max_position_embeddings"]))
+        tc = os.path.join(root, "tokenizer_config.json")      # the tokenizer's own setting decides the casing
+        if "do_lower_case" not in kw and os.path.isfile(tc):
+            with open(tc) as f:
+                kw["do_lower_case"] = bool(json.load(f).get("do_lower_case", True))
         return cls(sd, os.path.join(root, "vocab.txt"), config=cfg, **kw)
 
     # ---- tokenisation ------------------------------------------------------------------------
