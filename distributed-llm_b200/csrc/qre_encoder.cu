@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "qre_encoder.cuh"
+#include "qre_ptx.cuh"
 
 using namespace qre;
 
@@ -228,12 +229,6 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 // rows at a time and walks the keys 16 at a time with an online softmax; K and V fragments come out
 // of shared memory with ldmatrix (transposed for V), scores and probabilities never leave registers
 // (the accumulator layout of one m16n8k16 product is the A-operand layout of the next).
-// 2^x for x <= 0 or -inf (the online-softmax arguments): the bare MUFU, no range fix-up code
-__device__ __forceinline__ float ex2_fast(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* row_ptr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
@@ -332,23 +327,30 @@ __device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloa
     const float ms_lo = -mn_lo * scale_log2e, ms_hi = -mn_hi * scale_log2e;
     float p[2][4];
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      p[j][0] = ex2_fast(fmaf(s[j][0], scale_log2e, ms_lo));
-      p[j][1] = ex2_fast(fmaf(s[j][1], scale_log2e, ms_lo));
-      p[j][2] = ex2_fast(fmaf(s[j][2], scale_log2e, ms_hi));
-      p[j][3] = ex2_fast(fmaf(s[j][3], scale_log2e, ms_hi));
+    for (int j = 0; j < 2; ++j) {        // exp2 arguments two at a time (FFMA2)
+      const float2 a_lo = ffma2(make_float2(s[j][0], s[j][1]), splat(scale_log2e), splat(ms_lo));
+      const float2 a_hi = ffma2(make_float2(s[j][2], s[j][3]), splat(scale_log2e), splat(ms_hi));
+      p[j][0] = ex2_approx(a_lo.x);
+      p[j][1] = ex2_approx(a_lo.y);
+      p[j][2] = ex2_approx(a_hi.x);
+      p[j][3] = ex2_approx(a_hi.y);
     }
-    const float ps_lo = p[0][0] + p[0][1] + p[1][0] + p[1][1], ps_hi = p[0][2] + p[0][3] + p[1][2] + p[1][3];
+    const float2 ps_a = fadd2(make_float2(p[0][0], p[0][2]), make_float2(p[0][1], p[0][3]));
+    const float2 ps_b = fadd2(make_float2(p[1][0], p[1][2]), make_float2(p[1][1], p[1][3]));
+    const float2 ps = fadd2(ps_a, ps_b);
+    const float ps_lo = ps.x, ps_hi = ps.y;
     if (k0 > 0) {                         // rescale what earlier blocks accumulated (nothing yet in the first)
-      const float c_lo = ex2_fast(fmaf(m_lo, scale_log2e, ms_lo)), c_hi = ex2_fast(fmaf(m_hi, scale_log2e, ms_hi));
+      const float c_lo = ex2_approx(fmaf(m_lo, scale_log2e, ms_lo)), c_hi = ex2_approx(fmaf(m_hi, scale_log2e, ms_hi));
       l_lo = fmaf(l_lo, c_lo, ps_lo);
       l_hi = fmaf(l_hi, c_hi, ps_hi);
 #pragma unroll
       for (int nd = 0; nd < HD / 8; ++nd) {
-        o[nd][0] *= c_lo;
-        o[nd][1] *= c_lo;
-        o[nd][2] *= c_hi;
-        o[nd][3] *= c_hi;
+        const float2 r_lo = fmul2(make_float2(o[nd][0], o[nd][1]), splat(c_lo));
+        const float2 r_hi = fmul2(make_float2(o[nd][2], o[nd][3]), splat(c_hi));
+        o[nd][0] = r_lo.x;
+        o[nd][1] = r_lo.y;
+        o[nd][2] = r_hi.x;
+        o[nd][3] = r_hi.y;
       }
     } else {
       l_lo = ps_lo;
@@ -377,10 +379,10 @@ __device__ __forceinline__ void attend_block(__nv_bfloat16* Qs, const __nv_bfloa
   __syncwarp();                                   // every lane's ldmatrix of this block's Q rows has retired
 #pragma unroll
   for (int nd = 0; nd < HD / 8; ++nd) {
-    *reinterpret_cast<__nv_bfloat162*>(Qs + r_lo * KS + nd * 8 + 2 * t) =
-        __floats2bfloat162_rn(o[nd][0] * i_lo, o[nd][1] * i_lo);
-    *reinterpret_cast<__nv_bfloat162*>(Qs + r_hi * KS + nd * 8 + 2 * t) =
-        __floats2bfloat162_rn(o[nd][2] * i_hi, o[nd][3] * i_hi);
+    const float2 n_lo = fmul2(make_float2(o[nd][0], o[nd][1]), splat(i_lo));
+    const float2 n_hi = fmul2(make_float2(o[nd][2], o[nd][3]), splat(i_hi));
+    *reinterpret_cast<__nv_bfloat162*>(Qs + r_lo * KS + nd * 8 + 2 * t) = __floats2bfloat162_rn(n_lo.x, n_lo.y);
+    *reinterpret_cast<__nv_bfloat162*>(Qs + r_hi * KS + nd * 8 + 2 * t) = __floats2bfloat162_rn(n_hi.x, n_hi.y);
   }
 }
 
