@@ -404,10 +404,10 @@ enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __res
   __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(att_smem);
   __nv_bfloat16* Ks = Qs + static_cast<size_t>(Lp) * KS;
   __nv_bfloat16* Vs = Ks + static_cast<size_t>(Lp) * KS;
-  const int head = blockIdx.y, n = *n_long;
+  const int head = blockIdx.x, n = *n_long;        // heads vary fastest in launch order: see launch_attention
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long ld = 3LL * H;
-  for (int i = blockIdx.x; i < n; i += gridDim.x) {
+  for (int i = blockIdx.y; i < n; i += gridDim.y) {
     const int seq = long_list[i];
     const int t0 = offsets[seq];
     const int L = min(offsets[seq + 1] - t0, Lp);
@@ -455,7 +455,7 @@ enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t*
   __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(att_smem) + warp * 3 * slice;
   __nv_bfloat16* Ks = Qs + slice;
   __nv_bfloat16* Vs = Ks + slice;
-  const int seq = blockIdx.x, head = blockIdx.y * 4 + warp;
+  const int seq = blockIdx.y, head = blockIdx.x * 4 + warp;   // head groups vary fastest in launch order
   const int t0 = offsets[seq];
   const int L = offsets[seq + 1] - t0;
   if (L <= 0 || L > Lp || head >= heads) return;
@@ -627,7 +627,9 @@ int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len,
   int n = 0;
   // sequences of up to kShortLen tokens: warp per head
   const int Ls = ((max_len < kShortLen ? max_len : kShortLen) + 15) & ~15;
-  const dim3 grid_s(m, (e->cfg.heads + 3) / 4);
+  // x (fastest in launch order) = head group: the CTAs that read the 64-byte head slices of the same token rows
+  // are resident together, so each 2304-byte qkv row is touched once while its DRAM page is open
+  const dim3 grid_s((e->cfg.heads + 3) / 4, m);
   const __nv_bfloat16* qkv = e->qkv;
   if (e->hd == 32)
     launch_chain(enc_attention_short_kernel<32>, grid_s, dim3(128), attention_short_smem(32, Ls), st, true, qkv, offsets,
@@ -646,7 +648,8 @@ int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len,
     per_sm = per_sm < 1 ? 1 : (per_sm > 16 ? 16 : per_sm);
     int gx = (e->num_sms * per_sm + e->cfg.heads - 1) / e->cfg.heads;
     gx = gx < 1 ? 1 : (gx > m ? m : gx);
-    const dim3 grid(gx, e->cfg.heads);
+    if (gx > 65535) gx = 65535;
+    const dim3 grid(e->cfg.heads, gx);
     const int32_t* list = e->long_list + (bucket == 0 ? 0 : m);
     const int32_t* cnt = e->n_long + bucket;
     if (e->hd == 32)
@@ -769,8 +772,8 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
   if (c.max_seq_len <= 0 || c.max_seq_len > kMaxSeq || c.max_seq_len > c.max_positions)
     return set_error(QRE_ERR_INVALID, "encoder: max_seq_len must be in [1, min(%d, max_positions)]", kMaxSeq);
   if (!(c.ln_eps >= 0.f)) return set_error(QRE_ERR_INVALID, "encoder: bad ln_eps");
-  if (max_tokens <= 0 || max_seqs <= 0 || max_tokens > (1LL << 30))
-    return set_error(QRE_ERR_INVALID, "encoder: bad max_tokens / max_seqs");
+  if (max_tokens <= 0 || max_seqs <= 0 || max_tokens > (1LL << 30) || max_seqs > 65535)
+    return set_error(QRE_ERR_INVALID, "encoder: need 0 < max_tokens <= 2^30 and 0 < max_seqs <= 65535");
   int n_dev = 0;
   ENC_CUDA(cudaGetDeviceCount(&n_dev));
   if (device < 0 || device >= n_dev) return set_error(QRE_ERR_NO_DEVICE, "encoder: no CUDA device %d", device);

@@ -61,7 +61,7 @@ typedef struct {
 } qre_encoder_layer_t;
 
 /* Allocates weights and activation buffers for up to max_tokens packed tokens in up to
- * max_seqs sequences per call on `device`.  Replaces SentenceTransformer(model_name)
+ * max_seqs (<= 65535) sequences per call on `device`.  Replaces SentenceTransformer(model_name)
  * (qre:126, 511) minus the checkpoint download: weights are supplied by the caller. */
 QRE_API int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_tokens, int max_seqs,
                                qre_encoder_t** out);
