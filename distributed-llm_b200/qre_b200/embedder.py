@@ -221,32 +221,12 @@ class B200SentenceEncoder:
                                                      normalize=normalize_embeddings)
         return out[0] if single else out
 
-    def encode_to_device(self, sentences: Sequence[str], out_ptr: int, stream: int = 0,
-                         ids_dev=None, off_dev=None) -> Tuple[int, int]:
-        """Tokenise on the host, embed on the GPU, leave the fp32 [n, hidden] result at device
-        address `out_ptr` (e.g. a torch tensor's data_ptr()) for qre_scan_dev / qre_cache_append_dev:
-        the embeddings never visit the host.  `ids_dev` / `off_dev`: torch int32 device tensors to
-        stage the ids in (allocated if omitted).  Returns (n, n_tokens)."""
-        import torch
-        texts = list(sentences)
-        ids, off = self.tokenize(texts)
-        n, T = len(texts), int(off[-1])
-        if n > self.max_batch or T > self.max_tokens:
-            raise _cabi.QreError(f"batch of {n} texts / {T} tokens exceeds the encoder's capacity "
-                                 f"({self.max_batch} / {self.max_tokens})")
-        dev = torch.device("cuda", self.device)
-        s = torch.cuda.ExternalStream(stream, device=dev) if stream not in (0, 1) else torch.cuda.current_stream(dev)
-        with torch.cuda.stream(s):
-            ids_t = torch.from_numpy(ids).pin_memory().to(dev, non_blocking=True) if ids_dev is None else ids_dev
-            off_t = torch.from_numpy(off).pin_memory().to(dev, non_blocking=True) if off_dev is None else off_dev
-            if ids_dev is not None:
-                ids_dev[:T].copy_(torch.from_numpy(ids), non_blocking=True)
-                off_dev[:n + 1].copy_(torch.from_numpy(off), non_blocking=True)
-            max_len = int(np.diff(off).max()) if n else 0
-            self._enc.encode_dev(n, ids_t.data_ptr(), off_t.data_ptr(), T, max_len, out_ptr,
-                                 stream=s.cuda_stream or 1)
-            s.synchronize()           # ids_t / off_t may be freed once the encoder has consumed them
-        return n, T
+    @property
+    def engine(self) -> "_cabi.Encoder":
+        """The C-ABI encoder handle, for device-resident use: `engine.encode_dev(...)` writes fp32 rows where
+        `qre_scan_dev` / `qre_cache_append_dev` read them, and `ShardedLookup.embed_ids(engine, ids, offsets)`
+        embeds a batch data-parallel over the GPUs of a row-sharded cache."""
+        return self._enc
 
     def close(self) -> None:
         self._enc.close()
