@@ -37,7 +37,7 @@ def test_encode_matches_oracle_pipeline(tmp_path):
     one = enc.encode("Hello worlds!")
     assert one.shape == (128,) and np.array_equal(one, enc.encode(["Hello worlds!"])[0])
     assert enc.encode([]).shape == (0, 128)
-    assert enc.get_sentence_embedding_dimension() == 128
+    assert enc.get_sentence_embedding_dimension() == 128 and enc.engine.launch_count() > 0
     ids, off = enc.tokenize(["hello world", "café 中文"])          # C++ path + Unicode fallback
     assert ids[off[0]:off[1]].tolist() == MO.tokenize_ids("hello world", vocab, 48).tolist()
     assert ids[off[1]:off[2]].tolist() == MO.tokenize_ids("café 中文", vocab, 48).tolist()
