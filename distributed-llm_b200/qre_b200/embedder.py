@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import json
 import os
+import threading
 import unicodedata
 from typing import Callable, Dict, Iterable, List, Optional, Sequence, Tuple, Union
 
@@ -134,6 +135,9 @@ class B200SentenceEncoder:
         self._vocab_path = vocab_path
         self._fallback = fallback_tokenizer
         self.device = device
+        # The reference calls encode() from Flask worker threads (app.py:126, threaded=True); the device handle
+        # has one set of activation buffers and one stream, so calls are serialised here, like Engine's lock.
+        self._lock = threading.Lock()
 
     # ---- construction helpers ----------------------------------------------------------------
     @classmethod
@@ -215,10 +219,11 @@ class B200SentenceEncoder:
         texts = [sentences] if single else list(sentences)
         out = np.empty((len(texts), self.config.hidden), np.float32)
         if texts:
-            ids, off = self.tokenize(texts)
-            for i0, i1 in self._batches(off):
-                out[i0:i1] = self._enc.encode_packed(ids[off[i0]:off[i1]], off[i0:i1 + 1] - off[i0],
-                                                     normalize=normalize_embeddings)
+            ids, off = self.tokenize(texts)              # host threads, no shared state: outside the lock
+            with self._lock:
+                for i0, i1 in self._batches(off):
+                    out[i0:i1] = self._enc.encode_packed(ids[off[i0]:off[i1]], off[i0:i1 + 1] - off[i0],
+                                                         normalize=normalize_embeddings)
         return out[0] if single else out
 
     @property

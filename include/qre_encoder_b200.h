@@ -19,6 +19,9 @@
  * final normalisation are fp32.  Sequences are packed (no padding): `offsets[m+1]` delimits
  * each query's ids inside one flat array.
  *
+ * One batch at a time per encoder handle: it owns one set of activation buffers, so calls from several
+ * threads or on several streams must be ordered by the caller (the Python class holds a lock).
+ *
  * Conventions are those of qre_b200.h: int status codes (0 = OK), qre_last_error() for the
  * message, no exceptions, caller owns host buffers, no CPU fallback.
  */

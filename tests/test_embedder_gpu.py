@@ -112,3 +112,30 @@ def test_from_hf_dir_loads_a_saved_bert_checkpoint(tmp_path):
     assert cos.min() >= 0.999, float(cos.min())
     assert np.abs(got - want).max() <= 8e-3
     enc.close()
+
+
+def test_encode_from_several_threads(tmp_path):
+    """The reference embeds from Flask worker threads; concurrent encode() calls on one encoder must give
+    what serial calls give."""
+    import threading
+    enc, _, _ = _encoder(tmp_path, max_batch=8)
+    texts = [t for t in TEXTS if t]
+    serial = [enc.encode([t])[0] for t in texts]
+    out, errs = {}, []
+
+    def work(k):
+        try:
+            for rep in range(20):
+                for i in range(k, len(texts), 4):
+                    out[(k, rep, i)] = enc.encode([texts[i]])[0]
+        except Exception as e:      # pragma: no cover
+            errs.append(e)
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs
+    assert all(np.array_equal(v, serial[i]) for (_, _, i), v in out.items()) and len(out) == 20 * len(texts)
+    enc.close()
