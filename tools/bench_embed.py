@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--check", type=int, default=64, help="sequences compared with the fp32 oracle")
+    ap.add_argument("--shape", default="minilm-l6", choices=["minilm-l6", "minilm-l12", "bert-base"],
+                    help="encoder shape: all-MiniLM-L6-v2 (default), all-MiniLM-L12-v2, or BERT-base widths (768 / 12 x 64 / 3072)")
     ap.add_argument("--fused-cache-rows", type=int, default=0,
                     help="also time token ids -> embedding -> cache lookup + hybrid route against a cache of "
                          "this many random rows, everything on the device (SURVEY 8f-1 feeding 8a)")
@@ -32,7 +34,10 @@ def main():
     import torch
     from oracle import minilm_oracle as MO
     from qre_b200 import _cabi
-    cfg_o, cfg = MO.MINILM_L6, _cabi.EncoderConfig()
+    shapes = {"minilm-l6": (384, 6, 12, 1536), "minilm-l12": (384, 12, 12, 1536), "bert-base": (768, 12, 12, 3072)}
+    Hh, Ll, Nh, Ff = shapes[a.shape]
+    cfg_o = MO.EncoderConfig(hidden=Hh, layers=Ll, heads=Nh, intermediate=Ff)
+    cfg = _cabi.EncoderConfig(hidden=Hh, layers=Ll, heads=Nh, intermediate=Ff)
     w = MO.random_weights(cfg_o, seed=1)
     rs = np.random.Generator(np.random.PCG64(2))
     m = a.queries
@@ -80,7 +85,7 @@ def main():
     want = MO.encode_ids(w, [ids[off[i]:off[i + 1]] for i in sel], cfg_o)
     cos = (got[sel] * want).sum(1)
     line = {
-        "metric": "embedded queries/s (all-MiniLM-L6-v2 shape, random weights)", "value": m / ms * 1e3, "unit": "queries/s",
+        "metric": f"embedded queries/s ({a.shape} shape, random weights)", "value": m / ms * 1e3, "unit": "queries/s",
         "tokens_per_s": T / ms * 1e3, "ms_per_batch": ms, "queries": m, "tokens": T, "mean_len": float(lens.mean()),
         "max_len": max_len, "launches_per_batch": (enc.launch_count() - l0) // a.steps,
         "algorithmic_tflops": (gemm_flops + attn_flops) / ms / 1e9, "gemm_share_of_flops": gemm_flops / (gemm_flops + attn_flops),
