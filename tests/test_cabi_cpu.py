@@ -71,3 +71,26 @@ def test_bad_arguments_rejected_before_any_cuda_call():
     assert b"multiple of 8" in lib.qre_last_error()
     assert lib.qre_cache_create(0, 384, ctypes.c_int64(0), 4, ctypes.byref(h)) == 1
     assert lib.qre_cache_destroy(None) == 0
+
+
+def test_every_encoder_kernel_joins_the_dependent_launch_chain():
+    """Source check: each __global__ kernel of the embedder is launched with programmatic stream
+    serialization (qre_encoder.cuh), which is only safe if EVERY kernel of the chain executes
+    griddepcontrol.wait before touching global memory.  A kernel added without pdl_wait() would break the
+    transitive completion guarantee silently, so fail here instead."""
+    csrc = os.path.join(ROOT, "distributed-llm_b200", "csrc")
+    seen = 0
+    for fn in ("qre_encoder.cu", "qre_enc_gemm.cu"):
+        text = open(os.path.join(csrc, fn)).read()
+        for m in re.finditer(r"__global__[^{;]*?\b(\w+)\s*\([^;{]*?\)\s*\{", text, re.S):
+            body = text[m.end(): m.end() + 6000]
+            first_wait = body.find("pdl_wait();")
+            assert first_wait >= 0, (fn, m.group(1))
+            # nothing that dereferences a kernel argument may precede the wait
+            head = body[:first_wait]
+            assert "offsets[" not in head and "__ldg" not in head and "tma_load" not in head, (fn, m.group(1))
+            seen += 1
+    assert seen >= 9, seen
+    # and no kernel of the chain is launched with the <<<>>> syntax (which cannot carry the attribute)
+    for fn in ("qre_encoder.cu", "qre_enc_gemm.cu"):
+        assert "<<<" not in open(os.path.join(csrc, fn)).read(), fn

@@ -46,12 +46,16 @@ def _st_pipeline(model, seqs):
     return torch.nn.functional.normalize(emb, p=2, dim=1).numpy()
 
 
-@pytest.mark.parametrize("cfg,seed", [(SMALL, 3), (MO.MINILM_L6, 5)])
+WIDE_HEADS = MO.EncoderConfig(vocab_size=400, hidden=128, layers=2, heads=2, intermediate=320, max_positions=40,
+                              max_seq_len=40)      # 64-wide heads, as the BERT-base family
+
+
+@pytest.mark.parametrize("cfg,seed", [(SMALL, 3), (WIDE_HEADS, 4), (MO.MINILM_L6, 5)])
 def test_encoder_restatement_equals_bertmodel(cfg, seed):
     w = MO.random_weights(cfg, seed=seed)
     model = _hf_model(cfg, w)
     rs = np.random.Generator(np.random.PCG64(seed))
-    lens = [1, 2, 7, 16, 33, cfg.max_seq_len] if cfg is SMALL else [3, 11, 40]
+    lens = [3, 11, 40] if cfg is MO.MINILM_L6 else [1, 2, 7, 16, 33, cfg.max_seq_len]
     seqs = [rs.integers(0, cfg.vocab_size, n).astype(np.int32) for n in lens]
     want = _st_pipeline(model, seqs)
     got = MO.encode_ids(w, seqs, cfg)
