@@ -77,13 +77,14 @@ constexpr int kPairsMax = kMaxHidden / 64;   // 16
 
 // pos[t] = index of packed token t inside its sequence; one thread per sequence.
 __global__ void __launch_bounds__(256)
-enc_positions_kernel(const int32_t* __restrict__ offsets, int m, int32_t* __restrict__ pos) {
+enc_positions_kernel(const int32_t* __restrict__ offsets, int m, int max_positions, int32_t* __restrict__ pos) {
   pdl_launch_dependents();
   pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const int t0 = offsets[i], L = offsets[i + 1] - t0;
-  for (int p = 0; p < L; ++p) pos[t0 + p] = p;
+  // (clamped: a sequence longer than the caller promised must not index past the position table)
+  for (int p = 0; p < L; ++p) pos[t0 + p] = p < max_positions ? p : max_positions - 1;
 }
 
 // x[t] = LayerNorm(word[id[t]] + position[pos[t]] + token_type[0]); one warp per packed token, so that
@@ -677,7 +678,8 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
       chained = true;
       ++e->launches;
     }
-    launch_chain(enc_positions_kernel, dim3((m + 255) / 256), dim3(256), 0, st, chained, offsets, m, e->tok_pos);
+    launch_chain(enc_positions_kernel, dim3((m + 255) / 256), dim3(256), 0, st, chained, offsets, m, c.max_positions,
+                 e->tok_pos);
     launch_chain(enc_embed_ln_kernel, dim3(static_cast<unsigned>((T + 7) / 8)), dim3(256), 0, st, true, ids,
                  static_cast<const int32_t*>(e->tok_pos), static_cast<const float*>(e->word),
                  static_cast<const float*>(e->pos), static_cast<const float*>(e->type), static_cast<const float*>(e->eln_g),
