@@ -147,3 +147,35 @@ def make_workload(n_rows: int, n_queries: int, dim: int = 384, n_centroids: int 
     return Workload(rows, row_ctx, row_ts, row_lru, row_pred_dev, row_pred_conf,
                     Q, q_ctx, tok, heur_dev, heur_conf, cents, owner, perf,
                     now_us, ttl_us, planted_row, planted_cos)
+
+
+def encoder_random_weights(hidden: int = 384, layers: int = 6, intermediate: int = 1536, vocab_size: int = 30522,
+                           max_positions: int = 512, type_vocab: int = 2, seed: int = 0, std: float = 0.05) -> dict:
+    """Seeded random parameters of a BERT-style encoder under transformers' `BertModel.state_dict()` names
+    (the published all-MiniLM-L6-v2 checkpoint is not available offline): what the embedder benchmarks run on.
+    LayerNorm gains near 1 and non-zero biases everywhere, so no term of a kernel is multiplied by zero."""
+    rs = np.random.Generator(np.random.PCG64(seed))
+    H, F = hidden, intermediate
+    n = lambda *s: (rs.standard_normal(s) * std).astype(np.float32)   # noqa: E731
+    g = lambda: (1.0 + 0.1 * rs.standard_normal(H)).astype(np.float32)   # noqa: E731
+    w = {
+        "embeddings.word_embeddings.weight": n(vocab_size, H),
+        "embeddings.position_embeddings.weight": n(max_positions, H),
+        "embeddings.token_type_embeddings.weight": n(type_vocab, H),
+        "embeddings.LayerNorm.weight": g(),
+        "embeddings.LayerNorm.bias": n(H),
+    }
+    for l in range(layers):
+        p = f"encoder.layer.{l}."
+        for nm in ("attention.self.query", "attention.self.key", "attention.self.value", "attention.output.dense"):
+            w[p + nm + ".weight"] = n(H, H)
+            w[p + nm + ".bias"] = n(H)
+        w[p + "attention.output.LayerNorm.weight"] = g()
+        w[p + "attention.output.LayerNorm.bias"] = n(H)
+        w[p + "intermediate.dense.weight"] = n(F, H)
+        w[p + "intermediate.dense.bias"] = n(F)
+        w[p + "output.dense.weight"] = n(H, F)
+        w[p + "output.dense.bias"] = n(H)
+        w[p + "output.LayerNorm.weight"] = g()
+        w[p + "output.LayerNorm.bias"] = n(H)
+    return w

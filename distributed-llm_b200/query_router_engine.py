@@ -333,7 +333,10 @@ class HybridRouter(BaseRouter):
         self._names = _device_names(config)
         self.routers = {
             "token": TokenBasedRouter(config),
-            "semantic": SemanticRouter(config, engine=engine) if SENTENCE_TRANSFORMERS_AVAILABLE else None,
+            # the reference keys this on the sentence-transformers import (qre:380); an embedder supplied
+            # through config["embedder"] serves as well
+            "semantic": (SemanticRouter(config, engine=engine)
+                         if SENTENCE_TRANSFORMERS_AVAILABLE or config.get("embedder") is not None else None),
             "heuristic": HeuristicRouter(config),
         }
 

@@ -87,3 +87,33 @@ def test_heuristic_router_matches_live_reference():
         assert pa.route("q").__dict__ == pb.route("q").__dict__
     assert ref_qre.PRODUCTION_CFG == qre_mod.PRODUCTION_CFG and ref_qre.BENCHMARK_CFG == qre_mod.BENCHMARK_CFG
     assert ref_qre.QueryRouter._default_config(None) == qre_mod.QueryRouter._default_config(None)
+
+
+def test_config_embedder_works_without_sentence_transformers(monkeypatch):
+    """config["embedder"] (e.g. qre_b200.embedder.B200SentenceEncoder) must give the hybrid strategy its
+    semantic router and the cache its embedder even where the sentence-transformers package is not
+    installed — the situation the on-GPU embedder exists for."""
+    _, qre, _ = R.load_modules(engine_cls=OracleEngine)
+    monkeypatch.setattr(qre, "SENTENCE_TRANSFORMERS_AVAILABLE", False)
+    monkeypatch.delattr(qre, "SentenceTransformer", raising=False)
+
+    class Emb:
+        calls = 0
+
+        def encode(self, texts, **_):
+            Emb.calls += 1
+            out = np.zeros((len(texts), 8), np.float32)
+            for i, t in enumerate(texts):
+                out[i, len(t) % 8] = 1.0
+                out[i, 0] += 0.25
+            return out
+
+    cfg = dict(qre.PRODUCTION_CFG, embedder=Emb(), centroids=np.eye(2, 8, dtype=np.float32), centroid_owner=[0, 1])
+    router = qre.QueryRouter("hybrid", cfg)
+    assert router._fusable() and router.cache_embedder is cfg["embedder"]
+    assert router.router.routers["semantic"].embedder is cfg["embedder"]
+    a = router.route_query("hello there", context_key="k")
+    b = router.route_query("hello there", context_key="k")
+    assert a.method == "hybrid" and b.method == "hybrid_cached" and Emb.calls >= 2
+    with pytest.raises(ImportError):                      # and without an embedder the reference's error stays
+        qre.QueryRouter("semantic", dict(qre.PRODUCTION_CFG))

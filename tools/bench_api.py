@@ -13,7 +13,14 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-llm_b200"), os.path.join(ROOT, "oracle", "stubs")]
+sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-llm_b200")]
+
+
+class _NoEmbedder:
+    """Embeddings are passed in (`q_embs=`) and the centroids are explicit, so nothing is ever encoded."""
+
+    def encode(self, texts, **_):
+        raise RuntimeError("bench_api supplies embeddings itself")
 
 
 def main():
@@ -28,7 +35,7 @@ def main():
     d = 384
     cents = rs.standard_normal((2, d)).astype(np.float32)
     cfg = dict(Q.PRODUCTION_CFG, cache_max_size=a.entries + a.batch * (a.rounds + 2), max_batch=a.batch,
-               centroids=cents, centroid_owner=[0, 1], cache_ttl_seconds=10**6)
+               centroids=cents, centroid_owner=[0, 1], cache_ttl_seconds=10**6, embedder=_NoEmbedder())
     qr = Q.QueryRouter("hybrid", cfg)
     # bulk-load the device store directly (the Python insert path is per entry), then register
     # nothing on the host: these rows only serve as scan load; hits come from the batches below.

@@ -27,8 +27,7 @@ def main():
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
-    from oracle import minilm_oracle as MO
-    from qre_b200 import _cabi
+    from qre_b200 import _cabi, synth
     from qre_b200.sharded import ShardedLookup
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -43,7 +42,7 @@ def main():
     off[1:] = np.cumsum(lens)
     ids = rs.integers(0, 30522, int(off[-1])).astype(np.int32)
     per = (m + world - 1) // world
-    enc = _cabi.Encoder(_cabi.EncoderConfig(), MO.random_weights(MO.MINILM_L6, seed=1),
+    enc = _cabi.Encoder(_cabi.EncoderConfig(), synth.encoder_random_weights(seed=1),
                         max_tokens=int(max(off[min(m, (r + 1) * per)] - off[min(m, r * per)] for r in range(world))) + 256,
                         max_seqs=per, device=local)
     n_local = (a.rows - rank + world - 1) // world
