@@ -457,11 +457,70 @@ def gen_config1():
     print("config1:", Counter((o["method"], o["cache_hit"]) for o in out), stats, f"{time.time() - t0:.0f}s")
 
 
+def gen_embedder():
+    """Embedder fixtures from the THIRD-PARTY code the reference calls (transformers' BertModel and
+    BertTokenizer; sentence-transformers' Pooling(mean) + Normalize restated in three lines), not from the
+    restatement: seeded random weights of two shapes (`random_weights` of oracle/minilm_oracle.py regenerates
+    them from the seed stored here), token ids, expected embeddings; and the ids BertTokenizer assigns to the
+    texts of tests/wordpiece_cases.py."""
+    import tempfile
+    import torch
+    from transformers import BertConfig, BertModel, BertTokenizer
+    from oracle import minilm_oracle as MO
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from wordpiece_cases import TEXTS, VOCAB
+    out = {}
+    shapes = {"hd32": MO.EncoderConfig(vocab_size=500, hidden=128, layers=2, heads=4, intermediate=256,
+                                       max_positions=64, max_seq_len=48),
+              "hd64": MO.EncoderConfig(vocab_size=400, hidden=128, layers=2, heads=2, intermediate=320,
+                                       max_positions=40, max_seq_len=40),
+              "h384": MO.EncoderConfig(vocab_size=600, hidden=384, layers=2, heads=12, intermediate=1536,
+                                       max_positions=64, max_seq_len=64)}
+    for name, cfg in shapes.items():
+        seed = {"hd32": 31, "hd64": 32, "h384": 33}[name]
+        w = MO.random_weights(cfg, seed=seed)
+        hc = BertConfig(vocab_size=cfg.vocab_size, hidden_size=cfg.hidden, num_hidden_layers=cfg.layers,
+                        num_attention_heads=cfg.heads, intermediate_size=cfg.intermediate,
+                        max_position_embeddings=cfg.max_positions, hidden_act="gelu", layer_norm_eps=cfg.ln_eps)
+        model = BertModel(hc, add_pooling_layer=False).eval()
+        missing, unexpected = model.load_state_dict({k: torch.from_numpy(v) for k, v in w.items()}, strict=False)
+        assert not unexpected
+        rs = np.random.Generator(np.random.PCG64(seed + 100))
+        lens = [1, 2, 7, 15, 16, 17, 31, 32, 33, cfg.max_seq_len, 5, 24]
+        ids = [rs.integers(0, cfg.vocab_size, n).astype(np.int32) for n in lens]
+        L = max(lens)
+        tok = torch.zeros((len(ids), L), dtype=torch.long)
+        mask = torch.zeros((len(ids), L), dtype=torch.long)
+        for i, s_ in enumerate(ids):
+            tok[i, :len(s_)] = torch.from_numpy(s_.astype(np.int64))
+            mask[i, :len(s_)] = 1
+        with torch.no_grad():
+            h = model(input_ids=tok, attention_mask=mask).last_hidden_state
+        mf = mask.unsqueeze(-1).float()
+        pooled = (h * mf).sum(1) / mf.sum(1).clamp(min=1e-9)
+        out[name + "_cfg"] = np.array([cfg.vocab_size, cfg.hidden, cfg.layers, cfg.heads, cfg.intermediate,
+                                       cfg.max_positions, cfg.max_seq_len, seed], np.int64)
+        out[name + "_ids"] = np.concatenate(ids)
+        out[name + "_lens"] = np.array(lens, np.int32)
+        out[name + "_pooled"] = pooled.numpy().astype(np.float32)
+        out[name + "_emb"] = torch.nn.functional.normalize(pooled, p=2, dim=1).numpy().astype(np.float32)
+    d = tempfile.mkdtemp()
+    vp = os.path.join(d, "vocab.txt")
+    with open(vp, "w", encoding="utf-8") as f:
+        f.write("\n".join(VOCAB) + "\n")
+    bt = BertTokenizer(vp, do_lower_case=True)
+    tok_ids = {str(ml): [bt(t, truncation=True, max_length=ml)["input_ids"] for t in TEXTS] for ml in (256, 16)}
+    np.savez_compressed(os.path.join(GOLD, "embedder.npz"), **out)
+    json.dump({"texts": TEXTS, "ids": tok_ids, "transformers": __import__("transformers").__version__,
+               "torch": torch.__version__}, open(os.path.join(GOLD, "wordpiece.json"), "w"), ensure_ascii=True)
+    print("embedder:", {k: v.shape for k, v in out.items() if k.endswith("_emb")})
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     only = sys.argv[1:] 
     gens = dict(cache_scan=gen_cache_scan, route_arith=gen_route_arith, cache_ops=gen_cache_ops,
-                router_replay=gen_router_replay, config1=gen_config1)
+                router_replay=gen_router_replay, config1=gen_config1, embedder=gen_embedder)
     for name, fn in gens.items():
         if not only or name in only:
             fn()

@@ -98,6 +98,27 @@ def _assert_close(got, want, lens):
     assert np.allclose(np.linalg.norm(got[nz], axis=1), 1.0, atol=1e-5)
 
 
+def test_against_transformers_fixture(golden_dir):
+    """tests/golden/embedder.npz holds what transformers' BertModel + mean pooling + normalisation returned for
+    seeded weights and ids (oracle/gen_golden.py embedder): the CUDA path against the third-party code's own
+    output, 32- and 64-wide heads and the hidden-384 (fused LayerNorm) path."""
+    import os
+    from qre_b200 import _cabi
+    g = np.load(os.path.join(golden_dir, "embedder.npz"))
+    for name in ("hd32", "hd64", "h384"):
+        V, H, L, nh, F, P, S, seed = (int(x) for x in g[name + "_cfg"])
+        o = MO.EncoderConfig(vocab_size=V, hidden=H, layers=L, heads=nh, intermediate=F, max_positions=P, max_seq_len=S)
+        lens = g[name + "_lens"]
+        off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        enc = _cabi.Encoder(_cabi.EncoderConfig(V, H, L, nh, F, P, 2, 1e-12, S), MO.random_weights(o, seed=seed),
+                            max_tokens=int(off[-1]) + 64, max_seqs=len(lens))
+        got = enc.encode_packed(g[name + "_ids"], off)
+        _assert_close(got, g[name + "_emb"], lens)
+        raw = enc.encode_packed(g[name + "_ids"], off, normalize=False)
+        assert np.abs(raw - g[name + "_pooled"]).max() <= 2e-2 * np.abs(g[name + "_pooled"]).max(), name
+        enc.close()
+
+
 def test_small_encoder_head_dim_32():
     from qre_b200 import _cabi
     o = MO.EncoderConfig(vocab_size=500, hidden=128, layers=2, heads=4, intermediate=256, max_positions=64,
