@@ -160,7 +160,7 @@ struct qre_cache {
     uint8_t* h_in = nullptr;           // pinned staging
     uint8_t* d_res = nullptr;          // result block
     uint8_t* h_res = nullptr;          // pinned
-    cudaEvent_t e_in = nullptr, e_mid = nullptr, e_done = nullptr;
+    cudaEvent_t e_in = nullptr, e_done = nullptr;
     bool pending = false;
     int m = 0;
     qre_params_t p;
@@ -170,10 +170,14 @@ struct qre_cache {
     const double* d_hc = nullptr;
   } hs[2];
   cudaStream_t h2d = nullptr, d2h = nullptr;
+  // The pipeline (qre_submit_dev / qre_lookup_route_begin): query preparation on `aux`, the scan
+  // alone on the handle's main stream, re-score / settle / exchange / merge + route on `post`.
+  cudaStream_t aux = nullptr, post = nullptr;
+  cudaEvent_t ev_in[2] = {}, ev_prep[2] = {}, ev_route[2] = {}, ev_scan[2] = {}, ev_post[2] = {};
+  bool post_used[2] = {false, false};
   size_t in_bytes = 0;
   size_t res_bytes = 0;
-  qre_candidate_t* d_cand = nullptr;   // [max_batch, QRE_TOPK]
-  uint64_t* d_q_ctx = nullptr;         // [max_batch] copy of the last batch's contexts
+  int last_slot = 0;
   float* d_dump = nullptr;
   size_t dump_bytes = 0;
   int64_t launches = 0;
@@ -222,23 +226,41 @@ int validate_params(const qre_cache_t* h, const qre_params_t* p) {
   return QRE_OK;
 }
 
-// queries -> this shard's candidates (device pointers, enqueue only)
+// After the scan: exact re-score and, when the spill pool ran out, the device-driven brute-force pass.
+int rescore_enqueue(qre_cache_t* h, int m, const qre_params_t& p, int shard, qre_candidate_t* cand,
+                    cudaStream_t st) {
+  DeviceState& s = h->s;
+  if (p.scan_mode == QRE_SCAN_TENSOR && h->hwm > 0) {
+    h->launches += launch_rescore(s, m, h->hwm, p, shard, cand, st);
+    h->launches += launch_overflow_settle(s, h->hwm, p, shard, cand, st);
+  } else {
+    h->launches += launch_exact_scan(s, m, h->hwm, nullptr, m, false, p, shard, cand, st);
+  }
+  QRE_CUDA(cudaGetLastError());
+  return QRE_OK;
+}
+
+int tensor_scan_enqueue(qre_cache_t* h, int m, const qre_params_t& p, cudaStream_t st) {
+  if (p.scan_mode != QRE_SCAN_TENSOR || h->hwm <= 0) return QRE_OK;
+  const int n = launch_gemm_topk(h->s, m, h->hwm, p, nullptr, 0, 0, 0, st);
+  if (n < 0) return fail(QRE_ERR_CAPACITY, "scan geometry for m=%d, %lld rows does not fit the top-k scratch", m,
+                         (long long)h->hwm);
+  h->launches += n;
+  QRE_CUDA(cudaGetLastError());
+  return QRE_OK;
+}
+
+// queries -> this shard's candidates (device pointers, enqueue only), everything on one stream
 int scan_enqueue(qre_cache_t* h, int m, const float* q_dev, const uint64_t* q_ctx_dev, const qre_params_t& p,
                  int shard, qre_candidate_t* cand, cudaStream_t st) {
   DeviceState& s = h->s;
   s.slot = p.pipeline_slot & 1;
-  h->launches += launch_prep_queries(s, m, q_dev, q_ctx_dev, h->d_q_ctx, st);
+  h->last_slot = s.slot;
+  h->launches += launch_prep_queries(s, m, q_dev, q_ctx_dev, st);
   h->last_m = m;
-  if (p.scan_mode == QRE_SCAN_TENSOR && h->hwm > 0) {
-    h->launches += launch_gemm_topk(s, m, h->hwm, h->d_q_ctx, p, nullptr, 0, 0, 0, st);
-    h->launches += launch_rescore(s, m, h->hwm, p, shard, cand, st);
-    h->launches += launch_overflow_settle(s, h->hwm, h->d_q_ctx, p, shard, cand, st);
-  } else {
-    QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
-    h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, nullptr, m, false, p, shard, cand, st);
-  }
-  QRE_CUDA(cudaGetLastError());
-  return QRE_OK;
+  int rc = tensor_scan_enqueue(h, m, p, st);
+  if (rc != QRE_OK) return rc;
+  return rescore_enqueue(h, m, p, shard, cand, st);
 }
 
 }  // namespace
@@ -311,35 +333,32 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
   QRE_ALLOC(s.lru, sizeof(uint64_t) * (size_t)capacity);
   QRE_ALLOC(s.pred_dev, (size_t)capacity);
   QRE_ALLOC(s.pred_conf, sizeof(double) * (size_t)capacity);
-  for (int b = 0; b < 2; ++b) {
-    QRE_ALLOC(s.q_f32[b], sizeof(float) * (size_t)s.mb_pad * dim_pad);
-    QRE_ALLOC(s.q_norm[b], sizeof(float) * (size_t)s.mb_pad);
-    QRE_ALLOC(s.q_flags[b], (size_t)max_batch);
-  }
-  QRE_ALLOC(s.q_bf16, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad);
-  // scratch of the fused top-k: [mblocks*128][S][8] entries; S*mblocks <= 8 waves of SMs + slack
+  // top-k scratch from the hard bound on work units: at most 8 rounds of the SM count (or one unit
+  // per query block when the batch alone exceeds that), 128 queries x 8 entries per unit
+  s.partial_entries = 1024LL * (8LL * s.num_sms + s.mb_pad / kBM + 2);
   {
-    long long worst = 0;
-    for (int mb = 1; mb <= s.mb_pad / kBM; ++mb) {
-      const ScanGeometry g = plan_scan(mb * kBM, s.cap_pad, s.num_sms);
-      worst = std::max(worst, (long long)g.mblocks * kBM * g.splits * kTopK);
-      const ScanGeometry g2 = plan_scan_pair(mb * kBM, s.cap_pad, s.num_sms);
-      worst = std::max(worst, (long long)(g2.mblocks + 1) * kBM * g2.splits * kTopK);
-      if (mb > 64) mb += 7;   // the product is ~constant beyond one wave; sample sparsely
-    }
-    const ScanGeometry g = plan_scan(s.mb_pad, s.cap_pad, s.num_sms);
-    worst = std::max(worst, (long long)g.mblocks * kBM * g.splits * kTopK);
-    // head-room: the split search may pick a different S when SMs are reserved for other kernels
-    s.partial_entries = 2 * worst + (long long)kBM * kTopK * (s.num_sms + 8);
+    const long long want = std::max<long long>(1024, 128LL * max_batch);     // ~1,900 chained candidates / query
+    s.spill_cap = (uint32_t)std::min<long long>(want, 1LL << 22);            // <= 512 MB
   }
-  QRE_ALLOC(s.partial, sizeof(PartialEntry) * (size_t)s.partial_entries);
+  for (int b = 0; b < 2; ++b) {
+    DeviceState::Batch& B = s.batch[b];
+    QRE_ALLOC(B.q_f32, sizeof(float) * (size_t)s.mb_pad * dim_pad);
+    QRE_ALLOC(B.q_bf16, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad);
+    QRE_ALLOC(B.q_norm, sizeof(float) * (size_t)s.mb_pad);
+    QRE_ALLOC(B.q_ctx, sizeof(uint64_t) * (size_t)max_batch);
+    QRE_ALLOC(B.q_flags, (size_t)max_batch);
+    QRE_ALLOC(B.partial, sizeof(PartialEntry) * (size_t)s.partial_entries);
+    QRE_ALLOC(B.spill_head, sizeof(uint32_t) * (size_t)(s.partial_entries / kTopK));
+    QRE_ALLOC(B.spill_pool, sizeof(SpillChunk) * (size_t)s.spill_cap);
+    QRE_ALLOC(B.counters, sizeof(uint32_t) * 4);
+    QRE_ALLOC(B.ovf_list, sizeof(int32_t) * (size_t)max_batch);
+    QRE_ALLOC(B.cand, sizeof(qre_candidate_t) * (size_t)max_batch * QRE_TOPK);
+  }
   s.exact_grid = s.num_sms * 2;
   QRE_ALLOC(s.exact_partial, sizeof(ExactBest) * (size_t)kExactGroup * s.exact_grid);
-  QRE_ALLOC(s.ovf_count, sizeof(int32_t));
-  QRE_ALLOC(s.ovf_unresolved, sizeof(int32_t));
-  QRE_ALLOC(s.settle_tickets, sizeof(unsigned) * kSettleMaxGroups);
-  QRE_ALLOC(s.settle_partial, sizeof(ExactBest) * (size_t)kSettleMaxGroups * kExactGroup * s.exact_grid);
-  QRE_ALLOC(s.ovf_list, sizeof(int32_t) * (size_t)max_batch);
+  s.settle_groups = (max_batch + kExactGroup - 1) / kExactGroup;
+  QRE_ALLOC(s.settle_tickets, sizeof(unsigned) * (size_t)s.settle_groups);
+  QRE_ALLOC(s.settle_partial, sizeof(ExactBest) * (size_t)s.settle_groups * kExactGroup * s.exact_grid);
   QRE_ALLOC(s.centroids, sizeof(float) * (size_t)QRE_MAX_CENTROIDS * dim_pad);
   QRE_ALLOC(s.cent_norm, sizeof(float) * QRE_MAX_CENTROIDS);
   QRE_ALLOC(s.cent_owner, QRE_MAX_CENTROIDS);
@@ -355,27 +374,32 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     QRE_ALLOC(h->hs[b].d_in, h->in_bytes);
     QRE_ALLOC(h->hs[b].d_res, h->res_bytes);
   }
-  QRE_ALLOC(h->d_cand, sizeof(qre_candidate_t) * (size_t)max_batch * QRE_TOPK);
-  QRE_ALLOC(h->d_q_ctx, sizeof(uint64_t) * (size_t)max_batch);
   QRE_TRY([&]() -> int {
     for (int b = 0; b < 2; ++b) {
       QRE_CUDA(cudaMallocHost((void**)&h->hs[b].h_in, h->in_bytes));
       QRE_CUDA(cudaMallocHost((void**)&h->hs[b].h_res, h->res_bytes));
       QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_in, cudaEventDisableTiming));
-      QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_mid, cudaEventDisableTiming));
       QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_done, cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->ev_in[b], cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->ev_prep[b], cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->ev_route[b], cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->ev_scan[b], cudaEventDisableTiming));
+      QRE_CUDA(cudaEventCreateWithFlags(&h->ev_post[b], cudaEventDisableTiming));
     }
     QRE_CUDA(cudaStreamCreateWithFlags(&h->h2d, cudaStreamNonBlocking));
     QRE_CUDA(cudaStreamCreateWithFlags(&h->d2h, cudaStreamNonBlocking));
+    QRE_CUDA(cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking));
+    QRE_CUDA(cudaStreamCreateWithFlags(&h->post, cudaStreamNonBlocking));
     QRE_CUDA(cudaMemsetAsync(s.rows_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.meta, 0xFF, sizeof(RowMeta) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
-    QRE_CUDA(cudaMemsetAsync(s.q_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.perf_health, 0, sizeof(double) * QRE_MAX_DEVICES, s.stream));
-    QRE_CUDA(cudaMemsetAsync(s.settle_tickets, 0, sizeof(unsigned) * kSettleMaxGroups, s.stream));
-    QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), s.stream));
-    QRE_CUDA(cudaMemsetAsync(s.ovf_count, 0, sizeof(int32_t), s.stream));
-    for (int b = 0; b < 2; ++b) QRE_CUDA(cudaMemsetAsync(s.q_flags[b], 0, (size_t)max_batch, s.stream));
+    QRE_CUDA(cudaMemsetAsync(s.settle_tickets, 0, sizeof(unsigned) * (size_t)s.settle_groups, s.stream));
+    for (int b = 0; b < 2; ++b) {
+      QRE_CUDA(cudaMemsetAsync(s.batch[b].q_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad, s.stream));
+      QRE_CUDA(cudaMemsetAsync(s.batch[b].counters, 0, sizeof(uint32_t) * 4, s.stream));
+      QRE_CUDA(cudaMemsetAsync(s.batch[b].q_flags, 0, (size_t)max_batch, s.stream));
+    }
     QRE_CUDA(gemm_topk_init());
     QRE_CUDA(gemm_topk_pair_init());
     {
@@ -389,8 +413,11 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     if (rc != QRE_OK) return rc;
     rc = make_tmap_bf16(enc, &s.tmap_eh, s.rows_bf16, (uint64_t)dim_pad, (uint64_t)s.cap_pad, kBK, kBN / 2);
     if (rc != QRE_OK) return rc;
-    rc = make_tmap_bf16(enc, &s.tmap_q, s.q_bf16, (uint64_t)dim_pad, (uint64_t)s.mb_pad, kBK, kBM);
-    if (rc != QRE_OK) return rc;
+    for (int b = 0; b < 2; ++b) {
+      rc = make_tmap_bf16(enc, &s.batch[b].tmap_q, s.batch[b].q_bf16, (uint64_t)dim_pad, (uint64_t)s.mb_pad, kBK,
+                          kBM);
+      if (rc != QRE_OK) return rc;
+    }
     QRE_CUDA(cudaStreamSynchronize(s.stream));
     return QRE_OK;
   }());
@@ -406,19 +433,28 @@ int qre_cache_destroy(qre_cache_t* h) {
   DeviceGuard guard(h->s.device);
   DeviceState& s = h->s;
   if (s.stream) cudaStreamSynchronize(s.stream);
-  void* dev_ptrs[] = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf, s.q_f32[0],
-                      s.q_f32[1], s.q_bf16, s.q_norm[0], s.q_norm[1], s.partial, s.exact_partial, s.ovf_count, s.ovf_unresolved, s.settle_tickets, s.settle_partial,
-                      s.ovf_list, s.q_flags[0], s.q_flags[1],
-                      s.centroids, s.cent_norm, s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in,
-                      h->hs[1].d_in, h->hs[0].d_res, h->hs[1].d_res, h->d_cand, h->d_q_ctx, h->d_dump};
+  if (h->aux) cudaStreamSynchronize(h->aux);
+  if (h->post) cudaStreamSynchronize(h->post);
+  std::vector<void*> dev_ptrs = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf,
+                                 s.exact_partial, s.settle_tickets, s.settle_partial, s.centroids, s.cent_norm,
+                                 s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in, h->hs[1].d_in,
+                                 h->hs[0].d_res, h->hs[1].d_res, h->d_dump};
+  for (int b = 0; b < 2; ++b) {
+    DeviceState::Batch& B = s.batch[b];
+    for (void* p : {(void*)B.q_f32, (void*)B.q_bf16, (void*)B.q_norm, (void*)B.q_ctx, (void*)B.q_flags,
+                    (void*)B.partial, (void*)B.spill_head, (void*)B.spill_pool, (void*)B.counters,
+                    (void*)B.ovf_list, (void*)B.cand})
+      dev_ptrs.push_back(p);
+  }
   for (void* p : dev_ptrs)
     if (p) cudaFree(p);
   for (int b = 0; b < 2; ++b) {
     if (h->hs[b].h_in) cudaFreeHost(h->hs[b].h_in);
     if (h->hs[b].h_res) cudaFreeHost(h->hs[b].h_res);
     if (h->hs[b].e_in) cudaEventDestroy(h->hs[b].e_in);
-    if (h->hs[b].e_mid) cudaEventDestroy(h->hs[b].e_mid);
     if (h->hs[b].e_done) cudaEventDestroy(h->hs[b].e_done);
+    for (cudaEvent_t e : {h->ev_in[b], h->ev_prep[b], h->ev_route[b], h->ev_scan[b], h->ev_post[b]})
+      if (e) cudaEventDestroy(e);
   }
   for (int pr = 0; pr < 16; ++pr)
     if (h->xchg_open[pr] && h->xchg_peer[pr]) cudaIpcCloseMemHandle(h->xchg_peer[pr]);
@@ -426,6 +462,8 @@ int qre_cache_destroy(qre_cache_t* h) {
   if (h->xchg_ticket) cudaFree(h->xchg_ticket);
   if (h->h2d) cudaStreamDestroy(h->h2d);
   if (h->d2h) cudaStreamDestroy(h->d2h);
+  if (h->aux) cudaStreamDestroy(h->aux);
+  if (h->post) cudaStreamDestroy(h->post);
   if (s.prof_ev) {
     for (int i = 0; i < 2 * kProfMax; ++i) cudaEventDestroy(s.prof_ev[i]);
     delete[] s.prof_ev;
@@ -678,7 +716,8 @@ int qre_scan_dev(qre_cache_t* h, int m, const float* queries, const uint64_t* q_
   int rc = scan_enqueue(h, m, queries, q_ctx, *params, shard, cand_out, st);
   if (rc != QRE_OK) return rc;
   if (overflow_count)
-    QRE_CUDA(cudaMemcpyAsync(overflow_count, h->s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    QRE_CUDA(cudaMemcpyAsync(overflow_count, h->s.cur().ovf_unresolved(), sizeof(int32_t), cudaMemcpyDeviceToDevice,
+                             st));
   return QRE_OK;
 }
 
@@ -688,17 +727,17 @@ int qre_resolve_overflow_dev(qre_cache_t* h, int m, const qre_params_t* params, 
   if (m != h->last_m) return fail(QRE_ERR_INVALID, "m=%d does not match the last scan (%d)", m, h->last_m);
   DeviceGuard guard(h->s.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
+  h->s.slot = params->pipeline_slot & 1;
+  const DeviceState::Batch& B = h->s.cur();
   int32_t cnt[2] = {0, 0};
-  QRE_CUDA(cudaMemcpyAsync(&cnt[0], h->s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  QRE_CUDA(cudaMemcpyAsync(&cnt[1], h->s.ovf_unresolved, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  QRE_CUDA(cudaMemcpyAsync(&cnt[0], B.ovf_count(), sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  QRE_CUDA(cudaMemcpyAsync(&cnt[1], B.ovf_unresolved(), sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   QRE_CUDA(cudaStreamSynchronize(st));
   const int32_t n_ovf = cnt[0];
   if (cnt[1] <= 0 || n_ovf <= 0) return QRE_OK;
-  h->s.slot = params->pipeline_slot & 1;
-  h->launches += launch_exact_scan(h->s, m, h->hwm, h->d_q_ctx, h->s.ovf_list, n_ovf, true, *params, shard,
-                                   cand_inout, st);
+  h->launches += launch_exact_scan(h->s, m, h->hwm, B.ovf_list, n_ovf, true, *params, shard, cand_inout, st);
   QRE_CUDA(cudaGetLastError());
-  QRE_CUDA(cudaMemsetAsync(h->s.ovf_unresolved, 0, sizeof(int32_t), st));
+  QRE_CUDA(cudaMemsetAsync(B.ovf_unresolved(), 0, sizeof(int32_t), st));
   return QRE_OK;
 }
 
@@ -801,8 +840,14 @@ int qre_publish_dev(qre_cache_t* h, int m, const qre_candidate_t* cand, void* st
   if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
   for (int pr = 0; pr < h->xchg_world; ++pr)
     if (h->xchg_peer[pr] == nullptr) return fail(QRE_ERR_INVALID, "peer %d is not connected", pr);
-  if (h->xchg_pub_epoch - h->xchg_merge_epoch >= 2)
-    return fail(QRE_ERR_INVALID, "two batches already published and not merged (the exchange has two slots)");
+  // One published batch may be outstanding per handle: publish(e) must be followed by merge(e)
+  // before publish(e+1).  A peer's publish(e+2) reuses slot e&1 and is ordered (through its own
+  // merge(e+1), which waits for my publish(e+1)) only after my merge(e) HAS BEEN ENQUEUED when the
+  // calls alternate on one stream; a deeper host-side queue would let it overwrite lists my
+  // merge(e) is still reading.
+  if (h->xchg_pub_epoch != h->xchg_merge_epoch)
+    return fail(QRE_ERR_INVALID, "batch %u is published but not merged: call qre_merge_route_xchg_dev before "
+                "publishing again (publish and merge must alternate, on one stream)", h->xchg_pub_epoch);
   DeviceGuard guard(h->s.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : h->s.stream;
   const uint32_t epoch = ++h->xchg_pub_epoch;
@@ -823,9 +868,11 @@ int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint
                          const qre_params_t* params, int32_t* overflow_count, void* stream) {
   if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
   if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "call qre_xchg_init / qre_xchg_connect first");
-  int rc = qre_scan_dev(h, m, queries, q_ctx, params, h->xchg_rank, h->d_cand, overflow_count, stream);
+  if (params == nullptr) return fail(QRE_ERR_INVALID, "params is NULL");
+  qre_candidate_t* cand = h->s.batch[params->pipeline_slot & 1].cand;
+  int rc = qre_scan_dev(h, m, queries, q_ctx, params, h->xchg_rank, cand, overflow_count, stream);
   if (rc != QRE_OK) return rc;
-  return qre_publish_dev(h, m, h->d_cand, stream);
+  return qre_publish_dev(h, m, cand, stream);
 }
 
 int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,
@@ -854,6 +901,94 @@ int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const ui
   return QRE_OK;
 }
 
+// ---- the pipeline -----------------------------------------------------------------------------
+// One batch = prep (aux stream) -> scan (main stream, nothing else) -> re-score, settle, exchange,
+// merge + route (post stream).  `in_ready` (may be NULL) is an event after which the inputs are
+// valid.  Slot b's previous batch must have left the post stream before slot b's buffers are
+// overwritten: the aux stream waits for ev_post[b].  With `serial` everything is enqueued on the
+// main stream (small batches are latency-bound: cross-stream hand-offs would only add to it).
+static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, const uint64_t* d_ctx,
+                            const int32_t* d_tok, const uint8_t* d_hd, const double* d_hc, const qre_params_t& p_in,
+                            const qre_result_t& out_dev, cudaEvent_t in_ready, bool serial) {
+  DeviceState& s = h->s;
+  qre_params_t p = p_in;
+  p.pipeline_slot = slot;
+  s.slot = slot;
+  h->last_slot = slot;
+  h->last_m = m;
+  DeviceState::Batch& B = s.cur();
+  cudaStream_t aux = serial ? s.stream : h->aux, post = serial ? s.stream : h->post;
+  if (in_ready) QRE_CUDA(cudaStreamWaitEvent(aux, in_ready, 0));
+  if (h->post_used[slot]) QRE_CUDA(cudaStreamWaitEvent(aux, h->ev_post[slot], 0));
+  h->launches += launch_prep_queries(s, m, d_q, d_ctx, aux);
+  QRE_CUDA(cudaGetLastError());
+  qre_params_t p_merge = p;
+  if (!serial) {
+    QRE_CUDA(cudaEventRecord(h->ev_prep[slot], aux));
+    QRE_CUDA(cudaStreamWaitEvent(s.stream, h->ev_prep[slot], 0));
+    if (p.do_route) {
+      // routing needs the prepared queries only: it runs on the aux stream beside the scan, and
+      // the post stream's merge then fills in the lookup half of the results
+      h->launches += launch_route_only(s, m, d_tok, d_hd, d_hc, p, out_dev, aux);
+      QRE_CUDA(cudaGetLastError());
+      QRE_CUDA(cudaEventRecord(h->ev_route[slot], aux));
+      p_merge.do_route = 0;
+    }
+  }
+  int rc = tensor_scan_enqueue(h, m, p, s.stream);
+  if (rc != QRE_OK) return rc;
+  if (!serial) {
+    QRE_CUDA(cudaEventRecord(h->ev_scan[slot], s.stream));
+    QRE_CUDA(cudaStreamWaitEvent(post, h->ev_scan[slot], 0));
+  }
+  const bool sharded = h->xchg != nullptr && h->xchg_world > 1;
+  rc = rescore_enqueue(h, m, p, sharded ? h->xchg_rank : 0, B.cand, post);
+  if (rc != QRE_OK) return rc;
+  if (sharded) {
+    rc = qre_publish_dev(h, m, B.cand, post);
+    if (rc != QRE_OK) return rc;
+    rc = qre_merge_route_xchg_dev(h, m, d_tok, d_hd, d_hc, &p_merge, const_cast<qre_result_t*>(&out_dev), post);
+    if (rc != QRE_OK) return rc;
+  } else {
+    h->launches += launch_merge_route(s, m, 1, B.cand, d_tok, d_hd, d_hc, p_merge, out_dev, post);
+    QRE_CUDA(cudaGetLastError());
+  }
+  if (!serial && p.do_route) QRE_CUDA(cudaStreamWaitEvent(post, h->ev_route[slot], 0));   // batch done = both halves
+  QRE_CUDA(cudaEventRecord(h->ev_post[slot], post));
+  h->post_used[slot] = true;
+  return QRE_OK;
+}
+
+int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries, const uint64_t* q_ctx, const int32_t* tok,
+                   const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
+                   qre_result_t* out_dev, void* in_stream) {
+  if (h == nullptr || out_dev == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
+  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
+  if (!queries || !q_ctx) return fail(QRE_ERR_INVALID, "NULL argument");
+  int rc = validate_params(h, params);
+  if (rc != QRE_OK) return rc;
+  if (params->do_route && (!tok || !heur_dev || !heur_conf))
+    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
+  DeviceGuard guard(h->s.device);
+  cudaEvent_t ready = nullptr;
+  if (in_stream != nullptr) {
+    QRE_CUDA(cudaEventRecord(h->ev_in[slot], (cudaStream_t)in_stream));
+    ready = h->ev_in[slot];
+  }
+  return pipeline_enqueue(h, slot, m, queries, q_ctx, tok, heur_dev, heur_conf, *params, *out_dev, ready, false);
+}
+
+int qre_wait_dev(qre_cache_t* h, int slot, void* stream) {
+  if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
+  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (!h->post_used[slot]) return QRE_OK;
+  DeviceGuard guard(h->s.device);
+  if (stream != nullptr) QRE_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_post[slot], 0));
+  else QRE_CUDA(cudaEventSynchronize(h->ev_post[slot]));
+  return QRE_OK;
+}
+
 int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries, const uint64_t* q_ctx,
                            const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
                            const qre_params_t* params) {
@@ -871,7 +1006,6 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   DeviceState& s = h->s;
   S.m = m;
   S.p = *params;
-  S.p.pipeline_slot = 0;       // one compute stream: scan(i+1) is ordered after merge(i)
   // ---- inputs ----
   // Large batches: small arrays through pinned staging, the query matrix straight from the caller's
   // buffer when that is already page-locked, one H2D copy on the copy stream (it runs under the
@@ -896,7 +1030,6 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   S.d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m, true);
   S.d_hd = put(heur_dev, (size_t)m, true);
   S.d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m, true);
-  cudaStream_t st = s.stream;
   if (!zero_copy) {
     if (direct) {
       QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, h->h2d));
@@ -906,24 +1039,19 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
       QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, h->h2d));
     }
     QRE_CUDA(cudaEventRecord(S.e_in, h->h2d));
-    QRE_CUDA(cudaStreamWaitEvent(st, S.e_in, 0));
   }
-  rc = scan_enqueue(h, m, d_q, d_ctx, S.p, 0, h->d_cand, st);
-  if (rc != QRE_OK) return rc;
   const int K = S.p.do_route ? s.n_centroids : 0;
   const int D = S.p.do_route ? S.p.n_devices : 1;
   S.L.plan(m, K, D);
   uint8_t* res_base = zero_copy ? S.h_res : S.d_res;
   const qre_result_t dres = S.L.view(res_base);
-  h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p, dres, st);
-  QRE_CUDA(cudaGetLastError());
-  QRE_CUDA(cudaMemcpyAsync(res_base + S.L.ovf.off, s.ovf_unresolved, sizeof(int32_t),
-                           zero_copy ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+  rc = pipeline_enqueue(h, slot, m, d_q, d_ctx, S.d_tok, S.d_hd, S.d_hc, S.p, dres, zero_copy ? nullptr : S.e_in,
+                        zero_copy);
+  if (rc != QRE_OK) return rc;
   if (zero_copy) {
-    QRE_CUDA(cudaEventRecord(S.e_done, st));
+    QRE_CUDA(cudaEventRecord(S.e_done, s.stream));
   } else {
-    QRE_CUDA(cudaEventRecord(S.e_mid, st));
-    QRE_CUDA(cudaStreamWaitEvent(h->d2h, S.e_mid, 0));
+    QRE_CUDA(cudaStreamWaitEvent(h->d2h, h->ev_post[slot], 0));
     QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, h->d2h));
     QRE_CUDA(cudaEventRecord(S.e_done, h->d2h));
   }
@@ -939,10 +1067,8 @@ int qre_lookup_route_end(qre_cache_t* h, int slot, qre_result_t* out) {
   DeviceGuard guard(h->s.device);
   QRE_CUDA(cudaEventSynchronize(S.e_done));
   S.pending = false;
-  const int32_t n_left = *reinterpret_cast<const int32_t*>(S.h_res + S.L.ovf.off);
-  if (n_left > 0)
-    return fail(QRE_ERR_OVERFLOW, "%d overflowed queries beyond the device-side fallback's capacity; "
-                "re-run this batch with qre_lookup_route", (int)n_left);
+  // every overflowed query has been settled on the device (the settle pass covers a whole batch),
+  // so the asynchronous path is exact on its own
   const int K = S.p.do_route ? h->s.n_centroids : 0;
   const int D = S.p.do_route ? S.p.n_devices : 1;
   scatter_results(S, K, D, out);
@@ -957,28 +1083,7 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
     return fail(QRE_ERR_INVALID, "asynchronous batches in flight: finish them with qre_lookup_route_end first");
   int rc = qre_lookup_route_begin(h, 0, m, queries, q_ctx, tok, heur_dev, heur_conf, params);
   if (rc != QRE_OK) return rc;
-  rc = qre_lookup_route_end(h, 0, out);
-  if (rc != QRE_ERR_OVERFLOW) return rc;
-  // very rare: more overflowed queries than the device-side fallback settles per batch (512).
-  // The handle still holds this batch's state: settle all of them with host-driven brute-force
-  // passes, merge again and read the results back.
-  DeviceGuard guard(h->s.device);
-  DeviceState& s = h->s;
-  qre_cache_t::HostSlot& S = h->hs[0];
-  cudaStream_t st = s.stream;
-  int32_t n_ovf = 0;
-  QRE_CUDA(cudaMemcpy(&n_ovf, s.ovf_count, sizeof(int32_t), cudaMemcpyDeviceToHost));
-  h->launches += launch_exact_scan(s, m, h->hwm, h->d_q_ctx, s.ovf_list, n_ovf, true, S.p, 0, h->d_cand, st);
-  QRE_CUDA(cudaGetLastError());
-  QRE_CUDA(cudaMemsetAsync(s.ovf_unresolved, 0, sizeof(int32_t), st));
-  const bool zero_copy = m <= kBM;                  // same rule as qre_lookup_route_begin
-  h->launches += launch_merge_route(s, m, 1, h->d_cand, S.d_tok, S.d_hd, S.d_hc, S.p,
-                                    S.L.view(zero_copy ? S.h_res : S.d_res), st);
-  QRE_CUDA(cudaGetLastError());
-  if (!zero_copy) QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, st));
-  QRE_CUDA(cudaStreamSynchronize(st));
-  scatter_results(S, S.p.do_route ? s.n_centroids : 0, S.p.do_route ? S.p.n_devices : 1, out);
-  return QRE_OK;
+  return qre_lookup_route_end(h, 0, out);
 }
 
 // ---- binary snapshot -----------------------------------------------------
@@ -1152,7 +1257,12 @@ int qre_debug_gemm(qre_cache_t* h, int m, int64_t row0, int n, float* out) {
   memset(&p, 0, sizeof(p));
   p.similarity_threshold = 2.0;   // floor above any cosine: the candidate path stays idle
   p.ttl_us = 1;
-  h->launches += launch_gemm_topk(s, m, h->hwm, h->d_q_ctx, p, h->d_dump, n, row0, n, s.stream);
+  s.slot = h->last_slot;
+  {
+    const int nl = launch_gemm_topk(s, m, h->hwm, p, h->d_dump, n, row0, n, s.stream);
+    if (nl < 0) return fail(QRE_ERR_CAPACITY, "scan geometry does not fit the top-k scratch");
+    h->launches += nl;
+  }
   QRE_CUDA(cudaGetLastError());
   QRE_CUDA(cudaMemcpyAsync(out, h->d_dump, bytes, cudaMemcpyDeviceToHost, s.stream));
   QRE_CUDA(cudaStreamSynchronize(s.stream));

@@ -19,7 +19,9 @@ constexpr int kMaxKBStream = 16;  // streaming-A variant: dim_pad <= 1024
 constexpr int kTopK = QRE_TOPK;
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr int kExactGroup = 8;        // queries per brute-force pass
-constexpr int kSettleMaxGroups = 64;  // overflowed queries settled on the device per batch: 512
+constexpr uint32_t kNoChunk = 0xFFFFFFFFu;    // empty spill chain
+constexpr uint32_t kChunkLost = 0xFFFFFFFEu;  // spill pool exhausted: this (query, range) lost candidates
+constexpr int kSpillPer = 15;         // candidates per spill chunk (128-byte chunks)
 constexpr float kNormEps = 1e-9f;                 // src/cache.py:284,289 ; qre:136
 
 // |approx - cosine| bound of the bf16 tensor-core score: two bf16 roundings (2^-9 each)
@@ -35,6 +37,16 @@ struct __align__(8) PartialEntry {  // approximate candidate kept by the fused t
   float v;                          // bf16 tensor-core cosine
   uint32_t row;                     // slot, kNoRow = empty
 };
+
+// Candidates that fall off a (query, row range) top-k list while still inside the exactness
+// window are chained here instead of being dropped: each epilogue thread owns
+// its chain, chunks come from a per-batch pool by one atomic bump per 15 candidates.
+struct __align__(16) SpillChunk {
+  uint32_t next;                    // older chunk of the same chain, kNoChunk = end
+  uint32_t n;                       // entries used
+  PartialEntry e[kSpillPer];
+};
+static_assert(sizeof(SpillChunk) == 128, "one chunk = one 128-byte line");
 
 struct ExactBest {                  // per-(CTA, query) winner of the brute-force scan
   float sim;
@@ -55,6 +67,10 @@ struct GemmArgs {
   const uint64_t* q_ctx;    // [m]
   const RowMeta* meta;      // [capacity]
   PartialEntry* partial;    // [mblocks*128][S][kTopK]   (scratch)
+  uint32_t* spill_head;     // [mblocks*128][S]  chain head per (query, range): kNoChunk / kChunkLost / index
+  SpillChunk* spill_pool;   // [spill_cap]
+  uint32_t* spill_next;     // bump counter, zeroed per batch
+  uint32_t spill_cap;
   float* dump;              // debug: raw accumulators out[q * dump_ld + (row - dump_row0)]
   long long dump_ld, dump_row0;
 };
@@ -86,31 +102,44 @@ struct DeviceState {
   uint64_t* lru = nullptr;            // [capacity]
   uint8_t* pred_dev = nullptr;        // [capacity]
   double* pred_conf = nullptr;        // [capacity]
-  // per-batch query state
-  // q_f32 / q_norm / q_flags are double-buffered ("pipeline slots"): merge_route of batch i may
-  // still read slot i&1 on another stream while the scan of batch i+1 fills the other slot.
+  // Per-batch state.  Everything one in-flight batch reads or writes exists twice ("pipeline
+  // slots"): query preparation of batch i+1 and re-score / merge / routing of batch i-1 run on
+  // other streams beside the scan of batch i.
+  struct Batch {
+    float* q_f32 = nullptr;             // [mb_pad, dim_pad]  zero padded fp32 queries
+    __nv_bfloat16* q_bf16 = nullptr;    // [mb_pad, dim_pad]  L2-normalised bf16 operand of the scan
+    float* q_norm = nullptr;            // [mb_pad]
+    uint64_t* q_ctx = nullptr;          // [max_batch] private copy of the batch's contexts
+    uint8_t* q_flags = nullptr;         // [max_batch] QRE_FLAG_*
+    PartialEntry* partial = nullptr;    // [partial_entries]  per (query, range) approximate top-k
+    uint32_t* spill_head = nullptr;     // [partial_entries / kTopK]
+    SpillChunk* spill_pool = nullptr;   // [spill_cap]
+    uint32_t* counters = nullptr;       // [4]: 0 spill bump counter, 1 overflowed queries, 2 unresolved
+    int32_t* ovf_list = nullptr;        // [max_batch]
+    qre_candidate_t* cand = nullptr;    // [max_batch, kTopK] this shard's exactly re-scored candidates
+    CUtensorMap tmap_q;                 // 128-row boxes over q_bf16
+    int32_t* ovf_count() const { return reinterpret_cast<int32_t*>(counters + 1); }
+    int32_t* ovf_unresolved() const { return reinterpret_cast<int32_t*>(counters + 2); }
+  };
+  Batch batch[2];
   int slot = 0;
-  float* q_f32[2] = {nullptr, nullptr};     // [mb_pad, dim_pad]
-  __nv_bfloat16* q_bf16 = nullptr;          // [mb_pad, dim_pad]  (scan only: single buffer)
-  float* q_norm[2] = {nullptr, nullptr};    // [mb_pad]
-  // scratch
-  PartialEntry* partial = nullptr;    // [partial_entries]
+  Batch& cur() { return batch[slot]; }
+  const Batch& cur() const { return batch[slot]; }
+  // scratch shared by both slots (users are serialised on one stream)
   long long partial_entries = 0;
+  uint32_t spill_cap = 0;
   ExactBest* exact_partial = nullptr; // [kExactGroup * exact_grid]
   int exact_grid = 0;
-  int32_t* ovf_count = nullptr;       // [1]  queries whose candidate window overflowed (this batch)
-  int32_t* ovf_unresolved = nullptr;  // [1]  of those, not settled by the device-side fallback
-  unsigned* settle_tickets = nullptr; // [kSettleMaxGroups]
-  ExactBest* settle_partial = nullptr;  // [kSettleMaxGroups][kExactGroup][exact_grid]
-  int32_t* ovf_list = nullptr;        // [max_batch]
-  uint8_t* q_flags[2] = {nullptr, nullptr};  // [max_batch]  QRE_FLAG_* of the batch in each slot
+  int settle_groups = 0;              // ceil(max_batch / kExactGroup): every query of a batch can be settled
+  unsigned* settle_tickets = nullptr; // [settle_groups]
+  ExactBest* settle_partial = nullptr;  // [settle_groups][kExactGroup][exact_grid]
   // router state
   float* centroids = nullptr;         // [K, dim_pad]
   float* cent_norm = nullptr;         // [K]
   uint8_t* cent_owner = nullptr;      // [K]
   int n_centroids = 0;
   double* perf_health = nullptr;      // [QRE_MAX_DEVICES]
-  CUtensorMap tmap_q, tmap_e, tmap_eh;   // queries (128-row box), cache rows (256-row box / 128-row half box)
+  CUtensorMap tmap_e, tmap_eh;        // cache rows (256-row box / 128-row half box)
   bool allow_pair = true;               // QRE_SCAN_SINGLE_CTA=1 forces the single-CTA kernel
   // optional CUDA-event bracket around every scan-kernel launch (bench.py's live roofline)
   bool prof_on = false;
@@ -129,24 +158,30 @@ int launch_update_meta(DeviceState& s, long long n, const int64_t* slot_dev, con
                        cudaStream_t st);
 int launch_tombstone(DeviceState& s, long long n, const int64_t* slot_dev, cudaStream_t st);
 int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, float* out, cudaStream_t st);
-int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src,
-                        uint64_t* q_ctx_dst, cudaStream_t st);
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src, cudaStream_t st);
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st);
-int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const qre_params_t& p,
                      float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st);
-int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const qre_params_t& p,
                           float* dump, long long dump_ld, long long dump_row0, cudaStream_t st);
+// Shared by both scan launchers: the argument block of one launch on the current slot.
+GemmArgs make_gemm_args(const DeviceState& s, const ScanGeometry& g, int m, long long n_rows, const qre_params_t& p,
+                        float* dump, long long dump_ld, long long dump_row0);
 int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& p, int shard,
                    qre_candidate_t* cand, cudaStream_t st);
-int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const int32_t* qlist_dev,
+int launch_exact_scan(DeviceState& s, int m, long long n_rows, const int32_t* qlist_dev,
                       int nq_total, bool use_ovf_list, const qre_params_t& p, int shard, qre_candidate_t* cand,
                       cudaStream_t st);
-int launch_overflow_settle(DeviceState& s, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p, int shard,
+int launch_overflow_settle(DeviceState& s, long long n_rows, const qre_params_t& p, int shard,
                            qre_candidate_t* cand, cudaStream_t st);
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
                        const qre_result_t& out, cudaStream_t st, long long shard_stride = 0,
                        const uint32_t* wait_flags = nullptr, uint32_t wait_epoch = 0);
+// The routing half of merge_route alone (needs only the prepared queries): the pipeline runs it
+// beside the scan instead of after it.
+int launch_route_only(DeviceState& s, int m, const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
+                      const qre_params_t& p, const qre_result_t& out, cudaStream_t st);
 int launch_publish(int m, int world, const qre_candidate_t* cand, qre_candidate_t* const* dst, uint32_t* const* flag,
                    uint32_t epoch, unsigned* ticket, cudaStream_t st);
 

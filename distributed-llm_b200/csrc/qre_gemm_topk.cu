@@ -44,7 +44,7 @@ constexpr uint32_t kTmemCols = 512;
 template <bool kDump, bool kResident>
 __global__ void __launch_bounds__(kThreads, 1)
 qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_e,
-                     const GemmArgs a) {
+                     const __grid_constant__ GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   // resident: [A: 6 x 16 KB][B ring: 4 x 32 KB]; streaming: ring of 4 x (A 16 KB + B 32 KB)
@@ -54,11 +54,11 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (kResident ? kSmemA + kSmemB : kStages * kStageBytes));
   uint64_t* full = bars;                    // [kStages]  TMA -> MMA
   uint64_t* empty = bars + kStages;         // [kStages]  MMA -> TMA
-  uint64_t* a_full = bars + 2 * kStages;    // TMA -> MMA (resident A block landed)
-  uint64_t* a_empty = a_full + 1;           // MMA -> TMA (all MMAs reading A retired)
-  uint64_t* t_full = a_full + 2;            // [2] MMA -> epilogue
-  uint64_t* t_empty = a_full + 4;           // [2] epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 6);
+  uint64_t* a_full = bars + 2 * kStages;    // [kMaxKB] TMA -> MMA (resident A k-block landed)
+  uint64_t* a_empty = a_full + kMaxKB;      // [kMaxKB] MMA -> TMA (last MMA of the unit reading A[kb] retired)
+  uint64_t* t_full = a_empty + kMaxKB;      // [2] MMA -> epilogue
+  uint64_t* t_empty = t_full + 2;           // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -70,8 +70,10 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
-    mbar_init(a_full, 1);
-    mbar_init(a_empty, 1);
+    for (int i = 0; i < kMaxKB; ++i) {
+      mbar_init(&a_full[i], 1);
+      mbar_init(&a_empty[i], 1);
+    }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&t_full[i], 1);
       mbar_init(&t_empty[i], 128);
@@ -97,15 +99,13 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       for (int u = blockIdx.x; u < U; u += gridDim.x) {
         const int s = u / a.mblocks, mb = u - s * a.mblocks;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        if (kResident) {
-          mbar_wait(a_empty, (a_iter & 1) ^ 1);
-          mbar_arrive_expect_tx(a_full, static_cast<uint32_t>(a.num_kb) * kABytesPerKB);
-          for (int kb = 0; kb < a.num_kb; ++kb)
-            tma_load_2d(sA + kb * kABytesPerKB, &tmap_q, a_full, kb * kBK, mb * kBM);
-          ++a_iter;
-        }
         for (int t = t0; t < t1; ++t) {
           for (int kb = 0; kb < a.num_kb; ++kb) {
+            if (kResident && t == t0) {        // this unit's query block, handed over per k-block
+              mbar_wait(&a_empty[kb], (a_iter & 1) ^ 1);
+              mbar_arrive_expect_tx(&a_full[kb], kABytesPerKB);
+              tma_load_2d(sA + kb * kABytesPerKB, &tmap_q, &a_full[kb], kb * kBK, mb * kBM);
+            }
             mbar_wait(&empty[stage], phase ^ 1);
             mbar_arrive_expect_tx(&full[stage], kStageBytes);
             if (!kResident) tma_load_2d(sA + stage * kStageBytes, &tmap_q, &full[stage], kb * kBK, mb * kBM);
@@ -113,6 +113,7 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
+        ++a_iter;
       }
     }
   } else if (warp == 5) {
@@ -124,13 +125,13 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       for (int u = blockIdx.x; u < U; u += gridDim.x) {
         const int s = u / a.mblocks;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        if (kResident) mbar_wait(a_full, a_iter & 1);
         for (int t = t0; t < t1; ++t) {
           const uint32_t acc = tile_iter & 1;
           mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * kBN;
           for (int kb = 0; kb < a.num_kb; ++kb) {
+            if (kResident && t == t0) mbar_wait(&a_full[kb], a_iter & 1);
             mbar_wait(&full[stage], phase);
             tc_fence_after();
             const uint64_t adesc = umma_desc_sw128(sA_addr + (kResident ? kb * kABytesPerKB : stage * kStageBytes));
@@ -141,15 +142,13 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
               umma_bf16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
             }
             umma_commit(&empty[stage]);          // stage free once these MMAs retire
+            if (kResident && t == t1 - 1) umma_commit(&a_empty[kb]);   // last reader of A[kb] in this unit
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
           umma_commit(&t_full[acc]);             // accumulator complete -> epilogue
           ++tile_iter;
         }
-        if (kResident) {
-          umma_commit(a_empty);                  // resident A no longer read
-          ++a_iter;
-        }
+        ++a_iter;
       }
     }
   } else {
@@ -174,7 +173,7 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         mbar_arrive(&t_empty[acc]);
         ++tile_iter;
       }
-      if (active) topk_store(tk, a.partial + (static_cast<long long>(q) * a.splits + s) * kTopK);
+      if (active) topk_store(tk, a, static_cast<long long>(q) * a.splits + s);
     }
   }
 
@@ -247,11 +246,9 @@ cudaError_t gemm_topk_init() {
   return e;
 }
 
-int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
-                     float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st) {
-  (void)dump_n;
-  const ScanGeometry g = plan_for(s, m, n_rows, p);
-  if (g.pair) return launch_gemm_topk_pair(s, m, n_rows, q_ctx, p, dump, dump_ld, dump_row0, st);
+GemmArgs make_gemm_args(const DeviceState& s, const ScanGeometry& g, int m, long long n_rows, const qre_params_t& p,
+                        float* dump, long long dump_ld, long long dump_row0) {
+  const DeviceState::Batch& b = s.cur();
   GemmArgs a;
   a.m = m;
   a.mblocks = g.mblocks;
@@ -263,21 +260,42 @@ int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const uint64_t* q_
   a.floor_v = static_cast<float>(thr) - kApproxEps;
   a.now_us = p.now_us;
   a.ttl_us = p.ttl_us;
-  a.q_ctx = q_ctx;
+  a.q_ctx = b.q_ctx;
   a.meta = s.meta;
-  a.partial = s.partial;
+  a.partial = b.partial;
+  a.spill_head = b.spill_head;
+  a.spill_pool = b.spill_pool;
+  a.spill_next = b.counters;
+  a.spill_cap = s.spill_cap;
   a.dump = dump;
   a.dump_ld = dump_ld;
   a.dump_row0 = dump_row0;
+  return a;
+}
+
+// The scratch is sized from the hard bound on work units (8 rounds of the SM count); a geometry
+// that would not fit is a bug in the planner, never a silent overrun.
+bool geometry_fits(const DeviceState& s, const ScanGeometry& g) {
+  const long long blocks = g.pair ? 2LL * ((g.mblocks + 1) / 2) : g.mblocks;
+  return blocks * kBM * g.splits * kTopK <= s.partial_entries;
+}
+
+int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const qre_params_t& p,
+                     float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st) {
+  (void)dump_n;
+  const ScanGeometry g = plan_for(s, m, n_rows, p);
+  if (!geometry_fits(s, g)) return -1;
+  if (g.pair) return launch_gemm_topk_pair(s, m, n_rows, p, dump, dump_ld, dump_row0, st);
+  const GemmArgs a = make_gemm_args(s, g, m, n_rows, p, dump, dump_ld, dump_row0);
   const bool prof = s.prof_on && s.prof_ev != nullptr && s.prof_used < kProfMax && dump == nullptr;
   if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
   const bool resident = a.num_kb <= kMaxKB;
   if (dump != nullptr) {
-    if (resident) qre_gemm_topk_kernel<true, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
-    else qre_gemm_topk_kernel<true, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+    if (resident) qre_gemm_topk_kernel<true, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
+    else qre_gemm_topk_kernel<true, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
   } else {
-    if (resident) qre_gemm_topk_kernel<false, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
-    else qre_gemm_topk_kernel<false, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.tmap_q, s.tmap_e, a);
+    if (resident) qre_gemm_topk_kernel<false, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
+    else qre_gemm_topk_kernel<false, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
   }
   if (prof) {
     cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);

@@ -10,10 +10,14 @@
 // an 8-deep B ring.
 //
 // Protocol (barrier objects live at the same shared-memory offset in both CTAs):
-//   full[s], a_full   leader (rank 0) only, count 2: both CTAs' producers arrive (the leader
-//                     with expect_tx for both halves); both CTAs' TMA loads complete_tx there.
-//   empty[s], a_empty, t_full[acc]   in each CTA, signalled by the leader's MMA thread with a
-//                     multicast tcgen05.commit (mask 0b11).
+//   full[s], a_full[kb]   leader (rank 0) only, count 2: both CTAs' producers arrive (the
+//                     leader with expect_tx for both halves); both CTAs' TMA loads complete_tx there.
+//   empty[s], a_empty[kb], t_full[acc]   in each CTA, signalled by the leader's MMA thread with
+//                     a multicast tcgen05.commit (mask 0b11).
+// The resident query block is handed over per k-block: a_empty[kb] is committed right after the
+// LAST tile's MMAs on k-block kb, so the next work unit's A[kb] streams in (interleaved with the
+// first tile's cache-row loads) while the last tile is still being multiplied — no reload bubble
+// between units.
 //   t_empty[acc]      leader only, count 256: the epilogue threads of both CTAs arrive remotely.
 // Only the leader issues MMAs; both CTAs run a TMA producer and four epilogue warps over their
 // own 128 TMEM lanes.
@@ -31,7 +35,7 @@ namespace qre {
 namespace {
 
 constexpr int kThreads2 = 192;
-constexpr int kStages2 = 8;
+constexpr int kStages2 = 7;           // 7 x 16 KB: leaves ~18 KB of the SM's shared memory to small kernels running beside the scan
 constexpr int kABytesPerKB2 = kBM * kBK * 2;          // 16 KB
 constexpr int kBHalfRows = kBN / 2;                   // 128 cache rows per CTA per tile
 constexpr int kBHalfBytes = kBHalfRows * kBK * 2;     // 16 KB
@@ -107,7 +111,7 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
 template <bool kDump>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_eh,
-                          const GemmArgs a) {
+                          const __grid_constant__ GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -115,11 +119,11 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA2 + kSmemB2);
   uint64_t* full = bars;                       // [kStages2]
   uint64_t* empty = bars + kStages2;           // [kStages2]
-  uint64_t* a_full = bars + 2 * kStages2;
-  uint64_t* a_empty = a_full + 1;
-  uint64_t* t_full = a_full + 2;               // [2]
-  uint64_t* t_empty = a_full + 4;              // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 6);
+  uint64_t* a_full = bars + 2 * kStages2;      // [kMaxKB]
+  uint64_t* a_empty = a_full + kMaxKB;         // [kMaxKB]
+  uint64_t* t_full = a_empty + kMaxKB;         // [2]
+  uint64_t* t_empty = t_full + 2;              // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -135,8 +139,10 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       mbar_init(&full[i], 2);
       mbar_init(&empty[i], 1);
     }
-    mbar_init(a_full, 2);
-    mbar_init(a_empty, 1);
+    for (int i = 0; i < kMaxKB; ++i) {
+      mbar_init(&a_full[i], 2);
+      mbar_init(&a_empty[i], 1);
+    }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&t_full[i], 1);
       mbar_init(&t_empty[i], 256);
@@ -165,14 +171,14 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         const int s = u / npairs, pr = u - s * npairs;
         const int mb = 2 * pr + static_cast<int>(rank);
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        mbar_wait(a_empty, (a_iter & 1) ^ 1);
-        if (leader) mbar_arrive_expect_tx(a_full, 2u * static_cast<uint32_t>(a.num_kb) * kABytesPerKB2);
-        else mbar_arrive_remote(a_full, 0);
-        for (int kb = 0; kb < a.num_kb; ++kb)
-          tma_load_2d_pair(sA + kb * kABytesPerKB2, &tmap_q, a_full, kb * kBK, mb * kBM);
-        ++a_iter;
         for (int t = t0; t < t1; ++t) {
           for (int kb = 0; kb < a.num_kb; ++kb) {
+            if (t == t0) {                     // this unit's query block, one k-block at a time
+              mbar_wait(&a_empty[kb], (a_iter & 1) ^ 1);
+              if (leader) mbar_arrive_expect_tx(&a_full[kb], 2u * kABytesPerKB2);
+              else mbar_arrive_remote(&a_full[kb], 0);
+              tma_load_2d_pair(sA + kb * kABytesPerKB2, &tmap_q, &a_full[kb], kb * kBK, mb * kBM);
+            }
             mbar_wait(&empty[stage], phase ^ 1);
             if (leader) mbar_arrive_expect_tx(&full[stage], 2u * kBHalfBytes);
             else mbar_arrive_remote(&full[stage], 0);
@@ -181,6 +187,7 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             if (++stage == kStages2) { stage = 0; phase ^= 1; }
           }
         }
+        ++a_iter;
       }
     }
   } else if (warp == 5) {
@@ -192,13 +199,13 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       for (int u = cluster_id; u < U; u += n_clusters) {
         const int s = u / npairs;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        mbar_wait(a_full, a_iter & 1);
         for (int t = t0; t < t1; ++t) {
           const uint32_t acc = tile_iter & 1;
           mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * kBN;
           for (int kb = 0; kb < a.num_kb; ++kb) {
+            if (t == t0) mbar_wait(&a_full[kb], a_iter & 1);
             mbar_wait(&full[stage], phase);
             tc_fence_after();
             const uint64_t adesc = umma_desc_sw128(sA_addr + kb * kABytesPerKB2);
@@ -207,12 +214,12 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             for (int k = 0; k < kBK / 16; ++k)
               umma_bf16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
             umma_commit_pair(&empty[stage]);
+            if (t == t1 - 1) umma_commit_pair(&a_empty[kb]);   // last reader of A[kb] in this unit
             if (++stage == kStages2) { stage = 0; phase ^= 1; }
           }
           umma_commit_pair(&t_full[acc]);
           ++tile_iter;
         }
-        umma_commit_pair(a_empty);
         ++a_iter;
       }
     }
@@ -239,7 +246,7 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         mbar_arrive_remote(&t_empty[acc], 0);      // the leader's MMA thread owns the accumulator hand-off
         ++tile_iter;
       }
-      if (active) topk_store(tk, a.partial + (static_cast<long long>(q) * a.splits + s) * kTopK);
+      if (active) topk_store(tk, a, static_cast<long long>(q) * a.splits + s);
     }
   }
 
@@ -279,32 +286,17 @@ ScanGeometry plan_scan_pair(int m, long long n_rows, int num_sms) {
   return g;
 }
 
-int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p,
+int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const qre_params_t& p,
                           float* dump, long long dump_ld, long long dump_row0, cudaStream_t st) {
-  const ScanGeometry g = plan_scan_pair(m, n_rows, scan_sms(s, p));
-  GemmArgs a;
-  a.m = m;
-  a.mblocks = g.mblocks;
-  a.tiles_n = g.tiles_n;
-  a.splits = g.splits;
-  a.num_kb = s.dim_pad / kBK;
-  a.n_rows = n_rows;
-  const double thr = p.similarity_threshold > 0.0 ? p.similarity_threshold : 0.0;
-  a.floor_v = static_cast<float>(thr) - kApproxEps;
-  a.now_us = p.now_us;
-  a.ttl_us = p.ttl_us;
-  a.q_ctx = q_ctx;
-  a.meta = s.meta;
-  a.partial = s.partial;
-  a.dump = dump;
-  a.dump_ld = dump_ld;
-  a.dump_row0 = dump_row0;
+  ScanGeometry g = plan_scan_pair(m, n_rows, scan_sms(s, p));
+  g.pair = true;
+  const GemmArgs a = make_gemm_args(s, g, m, n_rows, p, dump, dump_ld, dump_row0);
   const bool prof = s.prof_on && s.prof_ev != nullptr && s.prof_used < kProfMax && dump == nullptr;
   if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
   if (dump != nullptr)
-    qre_gemm_topk_pair_kernel<true><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.tmap_q, s.tmap_eh, a);
+    qre_gemm_topk_pair_kernel<true><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.cur().tmap_q, s.tmap_eh, a);
   else
-    qre_gemm_topk_pair_kernel<false><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.tmap_q, s.tmap_eh, a);
+    qre_gemm_topk_pair_kernel<false><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.cur().tmap_q, s.tmap_eh, a);
   if (prof) {
     cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);
     ++s.prof_used;

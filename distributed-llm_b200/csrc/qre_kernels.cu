@@ -147,10 +147,10 @@ __global__ void gather_rows_kernel(long long n, const int64_t* slot, const float
 // Queries: fp32 copy (zero padded), |q|, and the L2-normalised bf16 operand of the scan.
 __global__ void prep_queries_kernel(int m, int rows_total, const float* q, int dim, int dim_pad, float* q_f32,
                                     __nv_bfloat16* q_bf16, float* q_norm, const uint64_t* q_ctx_src,
-                                    uint64_t* q_ctx_dst, int32_t* ovf_count) {
+                                    uint64_t* q_ctx_dst, uint32_t* counters) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (blockIdx.x == 0 && threadIdx.x == 0) *ovf_count = 0;     // per-batch overflow counter
+  if (blockIdx.x == 0 && threadIdx.x < 4) counters[threadIdx.x] = 0u;   // spill bump, overflow counters
   if (w >= rows_total) return;
   if (lane == 0 && w < m) q_ctx_dst[w] = q_ctx_src[w];          // private copy for the scan
   float* dst = q_f32 + static_cast<long long>(w) * dim_pad;
@@ -194,6 +194,8 @@ struct RescoreArgs {
   float floor_v;
   double thr;
   const PartialEntry* partial;
+  const uint32_t* spill_head;
+  const SpillChunk* spill_pool;
   const float* q_f32;
   const float* q_norm;
   const float* rows_f32;
@@ -229,6 +231,20 @@ __device__ __forceinline__ void list_insert(CandList& L, float sim, uint32_t row
   if (L.n < kTopK) ++L.n;
 }
 
+// Exact score of one candidate row for the warp's query; lane 0 keeps the (sim desc, lru asc) list.
+__device__ __forceinline__ void rescore_one(const RescoreArgs& a, CandList& L, const float* qv, float nq,
+                                            uint32_t row, int lane) {
+  const float ne = a.row_norm[row];
+  const float dot = warp_dot(qv, a.rows_f32 + static_cast<long long>(row) * a.dim_pad, a.dim_pad, lane);
+  if (ne >= kNormEps) {                                // cache.py:289-290
+    const float sim = exact_sim(dot, nq, ne);
+    if (static_cast<double>(sim) >= a.thr && sim > 0.f) {          // cache.py:292, best_sim starts at 0.0
+      if (lane == 0) list_insert(L, sim, row, a.lru[row]);
+    }
+  }
+  __syncwarp();
+}
+
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) rescore_kernel(const RescoreArgs a) {
   __shared__ CandList lists[kWarpsPerBlock];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -244,22 +260,22 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) rescore_kernel(const Resc
     flags |= QRE_FLAG_ZERO_NORM;                     // cache.py:284-285: return None
   } else {
     const PartialEntry* pe = a.partial + static_cast<long long>(q) * a.splits * kTopK;
+    const uint32_t* heads = a.spill_head + static_cast<long long>(q) * a.splits;
     const int cnt = a.splits * kTopK;
+    // a* = best approximate score of any masked row: the head of some range's list (chained
+    // candidates are never better than the list they fell off)
     float amax = -INFINITY;
-    for (int i = lane; i < cnt; i += 32) {
-      const PartialEntry e = pe[i];
+    for (int s = lane; s < a.splits; s += 32) {
+      const PartialEntry e = pe[s * kTopK];
       if (e.row != kNoRow) amax = fmaxf(amax, e.v);
+      if (heads[s] == kChunkLost) ovf = true;          // the spill pool ran out inside this range
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(kFull, amax, o));
-    if (amax != -INFINITY) {
-      // The exact winner has approx >= amax - 2 eps (DESIGN.md §4); nothing under the floor can hit.
+    ovf = __any_sync(kFull, ovf);
+    if (amax != -INFINITY && !ovf) {
+      // The exact winner has approx >= amax - 2 eps (DESIGN.md §3.2); nothing under the floor can hit.
       const float cut = fmaxf(amax - 2.f * kApproxEps, a.floor_v);
-      for (int s = lane; s < a.splits; s += 32) {
-        const PartialEntry e = pe[s * kTopK + kTopK - 1];
-        if (e.row != kNoRow && e.v >= cut) ovf = true;   // this range may have dropped a contender
-      }
-      ovf = __any_sync(kFull, ovf);
       const float* qv = a.q_f32 + static_cast<long long>(q) * a.dim_pad;
       for (int base = 0; base < cnt; base += 32) {
         const int i = base + lane;
@@ -271,16 +287,26 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) rescore_kernel(const Resc
         while (mask) {
           const int src = __ffs(mask) - 1;
           mask &= mask - 1;
-          const uint32_t row = __shfl_sync(kFull, e.row, src);
-          const float ne = a.row_norm[row];
-          const float dot = warp_dot(qv, a.rows_f32 + static_cast<long long>(row) * a.dim_pad, a.dim_pad, lane);
-          if (ne >= kNormEps) {                          // cache.py:289-290
-            const float sim = exact_sim(dot, nq, ne);
-            if (static_cast<double>(sim) >= a.thr && sim > 0.f) {   // cache.py:292, best_sim starts at 0.0
-              if (lane == 0) list_insert(L, sim, row, a.lru[row]);
-            }
+          rescore_one(a, L, qv, nq, __shfl_sync(kFull, e.row, src), lane);
+        }
+      }
+      // candidates chained off full lists
+      for (int s = 0; s < a.splits; ++s) {
+        uint32_t c = heads[s];
+        while (c != kNoChunk) {
+          const SpillChunk* ch = a.spill_pool + c;
+          const uint32_t n = ch->n;
+          PartialEntry e;
+          e.v = 0.f;
+          e.row = kNoRow;
+          if (lane < static_cast<int>(n)) e = ch->e[lane];
+          unsigned mask = __ballot_sync(kFull, e.row != kNoRow && e.v >= cut);
+          while (mask) {
+            const int src = __ffs(mask) - 1;
+            mask &= mask - 1;
+            rescore_one(a, L, qv, nq, __shfl_sync(kFull, e.row, src), lane);
           }
-          __syncwarp();
+          c = ch->next;
         }
       }
     }
@@ -466,16 +492,19 @@ __global__ void exact_reduce_kernel(int nq, int q_first, const int32_t* qlist, i
 
 // Device-driven overflow settlement: ONE launch after rescore_kernel, no host round trip.  Reads
 // the overflow counter the re-score pass left on the device; exits at once when it is zero (the
-// normal case); otherwise runs the brute-force pass for up to kSettleMaxGroups groups of 8
-// overflowed queries, the last CTA of each group (ticket counter) doing the reduction.
-// *unresolved = overflowed queries beyond that capacity (the host API settles those).
+// normal case: candidates that do not fit a list are chained, so a query overflows only when the
+// spill pool itself ran out); otherwise runs the brute-force pass over groups of 8 overflowed
+// queries, the last CTA of each group (ticket counter) doing the reduction.  The ticket / partial
+// arrays hold max_batch / 8 groups, so every query of a batch can be settled here and
+// *unresolved is always left at 0.
 struct SettleArgs {
   ExactArgs base;                 // nq / q_first / partial filled per group
   const int32_t* ovf_count;
   const int32_t* ovf_list;
   int32_t* unresolved;
-  unsigned* tickets;              // [kSettleMaxGroups], zero between launches
-  ExactBest* partial;             // [kSettleMaxGroups][kExactGroup][gridDim.x]
+  unsigned* tickets;              // [max_groups], zero between launches
+  ExactBest* partial;             // [max_groups][kExactGroup][gridDim.x]
+  int max_groups;                 // ceil(max_batch / kExactGroup): enough for every query of a batch
   int shard;
   const uint8_t* pdev;
   const double* pconf;
@@ -493,7 +522,7 @@ __global__ void __launch_bounds__(kExactWarps * 32) overflow_settle_kernel(const
     return;
   }
   const int groups_all = (n_ovf + kExactGroup - 1) / kExactGroup;
-  const int groups = groups_all < kSettleMaxGroups ? groups_all : kSettleMaxGroups;
+  const int groups = groups_all < sa.max_groups ? groups_all : sa.max_groups;
   for (int g = 0; g < groups; ++g) {
     ExactArgs a = sa.base;
     a.q_first = g * kExactGroup;
@@ -542,98 +571,14 @@ struct MergeArgs {
 };
 
 constexpr int kMergeMax = 128;     // n_shards * kTopK <= 128 (up to 16 shards)
+constexpr int kMergePerLane = kMergeMax / 32;
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const MergeArgs a) {
-  __shared__ qre_candidate_t s_c[kWarpsPerBlock][kMergeMax];
-  __shared__ float s_dsim[kWarpsPerBlock][QRE_MAX_DEVICES];
-  __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * kWarpsPerBlock + warp;
-  if (a.wait_flags != nullptr) {
-    // Peer exchange: every rank's publish kernel stores its candidates into THIS GPU's buffer over
-    // NVLink and then raises its flag to the batch's epoch.  The publishers run on other GPUs, so
-    // this wait never depends on work queued behind it on this GPU.  Bounded: a dead peer must
-    // abort the job, not hang the box.
-    if (threadIdx.x < a.n_shards) {
-      const volatile uint32_t* f = a.wait_flags + threadIdx.x * 32;
-      const long long t0 = clock64();
-      while (*f != a.wait_epoch) {
-        if (clock64() - t0 > 8000000000LL) {
-          printf("qre: peer %d never published epoch %u (saw %u)\n", threadIdx.x, a.wait_epoch, *f);
-          __trap();
-        }
-      }
-      __threadfence_system();
-    }
-    __syncthreads();
-  }
-  if (q >= a.m) return;
-
-  // ---- merge: n_shards * kTopK candidates, comparator (sim desc, lru asc) ----
-  qre_candidate_t* sc = s_c[warp];
-  const int n_cand = a.n_shards * kTopK;
-  for (int i = lane; i < n_cand; i += 32) {
-    const int r = i / kTopK, k = i - r * kTopK;
-    const int4* src = reinterpret_cast<const int4*>(a.cand_all + static_cast<long long>(r) * a.shard_stride +
-                                                    static_cast<long long>(q) * kTopK + k);
-    int4* dst = reinterpret_cast<int4*>(sc + i);     // read through L2: peers may have written it
-    dst[0] = __ldcg(src);
-    dst[1] = __ldcg(src + 1);
-  }
-  __syncwarp();
-  qre_candidate_t best0 = empty_cand();
-  // Most queries have zero or one live candidate, and callers that do not ask for the merged
-  // list only need the winner: run only as many selection rounds as can produce something.
-  int n_valid = 0;
-  for (int i = lane; i < n_cand; i += 32) n_valid += sc[i].slot >= 0 ? 1 : 0;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_xor_sync(kFull, n_valid, o);
-  const int want = a.out.cand != nullptr ? kTopK : 1;
-  const int rounds = n_valid < want ? n_valid : want;
-  if (a.out.cand != nullptr && lane >= rounds && lane < kTopK)
-    a.out.cand[static_cast<long long>(q) * kTopK + lane] = empty_cand();
-  for (int k = 0; k < rounds; ++k) {
-    int bi = -1;
-    float bs = -INFINITY;
-    uint64_t bl = ~0ull;
-    for (int i = lane; i < n_cand; i += 32) {
-      const qre_candidate_t c = sc[i];
-      if (c.slot >= 0 && (bi < 0 || cand_better(c.sim, c.lru_seq, bs, bl))) {
-        bi = i; bs = c.sim; bl = c.lru_seq;
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float os = __shfl_xor_sync(kFull, bs, o);
-      const uint64_t ol = __shfl_xor_sync(kFull, bl, o);
-      const int oi = __shfl_xor_sync(kFull, bi, o);
-      if (oi >= 0 && (bi < 0 || cand_better(os, ol, bs, bl) || (os == bs && ol == bl && oi < bi))) {
-        bi = oi; bs = os; bl = ol;
-      }
-    }
-    const qre_candidate_t win = bi >= 0 ? sc[bi] : empty_cand();
-    if (k == 0) best0 = win;
-    __syncwarp();
-    if (lane == 0) {
-      if (a.out.cand != nullptr) a.out.cand[static_cast<long long>(q) * kTopK + k] = win;
-      if (bi >= 0) sc[bi].slot = -1;
-    }
-    __syncwarp();
-  }
-  if (lane == 0) {
-    const bool hit = best0.slot >= 0;
-    if (a.out.hit_slot) a.out.hit_slot[q] = hit ? best0.slot : -1;
-    if (a.out.hit_sim) a.out.hit_sim[q] = hit ? best0.sim : 0.f;
-    if (a.out.hit_pred_dev) a.out.hit_pred_dev[q] = hit ? static_cast<uint8_t>(best0.shard >> 24) : 0;
-    if (a.out.hit_pred_conf) a.out.hit_pred_conf[q] = hit ? best0.pred_conf : 0.0;
-    if (a.out.hit_shard) a.out.hit_shard[q] = hit ? (best0.shard & 0xFFFFFFu) : 0u;
-    if (a.out.flags) a.out.flags[q] = a.q_flags[q];
-  }
-  if (!a.do_route) return;
-
-  // ---- SemanticRouter: cosine to every centroid, Sim[dev] = max over owned centroids ----
+// The routing epilogue of one query (one warp): SemanticRouter cosine to every centroid with
+// Sim[dev] = max over owned centroids, TokenBasedRouter, HybridRouter.  Depends on the query and
+// its host features only — not on the cache scan — so the pipeline runs it at preparation time.
+__device__ __forceinline__ void route_query(const MergeArgs& a, int q, int lane, float* ds, double* S) {
   const int D = a.p.n_devices;
-  for (int d = lane; d < D; d += 32) s_dsim[warp][d] = -INFINITY;
+  for (int d = lane; d < D; d += 32) ds[d] = -INFINITY;
   __syncwarp();
   const float nq = a.q_norm[q];
   const float* qv = a.q_f32 + static_cast<long long>(q) * a.dim_pad;
@@ -672,17 +617,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
         const float sim = (nq < kNormEps || nc < kNormEps) ? 0.f : exact_sim(dot[u], nq, nc);   // qre:135-138
         if (a.out.centroid_sim) a.out.centroid_sim[static_cast<long long>(q) * a.n_centroids + k] = sim;
         const int o = a.cent_owner[k];
-        if (sim > s_dsim[warp][o]) s_dsim[warp][o] = sim;
+        if (sim > ds[o]) ds[o] = sim;
       }
     }
   }
   if (lane != 0) return;
-  const float* ds = s_dsim[warp];
-  double* S = s_S[warp];
 
   // TokenBasedRouter (qre:98-99)
   const int tok = a.tok[q], thr = a.p.token_threshold;
-  const int tok_dev = tok > thr ? 1 : 0;
+  const int tok_dev = (tok > thr && D > 1) ? 1 : 0;   // "orin" = device 1; a single-device set-up has only device 0
   const int den = thr > 1 ? thr : 1;
   const int diff = tok > thr ? tok - thr : thr - tok;
   double tok_conf = static_cast<double>(diff) / static_cast<double>(den);
@@ -730,7 +673,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   for (int d = 0; d < D; ++d) S[d] = 0.0;
   S[tok_dev] = __dadd_rn(S[tok_dev], __dmul_rn(a.p.w_token, tok_conf));
   S[sem_dev] = __dadd_rn(S[sem_dev], __dmul_rn(a.p.w_semantic, sem_conf));
-  const int hd = a.heur_dev[q];
+  int hd = a.heur_dev[q];
+  if (hd >= D) hd = D - 1;                            // header contract: heur_dev < n_devices; never index past S[D)
   S[hd] = __dadd_rn(S[hd], __dmul_rn(a.p.w_heuristic, a.heur_conf[q]));
   if (a.p.w_perf != 0.0)
     for (int d = 0; d < D; ++d) S[d] = __dadd_rn(S[d], __dmul_rn(a.p.w_perf, a.perf_health[d]));
@@ -755,6 +699,120 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   if (a.out.conf) a.out.conf[q] = conf;
   if (a.out.score)
     for (int d = 0; d < D; ++d) a.out.score[static_cast<long long>(q) * D + d] = S[d];
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) route_only_kernel(const MergeArgs a) {
+  __shared__ float s_dsim[kWarpsPerBlock][QRE_MAX_DEVICES];
+  __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * kWarpsPerBlock + warp;
+  if (q >= a.m) return;
+  route_query(a, q, lane, s_dsim[warp], s_S[warp]);
+}
+
+// Candidates live in registers (lane l holds candidates l, l+32, l+64, l+96): no shared-memory
+// staging, so blocks of this kernel fit beside a resident scan CTA.
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const MergeArgs a) {
+  __shared__ float s_dsim[kWarpsPerBlock][QRE_MAX_DEVICES];
+  __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * kWarpsPerBlock + warp;
+  if (a.wait_flags != nullptr) {
+    // Peer exchange: every rank's publish kernel stores its candidates into THIS GPU's buffer over
+    // NVLink and then raises its flag to the batch's epoch.  The publishers run on other GPUs, so
+    // this wait never depends on work queued behind it on this GPU.  Bounded: a dead peer must
+    // abort the job, not hang the box.
+    if (threadIdx.x < a.n_shards) {
+      const volatile uint32_t* f = a.wait_flags + threadIdx.x * 32;
+      const long long t0 = clock64();
+      // signed distance: a flag that has already moved past this epoch cannot hang the wait
+      while (static_cast<int32_t>(*f - a.wait_epoch) < 0) {
+        if (clock64() - t0 > 8000000000LL) {
+          printf("qre: peer %d never published epoch %u (saw %u)\n", threadIdx.x, a.wait_epoch, *f);
+          __trap();
+        }
+      }
+      __threadfence_system();
+    }
+    __syncthreads();
+  }
+  if (q >= a.m) return;
+
+  // ---- merge: n_shards * kTopK candidates, comparator (sim desc, lru asc) ----
+  const int n_cand = a.n_shards * kTopK;
+  qre_candidate_t c[kMergePerLane];
+#pragma unroll
+  for (int j = 0; j < kMergePerLane; ++j) {
+    const int i = lane + 32 * j;
+    c[j] = empty_cand();
+    if (i < n_cand) {
+      const int r = i / kTopK, k = i - r * kTopK;
+      const int4* src = reinterpret_cast<const int4*>(a.cand_all + static_cast<long long>(r) * a.shard_stride +
+                                                      static_cast<long long>(q) * kTopK + k);
+      int4* dst = reinterpret_cast<int4*>(&c[j]);    // read through L2: peers may have written it
+      dst[0] = __ldcg(src);
+      dst[1] = __ldcg(src + 1);
+    }
+  }
+  // Most queries have zero or one live candidate, and callers that do not ask for the merged
+  // list only need the winner: run only as many selection rounds as can produce something.
+  int n_valid = 0;
+#pragma unroll
+  for (int j = 0; j < kMergePerLane; ++j) n_valid += c[j].slot >= 0 ? 1 : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_valid += __shfl_xor_sync(kFull, n_valid, o);
+  const int want = a.out.cand != nullptr ? kTopK : 1;
+  const int rounds = n_valid < want ? n_valid : want;
+  if (a.out.cand != nullptr && lane >= rounds && lane < kTopK)
+    a.out.cand[static_cast<long long>(q) * kTopK + lane] = empty_cand();
+  qre_candidate_t best0 = empty_cand();
+  for (int k = 0; k < rounds; ++k) {
+    int bi = -1;
+    float bs = -INFINITY;
+    uint64_t bl = ~0ull;
+#pragma unroll
+    for (int j = 0; j < kMergePerLane; ++j) {
+      if (c[j].slot >= 0 && (bi < 0 || cand_better(c[j].sim, c[j].lru_seq, bs, bl))) {
+        bi = lane + 32 * j; bs = c[j].sim; bl = c[j].lru_seq;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float os = __shfl_xor_sync(kFull, bs, o);
+      const uint64_t ol = __shfl_xor_sync(kFull, bl, o);
+      const int oi = __shfl_xor_sync(kFull, bi, o);
+      if (oi >= 0 && (bi < 0 || cand_better(os, ol, bs, bl) || (os == bs && ol == bl && oi < bi))) {
+        bi = oi; bs = os; bl = ol;
+      }
+    }
+    // the winner's owner hands the record to lane 0 and retires it
+    const int owner = bi & 31, wj = bi >> 5;
+    qre_candidate_t win = empty_cand();
+#pragma unroll
+    for (int j = 0; j < kMergePerLane; ++j) {
+      if (j == wj) {
+        win.sim = __shfl_sync(kFull, c[j].sim, owner);
+        win.shard = __shfl_sync(kFull, c[j].shard, owner);
+        win.slot = __shfl_sync(kFull, c[j].slot, owner);
+        win.lru_seq = __shfl_sync(kFull, c[j].lru_seq, owner);
+        win.pred_conf = __shfl_sync(kFull, c[j].pred_conf, owner);
+        if (lane == owner) c[j].slot = -1;
+      }
+    }
+    if (k == 0) best0 = win;
+    if (lane == 0 && a.out.cand != nullptr) a.out.cand[static_cast<long long>(q) * kTopK + k] = win;
+  }
+  if (lane == 0) {
+    const bool hit = best0.slot >= 0;
+    if (a.out.hit_slot) a.out.hit_slot[q] = hit ? best0.slot : -1;
+    if (a.out.hit_sim) a.out.hit_sim[q] = hit ? best0.sim : 0.f;
+    if (a.out.hit_pred_dev) a.out.hit_pred_dev[q] = hit ? static_cast<uint8_t>(best0.shard >> 24) : 0;
+    if (a.out.hit_pred_conf) a.out.hit_pred_conf[q] = hit ? best0.pred_conf : 0.0;
+    if (a.out.hit_shard) a.out.hit_shard[q] = hit ? (best0.shard & 0xFFFFFFu) : 0u;
+    if (a.out.flags) a.out.flags[q] = a.q_flags[q];
+  }
+  if (!a.do_route) return;
+  route_query(a, q, lane, s_dsim[warp], s_S[warp]);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -799,12 +857,11 @@ int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, flo
   gather_rows_kernel<<<blocks_for_warps(n, 256), 256, 0, st>>>(n, slot_dev, s.rows_f32, s.dim, s.dim_pad, out);
   return 1;
 }
-int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src,
-                        uint64_t* q_ctx_dst, cudaStream_t st) {
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src, cudaStream_t st) {
   const int rows_total = ((m + kBM - 1) / kBM) * kBM;
+  DeviceState::Batch& b = s.cur();
   prep_queries_kernel<<<blocks_for_warps(rows_total, 256), 256, 0, st>>>(
-      m, rows_total, q_dev, s.dim, s.dim_pad, s.q_f32[s.slot], s.q_bf16, s.q_norm[s.slot], q_ctx_src, q_ctx_dst,
-      s.ovf_count);
+      m, rows_total, q_dev, s.dim, s.dim_pad, b.q_f32, b.q_bf16, b.q_norm, q_ctx_src, b.q_ctx, b.counters);
   return 1;
 }
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st) {
@@ -815,53 +872,61 @@ int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st) {
 int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& p, int shard,
                    qre_candidate_t* cand, cudaStream_t st) {
   const ScanGeometry g = plan_for(s, m, n_rows, p);
+  const DeviceState::Batch& b = s.cur();
   RescoreArgs a;
   a.m = m; a.splits = g.splits; a.dim_pad = s.dim_pad; a.shard = shard;
   const double thr = p.similarity_threshold > 0.0 ? p.similarity_threshold : 0.0;
   a.floor_v = static_cast<float>(thr) - kApproxEps;
   a.thr = p.similarity_threshold;
-  a.partial = s.partial; a.q_f32 = s.q_f32[s.slot]; a.q_norm = s.q_norm[s.slot]; a.rows_f32 = s.rows_f32;
+  a.partial = b.partial; a.spill_head = b.spill_head; a.spill_pool = b.spill_pool;
+  a.q_f32 = b.q_f32; a.q_norm = b.q_norm; a.rows_f32 = s.rows_f32;
   a.row_norm = s.row_norm; a.lru = s.lru; a.pdev = s.pred_dev; a.pconf = s.pred_conf; a.cand = cand;
-  a.q_flags = s.q_flags[s.slot];
-  a.ovf_count = s.ovf_count; a.ovf_list = s.ovf_list;
+  a.q_flags = b.q_flags;
+  a.ovf_count = b.ovf_count(); a.ovf_list = b.ovf_list;
   rescore_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
   return 1;
 }
 
-int launch_exact_scan(DeviceState& s, int m, long long n_rows, const uint64_t* q_ctx, const int32_t* qlist_dev,
+static ExactArgs exact_args(const DeviceState& s, long long n_rows, const qre_params_t& p) {
+  const DeviceState::Batch& b = s.cur();
+  ExactArgs a;
+  a.nq = 0; a.q_first = 0; a.qlist = nullptr; a.n_rows = n_rows; a.dim_pad = s.dim_pad;
+  a.thr = p.similarity_threshold; a.now_us = p.now_us; a.ttl_us = p.ttl_us; a.q_f32 = b.q_f32;
+  a.q_norm = b.q_norm; a.q_ctx = b.q_ctx; a.rows_f32 = s.rows_f32; a.row_norm = s.row_norm; a.meta = s.meta;
+  a.lru = s.lru; a.partial = nullptr;
+  return a;
+}
+
+int launch_exact_scan(DeviceState& s, int m, long long n_rows, const int32_t* qlist_dev,
                       int nq_total, bool mark_overflow, const qre_params_t& p, int shard, qre_candidate_t* cand,
                       cudaStream_t st) {
   (void)m;
-  const size_t smem = static_cast<size_t>(kExactGroup) * s.dim_pad * sizeof(float);   // <= 12 KB
+  const size_t smem = static_cast<size_t>(kExactGroup) * s.dim_pad * sizeof(float);   // <= 32 KB
   int launches = 0;
-  uint8_t* q_flags = s.q_flags[s.slot];
+  const DeviceState::Batch& b = s.cur();
   for (int g0 = 0; g0 < nq_total; g0 += kExactGroup) {
-    ExactArgs a;
+    ExactArgs a = exact_args(s, n_rows, p);
     a.nq = nq_total - g0 < kExactGroup ? nq_total - g0 : kExactGroup;
-    a.q_first = g0; a.qlist = qlist_dev; a.n_rows = n_rows; a.dim_pad = s.dim_pad;
-    a.thr = p.similarity_threshold; a.now_us = p.now_us; a.ttl_us = p.ttl_us; a.q_f32 = s.q_f32[s.slot];
-    a.q_norm = s.q_norm[s.slot]; a.q_ctx = q_ctx; a.rows_f32 = s.rows_f32; a.row_norm = s.row_norm; a.meta = s.meta;
-    a.lru = s.lru; a.partial = s.exact_partial;
+    a.q_first = g0; a.qlist = qlist_dev; a.partial = s.exact_partial;
     exact_scan_kernel<<<s.exact_grid, kExactWarps * 32, smem, st>>>(a);
     exact_reduce_kernel<<<1, kExactGroup * 32, 0, st>>>(a.nq, g0, qlist_dev, s.exact_grid, s.exact_partial, shard,
-                                                       s.pred_dev, s.pred_conf, s.q_norm[s.slot], cand, q_flags,
+                                                       s.pred_dev, s.pred_conf, b.q_norm, cand, b.q_flags,
                                                        mark_overflow ? QRE_FLAG_OVERFLOW : 0);
     launches += 2;
   }
   return launches;
 }
 
-int launch_overflow_settle(DeviceState& s, long long n_rows, const uint64_t* q_ctx, const qre_params_t& p, int shard,
+int launch_overflow_settle(DeviceState& s, long long n_rows, const qre_params_t& p, int shard,
                            qre_candidate_t* cand, cudaStream_t st) {
+  const DeviceState::Batch& b = s.cur();
   SettleArgs sa;
-  ExactArgs& a = sa.base;
-  a.nq = 0; a.q_first = 0; a.qlist = s.ovf_list; a.n_rows = n_rows; a.dim_pad = s.dim_pad;
-  a.thr = p.similarity_threshold; a.now_us = p.now_us; a.ttl_us = p.ttl_us; a.q_f32 = s.q_f32[s.slot];
-  a.q_norm = s.q_norm[s.slot]; a.q_ctx = q_ctx; a.rows_f32 = s.rows_f32; a.row_norm = s.row_norm; a.meta = s.meta;
-  a.lru = s.lru; a.partial = nullptr;
-  sa.ovf_count = s.ovf_count; sa.ovf_list = s.ovf_list; sa.unresolved = s.ovf_unresolved;
-  sa.tickets = s.settle_tickets; sa.partial = s.settle_partial; sa.shard = shard; sa.pdev = s.pred_dev;
-  sa.pconf = s.pred_conf; sa.cand = cand; sa.q_flags = s.q_flags[s.slot];
+  sa.base = exact_args(s, n_rows, p);
+  sa.base.qlist = b.ovf_list;
+  sa.ovf_count = b.ovf_count(); sa.ovf_list = b.ovf_list; sa.unresolved = b.ovf_unresolved();
+  sa.tickets = s.settle_tickets; sa.partial = s.settle_partial; sa.max_groups = s.settle_groups;
+  sa.shard = shard; sa.pdev = s.pred_dev;
+  sa.pconf = s.pred_conf; sa.cand = cand; sa.q_flags = b.q_flags;
   const size_t smem = static_cast<size_t>(kExactGroup) * s.dim_pad * sizeof(float);
   overflow_settle_kernel<<<s.exact_grid, kExactWarps * 32, smem, st>>>(sa);
   return 1;
@@ -873,8 +938,8 @@ int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_
                        uint32_t wait_epoch) {
   MergeArgs a;
   a.m = m; a.n_shards = n_shards; a.dim_pad = s.dim_pad; a.n_centroids = s.n_centroids;
-  a.do_route = p.do_route; a.cand_all = cand_all; a.q_f32 = s.q_f32[s.slot]; a.q_norm = s.q_norm[s.slot];
-  a.q_flags = s.q_flags[s.slot];
+  a.do_route = p.do_route; a.cand_all = cand_all; a.q_f32 = s.cur().q_f32; a.q_norm = s.cur().q_norm;
+  a.q_flags = s.cur().q_flags;
   a.centroids = s.centroids; a.cent_norm = s.cent_norm; a.cent_owner = s.cent_owner;
   a.perf_health = s.perf_health; a.tok = tok; a.heur_dev = heur_dev; a.heur_conf = heur_conf; a.p = p;
   a.out = out;
@@ -882,6 +947,20 @@ int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_
   a.wait_flags = wait_flags;
   a.wait_epoch = wait_epoch;
   merge_route_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
+  return 1;
+}
+
+int launch_route_only(DeviceState& s, int m, const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
+                      const qre_params_t& p, const qre_result_t& out, cudaStream_t st) {
+  MergeArgs a;
+  a.m = m; a.n_shards = 0; a.dim_pad = s.dim_pad; a.n_centroids = s.n_centroids;
+  a.do_route = 1; a.cand_all = nullptr; a.q_f32 = s.cur().q_f32; a.q_norm = s.cur().q_norm;
+  a.q_flags = s.cur().q_flags;
+  a.centroids = s.centroids; a.cent_norm = s.cent_norm; a.cent_owner = s.cent_owner;
+  a.perf_health = s.perf_health; a.tok = tok; a.heur_dev = heur_dev; a.heur_conf = heur_conf; a.p = p;
+  a.out = out;
+  a.shard_stride = 0; a.wait_flags = nullptr; a.wait_epoch = 0;
+  route_only_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
   return 1;
 }
 

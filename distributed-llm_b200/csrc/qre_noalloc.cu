@@ -88,7 +88,7 @@ struct Args {
 };
 
 __global__ void __launch_bounds__(kWarps * 32) exact_lookup_noalloc_kernel(const Args a) {
-  extern __shared__ float qs[];                       // [m, dim]
+  extern __shared__ __align__(16) float qs[];         // [m, dim], read back as float4
   __shared__ float s_nq[kMaxQ];
   __shared__ unsigned long long s_ctx[kMaxQ];
   __shared__ Best s_best[kWarps][kMaxQ];
@@ -240,6 +240,9 @@ extern "C" QRE_API int qre_exact_lookup_noalloc(
     return report(err, err_len, QRE_ERR_CAPACITY, "qre_exact_lookup_noalloc: n_rows must be in [0, 2^31-1]");
   if (!queries || !q_ctx || !hit_row || !hit_sim || (n_rows > 0 && (!rows || !row_ctx || !row_ts_us || !row_lru)))
     return report(err, err_len, QRE_ERR_INVALID, "qre_exact_lookup_noalloc: NULL array");
+  if (n_rows > 0 && (reinterpret_cast<uintptr_t>(rows) & 15u) != 0)
+    return report(err, err_len, QRE_ERR_INVALID,
+                  "qre_exact_lookup_noalloc: rows must be 16-byte aligned (rows are read as float4)");
   if (device < 0 || device >= kMaxGpus)
     return report(err, err_len, QRE_ERR_INVALID, "qre_exact_lookup_noalloc: device index out of range");
   int prev = -1;

@@ -32,7 +32,7 @@ EXPORTS = (
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
     "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
-    "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
+    "qre_submit_dev", "qre_wait_dev", "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
     # include/qre_encoder_b200.h
     "qre_encoder_create", "qre_encoder_destroy", "qre_encoder_set_embeddings", "qre_encoder_set_layer",
     "qre_encode", "qre_encode_dev", "qre_encoder_launch_count", "qre_encoder_debug_gemm",
@@ -323,6 +323,19 @@ class Shard:
             self.h, C.c_int(m), C.c_int(n_shards), C.c_void_p(cand_all_ptr), C.c_void_p(tok_ptr or None),
             C.c_void_p(heur_dev_ptr or None), C.c_void_p(heur_conf_ptr or None), C.byref(p), C.byref(res),
             C.c_void_p(stream)))
+
+    def submit_dev(self, slot, m, q_ptr, q_ctx_ptr, cfg: RouteConfig, now_us, out_ptrs: dict, tok_ptr=0,
+                   heur_dev_ptr=0, heur_conf_ptr=0, in_stream=0):
+        """qre_submit_dev: one batch through the library's own three-stream pipeline (slot 0/1)."""
+        p = cfg.to_c(now_us, bool(tok_ptr))
+        res = Result(**{f: C.c_void_p(out_ptrs.get(f, 0) or None) for f in RESULT_FIELDS})
+        _check(self.lib, self.lib.qre_submit_dev(
+            self.h, C.c_int(slot), C.c_int(m), C.c_void_p(q_ptr), C.c_void_p(q_ctx_ptr), C.c_void_p(tok_ptr or None),
+            C.c_void_p(heur_dev_ptr or None), C.c_void_p(heur_conf_ptr or None), C.byref(p), C.byref(res),
+            C.c_void_p(in_stream or None)))
+
+    def wait_dev(self, slot, stream=0):
+        _check(self.lib, self.lib.qre_wait_dev(self.h, C.c_int(slot), C.c_void_p(stream or None)))
 
     def profile(self, enable: bool) -> None:
         _check(self.lib, self.lib.qre_profile(self.h, C.c_int(1 if enable else 0)))

@@ -10,11 +10,13 @@ other disjoint subset; queries and per-query features are replicated.  Per batch
 torch is plumbing here: device buffers, streams and the NCCL collective.  With world == 1 the
 collective is skipped.  CPU tests drive `merge_candidates_host` over gloo instead.
 
-`step_pipelined` overlaps the exchange with compute: the all-gather + merge of batch i run on a
-side stream while the scan of batch i+1 runs on the main stream.  The scan kernel is persistent
-(one CTA per SM, all shared memory), so it leaves `reserve_sms` SMs free for the side stream's
-kernels; candidate buffers, outputs and the handle's per-batch query state are double-buffered
-(`pipeline_slot`).
+`step_pipelined` overlaps everything that is not the scan with the scans of the neighbouring
+batches.  With the peer exchange (or one GPU) that is the library's own pipeline (`qre_submit_dev`):
+query preparation of batch i+1 and re-score / publish / merge + route of batch i-1 run on the
+handle's auxiliary streams beside the scan of batch i.  With the NCCL exchange the all-gather +
+merge of batch i run on a side stream here.  The scan kernel is persistent (one CTA per SM, all
+shared memory), so it leaves `reserve_sms` SMs free for those kernels; candidate buffers, outputs
+and the handle's per-batch state are double-buffered (`pipeline_slot`).
 """
 from __future__ import annotations
 
@@ -45,6 +47,30 @@ def merge_candidates_host(cand_all: np.ndarray) -> np.ndarray:
         order = np.lexsort((np.arange(c.size), c["lru_seq"], -c["sim"].astype(np.float64), ~valid))
         out[q] = c[order[:k]]
     return out
+
+
+class _SlotDone:
+    """Completion of one pipelined batch (the handle's post-stream event for that slot)."""
+
+    def __init__(self, shard, slot):
+        self.shard, self.slot = shard, slot
+
+    def synchronize(self):
+        self.shard.wait_dev(self.slot, 0)
+
+    def wait(self, stream):
+        self.shard.wait_dev(self.slot, stream.cuda_stream or 1)
+
+
+class _EventDone:
+    def __init__(self, ev):
+        self.ev = ev
+
+    def synchronize(self):
+        self.ev.synchronize()
+
+    def wait(self, stream):
+        stream.wait_event(self.ev)
 
 
 class ShardedLookup:
@@ -121,21 +147,34 @@ class ShardedLookup:
         self.out = self._new_out(m)
 
     def step_pipelined(self, q, q_ctx, now_us: int, tok=None, heur_dev=None, heur_conf=None):
-        """Like `step`, but the exchange + merge of this batch are queued on a side stream so the
-        NEXT call's scan overlaps them.  Returns (outputs, event): the outputs are valid once
-        `event` has completed (`event.synchronize()` or `stream.wait_event(event)`)."""
+        """Like `step`, but only the scan of this batch occupies the handle's main stream; the rest
+        is queued beside the neighbouring batches' scans.  Inputs must be valid on the current torch
+        stream.  Returns (outputs, done): the outputs are valid once `done.synchronize()` returns
+        or after `done.wait(stream)` on that stream.  Alternate calls use alternate slots, so a
+        batch's outputs are overwritten by the call after the next one."""
         torch = self.torch
         m = q.shape[0]
         b = self.iter & 1
         self.iter += 1
-        if self.side is None:
-            self.side = torch.cuda.Stream(device=self.dev)
         if self.out2[b] is None or self.out2[b]["hit_slot"].shape[0] != m:
             self.out2[b] = self._new_out(m)
-        main = torch.cuda.current_stream(self.dev)
-        if self.done[b] is not None:
-            main.wait_event(self.done[b])            # slot b (batch i-2) fully consumed
+        out = self.out2[b]
+        ptrs = {f: t.data_ptr() for f, t in out.items() if not f.startswith("_")}
         cfg = self.cfg2[b]
+        main = torch.cuda.current_stream(self.dev)
+        if self.exchange == "p2p" or self.world == 1:
+            self.shard.submit_dev(b, m, q.data_ptr(), q_ctx.data_ptr(), cfg, now_us, ptrs,
+                                  tok_ptr=0 if tok is None else tok.data_ptr(),
+                                  heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
+                                  heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(),
+                                  in_stream=main.cuda_stream or 1)
+            self.done[b] = _SlotDone(self.shard, b)
+            return out, self.done[b]
+        # NCCL exchange: scan chain on the current stream, all-gather + merge on a side stream
+        if self.side is None:
+            self.side = torch.cuda.Stream(device=self.dev)
+        if self.done[b] is not None:
+            self.done[b].wait(main)                  # slot b (batch i-2) fully consumed
         nbytes = m * _cabi.TOPK * 32
         self.shard.scan_dev(m, q.data_ptr(), q_ctx.data_ptr(), cfg, now_us, self.rank,
                             self.cand2[b].data_ptr(), 0, main.cuda_stream or 1)
@@ -143,24 +182,18 @@ class ShardedLookup:
         scanned.record(main)
         self.side.wait_event(scanned)
         with torch.cuda.stream(self.side):
-            out = self.out2[b]
-            ptrs = {f: t.data_ptr() for f, t in out.items() if not f.startswith("_")}
-            extra = dict(tok_ptr=0 if tok is None else tok.data_ptr(),
-                         heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
-                         heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(), stream=self.side.cuda_stream)
-            if self.exchange == "p2p":
-                self.shard.publish_dev(m, self.cand2[b].data_ptr(), self.side.cuda_stream)
-                self.shard.merge_route_xchg_dev(m, cfg, now_us, ptrs, **extra)
-            else:
-                if self.world > 1:
-                    import torch.distributed as dist
-                    dist.all_gather_into_tensor(self.cand_all2[b][: self.world * nbytes], self.cand2[b][:nbytes],
-                                                group=self.group)
-                self.shard.merge_route_dev(m, self.world, self.cand_all2[b].data_ptr(), cfg, now_us, ptrs, **extra)
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self.cand_all2[b][: self.world * nbytes], self.cand2[b][:nbytes],
+                                        group=self.group)
+            self.shard.merge_route_dev(m, self.world, self.cand_all2[b].data_ptr(), cfg, now_us, ptrs,
+                                       tok_ptr=0 if tok is None else tok.data_ptr(),
+                                       heur_dev_ptr=0 if heur_dev is None else heur_dev.data_ptr(),
+                                       heur_conf_ptr=0 if heur_conf is None else heur_conf.data_ptr(),
+                                       stream=self.side.cuda_stream)
             ev = torch.cuda.Event()
             ev.record(self.side)
-        self.done[b] = ev
-        return out, ev
+        self.done[b] = _EventDone(ev)
+        return out, self.done[b]
 
     @staticmethod
     def split_sequences(m: int, world: int):
@@ -215,9 +248,9 @@ class ShardedLookup:
     def drain(self):
         """Make the current stream wait for every pipelined batch issued so far."""
         main = self.torch.cuda.current_stream(self.dev)
-        for ev in self.done:
-            if ev is not None:
-                main.wait_event(ev)
+        for d in self.done:
+            if d is not None:
+                d.wait(main)
 
     def step(self, q, q_ctx, now_us: int, tok=None, heur_dev=None, heur_conf=None, check_overflow=False):
         """q: float32 [m, dim] cuda tensor; q_ctx: int64 view of the u64 ids.  Enqueues on the

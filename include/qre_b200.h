@@ -41,7 +41,8 @@ enum {
   QRE_ERR_CUDA = 2,        /* a CUDA call failed; see qre_last_error() */
   QRE_ERR_CAPACITY = 3,    /* cache full / batch larger than max_batch */
   QRE_ERR_NO_DEVICE = 4,   /* no usable sm_100 device */
-  QRE_ERR_OVERFLOW = 5     /* candidate window overflow could not be resolved */
+  QRE_ERR_OVERFLOW = 5     /* candidate window overflow could not be resolved (no longer returned: every
+                              overflowed query is settled on the device; kept for ABI stability) */
 };
 
 #define QRE_TOPK 8                 /* candidates kept per query (per shard) */
@@ -60,8 +61,9 @@ enum {
 
 /* result flags (per query) */
 #define QRE_FLAG_ZERO_NORM   1     /* ||q|| < 1e-9: lookup returns miss (src/cache.py:284) */
-#define QRE_FLAG_OVERFLOW    2     /* candidate window overflowed; settled by the brute-force fp32 pass:
-                                      the winner is exact, but cand[] then lists the winner only */
+#define QRE_FLAG_OVERFLOW    2     /* the batch's spill pool ran out while this query still had contenders;
+                                      settled by the brute-force fp32 pass: the winner is exact, but cand[]
+                                      then lists the winner only */
 
 typedef struct qre_cache qre_cache_t;
 
@@ -115,6 +117,8 @@ typedef struct {
   double*  conf;            /* [m]      qre:406-407 */
   double*  score;           /* [m, D]   S[dev] — qre:389-398 */
   uint8_t* flags;           /* [m]      QRE_FLAG_* */
+  /* heur_dev[i] must be < n_devices (larger values are clamped to the last device); with
+   * n_devices == 1 the token router's "large" answer (device 1, qre:98) is clamped to device 0. */
 } qre_result_t;
 
 /* ---- library ------------------------------------------------------------------------- */
@@ -185,6 +189,23 @@ QRE_API int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float*
                                    const double* heur_conf, const qre_params_t* params);
 QRE_API int qre_lookup_route_end(qre_cache_t* h, int slot, qre_result_t* out);
 
+/* The whole pass on DEVICE pointers, pipelined inside the library (no reference counterpart: the
+ * reference handles one query at a time on the host; this is the call a device-resident producer,
+ * e.g. the on-GPU embedder, feeds).  qre_submit_dev enqueues one batch and returns: query
+ * preparation runs on an auxiliary stream of the handle, the tensor-core scan ALONE on the handle's
+ * main stream, and exact re-score, overflow settlement, the candidate exchange (when qre_xchg_* is
+ * connected: every rank then submits the same batch) and merge + routing on a third stream, so
+ * consecutive scans run back to back while the small kernels of the neighbouring batches run
+ * beside them (leave them room with params->reserve_sms).  Two slots: submit batch i on slot i & 1;
+ * a slot's previous batch is waited for on the device, not on the host.  The inputs must be valid
+ * on `in_stream` at the time of the call (NULL: already valid) and, like *out_dev's arrays, stay
+ * untouched until the batch has finished.  qre_wait_dev makes `stream` wait for the batch last
+ * submitted on `slot` (stream == NULL: blocks the host instead). */
+QRE_API int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries, const uint64_t* q_ctx,
+                           const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
+                           const qre_params_t* params, qre_result_t* out_dev, void* in_stream);
+QRE_API int qre_wait_dev(qre_cache_t* h, int slot, void* stream);
+
 /* Device-pointer pipeline, one stage per call (all enqueue on `stream`):
  *   qre_scan_dev   : queries -> this shard's exactly re-scored candidates cand[m, QRE_TOPK]
  *   (multi-GPU: all-gather cand over NCCL, e.g. torch.distributed.all_gather_into_tensor)
@@ -232,8 +253,10 @@ QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64
  * reads its local buffer.  Set-up: every rank calls qre_xchg_init (allocates its buffer, returns
  * a 64-byte IPC handle), the ranks exchange handles out of band (e.g. all_gather_object) and call
  * qre_xchg_connect once per peer.  Per batch: qre_scan_publish_dev then
- * qre_merge_route_xchg_dev, in that order, the same number of times on every rank; at most two
- * published batches may be waiting for their merge (two slots).  A peer that never publishes
+ * qre_merge_route_xchg_dev, in that order and on ONE stream, the same number of times on every
+ * rank: publish(e) must be followed by merge(e) before publish(e+1) (a second publish without the
+ * merge in between is rejected — a peer two batches ahead would otherwise overwrite lists a merge
+ * is still reading).  A peer that never publishes
  * makes the merge kernel trap after a few seconds instead of hanging.  Before destroying a
  * handle, synchronise all ranks (peers write into its buffer). */
 #define QRE_IPC_HANDLE_BYTES 64
@@ -276,7 +299,8 @@ QRE_API int qre_profile_read(qre_cache_t* h, double* scan_ms_total, int* n_launc
  * the library, which therefore occupies that much memory on every GPU that loads the library
  * until the process exits.  Limits: m <= QRE_NOALLOC_MAX_QUERIES, dim <= QRE_NOALLOC_MAX_DIM,
  * n_rows <= QRE_NOALLOC_MAX_ROWS; anything larger is rejected with QRE_ERR_CAPACITY and a
- * message in `err` (caller's buffer of err_len bytes, may be NULL).
+ * message in `err` (caller's buffer of err_len bytes, may be NULL); a `rows` pointer that is not
+ * 16-byte aligned is rejected with QRE_ERR_INVALID before anything is launched.
  * All calls on a device share the array and it keeps the previous call's contents (the part
  * that must be zero is cleared at the start of each call), so calls that overlap on the same
  * GPU race with each other: issue them one after another.  The first call on each device

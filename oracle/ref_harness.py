@@ -41,6 +41,22 @@ class FakeClock:
 
         return _DT
 
+    def make_ticking_datetime_class(self, step_us: int = 1250):
+        """For the orchestrator (router.py:159,170 time a device call with two `datetime.now()`
+        reads and feed the difference to the perf strategy): every read advances by a fixed step,
+        so a device call always 'takes' step_us and two replays see identical latencies."""
+        clock = self
+        ticks = [0]
+
+        class _TickDT(datetime):
+            @classmethod
+            def now(cls, tz=None):
+                ticks[0] += 1
+                t = clock.t + timedelta(microseconds=step_us * ticks[0])
+                return cls(t.year, t.month, t.day, t.hour, t.minute, t.second, t.microsecond)
+
+        return _TickDT
+
 
 def load_reference(clock: FakeClock | None = None):
     """Returns (cache_module, qre_module, stub_st_module) freshly imported from the reference."""
@@ -102,6 +118,7 @@ def load_reference_router(dropin_dir: str | None, clock: FakeClock | None = None
         dt = clock.make_datetime_class()
         cache.datetime = dt
         qre.datetime = dt
+        router.datetime = clock.make_ticking_datetime_class()   # device latency = a fixed tick, not wall clock
     for name in names:
         sys.modules.pop(name, None)
     return router, cache, qre, st

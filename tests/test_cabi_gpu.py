@@ -195,9 +195,10 @@ def test_lru_tie_break_and_ttl():
     sh.close()
 
 
-def test_overflow_falls_back_to_exact_scan():
+def test_more_contenders_than_the_list_holds_are_chained():
     """More than QRE_TOPK near-identical contenders in one row range: the bf16 window cannot
-    separate them, the exact fp32 scan must settle it (and pick the LRU-earliest of the best)."""
+    separate them; the ones that fall off the top-8 list are chained in spill chunks and re-scored
+    exactly, so the answer equals the brute-force scan's (LRU-earliest of the best) without it."""
     d = 384
     rs = np.random.Generator(np.random.PCG64(10))
     e = rs.standard_normal(d).astype(np.float32)
@@ -216,17 +217,42 @@ def test_overflow_falls_back_to_exact_scan():
     exp_row, exp_sim = O.scan_batch(q, np.array([7], np.uint64), img, 1, 10**9, 0.85)
     cfg_e = _cabi.RouteConfig(ttl_us=10**9, scan_mode=_cabi.SCAN_EXACT)
     out_e = sh.lookup_route(q, np.array([7], np.uint64), cfg_e, now_us=1)
-    assert out["flags"][0] & _cabi.FLAG_OVERFLOW
-    assert out["hit_slot"][0] == out_e["hit_slot"][0]
+    assert not (out["flags"][0] & _cabi.FLAG_OVERFLOW)
+    assert out["hit_slot"][0] == out_e["hit_slot"][0] == exp_row[0]
     assert out["hit_sim"][0] == out_e["hit_sim"][0]
     np.testing.assert_allclose(out["hit_sim"][0], exp_sim[0], rtol=REL)
     sh.close()
 
 
+def test_spill_pool_exhaustion_falls_back_to_exact_scan():
+    """20,000 copies of one embedding against a handle whose spill pool holds 15,360 candidates
+    (max_batch 8): the pool runs out, the query is flagged and the device-side brute-force pass
+    settles it — still the exact answer (the LRU-earliest copy), on the asynchronous path too."""
+    d, n = 384, 20000
+    rs = np.random.Generator(np.random.PCG64(21))
+    e = rs.standard_normal(d).astype(np.float32)
+    rows = np.repeat(e[None, :], n, axis=0)
+    ctx = np.full(n, 7, np.uint64)
+    lru = rs.permutation(n).astype(np.uint64) + np.uint64(5)
+    sh = _cabi.Shard(dim=d, capacity=n, max_batch=8)
+    sh.append(rows, ctx, np.zeros(n, np.int64), lru, np.zeros(n, np.uint8), np.ones(n))
+    q = np.stack([e, rs.standard_normal(d).astype(np.float32)])
+    qc = np.array([7, 7], np.uint64)
+    cfg = _cabi.RouteConfig(ttl_us=10**9)
+    out = sh.lookup_route(q, qc, cfg, now_us=1)
+    assert out["flags"][0] & _cabi.FLAG_OVERFLOW and not (out["flags"][1] & _cabi.FLAG_OVERFLOW)
+    assert out["hit_slot"].tolist() == [int(np.argmin(lru)), -1]
+    sh.lookup_route_begin(0, q, qc, cfg, 1)
+    sh.lookup_route_begin(1, q[::-1].copy(), qc, cfg, 1)
+    a, b = sh.lookup_route_end(0), sh.lookup_route_end(1)
+    assert a["hit_slot"].tolist() == [int(np.argmin(lru)), -1] and b["hit_slot"].tolist() == [-1, int(np.argmin(lru))]
+    sh.close()
+
+
 def test_config4_768d_64_centroids_16_devices_perf_term():
-    """BASELINE config 4 at oracle size: 768-d rows (streaming-A scan variant), 64 centroids owned
+    """BASELINE config 4 at 262,144 rows: 768-d rows (streaming-A scan variant), 64 centroids owned
     by 16 devices, perf health vector in the hybrid score."""
-    w = synth.make_workload(12000, 260, 768, n_centroids=64, n_devices=16, seed=8, frac_near=0.06, frac_dup=0.03)
+    w = synth.make_workload(262144, 260, 768, n_centroids=64, n_devices=16, seed=8, frac_near=0.06, frac_dup=0.03)
     sh = _load(w)
     cfg = _cabi.RouteConfig(ttl_us=w.ttl_us, n_devices=16, w_perf=0.1)
     out = sh.lookup_route(w.queries, w.q_ctx, cfg, w.now_us, tok=w.tok, heur_dev=w.heur_dev,
@@ -297,9 +323,9 @@ def test_pipelined_slots_single_gpu(small):
     sh.close()
 
 
-def test_many_overflowed_queries_settled_on_device():
-    """20 queries, each facing 12 near-identical rows: three groups of the device-side fallback;
-    the async device pipeline (no host check) must return the exact-scan answers on its own."""
+def test_many_queries_with_crowded_ranges():
+    """20 queries, each facing 12 near-identical rows (more than a list holds): chained candidates,
+    no brute-force pass; the async device pipeline must return the exact-scan answers on its own."""
     import torch
     from qre_b200.sharded import ShardedLookup
     d, nq, per = 384, 20, 12
@@ -317,7 +343,7 @@ def test_many_overflowed_queries_settled_on_device():
     qc = np.full(q.shape[0], 3, np.uint64)
     out_e = sh.lookup_route(q, qc, _cabi.RouteConfig(ttl_us=10**9, scan_mode=_cabi.SCAN_EXACT), now_us=1)
     out_t = sh.lookup_route(q, qc, _cabi.RouteConfig(ttl_us=10**9), now_us=1)
-    assert np.all(out_t["flags"][:nq] & _cabi.FLAG_OVERFLOW) and not np.any(out_t["flags"][nq:] & _cabi.FLAG_OVERFLOW)
+    assert not np.any(out_t["flags"] & _cabi.FLAG_OVERFLOW)
     assert np.array_equal(out_t["hit_slot"], out_e["hit_slot"]) and np.array_equal(out_t["hit_sim"], out_e["hit_sim"])
     assert np.all(out_e["hit_slot"][:nq] >= 0) and np.all(out_e["hit_slot"][nq:] == -1)
     dev = torch.device("cuda", 0)

@@ -5,7 +5,7 @@ size-independent properties — the oracle cannot scan 4 G pairs in seconds, so:
   * idempotence: the same batch twice gives identical outputs;
   * agreement of the two independent GPU paths (tensor-core scan vs brute-force exact scan) on a
     slice of the queries;
-  * the oracle itself on a 24-query slice against all 1M rows (vectorised form)."""
+  * the oracle itself on a 256-query slice against all 1M rows (vectorised form), lookup and routing."""
 import argparse
 
 import numpy as np
@@ -50,9 +50,24 @@ def test_config2_full_size_properties():
     img = O.CacheImage(rows, torch.cat([k[1] for k in kept]).cpu().numpy().view(np.uint64),
                        torch.cat([k[2] for k in kept]).cpu().numpy(),
                        torch.cat([k[3] for k in kept]).cpu().numpy().view(np.uint64))
-    s2 = slice(0, 24)
+    s2 = slice(0, 256)
     exp_row, exp_sim = O.scan_batch(wq["Q"][s2], q_ctx[s2], img, B.NOW_US, B.TTL_US, 0.85, chunk=131072)
     assert np.array_equal(out["hit_slot"][s2], exp_row)
     hit = exp_row >= 0
+    assert hit.sum() > 80
     np.testing.assert_allclose(out["hit_sim"][s2][hit], exp_sim[hit], rtol=1e-5)
+    r = O.route_batch(wq["Q"][s2], wq["tok"][s2], wq["heur_dev"][s2], wq["heur_conf"][s2], wq["cents"], wq["owner"],
+                      O.RouteParams(), np.zeros(2))
+    np.testing.assert_allclose(out["centroid_sim"][s2], r["sims"], rtol=1e-5, atol=1e-7)
+    assert float(np.mean(out["dev"][s2] == r["dev"])) > 0.99
+    np.testing.assert_allclose(out["score"][s2], r["S"], rtol=1e-5, atol=2e-6)
+    # the asynchronous two-slot host path on the full batch: identical to the synchronous call
+    sh.lookup_route_begin(0, wq["Q"], q_ctx, cfg, B.NOW_US, tok=wq["tok"], heur_dev=wq["heur_dev"],
+                          heur_conf=wq["heur_conf"])
+    sh.lookup_route_begin(1, wq["Q"], q_ctx, cfg, B.NOW_US, tok=wq["tok"], heur_dev=wq["heur_dev"],
+                          heur_conf=wq["heur_conf"])
+    for sl_ in (0, 1):
+        o3 = sh.lookup_route_end(sl_)
+        for k in out:
+            assert np.array_equal(out[k], o3[k]), (sl_, k)
     sh.close()

@@ -75,6 +75,35 @@ def test_low_thresholds_load_the_candidate_path(thr):
         assert (exp_row >= 0).mean() > 0.85
 
 
+@pytest.mark.parametrize("contiguous", [True, False])
+def test_clustered_cache_of_paraphrases(contiguous):
+    """What a semantic cache really holds: clusters of paraphrases.  300 clusters x 100 rows at
+    cosine 0.90-0.99 to their centre, every query a hit; with the clusters stored contiguously a
+    single row range holds ~100 contenders per query (far more than the top-8 list): the chained
+    candidates must give exactly the oracle's winner."""
+    d, n_cl, per, m = 384, 300, 100, 192
+    rs = np.random.Generator(np.random.PCG64(31))
+    centres = rs.standard_normal((n_cl, d)).astype(np.float32)
+    centres /= np.linalg.norm(centres, axis=1, keepdims=True)
+    cos = rs.uniform(0.90, 0.99, (n_cl, per))
+    rows = np.concatenate([synth.plant(np.repeat(centres[c][None, :], per, 0), cos[c], rs) for c in range(n_cl)])
+    rows = (rows * rs.uniform(0.5, 2.0, (rows.shape[0], 1))).astype(np.float32)
+    if not contiguous:
+        rows = rows[rs.permutation(rows.shape[0])]
+    qc = rs.integers(0, n_cl, m)
+    queries = synth.plant(centres[qc], rs.uniform(0.97, 0.999, m), rs).astype(np.float32)
+    w = synth.make_workload(rows.shape[0], m, d, n_centroids=2, seed=3, rows=rows, n_ctx=2, frac_expired=0.0,
+                            n_zero_q=0, n_zero_rows=0, frac_planted=0.0, frac_dup=0.0, frac_near=0.0)
+    w.queries[:] = queries
+    w.row_ctx[:] = synth.ctx_id(0)
+    w.q_ctx[:] = synth.ctx_id(0)
+    out = _run(w, 0.85)
+    exp_row, exp_sim = _oracle(w, 0.85)
+    assert (exp_row >= 0).mean() > 0.95
+    _compare(out, exp_row, exp_sim, w, 0.85)
+    assert not np.any(out["flags"] & _cabi.FLAG_OVERFLOW)
+
+
 def test_empty_cache_and_nan_queries():
     w = synth.make_workload(300, 16, 384, n_centroids=2, seed=5, n_ctx=2, frac_planted=0.9, n_zero_q=0)
     empty = synth.make_workload(0, 16, 384, n_centroids=2, seed=5, rows=np.zeros((0, 384), np.float32))

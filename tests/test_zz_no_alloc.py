@@ -1,4 +1,4 @@
-"""GPU: qre_exact_lookup_noalloc against the existing entry point (qre_lookup_route).
+"""GPU: qre_exact_lookup_noalloc against the existing entry point (qre_lookup_route) and the oracle.
 
 The no-allocation entry point exists for hosts that may not call cudaMalloc when a lookup
 arrives (all HBM already handed to their own pool, request threads that cannot absorb the
@@ -6,8 +6,8 @@ device-wide stall of an allocation, plugins confined to a host framework's alloc
 takes every array from the caller and keeps its scratch in a static device array inside the
 library, so this test owns all device memory itself (torch tensors stand in for the caller's
 pool) and only checks results: the hit row and score must equal what the handle-based entry
-point returns for the same cache and queries, to the tolerance the other parity tests use
-(identical decisions, scores within 1e-5 relative).
+point returns for the same cache and queries, and what the CPU oracle computes, to the tolerance
+the other parity tests use (identical decisions, scores within 1e-5 relative).
 
 Two calls in a row with different queries: the second call sees the scratch exactly as the
 first one left it, which is the situation the "clear what must start at zero" rule is about.
@@ -18,6 +18,7 @@ run every other test; it needs nothing from them and also passes alone in a fres
 import numpy as np
 import pytest
 
+from oracle import qre_oracle as O
 from qre_b200 import _cabi, synth
 
 pytestmark = pytest.mark.gpu
@@ -33,11 +34,13 @@ def _existing(w, queries, q_ctx):
     return out["hit_slot"], out["hit_sim"]
 
 
-def test_noalloc_matches_existing_entry_point_twice():
+@pytest.mark.parametrize("dim,m,own_stream", [(384, 8, False), (1024, 5, True), (384, 1, True)])
+def test_noalloc_matches_existing_entry_point_twice(dim, m, own_stream):
     import torch
     dev = torch.device("cuda", 0)
-    w = synth.make_workload(20000, 16, 384, n_centroids=2, seed=17, frac_planted=0.6, frac_near=0.1,
-                            frac_dup=0.1, n_zero_q=1, n_zero_rows=2)
+    w = synth.make_workload(20000 if dim == 384 else 6000, 16, dim, n_centroids=2, seed=17 + dim + m,
+                            frac_planted=0.6, frac_near=0.1, frac_dup=0.1, n_zero_q=1, n_zero_rows=2)
+    img = O.CacheImage(w.rows, w.row_ctx, w.row_ts_us, w.row_lru)
     # the caller's memory: everything the entry point reads or writes
     rows = torch.from_numpy(w.rows).to(dev)
     ctx = torch.from_numpy(w.row_ctx.view(np.int64)).to(dev)
@@ -45,23 +48,29 @@ def test_noalloc_matches_existing_entry_point_twice():
     lru = torch.from_numpy(w.row_lru.view(np.int64)).to(dev)
     hit_row = torch.full((8,), -7, dtype=torch.int64, device=dev)
     hit_sim = torch.full((8,), -7.0, dtype=torch.float32, device=dev)
+    st = torch.cuda.Stream(device=dev) if own_stream else None
     n_hits = 0
     for call in range(2):                                   # two calls in a row, different queries
-        q_np = np.ascontiguousarray(w.queries[call * 8:(call + 1) * 8])
-        c_np = np.ascontiguousarray(w.q_ctx[call * 8:(call + 1) * 8])
+        q_np = np.ascontiguousarray(w.queries[call * 8:call * 8 + m])
+        c_np = np.ascontiguousarray(w.q_ctx[call * 8:call * 8 + m])
         q = torch.from_numpy(q_np).to(dev)
         qc = torch.from_numpy(c_np.view(np.int64)).to(dev)
         torch.cuda.synchronize()
-        _cabi.exact_lookup_noalloc(0, rows.shape[0], 384, rows.data_ptr(), ctx.data_ptr(), ts.data_ptr(),
-                                   lru.data_ptr(), 8, q.data_ptr(), qc.data_ptr(), 0.85, w.now_us, w.ttl_us,
-                                   hit_row.data_ptr(), hit_sim.data_ptr())
+        _cabi.exact_lookup_noalloc(0, rows.shape[0], dim, rows.data_ptr(), ctx.data_ptr(), ts.data_ptr(),
+                                   lru.data_ptr(), m, q.data_ptr(), qc.data_ptr(), 0.85, w.now_us, w.ttl_us,
+                                   hit_row.data_ptr(), hit_sim.data_ptr(),
+                                   stream=st.cuda_stream if st is not None else 0)
         torch.cuda.synchronize()
         exp_row, exp_sim = _existing(w, q_np, c_np)
-        got_row, got_sim = hit_row.cpu().numpy(), hit_sim.cpu().numpy()
+        got_row, got_sim = hit_row.cpu().numpy()[:m], hit_sim.cpu().numpy()[:m]
         assert np.array_equal(got_row, exp_row), (call, got_row, exp_row)
         np.testing.assert_allclose(got_sim, exp_sim, rtol=REL)
+        # and the CPU restatement of src/cache.py:280-296 directly
+        o_row, o_sim = O.scan_batch(q_np, c_np, img, w.now_us, w.ttl_us, 0.85)
+        assert np.array_equal(got_row, o_row), (call, got_row, o_row)
+        np.testing.assert_allclose(got_sim[o_row >= 0], o_sim[o_row >= 0], rtol=REL)
         n_hits += int((exp_row >= 0).sum())
-    assert 4 <= n_hits <= 14        # both hits and misses were exercised
+    assert 1 <= n_hits <= 2 * m - (1 if m > 1 else 0)       # hits were exercised (and misses when m > 1)
 
 
 def test_noalloc_rejects_sizes_beyond_the_maximum():
@@ -79,3 +88,7 @@ def test_noalloc_rejects_sizes_beyond_the_maximum():
         _cabi.exact_lookup_noalloc(**{**args, "dim": 1028})
     with pytest.raises(_cabi.QreError, match="n_rows"):
         _cabi.exact_lookup_noalloc(**{**args, "n_rows": 2**31})
+    # a slice of a pool allocation that is not 16-byte aligned: an error code, not a device fault
+    with pytest.raises(_cabi.QreError, match="16-byte aligned"):
+        _cabi.exact_lookup_noalloc(**{**args, "rows_ptr": z.data_ptr() + 4})
+    torch.cuda.synchronize()
