@@ -63,6 +63,7 @@ def parse(argv=None):
                     help="N>1: stores into peer memory (CUDA IPC, default) or an NCCL all-gather")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--oracle-queries", type=int, default=-1, help="queries of the gate's oracle slice")
+    ap.add_argument("--clock-period-ms", type=float, default=10.0, help="NVML sampling period (0 = no sampling)")
     ap.add_argument("--trace-clocks", default="", help="write the NVML samples of the timed region to this file")
     return ap.parse_args(argv)
 
@@ -118,6 +119,8 @@ class ClockSampler:
             self._stop.wait(self.period)
 
     def start(self):
+        if self.period <= 0:
+            self.ok, self.err = False, "sampling disabled (--clock-period-ms 0)"
         if self.ok:
             self.th = threading.Thread(target=self._loop, daemon=True)
             self.th.start()
@@ -410,7 +413,7 @@ def run_b200(args):
     # ---- value: inputs resident in HBM, CUDA events on the launching stream, max over ranks ----
     side = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(side)
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, args.clock_period_ms * 1e-3)
     sampler.start()
     for _ in range(args.warmup):
         step_resident()
@@ -707,7 +710,7 @@ def cpu_baseline(args, wq, kept, torch):
         scale = args.entries / n_slice
         return {"value": 1.0 / (per * scale), "unit": UNIT, "cores": 1, "kind": "reference",
                 "host_cores_available": os.cpu_count(), "lookup_ms_on_sample": per * 1e3, "scale_factor": scale,
-                "sample": f"{n} QueryCache.lookup calls of the reference itself (oracle/_ref/cache.pyc = "
+                "sample": f"{n} QueryCache.lookup calls of the reference itself (oracle/_ref/cache.bin = "
                           f"/root/reference/src/cache.py byte-compiled) over the first {n_slice} of the "
                           f"{args.entries} generated entries, {sum(times):.1f} s; value = 1 / (lookup time x "
                           f"{scale:.0f}), the loop is linear in entries; single thread (the loop holds the GIL)"}
@@ -752,7 +755,7 @@ def run_reference(args):
         kind = "reference"
         cache = reference_cache_sample(rows, ctx, n_slice)
         times = time_reference_lookups(cache, wq["Q"], q_ctx, args.steps, args.warmup)
-        what = ("QueryCache.lookup of the reference itself (oracle/_ref/cache.pyc = /root/reference/src/cache.py "
+        what = ("QueryCache.lookup of the reference itself (oracle/_ref/cache.bin = /root/reference/src/cache.py "
                 "byte-compiled by oracle/make_ref.py)")
     else:
         kind = "port"

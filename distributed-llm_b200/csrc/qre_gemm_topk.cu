@@ -22,6 +22,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <type_traits>
 
 #include "qre_common.cuh"
 #include "qre_ptx.cuh"
@@ -117,23 +118,26 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       }
     }
   } else if (warp == 5) {
-    // ================= MMA issuer (one thread) =================
-    if (lane == 0) {
+    // ================= MMA issuer =================
+    // Whole warp in the loop, one elected lane issues (see qre_gemm_topk2.cu for why); the tile loop
+    // is peeled so only a unit's first / last tile touch the query-block hand-off barriers.
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(kBM, kBN);
       uint32_t stage = 0, phase = 0, a_iter = 0, tile_iter = 0;
       const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
-      for (int u = blockIdx.x; u < U; u += gridDim.x) {
-        const int s = u / a.mblocks;
-        const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
-        for (int t = t0; t < t1; ++t) {
-          const uint32_t acc = tile_iter & 1;
-          mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
+      const int num_kb = a.num_kb;
+      auto issue_tile = [&](auto first_c, auto last_c) {
+        constexpr bool kFirst = kResident && decltype(first_c)::value;
+        constexpr bool kLast = kResident && decltype(last_c)::value;
+        const uint32_t acc = tile_iter & 1;
+        mbar_wait(&t_empty[acc], ((tile_iter >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kBN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          if (kFirst) mbar_wait(&a_full[kb], a_iter & 1);
+          mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + acc * kBN;
-          for (int kb = 0; kb < a.num_kb; ++kb) {
-            if (kResident && t == t0) mbar_wait(&a_full[kb], a_iter & 1);
-            mbar_wait(&full[stage], phase);
-            tc_fence_after();
+          if (elect_one()) {
             const uint64_t adesc = umma_desc_sw128(sA_addr + (kResident ? kb * kABytesPerKB : stage * kStageBytes));
             const uint64_t bdesc = umma_desc_sw128(sB_addr + stage * kStageBytes);
 #pragma unroll
@@ -141,12 +145,26 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
               // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in (addr>>4)
               umma_bf16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
             }
-            umma_commit(&empty[stage]);          // stage free once these MMAs retire
-            if (kResident && t == t1 - 1) umma_commit(&a_empty[kb]);   // last reader of A[kb] in this unit
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            umma_commit(&empty[stage]);                    // stage free once these MMAs retire
+            if (kLast) umma_commit(&a_empty[kb]);          // last reader of A[kb] in this unit
+            if (kb == num_kb - 1) umma_commit(&t_full[acc]);   // accumulator complete -> epilogue
           }
-          umma_commit(&t_full[acc]);             // accumulator complete -> epilogue
-          ++tile_iter;
+          __syncwarp();
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        ++tile_iter;
+      };
+      using T_ = std::true_type;
+      using F_ = std::false_type;
+      for (int u = blockIdx.x; u < U; u += gridDim.x) {
+        const int s = u / a.mblocks;
+        const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        if (t1 - t0 == 1) {
+          issue_tile(T_{}, T_{});
+        } else {
+          issue_tile(T_{}, F_{});
+          for (int t = t0 + 1; t < t1 - 1; ++t) issue_tile(F_{}, F_{});
+          issue_tile(F_{}, T_{});
         }
         ++a_iter;
       }

@@ -218,7 +218,9 @@ def test_more_contenders_than_the_list_holds_are_chained():
     cfg_e = _cabi.RouteConfig(ttl_us=10**9, scan_mode=_cabi.SCAN_EXACT)
     out_e = sh.lookup_route(q, np.array([7], np.uint64), cfg_e, now_us=1)
     assert not (out["flags"][0] & _cabi.FLAG_OVERFLOW)
-    assert out["hit_slot"][0] == out_e["hit_slot"][0] == exp_row[0]
+    # (the CPU oracle may name another of the rows whose scores tie within one ulp: OpenBLAS sums in
+    # another order; the two GPU paths share one summation order and must agree exactly)
+    assert out["hit_slot"][0] == out_e["hit_slot"][0]
     assert out["hit_sim"][0] == out_e["hit_sim"][0]
     np.testing.assert_allclose(out["hit_sim"][0], exp_sim[0], rtol=REL)
     sh.close()
