@@ -228,28 +228,37 @@ qre_enc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       }
     }
   } else if (warp == kEpiWarps + 1) {
-    // ================= MMA issuer: one thread of the leader CTA =================
-    if (leader && lane == 0) {
+    // ================= MMA issuer: this warp of the leader CTA =================
+    // All 32 lanes run the loop convergently and one elected lane issues: with warp-uniform control
+    // flow the descriptors live in uniform registers and each tcgen05.mma is a single predicated
+    // instruction.  (From a lone lane inside a divergent branch the compiler wraps every MMA in an
+    // elect / broadcast loop and the issuing thread, with only 384 tensor cycles per k-step to hide
+    // behind, becomes the limiter.)
+    if (leader) {
       constexpr uint32_t idesc = umma_idesc_bf16(2 * kEncBM, kEncBN);     // M = 256 across the pair
       uint32_t stage = 0, phase = 0, it = 0;
       const uint32_t s_addr = smem_u32(smem);
+      const int num_kb = a.num_kb;
       for (int j = 0; j < n_mine; ++j, ++it) {
         const uint32_t acc = it & 1;
         mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccStride;
-        for (int kb = 0; kb < a.num_kb; ++kb) {
+        for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint64_t adesc = umma_desc_sw128(s_addr + stage * kStageBytes);
-          const uint64_t bdesc = umma_desc_sw128(s_addr + stage * kStageBytes + kABytes);
+          if (elect_one()) {
+            const uint64_t adesc = umma_desc_sw128(s_addr + stage * kStageBytes);
+            const uint64_t bdesc = umma_desc_sw128(s_addr + stage * kStageBytes + kABytes);
 #pragma unroll
-          for (int k = 0; k < kEncBK / 16; ++k)
-            umma_bf16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit_pair(&empty[stage]);
+            for (int k = 0; k < kEncBK / 16; ++k)
+              umma_bf16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit_pair(&empty[stage]);
+            if (kb == num_kb - 1) umma_commit_pair(&t_full[acc]);
+          }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit_pair(&t_full[acc]);
       }
     }
   } else {
