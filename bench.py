@@ -57,6 +57,7 @@ def parse(argv=None):
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="N=1: skip the configs[3] / configs[4] sub-runs")
     ap.add_argument("--no-overlap", action="store_true", help="serialise prep / scan / re-score / merge")
+    ap.add_argument("--no-slices", action="store_true", help="N>1: every rank merges + routes all queries")
     ap.add_argument("--reserve-sms", type=int, default=-1,
                     help="SMs the scan leaves to the kernels running beside it (-1: 0, they share the SMs)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "nccl", "p2p"],
@@ -405,6 +406,17 @@ def run_b200(args):
                          f"max |sim - planted cos| = {sim_err:.2e}")
     n_or = args.oracle_queries if args.oracle_queries >= 0 else (32 if args.entries <= 2_000_000 else 8)
     oracle_rec = oracle_gate(args, wq, kept, out, rank, world, torch, n_or) if n_or > 0 else None
+    # N > 1: the timed path lets every rank merge + route only its own M/N queries (sliced results);
+    # the job's answer is the union of the slices, and each slice must equal the replicated pass above
+    sliced = pipelined and not args.no_slices and look.enable_slices(True)
+    q0, q1 = look.slice_range(M)
+    if sliced:
+        for _ in range(3):
+            o, done = look.step_pipelined(d_in["Q"], d_in["ctx"], NOW_US, d_in["tok"], d_in["hd"], d_in["hc"])
+        done.synchronize()
+        for k in ("hit_slot", "hit_shard", "hit_sim", "dev", "conf", "score", "sem_method", "flags"):
+            if not np.array_equal(o[k][q0:q1].cpu().numpy(), out[k][q0:q1]):
+                raise SystemExit(f"bench.py: sliced results differ from the replicated pass in '{k}' on rank {rank}")
     keep_for_cpu = kept if (world == 1 and rank == 0 and not args.no_cpu_baseline) else None
     if keep_for_cpu is None:
         kept = None
@@ -454,8 +466,12 @@ def run_b200(args):
     hq = dict(Q=h["Q"].numpy(), ctx=h["ctx"].numpy().view(np.uint64), tok=h["tok"].numpy(),
               hd=h["hd"].numpy(), hc=h["hc"].numpy())
 
+    import copy
+    cfg_h = copy.copy(cfg)
+    cfg_h.slice_results = 1 if sliced else 0     # rank r uploads and returns only its slice of the batch
+
     def begin(slot):
-        sh.lookup_route_begin(slot, hq["Q"], hq["ctx"], cfg, NOW_US, tok=hq["tok"], heur_dev=hq["hd"],
+        sh.lookup_route_begin(slot, hq["Q"], hq["ctx"], cfg_h, NOW_US, tok=hq["tok"], heur_dev=hq["hd"],
                               heur_conf=hq["hc"])
 
     def run_e2e(n):
@@ -468,9 +484,11 @@ def run_b200(args):
     e2e_ok = look.exchange == "p2p" or world == 1     # the library's own exchange is the peer-store one
     if e2e_ok:
         r = run_e2e(max(2, args.warmup))
-        d2h = int(sum(v.nbytes for v in r.values()))
-        assert np.array_equal(r["hit_slot"], hit_slot) and np.array_equal(r["dev"], out["dev"])
-        h2d = int(sum(v.numel() * v.element_size() for v in h.values()))
+        # bytes moved per step by the whole job: every rank reads back its full result block; with
+        # sliced results each input row is uploaded by exactly one rank, otherwise by all of them
+        d2h = int(sum(v.nbytes for v in r.values())) * world
+        assert np.array_equal(r["hit_slot"][q0:q1], hit_slot[q0:q1]) and np.array_equal(r["dev"][q0:q1], out["dev"][q0:q1])
+        h2d = int(sum(v.numel() * v.element_size() for v in h.values())) * (1 if sliced else world)
         barrier()
         t0 = time.perf_counter()
         run_e2e(args.steps)
@@ -522,7 +540,8 @@ def run_b200(args):
                         + ("(BASELINE.json configs[1])" if args.entries == 1_000_000 and args.dim == 384 else
                            "(BASELINE.json configs[2])" if args.entries == 10_000_000 else ""),
             "queries_per_batch": M, "cache_entries": args.entries, "dim": args.dim,
-            "parallelism": (f"row-sharded x{world}" if world > 1 else "single GPU") +
+            "parallelism": (f"row-sharded x{world}" + (", each rank merges + routes (and, end to end, uploads) its "
+                            f"own {q1 - q0}-query slice" if sliced else "") if world > 1 else "single GPU") +
                            (", prep / re-score / exchange / merge of the neighbouring batches on side streams "
                             f"beside the scan ({args.reserve_sms} SMs reserved)" if pipelined else ", serial chain") +
                            (", candidates exchanged by stores into peer memory (CUDA IPC)" if world > 1

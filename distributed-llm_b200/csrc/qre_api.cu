@@ -162,7 +162,7 @@ struct qre_cache {
     uint8_t* h_res = nullptr;          // pinned
     cudaEvent_t e_in = nullptr, e_done = nullptr;
     bool pending = false;
-    int m = 0;
+    int m = 0, q0 = 0, q1 = 0;           // [q0, q1): queries whose results this call returns
     qre_params_t p;
     ResultLayout L;
     const int32_t* d_tok = nullptr;
@@ -186,6 +186,11 @@ struct qre_cache {
   // [2][world][32] uint32 flags; mapped into every peer process with CUDA IPC
   uint8_t* xchg = nullptr;
   size_t xchg_flags_off = 0;
+  // input exchange of the host-buffer path: [2 slots]{queries fp32 [max_batch, dim], ctx [max_batch]},
+  // per-rank arrival flags [2][world][32]; same allocation, same offsets on every rank
+  size_t xin_flags_off = 0, xin_off = 0, xin_slot_bytes = 0, xin_ctx_off = 0;
+  uint32_t xin_epoch = 0;
+  unsigned* xin_ticket = nullptr;
   int xchg_world = 0, xchg_rank = 0;
   uint8_t* xchg_peer[16] = {};
   bool xchg_open[16] = {};
@@ -769,27 +774,29 @@ static bool is_pinned_host(const void* p) {
 }
 
 static void scatter_results(const qre_cache_t::HostSlot& S, int K, int D, qre_result_t* out) {
-  const int m = S.m;
+  const size_t q0 = (size_t)S.q0, n = (size_t)(S.q1 - S.q0);      // sliced results: only this rank's share
   const qre_result_t hres = S.L.view(S.h_res);
-#define QRE_OUT(field, bytes) \
-  if (out->field) memcpy(out->field, hres.field, (bytes))
-  QRE_OUT(hit_slot, sizeof(int64_t) * m);
-  QRE_OUT(hit_sim, sizeof(float) * m);
-  QRE_OUT(hit_pred_dev, (size_t)m);
-  QRE_OUT(hit_pred_conf, sizeof(double) * m);
-  QRE_OUT(hit_shard, sizeof(uint32_t) * m);
-  QRE_OUT(cand, sizeof(qre_candidate_t) * m * QRE_TOPK);
-  QRE_OUT(flags, (size_t)m);
+#define QRE_OUT(field, elem_bytes)                                                                 \
+  if (out->field && n)                                                                             \
+  memcpy(reinterpret_cast<uint8_t*>(out->field) + q0 * (elem_bytes),                               \
+         reinterpret_cast<const uint8_t*>(hres.field) + q0 * (elem_bytes), n * (elem_bytes))
+  QRE_OUT(hit_slot, sizeof(int64_t));
+  QRE_OUT(hit_sim, sizeof(float));
+  QRE_OUT(hit_pred_dev, 1);
+  QRE_OUT(hit_pred_conf, sizeof(double));
+  QRE_OUT(hit_shard, sizeof(uint32_t));
+  QRE_OUT(cand, sizeof(qre_candidate_t) * QRE_TOPK);
+  QRE_OUT(flags, 1);
   if (S.p.do_route) {
-    QRE_OUT(centroid_sim, sizeof(float) * (size_t)m * K);
-    QRE_OUT(tok_dev, (size_t)m);
-    QRE_OUT(tok_conf, sizeof(double) * m);
-    QRE_OUT(sem_dev, (size_t)m);
-    QRE_OUT(sem_conf, sizeof(double) * m);
-    QRE_OUT(sem_method, (size_t)m);
-    QRE_OUT(dev, (size_t)m);
-    QRE_OUT(conf, sizeof(double) * m);
-    QRE_OUT(score, sizeof(double) * (size_t)m * D);
+    QRE_OUT(centroid_sim, sizeof(float) * (size_t)K);
+    QRE_OUT(tok_dev, 1);
+    QRE_OUT(tok_conf, sizeof(double));
+    QRE_OUT(sem_dev, 1);
+    QRE_OUT(sem_conf, sizeof(double));
+    QRE_OUT(sem_method, 1);
+    QRE_OUT(dev, 1);
+    QRE_OUT(conf, sizeof(double));
+    QRE_OUT(score, sizeof(double) * (size_t)D);
   }
 #undef QRE_OUT
 }
@@ -805,11 +812,18 @@ int qre_xchg_init(qre_cache_t* h, int world, int rank, uint8_t* handle_out) {
   DeviceGuard guard(h->s.device);
   const size_t lists = sizeof(qre_candidate_t) * 2 * (size_t)world * xchg_list_records(h);
   h->xchg_flags_off = align_up(lists, 256);
-  const size_t total = h->xchg_flags_off + sizeof(uint32_t) * 2 * (size_t)world * 32;
+  const size_t flag_bytes = sizeof(uint32_t) * 2 * (size_t)world * 32;
+  h->xin_flags_off = h->xchg_flags_off + flag_bytes;
+  h->xin_off = align_up(h->xin_flags_off + flag_bytes, 256);
+  h->xin_ctx_off = align_up(sizeof(float) * (size_t)h->s.max_batch * h->s.dim, 256);
+  h->xin_slot_bytes = h->xin_ctx_off + align_up(sizeof(uint64_t) * (size_t)h->s.max_batch, 256);
+  const size_t total = h->xin_off + 2 * h->xin_slot_bytes;
   QRE_CUDA(cudaMalloc((void**)&h->xchg, total));
   QRE_CUDA(cudaMemset(h->xchg, 0, total));
-  QRE_CUDA(cudaMalloc((void**)&h->xchg_ticket, sizeof(unsigned)));
-  QRE_CUDA(cudaMemset(h->xchg_ticket, 0, sizeof(unsigned)));
+  QRE_CUDA(cudaMalloc((void**)&h->xchg_ticket, 2 * sizeof(unsigned)));
+  QRE_CUDA(cudaMemset(h->xchg_ticket, 0, 2 * sizeof(unsigned)));
+  h->xin_ticket = h->xchg_ticket + 1;
+  h->xin_epoch = 0;
   cudaIpcMemHandle_t ipc;
   QRE_CUDA(cudaIpcGetMemHandle(&ipc, h->xchg));
   memcpy(handle_out, &ipc, sizeof(ipc));
@@ -834,7 +848,14 @@ int qre_xchg_connect(qre_cache_t* h, int peer, const uint8_t* handle) {
   return QRE_OK;
 }
 
+static int publish_impl(qre_cache_t* h, int m, const qre_candidate_t* cand, void* stream, int per);
+
 int qre_publish_dev(qre_cache_t* h, int m, const qre_candidate_t* cand, void* stream) {
+  return publish_impl(h, m, cand, stream, 0);
+}
+
+// per > 0: peer p receives only the lists of queries [p * per, (p + 1) * per)
+static int publish_impl(qre_cache_t* h, int m, const qre_candidate_t* cand, void* stream, int per) {
   if (h == nullptr || cand == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
   if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "call qre_xchg_init / qre_xchg_connect first");
   if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
@@ -859,7 +880,7 @@ int qre_publish_dev(qre_cache_t* h, int m, const qre_candidate_t* cand, void* st
     dst[pr] = reinterpret_cast<qre_candidate_t*>(h->xchg_peer[pr]) + idx * xchg_list_records(h);
     flag[pr] = reinterpret_cast<uint32_t*>(h->xchg_peer[pr] + h->xchg_flags_off) + idx * 32;
   }
-  h->launches += launch_publish(m, h->xchg_world, cand, dst, flag, epoch, h->xchg_ticket, st);
+  h->launches += launch_publish(m, h->xchg_world, cand, dst, flag, epoch, h->xchg_ticket, st, per);
   QRE_CUDA(cudaGetLastError());
   return QRE_OK;
 }
@@ -875,9 +896,19 @@ int qre_scan_publish_dev(qre_cache_t* h, int m, const float* queries, const uint
   return qre_publish_dev(h, m, cand, stream);
 }
 
+static int merge_xchg_impl(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,
+                           const double* heur_conf, const qre_params_t* params, qre_result_t* out_dev,
+                           void* stream, int q0, int q1);
+
 int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,
                              const double* heur_conf, const qre_params_t* params, qre_result_t* out_dev,
                              void* stream) {
+  return merge_xchg_impl(h, m, tok, heur_dev, heur_conf, params, out_dev, stream, -1, -1);
+}
+
+static int merge_xchg_impl(qre_cache_t* h, int m, const int32_t* tok, const uint8_t* heur_dev,
+                           const double* heur_conf, const qre_params_t* params, qre_result_t* out_dev,
+                           void* stream, int q0, int q1) {
   if (h == nullptr || out_dev == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
   if (h->xchg == nullptr) return fail(QRE_ERR_INVALID, "exchange not initialised");
   if (h->xchg_merge_epoch >= h->xchg_pub_epoch) return fail(QRE_ERR_INVALID, "nothing published to merge");
@@ -896,7 +927,7 @@ int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const ui
                           (size_t)slot * h->xchg_world * 32;
   h->s.slot = params->pipeline_slot & 1;
   h->launches += launch_merge_route(h->s, m, h->xchg_world, lists, tok, heur_dev, heur_conf, *params, *out_dev, st,
-                                    (long long)xchg_list_records(h), flags, epoch);
+                                    (long long)xchg_list_records(h), flags, epoch, q0, q1);
   QRE_CUDA(cudaGetLastError());
   return QRE_OK;
 }
@@ -909,7 +940,7 @@ int qre_merge_route_xchg_dev(qre_cache_t* h, int m, const int32_t* tok, const ui
 // main stream (small batches are latency-bound: cross-stream hand-offs would only add to it).
 static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, const uint64_t* d_ctx,
                             const int32_t* d_tok, const uint8_t* d_hd, const double* d_hc, const qre_params_t& p_in,
-                            const qre_result_t& out_dev, cudaEvent_t in_ready, bool serial) {
+                            const qre_result_t& out_dev, cudaEvent_t in_ready, bool serial, bool scatter_inputs) {
   DeviceState& s = h->s;
   qre_params_t p = p_in;
   p.pipeline_slot = slot;
@@ -918,9 +949,40 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
   h->last_m = m;
   DeviceState::Batch& B = s.cur();
   cudaStream_t aux = serial ? s.stream : h->aux, post = serial ? s.stream : h->post;
+  const bool sharded = h->xchg != nullptr && h->xchg_world > 1;
+  // sliced results: this rank merges and routes queries [q0, q1) only
+  const bool sliced = sharded && p.slice_results != 0;
+  const int per = sliced ? (m + h->xchg_world - 1) / h->xchg_world : 0;
+  const int q0 = sliced ? std::min(m, h->xchg_rank * per) : 0;
+  const int q1 = sliced ? std::min(m, (h->xchg_rank + 1) * per) : m;
   if (in_ready) QRE_CUDA(cudaStreamWaitEvent(aux, in_ready, 0));
   if (h->post_used[slot]) QRE_CUDA(cudaStreamWaitEvent(aux, h->ev_post[slot], 0));
-  h->launches += launch_prep_queries(s, m, d_q, d_ctx, aux);
+  if (scatter_inputs && sliced) {
+    // only rows [q0, q1) of d_q / d_ctx were uploaded: store them into every rank's input buffer
+    // (NVLink) and prepare the batch from this rank's copy once all slices have arrived
+    for (int pr = 0; pr < h->xchg_world; ++pr)
+      if (h->xchg_peer[pr] == nullptr) return fail(QRE_ERR_INVALID, "peer %d is not connected", pr);
+    const uint32_t epoch = ++h->xin_epoch;
+    const size_t xs = (size_t)(epoch & 1u);
+    float* dq[16];
+    uint64_t* dc[16];
+    uint32_t* fl[16];
+    for (int pr = 0; pr < h->xchg_world; ++pr) {
+      uint8_t* base = h->xchg_peer[pr] + h->xin_off + xs * h->xin_slot_bytes;
+      dq[pr] = reinterpret_cast<float*>(base);
+      dc[pr] = reinterpret_cast<uint64_t*>(base + h->xin_ctx_off);
+      fl[pr] = reinterpret_cast<uint32_t*>(h->xchg_peer[pr] + h->xin_flags_off) + (xs * h->xchg_world + h->xchg_rank) * 32;
+    }
+    h->launches += launch_scatter_inputs(h->xchg_world, q0, q1, s.dim, d_q, d_ctx, dq, dc, fl, epoch, h->xin_ticket,
+                                         aux);
+    QRE_CUDA(cudaGetLastError());
+    const uint8_t* mine = h->xchg + h->xin_off + xs * h->xin_slot_bytes;
+    h->launches += launch_prep_queries(
+        s, m, reinterpret_cast<const float*>(mine), reinterpret_cast<const uint64_t*>(mine + h->xin_ctx_off), aux,
+        reinterpret_cast<const uint32_t*>(h->xchg + h->xin_flags_off) + xs * h->xchg_world * 32, h->xchg_world, epoch);
+  } else {
+    h->launches += launch_prep_queries(s, m, d_q, d_ctx, aux);
+  }
   QRE_CUDA(cudaGetLastError());
   qre_params_t p_merge = p;
   if (!serial) {
@@ -929,7 +991,7 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
     if (p.do_route) {
       // routing needs the prepared queries only: it runs on the aux stream beside the scan, and
       // the post stream's merge then fills in the lookup half of the results
-      h->launches += launch_route_only(s, m, d_tok, d_hd, d_hc, p, out_dev, aux);
+      h->launches += launch_route_only(s, m, d_tok, d_hd, d_hc, p, out_dev, aux, q0, q1);
       QRE_CUDA(cudaGetLastError());
       QRE_CUDA(cudaEventRecord(h->ev_route[slot], aux));
       p_merge.do_route = 0;
@@ -941,13 +1003,12 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
     QRE_CUDA(cudaEventRecord(h->ev_scan[slot], s.stream));
     QRE_CUDA(cudaStreamWaitEvent(post, h->ev_scan[slot], 0));
   }
-  const bool sharded = h->xchg != nullptr && h->xchg_world > 1;
   rc = rescore_enqueue(h, m, p, sharded ? h->xchg_rank : 0, B.cand, post);
   if (rc != QRE_OK) return rc;
   if (sharded) {
-    rc = qre_publish_dev(h, m, B.cand, post);
+    rc = publish_impl(h, m, B.cand, post, per);
     if (rc != QRE_OK) return rc;
-    rc = qre_merge_route_xchg_dev(h, m, d_tok, d_hd, d_hc, &p_merge, const_cast<qre_result_t*>(&out_dev), post);
+    rc = merge_xchg_impl(h, m, d_tok, d_hd, d_hc, &p_merge, const_cast<qre_result_t*>(&out_dev), post, q0, q1);
     if (rc != QRE_OK) return rc;
   } else {
     h->launches += launch_merge_route(s, m, 1, B.cand, d_tok, d_hd, d_hc, p_merge, out_dev, post);
@@ -976,7 +1037,8 @@ int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries, const 
     QRE_CUDA(cudaEventRecord(h->ev_in[slot], (cudaStream_t)in_stream));
     ready = h->ev_in[slot];
   }
-  return pipeline_enqueue(h, slot, m, queries, q_ctx, tok, heur_dev, heur_conf, *params, *out_dev, ready, false);
+  return pipeline_enqueue(h, slot, m, queries, q_ctx, tok, heur_dev, heur_conf, *params, *out_dev, ready, false,
+                          false);
 }
 
 int qre_wait_dev(qre_cache_t* h, int slot, void* stream) {
@@ -1014,29 +1076,53 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   // kernels read the inputs from, and write the results to, page-locked host memory directly.
   const bool zero_copy = m <= kBM;
   const bool direct = is_pinned_host(queries);
+  // Row-sharded cache with sliced results: this rank returns queries [q0, q1) and (large batches)
+  // uploads only that slice of every input array; the ranks exchange the query slices over NVLink.
+  const bool sharded = h->xchg != nullptr && h->xchg_world > 1;
+  const bool sliced = sharded && S.p.slice_results != 0;
+  const int per = sliced ? (m + h->xchg_world - 1) / h->xchg_world : 0;
+  S.q0 = sliced ? std::min(m, h->xchg_rank * per) : 0;
+  S.q1 = sliced ? std::min(m, (h->xchg_rank + 1) * per) : m;
+  const bool slice_up = sliced && !zero_copy;
+  const size_t u0 = slice_up ? (size_t)S.q0 : 0, un = slice_up ? (size_t)(S.q1 - S.q0) : (size_t)m;
   uint8_t* in_base = zero_copy ? S.h_in : S.d_in;      // pinned host memory is device-accessible (UVA)
   size_t o = 0;
-  auto put = [&](const void* src, size_t bytes, bool copy) -> uint8_t* {
+  struct Piece { size_t off, bytes; const void* direct_src; };
+  Piece pieces[5];
+  int n_pieces = 0;
+  // place one input array at the next offset; stage (and later upload) rows [u0, u0 + un) of it
+  auto put = [&](const void* src, size_t elem, bool copy) -> uint8_t* {
     uint8_t* d = in_base + o;
-    if (src && copy) memcpy(S.h_in + o, src, bytes);
-    o = align_up(o + bytes, 256);
+    if (src != nullptr) {
+      const size_t off = o + u0 * elem, bytes = un * elem;
+      if (copy && bytes) memcpy(S.h_in + off, static_cast<const uint8_t*>(src) + u0 * elem, bytes);
+      pieces[n_pieces++] = Piece{off, bytes, copy ? nullptr : static_cast<const uint8_t*>(src) + u0 * elem};
+    }
+    o = align_up(o + (size_t)m * elem, 256);
     return d;
   };
-  const size_t q_bytes = sizeof(float) * (size_t)m * s.dim;
-  const float* d_q = (const float*)put(queries, q_bytes, !direct);
+  const float* d_q = (const float*)put(queries, sizeof(float) * (size_t)s.dim, !direct);
   if (zero_copy && direct) d_q = queries;
-  const size_t small_off = o;
-  const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t) * (size_t)m, true);
-  S.d_tok = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m, true);
-  S.d_hd = put(heur_dev, (size_t)m, true);
-  S.d_hc = (const double*)put(heur_conf, sizeof(double) * (size_t)m, true);
+  const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t), true);
+  S.d_tok = (const int32_t*)put(tok, sizeof(int32_t), true);
+  S.d_hd = put(heur_dev, 1, true);
+  S.d_hc = (const double*)put(heur_conf, sizeof(double), true);
   if (!zero_copy) {
-    if (direct) {
-      QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, q_bytes, cudaMemcpyHostToDevice, h->h2d));
-      QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice,
-                               h->h2d));
+    if (!slice_up && !direct) {
+      QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, h->h2d));     // one copy of everything
+    } else if (!slice_up) {
+      // page-locked query matrix straight from the caller; the small arrays in one staged copy
+      QRE_CUDA(cudaMemcpyAsync(S.d_in, queries, pieces[0].bytes, cudaMemcpyHostToDevice, h->h2d));
+      const size_t small_off = align_up(pieces[0].bytes, 256);
+      if (o > small_off)
+        QRE_CUDA(cudaMemcpyAsync(S.d_in + small_off, S.h_in + small_off, o - small_off, cudaMemcpyHostToDevice,
+                                 h->h2d));
     } else {
-      QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, h->h2d));
+      for (int i = 0; i < n_pieces; ++i) {
+        if (pieces[i].bytes == 0) continue;
+        const void* src = pieces[i].direct_src ? pieces[i].direct_src : (const void*)(S.h_in + pieces[i].off);
+        QRE_CUDA(cudaMemcpyAsync(S.d_in + pieces[i].off, src, pieces[i].bytes, cudaMemcpyHostToDevice, h->h2d));
+      }
     }
     QRE_CUDA(cudaEventRecord(S.e_in, h->h2d));
   }
@@ -1046,7 +1132,7 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   uint8_t* res_base = zero_copy ? S.h_res : S.d_res;
   const qre_result_t dres = S.L.view(res_base);
   rc = pipeline_enqueue(h, slot, m, d_q, d_ctx, S.d_tok, S.d_hd, S.d_hc, S.p, dres, zero_copy ? nullptr : S.e_in,
-                        zero_copy);
+                        zero_copy, slice_up);
   if (rc != QRE_OK) return rc;
   if (zero_copy) {
     QRE_CUDA(cudaEventRecord(S.e_done, s.stream));

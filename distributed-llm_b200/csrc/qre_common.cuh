@@ -158,7 +158,11 @@ int launch_update_meta(DeviceState& s, long long n, const int64_t* slot_dev, con
                        cudaStream_t st);
 int launch_tombstone(DeviceState& s, long long n, const int64_t* slot_dev, cudaStream_t st);
 int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, float* out, cudaStream_t st);
-int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src, cudaStream_t st);
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src, cudaStream_t st,
+                        const uint32_t* wait_flags = nullptr, int n_wait = 0, uint32_t wait_epoch = 0);
+int launch_scatter_inputs(int world, int q0, int q1, int dim, const float* src_q, const uint64_t* src_ctx,
+                          float* const* dst_q, uint64_t* const* dst_ctx, uint32_t* const* flag, uint32_t epoch,
+                          unsigned* ticket, cudaStream_t st);
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st);
 int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const qre_params_t& p,
                      float* dump, long long dump_ld, long long dump_row0, int dump_n, cudaStream_t st);
@@ -177,12 +181,12 @@ int launch_overflow_settle(DeviceState& s, long long n_rows, const qre_params_t&
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
                        const qre_result_t& out, cudaStream_t st, long long shard_stride = 0,
-                       const uint32_t* wait_flags = nullptr, uint32_t wait_epoch = 0);
+                       const uint32_t* wait_flags = nullptr, uint32_t wait_epoch = 0, int q0 = -1, int q1 = -1);
 // The routing half of merge_route alone (needs only the prepared queries): the pipeline runs it
 // beside the scan instead of after it.
 int launch_route_only(DeviceState& s, int m, const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
-                      const qre_params_t& p, const qre_result_t& out, cudaStream_t st);
+                      const qre_params_t& p, const qre_result_t& out, cudaStream_t st, int q0 = -1, int q1 = -1);
 int launch_publish(int m, int world, const qre_candidate_t* cand, qre_candidate_t* const* dst, uint32_t* const* flag,
-                   uint32_t epoch, unsigned* ticket, cudaStream_t st);
+                   uint32_t epoch, unsigned* ticket, cudaStream_t st, int per = 0);
 
 }  // namespace qre

@@ -147,18 +147,36 @@ __global__ void gather_rows_kernel(long long n, const int64_t* slot, const float
 // Queries: fp32 copy (zero padded), |q|, and the L2-normalised bf16 operand of the scan.
 __global__ void prep_queries_kernel(int m, int rows_total, const float* q, int dim, int dim_pad, float* q_f32,
                                     __nv_bfloat16* q_bf16, float* q_norm, const uint64_t* q_ctx_src,
-                                    uint64_t* q_ctx_dst, uint32_t* counters) {
+                                    uint64_t* q_ctx_dst, uint32_t* counters, const uint32_t* wait_flags,
+                                    int n_wait, uint32_t wait_epoch) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (blockIdx.x == 0 && threadIdx.x < 4) counters[threadIdx.x] = 0u;   // spill bump, overflow counters
+  if (wait_flags != nullptr) {
+    // The batch's queries were uploaded in slices, one per rank, and stored into THIS GPU's input
+    // buffer by the ranks' scatter kernels: wait for every rank's flag (bounded, like the merge).
+    if (threadIdx.x < n_wait) {
+      const volatile uint32_t* f = wait_flags + threadIdx.x * 32;
+      const long long t0 = clock64();
+      while (static_cast<int32_t>(*f - wait_epoch) < 0) {
+        if (clock64() - t0 > 8000000000LL) {
+          printf("qre: rank %d never delivered its query slice for epoch %u (saw %u)\n", threadIdx.x, wait_epoch, *f);
+          __trap();
+        }
+      }
+      __threadfence_system();
+    }
+    __syncthreads();
+  }
   if (w >= rows_total) return;
-  if (lane == 0 && w < m) q_ctx_dst[w] = q_ctx_src[w];          // private copy for the scan
+  // (inputs may have been stored by peer GPUs: read them through L2, never from a stale L1 line)
+  if (lane == 0 && w < m) q_ctx_dst[w] = __ldcg(q_ctx_src + w);  // private copy for the scan
   float* dst = q_f32 + static_cast<long long>(w) * dim_pad;
   __nv_bfloat16* bdst = q_bf16 + static_cast<long long>(w) * dim_pad;
   float acc = 0.f;
   for (int i = lane * 4; i < dim_pad; i += 128) {
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (w < m && i < dim) x = *reinterpret_cast<const float4*>(q + static_cast<long long>(w) * dim + i);
+    if (w < m && i < dim) x = __ldcg(reinterpret_cast<const float4*>(q + static_cast<long long>(w) * dim + i));
     *reinterpret_cast<float4*>(dst + i) = x;
     acc = lane_fma4(x, x, acc);
   }
@@ -565,6 +583,7 @@ struct MergeArgs {
   const double* heur_conf;
   qre_params_t p;
   qre_result_t out;
+  int q0, q1;                        // queries [q0, q1) are handled by this launch (sliced results: one rank's share)
   long long shard_stride;            // records between consecutive shards' lists in cand_all
   const uint32_t* wait_flags;        // peer exchange: flags[shard * 32] must equal wait_epoch first
   uint32_t wait_epoch;
@@ -705,8 +724,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) route_only_kernel(const M
   __shared__ float s_dsim[kWarpsPerBlock][QRE_MAX_DEVICES];
   __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * kWarpsPerBlock + warp;
-  if (q >= a.m) return;
+  const int q = a.q0 + blockIdx.x * kWarpsPerBlock + warp;
+  if (q >= a.q1) return;
   route_query(a, q, lane, s_dsim[warp], s_S[warp]);
 }
 
@@ -716,7 +735,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
   __shared__ float s_dsim[kWarpsPerBlock][QRE_MAX_DEVICES];
   __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * kWarpsPerBlock + warp;
+  const int q = a.q0 + blockIdx.x * kWarpsPerBlock + warp;
   if (a.wait_flags != nullptr) {
     // Peer exchange: every rank's publish kernel stores its candidates into THIS GPU's buffer over
     // NVLink and then raises its flag to the batch's epoch.  The publishers run on other GPUs, so
@@ -736,7 +755,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const 
     }
     __syncthreads();
   }
-  if (q >= a.m) return;
+  if (q >= a.q1) return;
 
   // ---- merge: n_shards * kTopK candidates, comparator (sim desc, lru asc) ----
   const int n_cand = a.n_shards * kTopK;
@@ -857,13 +876,62 @@ int launch_gather_rows(DeviceState& s, long long n, const int64_t* slot_dev, flo
   gather_rows_kernel<<<blocks_for_warps(n, 256), 256, 0, st>>>(n, slot_dev, s.rows_f32, s.dim, s.dim_pad, out);
   return 1;
 }
-int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src, cudaStream_t st) {
+int launch_prep_queries(DeviceState& s, int m, const float* q_dev, const uint64_t* q_ctx_src, cudaStream_t st,
+                        const uint32_t* wait_flags, int n_wait, uint32_t wait_epoch) {
   const int rows_total = ((m + kBM - 1) / kBM) * kBM;
   DeviceState::Batch& b = s.cur();
   prep_queries_kernel<<<blocks_for_warps(rows_total, 256), 256, 0, st>>>(
-      m, rows_total, q_dev, s.dim, s.dim_pad, b.q_f32, b.q_bf16, b.q_norm, q_ctx_src, b.q_ctx, b.counters);
+      m, rows_total, q_dev, s.dim, s.dim_pad, b.q_f32, b.q_bf16, b.q_norm, q_ctx_src, b.q_ctx, b.counters,
+      wait_flags, n_wait, wait_epoch);
   return 1;
 }
+
+// Input exchange of the host-buffer path on a row-sharded cache: rank r uploaded queries
+// [q0, q1) only; this kernel stores them (and their context ids) into every rank's input
+// buffer over NVLink (plain stores) and then raises rank r's flag there.
+struct ScatterArgs {
+  int world, q0, q1, dim;
+  const float* src_q;            // [m, dim] layout; rows [q0, q1) valid
+  const uint64_t* src_ctx;       // [m]
+  float* dst_q[16];
+  uint64_t* dst_ctx[16];
+  uint32_t* flag[16];
+  uint32_t epoch;
+  unsigned* ticket;
+};
+
+__global__ void __launch_bounds__(256) scatter_inputs_kernel(const ScatterArgs a) {
+  __shared__ unsigned s_ticket;
+  const long long n4 = static_cast<long long>(a.q1 - a.q0) * a.dim / 4;     // dim % 8 == 0
+  const float4* src = reinterpret_cast<const float4*>(a.src_q + static_cast<long long>(a.q0) * a.dim);
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (int p = 0; p < a.world; ++p) {
+    float4* d = reinterpret_cast<float4*>(a.dst_q[p] + static_cast<long long>(a.q0) * a.dim);
+    for (long long i = tid; i < n4; i += nth) d[i] = src[i];
+    for (long long i = a.q0 + tid; i < a.q1; i += nth) a.dst_ctx[p][i] = a.src_ctx[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_ticket = atomicAdd(a.ticket, 1u);
+  __syncthreads();
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence_system();
+  if (threadIdx.x < a.world) *reinterpret_cast<volatile uint32_t*>(a.flag[threadIdx.x]) = a.epoch;
+  if (threadIdx.x == 0) *a.ticket = 0u;
+}
+
+int launch_scatter_inputs(int world, int q0, int q1, int dim, const float* src_q, const uint64_t* src_ctx,
+                          float* const* dst_q, uint64_t* const* dst_ctx, uint32_t* const* flag, uint32_t epoch,
+                          unsigned* ticket, cudaStream_t st) {
+  ScatterArgs a;
+  a.world = world; a.q0 = q0; a.q1 = q1; a.dim = dim; a.src_q = src_q; a.src_ctx = src_ctx; a.epoch = epoch;
+  a.ticket = ticket;
+  for (int p = 0; p < world; ++p) { a.dst_q[p] = dst_q[p]; a.dst_ctx[p] = dst_ctx[p]; a.flag[p] = flag[p]; }
+  scatter_inputs_kernel<<<16, 256, 0, st>>>(a);
+  return 1;
+}
+
 int launch_prep_centroids(DeviceState& s, int k, cudaStream_t st) {
   prep_centroids_kernel<<<blocks_for_warps(k, 128), 128, 0, st>>>(k, s.centroids, s.dim_pad, s.cent_norm);
   return 1;
@@ -935,7 +1003,7 @@ int launch_overflow_settle(DeviceState& s, long long n_rows, const qre_params_t&
 int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_t* cand_all, const int32_t* tok,
                        const uint8_t* heur_dev, const double* heur_conf, const qre_params_t& p,
                        const qre_result_t& out, cudaStream_t st, long long shard_stride, const uint32_t* wait_flags,
-                       uint32_t wait_epoch) {
+                       uint32_t wait_epoch, int q0, int q1) {
   MergeArgs a;
   a.m = m; a.n_shards = n_shards; a.dim_pad = s.dim_pad; a.n_centroids = s.n_centroids;
   a.do_route = p.do_route; a.cand_all = cand_all; a.q_f32 = s.cur().q_f32; a.q_norm = s.cur().q_norm;
@@ -946,12 +1014,15 @@ int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_
   a.shard_stride = shard_stride > 0 ? shard_stride : static_cast<long long>(m) * kTopK;
   a.wait_flags = wait_flags;
   a.wait_epoch = wait_epoch;
-  merge_route_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
+  a.q0 = q0 < 0 ? 0 : q0;
+  a.q1 = q1 < 0 || q1 > m ? m : q1;
+  const int nq = a.q1 - a.q0 > 0 ? a.q1 - a.q0 : 1;   // an empty slice still launches (it may have to wait for flags)
+  merge_route_kernel<<<(nq + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
   return 1;
 }
 
 int launch_route_only(DeviceState& s, int m, const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
-                      const qre_params_t& p, const qre_result_t& out, cudaStream_t st) {
+                      const qre_params_t& p, const qre_result_t& out, cudaStream_t st, int q0, int q1) {
   MergeArgs a;
   a.m = m; a.n_shards = 0; a.dim_pad = s.dim_pad; a.n_centroids = s.n_centroids;
   a.do_route = 1; a.cand_all = nullptr; a.q_f32 = s.cur().q_f32; a.q_norm = s.cur().q_norm;
@@ -960,7 +1031,10 @@ int launch_route_only(DeviceState& s, int m, const int32_t* tok, const uint8_t* 
   a.perf_health = s.perf_health; a.tok = tok; a.heur_dev = heur_dev; a.heur_conf = heur_conf; a.p = p;
   a.out = out;
   a.shard_stride = 0; a.wait_flags = nullptr; a.wait_epoch = 0;
-  route_only_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
+  a.q0 = q0 < 0 ? 0 : q0;
+  a.q1 = q1 < 0 || q1 > m ? m : q1;
+  if (a.q1 <= a.q0) return 0;
+  route_only_kernel<<<(a.q1 - a.q0 + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
   return 1;
 }
 
@@ -975,6 +1049,7 @@ struct PublishArgs {
   uint32_t* flag[16];            // per peer: my flag for this slot in that peer's buffer
   uint32_t epoch;
   unsigned* ticket;
+  int per;                       // sliced results: peer p only needs queries [p * per, (p + 1) * per); 0 = all
 };
 
 __global__ void __launch_bounds__(256) publish_kernel(const PublishArgs a) {
@@ -983,7 +1058,13 @@ __global__ void __launch_bounds__(256) publish_kernel(const PublishArgs a) {
   const int4* src = reinterpret_cast<const int4*>(a.cand);
   for (int p = 0; p < a.world; ++p) {
     int4* d = reinterpret_cast<int4*>(a.dst[p]);
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16;
+    long long i0 = 0, i1 = n16;
+    if (a.per > 0) {               // all-to-all of slices instead of an all-gather of whole lists
+      const long long q0 = static_cast<long long>(p) * a.per, q1 = q0 + a.per;
+      i0 = (q0 < a.m ? q0 : a.m) * kTopK * 2;
+      i1 = (q1 < a.m ? q1 : a.m) * kTopK * 2;
+    }
+    for (long long i = i0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < i1;
          i += static_cast<long long>(gridDim.x) * blockDim.x)
       d[i] = src[i];
   }
@@ -998,9 +1079,9 @@ __global__ void __launch_bounds__(256) publish_kernel(const PublishArgs a) {
 }
 
 int launch_publish(int m, int world, const qre_candidate_t* cand, qre_candidate_t* const* dst, uint32_t* const* flag,
-                   uint32_t epoch, unsigned* ticket, cudaStream_t st) {
+                   uint32_t epoch, unsigned* ticket, cudaStream_t st, int per) {
   PublishArgs a;
-  a.m = m; a.world = world; a.cand = cand; a.epoch = epoch; a.ticket = ticket;
+  a.m = m; a.world = world; a.cand = cand; a.epoch = epoch; a.ticket = ticket; a.per = per;
   for (int p = 0; p < world; ++p) { a.dst[p] = dst[p]; a.flag[p] = flag[p]; }
   publish_kernel<<<16, 256, 0, st>>>(a);
   return 1;

@@ -51,6 +51,7 @@ class Params(C.Structure):
         ("token_threshold", C.c_int32), ("w_token", C.c_double), ("w_semantic", C.c_double),
         ("w_heuristic", C.c_double), ("w_perf", C.c_double), ("sem_min_similarity", C.c_double),
         ("sem_margin_threshold", C.c_double), ("pipeline_slot", C.c_int32), ("reserve_sms", C.c_int32),
+        ("slice_results", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -123,12 +124,13 @@ class RouteConfig:
     scan_mode: int = SCAN_TENSOR
     pipeline_slot: int = 0
     reserve_sms: int = 0
+    slice_results: int = 0
 
     def to_c(self, now_us: int, do_route: bool) -> Params:
         return Params(self.similarity_threshold, int(now_us), int(self.ttl_us), self.scan_mode,
                       1 if do_route else 0, self.n_devices, self.token_threshold, self.w_token,
                       self.w_semantic, self.w_heuristic, self.w_perf, self.sem_min_similarity,
-                      self.sem_margin_threshold, self.pipeline_slot, self.reserve_sms)
+                      self.sem_margin_threshold, self.pipeline_slot, self.reserve_sms, self.slice_results, 0)
 
 
 class Shard:

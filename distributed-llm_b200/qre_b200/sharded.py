@@ -75,7 +75,7 @@ class _EventDone:
 
 class ShardedLookup:
     def __init__(self, shard: _cabi.Shard, cfg: _cabi.RouteConfig, rank: int = 0, world: int = 1,
-                 group=None, reserve_sms: int = 8, exchange: str = "nccl"):
+                 group=None, reserve_sms: int = 8, exchange: str = "nccl", slice_results: bool = False):
         import copy
         import torch
         self.torch = torch
@@ -124,6 +124,26 @@ class ShardedLookup:
             dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)     # every rank takes the same path
             if int(flag.item()) == 0:
                 self.exchange = "nccl"
+        # sliced results (pipelined peer-exchange path only): rank r merges + routes queries
+        # slice_range(m) and leaves the rest of the output arrays untouched
+        self.slice_results = False
+        self.enable_slices(slice_results)
+
+    def enable_slices(self, on: bool) -> bool:
+        """Switch sliced results on / off for the following `step_pipelined` calls (every rank must
+        switch at the same batch).  Returns whether slicing is now active."""
+        self.slice_results = bool(on) and self.exchange == "p2p" and self.world > 1
+        for c in self.cfg2:
+            c.slice_results = 1 if self.slice_results else 0
+        return self.slice_results
+
+    def slice_range(self, m: int):
+        """Queries [q0, q1) whose results this rank produces in `step_pipelined` (all of them unless
+        sliced results are enabled on a peer-exchange world)."""
+        if not self.slice_results:
+            return 0, m
+        per = (m + self.world - 1) // self.world
+        return min(m, self.rank * per), min(m, (self.rank + 1) * per)
 
     def _new_out(self, m: int):
         """Result tensors as views of ONE device buffer (`out["_blob"]`), so a caller that wants

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define QRE_ABI_VERSION 1
+#define QRE_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define QRE_API __attribute__((visibility("default")))
@@ -96,6 +96,15 @@ typedef struct {
                                        pass the same value; alternate it between batches to overlap the merge of
                                        batch i (another stream) with the scan of batch i+1.  0 otherwise. */
   int32_t reserve_sms;              /* SMs the scan leaves free for kernels running beside it (0 = none) */
+  int32_t slice_results;            /* Row-sharded cache (qre_xchg_* connected) only, through qre_submit_dev and
+                                       qre_lookup_route_begin / _end.  0: every rank merges and routes all m
+                                       queries (replicated results).  1: rank r merges and routes only queries
+                                       [r*per, min(m, (r+1)*per)), per = ceil(m / world) — the candidate
+                                       exchange becomes an all-to-all of slices, the output arrays stay m long
+                                       and only that slice of them is written, and the host-buffer call uploads
+                                       only that slice of the query matrix (the ranks exchange the slices over
+                                       NVLink).  Ignored without an exchange. */
+  int32_t reserved;                 /* 0 */
 } qre_params_t;
 
 /* Per-query outputs, struct-of-arrays.  Any pointer may be NULL (not wanted).

@@ -25,12 +25,12 @@ def test_header_symbols_all_exported():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(_cabi.EXPORTS) == names
-    assert lib.qre_abi_version() == 1
+    assert lib.qre_abi_version() == 2
 
 
 def test_struct_layout_matches_header():
     assert _cabi.CAND_DTYPE.itemsize == 32
-    assert ctypes.sizeof(_cabi.Params) == 8 * 3 + 4 * 4 + 8 * 6 + 4 * 2
+    assert ctypes.sizeof(_cabi.Params) == 8 * 3 + 4 * 4 + 8 * 6 + 4 * 4
     assert ctypes.sizeof(_cabi.Result) == 8 * len(_cabi.RESULT_FIELDS)
 
 
