@@ -88,6 +88,39 @@ def _worker(rank, world, port, ret):
         for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf"):
             ok = ok and np.array_equal(o[k].cpu().numpy(), serial[i][k])
     torch.cuda.synchronize()
+    # sliced results: each rank merges + routes only its own half of the batch; that half must equal
+    # the replicated answer, the other half of the output arrays stays untouched
+    assert look_p.enable_slices(True)
+    q0, q1 = look_p.slice_range(300)
+    ok = ok and (q0, q1) == ((0, 150) if rank == 0 else (150, 300))
+    handles = [look_p.step_pipelined(a, b, w.now_us, c, d, e) for a, b, c, d, e in ins + ins]
+    for i in (4, 5):
+        o, ev = handles[i]
+        ev.synchronize()
+        for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf", "score", "sem_method", "hit_pred_dev"):
+            ok = ok and np.array_equal(o[k][q0:q1].cpu().numpy(), serial[i % 3][k][q0:q1])
+    torch.cuda.synchronize()
+    # the host-buffer call on the sharded cache: every rank passes the whole batch, uploads only its
+    # slice (the ranks exchange the query slices over NVLink) and gets its slice of the results back
+    import copy
+    cfg_s = copy.copy(cfg)
+    cfg_s.slice_results = 1
+    for rep in range(2):
+        for sl_, pm in enumerate(perms[:2]):
+            sh.lookup_route_begin(sl_, w.queries[pm], w.q_ctx[pm], cfg_s, w.now_us, tok=w.tok[pm],
+                                  heur_dev=w.heur_dev[pm], heur_conf=w.heur_conf[pm])
+        for sl_ in range(2):
+            r_ = sh.lookup_route_end(sl_)
+            for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf", "score", "sem_method"):
+                ok = ok and np.array_equal(r_[k][q0:q1], serial[sl_][k][q0:q1])
+    # ... and with replicated results (every rank uploads and returns everything)
+    sh.lookup_route_begin(0, w.queries[perms[2]], w.q_ctx[perms[2]], cfg, w.now_us, tok=w.tok[perms[2]],
+                          heur_dev=w.heur_dev[perms[2]], heur_conf=w.heur_conf[perms[2]])
+    r_ = sh.lookup_route_end(0)
+    for k in ("hit_slot", "hit_sim", "hit_shard", "dev", "conf"):
+        ok = ok and np.array_equal(r_[k], serial[2][k])
+    look_p.enable_slices(False)
+    dist.barrier()
     # data-parallel embedding in front of the lookup: each rank embeds half of the sequences, one all-gather,
     # and the [m, hidden] matrix equals what a single encoder call over the whole batch produces, bit for bit
     from oracle import minilm_oracle as MO
