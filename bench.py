@@ -439,6 +439,7 @@ def run_b200(args):
     e0.record()
     for _ in range(args.steps):
         step_resident()
+    host_enqueue_ms = (time.perf_counter() - t_begin) * 1e3 / args.steps     # host time to queue one step
     if pipelined:
         look.drain()
     e1.record()
@@ -554,6 +555,7 @@ def run_b200(args):
         "clocks": clocks,
         "e2e": e2e,
         "gpu_launches": int(launches),
+        "host_enqueue_ms_per_step": host_enqueue_ms,
         "roofline": {
             "bound": "tensor", "kernel": scan_kernel_name(args), "achieved": achieved,
             "peak": peak, "unit": "TFLOP/s",

@@ -173,8 +173,11 @@ struct qre_cache {
   // The pipeline (qre_submit_dev / qre_lookup_route_begin): query preparation on `aux`, the scan
   // alone on the handle's main stream, re-score / settle / exchange / merge + route on `post`.
   cudaStream_t aux = nullptr, post = nullptr;
-  cudaEvent_t ev_in[2] = {}, ev_prep[2] = {}, ev_route[2] = {}, ev_scan[2] = {}, ev_post[2] = {};
-  bool post_used[2] = {false, false};
+  cudaEvent_t ev_in[2] = {};                                         // per API slot: inputs valid
+  cudaEvent_t ev_prep[kPipeSlots] = {}, ev_route[kPipeSlots] = {}, ev_scan[kPipeSlots] = {}, ev_post[kPipeSlots] = {};
+  bool post_used[kPipeSlots] = {};
+  uint64_t pipe_seq = 0;               // batches enqueued so far; batch i uses pipeline slot i % kPipeSlots
+  int api_ps[2] = {-1, -1};            // pipeline slot of the batch last submitted on each API slot
   size_t in_bytes = 0;
   size_t res_bytes = 0;
   int last_slot = 0;
@@ -186,8 +189,8 @@ struct qre_cache {
   // [2][world][32] uint32 flags; mapped into every peer process with CUDA IPC
   uint8_t* xchg = nullptr;
   size_t xchg_flags_off = 0;
-  // input exchange of the host-buffer path: [2 slots]{queries fp32 [max_batch, dim], ctx [max_batch]},
-  // per-rank arrival flags [2][world][32]; same allocation, same offsets on every rank
+  // input exchange of the host-buffer path: [kPipeSlots]{queries fp32 [max_batch, dim], ctx [max_batch]},
+  // per-rank arrival flags [kPipeSlots][world][32]; same allocation, same offsets on every rank
   size_t xin_flags_off = 0, xin_off = 0, xin_slot_bytes = 0, xin_ctx_off = 0;
   uint32_t xin_epoch = 0;
   unsigned* xin_ticket = nullptr;
@@ -330,7 +333,15 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     }                                 \
   } while (0)
 #define QRE_ALLOC(ptr, bytes) QRE_TRY([&]() -> int { QRE_CUDA(cudaMalloc((void**)&(ptr), (bytes))); return QRE_OK; }())
-  QRE_TRY([&]() -> int { QRE_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)); return QRE_OK; }());
+  // The scan's stream gets the highest priority, the streams of the small kernels that run beside it
+  // the lowest: when an SM frees up between two scans the block scheduler places the next scan's
+  // CTA (which needs nearly all of the SM's shared memory) before any queued small block.
+  int prio_least = 0, prio_greatest = 0;
+  QRE_TRY([&]() -> int {
+    QRE_CUDA(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    QRE_CUDA(cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_greatest));
+    return QRE_OK;
+  }());
   QRE_ALLOC(s.rows_f32, sizeof(float) * (size_t)capacity * dim_pad);
   QRE_ALLOC(s.rows_bf16, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad);
   QRE_ALLOC(s.row_norm, sizeof(float) * (size_t)capacity);
@@ -345,7 +356,7 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     const long long want = std::max<long long>(1024, 128LL * max_batch);     // ~1,900 chained candidates / query
     s.spill_cap = (uint32_t)std::min<long long>(want, 1LL << 22);            // <= 512 MB
   }
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < kPipeSlots; ++b) {
     DeviceState::Batch& B = s.batch[b];
     QRE_ALLOC(B.q_f32, sizeof(float) * (size_t)s.mb_pad * dim_pad);
     QRE_ALLOC(B.q_bf16, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad);
@@ -386,6 +397,8 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
       QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_in, cudaEventDisableTiming));
       QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_done, cudaEventDisableTiming));
       QRE_CUDA(cudaEventCreateWithFlags(&h->ev_in[b], cudaEventDisableTiming));
+    }
+    for (int b = 0; b < kPipeSlots; ++b) {
       QRE_CUDA(cudaEventCreateWithFlags(&h->ev_prep[b], cudaEventDisableTiming));
       QRE_CUDA(cudaEventCreateWithFlags(&h->ev_route[b], cudaEventDisableTiming));
       QRE_CUDA(cudaEventCreateWithFlags(&h->ev_scan[b], cudaEventDisableTiming));
@@ -393,14 +406,14 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     }
     QRE_CUDA(cudaStreamCreateWithFlags(&h->h2d, cudaStreamNonBlocking));
     QRE_CUDA(cudaStreamCreateWithFlags(&h->d2h, cudaStreamNonBlocking));
-    QRE_CUDA(cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking));
-    QRE_CUDA(cudaStreamCreateWithFlags(&h->post, cudaStreamNonBlocking));
+    QRE_CUDA(cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, prio_least));
+    QRE_CUDA(cudaStreamCreateWithPriority(&h->post, cudaStreamNonBlocking, prio_least));
     QRE_CUDA(cudaMemsetAsync(s.rows_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.meta, 0xFF, sizeof(RowMeta) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.perf_health, 0, sizeof(double) * QRE_MAX_DEVICES, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.settle_tickets, 0, sizeof(unsigned) * (size_t)s.settle_groups, s.stream));
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kPipeSlots; ++b) {
       QRE_CUDA(cudaMemsetAsync(s.batch[b].q_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.mb_pad * dim_pad, s.stream));
       QRE_CUDA(cudaMemsetAsync(s.batch[b].counters, 0, sizeof(uint32_t) * 4, s.stream));
       QRE_CUDA(cudaMemsetAsync(s.batch[b].q_flags, 0, (size_t)max_batch, s.stream));
@@ -418,7 +431,7 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     if (rc != QRE_OK) return rc;
     rc = make_tmap_bf16(enc, &s.tmap_eh, s.rows_bf16, (uint64_t)dim_pad, (uint64_t)s.cap_pad, kBK, kBN / 2);
     if (rc != QRE_OK) return rc;
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kPipeSlots; ++b) {
       rc = make_tmap_bf16(enc, &s.batch[b].tmap_q, s.batch[b].q_bf16, (uint64_t)dim_pad, (uint64_t)s.mb_pad, kBK,
                           kBM);
       if (rc != QRE_OK) return rc;
@@ -444,7 +457,7 @@ int qre_cache_destroy(qre_cache_t* h) {
                                  s.exact_partial, s.settle_tickets, s.settle_partial, s.centroids, s.cent_norm,
                                  s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in, h->hs[1].d_in,
                                  h->hs[0].d_res, h->hs[1].d_res, h->d_dump};
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < kPipeSlots; ++b) {
     DeviceState::Batch& B = s.batch[b];
     for (void* p : {(void*)B.q_f32, (void*)B.q_bf16, (void*)B.q_norm, (void*)B.q_ctx, (void*)B.q_flags,
                     (void*)B.partial, (void*)B.spill_head, (void*)B.spill_pool, (void*)B.counters,
@@ -458,9 +471,11 @@ int qre_cache_destroy(qre_cache_t* h) {
     if (h->hs[b].h_res) cudaFreeHost(h->hs[b].h_res);
     if (h->hs[b].e_in) cudaEventDestroy(h->hs[b].e_in);
     if (h->hs[b].e_done) cudaEventDestroy(h->hs[b].e_done);
-    for (cudaEvent_t e : {h->ev_in[b], h->ev_prep[b], h->ev_route[b], h->ev_scan[b], h->ev_post[b]})
-      if (e) cudaEventDestroy(e);
+    if (h->ev_in[b]) cudaEventDestroy(h->ev_in[b]);
   }
+  for (int b = 0; b < kPipeSlots; ++b)
+    for (cudaEvent_t e : {h->ev_prep[b], h->ev_route[b], h->ev_scan[b], h->ev_post[b]})
+      if (e) cudaEventDestroy(e);
   for (int pr = 0; pr < 16; ++pr)
     if (h->xchg_open[pr] && h->xchg_peer[pr]) cudaIpcCloseMemHandle(h->xchg_peer[pr]);
   if (h->xchg) cudaFree(h->xchg);
@@ -813,11 +828,12 @@ int qre_xchg_init(qre_cache_t* h, int world, int rank, uint8_t* handle_out) {
   const size_t lists = sizeof(qre_candidate_t) * 2 * (size_t)world * xchg_list_records(h);
   h->xchg_flags_off = align_up(lists, 256);
   const size_t flag_bytes = sizeof(uint32_t) * 2 * (size_t)world * 32;
+  const size_t xin_flag_bytes = sizeof(uint32_t) * kPipeSlots * (size_t)world * 32;
   h->xin_flags_off = h->xchg_flags_off + flag_bytes;
-  h->xin_off = align_up(h->xin_flags_off + flag_bytes, 256);
+  h->xin_off = align_up(h->xin_flags_off + xin_flag_bytes, 256);
   h->xin_ctx_off = align_up(sizeof(float) * (size_t)h->s.max_batch * h->s.dim, 256);
   h->xin_slot_bytes = h->xin_ctx_off + align_up(sizeof(uint64_t) * (size_t)h->s.max_batch, 256);
-  const size_t total = h->xin_off + 2 * h->xin_slot_bytes;
+  const size_t total = h->xin_off + kPipeSlots * h->xin_slot_bytes;
   QRE_CUDA(cudaMalloc((void**)&h->xchg, total));
   QRE_CUDA(cudaMemset(h->xchg, 0, total));
   QRE_CUDA(cudaMalloc((void**)&h->xchg_ticket, 2 * sizeof(unsigned)));
@@ -935,14 +951,25 @@ static int merge_xchg_impl(qre_cache_t* h, int m, const int32_t* tok, const uint
 // ---- the pipeline -----------------------------------------------------------------------------
 // One batch = prep (aux stream) -> scan (main stream, nothing else) -> re-score, settle, exchange,
 // merge + route (post stream).  `in_ready` (may be NULL) is an event after which the inputs are
-// valid.  Slot b's previous batch must have left the post stream before slot b's buffers are
-// overwritten: the aux stream waits for ev_post[b].  With `serial` everything is enqueued on the
-// main stream (small batches are latency-bound: cross-stream hand-offs would only add to it).
+// valid.  Batch i uses pipeline slot i % kPipeSlots; that slot's previous batch (i - 3) must have
+// left the post stream before its buffers are overwritten: the aux stream waits for its ev_post.
+// Three slots, not two, so that the chain "re-score + exchange + merge of batch i-1 -> prep of
+// batch i+1 -> scan of batch i+1" is NOT on the critical path: prep(i+1) only waits for batch
+// i-2, which finished a whole scan earlier (with two slots that chain had to fit under one
+// 250 us scan at 8 GPUs and left ~13 us gaps between scans).  The caller's output arrays belong
+// to the API slot (0 / 1): the routing kernel of a batch, which writes them early, additionally
+// waits for the batch previously submitted on the same API slot.  With `serial` everything is
+// enqueued on the main stream (small batches are latency-bound: cross-stream hand-offs would
+// only add to it).
 static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, const uint64_t* d_ctx,
                             const int32_t* d_tok, const uint8_t* d_hd, const double* d_hc, const qre_params_t& p_in,
                             const qre_result_t& out_dev, cudaEvent_t in_ready, bool serial, bool scatter_inputs) {
   DeviceState& s = h->s;
   qre_params_t p = p_in;
+  const int api_slot = slot;
+  const int prev_ps = h->api_ps[api_slot];                 // batch whose outputs this one overwrites
+  slot = (int)(h->pipe_seq++ % kPipeSlots);                // from here on: the pipeline slot
+  h->api_ps[api_slot] = slot;
   p.pipeline_slot = slot;
   s.slot = slot;
   h->last_slot = slot;
@@ -963,7 +990,7 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
     for (int pr = 0; pr < h->xchg_world; ++pr)
       if (h->xchg_peer[pr] == nullptr) return fail(QRE_ERR_INVALID, "peer %d is not connected", pr);
     const uint32_t epoch = ++h->xin_epoch;
-    const size_t xs = (size_t)(epoch & 1u);
+    const size_t xs = (size_t)slot;                        // same on every rank: they submit in lockstep
     float* dq[16];
     uint64_t* dc[16];
     uint32_t* fl[16];
@@ -991,6 +1018,8 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
     if (p.do_route) {
       // routing needs the prepared queries only: it runs on the aux stream beside the scan, and
       // the post stream's merge then fills in the lookup half of the results
+      if (prev_ps >= 0 && prev_ps != slot && h->post_used[prev_ps])
+        QRE_CUDA(cudaStreamWaitEvent(aux, h->ev_post[prev_ps], 0));
       h->launches += launch_route_only(s, m, d_tok, d_hd, d_hc, p, out_dev, aux, q0, q1);
       QRE_CUDA(cudaGetLastError());
       QRE_CUDA(cudaEventRecord(h->ev_route[slot], aux));
@@ -1044,10 +1073,11 @@ int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries, const 
 int qre_wait_dev(qre_cache_t* h, int slot, void* stream) {
   if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
   if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
-  if (!h->post_used[slot]) return QRE_OK;
+  const int ps = h->api_ps[slot];
+  if (ps < 0 || !h->post_used[ps]) return QRE_OK;
   DeviceGuard guard(h->s.device);
-  if (stream != nullptr) QRE_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_post[slot], 0));
-  else QRE_CUDA(cudaEventSynchronize(h->ev_post[slot]));
+  if (stream != nullptr) QRE_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_post[ps], 0));
+  else QRE_CUDA(cudaEventSynchronize(h->ev_post[ps]));
   return QRE_OK;
 }
 
@@ -1137,7 +1167,7 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
   if (zero_copy) {
     QRE_CUDA(cudaEventRecord(S.e_done, s.stream));
   } else {
-    QRE_CUDA(cudaStreamWaitEvent(h->d2h, h->ev_post[slot], 0));
+    QRE_CUDA(cudaStreamWaitEvent(h->d2h, h->ev_post[h->api_ps[slot]], 0));
     QRE_CUDA(cudaMemcpyAsync(S.h_res, S.d_res, S.L.total, cudaMemcpyDeviceToHost, h->d2h));
     QRE_CUDA(cudaEventRecord(S.e_done, h->d2h));
   }

@@ -19,6 +19,9 @@ constexpr int kMaxKBStream = 16;  // streaming-A variant: dim_pad <= 1024
 constexpr int kTopK = QRE_TOPK;
 constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 constexpr int kExactGroup = 8;        // queries per brute-force pass
+constexpr int kPipeSlots = 3;         // copies of the per-batch state: the pipeline keeps up to three batches
+                                      // in flight (prep of i+1, scan of i, re-score / merge of i-1) and a
+                                      // slot is reused only three batches later
 constexpr uint32_t kNoChunk = 0xFFFFFFFFu;    // empty spill chain
 constexpr uint32_t kChunkLost = 0xFFFFFFFEu;  // spill pool exhausted: this (query, range) lost candidates
 constexpr int kSpillPer = 15;         // candidates per spill chunk (128-byte chunks)
@@ -102,9 +105,10 @@ struct DeviceState {
   uint64_t* lru = nullptr;            // [capacity]
   uint8_t* pred_dev = nullptr;        // [capacity]
   double* pred_conf = nullptr;        // [capacity]
-  // Per-batch state.  Everything one in-flight batch reads or writes exists twice ("pipeline
-  // slots"): query preparation of batch i+1 and re-score / merge / routing of batch i-1 run on
-  // other streams beside the scan of batch i.
+  // Per-batch state.  Everything one in-flight batch reads or writes exists kPipeSlots times
+  // ("pipeline slots"): query preparation of batch i+1 and re-score / merge / routing of batch
+  // i-1 run on other streams beside the scan of batch i.  (The stage-per-call API addresses
+  // slots 0 / 1 through qre_params_t.pipeline_slot.)
   struct Batch {
     float* q_f32 = nullptr;             // [mb_pad, dim_pad]  zero padded fp32 queries
     __nv_bfloat16* q_bf16 = nullptr;    // [mb_pad, dim_pad]  L2-normalised bf16 operand of the scan
@@ -121,7 +125,7 @@ struct DeviceState {
     int32_t* ovf_count() const { return reinterpret_cast<int32_t*>(counters + 1); }
     int32_t* ovf_unresolved() const { return reinterpret_cast<int32_t*>(counters + 2); }
   };
-  Batch batch[2];
+  Batch batch[kPipeSlots];
   int slot = 0;
   Batch& cur() { return batch[slot]; }
   const Batch& cur() const { return batch[slot]; }
