@@ -36,7 +36,18 @@ from typing import Any, Dict, List, Optional, Tuple
 import numpy as np
 
 from qre_b200 import _cabi
-from qre_b200.engine import Engine
+from qre_b200.engine import Engine, ShardedEngine
+
+
+def _new_engine(config, capacity: int, max_batch: int = 64):
+    """Device store from a config dict: `gpus` = [i, j, ...] shards the rows over those GPUs (one
+    process drives them all), `gpu` = i (default 0) keeps everything on one."""
+    cfg = config or {}
+    gpus = list(cfg["gpus"]) if cfg.get("gpus") is not None else []
+    if len(gpus) > 1:
+        return ShardedEngine(capacity=capacity, devices=gpus, max_batch=max_batch)
+    return Engine(capacity=capacity, device=int(gpus[0]) if gpus else int(cfg.get("gpu", 0)), max_batch=max_batch)
+
 
 logger = logging.getLogger(__name__)
 
@@ -158,12 +169,14 @@ class QueryCache:
     Constructor and method signatures are the reference's (cache.py:210-217, 236, 328, 372,
     398, 426, 434, 471, 502).  Keyword-only extras: `engine` (share a device store with the
     router so lookup and routing fuse into one launch sequence), `device` (GPU index),
-    `max_batch` (largest `lookup_batch`)."""
+    `max_batch` (largest `lookup_batch`), `gpus` (list of GPU indices: the rows are sharded over
+    them and one process drives them all)."""
 
     def __init__(self, max_size: int = 100, ttl_seconds: int = 300, similarity_threshold: float = 0.85,
                  use_semantic: bool = True,
                  prediction_confidence_threshold: float = PREDICTION_CONFIDENCE_THRESHOLD, *,
-                 engine: Optional[Any] = None, device: int = 0, max_batch: int = 64):
+                 engine: Optional[Any] = None, device: int = 0, max_batch: int = 64,
+                 gpus: Optional[List[int]] = None):
         self.max_size = max_size
         self.ttl_seconds = ttl_seconds
         self.similarity_threshold = similarity_threshold
@@ -172,8 +185,8 @@ class QueryCache:
 
         self._store: "OrderedDict[str, CacheEntry]" = OrderedDict()
         self._lock = threading.RLock()
-        self._engine = engine if engine is not None else Engine(capacity=max(max_size, 1), device=device,
-                                                                max_batch=max_batch)
+        self._engine = engine if engine is not None else _new_engine(
+            {"gpus": gpus, "gpu": device}, max(max_size, 1), max_batch)
         self._slot_key: Dict[int, str] = {}          # device slot -> query_hash
         self._ctx_ids: Dict[str, int] = {}           # context_key -> u64 id the device compares
         self._seq = 0                                # LRU clock: larger = more recently used
@@ -570,6 +583,8 @@ class QueryCache:
         without embeddings."""
         self._evict_expired()
         with self._lock:
+            if getattr(self._engine, "n", 1) > 1:
+                raise _cabi.QreError("save_snapshot / load_snapshot work on a one-GPU cache; use save / load")
             if self._engine.shard is None:
                 raise _cabi.QreError("nothing on the device to snapshot")
             self._engine.shard.snapshot_save(path + ".rows")

@@ -181,6 +181,8 @@ struct qre_cache {
   size_t in_bytes = 0;
   size_t res_bytes = 0;
   int last_slot = 0;
+  qre_candidate_t* d_gather = nullptr;  // qre_group_lookup_route: [16][max_batch * QRE_TOPK] lists of the group
+  cudaEvent_t ev_group = nullptr;
   float* d_dump = nullptr;
   size_t dump_bytes = 0;
   int64_t launches = 0;
@@ -456,7 +458,7 @@ int qre_cache_destroy(qre_cache_t* h) {
   std::vector<void*> dev_ptrs = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf,
                                  s.exact_partial, s.settle_tickets, s.settle_partial, s.centroids, s.cent_norm,
                                  s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in, h->hs[1].d_in,
-                                 h->hs[0].d_res, h->hs[1].d_res, h->d_dump};
+                                 h->hs[0].d_res, h->hs[1].d_res, h->d_dump, h->d_gather};
   for (int b = 0; b < kPipeSlots; ++b) {
     DeviceState::Batch& B = s.batch[b];
     for (void* p : {(void*)B.q_f32, (void*)B.q_bf16, (void*)B.q_norm, (void*)B.q_ctx, (void*)B.q_flags,
@@ -478,6 +480,7 @@ int qre_cache_destroy(qre_cache_t* h) {
       if (e) cudaEventDestroy(e);
   for (int pr = 0; pr < 16; ++pr)
     if (h->xchg_open[pr] && h->xchg_peer[pr]) cudaIpcCloseMemHandle(h->xchg_peer[pr]);
+  if (h->ev_group) cudaEventDestroy(h->ev_group);
   if (h->xchg) cudaFree(h->xchg);
   if (h->xchg_ticket) cudaFree(h->xchg_ticket);
   if (h->h2d) cudaStreamDestroy(h->h2d);
@@ -1200,6 +1203,102 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
   int rc = qre_lookup_route_begin(h, 0, m, queries, q_ctx, tok, heur_dev, heur_conf, params);
   if (rc != QRE_OK) return rc;
   return qre_lookup_route_end(h, 0, out);
+}
+
+// ---- one process, several GPUs ---------------------------------------------------------------
+// The row-sharded lookup for a host that drives all GPUs of the box from ONE process (the
+// drop-in QueryCache with config["gpus"]): every handle scans and re-scores its rows for the
+// whole batch on its own GPU and stream, the per-shard candidate lists are copied to the first
+// handle's GPU (peer copies over NVLink), and the merge + routing kernel runs there over all of
+// them — the same kernel that merges the ranks' lists in the multi-process path.
+int qre_group_lookup_route(qre_cache_t* const* hs, int n_handles, int m, const float* queries,
+                           const uint64_t* q_ctx, const int32_t* tok, const uint8_t* heur_dev,
+                           const double* heur_conf, const qre_params_t* params, qre_result_t* out) {
+  if (hs == nullptr || out == nullptr || queries == nullptr || q_ctx == nullptr)
+    return fail(QRE_ERR_INVALID, "NULL argument");
+  if (n_handles < 1 || n_handles * QRE_TOPK > 128) return fail(QRE_ERR_INVALID, "n_handles out of range [1, 16]");
+  for (int i = 0; i < n_handles; ++i) {
+    if (hs[i] == nullptr) return fail(QRE_ERR_INVALID, "handle %d is NULL", i);
+    if (hs[i]->s.dim != hs[0]->s.dim) return fail(QRE_ERR_INVALID, "handle %d has another dimension", i);
+    if (m < 1 || m > hs[i]->s.max_batch)
+      return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d] of handle %d", m, hs[i]->s.max_batch, i);
+    if (hs[i]->hs[0].pending || hs[i]->hs[1].pending)
+      return fail(QRE_ERR_INVALID, "handle %d has asynchronous batches in flight", i);
+  }
+  qre_cache_t* h0 = hs[0];
+  int rc = validate_params(h0, params);
+  if (rc != QRE_OK) return rc;
+  if (params->do_route && (!tok || !heur_dev || !heur_conf))
+    return fail(QRE_ERR_INVALID, "do_route needs tok, heur_dev and heur_conf");
+  const int dim = h0->s.dim;
+  const size_t list_bytes = sizeof(qre_candidate_t) * (size_t)m * QRE_TOPK;
+  const size_t stride = (size_t)h0->s.max_batch * QRE_TOPK;
+  {
+    DeviceGuard g0(h0->s.device);
+    if (h0->d_gather == nullptr) {
+      QRE_CUDA(cudaMalloc((void**)&h0->d_gather, sizeof(qre_candidate_t) * 16 * stride));
+      QRE_CUDA(cudaEventCreateWithFlags(&h0->ev_group, cudaEventDisableTiming));
+    }
+  }
+  qre_params_t p = *params;
+  p.pipeline_slot = 0;
+  p.slice_results = 0;
+  const int32_t* d_tok0 = nullptr;
+  const uint8_t* d_hd0 = nullptr;
+  const double* d_hc0 = nullptr;
+  // ---- every shard: inputs in, prep + scan + exact re-score on its own stream, list to GPU 0 ----
+  for (int i = 0; i < n_handles; ++i) {
+    qre_cache_t* h = hs[i];
+    DeviceGuard guard(h->s.device);
+    qre_cache_t::HostSlot& S = h->hs[0];
+    size_t o = 0;
+    auto put = [&](const void* src, size_t bytes) -> uint8_t* {
+      uint8_t* d = S.d_in + o;
+      if (src) memcpy(S.h_in + o, src, bytes);
+      o = align_up(o + bytes, 256);
+      return d;
+    };
+    const float* d_q = (const float*)put(queries, sizeof(float) * (size_t)m * dim);
+    const uint64_t* d_ctx = (const uint64_t*)put(q_ctx, sizeof(uint64_t) * (size_t)m);
+    if (i == 0) {                                   // routing inputs are only read where the merge runs
+      d_tok0 = (const int32_t*)put(tok, sizeof(int32_t) * (size_t)m);
+      d_hd0 = put(heur_dev, (size_t)m);
+      d_hc0 = (const double*)put(heur_conf, sizeof(double) * (size_t)m);
+    }
+    cudaStream_t st = h->s.stream;
+    QRE_CUDA(cudaMemcpyAsync(S.d_in, S.h_in, o, cudaMemcpyHostToDevice, st));
+    h->s.slot = 0;
+    rc = scan_enqueue(h, m, d_q, d_ctx, p, i, h->s.batch[0].cand, st);
+    if (rc != QRE_OK) return rc;
+    if (i == 0) {
+      QRE_CUDA(cudaMemcpyAsync(h0->d_gather, h->s.batch[0].cand, list_bytes, cudaMemcpyDeviceToDevice, st));
+    } else {
+      QRE_CUDA(cudaMemcpyPeerAsync(h0->d_gather + (size_t)i * stride, h0->s.device, h->s.batch[0].cand,
+                                   h->s.device, list_bytes, st));
+      QRE_CUDA(cudaEventRecord(h->ev_scan[0], st));
+    }
+  }
+  // ---- GPU 0: merge the n lists per query, route, results out ----
+  DeviceGuard g0(h0->s.device);
+  DeviceState& s0 = h0->s;
+  qre_cache_t::HostSlot& S0 = h0->hs[0];
+  for (int i = 1; i < n_handles; ++i) QRE_CUDA(cudaStreamWaitEvent(s0.stream, hs[i]->ev_scan[0], 0));
+  S0.m = m; S0.p = p; S0.q0 = 0; S0.q1 = m;
+  const int K = p.do_route ? s0.n_centroids : 0;
+  const int D = p.do_route ? p.n_devices : 1;
+  S0.L.plan(m, K, D);
+  s0.slot = 0;
+  h0->launches += launch_merge_route(s0, m, n_handles, h0->d_gather, d_tok0, d_hd0, d_hc0, p, S0.L.view(S0.d_res),
+                                     s0.stream, (long long)stride);
+  QRE_CUDA(cudaGetLastError());
+  QRE_CUDA(cudaMemcpyAsync(S0.h_res, S0.d_res, S0.L.total, cudaMemcpyDeviceToHost, s0.stream));
+  QRE_CUDA(cudaStreamSynchronize(s0.stream));
+  scatter_results(S0, K, D, out);
+  for (int i = 1; i < n_handles; ++i) {              // nothing of this batch may be left in flight
+    DeviceGuard guard(hs[i]->s.device);
+    QRE_CUDA(cudaStreamSynchronize(hs[i]->s.stream));
+  }
+  return QRE_OK;
 }
 
 // ---- binary snapshot -----------------------------------------------------

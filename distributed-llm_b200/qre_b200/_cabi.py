@@ -32,7 +32,7 @@ EXPORTS = (
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
     "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
-    "qre_submit_dev", "qre_wait_dev", "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
+    "qre_submit_dev", "qre_wait_dev", "qre_group_lookup_route", "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
     # include/qre_encoder_b200.h
     "qre_encoder_create", "qre_encoder_destroy", "qre_encoder_set_embeddings", "qre_encoder_set_layer",
     "qre_encode", "qre_encode_dev", "qre_encoder_launch_count", "qre_encoder_debug_gemm",
@@ -395,6 +395,31 @@ class Shard:
         out = np.empty((m, n), np.float32)
         _check(self.lib, self.lib.qre_debug_gemm(self.h, C.c_int(m), C.c_int64(row0), C.c_int(n), _ptr(out)))
         return out
+
+
+def group_lookup_route(shards, queries, q_ctx, cfg: RouteConfig, now_us: int, tok=None, heur_dev=None,
+                       heur_conf=None, want_cand: bool = False) -> dict:
+    """qre_group_lookup_route over a list of `Shard`s (one per GPU, one process): the row-sharded
+    lookup + route with the merge on the first shard's GPU.  Same outputs as `Shard.lookup_route`;
+    `hit_shard` indexes `shards`."""
+    first = shards[0]
+    q = _arr(queries, np.float32)
+    m = q.shape[0]
+    if q.ndim != 2 or q.shape[1] != first.dim:
+        raise ValueError(f"queries must be [m, {first.dim}]")
+    q_ctx = _arr(q_ctx, np.uint64, (m,))
+    do_route = tok is not None
+    if do_route:
+        tok, heur_dev = _arr(tok, np.int32, (m,)), _arr(heur_dev, np.uint8, (m,))
+        heur_conf = _arr(heur_conf, np.float64, (m,))
+    out = first._host_outputs(m, do_route, cfg.n_devices, want_cand)
+    res = Result(**{f: _ptr(out.get(f)) for f in RESULT_FIELDS})
+    p = cfg.to_c(now_us, do_route)
+    hs = (C.c_void_p * len(shards))(*[s.h for s in shards])
+    _check(first.lib, first.lib.qre_group_lookup_route(hs, C.c_int(len(shards)), C.c_int(m), _ptr(q), _ptr(q_ctx),
+                                                       _ptr(tok), _ptr(heur_dev), _ptr(heur_conf), C.byref(p),
+                                                       C.byref(res)))
+    return out
 
 
 NOALLOC_MAX_QUERIES, NOALLOC_MAX_DIM = 8, 1024

@@ -138,3 +138,144 @@ class Engine:
             return sh.lookup_route(q, q_ctx, cfg, now_us)
         return sh.lookup_route(q, q_ctx, cfg, now_us, tok=route_in["tok"], heur_dev=route_in["heur_dev"],
                                heur_conf=route_in["heur_conf"])
+
+
+class ShardedEngine:
+    """The same store interface over SEVERAL GPUs driven by one process (`config["gpus"] = [0, 1, ..]`):
+    one `Engine` per GPU, rows dealt round-robin, slots numbered `local_slot * n + shard` so the
+    host classes keep addressing rows by one integer.  A scan is one `qre_group_lookup_route` call:
+    every GPU scans and exactly re-scores its rows, the candidate lists meet on the first GPU and
+    the merge + routing kernel runs there.  Decisions equal the one-GPU engine's (tested)."""
+
+    def __init__(self, capacity: int = 512, devices: Sequence[int] = (0,), max_batch: int = 64,
+                 dim: Optional[int] = None, scan_mode: int = _cabi.SCAN_TENSOR):
+        self.devices = [int(d) for d in devices]
+        if not self.devices or len(self.devices) > 16:
+            raise ValueError("config['gpus'] must list 1..16 GPU indices")
+        self.n = len(self.devices)
+        self.capacity = max(int(capacity), 1)
+        self.max_batch, self.scan_mode = int(max_batch), int(scan_mode)
+        self._lock = threading.RLock()
+        self._next = 0
+        self._centroids = None
+        self._parts = [Engine(self._per(), d, max_batch, None, scan_mode) for d in self.devices]
+        if dim is not None:
+            self.ensure(dim)
+
+    def _per(self) -> int:
+        return (self.capacity + self.n - 1) // self.n + 1
+
+    # ---- lifetime ----
+    @_locked
+    def ensure(self, dim: int):
+        for p in self._parts:
+            p.capacity = max(p.capacity, self._per())
+            p.ensure(dim)
+        return self._parts[0].shard
+
+    @property
+    def shard(self):
+        return self._parts[0].shard
+
+    @_locked
+    def close(self) -> None:
+        for p in self._parts:
+            p.close()
+
+    @_locked
+    def set_centroids(self, centroids, owner) -> None:
+        self._centroids = np.ascontiguousarray(centroids, np.float32)
+        for p in self._parts:
+            p.set_centroids(centroids, owner)
+
+    @_locked
+    def set_perf_health(self, health) -> None:
+        for p in self._parts:
+            p.set_perf_health(health)
+
+    @property
+    def n_centroids(self) -> int:
+        return self._parts[0].n_centroids
+
+    # ---- rows: global slot = local * n + shard ----
+    def _split(self, slots):
+        slots = np.asarray(list(slots) if not isinstance(slots, np.ndarray) else slots, np.int64)
+        return slots, slots % self.n, slots // self.n
+
+    @_locked
+    def append(self, row, ctx: int, ts_us: int, lru: int, pdev: int, pconf: float) -> int:
+        d = self._next % self.n
+        self._next += 1
+        return self._parts[d].append(row, ctx, ts_us, lru, pdev, pconf) * self.n + d
+
+    @_locked
+    def append_many(self, rows, ctx, ts_us, lru, pdev, pconf) -> np.ndarray:
+        rows = np.ascontiguousarray(rows, np.float32)
+        k = rows.shape[0]
+        dest = (self._next + np.arange(k)) % self.n
+        self._next += k
+        out = np.empty(k, np.int64)
+        col = lambda v, sel: np.asarray(v)[sel]   # noqa: E731
+        for d in range(self.n):
+            sel = np.nonzero(dest == d)[0]
+            if sel.size:
+                loc = self._parts[d].append_many(rows[sel], col(ctx, sel), col(ts_us, sel), col(lru, sel),
+                                                 col(pdev, sel), col(pconf, sel))
+                out[sel] = np.asarray(loc, np.int64) * self.n + d
+        return out
+
+    @_locked
+    def update(self, slot: int, row=None, ts_us=None, lru=None, pdev=None, pconf=None) -> None:
+        self._parts[int(slot) % self.n].update(int(slot) // self.n, row, ts_us, lru, pdev, pconf)
+
+    @_locked
+    def update_many(self, slots, rows=None, ts_us=None, lru=None, pdev=None, pconf=None) -> None:
+        slots, sh, loc = self._split(slots)
+        pick = lambda v, sel: None if v is None else np.asarray(v)[sel]   # noqa: E731
+        for d in range(self.n):
+            sel = np.nonzero(sh == d)[0]
+            if sel.size:
+                self._parts[d].update_many(loc[sel], pick(rows, sel), pick(ts_us, sel), pick(lru, sel),
+                                           pick(pdev, sel), pick(pconf, sel))
+
+    @_locked
+    def tombstone(self, slots) -> None:
+        slots, sh, loc = self._split(slots)
+        for d in range(self.n):
+            sel = np.nonzero(sh == d)[0]
+            if sel.size:
+                self._parts[d].tombstone(loc[sel])
+
+    @_locked
+    def clear(self) -> None:
+        for p in self._parts:
+            p.clear()
+
+    @_locked
+    def read_rows(self, slots) -> np.ndarray:
+        slots, sh, loc = self._split(slots)
+        out = np.empty((slots.size, self._parts[0].shard.dim), np.float32)
+        for d in range(self.n):
+            sel = np.nonzero(sh == d)[0]
+            if sel.size:
+                out[sel] = self._parts[d].read_rows(loc[sel])
+        return out
+
+    @_locked
+    def scan(self, q, q_ctx, now_us: int, cfg: _cabi.RouteConfig, route_in: Optional[dict] = None) -> dict:
+        q = np.ascontiguousarray(q, np.float32)
+        if q.ndim == 1:
+            q = q.reshape(1, -1)
+        self.ensure(q.shape[1])
+        if q.shape[0] > self.max_batch:
+            raise _cabi.QreError(f"batch of {q.shape[0]} exceeds max_batch={self.max_batch}")
+        cfg.scan_mode = self.scan_mode
+        shards = [p.shard for p in self._parts]
+        ri = route_in or {}
+        out = _cabi.group_lookup_route(shards, q, q_ctx, cfg, now_us, tok=ri.get("tok"),
+                                       heur_dev=ri.get("heur_dev"), heur_conf=ri.get("heur_conf"))
+        hit = out["hit_slot"] >= 0
+        out["hit_slot"] = np.where(hit, out["hit_slot"] * self.n + out["hit_shard"].astype(np.int64), -1)
+        return out
+
+

@@ -38,7 +38,18 @@ except ImportError as _e:   # pragma: no cover
                       f"(distributed-llm_b200/): {_e}") from _e
 
 from qre_b200 import _cabi, heuristic_tables
-from qre_b200.engine import Engine
+from qre_b200.engine import Engine, ShardedEngine
+
+
+def _new_engine(config, capacity: int, max_batch: int = 64):
+    """Device store from a config dict: `gpus` = [i, j, ...] shards the rows over those GPUs (one
+    process drives them all), `gpu` = i (default 0) keeps everything on one."""
+    cfg = config or {}
+    gpus = list(cfg["gpus"]) if cfg.get("gpus") is not None else []
+    if len(gpus) > 1:
+        return ShardedEngine(capacity=capacity, devices=gpus, max_batch=max_batch)
+    return Engine(capacity=capacity, device=int(gpus[0]) if gpus else int(cfg.get("gpu", 0)), max_batch=max_batch)
+
 
 logger = logging.getLogger(__name__)
 
@@ -145,7 +156,7 @@ class SemanticRouter(BaseRouter):
             self.nano_center, self.orin_center = self._load_and_build_centroids(self.label_path)
             self.centroids = np.stack([self.nano_center, self.orin_center]).astype(np.float32)
             self.owner = np.array([0, 1], np.uint8)
-        self._engine = engine if engine is not None else Engine(capacity=1, device=int(config.get("gpu", 0)))
+        self._engine = engine if engine is not None else _new_engine(config, 1)
         self._engine.set_centroids(self.centroids, self.owner)
 
     _SIMPLE_SEED = ("Hello", "What is 2+2?", "Define machine learning", "What is the weather today?")
@@ -452,8 +463,9 @@ class QueryRouter:
         self.strategy_name = strategy
         self.cache_enabled = bool(self.config.get("cache_enabled", True))
         max_size = int(self.config.get("cache_max_size", 500))
-        self._engine = Engine(capacity=max(max_size, 1), device=int(self.config.get("gpu", 0)),
-                              max_batch=int(self.config.get("max_batch", 64)))
+        # config["gpus"] = [0, 1, ...]: the cache is row-sharded over those GPUs (one process drives
+        # them all); config["gpu"] = i or nothing: one GPU.  Additive keys, reference defaults otherwise.
+        self._engine = _new_engine(self.config, max(max_size, 1), int(self.config.get("max_batch", 64)))
         self.router = self._make_router(strategy)
         self._cache = QueryCache(
             max_size=max_size,

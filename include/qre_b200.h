@@ -215,6 +215,18 @@ QRE_API int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries
                            const qre_params_t* params, qre_result_t* out_dev, void* in_stream);
 QRE_API int qre_wait_dev(qre_cache_t* h, int slot, void* stream);
 
+/* One process driving several GPUs: the same call over a GROUP of handles, one per GPU, that
+ * together hold one row-sharded cache (the single-process shape of SURVEY §8b/§8e; the reference
+ * builds its one cache at src/query_router_engine.py:497-505).  Every handle scans and exactly
+ * re-scores its own rows for the whole batch on its GPU, the per-shard candidate lists are copied
+ * to the first handle's GPU and merged there with the reference's comparator (sim desc, LRU order
+ * asc, src/cache.py:292), followed by the routing epilogue.  Host buffers, synchronous.
+ * out->hit_shard[i] = index in hs[] of the handle that holds the hit row, out->hit_slot[i] its slot
+ * there.  Centroids / perf health are read from hs[0]. */
+QRE_API int qre_group_lookup_route(qre_cache_t* const* hs, int n_handles, int m, const float* queries,
+                                   const uint64_t* q_ctx, const int32_t* tok, const uint8_t* heur_dev,
+                                   const double* heur_conf, const qre_params_t* params, qre_result_t* out);
+
 /* Device-pointer pipeline, one stage per call (all enqueue on `stream`):
  *   qre_scan_dev   : queries -> this shard's exactly re-scored candidates cand[m, QRE_TOPK]
  *   (multi-GPU: all-gather cand over NCCL, e.g. torch.distributed.all_gather_into_tensor)

@@ -383,3 +383,42 @@ def test_begin_end_slots_overlap_and_pinned_inputs(small):
     assert sh.lib.qre_lookup_route_end(sh.h, 0, ctypes.byref(_cabi.Result())) == 1
     assert b"no batch in flight" in sh.lib.qre_last_error()
     sh.close()
+
+
+def test_group_lookup_route_two_shards_one_process(small):
+    """qre_group_lookup_route: one process, the rows dealt over two handles (two GPUs when the box has
+    them, else both on GPU 0), lists gathered and merged on the first handle's GPU.  Must equal the
+    oracle over the whole cache, including the cross-shard tie-break by LRU order."""
+    import torch
+    w = small
+    devs = [0, 1] if torch.cuda.device_count() >= 2 else [0, 0]
+    n = w.rows.shape[0]
+    rows = w.rows.copy()
+    ctx = w.row_ctx.copy()
+    rows[1:41:2] = rows[0:40:2]               # twins in different shards: lru decides
+    ctx[1:41:2] = ctx[0:40:2]
+    shards = []
+    for r, dev in enumerate(devs):
+        idx = np.arange(r, n, 2)
+        sh = _cabi.Shard(dim=384, capacity=idx.size, max_batch=300, device=dev)
+        sh.append(rows[idx], ctx[idx], w.row_ts_us[idx], w.row_lru[idx], w.row_pred_dev[idx], w.row_pred_conf[idx])
+        sh.set_centroids(w.centroids, w.owner)
+        shards.append(sh)
+    cfg = _cabi.RouteConfig(ttl_us=w.ttl_us)
+    out = _cabi.group_lookup_route(shards, w.queries, w.q_ctx, cfg, w.now_us, tok=w.tok, heur_dev=w.heur_dev,
+                                   heur_conf=w.heur_conf)
+    img = O.CacheImage(rows, ctx, w.row_ts_us, w.row_lru)
+    exp_row, exp_sim = O.scan_batch(w.queries, w.q_ctx, img, w.now_us, w.ttl_us, 0.85)
+    glob = np.where(out["hit_slot"] >= 0, out["hit_slot"] * 2 + out["hit_shard"], -1)
+    assert np.array_equal(glob, exp_row)
+    hit = exp_row >= 0
+    assert hit.sum() > 50
+    np.testing.assert_allclose(out["hit_sim"][hit], exp_sim[hit], rtol=REL)
+    assert np.array_equal(out["hit_pred_dev"][hit], w.row_pred_dev[exp_row[hit]])
+    r = O.route_batch(w.queries, w.tok, w.heur_dev, w.heur_conf, w.centroids, w.owner, O.RouteParams())
+    np.testing.assert_allclose(out["centroid_sim"], r["sims"], rtol=REL, atol=1e-7)
+    assert float(np.mean(out["dev"] == r["dev"])) > 0.995
+    out2 = _cabi.group_lookup_route(shards, w.queries, w.q_ctx, cfg, w.now_us)      # lookup only, again
+    assert np.array_equal(out2["hit_slot"], out["hit_slot"]) and np.array_equal(out2["hit_sim"], out["hit_sim"])
+    for sh in shards:
+        sh.close()

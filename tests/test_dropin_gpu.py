@@ -11,6 +11,13 @@ from tests import replay_common as R
 pytestmark = pytest.mark.gpu
 
 
+def _two_gpus():
+    """GPU indices for a two-shard store: two different GPUs when the box has them, else two shards
+    on GPU 0 (the same code path: per-shard scans, lists gathered on the first shard, one merge)."""
+    import torch
+    return [0, 1] if torch.cuda.device_count() >= 2 else [0, 0]
+
+
 def test_cache_ops_replay_gpu():
     clock = ref_harness.FakeClock()
     cache_mod, _, _ = R.load_modules(clock)
@@ -119,7 +126,8 @@ def test_binary_snapshot_roundtrip(tmp_path):
     assert b.lookup("probe", "ctx0", w.rows[0]).entry.query == "fresh"
 
 
-def test_config1_sequential_replay_matches_reference_run():
+@pytest.mark.parametrize("n_shards", [1, 2])
+def test_config1_sequential_replay_matches_reference_run(n_shards):
     """BASELINE.json configs[0] — the reference's own CPU-runnable case: hybrid strategy + semantic
     cache, 10,000 pre-inserted entries, 1,000 queries routed ONE AT A TIME through
     QueryRouter.route_query (so query i can hit what query i-1 inserted), 384-d fp32.  The
@@ -135,7 +143,10 @@ def test_config1_sequential_replay_matches_reference_run():
     _, qre_mod, st = R.load_modules(clock)
 
     def patch(cfg, qr=None):
-        return {"centroids": cents, "centroid_owner": [0, 1]}
+        extra = {"centroids": cents, "centroid_owner": [0, 1]}
+        if n_shards == 2:            # config["gpus"]: rows sharded over two device stores, same decisions
+            extra["gpus"] = _two_gpus()
+        return extra
 
     t0 = time.time()
     out, stats, checksum = G.run_config1(qre_mod, st, clock, patch)
@@ -148,11 +159,11 @@ def test_config1_sequential_replay_matches_reference_run():
         assert abs(a["confidence"] - b["confidence"]) <= 4e-6 + 1e-5 * abs(b["confidence"]), (a, b)
     for k, v in g["stats"].items():
         assert stats[k] == v, (k, stats[k], v)
-    print(f"config 1: reference {g['reference_seconds']} s, drop-in on GPU {ours_s:.1f} s")
+    print(f"config 1 ({n_shards} shard(s)): reference {g['reference_seconds']} s, drop-in on GPU {ours_s:.1f} s")
 
 
-@pytest.mark.parametrize("seed", [0, 1])
-def test_random_ops_device_engine_vs_oracle_engine(seed, tmp_path):
+@pytest.mark.parametrize("seed,sharded", [(0, False), (1, False), (2, True), (3, True)])
+def test_random_ops_device_engine_vs_oracle_engine(seed, sharded, tmp_path):
     """Differential test of the device store under realistic interleavings: the same random
     sequence of inserts / refreshes / lookups / evictions / invalidations / snapshot round trips is
     applied to two QueryCache objects, one on the real libqre_b200 engine and one on the
@@ -165,7 +176,9 @@ def test_random_ops_device_engine_vs_oracle_engine(seed, tmp_path):
     base = rs.standard_normal((40, d)).astype(np.float32)
     kw = dict(max_size=int(rs.integers(8, 20)), ttl_seconds=int(rs.integers(30, 90)), similarity_threshold=0.85,
               prediction_confidence_threshold=0.7)
-    gpu = cache_mod.QueryCache(**kw)
+    gkw = dict(kw, gpus=_two_gpus()) if sharded else kw
+    gpu = cache_mod.QueryCache(**gkw)
+    assert type(gpu._engine).__name__ == ("ShardedEngine" if sharded else "Engine")
     cpu = cache_mod.QueryCache(**kw, engine=OracleEngine(capacity=64, dim=d))
     ctxs = ["A", "B"]
     hits = 0
@@ -202,7 +215,7 @@ def test_random_ops_device_engine_vs_oracle_engine(seed, tmp_path):
         elif op == "invalidate":
             pat = rf"item {int(rs.integers(0, 4))}\d?$"
             assert gpu.invalidate(query_pattern=pat) == cpu.invalidate(query_pattern=pat)
-        elif op == "snapshot" and gpu._engine.shard is not None:
+        elif op == "snapshot" and gpu._engine.shard is not None and not sharded:
             p = str(tmp_path / f"s{step}.json")
             gpu.save_snapshot(p)
             cpu._evict_expired()                        # save_snapshot drops expired entries first, like save()
