@@ -106,6 +106,7 @@ class CacheEntry:
     routing_history: List[RoutingRecord] = field(default_factory=list)
     _slot: Optional[int] = field(default=None, repr=False, compare=False)
     _seq: int = field(default=0, repr=False, compare=False)
+    _pred: Optional[tuple] = field(default=None, repr=False, compare=False)   # memo: (len, id of last, result)
 
     MAX_HISTORY = 20
 
@@ -113,12 +114,23 @@ class CacheEntry:
         self.routing_history.append(RoutingRecord(device, confidence, method, datetime.now().isoformat()))
         del self.routing_history[:-self.MAX_HISTORY]
         self.device_used = device
+        self._pred = None
 
     def predict_device(self) -> Tuple[str, float]:
         """Recency-weighted vote (reference cache.py:106-140): newest record weighs
         confidence, the i-th newest 0.85**i * confidence; the winner's share of the total is
         the confidence; equal scores go to the HIGHER device index ("orin" >= "nano");
-        no history or ~zero weight -> (device_used, 0.5)."""
+        no history or ~zero weight -> (device_used, 0.5).  The vote only depends on the history,
+        so it is memoised until the history (or device_used) changes."""
+        h = self.routing_history
+        memo = self._pred
+        if memo is not None and memo[0] == len(h) and (not h or memo[1] is h[-1]) and memo[2] == self.device_used:
+            return memo[3]
+        res = self._predict_device()
+        self._pred = (len(h), h[-1] if h else None, self.device_used, res)
+        return res
+
+    def _predict_device(self) -> Tuple[str, float]:
         if not self.routing_history:
             return self.device_used, 0.5
         score = [0.0] * len(DEVICE_NAMES)
@@ -442,6 +454,7 @@ class QueryCache:
                 outs.append(self._engine.scan(q_embs[sl], ctx[sl], _to_us(now), cfg, ri))
             out = {k: np.concatenate([o[k] for o in outs]) for k in outs[0]} if outs else {}
             results: List[Optional[CacheLookupResult]] = []
+            self._batch_keys = [self._make_hash(q, c) for q, c in zip(queries, context_keys)]   # one md5 per query
             with self._deferred():
                 self._apply_batch_hits(queries, context_keys, out, now, results)
             return results, out
@@ -449,12 +462,14 @@ class QueryCache:
     def _apply_batch_hits(self, queries, context_keys, out, now, results) -> None:
         """Host bookkeeping of a batch's hits, in order (exact-hash match first, then the device
         scan's row), as `lookup` does for one query."""
+        keys = self._batch_keys
+        slots = out["hit_slot"].tolist() if self.use_semantic else [-1] * len(queries)
         for i, (q, c) in enumerate(zip(queries, context_keys)):
             self._attempts += 1
-            entry = self._store.get(self._make_hash(q, c))
+            entry = self._store.get(keys[i])
             if entry is None or entry.context_key != c or not self._is_valid(entry, now):
                 entry = None
-                slot = int(out["hit_slot"][i]) if self.use_semantic else -1
+                slot = slots[i]
                 if slot >= 0:
                     entry = self._store.get(self._slot_key.get(slot, ""))
                     if entry is not None and not self._is_valid(entry, now):
@@ -473,9 +488,10 @@ class QueryCache:
 
     def insert(self, query: str, context_key: str, device: str, confidence: float = 1.0,
                method: str = "unknown", q_emb: Optional[np.ndarray] = None,
-               response_time: Optional[float] = None) -> None:
-        """Insert, or refresh in place when the hash exists (reference cache.py:328-370)."""
-        key = self._make_hash(query, context_key)
+               response_time: Optional[float] = None, *, _key: Optional[str] = None) -> None:
+        """Insert, or refresh in place when the hash exists (reference cache.py:328-370).
+        (`_key`: the batch path hands over the md5 it already computed for the lookup.)"""
+        key = _key if _key is not None else self._make_hash(query, context_key)
         with self._lock:
             now = datetime.now()
             entry = self._store.get(key)

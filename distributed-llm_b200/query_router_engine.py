@@ -78,6 +78,37 @@ class RoutingDecision:
     cache_hit: bool = False
 
 
+class LazyRoutingDecision(RoutingDecision):
+    """A RoutingDecision whose `reasoning` string is formatted on first access (batch path: 4096
+    f-strings per batch cost more than the device pass).  Everything else — fields, equality with
+    plain decisions, repr — is the reference's record (qre:55-62)."""
+
+    def __init__(self, device, confidence, method, reasoning_fn, complexity_score=None, cache_hit=False):
+        self.device, self.confidence, self.method = device, confidence, method
+        self.complexity_score, self.cache_hit = complexity_score, cache_hit
+        self.__dict__["_lazy"] = reasoning_fn
+
+    def __getattr__(self, name):
+        if name == "reasoning":
+            fn = self.__dict__.pop("_lazy")
+            self.__dict__["reasoning"] = r = fn()
+            return r
+        raise AttributeError(name)
+
+    def _t(self):
+        return (self.device, self.confidence, self.method, self.reasoning, self.complexity_score, self.cache_hit)
+
+    def __eq__(self, other):
+        return isinstance(other, RoutingDecision) and self._t() == (
+            other.device, other.confidence, other.method, other.reasoning, other.complexity_score, other.cache_hit)
+
+    __hash__ = None
+
+    def __repr__(self):
+        return ("RoutingDecision(device={!r}, confidence={!r}, method={!r}, reasoning={!r}, "
+                "complexity_score={!r}, cache_hit={!r})").format(*self._t())
+
+
 class BaseRouter(ABC):
     def __init__(self, config: Dict[str, Any]):
         self.config = config
@@ -287,6 +318,25 @@ class HeuristicRouter(BaseRouter):
         dev, conf, method, why, score = self.classify(query, context)
         return RoutingDecision(device=self._names[dev], confidence=conf, method=method, reasoning=why,
                                complexity_score=score)
+
+    def features_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
+        """What the fused device pass needs from the host for a batch — token counts and the
+        heuristic (device, confidence) pairs — as arrays, without building any per-query object
+        (qre_host_features on C++ threads; non-ASCII queries, and every query when a real
+        tokenizer is installed, go through the Python rules)."""
+        if LITELLM_AVAILABLE:
+            feats, toks = self.classify_batch(queries, contexts)
+            return (np.asarray(toks, np.int32), np.array([f[0] for f in feats], np.uint8),
+                    np.array([f[1] for f in feats], np.float64))
+        hp = _cabi.HeurParams(self.long_text_threshold, self.multi_question_threshold, self.code_markers_needed,
+                              self.context_chars_threshold, self._token_fallback.threshold, len(self._names))
+        r = _cabi.host_features([(q or "") for q in queries], [len(c) if c else 0 for c in contexts], hp)
+        tok, hd, hc = r["tok"], r["heur_dev"], r["heur_conf"]
+        for i in np.nonzero(r["rule"] < 0)[0].tolist():
+            f = self.classify(queries[i], contexts[i])
+            hd[i], hc[i] = f[0], f[1]
+            tok[i] = self._token_fallback.count(queries[i], contexts[i])
+        return tok, hd, hc
 
     def classify_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
         """`classify` for a whole batch on C++ threads (libqre_b200 qre_host_features); the few
@@ -566,15 +616,15 @@ class QueryRouter:
         r = self.router
         hybrid = isinstance(r, HybridRouter)
         sem = r.routers["semantic"] if hybrid else r
-        if hybrid:        # heuristic rules + token estimate for the whole batch on C++ threads
-            hfeats, toks = r.routers["heuristic"].classify_batch(list(queries), contexts)
-            tr = r.routers["token"]
-            feats = [(tr._decision(t, *tr.decide(t)), h) for t, h in zip(toks, hfeats)]
+        if hybrid:        # heuristic rules + token estimate for the whole batch on C++ threads, as arrays
+            tok, hd, hc = r.routers["heuristic"].features_batch(list(queries), contexts)
+            feats = (tok.tolist(), hd.tolist(), hc.tolist())
+            route_in = dict(tok=tok, heur_dev=hd, heur_conf=hc)
         else:
             feats = [(r._token_fallback.route(q, c), (0, 0.0, "", "", None)) for q, c in zip(queries, contexts)]
-        route_in = dict(tok=np.array([int(t.complexity_score) for t, _ in feats], np.int32),
-                        heur_dev=np.array([h[0] for _, h in feats], np.uint8),
-                        heur_conf=np.array([h[1] for _, h in feats], np.float64))
+            route_in = dict(tok=np.array([int(t.complexity_score) for t, _ in feats], np.int32),
+                            heur_dev=np.array([h[0] for _, h in feats], np.uint8),
+                            heur_conf=np.array([h[1] for _, h in feats], np.float64))
         results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg())
         with self._cache._deferred():        # all inserts of the batch reach the device in a few calls
             return self._finish_batch(queries, contexts, ctxks, q_embs, feats, results, out, hybrid)
@@ -583,31 +633,57 @@ class QueryRouter:
         r = self.router
         decisions: List[RoutingDecision] = []
         threshold = int(self.config.get("heuristic_context_chars", 800))
+        keys = self._cache._batch_keys
+        now = datetime.now()
+        cached_method = f"{self.strategy_name}_cached"
+        if hybrid:
+            # decisions straight from the result arrays; the reasoning string (and the token /
+            # semantic sub-decisions it quotes) is only formatted if somebody reads it
+            toks, hds, hcs = feats
+            names, tr = r._names, r.routers["token"]
+            devs, confs = out["dev"].tolist(), out["conf"].tolist()
+
+            def why(i):
+                tok_d = tr._decision(toks[i], *tr.decide(toks[i]))
+                return r._decision(out, i, tok_d, (hds[i], hcs[i])).reasoning
         for i, (q, c, k) in enumerate(zip(queries, contexts, ctxks)):
-            tok_d, heur = feats[i]
-            routed = r._decision(out, i, tok_d, heur) if hybrid else r._decision(out, i, tok_d)
             res = results[i]
+            routed = None
             if res is not None:
                 context_len = len(c) if c else 0
                 heavy_ctx = context_len >= threshold and res.predicted_device == DEVICE_NAMES[0]
                 if not (heavy_ctx or res.use_hybrid_fallback):
-                    age = int((datetime.now() - res.entry.timestamp).total_seconds())
-                    decisions.append(RoutingDecision(
-                        device=res.predicted_device, confidence=res.predicted_confidence,
-                        method=f"{self.strategy_name}_cached",
-                        reasoning=(f"cache hit age={age}s hits={res.entry.hit_count} "
-                                   f"predicted={res.predicted_device} conf={res.predicted_confidence:.2f} "
-                                   f"context_len={context_len} history={len(res.entry.routing_history)}"),
+                    # the figures the reasoning quotes are taken NOW (hit count / history may move on)
+                    snap = (int((now - res.entry.timestamp).total_seconds()), res.entry.hit_count,
+                            res.predicted_device, res.predicted_confidence, context_len,
+                            len(res.entry.routing_history))
+                    decisions.append(LazyRoutingDecision(
+                        res.predicted_device, res.predicted_confidence, cached_method,
+                        (lambda t=snap: f"cache hit age={t[0]}s hits={t[1]} predicted={t[2]} conf={t[3]:.2f} "
+                                        f"context_len={t[4]} history={t[5]}"),
                         cache_hit=True))
                     continue
                 reason = (f"context_len={context_len}>={threshold} overrides cached nano" if heavy_ctx
                           else f"low prediction confidence={res.predicted_confidence:.2f}")
+                routed = self._routed(i, feats, out, hybrid)
                 routed.reasoning = f"cache hit (hybrid re-route: {reason}) | " + routed.reasoning
                 routed.cache_hit = True
+            if routed is None:
+                routed = (LazyRoutingDecision(names[devs[i]], confs[i], "hybrid", (lambda i=i: why(i)))
+                          if hybrid else self._routed(i, feats, out, hybrid))
             self._cache.insert(q, k, device=routed.device, confidence=routed.confidence, method=routed.method,
-                               q_emb=q_embs[i])
+                               q_emb=q_embs[i], _key=keys[i])
             decisions.append(routed)
         return decisions
+
+    def _routed(self, i: int, feats, out, hybrid: bool) -> RoutingDecision:
+        """The fully formatted routing decision of batch item i (the per-query path's form)."""
+        r = self.router
+        if not hybrid:
+            return r._decision(out, i, feats[i][0])
+        toks, hds, hcs = feats
+        tr = r.routers["token"]
+        return r._decision(out, i, tr._decision(toks[i], *tr.decide(toks[i])), (hds[i], hcs[i]))
 
     def _route(self, query: str, context: Optional[str], q_emb: Optional[np.ndarray]) -> RoutingDecision:
         if isinstance(self.router, HybridRouter) and q_emb is not None:
