@@ -1015,6 +1015,19 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
   }
   QRE_CUDA(cudaGetLastError());
   qre_params_t p_merge = p;
+  if (serial && p.do_route) {
+    // small batch: the chain stays on the main stream (launched as a programmatic-dependent chain),
+    // only the routing epilogue forks to the aux stream and runs under the scan
+    QRE_CUDA(cudaEventRecord(h->ev_prep[slot], s.stream));
+    QRE_CUDA(cudaStreamWaitEvent(h->aux, h->ev_prep[slot], 0));
+    if (prev_ps >= 0 && prev_ps != slot && h->post_used[prev_ps])
+      QRE_CUDA(cudaStreamWaitEvent(h->aux, h->ev_post[prev_ps], 0));
+    h->launches += launch_route_only(s, m, d_tok, d_hd, d_hc, p, out_dev, h->aux, q0, q1);
+    QRE_CUDA(cudaGetLastError());
+    QRE_CUDA(cudaEventRecord(h->ev_route[slot], h->aux));
+    p_merge.do_route = 0;
+  }
+  s.pdl = serial;
   if (!serial) {
     QRE_CUDA(cudaEventRecord(h->ev_prep[slot], aux));
     QRE_CUDA(cudaStreamWaitEvent(s.stream, h->ev_prep[slot], 0));
@@ -1030,23 +1043,26 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
     }
   }
   int rc = tensor_scan_enqueue(h, m, p, s.stream);
-  if (rc != QRE_OK) return rc;
+  if (rc != QRE_OK) { s.pdl = false; return rc; }
   if (!serial) {
     QRE_CUDA(cudaEventRecord(h->ev_scan[slot], s.stream));
     QRE_CUDA(cudaStreamWaitEvent(post, h->ev_scan[slot], 0));
   }
   rc = rescore_enqueue(h, m, p, sharded ? h->xchg_rank : 0, B.cand, post);
-  if (rc != QRE_OK) return rc;
+  if (rc != QRE_OK) { s.pdl = false; return rc; }
   if (sharded) {
+    s.pdl = false;                           // the exchange kernels are plain launches
     rc = publish_impl(h, m, B.cand, post, per);
     if (rc != QRE_OK) return rc;
     rc = merge_xchg_impl(h, m, d_tok, d_hd, d_hc, &p_merge, const_cast<qre_result_t*>(&out_dev), post, q0, q1);
     if (rc != QRE_OK) return rc;
   } else {
     h->launches += launch_merge_route(s, m, 1, B.cand, d_tok, d_hd, d_hc, p_merge, out_dev, post);
+    s.pdl = false;
     QRE_CUDA(cudaGetLastError());
   }
-  if (!serial && p.do_route) QRE_CUDA(cudaStreamWaitEvent(post, h->ev_route[slot], 0));   // batch done = both halves
+  s.pdl = false;
+  if (p.do_route) QRE_CUDA(cudaStreamWaitEvent(post, h->ev_route[slot], 0));   // batch done = both halves
   QRE_CUDA(cudaEventRecord(h->ev_post[slot], post));
   h->post_used[slot] = true;
   return QRE_OK;

@@ -145,6 +145,10 @@ struct DeviceState {
   double* perf_health = nullptr;      // [QRE_MAX_DEVICES]
   CUtensorMap tmap_e, tmap_eh;        // cache rows (256-row box / 128-row half box)
   bool allow_pair = true;               // QRE_SCAN_SINGLE_CTA=1 forces the single-CTA kernel
+  // Small batches run prep -> scan -> re-score -> settle -> merge on ONE stream; with this set the
+  // links after prep are launched with programmatic stream serialization (qre_encoder.cuh): each
+  // kernel's CTAs are scheduled and set up while its predecessor drains, and block in pdl_wait().
+  bool pdl = false;
   // optional CUDA-event bracket around every scan-kernel launch (bench.py's live roofline)
   bool prof_on = false;
   cudaEvent_t* prof_ev = nullptr;     // [2 * kProfMax]

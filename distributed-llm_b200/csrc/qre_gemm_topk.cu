@@ -25,6 +25,7 @@
 #include <type_traits>
 
 #include "qre_common.cuh"
+#include "qre_encoder.cuh"      // programmatic dependent launch helpers
 #include "qre_ptx.cuh"
 #include "qre_scan_epilogue.cuh"
 
@@ -61,6 +62,7 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   uint64_t* t_empty = t_full + 2;           // [2] epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
@@ -89,6 +91,7 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                               // set-up done; the queries (prep kernel) must be complete from here
 
   const int U = a.splits * a.mblocks;
   const long long T = a.tiles_n;
@@ -309,11 +312,11 @@ int launch_gemm_topk(DeviceState& s, int m, long long n_rows, const qre_params_t
   if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
   const bool resident = a.num_kb <= kMaxKB;
   if (dump != nullptr) {
-    if (resident) qre_gemm_topk_kernel<true, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
-    else qre_gemm_topk_kernel<true, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
+    if (resident) launch_chain(qre_gemm_topk_kernel<true, true>, dim3(g.grid), dim3(kThreads), kSmemTotal, st, s.pdl, s.cur().tmap_q, s.tmap_e, a);
+    else launch_chain(qre_gemm_topk_kernel<true, false>, dim3(g.grid), dim3(kThreads), kSmemTotal, st, s.pdl, s.cur().tmap_q, s.tmap_e, a);
   } else {
-    if (resident) qre_gemm_topk_kernel<false, true><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
-    else qre_gemm_topk_kernel<false, false><<<g.grid, kThreads, kSmemTotal, st>>>(s.cur().tmap_q, s.tmap_e, a);
+    if (resident) launch_chain(qre_gemm_topk_kernel<false, true>, dim3(g.grid), dim3(kThreads), kSmemTotal, st, s.pdl, s.cur().tmap_q, s.tmap_e, a);
+    else launch_chain(qre_gemm_topk_kernel<false, false>, dim3(g.grid), dim3(kThreads), kSmemTotal, st, s.pdl, s.cur().tmap_q, s.tmap_e, a);
   }
   if (prof) {
     cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);

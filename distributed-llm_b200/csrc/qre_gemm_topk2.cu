@@ -28,6 +28,7 @@
 #include <type_traits>
 
 #include "qre_common.cuh"
+#include "qre_encoder.cuh"      // programmatic dependent launch helpers
 #include "qre_ptx.cuh"
 #include "qre_scan_epilogue.cuh"
 
@@ -126,6 +127,7 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   uint64_t* t_empty = t_full + 2;              // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -159,6 +161,7 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                  // set-up done; the queries (prep kernel) must be complete from here
 
   const int npairs = (a.mblocks + 1) >> 1;
   const int U = a.splits * npairs;
@@ -316,9 +319,11 @@ int launch_gemm_topk_pair(DeviceState& s, int m, long long n_rows, const qre_par
   const bool prof = s.prof_on && s.prof_ev != nullptr && s.prof_used < kProfMax && dump == nullptr;
   if (prof) cudaEventRecord(s.prof_ev[2 * s.prof_used], st);
   if (dump != nullptr)
-    qre_gemm_topk_pair_kernel<true><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.cur().tmap_q, s.tmap_eh, a);
+    launch_chain(qre_gemm_topk_pair_kernel<true>, dim3(g.grid), dim3(kThreads2), kSmemTotal2, st, s.pdl,
+                 s.cur().tmap_q, s.tmap_eh, a);
   else
-    qre_gemm_topk_pair_kernel<false><<<g.grid, kThreads2, kSmemTotal2, st>>>(s.cur().tmap_q, s.tmap_eh, a);
+    launch_chain(qre_gemm_topk_pair_kernel<false>, dim3(g.grid), dim3(kThreads2), kSmemTotal2, st, s.pdl,
+                 s.cur().tmap_q, s.tmap_eh, a);
   if (prof) {
     cudaEventRecord(s.prof_ev[2 * s.prof_used + 1], st);
     ++s.prof_used;

@@ -13,6 +13,7 @@
 #include <stdio.h>
 
 #include "qre_common.cuh"
+#include "qre_encoder.cuh"      // pdl_wait / pdl_launch_dependents / launch_chain
 
 namespace qre {
 
@@ -149,6 +150,7 @@ __global__ void prep_queries_kernel(int m, int rows_total, const float* q, int d
                                     __nv_bfloat16* q_bf16, float* q_norm, const uint64_t* q_ctx_src,
                                     uint64_t* q_ctx_dst, uint32_t* counters, const uint32_t* wait_flags,
                                     int n_wait, uint32_t wait_epoch) {
+  pdl_launch_dependents();      // head of the small-batch chain: let the scan's CTAs set up meanwhile
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (blockIdx.x == 0 && threadIdx.x < 4) counters[threadIdx.x] = 0u;   // spill bump, overflow counters
@@ -265,6 +267,8 @@ __device__ __forceinline__ void rescore_one(const RescoreArgs& a, CandList& L, c
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) rescore_kernel(const RescoreArgs a) {
   __shared__ CandList lists[kWarpsPerBlock];
+  pdl_launch_dependents();
+  pdl_wait();                   // no-ops unless launched as a link of the small-batch chain
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = blockIdx.x * kWarpsPerBlock + warp;
   if (q >= a.m) return;
@@ -534,6 +538,8 @@ __global__ void __launch_bounds__(kExactWarps * 32) overflow_settle_kernel(const
   extern __shared__ float qs[];
   __shared__ ExactSmem sm;
   __shared__ unsigned s_ticket;
+  pdl_launch_dependents();
+  pdl_wait();
   const int n_ovf = *sa.ovf_count;
   if (n_ovf <= 0) {
     if (blockIdx.x == 0 && threadIdx.x == 0) *sa.unresolved = 0;
@@ -734,6 +740,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) route_only_kernel(const M
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) merge_route_kernel(const MergeArgs a) {
   __shared__ float s_dsim[kWarpsPerBlock][QRE_MAX_DEVICES];
   __shared__ double s_S[kWarpsPerBlock][QRE_MAX_DEVICES];
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = a.q0 + blockIdx.x * kWarpsPerBlock + warp;
   if (a.wait_flags != nullptr) {
@@ -951,7 +959,8 @@ int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& 
   a.row_norm = s.row_norm; a.lru = s.lru; a.pdev = s.pred_dev; a.pconf = s.pred_conf; a.cand = cand;
   a.q_flags = b.q_flags;
   a.ovf_count = b.ovf_count(); a.ovf_list = b.ovf_list;
-  rescore_kernel<<<(m + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
+  launch_chain(rescore_kernel, dim3((m + kWarpsPerBlock - 1) / kWarpsPerBlock), dim3(kWarpsPerBlock * 32), 0, st,
+               s.pdl, a);
   return 1;
 }
 
@@ -996,7 +1005,7 @@ int launch_overflow_settle(DeviceState& s, long long n_rows, const qre_params_t&
   sa.shard = shard; sa.pdev = s.pred_dev;
   sa.pconf = s.pred_conf; sa.cand = cand; sa.q_flags = b.q_flags;
   const size_t smem = static_cast<size_t>(kExactGroup) * s.dim_pad * sizeof(float);
-  overflow_settle_kernel<<<s.exact_grid, kExactWarps * 32, smem, st>>>(sa);
+  launch_chain(overflow_settle_kernel, dim3(s.exact_grid), dim3(kExactWarps * 32), smem, st, s.pdl, sa);
   return 1;
 }
 
@@ -1017,7 +1026,8 @@ int launch_merge_route(DeviceState& s, int m, int n_shards, const qre_candidate_
   a.q0 = q0 < 0 ? 0 : q0;
   a.q1 = q1 < 0 || q1 > m ? m : q1;
   const int nq = a.q1 - a.q0 > 0 ? a.q1 - a.q0 : 1;   // an empty slice still launches (it may have to wait for flags)
-  merge_route_kernel<<<(nq + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, st>>>(a);
+  launch_chain(merge_route_kernel, dim3((nq + kWarpsPerBlock - 1) / kWarpsPerBlock), dim3(kWarpsPerBlock * 32), 0, st,
+               s.pdl, a);
   return 1;
 }
 
