@@ -368,7 +368,8 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     QRE_ALLOC(B.partial, sizeof(PartialEntry) * (size_t)s.partial_entries);
     QRE_ALLOC(B.spill_head, sizeof(uint32_t) * (size_t)(s.partial_entries / kTopK));
     QRE_ALLOC(B.spill_pool, sizeof(SpillChunk) * (size_t)s.spill_cap);
-    QRE_ALLOC(B.counters, sizeof(uint32_t) * 4);
+    QRE_ALLOC(B.counters, sizeof(uint32_t) * 8);
+    QRE_TRY([&]() -> int { QRE_CUDA(cudaMemset(B.counters, 0, sizeof(uint32_t) * 8)); return QRE_OK; }());
     QRE_ALLOC(B.ovf_list, sizeof(int32_t) * (size_t)max_batch);
     QRE_ALLOC(B.cand, sizeof(qre_candidate_t) * (size_t)max_batch * QRE_TOPK);
   }

@@ -74,6 +74,7 @@ struct GemmArgs {
   SpillChunk* spill_pool;   // [spill_cap]
   uint32_t* spill_next;     // bump counter, zeroed per batch
   uint32_t spill_cap;
+  uint32_t* work_ctr;       // [2] CTA-pair scan: next work unit to claim, pairs finished (both 0 between launches)
   float* dump;              // debug: raw accumulators out[q * dump_ld + (row - dump_row0)]
   long long dump_ld, dump_row0;
 };
@@ -118,7 +119,8 @@ struct DeviceState {
     PartialEntry* partial = nullptr;    // [partial_entries]  per (query, range) approximate top-k
     uint32_t* spill_head = nullptr;     // [partial_entries / kTopK]
     SpillChunk* spill_pool = nullptr;   // [spill_cap]
-    uint32_t* counters = nullptr;       // [4]: 0 spill bump counter, 1 overflowed queries, 2 unresolved
+    uint32_t* counters = nullptr;       // [8]: 0 spill bump counter, 1 overflowed queries, 2 unresolved (zeroed per
+                                        // batch by the prep kernel); 4, 5 the pair scan's work-unit counters (self-resetting)
     int32_t* ovf_list = nullptr;        // [max_batch]
     qre_candidate_t* cand = nullptr;    // [max_batch, kTopK] this shard's exactly re-scored candidates
     CUtensorMap tmap_q;                 // 128-row boxes over q_bf16

@@ -182,8 +182,8 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       const int q = mb * kBM + warp * 32 + lane;
       const bool active = q < a.m;
       const uint64_t myctx = active ? a.q_ctx[q] : 0ull;
-      topk_reset(tk, a.floor_v);
       float kth = active ? a.floor_v : __int_as_float(0x7f800000);
+      topk_reset(tk, a, static_cast<long long>(q) * a.splits + s, kth);
       for (int t = t0; t < t1; ++t) {
         const uint32_t acc = tile_iter & 1;
         mbar_wait(&t_full[acc], (tile_iter >> 1) & 1);
@@ -288,6 +288,7 @@ GemmArgs make_gemm_args(const DeviceState& s, const ScanGeometry& g, int m, long
   a.spill_pool = b.spill_pool;
   a.spill_next = b.counters;
   a.spill_cap = s.spill_cap;
+  a.work_ctr = b.counters + 4;
   a.dump = dump;
   a.dump_ld = dump_ld;
   a.dump_row0 = dump_row0;

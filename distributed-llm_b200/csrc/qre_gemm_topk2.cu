@@ -108,6 +108,49 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
       : "memory");
 }
 
+
+// ---- work-unit queue (dynamic scheduling) ----
+// The pair's leader producer claims work units from a global counter and hands each id to every
+// role of both CTAs through a small ring in each CTA's shared memory: value store + release
+// arrive at cluster scope, the readers wait with acquire at cluster scope.  The ring is never
+// overrun without an "empty" barrier: a reader lags the claimer by at most the B ring (7 tiles),
+// two accumulators and two units in flight, and a unit is at least one tile (< kUQ).
+constexpr int kUQ = 16;
+__device__ __forceinline__ void uq_publish(uint64_t* bar, int* val, uint32_t k, int u) {
+  const uint32_t b = smem_u32(&bar[k % kUQ]), v = smem_u32(&val[k % kUQ]);
+#pragma unroll
+  for (uint32_t r = 0; r < 2; ++r)
+    asm volatile(
+        "{\n\t.reg .b32 ra, rb;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %2;\n\t"
+        "mapa.shared::cluster.u32 rb, %1, %2;\n\t"
+        "st.shared::cluster.u32 [ra], %3;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [rb];\n\t}"
+        :
+        : "r"(v), "r"(b), "r"(r), "r"(u)
+        : "memory");
+}
+__device__ __forceinline__ int uq_take(uint64_t* bar, const int* val, uint32_t k) {
+  const uint32_t b = smem_u32(&bar[k % kUQ]), parity = (k / kUQ) & 1u;
+  uint32_t spins = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(b), "r"(parity)
+        : "memory");
+    if (ok) break;
+    if (++spins > (1u << 26)) {
+      printf("qre: work-unit queue wait timed out (block %d thread %d k %u)\n", blockIdx.x, threadIdx.x, k);
+      __trap();
+    }
+  }
+  return *reinterpret_cast<const volatile int*>(&val[k % kUQ]);
+}
+
 }  // namespace
 
 template <bool kDump>
@@ -125,7 +168,9 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   uint64_t* a_empty = a_full + kMaxKB;         // [kMaxKB]
   uint64_t* t_full = a_empty + kMaxKB;         // [2]
   uint64_t* t_empty = t_full + 2;              // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  uint64_t* uq_full = t_empty + 2;              // [kUQ]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(uq_full + kUQ);
+  int* uq_val = reinterpret_cast<int*>(tmem_slot + 2);     // [kUQ]
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
@@ -150,6 +195,7 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       mbar_init(&t_full[i], 1);
       mbar_init(&t_empty[i], 256);
     }
+    for (int i = 0; i < kUQ; ++i) mbar_init(&uq_full[i], 1);
     fence_barrier_init();
   }
   cluster_sync_all();                          // barriers of both CTAs are initialised
@@ -170,12 +216,20 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   if (warp == 4) {
     // ================= TMA producer (one per CTA) =================
     if (lane == 0) {
-      uint32_t stage = 0, phase = 0, a_iter = 0;
-      for (int u = cluster_id; u < U; u += n_clusters) {
+      uint32_t stage = 0, phase = 0, a_iter = 0, k = 0;
+      int u = cluster_id;                      // the first unit is static, the rest are claimed
+      while (u < U) {
         const int s = u / npairs, pr = u - s * npairs;
         const int mb = 2 * pr + static_cast<int>(rank);
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        // The leader claims the pair's next unit a few tiles before this one ends (late, so that
+        // pairs which finish together sweep the same row range together; early enough for the
+        // atomic's latency to hide under one tile's loads and for the peer to see the id in time).
+        const int t_claim = t1 - 3 > t0 ? t1 - 3 : t0;
+        int u_next = U;
         for (int t = t0; t < t1; ++t) {
+          unsigned claimed = 0;
+          if (leader && t == t_claim) claimed = atomicAdd(a.work_ctr, 1u);
           for (int kb = 0; kb < a.num_kb; ++kb) {
             if (t == t0) {                     // this unit's query block, one k-block at a time
               mbar_wait(&a_empty[kb], (a_iter & 1) ^ 1);
@@ -190,8 +244,25 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                              t * kBN + static_cast<int>(rank) * kBHalfRows);
             if (++stage == kStages2) { stage = 0; phase ^= 1; }
           }
+          if (leader && t == t_claim) {
+            const unsigned long long nx = static_cast<unsigned long long>(n_clusters) + claimed;
+            u_next = nx < static_cast<unsigned long long>(U) ? static_cast<int>(nx) : U;
+            uq_publish(uq_full, uq_val, k + 1, u_next);
+          }
         }
         ++a_iter;
+        ++k;
+        u = leader ? u_next : uq_take(uq_full, uq_val, k);
+      }
+      if (leader) {
+        // every pair claims exactly once past the end; the last pair to do so re-arms the counters
+        // for the next launch on this batch slot
+        __threadfence();
+        if (atomicAdd(a.work_ctr + 1, 1u) == static_cast<unsigned>(n_clusters) - 1u) {
+          a.work_ctr[0] = 0u;
+          a.work_ctr[1] = 0u;
+          __threadfence();
+        }
       }
     }
   } else if (warp == 5) {
@@ -235,7 +306,9 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       };
       using T_ = std::true_type;
       using F_ = std::false_type;
-      for (int u = cluster_id; u < U; u += n_clusters) {
+      uint32_t k = 0;
+      int u = cluster_id;
+      while (u < U) {
         const int s = u / npairs;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
         if (t1 - t0 == 1) {
@@ -246,21 +319,24 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           issue_tile(F_{}, T_{});
         }
         ++a_iter;
+        ++k;
+        u = uq_take(uq_full, uq_val, k);
       }
     }
   } else {
     // ================= epilogue (both CTAs): fused per-query top-k =================
-    uint32_t tile_iter = 0;
+    uint32_t tile_iter = 0, k = 0;
     TopK tk;
-    for (int u = cluster_id; u < U; u += n_clusters) {
+    int u = cluster_id;
+    while (u < U) {
       const int s = u / npairs, pr = u - s * npairs;
       const int mb = 2 * pr + static_cast<int>(rank);
       const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
       const int q = mb * kBM + warp * 32 + lane;
       const bool active = q < a.m;
       const uint64_t myctx = active ? a.q_ctx[q] : 0ull;
-      topk_reset(tk, a.floor_v);
       float kth = active ? a.floor_v : __int_as_float(0x7f800000);
+      topk_reset(tk, a, static_cast<long long>(q) * a.splits + s, kth);
       for (int t = t0; t < t1; ++t) {
         const uint32_t acc = tile_iter & 1;
         mbar_wait(&t_full[acc], (tile_iter >> 1) & 1);
@@ -272,6 +348,8 @@ qre_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         ++tile_iter;
       }
       if (active) topk_store(tk, a, static_cast<long long>(q) * a.splits + s);
+      ++k;
+      u = uq_take(uq_full, uq_val, k);
     }
   }
 

@@ -218,6 +218,9 @@ struct RescoreArgs {
   const SpillChunk* spill_pool;
   const float* q_f32;
   const float* q_norm;
+  const uint64_t* q_ctx;
+  const RowMeta* meta;
+  long long now_us, ttl_us;
   const float* rows_f32;
   const float* row_norm;
   const uint64_t* lru;
@@ -284,52 +287,61 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) rescore_kernel(const Resc
     const PartialEntry* pe = a.partial + static_cast<long long>(q) * a.splits * kTopK;
     const uint32_t* heads = a.spill_head + static_cast<long long>(q) * a.splits;
     const int cnt = a.splits * kTopK;
-    // a* = best approximate score of any masked row: the head of some range's list (chained
-    // candidates are never better than the list they fell off)
-    float amax = -INFINITY;
-    for (int s = lane; s < a.splits; s += 32) {
-      const PartialEntry e = pe[s * kTopK];
-      if (e.row != kNoRow) amax = fmaxf(amax, e.v);
-      if (heads[s] == kChunkLost) ovf = true;          // the spill pool ran out inside this range
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(kFull, amax, o));
-    ovf = __any_sync(kFull, ovf);
-    if (amax != -INFINITY && !ovf) {
-      // The exact winner has approx >= amax - 2 eps; nothing under the floor can hit.
-      const float cut = fmaxf(amax - 2.f * kApproxEps, a.floor_v);
-      const float* qv = a.q_f32 + static_cast<long long>(q) * a.dim_pad;
+    const uint64_t myctx = a.q_ctx[q];
+    // The scan appended every score above its gate WITHOUT looking at the row (qre_scan_epilogue.cuh):
+    // the row mask (context, TTL: cache.py:274-276) is applied here, 32 candidates at a time.
+    auto valid = [&](const PartialEntry& e) {
+      if (e.row == kNoRow || !(e.v >= a.floor_v)) return false;
+      const RowMeta mt = a.meta[e.row];
+      return mt.ctx == myctx && (a.now_us - mt.ts_us) <= a.ttl_us;
+    };
+    // Both passes walk the same entries: the inline slots of every range, then the chains.
+    auto walk = [&](auto&& visit) {
       for (int base = 0; base < cnt; base += 32) {
         const int i = base + lane;
         PartialEntry e;
         e.v = 0.f;
         e.row = kNoRow;
         if (i < cnt) e = pe[i];
-        unsigned mask = __ballot_sync(kFull, e.row != kNoRow && e.v >= cut);
-        while (mask) {
-          const int src = __ffs(mask) - 1;
-          mask &= mask - 1;
-          rescore_one(a, L, qv, nq, __shfl_sync(kFull, e.row, src), lane);
-        }
+        visit(e);
       }
-      // candidates chained off full lists
       for (int s = 0; s < a.splits; ++s) {
         uint32_t c = heads[s];
-        while (c != kNoChunk) {
+        while (c != kNoChunk && c != kChunkLost) {
           const SpillChunk* ch = a.spill_pool + c;
           const uint32_t n = ch->n;
           PartialEntry e;
           e.v = 0.f;
           e.row = kNoRow;
           if (lane < static_cast<int>(n)) e = ch->e[lane];
-          unsigned mask = __ballot_sync(kFull, e.row != kNoRow && e.v >= cut);
+          visit(e);
+          c = ch->next;
+        }
+      }
+    };
+    for (int s = lane; s < a.splits; s += 32)
+      if (heads[s] == kChunkLost) ovf = true;            // the spill pool ran out inside this range
+    ovf = __any_sync(kFull, ovf);
+    if (!ovf) {
+      // pass 1: a* = best approximate score of any valid row that was appended
+      float amax = -INFINITY;
+      walk([&](const PartialEntry& e) {
+        if (valid(e)) amax = fmaxf(amax, e.v);
+      });
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(kFull, amax, o));
+      if (amax != -INFINITY) {
+        // pass 2: the exact winner has approx >= a* - 2 eps; nothing under the floor can hit
+        const float cut = fmaxf(amax - 2.f * kApproxEps, a.floor_v);
+        const float* qv = a.q_f32 + static_cast<long long>(q) * a.dim_pad;
+        walk([&](const PartialEntry& e) {
+          unsigned mask = __ballot_sync(kFull, e.v >= cut && valid(e));
           while (mask) {
             const int src = __ffs(mask) - 1;
             mask &= mask - 1;
             rescore_one(a, L, qv, nq, __shfl_sync(kFull, e.row, src), lane);
           }
-          c = ch->next;
-        }
+        });
       }
     }
   }
@@ -956,6 +968,7 @@ int launch_rescore(DeviceState& s, int m, long long n_rows, const qre_params_t& 
   a.thr = p.similarity_threshold;
   a.partial = b.partial; a.spill_head = b.spill_head; a.spill_pool = b.spill_pool;
   a.q_f32 = b.q_f32; a.q_norm = b.q_norm; a.rows_f32 = s.rows_f32;
+  a.q_ctx = b.q_ctx; a.meta = s.meta; a.now_us = p.now_us; a.ttl_us = p.ttl_us;
   a.row_norm = s.row_norm; a.lru = s.lru; a.pdev = s.pred_dev; a.pconf = s.pred_conf; a.cand = cand;
   a.q_flags = b.q_flags;
   a.ovf_count = b.ovf_count(); a.ovf_list = b.ovf_list;

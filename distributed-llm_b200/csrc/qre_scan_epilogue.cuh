@@ -6,15 +6,20 @@
 // and compares it with the query's current gate; only chunks that can still matter take the
 // candidate path (row mask + insertion).
 //
-// Gate.  The exact winner of a query has approx >= a* - 2 eps where a* is the
-// best approximate score over all masked rows; nothing under the hit floor can hit.  Within one
-// (query, row range) the thread keeps the 8 best approximate scores in a sorted list plus a
-// chain of spill chunks for candidates that do not fit but are still inside the window of the
-// running best.  A score is looked at iff
-//     v >= gate,   gate = min( list[7],  max(floor, list[0] - 2 eps) )
-// (while the list is not full list[7] is the floor).  Nothing with v >= final window is ever
-// dropped: it is in the list or in the chain, so the re-score pass is exact without a second
-// look at the rows, however many near-ties a range holds.
+// Candidate path.  The exact winner of a query has approx >= a* - 2 eps where a*
+// is the best approximate score over all VALID rows (same context, not expired); nothing under the
+// hit floor can hit.  The scan does not look at a row's (context, timestamp) itself: a global
+// load per candidate in the thread that also has to hand the accumulator back stalls the tile
+// pipeline of the whole CTA pair (measured: a cache of paraphrase clusters ran at half speed).
+// Instead every score >= gate is APPENDED, unvalidated, with plain stores: the first 8 of a
+// (query, row range) into its slots of `partial`, the rest into a chain of 128-byte spill chunks
+// (15 candidates + link) taken from a per-batch pool in groups of 1, 2, 4, 8, 8, ... chunks per
+// atomic.  The gate starts at the floor.  Only when a thread has to take a new group (>= 8
+// candidates in one range already) does it validate a SAMPLE — the inline slots the first time,
+// afterwards the chunk it has just filled — with independent loads under the atomic's latency,
+// and lifts the gate to max(floor, best valid sample - 2 eps).  A sample's best is <= a*, so
+// nothing with approx >= a* - 2 eps is ever dropped, however few rows were validated; the
+// re-score kernel applies the row mask to everything that was appended and takes a* from there.
 #pragma once
 #include "qre_common.cuh"
 #include "qre_ptx.cuh"
@@ -22,75 +27,105 @@
 namespace qre {
 
 struct TopK {              // per-thread candidate state; lives in local memory (rare path only)
-  float v[kTopK];
-  uint32_t r[kTopK];
-  uint32_t chunk;          // head of this (query, range)'s spill chain
+  PartialEntry* inl;       // this (query, range)'s kTopK inline slots in `partial`
+  uint32_t n_inl;          // inline slots used
+  uint32_t chunk;          // head of the spill chain: kNoChunk / kChunkLost / pool index
   uint32_t fill;           // entries used in the head chunk
+  uint32_t free_next;      // next unused chunk of the group reserved last
+  uint32_t free_left;      // chunks left in that group
+  uint32_t group;          // size of the next group to reserve
+  float gate;
 };
 
-__device__ __forceinline__ float gate_of(const TopK* tk, float floor_v) {
-  return fminf(tk->v[kTopK - 1], fmaxf(floor_v, tk->v[0] - 2.f * kApproxEps));
+constexpr uint32_t kSpillGroupMax = 8;
+
+__device__ __forceinline__ bool row_valid(const RowMeta* meta, uint32_t row, uint64_t myctx, long long now_us,
+                                          long long ttl_us) {
+  const int4 raw = __ldg(reinterpret_cast<const int4*>(meta + row));
+  const uint64_t ctx = (static_cast<uint64_t>(static_cast<uint32_t>(raw.y)) << 32) | static_cast<uint32_t>(raw.x);
+  const long long ts = static_cast<long long>((static_cast<uint64_t>(static_cast<uint32_t>(raw.w)) << 32) |
+                                              static_cast<uint32_t>(raw.z));
+  return ctx == myctx && (now_us - ts) <= ttl_us;     // src/cache.py:274-276, 523-524
 }
 
-// Chain one candidate.  A new chunk costs one atomic on the batch's bump counter.
-static __device__ __noinline__ void spill(TopK* tk, float v, uint32_t row, const GemmArgs* a) {
+// Best approximate score among the VALID entries of e[0..n) (n <= kSpillPer); -inf if none.
+// Entries were written by this thread (program order makes them visible to it).
+__device__ __forceinline__ float best_valid_of(const PartialEntry* e, uint32_t n, uint64_t myctx, const GemmArgs* a) {
+  PartialEntry c[kSpillPer];
+#pragma unroll
+  for (int i = 0; i < kSpillPer; ++i) {
+    c[i].row = kNoRow;
+    if (i < static_cast<int>(n)) c[i] = e[i];
+  }
+  bool ok[kSpillPer];
+#pragma unroll
+  for (int i = 0; i < kSpillPer; ++i)
+    ok[i] = c[i].row != kNoRow && row_valid(a->meta, c[i].row, myctx, a->now_us, a->ttl_us);
+  float best = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < kSpillPer; ++i)
+    if (ok[i]) best = fmaxf(best, c[i].v);
+  return best;
+}
+
+// Append one candidate (unvalidated).  Returns the gate.  Deliberately not inlined: the fast path
+// must stay tiny.
+static __device__ __noinline__ float consider(TopK* tk, float v, long long row, uint64_t myctx, const GemmArgs* a) {
+  if (row >= a->n_rows) return tk->gate;
+  const PartialEntry e{v, static_cast<uint32_t>(row)};
+  if (tk->n_inl < kTopK) {
+    tk->inl[tk->n_inl] = e;
+    ++tk->n_inl;
+    return tk->gate;
+  }
   uint32_t c = tk->chunk;
-  if (c == kChunkLost) return;
+  if (c == kChunkLost) return tk->gate;
   if (c == kNoChunk || tk->fill == kSpillPer) {
-    const uint32_t nc = atomicAdd(a->spill_next, 1u);
-    if (nc >= a->spill_cap) {          // pool exhausted: the re-score pass settles this query by brute force
-      tk->chunk = kChunkLost;
-      return;
+    if (tk->free_left == 0) {
+      // reserve the next group; validate a sample while the atomic is in flight
+      const uint32_t g = tk->group;
+      const uint32_t first = atomicAdd(a->spill_next, g);
+      const float bv = (c == kNoChunk) ? best_valid_of(tk->inl, kTopK, myctx, a)
+                                       : best_valid_of(a->spill_pool[c].e, kSpillPer, myctx, a);
+      tk->gate = fmaxf(tk->gate, bv - 2.f * kApproxEps);
+      if (first + g > a->spill_cap || first + g < first) {   // pool exhausted: the re-score pass settles this
+        tk->chunk = kChunkLost;                              // query by brute force
+        return tk->gate;
+      }
+      tk->free_next = first;
+      tk->free_left = g;
+      tk->group = g < kSpillGroupMax ? g * 2 : g;
+      if (v < tk->gate) return tk->gate;                     // the lifted gate already excludes this one
     }
+    const uint32_t nc = tk->free_next;
+    ++tk->free_next;
+    --tk->free_left;
     if (c != kNoChunk) a->spill_pool[c].n = kSpillPer;
     a->spill_pool[nc].next = c;
     tk->chunk = c = nc;
     tk->fill = 0;
   }
-  a->spill_pool[c].e[tk->fill] = PartialEntry{v, row};
+  a->spill_pool[c].e[tk->fill] = e;
   ++tk->fill;
+  return tk->gate;
 }
 
-// Candidate path: mask (row bound, context, TTL — src/cache.py:274-276) then insert or chain.
-// Returns the new gate.  Deliberately not inlined: the fast path must stay tiny.
-static __device__ __noinline__ float consider(TopK* tk, float v, long long row, uint64_t myctx, const GemmArgs* a) {
-  const float floor_v = a->floor_v;
-  if (row >= a->n_rows) return gate_of(tk, floor_v);
-  const int4 raw = __ldg(reinterpret_cast<const int4*>(a->meta + row));
-  const uint64_t ctx = (static_cast<uint64_t>(static_cast<uint32_t>(raw.y)) << 32) | static_cast<uint32_t>(raw.x);
-  const long long ts = static_cast<long long>((static_cast<uint64_t>(static_cast<uint32_t>(raw.w)) << 32) |
-                                              static_cast<uint32_t>(raw.z));
-  if (ctx != myctx || (a->now_us - ts) > a->ttl_us) return gate_of(tk, floor_v);
-  if (v > tk->v[kTopK - 1]) {
-    const float ev = tk->v[kTopK - 1];
-    const uint32_t er = tk->r[kTopK - 1];
-    int i = kTopK - 1;
-    while (i > 0 && v > tk->v[i - 1]) {      // strict: equal scores keep the earlier row first
-      tk->v[i] = tk->v[i - 1];
-      tk->r[i] = tk->r[i - 1];
-      --i;
-    }
-    tk->v[i] = v;
-    tk->r[i] = static_cast<uint32_t>(row);
-    // the entry pushed off the list stays a contender while it is inside the window of the best
-    if (er != kNoRow && ev >= fmaxf(floor_v, tk->v[0] - 2.f * kApproxEps)) spill(tk, ev, er, a);
-  } else if (v >= fmaxf(floor_v, tk->v[0] - 2.f * kApproxEps)) {
-    spill(tk, v, static_cast<uint32_t>(row), a);
-  }
-  return gate_of(tk, floor_v);
-}
-
-__device__ __forceinline__ void topk_reset(TopK& tk, float floor_v) {
-#pragma unroll
-  for (int i = 0; i < kTopK; ++i) { tk.v[i] = floor_v; tk.r[i] = kNoRow; }
+__device__ __forceinline__ void topk_reset(TopK& tk, const GemmArgs& a, long long unit, float gate0) {
+  tk.inl = a.partial + unit * kTopK;
+  tk.n_inl = 0;
   tk.chunk = kNoChunk;
   tk.fill = 0;
+  tk.free_left = 0;
+  tk.group = 1;
+  tk.gate = gate0;
 }
 
+// End of a (query, range): mark the unused inline slots empty and publish the chain head.
 __device__ __forceinline__ void topk_store(const TopK& tk, const GemmArgs& a, long long unit) {
   PartialEntry* out = a.partial + unit * kTopK;
 #pragma unroll
-  for (int i = 0; i < kTopK; ++i) out[i] = PartialEntry{tk.v[i], tk.r[i]};
+  for (int i = 0; i < kTopK; ++i)
+    if (i >= static_cast<int>(tk.n_inl)) out[i] = PartialEntry{0.f, kNoRow};
   const uint32_t c = tk.chunk;
   if (c != kNoChunk && c != kChunkLost) a.spill_pool[c].n = tk.fill;
   a.spill_head[unit] = c;
@@ -117,19 +152,25 @@ __device__ __forceinline__ float scan_tile(uint32_t taddr, long long row_base, i
         }
       }
     }
-    float m0 = fmaxf(v[0], v[1]), m1 = fmaxf(v[2], v[3]), m2 = fmaxf(v[4], v[5]), m3 = fmaxf(v[6], v[7]);
+    // maxima of the 8 groups of 8 consecutive scores (3-input FMNMX), then of the chunk: a chunk
+    // that holds a candidate costs 8 group tests plus 8 score tests per group that has one,
+    // instead of 64 score tests for the whole warp
+    float g[8];
 #pragma unroll
-    for (int i = 8; i < 64; i += 8) {
-      m0 = fmaxf(m0, fmaxf(v[i], v[i + 1]));
-      m1 = fmaxf(m1, fmaxf(v[i + 2], v[i + 3]));
-      m2 = fmaxf(m2, fmaxf(v[i + 4], v[i + 5]));
-      m3 = fmaxf(m3, fmaxf(v[i + 6], v[i + 7]));
+    for (int j = 0; j < 8; ++j) {
+      const float* w = v + 8 * j;
+      g[j] = fmaxf(fmaxf(fmaxf(fmaxf(w[0], w[1]), w[2]), fmaxf(fmaxf(w[3], w[4]), w[5])), fmaxf(w[6], w[7]));
     }
-    const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+    const float mx = fmaxf(fmaxf(fmaxf(fmaxf(g[0], g[1]), g[2]), fmaxf(fmaxf(g[3], g[4]), g[5])), fmaxf(g[6], g[7]));
     if (mx >= gate) {
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        if (v[i] >= gate) gate = consider(&tk, v[i], row_base + c * 64 + i, myctx, &a);
+      for (int j = 0; j < 8; ++j) {
+        if (g[j] >= gate) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (v[8 * j + i] >= gate) gate = consider(&tk, v[8 * j + i], row_base + c * 64 + 8 * j + i, myctx, &a);
+          }
+        }
       }
     }
   }
