@@ -176,25 +176,26 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
     // ================= epilogue: fused per-query top-k =================
     uint32_t tile_iter = 0;
     TopK tk;
+    Cursor cu;
     for (int u = blockIdx.x; u < U; u += gridDim.x) {
       const int s = u / a.mblocks, mb = u - s * a.mblocks;
       const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
       const int q = mb * kBM + warp * 32 + lane;
       const bool active = q < a.m;
       const uint64_t myctx = active ? a.q_ctx[q] : 0ull;
-      float kth = active ? a.floor_v : __int_as_float(0x7f800000);
-      topk_reset(tk, a, static_cast<long long>(q) * a.splits + s, kth);
+      const float kth = active ? a.floor_v : __int_as_float(0x7f800000);
+      topk_reset(cu, tk, a, static_cast<long long>(q) * a.splits + s, kth);
       for (int t = t0; t < t1; ++t) {
         const uint32_t acc = tile_iter & 1;
         mbar_wait(&t_full[acc], (tile_iter >> 1) & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + acc * kBN;
-        kth = scan_tile<kDump>(taddr, static_cast<long long>(t) * kBN, q, active, kth, tk, myctx, a);
+        scan_tile<kDump>(taddr, static_cast<long long>(t) * kBN, q, active, cu, tk, myctx, a);
         tc_fence_before();
         mbar_arrive(&t_empty[acc]);
         ++tile_iter;
       }
-      if (active) topk_store(tk, a, static_cast<long long>(q) * a.splits + s);
+      if (active) topk_store(cu, tk, a, static_cast<long long>(q) * a.splits + s);
     }
   }
 

@@ -4,7 +4,7 @@
 // One epilogue thread owns one query (one TMEM lane).  Per 256-column accumulator tile it reads
 // 4 chunks of 64 scores with tcgen05.ld, reduces each chunk to its maximum with 3-input FMNMX
 // and compares it with the query's current gate; only chunks that can still matter take the
-// candidate path (row mask + insertion).
+// candidate path (append to the (query, range)'s list).
 //
 // Candidate path.  The exact winner of a query has approx >= a* - 2 eps where a*
 // is the best approximate score over all VALID rows (same context, not expired); nothing under the
@@ -26,15 +26,19 @@
 
 namespace qre {
 
-struct TopK {              // per-thread candidate state; lives in local memory (rare path only)
+// Append cursor of one (query, row range): lives in the epilogue thread's registers.
+struct Cursor {
+  PartialEntry* nxt;       // where the next candidate goes
+  uint32_t room;           // entries left at nxt (inline slots first, then the head spill chunk)
+  float gate;
+};
+
+struct TopK {              // the rest of the per-thread candidate state; local memory, touched only at chunk boundaries
   PartialEntry* inl;       // this (query, range)'s kTopK inline slots in `partial`
-  uint32_t n_inl;          // inline slots used
   uint32_t chunk;          // head of the spill chain: kNoChunk / kChunkLost / pool index
-  uint32_t fill;           // entries used in the head chunk
   uint32_t free_next;      // next unused chunk of the group reserved last
   uint32_t free_left;      // chunks left in that group
   uint32_t group;          // size of the next group to reserve
-  float gate;
 };
 
 constexpr uint32_t kSpillGroupMax = 8;
@@ -68,74 +72,84 @@ __device__ __forceinline__ float best_valid_of(const PartialEntry* e, uint32_t n
   return best;
 }
 
-// Append one candidate (unvalidated).  Returns the gate.  Deliberately not inlined: the fast path
-// must stay tiny.
-static __device__ __noinline__ float consider(TopK* tk, float v, long long row, uint64_t myctx, const GemmArgs* a) {
-  if (row >= a->n_rows) return tk->gate;
-  const PartialEntry e{v, static_cast<uint32_t>(row)};
-  if (tk->n_inl < kTopK) {
-    tk->inl[tk->n_inl] = e;
-    ++tk->n_inl;
-    return tk->gate;
-  }
+// The cursor ran out of room (inline slots or the head chunk are full) and candidate (v, row)
+// is waiting: link a new head chunk — reserving the next group of chunks and validating a sample
+// when the last group is used up — store the candidate there and return the new cursor.
+// Deliberately not inlined: the fast path must stay tiny.
+static __device__ __noinline__ Cursor refill(TopK* tk, float gate, float v, uint32_t row, uint64_t myctx,
+                                             const GemmArgs* a) {
   uint32_t c = tk->chunk;
-  if (c == kChunkLost) return tk->gate;
-  if (c == kNoChunk || tk->fill == kSpillPer) {
-    if (tk->free_left == 0) {
-      // reserve the next group; validate a sample while the atomic is in flight
-      const uint32_t g = tk->group;
-      const uint32_t first = atomicAdd(a->spill_next, g);
-      const float bv = (c == kNoChunk) ? best_valid_of(tk->inl, kTopK, myctx, a)
-                                       : best_valid_of(a->spill_pool[c].e, kSpillPer, myctx, a);
-      tk->gate = fmaxf(tk->gate, bv - 2.f * kApproxEps);
-      if (first + g > a->spill_cap || first + g < first) {   // pool exhausted: the re-score pass settles this
-        tk->chunk = kChunkLost;                              // query by brute force
-        return tk->gate;
-      }
-      tk->free_next = first;
-      tk->free_left = g;
-      tk->group = g < kSpillGroupMax ? g * 2 : g;
-      if (v < tk->gate) return tk->gate;                     // the lifted gate already excludes this one
+  if (c == kChunkLost) return Cursor{nullptr, 0u, gate};
+  if (tk->free_left == 0) {
+    // reserve the next group; validate a sample while the atomic is in flight
+    const uint32_t g = tk->group;
+    const uint32_t first = atomicAdd(a->spill_next, g);
+    const float bv = (c == kNoChunk) ? best_valid_of(tk->inl, kTopK, myctx, a)
+                                     : best_valid_of(a->spill_pool[c].e, kSpillPer, myctx, a);
+    gate = fmaxf(gate, bv - 2.f * kApproxEps);
+    if (first + g > a->spill_cap || first + g < first) {   // pool exhausted: the re-score pass settles this
+      if (c != kNoChunk) a->spill_pool[c].n = kSpillPer;   // query by brute force
+      tk->chunk = kChunkLost;
+      return Cursor{nullptr, 0u, gate};
     }
-    const uint32_t nc = tk->free_next;
-    ++tk->free_next;
-    --tk->free_left;
-    if (c != kNoChunk) a->spill_pool[c].n = kSpillPer;
-    a->spill_pool[nc].next = c;
-    tk->chunk = c = nc;
-    tk->fill = 0;
+    tk->free_next = first;
+    tk->free_left = g;
+    tk->group = g < kSpillGroupMax ? g * 2 : g;
   }
-  a->spill_pool[c].e[tk->fill] = e;
-  ++tk->fill;
-  return tk->gate;
+  const uint32_t nc = tk->free_next;
+  ++tk->free_next;
+  --tk->free_left;
+  if (c != kNoChunk) a->spill_pool[c].n = kSpillPer;
+  SpillChunk* ch = a->spill_pool + nc;
+  ch->next = c;
+  tk->chunk = nc;
+  if (v >= gate) {                                         // (the lifted gate may already exclude it)
+    ch->e[0] = PartialEntry{v, row};
+    return Cursor{ch->e + 1, kSpillPer - 1, gate};
+  }
+  return Cursor{ch->e, kSpillPer, gate};
 }
 
-__device__ __forceinline__ void topk_reset(TopK& tk, const GemmArgs& a, long long unit, float gate0) {
+// One score that passed the gate: append it (registers + one store), or take the slow call.
+__device__ __forceinline__ void consider(Cursor& cu, TopK& tk, float v, long long row, uint64_t myctx,
+                                         const GemmArgs& a) {
+  if (row >= a.n_rows) return;
+  if (cu.room != 0) {
+    *cu.nxt = PartialEntry{v, static_cast<uint32_t>(row)};
+    ++cu.nxt;
+    --cu.room;
+  } else {
+    cu = refill(&tk, cu.gate, v, static_cast<uint32_t>(row), myctx, &a);
+  }
+}
+
+__device__ __forceinline__ void topk_reset(Cursor& cu, TopK& tk, const GemmArgs& a, long long unit, float gate0) {
   tk.inl = a.partial + unit * kTopK;
-  tk.n_inl = 0;
   tk.chunk = kNoChunk;
-  tk.fill = 0;
   tk.free_left = 0;
   tk.group = 1;
-  tk.gate = gate0;
+  cu.nxt = tk.inl;
+  cu.room = kTopK;
+  cu.gate = gate0;
 }
 
 // End of a (query, range): mark the unused inline slots empty and publish the chain head.
-__device__ __forceinline__ void topk_store(const TopK& tk, const GemmArgs& a, long long unit) {
+__device__ __forceinline__ void topk_store(const Cursor& cu, const TopK& tk, const GemmArgs& a, long long unit) {
+  const uint32_t c = tk.chunk;
+  const uint32_t n_inl = c == kNoChunk ? kTopK - cu.room : kTopK;
   PartialEntry* out = a.partial + unit * kTopK;
 #pragma unroll
   for (int i = 0; i < kTopK; ++i)
-    if (i >= static_cast<int>(tk.n_inl)) out[i] = PartialEntry{0.f, kNoRow};
-  const uint32_t c = tk.chunk;
-  if (c != kNoChunk && c != kChunkLost) a.spill_pool[c].n = tk.fill;
+    if (i >= static_cast<int>(n_inl)) out[i] = PartialEntry{0.f, kNoRow};
+  if (c != kNoChunk && c != kChunkLost) a.spill_pool[c].n = kSpillPer - cu.room;
   a.spill_head[unit] = c;
 }
 
-// Scan one accumulator tile (this thread's lane, kBN columns starting at `taddr`); returns the
-// updated gate.  kDump additionally writes the raw scores out (bring-up / tests).
+// Scan one accumulator tile (this thread's lane, kBN columns starting at `taddr`); the append
+// cursor is updated in place.  kDump additionally writes the raw scores out (bring-up / tests).
 template <bool kDump>
-__device__ __forceinline__ float scan_tile(uint32_t taddr, long long row_base, int q, bool active, float gate,
-                                           TopK& tk, uint64_t myctx, const GemmArgs& a) {
+__device__ __forceinline__ void scan_tile(uint32_t taddr, long long row_base, int q, bool active, Cursor& cu,
+                                          TopK& tk, uint64_t myctx, const GemmArgs& a) {
 #pragma unroll 1
   for (int c = 0; c < kBN / 64; ++c) {
     float v[64];
@@ -162,19 +176,18 @@ __device__ __forceinline__ float scan_tile(uint32_t taddr, long long row_base, i
       g[j] = fmaxf(fmaxf(fmaxf(fmaxf(w[0], w[1]), w[2]), fmaxf(fmaxf(w[3], w[4]), w[5])), fmaxf(w[6], w[7]));
     }
     const float mx = fmaxf(fmaxf(fmaxf(fmaxf(g[0], g[1]), g[2]), fmaxf(fmaxf(g[3], g[4]), g[5])), fmaxf(g[6], g[7]));
-    if (mx >= gate) {
+    if (mx >= cu.gate) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        if (g[j] >= gate) {
+        if (g[j] >= cu.gate) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            if (v[8 * j + i] >= gate) gate = consider(&tk, v[8 * j + i], row_base + c * 64 + 8 * j + i, myctx, &a);
+            if (v[8 * j + i] >= cu.gate) consider(cu, tk, v[8 * j + i], row_base + c * 64 + 8 * j + i, myctx, a);
           }
         }
       }
     }
   }
-  return gate;
 }
 
 }  // namespace qre
