@@ -36,9 +36,22 @@ constexpr int kABytesPerKB = kBM * kBK * 2;         // 16 KB
 constexpr int kBBytes = kBN * kBK * 2;              // 32 KB
 constexpr int kSmemA = kMaxKB * kABytesPerKB;       // 96 KB
 constexpr int kSmemB = kStages * kBBytes;           // 128 KB
-constexpr int kSmemBar = 256;
+constexpr int kSmemBar = 512;
 constexpr int kSmemTotal = kSmemA + kSmemB + kSmemBar + 1024;   // + alignment slack
 constexpr uint32_t kTmemCols = 512;
+
+// Work units are claimed dynamically (see qre_gemm_topk2.cu): the producer thread takes the next
+// id from a global counter and hands it to the MMA and epilogue warps through a ring in shared
+// memory.  A reader lags the claimer by at most the B ring, two accumulators and two units in flight.
+constexpr int kUQ1 = 16;
+__device__ __forceinline__ void uq1_publish(uint64_t* bar, int* val, uint32_t k, int u) {
+  *reinterpret_cast<volatile int*>(&val[k % kUQ1]) = u;
+  mbar_arrive(&bar[k % kUQ1]);                      // release at CTA scope orders the store above
+}
+__device__ __forceinline__ int uq1_take(uint64_t* bar, const int* val, uint32_t k) {
+  mbar_wait(&bar[k % kUQ1], (k / kUQ1) & 1u);
+  return *reinterpret_cast<const volatile int*>(&val[k % kUQ1]);
+}
 
 // kResident: the 128-query A block fits in shared memory next to the B ring (dim_pad <= 384)
 // and is loaded once per work unit.  Otherwise (dim_pad up to 1024, e.g. 768-d embeddings) each
@@ -60,7 +73,9 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   uint64_t* a_empty = a_full + kMaxKB;      // [kMaxKB] MMA -> TMA (last MMA of the unit reading A[kb] retired)
   uint64_t* t_full = a_empty + kMaxKB;      // [2] MMA -> epilogue
   uint64_t* t_empty = t_full + 2;           // [2] epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  uint64_t* uq_full = t_empty + 2;          // [kUQ1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(uq_full + kUQ1);
+  int* uq_val = reinterpret_cast<int*>(tmem_slot + 2);     // [kUQ1]
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
@@ -69,6 +84,7 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
     tma_prefetch_desc(&tmap_e);
+    for (int i = 0; i < kUQ1; ++i) mbar_init(&uq_full[i], 1);
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
@@ -99,11 +115,16 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   if (warp == 4) {
     // ================= TMA producer =================
     if (lane == 0) {
-      uint32_t stage = 0, phase = 0, a_iter = 0;
-      for (int u = blockIdx.x; u < U; u += gridDim.x) {
+      uint32_t stage = 0, phase = 0, a_iter = 0, k = 0;
+      int u = blockIdx.x;                        // the first unit is static, the rest are claimed
+      while (u < U) {
         const int s = u / a.mblocks, mb = u - s * a.mblocks;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
+        const int t_claim = t1 - 3 > t0 ? t1 - 3 : t0;
+        int u_next = U;
         for (int t = t0; t < t1; ++t) {
+          unsigned claimed = 0;
+          if (t == t_claim) claimed = atomicAdd(a.work_ctr, 1u);
           for (int kb = 0; kb < a.num_kb; ++kb) {
             if (kResident && t == t0) {        // this unit's query block, handed over per k-block
               mbar_wait(&a_empty[kb], (a_iter & 1) ^ 1);
@@ -116,8 +137,22 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
             tma_load_2d(sB + stage * kStageBytes, &tmap_e, &full[stage], kb * kBK, t * kBN);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
+          if (t == t_claim) {
+            const unsigned long long nx = static_cast<unsigned long long>(gridDim.x) + claimed;
+            u_next = nx < static_cast<unsigned long long>(U) ? static_cast<int>(nx) : U;
+            uq1_publish(uq_full, uq_val, k + 1, u_next);
+          }
         }
         ++a_iter;
+        ++k;
+        u = u_next;
+      }
+      // every CTA claims exactly once past the end; the last one re-arms the counters
+      __threadfence();
+      if (atomicAdd(a.work_ctr + 1, 1u) == gridDim.x - 1u) {
+        a.work_ctr[0] = 0u;
+        a.work_ctr[1] = 0u;
+        __threadfence();
       }
     }
   } else if (warp == 5) {
@@ -159,7 +194,9 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       };
       using T_ = std::true_type;
       using F_ = std::false_type;
-      for (int u = blockIdx.x; u < U; u += gridDim.x) {
+      uint32_t k = 0;
+      int u = blockIdx.x;
+      while (u < U) {
         const int s = u / a.mblocks;
         const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
         if (t1 - t0 == 1) {
@@ -170,14 +207,17 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
           issue_tile(F_{}, T_{});
         }
         ++a_iter;
+        ++k;
+        u = uq1_take(uq_full, uq_val, k);
       }
     }
   } else {
     // ================= epilogue: fused per-query top-k =================
-    uint32_t tile_iter = 0;
+    uint32_t tile_iter = 0, k = 0;
     TopK tk;
     Cursor cu;
-    for (int u = blockIdx.x; u < U; u += gridDim.x) {
+    int u = blockIdx.x;
+    while (u < U) {
       const int s = u / a.mblocks, mb = u - s * a.mblocks;
       const int t0 = static_cast<int>((T * s) / a.splits), t1 = static_cast<int>((T * (s + 1)) / a.splits);
       const int q = mb * kBM + warp * 32 + lane;
@@ -196,6 +236,8 @@ qre_gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         ++tile_iter;
       }
       if (active) topk_store(cu, tk, a, static_cast<long long>(q) * a.splits + s);
+      ++k;
+      u = uq1_take(uq_full, uq_val, k);
     }
   }
 
