@@ -20,6 +20,7 @@ needs the device raises `qre_b200._cabi.QreError`.
 """
 from __future__ import annotations
 
+import gc
 import hashlib
 import heapq
 import json
@@ -31,7 +32,7 @@ from collections import OrderedDict
 from dataclasses import dataclass, field
 from datetime import datetime, timedelta
 from pathlib import Path
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -54,6 +55,37 @@ logger = logging.getLogger(__name__)
 PREDICTION_CONFIDENCE_THRESHOLD = 0.60      # reference cache.py:42
 RECENCY_DECAY = 0.85                        # reference cache.py:46
 DEVICE_NAMES: List[str] = ["nano", "orin"]  # index = device id on the GPU side
+
+@contextlib.contextmanager
+def _gc_paused():
+    """The batch entry points create a few thousand small acyclic objects per call; a cyclic
+    collection that happens to start in the middle walks the whole store (every entry, record and
+    list of a large cache) and costs more than the batch.  Collection is switched back on — if it
+    was on — when the batch is done."""
+    was = gc.isenabled()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if was:
+            gc.enable()
+
+
+class _KeyBlock:
+    """Payload of ONE expiry-heap record standing for many entries stamped at the same instant (a
+    batch insert).  Never ordered before or after anything: heap ties between it and a plain key are
+    left as they are."""
+    __slots__ = ("keys",)
+
+    def __init__(self, keys: List[str]):
+        self.keys = keys
+
+    def __lt__(self, other):
+        return False
+
+    def __gt__(self, other):
+        return False
+
 
 _EPOCH = datetime(1970, 1, 1)
 _ONE_US = timedelta(microseconds=1)
@@ -319,9 +351,10 @@ class QueryCache:
         limit = now_us - self._ttl_us()
         while self._exp_heap and self._exp_heap[0][0] < limit:
             ts, key = heapq.heappop(self._exp_heap)
-            e = self._store.get(key)
-            if e is not None and _to_us(e.timestamp) == ts:
-                heapq.heappush(self._stale_heap, (e._seq, key, ts))
+            for k in (key.keys if type(key) is _KeyBlock else (key,)):
+                e = self._store.get(k)
+                if e is not None and _to_us(e.timestamp) == ts:
+                    heapq.heappush(self._stale_heap, (e._seq, k, ts))
 
     def _pop_stale(self, now_us: int) -> Optional[str]:
         """Earliest-in-LRU-order entry that is expired right now, or None."""
@@ -435,7 +468,8 @@ class QueryCache:
         return self._batch_pass(queries, context_keys, q_embs, None, None)[0]
 
     def _batch_pass(self, queries: List[str], context_keys: List[str], q_embs: np.ndarray,
-                    route_in: Optional[dict], route_cfg: Optional[_cabi.RouteConfig]):
+                    route_in: Optional[dict], route_cfg: Optional[_cabi.RouteConfig],
+                    keys: Optional[List[Optional[str]]] = None):
         """Snapshot lookup of a whole batch (+ routing epilogue when `route_in` is given) in one
         device pass per `max_batch` chunk.  Returns (results, device outputs)."""
         with self._lock:
@@ -454,7 +488,12 @@ class QueryCache:
                 outs.append(self._engine.scan(q_embs[sl], ctx[sl], _to_us(now), cfg, ri))
             out = {k: np.concatenate([o[k] for o in outs]) for k in outs[0]} if outs else {}
             results: List[Optional[CacheLookupResult]] = []
-            self._batch_keys = [self._make_hash(q, c) for q, c in zip(queries, context_keys)]   # one md5 per query
+            if keys is None:                         # one md5 per query (or handed in by the C++ feature pass)
+                keys = [self._make_hash(q, c) for q, c in zip(queries, context_keys)]
+            else:
+                keys = [k if k is not None else self._make_hash(q, c)
+                        for k, q, c in zip(keys, queries, context_keys)]
+            self._batch_keys = keys
             with self._deferred():
                 self._apply_batch_hits(queries, context_keys, out, now, results)
             return results, out
@@ -464,27 +503,46 @@ class QueryCache:
         scan's row), as `lookup` does for one query."""
         keys = self._batch_keys
         slots = out["hit_slot"].tolist() if self.use_semantic else [-1] * len(queries)
-        for i, (q, c) in enumerate(zip(queries, context_keys)):
-            self._attempts += 1
-            entry = self._store.get(keys[i])
-            if entry is None or entry.context_key != c or not self._is_valid(entry, now):
+        store, slot_key = self._store, self._slot_key
+        ttl = self.ttl_seconds
+        thr = self.prediction_confidence_threshold
+        lru = self._defer["lru"] if self._defer is not None else None
+        move, append, new_obj = store.move_to_end, results.append, object.__new__
+        self._attempts += len(queries)
+        for i, c in enumerate(context_keys):
+            entry = store.get(keys[i])
+            if entry is None or entry.context_key != c or (now - entry.timestamp).total_seconds() > ttl:
                 entry = None
                 slot = slots[i]
                 if slot >= 0:
-                    entry = self._store.get(self._slot_key.get(slot, ""))
-                    if entry is not None and not self._is_valid(entry, now):
+                    entry = store.get(slot_key.get(slot, ""))
+                    if entry is not None and (now - entry.timestamp).total_seconds() > ttl:
                         entry = None
             if entry is None:
-                results.append(None)
+                append(None)
                 continue
             entry.hit_count += 1
-            self._touch(entry.query_hash, entry)
-            self._bump_lru(entry)
+            move(entry.query_hash)                     # _touch: LRU order on the host ...
+            self._seq = entry._seq = self._seq + 1
+            if entry._slot is not None:                # ... and the matching lru_seq on the device row
+                if lru is not None:
+                    lru[entry._slot] = entry._seq
+                else:
+                    self._engine.update(entry._slot, lru=entry._seq)
             self._hits += 1
-            pdev, pconf = entry.predict_device()
-            fb = pconf < self.prediction_confidence_threshold
-            self._hybrid_fallbacks += int(fb)
-            results.append(CacheLookupResult(entry, pdev, pconf, fb))
+            memo = entry._pred                           # predict_device(), memo check inlined
+            h = entry.routing_history
+            if memo is not None and memo[0] == len(h) and (not h or memo[1] is h[-1]) and memo[2] == entry.device_used:
+                pdev, pconf = memo[3]
+            else:
+                pdev, pconf = entry.predict_device()
+            fb = pconf < thr
+            if fb:
+                self._hybrid_fallbacks += 1
+            r = new_obj(CacheLookupResult)
+            r.__dict__ = {"entry": entry, "predicted_device": pdev, "predicted_confidence": pconf,
+                          "use_hybrid_fallback": fb}
+            append(r)
 
     def insert(self, query: str, context_key: str, device: str, confidence: float = 1.0,
                method: str = "unknown", q_emb: Optional[np.ndarray] = None,
@@ -515,6 +573,92 @@ class QueryCache:
             self._stamp(key, entry, now)
             self._touch(key, entry)
             self._sync_row(entry, row_changed=True)
+
+    def insert_batch(self, queries: Sequence[str], context_keys: Sequence[str], devices: Sequence[str],
+                     confidences: Sequence[float], method: str = "unknown",
+                     q_embs: Optional[np.ndarray] = None, *, _keys: Optional[List[str]] = None) -> None:
+        """Additive batch form of `insert` (the reference inserts one entry per call,
+        cache.py:328): the same entries, in the same order, as a loop of `insert`, with the host
+        bookkeeping of brand-new entries done without per-entry device calls or per-entry array
+        copies — one copy of the embedding block (entries hold row views of it), one timestamp for
+        the whole batch, one `append` to the device for all new rows.  Keys that already exist,
+        entries that need an eviction first and NaN confidences take `insert` itself."""
+        n = len(queries)
+        if n == 0:
+            return
+        keys = _keys if _keys is not None else [self._make_hash(q, c) for q, c in zip(queries, context_keys)]
+        with self._lock, self._deferred():
+            emb = None if q_embs is None else np.array(q_embs, dtype=np.float32, copy=True)
+            if emb is None or emb.ndim != 2:
+                for i in range(n):
+                    self.insert(queries[i], context_keys[i], devices[i], confidences[i], method,
+                                None if emb is None else emb[i], _key=keys[i])
+                return
+            now = datetime.now()
+            ts_us, iso = _to_us(now), now.isoformat()
+            store = self._store
+            new_obj = object.__new__
+            ent: List[CacheEntry] = []               # entries created here, in order
+            pos: Optional[List[int]] = None          # their batch indices, once some item went the slow way
+            room = self.max_size - len(store)
+            seq = self._seq
+            for i in range(n):
+                key, conf, dev = keys[i], confidences[i], devices[i]
+                if key in store or room <= 0 or conf != conf:
+                    if pos is None:
+                        pos = list(range(i))
+                    self._seq = seq
+                    self.insert(queries[i], context_keys[i], dev, conf, method, emb[i], _key=key)
+                    seq = self._seq
+                    room = self.max_size - len(store)
+                    continue
+                room -= 1
+                seq += 1
+                rec = new_obj(RoutingRecord)
+                rec.__dict__ = {"device": dev, "confidence": conf, "method": method, "timestamp": iso}
+                # (response_time, hit_count, _slot keep their class defaults; with one record the
+                # recency vote is (device, 1.0), or (device, 0.5) without weight)
+                e = new_obj(CacheEntry)
+                e.__dict__ = {"query": queries[i], "query_hash": key, "context_key": context_keys[i],
+                              "embedding": emb[i], "timestamp": now, "device_used": dev, "routing_history": [rec],
+                              "_seq": seq, "_pred": (1, rec, dev, (dev, 1.0 if conf >= 1e-9 else 0.5))}
+                store[key] = e
+                ent.append(e)
+                if pos is not None:
+                    pos.append(i)
+            self._seq = seq
+            if ent:                                  # one expiry record for the lot (same timestamp)
+                heapq.heappush(self._exp_heap, (ts_us, _KeyBlock([e.query_hash for e in ent])))
+            if pos is not None:
+                # (an entry evicted again later in this same batch has lost its embedding: no row for it)
+                keep = [j for j, e in enumerate(ent) if e.embedding is not None and e._slot is None]
+                ent, pos = [ent[j] for j in keep], [pos[j] for j in keep]
+            if not ent:
+                return
+            d = self._defer
+            if d is not None and d["tomb"]:              # free the device slots of this batch's evictions first
+                self._engine.tombstone(d["tomb"])
+                d["tomb"] = []
+            rows = emb if pos is None else emb[pos]
+            ctx_of = {ck: self._ctx_id(ck) for ck in dict.fromkeys(e.context_key for e in ent)}   # first-seen order
+            dev_of = {dv: device_index(dv) for dv in set(devices)}
+            m = len(ent)
+            if pos is None:
+                ctx = [ctx_of[ck] for ck in context_keys]
+                pdev = [dev_of[dv] for dv in devices]
+                pconf = np.where(np.asarray(confidences, np.float64) >= 1e-9, 1.0, 0.5)
+                lru = np.arange(seq - m + 1, seq + 1, dtype=np.uint64)
+            else:
+                pred = [e.predict_device() for e in ent]     # (a later item of the batch may have refreshed one)
+                ctx = [ctx_of[e.context_key] for e in ent]
+                pdev = [device_index(p[0]) for p in pred]
+                pconf = [p[1] for p in pred]
+                lru = [e._seq for e in ent]
+            slots = self._engine.append_many(rows, ctx, np.full(m, ts_us, np.int64), lru, pdev, pconf)
+            slot_key = self._slot_key
+            for e, sl in zip(ent, slots.tolist() if hasattr(slots, "tolist") else slots):
+                e._slot = sl
+                slot_key[sl] = e.query_hash
 
     def invalidate(self, context_key: Optional[str] = None, query_pattern: Optional[str] = None) -> int:
         """Remove entries by context and/or case-insensitive regex on the query text; neither

@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <string>
+#include <cmath>
 #include <thread>
 #include <utility>
 #include <vector>
@@ -31,6 +32,17 @@ inline bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
 struct View {
   const char* p;
   int n;
+  uint64_t has[4] = {0, 0, 0, 0};                // which byte values occur (prefilter for the literal search)
+  void index() {
+    for (int i = 0; i < n; ++i) {
+      const unsigned char c = static_cast<unsigned char>(p[i]);
+      has[c >> 6] |= 1ull << (c & 63);
+    }
+  }
+  bool may_contain(const std::string& lit) const {   // every literal here is non-empty
+    const unsigned char a = static_cast<unsigned char>(lit[0]), b = static_cast<unsigned char>(lit.back());
+    return ((has[a >> 6] >> (a & 63)) & (has[b >> 6] >> (b & 63)) & 1ull) != 0 && static_cast<int>(lit.size()) <= n;
+  }
   unsigned char at(int i) const { return (i >= 0 && i < n) ? static_cast<unsigned char>(p[i]) : 0; }
   bool boundary(int i) const {                   // \b between positions i-1 and i
     const bool a = i > 0 && is_word(at(i - 1));
@@ -52,9 +64,14 @@ struct Pat {
 void seg_matches(const View& s, const Seg& g, std::vector<std::pair<int, int>>& out) {
   out.clear();
   for (const std::string& a : g.alts) {
+    if (!s.may_contain(a)) continue;
     const int L = static_cast<int>(a.size());
-    for (int i = 0; i + L <= s.n; ++i) {
-      if (memcmp(s.p + i, a.data(), L) != 0) continue;
+    const char* end = s.p + (s.n - L + 1);         // one past the last possible start
+    for (const char* h = s.p; h < end; ++h) {
+      h = static_cast<const char*>(memchr(h, a[0], static_cast<size_t>(end - h)));
+      if (h == nullptr) break;
+      if (memcmp(h, a.data(), L) != 0) continue;
+      const int i = static_cast<int>(h - s.p);
       if (g.wb_start && !s.boundary(i)) continue;
       if (g.wb_end && !s.boundary(i + L)) continue;
       out.emplace_back(i, i + L);
@@ -202,9 +219,14 @@ const Tables& tables() {
 }
 
 bool contains(const View& s, const std::string& m) {
+  if (!s.may_contain(m)) return false;
   const int L = static_cast<int>(m.size());
-  for (int i = 0; i + L <= s.n; ++i)
-    if (memcmp(s.p + i, m.data(), L) == 0) return true;
+  const char* end = s.p + (s.n - L + 1);
+  for (const char* h = s.p; h < end; ++h) {
+    h = static_cast<const char*>(memchr(h, m[0], static_cast<size_t>(end - h)));
+    if (h == nullptr) return false;
+    if (memcmp(h, m.data(), L) == 0) return true;
+  }
   return false;
 }
 
@@ -222,11 +244,13 @@ void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_h
   int64_t b = 0, e = q_len;
   while (b < e && is_space(static_cast<unsigned char>(q_raw[b]))) ++b;
   while (e > b && is_space(static_cast<unsigned char>(q_raw[e - 1]))) --e;
-  const View q{q_raw + b, static_cast<int>(e - b)};
+  View q{q_raw + b, static_cast<int>(e - b)};
+  q.index();
   std::string low(q.p, q.n);
   for (char& c : low)
     if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
-  const View ql{low.data(), q.n};
+  View ql{low.data(), q.n};
+  ql.index();
   const uint8_t heavy = static_cast<uint8_t>(hp.n_devices - 1), light = 0;
   *cat = -1;
   for (size_t c = 0; c < T.complex_cats.size(); ++c)
@@ -260,6 +284,73 @@ void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_h
   *conf = c * 0.5;
 }
 
+// ---- MD5 (RFC 1321), for the cache's exact-match key: md5("<ctx>||<query lowered, stripped>") ----
+struct Md5 {
+  uint32_t K[64];
+  Md5() {
+    for (int i = 0; i < 64; ++i) K[i] = static_cast<uint32_t>(std::floor(std::fabs(std::sin(static_cast<double>(i + 1))) * 4294967296.0));
+  }
+  static uint32_t rotl(uint32_t x, int c) { return (x << c) | (x >> (32 - c)); }
+  void block(uint32_t st[4], const unsigned char* p) const {
+    static const int R[64] = {7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 5, 9,  14, 20, 5, 9,
+                              14, 20, 5, 9,  14, 20, 5, 9,  14, 20, 4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23,
+                              4, 11, 16, 23, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21};
+    uint32_t M[16];
+    for (int i = 0; i < 16; ++i)
+      M[i] = static_cast<uint32_t>(p[4 * i]) | (static_cast<uint32_t>(p[4 * i + 1]) << 8) |
+             (static_cast<uint32_t>(p[4 * i + 2]) << 16) | (static_cast<uint32_t>(p[4 * i + 3]) << 24);
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3];
+    for (int i = 0; i < 64; ++i) {
+      uint32_t f;
+      int g;
+      if (i < 16) { f = (b & c) | (~b & d); g = i; }
+      else if (i < 32) { f = (d & b) | (~d & c); g = (5 * i + 1) & 15; }
+      else if (i < 48) { f = b ^ c ^ d; g = (3 * i + 5) & 15; }
+      else { f = c ^ (b | ~d); g = (7 * i) & 15; }
+      const uint32_t t = d;
+      d = c;
+      c = b;
+      b = b + rotl(a + f + K[i] + M[g], R[i]);
+      a = t;
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d;
+  }
+  // hex digest of the concatenation of up to three byte ranges
+  void hex(const char* const* parts, const int64_t* lens, int n_parts, char* out32) const {
+    uint32_t st[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+    unsigned char buf[64];
+    int fill = 0;
+    uint64_t total = 0;
+    for (int k = 0; k < n_parts; ++k) {
+      const unsigned char* p = reinterpret_cast<const unsigned char*>(parts[k]);
+      int64_t n = lens[k];
+      total += static_cast<uint64_t>(n);
+      while (n > 0) {
+        const int take = static_cast<int>(n < 64 - fill ? n : 64 - fill);
+        memcpy(buf + fill, p, take);
+        fill += take; p += take; n -= take;
+        if (fill == 64) { block(st, buf); fill = 0; }
+      }
+    }
+    buf[fill++] = 0x80;
+    if (fill > 56) { memset(buf + fill, 0, 64 - fill); block(st, buf); fill = 0; }
+    memset(buf + fill, 0, 56 - fill);
+    const uint64_t bits = total * 8;
+    for (int i = 0; i < 8; ++i) buf[56 + i] = static_cast<unsigned char>(bits >> (8 * i));
+    block(st, buf);
+    static const char* H = "0123456789abcdef";
+    for (int i = 0; i < 16; ++i) {
+      const unsigned char v = static_cast<unsigned char>(st[i >> 2] >> (8 * (i & 3)));
+      out32[2 * i] = H[v >> 4];
+      out32[2 * i + 1] = H[v & 15];
+    }
+  }
+};
+const Md5& md5() {
+  static const Md5 m;
+  return m;
+}
+
 }  // namespace
 
 extern "C" QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64_t* query_len,
@@ -278,6 +369,64 @@ extern "C" QRE_API int qre_host_features(int64_t n, const char* const* queries, 
     for (int64_t i = i0; i < i1; ++i)
       classify_one(queries[i] ? queries[i] : "", queries[i] ? query_len[i] : 0, context_len ? context_len[i] : 0,
                    *hp, &tok[i], &heur_dev[i], &heur_conf[i], &heur_rule[i], &heur_cat[i]);
+  };
+  if (n_threads == 1) {
+    work(0, n);
+    return QRE_OK;
+  }
+  std::vector<std::thread> th;
+  for (int t = 0; t < n_threads; ++t) th.emplace_back(work, n * t / n_threads, n * (t + 1) / n_threads);
+  for (auto& x : th) x.join();
+  return QRE_OK;
+}
+
+// The same over ONE byte blob (queries[i] = blob[offsets[i] .. offsets[i+1])), which spares the
+// caller an array of n pointers, plus — when key_hex is given — the cache's exact-match key of every
+// ASCII query: md5(ctx_keys[ctx_index[i]] + "||" + lower(strip(query))) as 32 hex characters
+// (src/cache.py:518-521).  Rows with heur_rule -1 (non-ASCII query) are left for the caller.
+extern "C" QRE_API int qre_host_features_packed(int64_t n, const char* blob, const int64_t* offsets,
+                                                const int64_t* context_len, const qre_heur_params_t* hp,
+                                                int n_threads, int32_t* tok, uint8_t* heur_dev, double* heur_conf,
+                                                int32_t* heur_rule, int32_t* heur_cat, const char* ctx_blob,
+                                                const int64_t* ctx_offsets, const int32_t* ctx_index,
+                                                int32_t n_ctx, char* key_hex) {
+  if (n < 0 || hp == nullptr ||
+      (n > 0 && (!blob || !offsets || !tok || !heur_dev || !heur_conf || !heur_rule || !heur_cat)))
+    return QRE_ERR_INVALID;
+  if (hp->n_devices < 1) return QRE_ERR_INVALID;
+  if (key_hex != nullptr && (!ctx_blob || !ctx_offsets || !ctx_index || n_ctx < 1)) return QRE_ERR_INVALID;
+  for (int64_t i = 0; i < n; ++i)
+    if (offsets[i + 1] < offsets[i]) return QRE_ERR_INVALID;
+  if (key_hex != nullptr)
+    for (int64_t i = 0; i < n; ++i)
+      if (ctx_index[i] < 0 || ctx_index[i] >= n_ctx) return QRE_ERR_INVALID;
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 256) n_threads = 256;
+  if (n < 64) n_threads = 1;
+  tables();
+  const Md5& H = md5();
+  auto work = [&](int64_t i0, int64_t i1) {
+    std::string low;
+    for (int64_t i = i0; i < i1; ++i) {
+      const char* q = blob + offsets[i];
+      const int64_t len = offsets[i + 1] - offsets[i];
+      classify_one(q, len, context_len ? context_len[i] : 0, *hp, &tok[i], &heur_dev[i], &heur_conf[i],
+                   &heur_rule[i], &heur_cat[i]);
+      if (key_hex == nullptr) continue;
+      char* out = key_hex + 32 * i;
+      if (heur_rule[i] < 0) { memset(out, 0, 32); continue; }
+      // query.lower().strip() == strip then lower for ASCII
+      int64_t b = 0, e = len;
+      while (b < e && is_space(static_cast<unsigned char>(q[b]))) ++b;
+      while (e > b && is_space(static_cast<unsigned char>(q[e - 1]))) --e;
+      low.assign(q + b, static_cast<size_t>(e - b));
+      for (char& c : low)
+        if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
+      const int32_t ci = ctx_index[i];
+      const char* parts[3] = {ctx_blob + ctx_offsets[ci], "||", low.data()};
+      const int64_t lens[3] = {ctx_offsets[ci + 1] - ctx_offsets[ci], 2, static_cast<int64_t>(low.size())};
+      H.hex(parts, lens, 3, out);
+    }
   };
   if (n_threads == 1) {
     work(0, n);

@@ -31,7 +31,7 @@ EXPORTS = (
     "qre_set_perf_health", "qre_lookup_route", "qre_scan_dev", "qre_resolve_overflow_dev",
     "qre_merge_route_dev", "qre_launch_count", "qre_debug_gemm", "qre_profile", "qre_profile_read",
     "qre_exact_lookup_noalloc", "qre_cache_snapshot_save", "qre_cache_snapshot_load",
-    "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features",
+    "qre_lookup_route_begin", "qre_lookup_route_end", "qre_host_features", "qre_host_features_packed",
     "qre_submit_dev", "qre_wait_dev", "qre_group_lookup_route", "qre_xchg_init", "qre_xchg_connect", "qre_scan_publish_dev", "qre_merge_route_xchg_dev", "qre_publish_dev",
     # include/qre_encoder_b200.h
     "qre_encoder_create", "qre_encoder_destroy", "qre_encoder_set_embeddings", "qre_encoder_set_layer",
@@ -465,6 +465,56 @@ def host_features(queries, context_lens, hp: HeurParams, n_threads: int = 0) -> 
                                _ptr(out["cat"]))
     if rc != 0:
         raise QreError(f"qre_host_features failed with {rc}")
+    return out
+
+
+def host_features_packed(queries, context_lens, hp: HeurParams, context_keys=None, n_threads: int = 0) -> dict:
+    """`host_features` without per-query marshalling: the queries travel as one UTF-8 blob plus
+    offsets (qre_host_features_packed).  With `context_keys` (one per query) the result also
+    carries `keys`: the cache's exact-match md5 key of every query (None where rule == -1, i.e. a
+    non-ASCII query the caller hashes itself)."""
+    lib = load()
+    n = len(queries)
+    if n == 0:
+        out = dict(tok=np.empty(0, np.int32), heur_dev=np.empty(0, np.uint8), heur_conf=np.empty(0, np.float64),
+                   rule=np.empty(0, np.int32), cat=np.empty(0, np.int32))
+        if context_keys is not None:
+            out["keys"] = []
+        return out
+    blob = "".join(queries).encode("utf-8")
+    lens = np.fromiter(map(len, queries), np.int64, n)
+    if int(lens.sum()) != len(blob):                 # some query is not ASCII: byte lengths differ
+        lens = np.fromiter((len(q.encode("utf-8")) for q in queries), np.int64, n)
+    off = np.zeros(n + 1, np.int64)
+    np.cumsum(lens, out=off[1:])
+    clen = np.ascontiguousarray(context_lens, np.int64)
+    out = dict(tok=np.empty(n, np.int32), heur_dev=np.empty(n, np.uint8), heur_conf=np.empty(n, np.float64),
+               rule=np.empty(n, np.int32), cat=np.empty(n, np.int32))
+    if n_threads <= 0:
+        n_threads = min(32, os.cpu_count() or 1)
+    cblob, coff, cidx, n_ctx, hexbuf = None, None, None, 0, None
+    if context_keys is not None:
+        table: dict = {}
+        cidx = np.fromiter((table.setdefault(k, len(table)) for k in context_keys), np.int32, n)
+        enc = [k.encode("utf-8") for k in table]
+        cblob = b"".join(enc)
+        coff = np.zeros(len(enc) + 1, np.int64)
+        np.cumsum([len(b) for b in enc], out=coff[1:])
+        n_ctx = len(enc)
+        hexbuf = np.zeros(32 * n, np.uint8)
+    rc = lib.qre_host_features_packed(
+        C.c_int64(n), C.c_char_p(blob), _ptr(off), _ptr(clen), C.byref(hp), C.c_int(n_threads),
+        _ptr(out["tok"]), _ptr(out["heur_dev"]), _ptr(out["heur_conf"]), _ptr(out["rule"]), _ptr(out["cat"]),
+        C.c_char_p(cblob) if cblob is not None else None, _ptr(coff) if coff is not None else None,
+        _ptr(cidx) if cidx is not None else None, C.c_int32(n_ctx), _ptr(hexbuf) if hexbuf is not None else None)
+    if rc != 0:
+        raise QreError(f"qre_host_features_packed failed with {rc}")
+    if hexbuf is not None:
+        hx = hexbuf.tobytes().decode("latin-1")
+        keys = [hx[i:i + 32] for i in range(0, 32 * n, 32)]
+        for i in np.nonzero(out["rule"] < 0)[0].tolist():
+            keys[i] = None
+        out["keys"] = keys
     return out
 
 

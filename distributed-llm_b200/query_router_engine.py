@@ -32,7 +32,7 @@ from typing import Any, Dict, List, Literal, Optional, Sequence, Tuple
 import numpy as np
 
 try:
-    from cache import CacheEntry, CacheLookupResult, QueryCache, DEVICE_NAMES
+    from cache import CacheEntry, CacheLookupResult, QueryCache, DEVICE_NAMES, _gc_paused
 except ImportError as _e:   # pragma: no cover
     raise ImportError("query_router_engine needs the B200 cache.py next to it on sys.path "
                       f"(distributed-llm_b200/): {_e}") from _e
@@ -83,15 +83,16 @@ class LazyRoutingDecision(RoutingDecision):
     f-strings per batch cost more than the device pass).  Everything else — fields, equality with
     plain decisions, repr — is the reference's record (qre:55-62)."""
 
-    def __init__(self, device, confidence, method, reasoning_fn, complexity_score=None, cache_hit=False):
-        self.device, self.confidence, self.method = device, confidence, method
-        self.complexity_score, self.cache_hit = complexity_score, cache_hit
-        self.__dict__["_lazy"] = reasoning_fn
+    def __init__(self, device, confidence, method, reasoning_fn, reasoning_arg=None, complexity_score=None,
+                 cache_hit=False):
+        self.__dict__.update(device=device, confidence=confidence, method=method,
+                             complexity_score=complexity_score, cache_hit=cache_hit,
+                             _lazy=(reasoning_fn, reasoning_arg))
 
     def __getattr__(self, name):
         if name == "reasoning":
-            fn = self.__dict__.pop("_lazy")
-            self.__dict__["reasoning"] = r = fn()
+            fn, arg = self.__dict__.pop("_lazy")
+            self.__dict__["reasoning"] = r = fn(arg)
             return r
         raise AttributeError(name)
 
@@ -107,6 +108,12 @@ class LazyRoutingDecision(RoutingDecision):
     def __repr__(self):
         return ("RoutingDecision(device={!r}, confidence={!r}, method={!r}, reasoning={!r}, "
                 "complexity_score={!r}, cache_hit={!r})").format(*self._t())
+
+
+def _cached_why(t) -> str:
+    """Reasoning string of a cached decision from its snapshot tuple (reference qre:585-592)."""
+    return (f"cache hit age={int((t[0] - t[1]).total_seconds())}s hits={t[2]} predicted={t[3]} conf={t[4]:.2f} "
+            f"context_len={t[5]} history={t[6]}")
 
 
 class BaseRouter(ABC):
@@ -319,24 +326,28 @@ class HeuristicRouter(BaseRouter):
         return RoutingDecision(device=self._names[dev], confidence=conf, method=method, reasoning=why,
                                complexity_score=score)
 
-    def features_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
+    def features_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]],
+                       context_keys: Optional[Sequence[str]] = None):
         """What the fused device pass needs from the host for a batch — token counts and the
         heuristic (device, confidence) pairs — as arrays, without building any per-query object
-        (qre_host_features on C++ threads; non-ASCII queries, and every query when a real
-        tokenizer is installed, go through the Python rules)."""
+        (qre_host_features_packed on C++ threads; non-ASCII queries, and every query when a real
+        tokenizer is installed, go through the Python rules).  With `context_keys` a fourth value is
+        returned: the cache's exact-match key of every query (computed in the same C++ pass)."""
         if LITELLM_AVAILABLE:
             feats, toks = self.classify_batch(queries, contexts)
-            return (np.asarray(toks, np.int32), np.array([f[0] for f in feats], np.uint8),
-                    np.array([f[1] for f in feats], np.float64))
+            r3 = (np.asarray(toks, np.int32), np.array([f[0] for f in feats], np.uint8),
+                  np.array([f[1] for f in feats], np.float64))
+            return r3 if context_keys is None else r3 + ([None] * len(queries),)
         hp = _cabi.HeurParams(self.long_text_threshold, self.multi_question_threshold, self.code_markers_needed,
                               self.context_chars_threshold, self._token_fallback.threshold, len(self._names))
-        r = _cabi.host_features([(q or "") for q in queries], [len(c) if c else 0 for c in contexts], hp)
+        r = _cabi.host_features_packed([(q or "") for q in queries], [len(c) if c else 0 for c in contexts], hp,
+                                       context_keys=context_keys)
         tok, hd, hc = r["tok"], r["heur_dev"], r["heur_conf"]
         for i in np.nonzero(r["rule"] < 0)[0].tolist():
             f = self.classify(queries[i], contexts[i])
             hd[i], hc[i] = f[0], f[1]
             tok[i] = self._token_fallback.count(queries[i], contexts[i])
-        return tok, hd, hc
+        return (tok, hd, hc) if context_keys is None else (tok, hd, hc, r["keys"])
 
     def classify_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
         """`classify` for a whole batch on C++ threads (libqre_b200 qre_host_features); the few
@@ -616,8 +627,9 @@ class QueryRouter:
         r = self.router
         hybrid = isinstance(r, HybridRouter)
         sem = r.routers["semantic"] if hybrid else r
+        keys = None
         if hybrid:        # heuristic rules + token estimate for the whole batch on C++ threads, as arrays
-            tok, hd, hc = r.routers["heuristic"].features_batch(list(queries), contexts)
+            tok, hd, hc, keys = r.routers["heuristic"].features_batch(list(queries), contexts, ctxks)
             feats = (tok.tolist(), hd.tolist(), hc.tolist())
             route_in = dict(tok=tok, heur_dev=hd, heur_conf=hc)
         else:
@@ -625,9 +637,10 @@ class QueryRouter:
             route_in = dict(tok=np.array([int(t.complexity_score) for t, _ in feats], np.int32),
                             heur_dev=np.array([h[0] for _, h in feats], np.uint8),
                             heur_conf=np.array([h[1] for _, h in feats], np.float64))
-        results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg())
-        with self._cache._deferred():        # all inserts of the batch reach the device in a few calls
-            return self._finish_batch(queries, contexts, ctxks, q_embs, feats, results, out, hybrid)
+        with _gc_paused():
+            results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg(), keys)
+            with self._cache._deferred():        # all inserts of the batch reach the device in a few calls
+                return self._finish_batch(queries, contexts, ctxks, q_embs, feats, results, out, hybrid)
 
     def _finish_batch(self, queries, contexts, ctxks, q_embs, feats, results, out, hybrid) -> List[RoutingDecision]:
         r = self.router
@@ -646,22 +659,35 @@ class QueryRouter:
             def why(i):
                 tok_d = tr._decision(toks[i], *tr.decide(toks[i]))
                 return r._decision(out, i, tok_d, (hds[i], hcs[i])).reasoning
+        if hybrid and not any(results):
+            # nothing was cached: every query takes the device's decision and is inserted
+            new_obj, cls = object.__new__, LazyRoutingDecision
+            dev_names = [names[d] for d in devs]
+            for i in range(len(dev_names)):
+                d = new_obj(cls)
+                d.__dict__ = {"device": dev_names[i], "confidence": confs[i], "method": "hybrid",
+                              "complexity_score": None, "cache_hit": False, "_lazy": (why, i)}
+                decisions.append(d)
+            self._cache.insert_batch(list(queries), ctxks, dev_names, confs, "hybrid", q_embs, _keys=keys)
+            return decisions
+        ins: List[int] = []                  # batch indices to insert, in order (all lookups came first)
+        new_obj, lazy_cls, nano = object.__new__, LazyRoutingDecision, DEVICE_NAMES[0]
         for i, (q, c, k) in enumerate(zip(queries, contexts, ctxks)):
             res = results[i]
             routed = None
             if res is not None:
                 context_len = len(c) if c else 0
-                heavy_ctx = context_len >= threshold and res.predicted_device == DEVICE_NAMES[0]
+                heavy_ctx = context_len >= threshold and res.predicted_device == nano
                 if not (heavy_ctx or res.use_hybrid_fallback):
                     # the figures the reasoning quotes are taken NOW (hit count / history may move on)
-                    snap = (int((now - res.entry.timestamp).total_seconds()), res.entry.hit_count,
-                            res.predicted_device, res.predicted_confidence, context_len,
-                            len(res.entry.routing_history))
-                    decisions.append(LazyRoutingDecision(
-                        res.predicted_device, res.predicted_confidence, cached_method,
-                        (lambda t=snap: f"cache hit age={t[0]}s hits={t[1]} predicted={t[2]} conf={t[3]:.2f} "
-                                        f"context_len={t[4]} history={t[5]}"),
-                        cache_hit=True))
+                    e = res.entry
+                    d = new_obj(lazy_cls)
+                    d.__dict__ = {"device": res.predicted_device, "confidence": res.predicted_confidence,
+                                  "method": cached_method, "complexity_score": None, "cache_hit": True,
+                                  "_lazy": (_cached_why, (now, e.timestamp, e.hit_count, res.predicted_device,
+                                                          res.predicted_confidence, context_len,
+                                                          len(e.routing_history)))}
+                    decisions.append(d)
                     continue
                 reason = (f"context_len={context_len}>={threshold} overrides cached nano" if heavy_ctx
                           else f"low prediction confidence={res.predicted_confidence:.2f}")
@@ -669,11 +695,24 @@ class QueryRouter:
                 routed.reasoning = f"cache hit (hybrid re-route: {reason}) | " + routed.reasoning
                 routed.cache_hit = True
             if routed is None:
-                routed = (LazyRoutingDecision(names[devs[i]], confs[i], "hybrid", (lambda i=i: why(i)))
+                routed = (LazyRoutingDecision(names[devs[i]], confs[i], "hybrid", why, i)
                           if hybrid else self._routed(i, feats, out, hybrid))
-            self._cache.insert(q, k, device=routed.device, confidence=routed.confidence, method=routed.method,
-                               q_emb=q_embs[i], _key=keys[i])
+            ins.append(i)
             decisions.append(routed)
+        if ins:
+            whole = len(ins) == len(decisions)
+            pick = (lambda xs: xs) if whole else (lambda xs: [xs[i] for i in ins])
+            routed_d = pick(decisions)
+            methods = {d.method for d in routed_d}
+            if len(methods) == 1:
+                self._cache.insert_batch(pick(list(queries)), pick(ctxks), [d.device for d in routed_d],
+                                         [d.confidence for d in routed_d], methods.pop(),
+                                         q_embs if whole else q_embs[ins], _keys=pick(keys))
+            else:
+                for i in ins:
+                    d = decisions[i]
+                    self._cache.insert(queries[i], ctxks[i], device=d.device, confidence=d.confidence,
+                                       method=d.method, q_emb=q_embs[i], _key=keys[i])
         return decisions
 
     def _routed(self, i: int, feats, out, hybrid: bool) -> RoutingDecision:

@@ -264,6 +264,17 @@ QRE_API int qre_host_features(int64_t n, const char* const* queries, const int64
                               const int64_t* context_len, const qre_heur_params_t* hp, int n_threads,
                               int32_t* tok, uint8_t* heur_dev, double* heur_conf, int32_t* heur_rule,
                               int32_t* heur_cat);
+/* The same with the queries in ONE byte blob (query i = blob[offsets[i] .. offsets[i+1]), n + 1
+ * offsets), which spares a Python caller an array of n pointers; plus, when key_hex != NULL, the
+ * cache's exact-match key of every ASCII query (QueryCache._make_hash, cache.py:518-521):
+ * md5(ctx_keys[ctx_index[i]] + "||" + query.lower().strip()) as 32 lower-case hex characters at
+ * key_hex + 32*i (zero bytes where heur_rule[i] == -1: the caller hashes those itself).  The n_ctx
+ * distinct context keys are UTF-8 in ctx_blob with n_ctx + 1 offsets. */
+QRE_API int qre_host_features_packed(int64_t n, const char* blob, const int64_t* offsets,
+                                     const int64_t* context_len, const qre_heur_params_t* hp, int n_threads,
+                                     int32_t* tok, uint8_t* heur_dev, double* heur_conf, int32_t* heur_rule,
+                                     int32_t* heur_cat, const char* ctx_blob, const int64_t* ctx_offsets,
+                                     const int32_t* ctx_index, int32_t n_ctx, char* key_hex);
 
 /* ---- peer exchange: the all-gather written as stores into peer memory ------------------------
  * No counterpart in the reference (it never shards its cache; SURVEY §8e defines this exchange).
