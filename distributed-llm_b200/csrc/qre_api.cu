@@ -173,6 +173,11 @@ struct qre_cache {
   // The pipeline (qre_submit_dev / qre_lookup_route_begin): query preparation on `aux`, the scan
   // alone on the handle's main stream, re-score / settle / exchange / merge + route on `post`.
   cudaStream_t aux = nullptr, post = nullptr;
+  // Consecutive large-batch scans alternate between the main stream and this one (same priority):
+  // as two independent kernels the next scan's CTAs move onto SMs as the previous scan's CTAs retire,
+  // so its set-up and the previous scan's tail overlap instead of adding up (QRE_ONE_SCAN_STREAM=1: off).
+  cudaStream_t scan2 = nullptr;
+  bool alt_scan = true;
   cudaEvent_t ev_in[2] = {};                                         // per API slot: inputs valid
   cudaEvent_t ev_prep[kPipeSlots] = {}, ev_route[kPipeSlots] = {}, ev_scan[kPipeSlots] = {}, ev_post[kPipeSlots] = {};
   bool post_used[kPipeSlots] = {};
@@ -411,6 +416,7 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     QRE_CUDA(cudaStreamCreateWithFlags(&h->d2h, cudaStreamNonBlocking));
     QRE_CUDA(cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, prio_least));
     QRE_CUDA(cudaStreamCreateWithPriority(&h->post, cudaStreamNonBlocking, prio_least));
+    QRE_CUDA(cudaStreamCreateWithPriority(&h->scan2, cudaStreamNonBlocking, prio_greatest));
     QRE_CUDA(cudaMemsetAsync(s.rows_bf16, 0, sizeof(__nv_bfloat16) * (size_t)s.cap_pad * dim_pad, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.meta, 0xFF, sizeof(RowMeta) * (size_t)capacity, s.stream));
     QRE_CUDA(cudaMemsetAsync(s.row_norm, 0, sizeof(float) * (size_t)capacity, s.stream));
@@ -426,6 +432,8 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     {
       const char* e = getenv("QRE_SCAN_SINGLE_CTA");
       s.allow_pair = !(e != nullptr && e[0] == '1');
+      const char* o = getenv("QRE_ONE_SCAN_STREAM");
+      h->alt_scan = !(o != nullptr && o[0] == '1');
     }
     EncodeTiledFn enc = nullptr;
     int rc = get_encode_fn(&enc);
@@ -456,6 +464,7 @@ int qre_cache_destroy(qre_cache_t* h) {
   if (s.stream) cudaStreamSynchronize(s.stream);
   if (h->aux) cudaStreamSynchronize(h->aux);
   if (h->post) cudaStreamSynchronize(h->post);
+  if (h->scan2) cudaStreamSynchronize(h->scan2);
   std::vector<void*> dev_ptrs = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf,
                                  s.exact_partial, s.settle_tickets, s.settle_partial, s.centroids, s.cent_norm,
                                  s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in, h->hs[1].d_in,
@@ -488,6 +497,7 @@ int qre_cache_destroy(qre_cache_t* h) {
   if (h->d2h) cudaStreamDestroy(h->d2h);
   if (h->aux) cudaStreamDestroy(h->aux);
   if (h->post) cudaStreamDestroy(h->post);
+  if (h->scan2) cudaStreamDestroy(h->scan2);
   if (s.prof_ev) {
     for (int i = 0; i < 2 * kProfMax; ++i) cudaEventDestroy(s.prof_ev[i]);
     delete[] s.prof_ev;
@@ -980,6 +990,7 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
   h->last_m = m;
   DeviceState::Batch& B = s.cur();
   cudaStream_t aux = serial ? s.stream : h->aux, post = serial ? s.stream : h->post;
+  cudaStream_t scan_st = (!serial && h->alt_scan && (h->pipe_seq & 1)) ? h->scan2 : s.stream;
   const bool sharded = h->xchg != nullptr && h->xchg_world > 1;
   // sliced results: this rank merges and routes queries [q0, q1) only
   const bool sliced = sharded && p.slice_results != 0;
@@ -1031,7 +1042,7 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
   s.pdl = serial;
   if (!serial) {
     QRE_CUDA(cudaEventRecord(h->ev_prep[slot], aux));
-    QRE_CUDA(cudaStreamWaitEvent(s.stream, h->ev_prep[slot], 0));
+    QRE_CUDA(cudaStreamWaitEvent(scan_st, h->ev_prep[slot], 0));
     if (p.do_route) {
       // routing needs the prepared queries only: it runs on the aux stream beside the scan, and
       // the post stream's merge then fills in the lookup half of the results
@@ -1043,10 +1054,10 @@ static int pipeline_enqueue(qre_cache_t* h, int slot, int m, const float* d_q, c
       p_merge.do_route = 0;
     }
   }
-  int rc = tensor_scan_enqueue(h, m, p, s.stream);
+  int rc = tensor_scan_enqueue(h, m, p, scan_st);
   if (rc != QRE_OK) { s.pdl = false; return rc; }
   if (!serial) {
-    QRE_CUDA(cudaEventRecord(h->ev_scan[slot], s.stream));
+    QRE_CUDA(cudaEventRecord(h->ev_scan[slot], scan_st));
     QRE_CUDA(cudaStreamWaitEvent(post, h->ev_scan[slot], 0));
   }
   rc = rescore_enqueue(h, m, p, sharded ? h->xchg_rank : 0, B.cand, post);
@@ -1458,11 +1469,20 @@ int qre_profile_read(qre_cache_t* h, double* scan_ms_total, int* n_launches) {
     return fail(QRE_ERR_INVALID, "NULL argument");
   DeviceGuard guard(h->s.device);
   DeviceState& s = h->s;
+  // Consecutive scans run on alternating streams and overlap at their edges (the next one's start
+  // event fires while the previous kernel still holds the SMs), so a launch is charged from its own
+  // start event or the previous launch's end event, whichever is later, to its own end event: the
+  // sum is the time the scan kernels hold the GPU, not the sum of overlapping brackets.
   double total = 0.0;
   for (int i = 0; i < s.prof_used; ++i) {
     float ms = 0.f;
     QRE_CUDA(cudaEventSynchronize(s.prof_ev[2 * i + 1]));
     QRE_CUDA(cudaEventElapsedTime(&ms, s.prof_ev[2 * i], s.prof_ev[2 * i + 1]));
+    if (i > 0) {
+      float since_prev = 0.f;
+      QRE_CUDA(cudaEventElapsedTime(&since_prev, s.prof_ev[2 * i - 1], s.prof_ev[2 * i + 1]));
+      if (since_prev >= 0.f && since_prev < ms) ms = since_prev;
+    }
     total += ms;
   }
   *scan_ms_total = total;
