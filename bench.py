@@ -460,7 +460,7 @@ def run_b200(args):
     value = M / (ms_per_step * 1e-3)
 
     # ---- e2e: the C-ABI call with HOST buffers (H2D of the inputs + D2H of the results) ----
-    # qre_lookup_route_begin / _end: page-locked host arrays in, host arrays out, two batches in
+    # qre_lookup_route_begin / _end: page-locked host arrays in, host arrays out, three batches in
     # flight so the copies of the neighbouring batches run under the scan.  With N > 1 every rank
     # makes the same call with the same (replicated) host batch; the candidate exchange between
     # the ranks happens inside the library.
@@ -476,12 +476,15 @@ def run_b200(args):
                               heur_conf=hq["hc"])
 
     def run_e2e(n):
-        begin(0)
+        # three batches in flight (begin i+2 before end i): with several ranks the batch only starts
+        # once EVERY rank has submitted it, so one late host thread would otherwise idle all GPUs
         r = None
-        for i in range(1, n):
-            begin(i & 1)
-            r = sh.lookup_route_end((i - 1) & 1)
-        return sh.lookup_route_end((n - 1) & 1) if n else r
+        for i in range(n + 2):
+            if i < n:
+                begin(i % 3)
+            if i >= 2:
+                r = sh.lookup_route_end((i - 2) % 3)
+        return r
     e2e_ok = look.exchange == "p2p" or world == 1     # the library's own exchange is the peer-store one
     if e2e_ok:
         r = run_e2e(max(2, args.warmup))

@@ -168,7 +168,7 @@ struct qre_cache {
     const int32_t* d_tok = nullptr;
     const uint8_t* d_hd = nullptr;
     const double* d_hc = nullptr;
-  } hs[2];
+  } hs[kApiSlots];
   cudaStream_t h2d = nullptr, d2h = nullptr;
   // The pipeline (qre_submit_dev / qre_lookup_route_begin): query preparation on `aux`, the scan
   // alone on the handle's main stream, re-score / settle / exchange / merge + route on `post`.
@@ -178,11 +178,11 @@ struct qre_cache {
   // so its set-up and the previous scan's tail overlap instead of adding up (QRE_ONE_SCAN_STREAM=1: off).
   cudaStream_t scan2 = nullptr;
   bool alt_scan = true;
-  cudaEvent_t ev_in[2] = {};                                         // per API slot: inputs valid
+  cudaEvent_t ev_in[kApiSlots] = {};                                 // per API slot: inputs valid
   cudaEvent_t ev_prep[kPipeSlots] = {}, ev_route[kPipeSlots] = {}, ev_scan[kPipeSlots] = {}, ev_post[kPipeSlots] = {};
   bool post_used[kPipeSlots] = {};
   uint64_t pipe_seq = 0;               // batches enqueued so far; batch i uses pipeline slot i % kPipeSlots
-  int api_ps[2] = {-1, -1};            // pipeline slot of the batch last submitted on each API slot
+  int api_ps[kApiSlots] = {-1, -1, -1};  // pipeline slot of the batch last submitted on each API slot
   size_t in_bytes = 0;
   size_t res_bytes = 0;
   int last_slot = 0;
@@ -394,12 +394,12 @@ int qre_cache_create(int device, int dim, int64_t capacity, int max_batch, qre_c
     L.plan(max_batch, QRE_MAX_CENTROIDS, QRE_MAX_DEVICES);
     h->res_bytes = L.total;
   }
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < kApiSlots; ++b) {
     QRE_ALLOC(h->hs[b].d_in, h->in_bytes);
     QRE_ALLOC(h->hs[b].d_res, h->res_bytes);
   }
   QRE_TRY([&]() -> int {
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kApiSlots; ++b) {
       QRE_CUDA(cudaMallocHost((void**)&h->hs[b].h_in, h->in_bytes));
       QRE_CUDA(cudaMallocHost((void**)&h->hs[b].h_res, h->res_bytes));
       QRE_CUDA(cudaEventCreateWithFlags(&h->hs[b].e_in, cudaEventDisableTiming));
@@ -468,7 +468,8 @@ int qre_cache_destroy(qre_cache_t* h) {
   std::vector<void*> dev_ptrs = {s.rows_f32, s.rows_bf16, s.row_norm, s.meta, s.lru, s.pred_dev, s.pred_conf,
                                  s.exact_partial, s.settle_tickets, s.settle_partial, s.centroids, s.cent_norm,
                                  s.cent_owner, s.perf_health, h->d_stage, h->hs[0].d_in, h->hs[1].d_in,
-                                 h->hs[0].d_res, h->hs[1].d_res, h->d_dump, h->d_gather};
+                                 h->hs[2].d_in, h->hs[0].d_res, h->hs[1].d_res, h->hs[2].d_res, h->d_dump,
+                                 h->d_gather};
   for (int b = 0; b < kPipeSlots; ++b) {
     DeviceState::Batch& B = s.batch[b];
     for (void* p : {(void*)B.q_f32, (void*)B.q_bf16, (void*)B.q_norm, (void*)B.q_ctx, (void*)B.q_flags,
@@ -478,7 +479,7 @@ int qre_cache_destroy(qre_cache_t* h) {
   }
   for (void* p : dev_ptrs)
     if (p) cudaFree(p);
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < kApiSlots; ++b) {
     if (h->hs[b].h_in) cudaFreeHost(h->hs[b].h_in);
     if (h->hs[b].h_res) cudaFreeHost(h->hs[b].h_res);
     if (h->hs[b].e_in) cudaEventDestroy(h->hs[b].e_in);
@@ -1084,7 +1085,7 @@ int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries, const 
                    const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
                    qre_result_t* out_dev, void* in_stream) {
   if (h == nullptr || out_dev == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
-  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (slot < 0 || slot >= kApiSlots) return fail(QRE_ERR_INVALID, "slot must be 0, 1 or 2");
   if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
   if (!queries || !q_ctx) return fail(QRE_ERR_INVALID, "NULL argument");
   int rc = validate_params(h, params);
@@ -1103,7 +1104,7 @@ int qre_submit_dev(qre_cache_t* h, int slot, int m, const float* queries, const 
 
 int qre_wait_dev(qre_cache_t* h, int slot, void* stream) {
   if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
-  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (slot < 0 || slot >= kApiSlots) return fail(QRE_ERR_INVALID, "slot must be 0, 1 or 2");
   const int ps = h->api_ps[slot];
   if (ps < 0 || !h->post_used[ps]) return QRE_OK;
   DeviceGuard guard(h->s.device);
@@ -1116,7 +1117,7 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
                            const int32_t* tok, const uint8_t* heur_dev, const double* heur_conf,
                            const qre_params_t* params) {
   if (h == nullptr) return fail(QRE_ERR_INVALID, "handle is NULL");
-  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (slot < 0 || slot >= kApiSlots) return fail(QRE_ERR_INVALID, "slot must be 0, 1 or 2");
   if (m < 1 || m > h->s.max_batch) return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d]", m, h->s.max_batch);
   if (!queries || !q_ctx) return fail(QRE_ERR_INVALID, "NULL argument");
   int rc = validate_params(h, params);
@@ -1208,7 +1209,7 @@ int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries
 
 int qre_lookup_route_end(qre_cache_t* h, int slot, qre_result_t* out) {
   if (h == nullptr || out == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
-  if (slot < 0 || slot > 1) return fail(QRE_ERR_INVALID, "slot must be 0 or 1");
+  if (slot < 0 || slot >= kApiSlots) return fail(QRE_ERR_INVALID, "slot must be 0, 1 or 2");
   qre_cache_t::HostSlot& S = h->hs[slot];
   if (!S.pending) return fail(QRE_ERR_INVALID, "slot %d has no batch in flight", slot);
   DeviceGuard guard(h->s.device);
@@ -1226,7 +1227,7 @@ int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const uint64_t
                      const uint8_t* heur_dev, const double* heur_conf, const qre_params_t* params,
                      qre_result_t* out) {
   if (out == nullptr) return fail(QRE_ERR_INVALID, "NULL argument");
-  if (h != nullptr && (h->hs[0].pending || h->hs[1].pending))
+  if (h != nullptr && (h->hs[0].pending || h->hs[1].pending || h->hs[2].pending))
     return fail(QRE_ERR_INVALID, "asynchronous batches in flight: finish them with qre_lookup_route_end first");
   int rc = qre_lookup_route_begin(h, 0, m, queries, q_ctx, tok, heur_dev, heur_conf, params);
   if (rc != QRE_OK) return rc;
@@ -1250,7 +1251,7 @@ int qre_group_lookup_route(qre_cache_t* const* hs, int n_handles, int m, const f
     if (hs[i]->s.dim != hs[0]->s.dim) return fail(QRE_ERR_INVALID, "handle %d has another dimension", i);
     if (m < 1 || m > hs[i]->s.max_batch)
       return fail(QRE_ERR_CAPACITY, "m=%d outside [1, max_batch=%d] of handle %d", m, hs[i]->s.max_batch, i);
-    if (hs[i]->hs[0].pending || hs[i]->hs[1].pending)
+    if (hs[i]->hs[0].pending || hs[i]->hs[1].pending || hs[i]->hs[2].pending)
       return fail(QRE_ERR_INVALID, "handle %d has asynchronous batches in flight", i);
   }
   qre_cache_t* h0 = hs[0];

@@ -22,6 +22,7 @@ constexpr int kExactGroup = 8;        // queries per brute-force pass
 constexpr int kPipeSlots = 3;         // copies of the per-batch state: the pipeline keeps up to three batches
                                       // in flight (prep of i+1, scan of i, re-score / merge of i-1) and a
                                       // slot is reused only three batches later
+constexpr int kApiSlots = 3;          // host-buffer / output slots a caller may have in flight (begin/end, submit)
 constexpr uint32_t kNoChunk = 0xFFFFFFFFu;    // empty spill chain
 constexpr uint32_t kChunkLost = 0xFFFFFFFEu;  // spill pool exhausted: this (query, range) lost candidates
 constexpr int kSpillPer = 15;         // candidates per spill chunk (128-byte chunks)

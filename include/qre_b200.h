@@ -189,10 +189,12 @@ QRE_API int qre_lookup_route(qre_cache_t* h, int m, const float* queries, const 
 
 /* The same call split in two so that consecutive batches overlap: `begin` enqueues the H2D
  * copy of the inputs (own copy stream), the kernels and the D2H copy of the results (own copy
- * stream) and returns; `end` waits for that batch and fills `out`.  Two slots (0 / 1): begin
- * batch i+1 on the other slot before ending batch i and its input copy runs under batch i's
- * scan.  The inputs must stay unchanged until `end`; if `queries` is page-locked memory it is
- * copied straight from the caller's buffer.  qre_lookup_route == begin(0) + end(0). */
+ * stream) and returns; `end` waits for that batch and fills `out`.  Three slots (0 / 1 / 2): begin
+ * batch i+1 on another slot before ending batch i and its input copy runs under batch i's
+ * scan; with several ranks of a row-sharded cache (qre_xchg_*) keep two batches ahead (begin i+2
+ * before end i), so that one rank's late host thread does not stall the scans of all of them.
+ * The inputs must stay unchanged until `end`; if `queries` is page-locked memory it is copied
+ * straight from the caller's buffer.  qre_lookup_route == begin(0) + end(0). */
 QRE_API int qre_lookup_route_begin(qre_cache_t* h, int slot, int m, const float* queries,
                                    const uint64_t* q_ctx, const int32_t* tok, const uint8_t* heur_dev,
                                    const double* heur_conf, const qre_params_t* params);
@@ -201,12 +203,15 @@ QRE_API int qre_lookup_route_end(qre_cache_t* h, int slot, qre_result_t* out);
 /* The whole pass on DEVICE pointers, pipelined inside the library (no reference counterpart: the
  * reference handles one query at a time on the host; this is the call a device-resident producer,
  * e.g. the on-GPU embedder, feeds).  qre_submit_dev enqueues one batch and returns: query
- * preparation runs on an auxiliary stream of the handle, the tensor-core scan ALONE on the handle's
- * main stream, and exact re-score, overflow settlement, the candidate exchange (when qre_xchg_* is
+ * preparation runs on an auxiliary stream of the handle, the tensor-core scans ALONE on the handle's
+ * main stream and a twin of it in turn (consecutive scans overlap only where one retires its CTAs
+ * and the next moves in), and exact re-score, overflow settlement, the candidate exchange (when qre_xchg_* is
  * connected: every rank then submits the same batch) and merge + routing on a third stream, so
  * consecutive scans run back to back while the small kernels of the neighbouring batches run
- * beside them (leave them room with params->reserve_sms).  Two slots: submit batch i on slot i & 1;
- * a slot's previous batch is waited for on the device, not on the host.  The inputs must be valid
+ * beside them (leave them room with params->reserve_sms).  Slots 0 / 1 / 2 name the caller's output
+ * arrays: submit batch i on slot i & 1 (or i % 3); a slot's previous batch is waited for on the
+ * device, not on the host.  Cache rows must not be written (append / update / tombstone / clear)
+ * while a submitted batch is in flight: wait for it first.  The inputs must be valid
  * on `in_stream` at the time of the call (NULL: already valid) and, like *out_dev's arrays, stay
  * untouched until the batch has finished.  qre_wait_dev makes `stream` wait for the batch last
  * submitted on `slot` (stream == NULL: blocks the host instead). */

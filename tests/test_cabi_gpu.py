@@ -385,6 +385,41 @@ def test_begin_end_slots_overlap_and_pinned_inputs(small):
     sh.close()
 
 
+def test_three_batches_in_flight_and_a_stream_of_them(small):
+    """Three host slots: three batches in flight at once, then a run of 9 batches kept two ahead
+    (begin i+2 before end i, the multi-rank calling pattern); every result equals the synchronous
+    call.  The large batches alternate between the handle's two scan streams."""
+    w = small
+    big = synth.make_workload(6000, 520, 384, n_centroids=8, seed=21)          # > one query block: pipelined path
+    for wk, step in ((w, 100), (big, 260)):
+        sh = _load(wk)
+        cfg = _cabi.RouteConfig(ttl_us=wk.ttl_us)
+        parts = [slice(i * step // 2, i * step // 2 + step) for i in range(3)]
+        sync = [sh.lookup_route(wk.queries[p], wk.q_ctx[p], cfg, wk.now_us, tok=wk.tok[p], heur_dev=wk.heur_dev[p],
+                                heur_conf=wk.heur_conf[p]) for p in parts]
+
+        def begin(slot, p):
+            sh.lookup_route_begin(slot, wk.queries[p], wk.q_ctx[p], cfg, wk.now_us, tok=wk.tok[p],
+                                  heur_dev=wk.heur_dev[p], heur_conf=wk.heur_conf[p])
+        for i, p in enumerate(parts):
+            begin(i, p)
+        with pytest.raises(_cabi.QreError, match="slot must be 0, 1 or 2"):
+            begin(3, parts[0])
+        for i in (2, 0, 1):                              # any order of completion
+            g = sh.lookup_route_end(i)
+            for k in sync[i]:
+                assert np.array_equal(g[k], sync[i][k]), (i, k)
+        n = 9
+        for i in range(n + 2):
+            if i < n:
+                begin(i % 3, parts[i % 3])
+            if i >= 2:
+                g = sh.lookup_route_end((i - 2) % 3)
+                for k in sync[(i - 2) % 3]:
+                    assert np.array_equal(g[k], sync[(i - 2) % 3][k]), (i, k)
+        sh.close()
+
+
 def test_group_lookup_route_two_shards_one_process(small):
     """qre_group_lookup_route: one process, the rows dealt over two handles (two GPUs when the box has
     them, else both on GPU 0), lists gathered and merged on the first handle's GPU.  Must equal the
