@@ -241,7 +241,21 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* 
                : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(row_ptr))));
 }
 
-// Q, K and V rows of one (sequence, head) -> shared memory, 16 bytes per thread per load.
+// 16-byte asynchronous copy global -> shared (LDGSTS, L2 only); src_bytes = 0 writes zeros instead.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+               "l"(gmem_src), "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+// Q, K and V rows of one (sequence, head) -> shared memory with asynchronous 16-byte copies: every
+// copy of the head is in flight before the first one is waited for (a register-staged loop kept
+// three loads per lane in flight and the kernel ran at 2.6 TB/s, waiting on them one round trip at a
+// time).  The caller waits (cp_async_wait_all) and synchronises.
 template <int HD>
 __device__ __forceinline__ void stage_qkv(__nv_bfloat16* Qs, __nv_bfloat16* Ks, __nv_bfloat16* Vs,
                                           const __nv_bfloat16* base, long long ld, int H, int L, int Lk, int tid,
@@ -249,16 +263,12 @@ __device__ __forceinline__ void stage_qkv(__nv_bfloat16* Qs, __nv_bfloat16* Ks, 
   constexpr int KS = HD + 8;
   for (int idx = tid; idx < Lk * (HD / 8); idx += nthreads) {
     const int key = idx / (HD / 8), part = idx - key * (HD / 8);
-    uint4 qv = make_uint4(0, 0, 0, 0), kv = qv, vv = qv;               // padded rows: zeros (keys are masked below)
-    if (key < L) {
-      const __nv_bfloat16* p = base + key * ld + part * 8;
-      qv = *reinterpret_cast<const uint4*>(p);
-      kv = *reinterpret_cast<const uint4*>(p + H);
-      vv = *reinterpret_cast<const uint4*>(p + 2 * H);
-    }
-    *reinterpret_cast<uint4*>(Qs + key * KS + part * 8) = qv;
-    *reinterpret_cast<uint4*>(Ks + key * KS + part * 8) = kv;
-    *reinterpret_cast<uint4*>(Vs + key * KS + part * 8) = vv;
+    const bool live = key < L;                                          // padded rows: zeros (keys are masked below)
+    const __nv_bfloat16* p = base + (live ? key : 0) * ld + part * 8;
+    const int nb = live ? 16 : 0;
+    cp_async16(Qs + key * KS + part * 8, p, nb);
+    cp_async16(Ks + key * KS + part * 8, p + H, nb);
+    cp_async16(Vs + key * KS + part * 8, p + 2 * H, nb);
   }
 }
 
@@ -416,6 +426,7 @@ enc_attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __res
     const __nv_bfloat16* base = qkv + static_cast<long long>(t0) * ld + head * HD;
     __syncthreads();                               // previous sequence's rows fully copied out
     stage_qkv<HD>(Qs, Ks, Vs, base, ld, H, L, Lk, threadIdx.x, blockDim.x);
+    cp_async_wait_all();
     __syncthreads();
     for (int qb = warp; qb * 16 < L; qb += blockDim.x >> 5) attend_block<HD>(Qs, Ks, Vs, L, Lk, qb, scale_log2e, lane);
     __syncthreads();
@@ -463,6 +474,7 @@ enc_attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t*
   const int Lk = (L + 15) & ~15;
   const long long ld = 3LL * H;
   stage_qkv<HD>(Qs, Ks, Vs, qkv + static_cast<long long>(t0) * ld + head * HD, ld, H, L, Lk, lane, 32);
+  cp_async_wait_all();
   __syncwarp();
   attend_block<HD>(Qs, Ks, Vs, L, Lk, 0, scale_log2e, lane);
   if (L > 16) attend_block<HD>(Qs, Ks, Vs, L, Lk, 1, scale_log2e, lane);
@@ -535,6 +547,9 @@ struct qre_encoder {
   int64_t max_tokens = 0, tok_pad = 0;
   int max_seqs = 0;
   cudaStream_t stream = nullptr;
+  // attention over the longer sequences of a batch runs on `side`, beside the short-sequence kernel
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   float *word = nullptr, *pos = nullptr, *type = nullptr, *eln_g = nullptr, *eln_b = nullptr;
   std::vector<Layer> layers;
   __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *h = nullptr;
@@ -608,7 +623,7 @@ void free_linear(Linear& L) {
 
 int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_t T, const CUtensorMap& box_out,
                const CUtensorMap* box_res, int epi, cudaStream_t st, const float* ln_g = nullptr,
-               const float* ln_b = nullptr) {
+               const float* ln_b = nullptr, bool after_kernel = true) {
   EncGemmArgs a;
   a.num_kb = L.k / kEncBK;
   a.tiles_m = static_cast<int>((T + kEncBM - 1) / kEncBM);
@@ -617,50 +632,62 @@ int run_linear(qre_encoder* e, const CUtensorMap& map_a, const Linear& L, int64_
   a.ln_g = ln_g;
   a.ln_b = ln_b;
   a.ln_eps = e->cfg.ln_eps;
-  return launch_enc_gemm(map_a, L.map, box_out, box_res, a, epi, e->num_sms, st, true);
+  return launch_enc_gemm(map_a, L.map, box_out, box_res, a, epi, e->num_sms, st, after_kernel);
 }
 
 size_t attention_short_smem(int hd, int Lp) { return 4 * attention_smem(hd, Lp); }
 
+// The three length buckets are independent of each other (all read the QKV projection, each writes its
+// own sequences' context rows), so the two CTA-per-head launches for the longer sequences go to a
+// side stream and run beside the warp-per-head kernel instead of after it: their tails (a handful of
+// 100+ token sequences) no longer add to the layer.  The fork / join events cost the two neighbouring
+// kernels their programmatic-dependent overlap; measured it is a clear net gain.
 int launch_attention(qre_encoder* e, int m, const int32_t* offsets, int max_len, cudaStream_t st) {
   const int H = e->cfg.hidden;
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(e->hd));
   int n = 0;
+  const __nv_bfloat16* qkv = e->qkv;
+  const bool fork = max_len > kShortLen;
+  if (fork) {
+    // longer sequences (listed by enc_find_long_kernel): CTA per (sequence, head), once for the mid bucket
+    // with a 64-row footprint (many CTAs per SM) and once, if the batch has any, for the long bucket
+    ENC_CUDA(cudaEventRecord(e->ev_fork, st));
+    ENC_CUDA(cudaStreamWaitEvent(e->side, e->ev_fork, 0));
+    for (int bucket = 1; bucket >= 0; --bucket) {        // the long bucket first: it has the longest items
+      if (max_len <= (bucket == 0 ? kShortLen : kMidLen)) continue;
+      const int Lp = bucket == 0 ? (((max_len < kMidLen ? max_len : kMidLen) + 15) & ~15) : ((max_len + 15) & ~15);
+      const size_t smem = attention_smem(e->hd, Lp);
+      int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
+      per_sm = per_sm < 1 ? 1 : (per_sm > 16 ? 16 : per_sm);
+      int gx = (e->num_sms * per_sm + e->cfg.heads - 1) / e->cfg.heads;
+      gx = gx < 1 ? 1 : (gx > m ? m : gx);
+      if (gx > 65535) gx = 65535;
+      const dim3 grid(e->cfg.heads, gx);
+      const int32_t* list = e->long_list + (bucket == 0 ? 0 : m);
+      const int32_t* cnt = e->n_long + bucket;
+      if (e->hd == 32)
+        launch_chain(enc_attention_kernel<32>, grid, dim3(128), smem, e->side, false, qkv, offsets, list, cnt, e->ctx, H,
+                     Lp, scale_log2e);
+      else
+        launch_chain(enc_attention_kernel<64>, grid, dim3(128), smem, e->side, false, qkv, offsets, list, cnt, e->ctx, H,
+                     Lp, scale_log2e);
+      ++n;
+    }
+    ENC_CUDA(cudaEventRecord(e->ev_join, e->side));
+  }
   // sequences of up to kShortLen tokens: warp per head
   const int Ls = ((max_len < kShortLen ? max_len : kShortLen) + 15) & ~15;
   // x (fastest in launch order) = head group: the CTAs that read the 64-byte head slices of the same token rows
   // are resident together, so each 2304-byte qkv row is touched once while its DRAM page is open
   const dim3 grid_s((e->cfg.heads + 3) / 4, m);
-  const __nv_bfloat16* qkv = e->qkv;
   if (e->hd == 32)
-    launch_chain(enc_attention_short_kernel<32>, grid_s, dim3(128), attention_short_smem(32, Ls), st, true, qkv, offsets,
-                 e->ctx, H, e->cfg.heads, Ls, scale_log2e);
+    launch_chain(enc_attention_short_kernel<32>, grid_s, dim3(128), attention_short_smem(32, Ls), st, !fork, qkv,
+                 offsets, e->ctx, H, e->cfg.heads, Ls, scale_log2e);
   else
-    launch_chain(enc_attention_short_kernel<64>, grid_s, dim3(128), attention_short_smem(64, Ls), st, true, qkv, offsets,
-                 e->ctx, H, e->cfg.heads, Ls, scale_log2e);
+    launch_chain(enc_attention_short_kernel<64>, grid_s, dim3(128), attention_short_smem(64, Ls), st, !fork, qkv,
+                 offsets, e->ctx, H, e->cfg.heads, Ls, scale_log2e);
   ++n;
-  // longer sequences (listed by enc_find_long_kernel): CTA per (sequence, head), once for the mid bucket with
-  // a 64-row footprint (many CTAs per SM) and once, if the batch has any, for the long bucket
-  for (int bucket = 0; bucket < 2; ++bucket) {
-    if (max_len <= (bucket == 0 ? kShortLen : kMidLen)) break;
-    const int Lp = bucket == 0 ? (((max_len < kMidLen ? max_len : kMidLen) + 15) & ~15) : ((max_len + 15) & ~15);
-    const size_t smem = attention_smem(e->hd, Lp);
-    int per_sm = static_cast<int>((200u << 10) / (smem + 1024));
-    per_sm = per_sm < 1 ? 1 : (per_sm > 16 ? 16 : per_sm);
-    int gx = (e->num_sms * per_sm + e->cfg.heads - 1) / e->cfg.heads;
-    gx = gx < 1 ? 1 : (gx > m ? m : gx);
-    if (gx > 65535) gx = 65535;
-    const dim3 grid(e->cfg.heads, gx);
-    const int32_t* list = e->long_list + (bucket == 0 ? 0 : m);
-    const int32_t* cnt = e->n_long + bucket;
-    if (e->hd == 32)
-      launch_chain(enc_attention_kernel<32>, grid, dim3(128), smem, st, true, qkv, offsets, list, cnt, e->ctx, H, Lp,
-                   scale_log2e);
-    else
-      launch_chain(enc_attention_kernel<64>, grid, dim3(128), smem, st, true, qkv, offsets, list, cnt, e->ctx, H, Lp,
-                   scale_log2e);
-    ++n;
-  }
+  if (fork) ENC_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
   return n;
 }
 
@@ -691,10 +718,12 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
       Layer& L = e->layers[l];
       e->launches += run_linear(e, e->map_x, L.qkv, T, e->box_qkv, nullptr, kEpiBias, st);
       e->launches += launch_attention(e, m, offsets, max_len, st);
+      const bool joined = max_len > kShortLen;    // the stream has just waited for the side stream: plain launch next
       if (H == 2 * kEncBN) {
         // hidden 384 = two feature tiles = the two TMEM accumulators: LayerNorm runs in the projection's
         // epilogue and the result replaces the residual rows of x it was computed from
-        e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln1_g, L.ln1_b);
+        e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln1_g, L.ln1_b,
+                                  !joined);
         e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
         if (2 * ((T + 255) / 256) >= e->num_sms / 2) {
           e->launches += run_linear(e, e->map_h, L.down, T, e->box_x, &e->box_x, kEpiResidualLN, st, L.ln2_g, L.ln2_b);
@@ -705,7 +734,8 @@ int encode_on_device(qre_encoder* e, int m, const int32_t* ids, const int32_t* o
           e->launches += launch_layernorm(e->y, L.ln2_g, L.ln2_b, c.ln_eps, H, T, e->x, st);
         }
       } else {
-        e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_y, &e->box_x, kEpiResidual, st);
+        e->launches += run_linear(e, e->map_ctx, L.out, T, e->box_y, &e->box_x, kEpiResidual, st, nullptr, nullptr,
+                                  !joined);
         e->launches += launch_layernorm(e->y, L.ln1_g, L.ln1_b, c.ln_eps, H, T, e->x, st);
         e->launches += run_linear(e, e->map_x, L.up, T, e->box_h, nullptr, kEpiGelu, st);
         e->launches += run_linear(e, e->map_h, L.down, T, e->box_y, &e->box_x, kEpiResidual, st);
@@ -750,6 +780,9 @@ void destroy(qre_encoder* e) {
   cudaFreeHost(e->h_off);
   cudaFreeHost(e->h_out);
   if (e->stream) cudaStreamDestroy(e->stream);
+  if (e->side) cudaStreamDestroy(e->side);
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
   delete e;
 }
 
@@ -808,6 +841,9 @@ int qre_encoder_create(int device, const qre_encoder_config_t* cfg, int64_t max_
                                  "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__)); \
   } while (0)
   ENC_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  ENC_TRY(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
+  ENC_TRY(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+  ENC_TRY(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
   ENC_TRY(enc_gemm_init());
   const size_t att_s = attention_short_smem(e->hd, kShortLen);
   if (att_s > 48 * 1024) {
