@@ -104,6 +104,44 @@ def test_clustered_cache_of_paraphrases(contiguous):
     assert not np.any(out["flags"] & _cabi.FLAG_OVERFLOW)
 
 
+@pytest.mark.parametrize("live_at", ["first", "middle", "last"])
+def test_masked_twins_outscore_the_live_row(live_at):
+    """The scan appends candidates without looking at the row's context / timestamp and only samples
+    them to lift its gate; the mask is applied in the re-score pass.  Here every live hit (cosine
+    0.88-0.93) shares its 256-row tile with 48 expired or other-context rows that are MORE similar to
+    the query (0.97-0.995) — more than the 8 inline slots and the first spill chunks hold — placed
+    before, around or after it: the gate must never rise above the live row because of rows that do
+    not count, and the winner must be the oracle's."""
+    d, n, m, grp = 384, 24000, 320, 49
+    rs = np.random.Generator(np.random.PCG64(41))
+    w = synth.make_workload(n, m, d, n_centroids=2, seed=9, n_ctx=2, frac_expired=0.0, n_zero_q=0, n_zero_rows=0,
+                            frac_planted=0.0, frac_dup=0.0, frac_near=0.0)
+    q = w.queries / np.linalg.norm(w.queries, axis=1, keepdims=True)
+    w.q_ctx[:] = synth.ctx_id(0)
+    w.row_ctx[:] = synth.ctx_id(0)
+    n_hit = 300
+    starts = rs.permutation(n // 64)[:n_hit] * 64
+    for i, p0 in enumerate(starts):
+        live = {"first": 0, "middle": grp // 2, "last": grp - 1}[live_at]
+        for j in range(grp):
+            if j == live:
+                w.rows[p0 + j] = synth.plant(q[i][None, :], np.array([rs.uniform(0.88, 0.93)]), rs)[0] * 1.7
+            else:
+                w.rows[p0 + j] = synth.plant(q[i][None, :], np.array([rs.uniform(0.97, 0.995)]), rs)[0]
+                if j % 2:
+                    w.row_ctx[p0 + j] = synth.ctx_id(1)
+                else:
+                    w.row_ts_us[p0 + j] = w.now_us - w.ttl_us - 7
+    out = _run(w, 0.85)
+    exp_row, exp_sim = _oracle(w, 0.85)
+    assert (exp_row[:n_hit] >= 0).all() and (exp_row[n_hit:] < 0).all()
+    _compare(out, exp_row, exp_sim, w, 0.85)
+    assert np.array_equal(out["hit_slot"], exp_row)
+    assert not np.any(out["flags"] & _cabi.FLAG_OVERFLOW)
+    out_e = _run(w, 0.85, scan_mode=_cabi.SCAN_EXACT)
+    assert np.array_equal(out["hit_slot"], out_e["hit_slot"]) and np.array_equal(out["hit_sim"], out_e["hit_sim"])
+
+
 def test_empty_cache_and_nan_queries():
     w = synth.make_workload(300, 16, 384, n_centroids=2, seed=5, n_ctx=2, frac_planted=0.9, n_zero_q=0)
     empty = synth.make_workload(0, 16, 384, n_centroids=2, seed=5, rows=np.zeros((0, 384), np.float32))
