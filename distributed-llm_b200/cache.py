@@ -481,27 +481,42 @@ class QueryCache:
             cfg.similarity_threshold = float(self.similarity_threshold)
             cfg.ttl_us = self._ttl_us()
             step = max(1, int(getattr(self._engine, "max_batch", 64)))
-            outs = []
-            for i0 in range(0, len(queries), step):
-                sl = slice(i0, min(len(queries), i0 + step))
-                ri = None if route_in is None else {k: v[sl] for k, v in route_in.items()}
-                outs.append(self._engine.scan(q_embs[sl], ctx[sl], _to_us(now), cfg, ri))
-            out = {k: np.concatenate([o[k] for o in outs]) for k in outs[0]} if outs else {}
-            results: List[Optional[CacheLookupResult]] = []
-            if keys is None:                         # one md5 per query (or handed in by the C++ feature pass)
-                keys = [self._make_hash(q, c) for q, c in zip(queries, context_keys)]
+
+            def host_side():
+                # what does not need the device's answer: the exact-match keys (one md5 per query,
+                # unless the C++ feature pass handed them in) and the cache's own copy of the
+                # embedding block, which a later insert_batch of this batch keeps
+                nonlocal keys
+                if keys is None:
+                    keys = [self._make_hash(q, c) for q, c in zip(queries, context_keys)]
+                else:
+                    keys = [k if k is not None else self._make_hash(q, c)
+                            for k, q, c in zip(keys, queries, context_keys)]
+                side["emb"] = np.array(q_embs, dtype=np.float32, copy=True) if route_in is not None else None
+
+            side: Dict[str, Any] = {"emb": None}
+            overlapped = getattr(self._engine, "scan_overlapped", None)
+            if overlapped is not None and 0 < len(queries) <= step:
+                out = overlapped(q_embs, ctx, _to_us(now), cfg, route_in, host_side)    # host_side runs under the scan
             else:
-                keys = [k if k is not None else self._make_hash(q, c)
-                        for k, q, c in zip(keys, queries, context_keys)]
-            self._batch_keys = keys
+                outs = []
+                for i0 in range(0, len(queries), step):
+                    sl = slice(i0, min(len(queries), i0 + step))
+                    ri = None if route_in is None else {k: v[sl] for k, v in route_in.items()}
+                    outs.append(self._engine.scan(q_embs[sl], ctx[sl], _to_us(now), cfg, ri))
+                out = {k: np.concatenate([o[k] for o in outs]) for k in outs[0]} if outs else {}
+                host_side()
+            results: List[Optional[CacheLookupResult]] = []
             with self._deferred():
-                self._apply_batch_hits(queries, context_keys, out, now, results)
+                self._apply_batch_hits(queries, context_keys, keys, out, now, results)
+            # the batch's keys and the private embedding copy travel with the device outputs (by value:
+            # another thread's batch may run before the caller has finished with this one)
+            out["_keys"], out["_emb"] = keys, side["emb"]
             return results, out
 
-    def _apply_batch_hits(self, queries, context_keys, out, now, results) -> None:
+    def _apply_batch_hits(self, queries, context_keys, keys, out, now, results) -> None:
         """Host bookkeeping of a batch's hits, in order (exact-hash match first, then the device
         scan's row), as `lookup` does for one query."""
-        keys = self._batch_keys
         slots = out["hit_slot"].tolist() if self.use_semantic else [-1] * len(queries)
         store, slot_key = self._store, self._slot_key
         ttl = self.ttl_seconds
@@ -576,7 +591,8 @@ class QueryCache:
 
     def insert_batch(self, queries: Sequence[str], context_keys: Sequence[str], devices: Sequence[str],
                      confidences: Sequence[float], method: str = "unknown",
-                     q_embs: Optional[np.ndarray] = None, *, _keys: Optional[List[str]] = None) -> None:
+                     q_embs: Optional[np.ndarray] = None, *, _keys: Optional[List[str]] = None,
+                     _emb_owned: Optional[np.ndarray] = None) -> None:
         """Additive batch form of `insert` (the reference inserts one entry per call,
         cache.py:328): the same entries, in the same order, as a loop of `insert`, with the host
         bookkeeping of brand-new entries done without per-entry device calls or per-entry array
@@ -588,7 +604,11 @@ class QueryCache:
             return
         keys = _keys if _keys is not None else [self._make_hash(q, c) for q, c in zip(queries, context_keys)]
         with self._lock, self._deferred():
-            emb = None if q_embs is None else np.array(q_embs, dtype=np.float32, copy=True)
+            if (_emb_owned is not None and _emb_owned.dtype == np.float32 and _emb_owned.ndim == 2
+                    and _emb_owned.shape[0] == n and _emb_owned.flags.c_contiguous):
+                emb = _emb_owned                     # a private copy made earlier (under the device pass)
+            else:
+                emb = None if q_embs is None else np.array(q_embs, dtype=np.float32, copy=True)
             if emb is None or emb.ndim != 2:
                 for i in range(n):
                     self.insert(queries[i], context_keys[i], devices[i], confidences[i], method,

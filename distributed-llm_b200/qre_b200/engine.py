@@ -140,6 +140,29 @@ class Engine:
                                heur_conf=route_in["heur_conf"])
 
 
+    @_locked
+    def scan_overlapped(self, q, q_ctx, now_us: int, cfg: _cabi.RouteConfig, route_in: Optional[dict],
+                        host_work) -> dict:
+        """`scan` with the caller's `host_work()` run on this thread while the GPU is busy with the
+        batch (begin -> host_work -> end, all under the handle's lock): host bookkeeping that does
+        not need the results — copying the embedding block the cache will keep — costs no wall time."""
+        q = np.ascontiguousarray(q, np.float32)
+        if q.ndim == 1:
+            q = q.reshape(1, -1)
+        sh = self.ensure(q.shape[1])
+        if q.shape[0] > sh.max_batch:
+            raise _cabi.QreError(f"batch of {q.shape[0]} exceeds max_batch={sh.max_batch}")
+        cfg.scan_mode = self.scan_mode
+        kw = {} if route_in is None else dict(tok=route_in["tok"], heur_dev=route_in["heur_dev"],
+                                              heur_conf=route_in["heur_conf"])
+        sh.lookup_route_begin(0, q, q_ctx, cfg, now_us, **kw)
+        try:
+            host_work()
+        finally:
+            out = sh.lookup_route_end(0)
+        return out
+
+
 class ShardedEngine:
     """The same store interface over SEVERAL GPUs driven by one process (`config["gpus"] = [0, 1, ..]`):
     one `Engine` per GPU, rows dealt round-robin, slots numbered `local_slot * n + shard` so the

@@ -646,7 +646,7 @@ class QueryRouter:
         r = self.router
         decisions: List[RoutingDecision] = []
         threshold = int(self.config.get("heuristic_context_chars", 800))
-        keys = self._cache._batch_keys
+        keys, own_emb = out.get("_keys"), out.get("_emb")
         now = datetime.now()
         cached_method = f"{self.strategy_name}_cached"
         if hybrid:
@@ -668,7 +668,8 @@ class QueryRouter:
                 d.__dict__ = {"device": dev_names[i], "confidence": confs[i], "method": "hybrid",
                               "complexity_score": None, "cache_hit": False, "_lazy": (why, i)}
                 decisions.append(d)
-            self._cache.insert_batch(list(queries), ctxks, dev_names, confs, "hybrid", q_embs, _keys=keys)
+            self._cache.insert_batch(list(queries), ctxks, dev_names, confs, "hybrid", q_embs, _keys=keys,
+                                     _emb_owned=own_emb)
             return decisions
         ins: List[int] = []                  # batch indices to insert, in order (all lookups came first)
         new_obj, lazy_cls, nano = object.__new__, LazyRoutingDecision, DEVICE_NAMES[0]
@@ -705,9 +706,11 @@ class QueryRouter:
             routed_d = pick(decisions)
             methods = {d.method for d in routed_d}
             if len(methods) == 1:
+                own = own_emb
                 self._cache.insert_batch(pick(list(queries)), pick(ctxks), [d.device for d in routed_d],
                                          [d.confidence for d in routed_d], methods.pop(),
-                                         q_embs if whole else q_embs[ins], _keys=pick(keys))
+                                         q_embs if whole else q_embs[ins], _keys=pick(keys),
+                                         _emb_owned=own if (whole or own is None) else own[ins])
             else:
                 for i in ins:
                     d = decisions[i]

@@ -28,6 +28,8 @@ def main():
     ap.add_argument("--entries", type=int, default=1_000_000)
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--rounds", type=int, default=5)
+    ap.add_argument("--sections", action="store_true",
+                    help="also report where a batch's time goes (wall-clock wrappers around the stages)")
     a = ap.parse_args()
     import query_router_engine as Q
     from qre_b200 import synth
@@ -46,6 +48,28 @@ def main():
     eng.append_many(rows, np.full(n0, 999, np.uint64), np.zeros(n0, np.int64), np.arange(1, n0 + 1, dtype=np.uint64),
                     np.zeros(n0, np.uint8), np.ones(n0))
     load_s = time.perf_counter() - t0
+    sec = {}
+    if a.sections:
+        import functools
+        import cache as cache_mod
+        from qre_b200 import _cabi
+
+        def wrap(obj, name, label=None):
+            f = getattr(obj, name)
+
+            @functools.wraps(f)
+            def g(*aa, **kk):
+                t = time.perf_counter()
+                try:
+                    return f(*aa, **kk)
+                finally:
+                    sec[label or name] = sec.get(label or name, 0.0) + time.perf_counter() - t
+            setattr(obj, name, g)
+        wrap(cache_mod.QueryCache, "insert_batch"); wrap(cache_mod.QueryCache, "_batch_pass")
+        wrap(cache_mod.QueryCache, "_apply_batch_hits"); wrap(cache_mod.QueryCache, "_flush")
+        wrap(Q.QueryRouter, "_finish_batch"); wrap(_cabi, "host_features_packed")
+        wrap(type(eng), "scan", "engine.scan"); wrap(type(eng), "append_many", "engine.append_many")
+        wrap(type(eng), "update_many", "engine.update_many")
     words = ["alpha", "beta", "gamma", "delta", "what is", "implement", "compare", "hello", "report", "weather"]
     res = []
     for r in range(a.rounds):
@@ -58,8 +82,11 @@ def main():
         t2 = time.perf_counter()
         res.append(dict(miss_pass_qps=a.batch / (t1 - t0), cached_pass_qps=a.batch / (t2 - t1),
                         cached=sum(x.method.endswith("_cached") for x in dec2), routed=sum(x.method == "hybrid" for x in dec)))
-    print(json.dumps({"workload": f"route_queries, batch {a.batch}, {a.entries} filler rows on the device",
-                      "bulk_load_s": load_s, "rounds": res}))
+    out = {"workload": f"route_queries, batch {a.batch}, {a.entries} filler rows on the device",
+           "bulk_load_s": load_s, "rounds": res}
+    if a.sections:
+        out["ms_per_batch_by_stage_avg_of_both_passes"] = {k: round(v / (2 * a.rounds) * 1e3, 3) for k, v in sec.items()}
+    print(json.dumps(out))
 
 
 if __name__ == "__main__":
