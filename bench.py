@@ -114,7 +114,11 @@ class ClockSampler:
                 sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
                 rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                self.rows.append((time.perf_counter(), float(sm), pw, int(rs)))
+                try:
+                    en = float(nv.nvmlDeviceGetTotalEnergyConsumption(self.h))      # mJ since the driver loaded
+                except Exception:       # noqa: BLE001
+                    en = float("nan")
+                self.rows.append((time.perf_counter(), float(sm), pw, int(rs), en))
             except Exception:           # noqa: BLE001
                 pass
             self._stop.wait(self.period)
@@ -151,6 +155,11 @@ class ClockSampler:
                "power_w_median": float(np.median([r[2] for r in inside])) if inside else None,
                "power_w_max": float(max(r[2] for r in inside)) if inside else None,
                "reasons": sorted(reasons), "source": "NVML in-process"}
+        # board energy over the timed region from NVML's cumulative counter (the power READING above
+        # is a ~1 s moving average and lags a short region badly; the counter does not)
+        ej = [(r[0], r[4]) for r in inside if len(r) > 4 and r[4] == r[4]]
+        if len(ej) >= 2 and ej[-1][0] > ej[0][0] and ej[-1][1] > ej[0][1]:     # (the counter ticks every ~100 ms)
+            out["board_w_from_energy_counter"] = (ej[-1][1] - ej[0][1]) / 1e3 / (ej[-1][0] - ej[0][0])
         if note:
             out["note"] = note
         if trace_path:
@@ -446,6 +455,9 @@ def run_b200(args):
     barrier()
     sampler.mark(t_begin, time.perf_counter())
     clocks = sampler.stop(args.trace_clocks if rank == 0 else "")
+    if clocks.get("board_w_from_energy_counter") is not None:
+        # joules per batch on THIS rank's GPU (NVML energy counter over the timed region)
+        clocks["energy_j_per_step"] = clocks["board_w_from_energy_counter"] * (sampler.window[1] - t_begin) / max(args.steps, 1)
     launches = sh.launch_count() - l0
     scan_ms, scan_n = sh.profile_read()
     sh.profile(False)

@@ -31,6 +31,8 @@ def run(dim, n, m, k, d_):
 
 if __name__ == "__main__":
     print("hits", run(384, 1500, 300, 8, 2), run(384, 700, 40, 2, 2), run(768, 900, 140, 16, 4), run(64, 300, 7, 2, 2))
+    # more work units than CTAs: the scans claim units dynamically (pair kernel, then streaming-A single-CTA)
+    print("hits (claimed units)", run(384, 20000, 2100, 8, 2), run(768, 42000, 700, 8, 2))
     import torch
     w = synth.make_workload(2000, 8, 384, n_centroids=2, seed=3)
     dev = torch.device("cuda", 0)
