@@ -701,8 +701,14 @@ class QueryCache:
                 vecs = list(embedder.encode([q for q, _, _ in pairs]))
             except Exception as exc:
                 logger.warning("warm_up: embedding failed, inserting without vectors: %s", exc)
-        for (q, ctx, dev), v in zip(pairs, vecs):
-            self.insert(q, ctx, dev, q_emb=v)
+        if pairs and all(v is not None for v in vecs):
+            # the same entries in the same order as the loop below, with one device append
+            self.insert_batch([q for q, _, _ in pairs], [c for _, c, _ in pairs], [d for _, _, d in pairs],
+                              [1.0] * len(pairs), "unknown", np.asarray(vecs, dtype=np.float32))
+        else:
+            with self._deferred():
+                for (q, ctx, dev), v in zip(pairs, vecs):
+                    self.insert(q, ctx, dev, q_emb=v)
         logger.info("cache warmed up with %d entries", len(pairs))
 
     # ------------------------------------------------------------------ persistence

@@ -125,3 +125,34 @@ def test_packed_features_equal_pointer_form_and_keys_equal_md5():
     # without context keys no key is computed; an empty batch is fine
     assert "keys" not in _cabi.host_features_packed(qs[:5], clen[:5], hp)
     assert _cabi.host_features_packed([], [], hp, context_keys=[])["keys"] == []
+
+
+def test_warm_up_equals_insert_loop_with_and_without_vectors():
+    """warm_up (reference cache.py:398-420) goes through insert_batch when the embedder delivers; an
+    embedder that fails leaves entries without vectors, as in the reference."""
+    clock = ref_harness.FakeClock()
+    cache_mod, _, _ = R.load_modules(clock, OracleEngine)
+    rs = np.random.Generator(np.random.PCG64(12))
+    pairs = [(f"warm {i % 9}", "c" if i % 3 else "d", "orin" if i % 2 else "nano") for i in range(14)]   # repeats refresh
+    table = {q: rs.standard_normal(24).astype(np.float32) for q, _, _ in pairs}
+
+    class Emb:
+        def encode(self, texts):
+            return np.stack([table[t] for t in texts])
+
+    class Broken:
+        def encode(self, texts):
+            raise RuntimeError("no model")
+
+    a = cache_mod.QueryCache(max_size=32, ttl_seconds=50, engine=OracleEngine(capacity=32, dim=24))
+    b = cache_mod.QueryCache(max_size=32, ttl_seconds=50, engine=OracleEngine(capacity=32, dim=24))
+    a.warm_up(pairs, Emb())
+    for q, c, d in pairs:
+        b.insert(q, c, d, q_emb=table[q])
+    _same_state(a, b)
+    r = a.lookup("warm 4 paraphrase", "c", table["warm 4"] * 3)
+    assert r is not None and r.entry.query == "warm 4"
+    e = cache_mod.QueryCache(max_size=32, ttl_seconds=50, engine=OracleEngine(capacity=32, dim=24))
+    e.warm_up(pairs, Broken())
+    assert len(e._store) == len({(q, c) for q, c, _ in pairs}) and all(x.embedding is None for x in e._store.values())
+    assert e.lookup("warm 4", "c") is not None and e.lookup("warm 4 paraphrase", "c", table["warm 4"]) is None
