@@ -734,7 +734,7 @@ class QueryCache:
             logger.error("cache load: bad JSON: %s", exc)
             return 0
         loaded = 0
-        with self._lock:
+        with self._lock, self._deferred():       # the rows reach the device in one append at the end
             now = datetime.now()
             for d in raw:
                 try:
@@ -749,7 +749,9 @@ class QueryCache:
                     entry._seq = old._seq
                     if old._slot is not None:
                         self._slot_key.pop(old._slot, None)
-                        self._engine.tombstone([old._slot])
+                        self._defer["tomb"].append(old._slot)
+                        self._defer["lru"].pop(old._slot, None)
+                        old._slot = None
                     self._store[entry.query_hash] = entry
                 else:
                     self._store[entry.query_hash] = entry
@@ -832,6 +834,9 @@ class QueryCache:
         if eng.shard is not None:
             eng.close()
         eng.capacity = new_cap
+        if self._defer is not None:                  # queued row operations named slots of the old store
+            self._defer["tomb"].clear()
+            self._defer["lru"].clear()
         self._slot_key.clear()
         for e in self._store.values():
             e._slot = None

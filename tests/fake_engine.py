@@ -14,7 +14,6 @@ class OracleEngine:
         self.capacity = capacity
         self.dim = dim
         self.max_batch = max_batch
-        self.shard = None
         self.rows = np.zeros((capacity, dim), np.float32)
         self.ctx = np.full(capacity, O.CTX_TOMBSTONE, np.uint64)
         self.ts = np.zeros(capacity, np.int64)
@@ -24,6 +23,11 @@ class OracleEngine:
         self.hwm, self.free = 0, []
         self._centroids = self._owner = None
         self.calls = 0
+
+    @property
+    def shard(self):
+        """Truthy once rows exist (the real Engine creates its device handle lazily; callers only test for None)."""
+        return self if self.hwm else None
 
     def close(self):
         self.clear()

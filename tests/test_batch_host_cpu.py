@@ -156,3 +156,34 @@ def test_warm_up_equals_insert_loop_with_and_without_vectors():
     e.warm_up(pairs, Broken())
     assert len(e._store) == len({(q, c) for q, c, _ in pairs}) and all(x.embedding is None for x in e._store.values())
     assert e.lookup("warm 4", "c") is not None and e.lookup("warm 4 paraphrase", "c", table["warm 4"]) is None
+
+
+def test_load_replaces_rows_in_one_deferred_flush(tmp_path):
+    """load() (reference cache.py:434-465) over a cache that already holds some of the keys: the
+    file's rows replace them (the old vectors no longer hit), new keys are appended, entries that
+    are not in the file stay, and a file larger than the store grows it — all mirrored to the device
+    through one deferred flush."""
+    clock = ref_harness.FakeClock()
+    cache_mod, _, _ = R.load_modules(clock, OracleEngine)
+    rs = np.random.Generator(np.random.PCG64(13))
+    d = 16
+    va, vb = rs.standard_normal((6, d)).astype(np.float32), rs.standard_normal((4, d)).astype(np.float32)
+    a = cache_mod.QueryCache(max_size=8, ttl_seconds=100, engine=OracleEngine(capacity=8, dim=d))
+    for i in range(6):
+        a.insert(f"k{i}", "c", "orin", 0.9, "hybrid", va[i])
+    path = str(tmp_path / "a.json")
+    a.save(path)
+    b = cache_mod.QueryCache(max_size=4, ttl_seconds=100, engine=OracleEngine(capacity=4, dim=d))
+    for i, q in enumerate(["k1", "k4", "own0", "own1"]):
+        b.insert(q, "c", "nano", 0.9, "hybrid", vb[i])
+    assert b.load(path) == 6 and len(b._store) == 8               # 4 + 6 - 2 shared keys; grew past max_size
+    for i in range(6):                                            # every file row is what the device now scans
+        r = b.lookup("paraphrase", "c", va[i] * 2)
+        assert r is not None and r.entry.query == f"k{i}" and r.predicted_device == "orin"
+    for i, q in enumerate(["k1", "k4"]):                          # the replaced vectors are gone
+        r = b.lookup("paraphrase", "c", vb[i])
+        assert r is None or r.entry.query != q
+    for i, q in enumerate(["own0", "own1"], start=2):             # untouched entries still hit
+        r = b.lookup("paraphrase", "c", vb[i])
+        assert r is not None and r.entry.query == q
+    assert sorted(b._slot_key.values()) == sorted(b._store)
