@@ -371,12 +371,14 @@ class QueryCache:
         with self._lock:
             now_us = _to_us(datetime.now() if now is None else now)
             self._collect_stale(now_us)
-            while True:
-                key = self._pop_stale(now_us)
-                if key is None:
-                    break
-                self._delete_entry(key)
-                self._evictions += 1
+            key = self._pop_stale(now_us)
+            if key is None:
+                return
+            with self._deferred():                   # a wave of expiries frees its device rows in one call
+                while key is not None:
+                    self._delete_entry(key)
+                    self._evictions += 1
+                    key = self._pop_stale(now_us)
 
     def _evict_one(self, now: datetime) -> None:
         """At capacity: first expired entry in LRU order, else the LRU front
@@ -688,8 +690,9 @@ class QueryCache:
             doomed = [k for k, e in self._store.items()
                       if (context_key is None or e.context_key == context_key)
                       and (rx is None or rx.search(e.query))]
-            for k in doomed:
-                self._delete_entry(k)
+            with self._deferred():                   # one tombstone call for the lot
+                for k in doomed:
+                    self._delete_entry(k)
         logger.debug("invalidate removed %d entries", len(doomed))
         return len(doomed)
 
