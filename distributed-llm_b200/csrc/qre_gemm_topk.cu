@@ -11,13 +11,15 @@
 //   * a single elected thread issues tcgen05.mma (M=128, N=256, K=16, bf16 -> fp32) into one
 //     of two 256-column TMEM accumulators, so the epilogue of tile t overlaps the MMAs of t+1;
 //   * four epilogue warps read their 32 TMEM lanes with tcgen05.ld (one lane = one query),
-//     reduce each 64-column chunk to its max and compare with the query's current k-th best
-//     (initialised to the hit floor thr-eps): only chunks that can still matter take the slow
-//     path (context / TTL mask from RowMeta, insertion into the top-k).
+//     reduce each 64-column chunk to its max and compare with the query's gate (initialised
+//     to the hit floor thr-eps): only chunks that can still matter take the slow path (append
+//     the candidate to the (query, range)'s list; the context / TTL mask from RowMeta is applied
+//     by the re-score kernel, qre_scan_epilogue.cuh).
 //
-// Units are ordered row-range-major (u = s * mblocks + mb) and dealt round-robin, so at any
-// moment the resident CTAs sweep the SAME rows for different query blocks and the 32 re-reads
-// of each cache-row tile are served by L2, not HBM.
+// Units are ordered row-range-major (u = s * mblocks + mb); a CTA's first unit is static, the
+// rest are claimed from a global counter, so at any moment the resident CTAs sweep the SAME rows
+// for different query blocks — also when some units take longer than others — and the 32
+// re-reads of each cache-row tile are served by L2, not HBM.
 #include <stdio.h>
 
 #include <algorithm>
