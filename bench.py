@@ -25,6 +25,7 @@ Prints ONE JSON line (rank 0).  Keys: see the task contract; additionally
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import sys
@@ -444,6 +445,11 @@ def run_b200(args):
     sh.profile(True)
     l0 = sh.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # The host loops of the timed regions run with Python's cyclic collector paused: with several
+    # ranks a batch starts only when every rank has queued it, and one rank's collection pause
+    # would be charged to all of them (a C or C++ host has no such pauses).
+    gc_was_on = gc.isenabled()
+    gc.disable()
     t_begin = time.perf_counter()
     e0.record()
     for _ in range(args.steps):
@@ -452,6 +458,8 @@ def run_b200(args):
     if pipelined:
         look.drain()
     e1.record()
+    if gc_was_on:
+        gc.enable()
     barrier()
     sampler.mark(t_begin, time.perf_counter())
     clocks = sampler.stop(args.trace_clocks if rank == 0 else "")
@@ -487,15 +495,19 @@ def run_b200(args):
         sh.lookup_route_begin(slot, hq["Q"], hq["ctx"], cfg_h, NOW_US, tok=hq["tok"], heur_dev=hq["hd"],
                               heur_conf=hq["hc"])
 
+    e2e_out = [None, None, None]
+
     def run_e2e(n):
         # three batches in flight (begin i+2 before end i): with several ranks the batch only starts
         # once EVERY rank has submitted it, so one late host thread would otherwise idle all GPUs
+        # (the result arrays of a slot are handed back to be refilled, as a C caller would keep its own)
         r = None
         for i in range(n + 2):
             if i < n:
                 begin(i % 3)
             if i >= 2:
-                r = sh.lookup_route_end((i - 2) % 3)
+                s_ = (i - 2) % 3
+                r = e2e_out[s_] = sh.lookup_route_end(s_, e2e_out[s_])
         return r
     e2e_ok = look.exchange == "p2p" or world == 1     # the library's own exchange is the peer-store one
     if e2e_ok:
@@ -506,17 +518,21 @@ def run_b200(args):
         assert np.array_equal(r["hit_slot"][q0:q1], hit_slot[q0:q1]) and np.array_equal(r["dev"][q0:q1], out["dev"][q0:q1])
         h2d = int(sum(v.numel() * v.element_size() for v in h.values())) * (1 if sliced else world)
         barrier()
+        gc.disable()
         t0 = time.perf_counter()
         run_e2e(args.steps)
         torch.cuda.synchronize()
         t_e2e = time.perf_counter() - t0
+        if gc_was_on:
+            gc.enable()
         if world > 1:
             import torch.distributed as dist
             t = torch.tensor([t_e2e], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             t_e2e = float(t.item())
         e2e = {"value": M * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "host_buffers": "page-locked (copied straight from the caller's arrays)"}
+               "d2h_bytes_per_step": d2h, "host_buffers": "page-locked (copied straight from the caller's arrays)",
+               "host_loop": "three batches in flight, result arrays reused per slot, Python GC paused"}
         if world == 1:
             # the same call with PAGEABLE inputs (what a plain numpy caller passes): the library stages
             # them through its own pinned buffer first

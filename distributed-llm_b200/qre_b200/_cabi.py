@@ -259,7 +259,7 @@ class Shard:
 
     def lookup_route_begin(self, slot: int, queries, q_ctx, cfg: RouteConfig, now_us: int, tok=None,
                            heur_dev=None, heur_conf=None, want_cand: bool = False) -> None:
-        """Enqueue one batch on host slot 0/1 and return; pair with `lookup_route_end(slot)`.
+        """Enqueue one batch on host slot 0 / 1 / 2 and return; pair with `lookup_route_end(slot)`.
         The arrays must stay alive and unchanged until then (they are kept referenced here)."""
         q = _arr(queries, np.float32)
         m = q.shape[0]
@@ -278,9 +278,14 @@ class Shard:
             self._inflight = {}
         self._inflight[slot] = (m, do_route, cfg.n_devices, want_cand, (q, q_ctx, tok, heur_dev, heur_conf))
 
-    def lookup_route_end(self, slot: int) -> dict:
+    def lookup_route_end(self, slot: int, out: Optional[dict] = None) -> dict:
+        """Wait for the batch begun on `slot` and return its result arrays.  `out`: a dict returned
+        by an earlier `lookup_route_end` for a batch of the same shape, to be filled again instead of
+        allocating fresh arrays (the C call writes into the caller's arrays either way)."""
         m, do_route, D, want_cand, _keep = self._inflight.pop(slot)
-        out = self._host_outputs(m, do_route, D, want_cand)
+        if out is None or out["hit_slot"].shape[0] != m or ("dev" in out) != do_route or ("cand" in out) != want_cand \
+                or (do_route and out["score"].shape[1] != D):
+            out = self._host_outputs(m, do_route, D, want_cand)
         res = Result(**{f: _ptr(out.get(f)) for f in RESULT_FIELDS})
         _check(self.lib, self.lib.qre_lookup_route_end(self.h, C.c_int(slot), C.byref(res)))
         return out
