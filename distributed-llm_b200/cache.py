@@ -471,7 +471,7 @@ class QueryCache:
 
     def _batch_pass(self, queries: List[str], context_keys: List[str], q_embs: np.ndarray,
                     route_in: Optional[dict], route_cfg: Optional[_cabi.RouteConfig],
-                    keys: Optional[List[Optional[str]]] = None):
+                    keys: Optional[List[Optional[str]]] = None, as_tuples: bool = False):
         """Snapshot lookup of a whole batch (+ routing epilogue when `route_in` is given) in one
         device pass per `max_batch` chunk.  Returns (results, device outputs)."""
         with self._lock:
@@ -510,13 +510,13 @@ class QueryCache:
                 host_side()
             results: List[Optional[CacheLookupResult]] = []
             with self._deferred():
-                self._apply_batch_hits(queries, context_keys, keys, out, now, results)
+                self._apply_batch_hits(queries, context_keys, keys, out, now, results, as_tuples)
             # the batch's keys and the private embedding copy travel with the device outputs (by value:
             # another thread's batch may run before the caller has finished with this one)
             out["_keys"], out["_emb"] = keys, side["emb"]
             return results, out
 
-    def _apply_batch_hits(self, queries, context_keys, keys, out, now, results) -> None:
+    def _apply_batch_hits(self, queries, context_keys, keys, out, now, results, as_tuples=False) -> None:
         """Host bookkeeping of a batch's hits, in order (exact-hash match first, then the device
         scan's row), as `lookup` does for one query."""
         slots = out["hit_slot"].tolist() if self.use_semantic else [-1] * len(queries)
@@ -556,6 +556,9 @@ class QueryCache:
             fb = pconf < thr
             if fb:
                 self._hybrid_fallbacks += 1
+            if as_tuples:                              # the router's batch path unpacks it at once
+                append((entry, pdev, pconf, fb))
+                continue
             r = new_obj(CacheLookupResult)
             r.__dict__ = {"entry": entry, "predicted_device": pdev, "predicted_confidence": pconf,
                           "use_hybrid_fallback": fb}

@@ -638,7 +638,8 @@ class QueryRouter:
                             heur_dev=np.array([h[0] for _, h in feats], np.uint8),
                             heur_conf=np.array([h[1] for _, h in feats], np.float64))
         with _gc_paused():
-            results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg(), keys)
+            results, out = self._cache._batch_pass(list(queries), ctxks, q_embs, route_in, sem._route_cfg(), keys,
+                                                   as_tuples=True)
             with self._cache._deferred():        # all inserts of the batch reach the device in a few calls
                 return self._finish_batch(queries, contexts, ctxks, q_embs, feats, results, out, hybrid)
 
@@ -673,25 +674,24 @@ class QueryRouter:
             return decisions
         ins: List[int] = []                  # batch indices to insert, in order (all lookups came first)
         new_obj, lazy_cls, nano = object.__new__, LazyRoutingDecision, DEVICE_NAMES[0]
-        for i, (q, c, k) in enumerate(zip(queries, contexts, ctxks)):
-            res = results[i]
+        for i, c in enumerate(contexts):
+            res = results[i]                 # None, or (entry, predicted device, its confidence, weak prediction)
             routed = None
             if res is not None:
+                e, pdev, pconf, weak = res
                 context_len = len(c) if c else 0
-                heavy_ctx = context_len >= threshold and res.predicted_device == nano
-                if not (heavy_ctx or res.use_hybrid_fallback):
+                heavy_ctx = context_len >= threshold and pdev == nano
+                if not (heavy_ctx or weak):
                     # the figures the reasoning quotes are taken NOW (hit count / history may move on)
-                    e = res.entry
                     d = new_obj(lazy_cls)
-                    d.__dict__ = {"device": res.predicted_device, "confidence": res.predicted_confidence,
-                                  "method": cached_method, "complexity_score": None, "cache_hit": True,
-                                  "_lazy": (_cached_why, (now, e.timestamp, e.hit_count, res.predicted_device,
-                                                          res.predicted_confidence, context_len,
+                    d.__dict__ = {"device": pdev, "confidence": pconf, "method": cached_method,
+                                  "complexity_score": None, "cache_hit": True,
+                                  "_lazy": (_cached_why, (now, e.timestamp, e.hit_count, pdev, pconf, context_len,
                                                           len(e.routing_history)))}
                     decisions.append(d)
                     continue
                 reason = (f"context_len={context_len}>={threshold} overrides cached nano" if heavy_ctx
-                          else f"low prediction confidence={res.predicted_confidence:.2f}")
+                          else f"low prediction confidence={pconf:.2f}")
                 routed = self._routed(i, feats, out, hybrid)
                 routed.reasoning = f"cache hit (hybrid re-route: {reason}) | " + routed.reasoning
                 routed.cache_hit = True
