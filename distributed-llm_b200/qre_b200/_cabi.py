@@ -36,7 +36,7 @@ EXPORTS = (
     # include/qre_encoder_b200.h
     "qre_encoder_create", "qre_encoder_destroy", "qre_encoder_set_embeddings", "qre_encoder_set_layer",
     "qre_encode", "qre_encode_dev", "qre_encoder_launch_count", "qre_encoder_debug_gemm",
-    "qre_wordpiece_create", "qre_wordpiece_destroy", "qre_wordpiece_encode",
+    "qre_wordpiece_create", "qre_wordpiece_destroy", "qre_wordpiece_encode", "qre_wordpiece_encode_packed",
 )
 
 
@@ -660,12 +660,18 @@ class WordPiece:
     def encode(self, texts, max_len: int = 256, n_threads: int = 0):
         """-> (ids int32 [total], lens int32 [n]); lens[i] == -1 marks a text this tokenizer declined."""
         n = len(texts)
-        raw = [t.encode("utf-8") for t in texts]
-        arr = (C.c_char_p * n)(*raw)
-        tl = np.fromiter((len(b) for b in raw), np.int64, n)
+        # one blob + offsets (qre_wordpiece_encode_packed): n bytes objects and n pointers cost more
+        # Python time than the C++ threads need to tokenise
+        blob = "".join(texts).encode("utf-8")
+        tl = np.fromiter(map(len, texts), np.int64, n)
+        if n and int(tl.sum()) != len(blob):             # some text is not ASCII: byte lengths differ
+            tl = np.fromiter((len(t.encode("utf-8")) for t in texts), np.int64, n)
+        off = np.zeros(n + 1, np.int64)
+        np.cumsum(tl, out=off[1:])
         cap = int(np.minimum(tl + 2, max_len).sum()) if n else 0
         ids = np.empty(max(cap, 1), np.int32)
         lens = np.empty(n, np.int32)
-        _check(self._lib, self._lib.qre_wordpiece_encode(self._h, C.c_int64(n), arr, _ptr(tl), C.c_int(max_len),
-                                                         _ptr(ids), C.c_int64(cap), _ptr(lens), C.c_int(n_threads)))
+        _check(self._lib, self._lib.qre_wordpiece_encode_packed(self._h, C.c_int64(n), C.c_char_p(blob), _ptr(off),
+                                                                C.c_int(max_len), _ptr(ids), C.c_int64(cap),
+                                                                _ptr(lens), C.c_int(n_threads)))
         return ids[: int(lens[lens > 0].sum())], lens

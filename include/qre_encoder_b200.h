@@ -115,6 +115,11 @@ QRE_API int qre_wordpiece_destroy(qre_wordpiece_t* t);
 QRE_API int qre_wordpiece_encode(const qre_wordpiece_t* t, int64_t n, const char* const* texts,
                                  const int64_t* text_len, int max_len, int32_t* ids_out, int64_t cap,
                                  int32_t* lens_out, int n_threads);
+/* The same with the texts in ONE byte blob: text i = blob[offsets[i] .. offsets[i+1]), n + 1 offsets
+ * (what a Python caller builds with one join + encode instead of n byte strings and n pointers). */
+QRE_API int qre_wordpiece_encode_packed(const qre_wordpiece_t* t, int64_t n, const char* blob,
+                                        const int64_t* offsets, int max_len, int32_t* ids_out, int64_t cap,
+                                        int32_t* lens_out, int n_threads);
 
 #ifdef __cplusplus
 }

@@ -109,3 +109,33 @@ def test_product_unicode_fallback_equals_oracle():
         text = "".join(rnd.choice(words + extra) + rnd.choice(glue) for _ in range(rnd.randint(0, 12)))
         for max_len in (256, 7):
             assert wordpiece_unicode(text, vocab, max_len) == MO.tokenize_ids(text, vocab, max_len).tolist(), repr(text)
+
+
+def test_packed_entry_equals_pointer_entry(tmp_path):
+    """qre_wordpiece_encode_packed (one blob + offsets) against qre_wordpiece_encode (one pointer per
+    text) through ctypes: same ids, same lengths, non-ASCII texts declined by both, empty texts and an
+    empty batch included."""
+    import ctypes as C
+    from qre_b200 import _cabi
+    vocab = ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + list("abcdefghijklmnopqrstuvwxyz0123456789!?,.'") + \
+        ["##" + c for c in "abcdefghijklmnopqrstuvwxyz"] + ["hello", "world", "token", "##ing", "##s", "cache", "route"]
+    vp = tmp_path / "vocab.txt"
+    vp.write_text("\n".join(vocab) + "\n")
+    wp = _cabi.WordPiece(str(vp))
+    rs = np.random.Generator(np.random.PCG64(5))
+    base = ["hello", "world!", "tokens", "routing", "cache,", "café", "", "  ", "Hello  WORLD", "x" * 300]
+    texts = [" ".join(base[int(j)] for j in rs.integers(0, len(base), int(rs.integers(0, 7)))) for _ in range(700)]
+    ids_p, lens_p = wp.encode(texts, max_len=64, n_threads=3)            # the packed entry
+    raw = [t.encode("utf-8") for t in texts]
+    arr = (C.c_char_p * len(raw))(*raw)
+    tl = np.array([len(b) for b in raw], np.int64)
+    cap = int(np.minimum(tl + 2, 64).sum())
+    ids = np.empty(max(cap, 1), np.int32)
+    lens = np.empty(len(raw), np.int32)
+    rc = wp._lib.qre_wordpiece_encode(wp._h, C.c_int64(len(raw)), arr, _cabi._ptr(tl), C.c_int(64), _cabi._ptr(ids),
+                                      C.c_int64(cap), _cabi._ptr(lens), C.c_int(2))
+    assert rc == 0
+    assert np.array_equal(lens, lens_p) and np.array_equal(ids[: int(lens[lens > 0].sum())], ids_p)
+    assert (lens == -1).sum() > 0 and (lens == 2).sum() > 0               # declined texts; empty texts = [CLS][SEP]
+    e_ids, e_lens = wp.encode([], max_len=64)
+    assert e_ids.size == 0 and e_lens.size == 0
