@@ -6,9 +6,14 @@
 // characters, fold \t \n \r to space), lower-case, split on whitespace, make every ASCII
 // punctuation character its own token, then greedy longest-match-first pieces with the "##"
 // continuation prefix (a word with no full cover, or longer than 100 characters, is [UNK]).
-// Output is `[CLS] pieces [SEP]`, truncated to max_len.  Restated with full Unicode handling in
-// oracle/minilm_oracle.py and pinned against transformers' BertTokenizer there; texts with any
-// non-ASCII byte are left to the caller (length -1), as qre_host_features does.
+// Output is `[CLS] pieces [SEP]`, truncated to max_len.  Restated in oracle/minilm_oracle.py and
+// pinned against transformers' BertTokenizer there.  Texts with non-ASCII characters take a second
+// path here (encode_one_unicode): UTF-8 decode, BasicTokenizer's cleaning / CJK spacing on the
+// original characters, NFD + strip-Mn + lower through a table generated from Python's unicodedata
+// (qre_unicode_tables.inc, qre_b200/gen_unicode_tables.py), Unicode whitespace and punctuation
+// classes, pieces matched on character boundaries.  Only texts holding a character whose handling
+// depends on its neighbours (capital sigma, reordering combining marks) or invalid UTF-8 are left
+// to the caller (length -1).
 // No CUDA in this file; it is a .cu only so that one compiler invocation builds the library.
 #include <stdint.h>
 #include <stdio.h>
@@ -35,6 +40,109 @@ namespace {
 
 inline bool is_punct(unsigned char c) {
   return (c >= 33 && c <= 47) || (c >= 58 && c <= 64) || (c >= 91 && c <= 96) || (c >= 123 && c <= 126);
+}
+
+#include "qre_unicode_tables.inc"
+
+inline bool in_ranges(const uint32_t (*r)[2], int n, uint32_t cp) {
+  int lo = 0, hi = n - 1;
+  while (lo <= hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cp < r[mid][0]) hi = mid - 1;
+    else if (cp > r[mid][1]) lo = mid + 1;
+    else return true;
+  }
+  return false;
+}
+inline const UniMap* find_map(uint32_t cp) {
+  int lo = 0, hi = kUniMapN - 1;
+  while (lo <= hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cp < kUniMap[mid].cp) hi = mid - 1;
+    else if (cp > kUniMap[mid].cp) lo = mid + 1;
+    else return &kUniMap[mid];
+  }
+  return nullptr;
+}
+inline bool is_cjk(uint32_t cp) {            // BasicTokenizer._is_chinese_char
+  return (cp >= 0x4E00 && cp <= 0x9FFF) || (cp >= 0x3400 && cp <= 0x4DBF) || (cp >= 0x20000 && cp <= 0x2A6DF) ||
+         (cp >= 0x2A700 && cp <= 0x2B73F) || (cp >= 0x2B740 && cp <= 0x2B81F) || (cp >= 0x2B820 && cp <= 0x2CEAF) ||
+         (cp >= 0xF900 && cp <= 0xFAFF) || (cp >= 0x2F800 && cp <= 0x2FA1F);
+}
+// Strict UTF-8 decode of the character at s[i]; false on a malformed, overlong or surrogate sequence.
+inline bool decode_utf8(const char* s, int64_t n, int64_t& i, uint32_t& cp) {
+  const unsigned char c0 = static_cast<unsigned char>(s[i]);
+  int extra;
+  uint32_t v, min_v;
+  if (c0 < 0x80) { cp = c0; ++i; return true; }
+  if ((c0 & 0xE0) == 0xC0) { extra = 1; v = c0 & 0x1F; min_v = 0x80; }
+  else if ((c0 & 0xF0) == 0xE0) { extra = 2; v = c0 & 0x0F; min_v = 0x800; }
+  else if ((c0 & 0xF8) == 0xF0) { extra = 3; v = c0 & 0x07; min_v = 0x10000; }
+  else return false;
+  if (i + extra >= n) return false;                 // truncated sequence
+  for (int k = 1; k <= extra; ++k) {
+    const unsigned char c = static_cast<unsigned char>(s[i + k]);
+    if ((c & 0xC0) != 0x80) return false;
+    v = (v << 6) | (c & 0x3F);
+  }
+  if (v < min_v || v > 0x10FFFF || (v >= 0xD800 && v <= 0xDFFF)) return false;
+  cp = v;
+  i += extra + 1;
+  return true;
+}
+inline void append_utf8(std::string& w, uint32_t cp) {
+  if (cp < 0x80) {
+    w.push_back(static_cast<char>(cp));
+  } else if (cp < 0x800) {
+    w.push_back(static_cast<char>(0xC0 | (cp >> 6)));
+    w.push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+  } else if (cp < 0x10000) {
+    w.push_back(static_cast<char>(0xE0 | (cp >> 12)));
+    w.push_back(static_cast<char>(0x80 | ((cp >> 6) & 0x3F)));
+    w.push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+  } else {
+    w.push_back(static_cast<char>(0xF0 | (cp >> 18)));
+    w.push_back(static_cast<char>(0x80 | ((cp >> 12) & 0x3F)));
+    w.push_back(static_cast<char>(0x80 | ((cp >> 6) & 0x3F)));
+    w.push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+  }
+}
+
+// word_to_ids for a UTF-8 word of `nchars` characters: pieces start and end on character boundaries.
+void word_to_ids_u(const qre_wordpiece& t, const std::string& w, int nchars, std::vector<int32_t>& out,
+                   std::string& probe, std::vector<uint32_t>& b) {
+  if (nchars > 100) {
+    out.push_back(t.unk);
+    return;
+  }
+  b.clear();
+  for (size_t i = 0; i < w.size(); ++i)
+    if ((static_cast<unsigned char>(w[i]) & 0xC0) != 0x80) b.push_back(static_cast<uint32_t>(i));
+  b.push_back(static_cast<uint32_t>(w.size()));
+  const size_t n = b.size() - 1, mark = out.size();
+  size_t start = 0;
+  while (start < n) {
+    size_t end = n;
+    while (end > start + 1 && b[end] - b[start] > t.max_piece) --end;     // longer than any vocab entry
+    int32_t found = -1;
+    for (; end > start; --end) {
+      probe.clear();
+      if (start > 0) probe.append("##");
+      probe.append(w, b[start], b[end] - b[start]);
+      auto it = t.vocab.find(probe);
+      if (it != t.vocab.end()) {
+        found = it->second;
+        break;
+      }
+    }
+    if (found < 0) {
+      out.resize(mark);
+      out.push_back(t.unk);
+      return;
+    }
+    out.push_back(found);
+    start = end;
+  }
 }
 
 // Appends the pieces of one word; returns false when the word has no cover ([UNK]).
@@ -68,11 +176,97 @@ void word_to_ids(const qre_wordpiece& t, const std::string& w, std::vector<int32
   }
 }
 
-// Returns false for a text with a non-ASCII byte.
+// The general path (any Unicode text).  Returns false — nothing appended — for a text that must go to
+// the caller's tokenizer: malformed UTF-8, or a character whose handling depends on its neighbours.
+bool encode_one_unicode(const qre_wordpiece& t, const char* s, int64_t n, int max_len, std::vector<int32_t>& out,
+                        std::string& word, std::string& probe) {
+  const size_t mark = out.size();
+  std::vector<uint32_t> bounds;
+  out.push_back(t.cls);
+  word.clear();
+  int nchars = 0;
+  auto flush = [&]() {
+    if (!word.empty()) {
+      word_to_ids_u(t, word, nchars, out, probe, bounds);
+      word.clear();
+      nchars = 0;
+    }
+  };
+  auto put = [&](uint32_t m) {                   // one character of the normalised text
+    if (m < 0x80) {
+      const unsigned char c = static_cast<unsigned char>(m);
+      if (c == ' ' || (c >= 0x09 && c <= 0x0D) || (c >= 0x1C && c <= 0x1F)) {
+        flush();
+      } else if (is_punct(c)) {
+        flush();
+        word.push_back(static_cast<char>(c));
+        nchars = 1;
+        flush();
+      } else {
+        word.push_back(static_cast<char>(c));
+        ++nchars;
+      }
+    } else if (in_ranges(kUniWhite, kUniWhiteN, m)) {
+      flush();
+    } else if (in_ranges(kUniPunct, kUniPunctN, m)) {
+      flush();
+      append_utf8(word, m);
+      nchars = 1;
+      flush();
+    } else {
+      append_utf8(word, m);
+      ++nchars;
+    }
+  };
+  int64_t i = 0;
+  while (i < n) {
+    uint32_t cp;
+    if (!decode_utf8(s, n, i, cp)) {
+      out.resize(mark);
+      return false;
+    }
+    if (cp < 0x80) {
+      unsigned char c = static_cast<unsigned char>(cp);
+      if (c == ' ' || c == '\t' || c == '\n' || c == '\r') { flush(); continue; }
+      if (c < 32 || c == 127) continue;          // NUL and the other control characters vanish
+      if (t.lower && c >= 'A' && c <= 'Z') c = static_cast<unsigned char>(c - 'A' + 'a');
+      put(c);
+      continue;
+    }
+    if (in_ranges(kUniDecline, kUniDeclineN, cp)) {
+      out.resize(mark);
+      return false;
+    }
+    if (cp == 0xFFFD || in_ranges(kUniSkip, kUniSkipN, cp)) continue;
+    if (in_ranges(kUniSpace, kUniSpaceN, cp)) { flush(); continue; }
+    const bool cjk = is_cjk(cp);                 // spaced out BEFORE normalisation
+    if (cjk) flush();
+    if (!t.lower) {
+      put(cp);
+    } else if (cp >= 0xAC00 && cp <= 0xD7A3) {   // Hangul syllable: NFD is arithmetic
+      const uint32_t si = cp - 0xAC00;
+      put(0x1100 + si / 588);
+      put(0x1161 + (si % 588) / 28);
+      if (si % 28) put(0x11A7 + si % 28);
+    } else if (const UniMap* m = find_map(cp)) {
+      for (uint32_t k = 0; k < m->len; ++k) put(kUniPool[m->off + k]);
+    } else {
+      put(cp);
+    }
+    if (cjk) flush();
+  }
+  flush();
+  const size_t keep = static_cast<size_t>(max_len > 2 ? max_len - 2 : 0);
+  if (out.size() - mark - 1 > keep) out.resize(mark + 1 + keep);
+  out.push_back(t.sep);
+  return true;
+}
+
+// ASCII texts take the byte-wise path below; anything else the general one.
 bool encode_one(const qre_wordpiece& t, const char* s, int64_t n, int max_len, std::vector<int32_t>& out,
                 std::string& word, std::string& probe) {
   for (int64_t i = 0; i < n; ++i)
-    if (static_cast<unsigned char>(s[i]) >= 0x80) return false;
+    if (static_cast<unsigned char>(s[i]) >= 0x80) return encode_one_unicode(t, s, n, max_len, out, word, probe);
   const size_t mark = out.size();
   out.push_back(t.cls);
   word.clear();

@@ -638,7 +638,9 @@ def encoder_debug_gemm(a, w, bias, residual=None, epilogue: int = 0, device: int
 
 
 class WordPiece:
-    """Host-thread WordPiece (qre_wordpiece_t): ASCII texts only; others come back as None."""
+    """Host-thread WordPiece (qre_wordpiece_t), ASCII and general Unicode texts; the rare text it hands back
+    (a character whose tokenisation depends on its neighbours or differs between the reference tokenizers,
+    an unassigned code point) has length -1."""
 
     def __init__(self, vocab_path: str, do_lower_case: bool = True):
         self._lib = load()

@@ -19,7 +19,7 @@ LIB_DIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIB_DIR, "libqre_b200.so")
 SOURCES = ["qre_api.cu", "qre_kernels.cu", "qre_gemm_topk.cu", "qre_gemm_topk2.cu", "qre_noalloc.cu",
            "qre_host_features.cu", "qre_enc_gemm.cu", "qre_encoder.cu", "qre_wordpiece.cu"]
-HEADERS = ["qre_common.cuh", "qre_ptx.cuh", "qre_scan_epilogue.cuh", "qre_encoder.cuh",
+HEADERS = ["qre_common.cuh", "qre_ptx.cuh", "qre_scan_epilogue.cuh", "qre_encoder.cuh", "qre_unicode_tables.inc",
            os.path.join("..", "..", "include", "qre_b200.h"), os.path.join("..", "..", "include", "qre_encoder_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

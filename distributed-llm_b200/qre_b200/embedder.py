@@ -38,7 +38,8 @@ def _strip_prefix(sd: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
     raise KeyError("state dict has no embeddings.word_embeddings.weight (BertModel naming expected)")
 
 
-# ---- Unicode fallback tokenizer (texts the C++ ASCII tokenizer declines) ------------------------
+# ---- Python fallback tokenizer (the few texts the C++ tokenizer hands back: capital sigma, characters on
+# ---- which the Python and Rust reference tokenizers disagree, unassigned code points) ----------------
 def _is_punct(ch: str) -> bool:
     cp = ord(ch)
     return (33 <= cp <= 47 or 58 <= cp <= 64 or 91 <= cp <= 96 or 123 <= cp <= 126
@@ -179,7 +180,7 @@ class B200SentenceEncoder:
     def tokenize(self, texts: Sequence[str]) -> Tuple[np.ndarray, np.ndarray]:
         """-> (ids int32 [total], offsets int32 [n + 1]); `[CLS] pieces [SEP]`, truncated."""
         ids, lens = self._wp.encode(list(texts), max_len=self.max_seq_length)
-        if (lens < 0).any():                      # non-ASCII texts: Python path, spliced back in order
+        if (lens < 0).any():                      # texts the C++ tokenizer handed back: Python path, spliced in order
             parts, o = [], 0
             for t, n in zip(texts, lens):
                 if n >= 0:

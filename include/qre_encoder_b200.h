@@ -104,13 +104,17 @@ QRE_API int qre_encoder_debug_gemm(int device, int rows, int n, int k, const flo
 /* ---- WordPiece on host threads --------------------------------------------------------------
  * BERT uncased tokenisation (BasicTokenizer + greedy longest-match-first WordPiece), the step
  * SentenceTransformer.encode runs in Python before the model.  `vocab_path`: a vocab.txt, one
- * piece per line.  Texts containing non-ASCII bytes are NOT tokenised here (Unicode
- * normalisation tables are out of scope): their length is reported as -1 and the caller routes
- * them to its own tokenizer. */
+ * piece per line.  ASCII texts take a byte-wise path; other texts are decoded, cleaned, NFD-
+ * decomposed, stripped of accents and lower-cased through tables generated from Python's unicodedata
+ * and cross-checked against the Rust `tokenizers` backend (csrc/qre_unicode_tables.inc).  Texts holding
+ * a character whose handling depends on its neighbours (capital sigma), on which those two reference
+ * implementations disagree (unassigned code points, a few hundred recent characters) or malformed
+ * UTF-8 are NOT tokenised here: their length is reported as -1 and the caller routes them to its
+ * own tokenizer. */
 QRE_API int qre_wordpiece_create(const char* vocab_path, int do_lower_case, qre_wordpiece_t** out);
 QRE_API int qre_wordpiece_destroy(qre_wordpiece_t* t);
 /* ids_out: capacity `cap` ids in total; lens_out[n]: ids written for text i ([CLS] .. [SEP]
- * included, truncated to max_len), or -1 for a non-ASCII text.  Sequence i starts at the sum of
+ * included, truncated to max_len), or -1 for a text handed back.  Sequence i starts at the sum of
  * the non-negative lens before it.  n_threads <= 0: all host cores. */
 QRE_API int qre_wordpiece_encode(const qre_wordpiece_t* t, int64_t n, const char* const* texts,
                                  const int64_t* text_len, int max_len, int32_t* ids_out, int64_t cap,

@@ -121,3 +121,31 @@ def test_wordpiece_restatement_on_random_texts(tmp_path):
             want = tok(text, truncation=True, max_length=max_len)["input_ids"]
             got = MO.tokenize_ids(text, vocab, max_len).tolist()
             assert got == want, (i, repr(text), max_len, got, want)
+
+
+def test_cpp_wordpiece_equals_berttokenizer_on_unicode_texts(tmp_path):
+    """The product's C++ tokenizer against transformers' BertTokenizer ITSELF (backed by the Rust
+    `tokenizers` package, what sentence-transformers loads for the reference's model) on 4,000 generated
+    Unicode texts incl. arbitrary assigned code points, both casings: every text the C++ path accepts
+    must give BertTokenizer's ids; the ones it hands back (-1) are those holding a character its tables
+    list as ambiguous between the implementations."""
+    from transformers import BertTokenizer
+    from qre_b200 import _cabi
+    from tests.test_wordpiece_cpu import UNI_VOCAB, unicode_texts
+    vp = os.path.join(tmp_path, "vocab_u.txt")
+    with open(vp, "w", encoding="utf-8") as f:
+        f.write("\n".join(UNI_VOCAB) + "\n")
+    texts, n_mixed = unicode_texts(seed=29)
+    for lower in (True, False):
+        tok = BertTokenizer(vp, do_lower_case=lower)
+        wp = _cabi.WordPiece(vp, do_lower_case=lower)
+        ids, lens = wp.encode(texts, max_len=48)
+        ref = tok(texts, truncation=True, max_length=48)["input_ids"]
+        o, accepted = 0, 0
+        for t, n, r in zip(texts, lens.tolist(), ref):
+            if n < 0:
+                continue
+            assert ids[o:o + n].tolist() == r, (repr(t), lower)
+            o += n
+            accepted += 1
+        assert accepted >= 0.93 * len(texts)
