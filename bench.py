@@ -49,6 +49,10 @@ def parse(argv=None):
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ref-worker", default="", help=argparse.SUPPRESS)      # internal: one process of the CPU arm
+    ap.add_argument("--ref-count", type=int, default=1, help=argparse.SUPPRESS)
+    ap.add_argument("--ref-first", type=int, default=0, help=argparse.SUPPRESS)
+    ap.add_argument("--ref-seconds", type=float, default=0.0, help=argparse.SUPPRESS)
     ap.add_argument("--entries", type=int, default=1_000_000)
     ap.add_argument("--queries", type=int, default=4096)
     ap.add_argument("--dim", type=int, default=384)
@@ -761,6 +765,74 @@ def time_reference_lookups(cache, Q, q_ctx, n_steps, n_warm):
     return times
 
 
+def ref_worker(path: str, first: int, count: int, n_warm: int, seconds: float = 0.0) -> None:
+    """One process of the CPU arm: builds the reference's QueryCache from the sample file, warms up,
+    waits for the parent's go-ahead (so that all workers time their lookups at the same moment, sharing
+    the host as they would in a real multi-process deployment), times `count` lookups."""
+    d = np.load(os.path.join(path, "sample.npz"))
+    cache = reference_cache_sample(d["rows"], d["ctx"], d["rows"].shape[0])
+    Q, q_ctx = d["Q"], d["q_ctx"]
+    time_reference_lookups(cache, Q[first:], q_ctx[first:], 0, n_warm)
+    tag = f"{first:06d}"
+    open(os.path.join(path, f"ready.{tag}"), "w").close()
+    while not os.path.exists(os.path.join(path, "go")):
+        time.sleep(0.002)
+    t0 = time.perf_counter()
+    if seconds > 0:                              # time-bounded: as many lookups as fit (at least two)
+        times = []
+        while len(times) < 2 or time.perf_counter() - t0 < seconds:
+            j = first + len(times)
+            times += time_reference_lookups(cache, Q[j % Q.shape[0]:], q_ctx[j % Q.shape[0]:], 1, 0)
+    else:
+        times = time_reference_lookups(cache, Q[first:], q_ctx[first:], count, 0)
+    with open(os.path.join(path, f"done.{tag}.json"), "w") as f:
+        json.dump({"elapsed": time.perf_counter() - t0, "times": times}, f)
+
+
+def reference_lookups_all_cores(rows, ctx, Q, q_ctx, n_steps, n_warm, seconds=0.0):
+    """`n_steps` QueryCache.lookup calls of the reference spread over one process per host core (the
+    loop is pure Python + numpy and holds the GIL, so processes are the only way to use the cores; the
+    queries of a batch are independent).  Returns (lookups/s of the whole job, mean single-lookup
+    seconds under that load, processes used)."""
+    import shutil
+    import subprocess
+    import tempfile
+    n_proc = max(1, min(os.cpu_count() or 1, n_steps if seconds <= 0 else 64, 64))
+    path = tempfile.mkdtemp(prefix="qre_ref_")
+    try:
+        np.savez(os.path.join(path, "sample.npz"), rows=rows, ctx=ctx, Q=Q, q_ctx=q_ctx)
+        counts = [n_steps // n_proc + (1 if w < n_steps % n_proc else 0) for w in range(n_proc)]
+        if seconds > 0:                          # time-bounded run: disjoint stretches of the query batch
+            counts = [max(1, Q.shape[0] // n_proc)] * n_proc
+        procs, first = [], 0
+        env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1", MKL_NUM_THREADS="1",
+                   CUDA_VISIBLE_DEVICES="")
+        for w in range(n_proc):
+            procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "--impl", "reference",
+                                           "--ref-worker", path, "--ref-first", str(first), "--ref-count",
+                                           str(counts[w]), "--warmup", str(n_warm), "--ref-seconds",
+                                           str(seconds)], env=env))
+            first += counts[w]
+        deadline = time.time() + 600
+        while sum(f.startswith("ready.") for f in os.listdir(path)) < n_proc:
+            if time.time() > deadline or any(p.poll() not in (None, 0) for p in procs):
+                raise RuntimeError("a reference worker failed before it was ready")
+            time.sleep(0.01)
+        open(os.path.join(path, "go"), "w").close()
+        for p_ in procs:
+            if p_.wait(timeout=900) != 0:
+                raise RuntimeError("a reference worker failed")
+        res = [json.load(open(os.path.join(path, f))) for f in sorted(os.listdir(path)) if f.startswith("done.")]
+        wall = max(r["elapsed"] for r in res)
+        times = [t for r in res for t in r["times"]]
+        return len(times) / wall, float(np.mean(times)), n_proc
+    finally:
+        for p_ in locals().get("procs", []):
+            if p_.poll() is None:
+                p_.kill()
+        shutil.rmtree(path, ignore_errors=True)
+
+
 def cpu_baseline(args, wq, kept, torch):
     """Bounded sample of the SAME workload on the host: the reference's own QueryCache.lookup over
     a slice of the generated rows (or the oracle's faithful loop when oracle/_ref is absent)."""
@@ -769,21 +841,17 @@ def cpu_baseline(args, wq, kept, torch):
     if make_ref.available():
         n_slice = min(args.entries, 50_000)
         rows, ctx, _, _ = host_image(kept, torch, n_slice)
-        cache = reference_cache_sample(rows, ctx, n_slice)
-        n = 0
         t0 = time.perf_counter()
-        times = []
-        while n < 3 or (time.perf_counter() - t0 < args.cpu_seconds and n < args.queries):
-            times += time_reference_lookups(cache, wq["Q"][n:n + 1], q_ctx[n:n + 1], 1, 0)
-            n += 1
-        per = float(np.mean(times))
+        rate, per, cores = reference_lookups_all_cores(rows, ctx, wq["Q"], q_ctx, 0, 1, seconds=args.cpu_seconds)
         scale = args.entries / n_slice
-        return {"value": 1.0 / (per * scale), "unit": UNIT, "cores": 1, "kind": "reference",
+        return {"value": rate / scale, "unit": UNIT, "cores": cores, "kind": "reference",
                 "host_cores_available": os.cpu_count(), "lookup_ms_on_sample": per * 1e3, "scale_factor": scale,
-                "sample": f"{n} QueryCache.lookup calls of the reference itself (oracle/_ref/cache.bin = "
+                "sample": f"QueryCache.lookup of the reference itself (oracle/_ref/cache.bin = "
                           f"/root/reference/src/cache.py byte-compiled) over the first {n_slice} of the "
-                          f"{args.entries} generated entries, {sum(times):.1f} s; value = 1 / (lookup time x "
-                          f"{scale:.0f}), the loop is linear in entries; single thread (the loop holds the GIL)"}
+                          f"{args.entries} generated entries, in {cores} processes (one per host core: the loop holds "
+                          f"the GIL) for {args.cpu_seconds:.0f} s each at the same time, {time.perf_counter() - t0:.0f} s "
+                          f"in all with building their caches; {rate:.1f} lookups/s on the slice, value = that / "
+                          f"{scale:.0f} (the loop is linear in entries); one lookup under that load {per * 1e3:.0f} ms"}
     from oracle import qre_oracle as O
     rows, ctx, ts, lru = host_image(kept, torch)
     img = O.CacheImage(rows, ctx, ts, lru)
@@ -821,10 +889,13 @@ def run_reference(args):
     rows = rows_t[:n_slice].cpu().numpy(); ctx = ctx_t[:n_slice].cpu().numpy().view(np.uint64)
     q_ctx = wq["ctx_tab"][wq["q_ci"]]
     scale = args.entries / n_slice
+    cores, rate = 1, None
     if make_ref.available():
         kind = "reference"
-        cache = reference_cache_sample(rows, ctx, n_slice)
-        times = time_reference_lookups(cache, wq["Q"], q_ctx, args.steps, args.warmup)
+        # all the host cores: one process per core, each with its own copy of the reference's cache,
+        # the K lookups dealt over them and timed at the same moment
+        rate, per_loaded, cores = reference_lookups_all_cores(rows, ctx, wq["Q"], q_ctx, args.steps, args.warmup)
+        times = [per_loaded]
         what = ("QueryCache.lookup of the reference itself (oracle/_ref/cache.bin = /root/reference/src/cache.py "
                 "byte-compiled by oracle/make_ref.py)")
     else:
@@ -839,21 +910,26 @@ def run_reference(args):
                 times.append(time.perf_counter() - t0)
         what = "oracle.scan_faithful (port of src/cache.py:280-296; oracle/_ref not built)"
     per = float(np.mean(times))
-    value = 1.0 / (per * scale)
+    if rate is None:
+        rate = 1.0 / per                         # lookups/s on the slice, one thread
+    value = rate / scale
     sample = (f"per step: 1 query through {what} over the first {n_slice} of the {args.entries} generated entries "
-              f"({'same generator as the GPU arm' if use_cuda else 'CPU generator: no GPU here'}); ms_per_step is "
-              f"the measured time on that slice, value = 1 / (ms_per_step x {scale:.0f}) since the loop is linear "
-              "in entries; single thread (the reference loop holds the GIL)")
+              f"({'same generator as the GPU arm' if use_cuda else 'CPU generator: no GPU here'}); the {args.steps} "
+              f"steps are dealt over {cores} processes (one per host core: the loop is pure Python + numpy and holds "
+              f"the GIL; queries are independent) that time their lookups simultaneously; ms_per_step = wall time of "
+              f"the job / steps on that slice, value = steps/s / {scale:.0f} since the loop is linear in entries; "
+              f"one lookup under that load takes {per * 1e3:.1f} ms")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per * 1e3,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / rate,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"{args.queries} queries x {args.entries} cache entries x {args.dim}-d "
                                "(BASELINE.json configs[1]); one step = one query's lookup on a bounded slice",
                    "entries_in_sample": n_slice, "scale_factor": scale},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": kind,
-                         "host_cores_available": os.cpu_count(), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "host_cores_available": os.cpu_count(), "single_lookup_ms_under_load": per * 1e3,
+                         "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -861,7 +937,9 @@ def run_reference(args):
 
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.ref_worker:
+        ref_worker(a.ref_worker, a.ref_first, a.ref_count, a.warmup, a.ref_seconds)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)
