@@ -6,8 +6,12 @@
 // no-tokenizer token estimate of TokenBasedRouter (qre:91,96: max(1, len(text)//4)).  The
 // Python `re` patterns are compiled by hand into "segments": sets of literal alternatives with
 // \b conditions at either end, joined by `.*` (which, as in Python, does not cross a newline).
-// Queries containing non-ASCII bytes are NOT classified here (rule = -1): \b, \w and len()
-// are Unicode-aware in Python, so the caller keeps those on its own path.
+// ASCII queries are matched byte-wise.  Other queries are decoded, stripped and lowered with the
+// full str.lower() table, and every character gets Python `re`'s class on str patterns (\w = isalnum
+// or '_', \s = isspace, \d = isdecimal; tables generated from unicodedata, qre_unicode_tables.inc), so
+// \b, \s, \d, len() and split() mean what they mean in the reference.  Only malformed UTF-8 and texts
+// with a capital sigma (str.lower()'s final-sigma rule looks at the neighbours) are handed back
+// (rule = -1).
 #include <stdint.h>
 #include <string.h>
 
@@ -29,9 +33,70 @@ inline bool is_space(unsigned char c) {          // str.isspace() / \s for code 
 }
 inline bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
 
+#include "qre_unicode_tables.inc"
+
+inline bool uni_in(const uint32_t (*r)[2], int n, uint32_t cp) {
+  int lo = 0, hi = n - 1;
+  while (lo <= hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cp < r[mid][0]) hi = mid - 1;
+    else if (cp > r[mid][1]) lo = mid + 1;
+    else return true;
+  }
+  return false;
+}
+constexpr uint8_t kWord = 1, kSpace = 2, kDigit = 4, kCont = 0x80;   // per-byte classes of a Unicode text
+inline uint8_t class_of(uint32_t cp) {
+  if (cp < 0x80) {
+    const unsigned char c = static_cast<unsigned char>(cp);
+    return static_cast<uint8_t>((is_word(c) ? kWord : 0) | (is_space(c) ? kSpace : 0) | (is_digit(c) ? kDigit : 0));
+  }
+  return static_cast<uint8_t>((uni_in(kUniAlnum, kUniAlnumN, cp) ? kWord : 0) | (uni_in(kUniWhite, kUniWhiteN, cp) ? kSpace : 0) |
+                              (uni_in(kUniDecimal, kUniDecimalN, cp) ? kDigit : 0));
+}
+inline bool utf8_next(const char* s, int64_t n, int64_t& i, uint32_t& cp) {      // strict decode, as in qre_wordpiece.cu
+  const unsigned char c0 = static_cast<unsigned char>(s[i]);
+  int extra;
+  uint32_t v, min_v;
+  if (c0 < 0x80) { cp = c0; ++i; return true; }
+  if ((c0 & 0xE0) == 0xC0) { extra = 1; v = c0 & 0x1F; min_v = 0x80; }
+  else if ((c0 & 0xF0) == 0xE0) { extra = 2; v = c0 & 0x0F; min_v = 0x800; }
+  else if ((c0 & 0xF8) == 0xF0) { extra = 3; v = c0 & 0x07; min_v = 0x10000; }
+  else return false;
+  if (i + extra >= n) return false;
+  for (int k = 1; k <= extra; ++k) {
+    const unsigned char c = static_cast<unsigned char>(s[i + k]);
+    if ((c & 0xC0) != 0x80) return false;
+    v = (v << 6) | (c & 0x3F);
+  }
+  if (v < min_v || v > 0x10FFFF || (v >= 0xD800 && v <= 0xDFFF)) return false;
+  cp = v;
+  i += extra + 1;
+  return true;
+}
+inline void utf8_put(std::string& w, uint32_t cp) {
+  if (cp < 0x80) {
+    w.push_back(static_cast<char>(cp));
+  } else if (cp < 0x800) {
+    w.push_back(static_cast<char>(0xC0 | (cp >> 6)));
+    w.push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+  } else if (cp < 0x10000) {
+    w.push_back(static_cast<char>(0xE0 | (cp >> 12)));
+    w.push_back(static_cast<char>(0x80 | ((cp >> 6) & 0x3F)));
+    w.push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+  } else {
+    w.push_back(static_cast<char>(0xF0 | (cp >> 18)));
+    w.push_back(static_cast<char>(0x80 | ((cp >> 12) & 0x3F)));
+    w.push_back(static_cast<char>(0x80 | ((cp >> 6) & 0x3F)));
+    w.push_back(static_cast<char>(0x80 | (cp & 0x3F)));
+  }
+}
+
 struct View {
   const char* p;
   int n;
+  const uint8_t* cls = nullptr;                  // Unicode text only: class bits of the character starting at each byte
+  int nchars = 0;                                // characters (== n for ASCII text)
   uint64_t has[4] = {0, 0, 0, 0};                // which byte values occur (prefilter for the literal search)
   void index() {
     for (int i = 0; i < n; ++i) {
@@ -44,11 +109,22 @@ struct View {
     return ((has[a >> 6] >> (a & 63)) & (has[b >> 6] >> (b & 63)) & 1ull) != 0 && static_cast<int>(lit.size()) <= n;
   }
   unsigned char at(int i) const { return (i >= 0 && i < n) ? static_cast<unsigned char>(p[i]) : 0; }
-  bool boundary(int i) const {                   // \b between positions i-1 and i
-    const bool a = i > 0 && is_word(at(i - 1));
-    const bool b = i < n && is_word(at(i));
-    return a != b;
+  // class tests of the character that STARTS at byte i (false outside the text)
+  bool word_at(int i) const { return i >= 0 && i < n && (cls ? (cls[i] & kWord) != 0 : is_word(at(i))); }
+  bool space_at(int i) const { return i >= 0 && i < n && (cls ? (cls[i] & kSpace) != 0 : is_space(at(i))); }
+  bool digit_at(int i) const { return i >= 0 && i < n && (cls ? (cls[i] & kDigit) != 0 : is_digit(at(i))); }
+  int next(int i) const {                        // start of the following character
+    ++i;
+    if (cls) while (i < n && (cls[i] & kCont)) ++i;
+    return i;
   }
+  bool word_before(int i) const {                // the character that ends at byte i
+    if (i <= 0) return false;
+    int j = i - 1;
+    if (cls) while (j > 0 && (cls[j] & kCont)) --j;
+    return word_at(j);
+  }
+  bool boundary(int i) const { return word_before(i) != word_at(i); }      // \b between positions i-1 and i
 };
 
 struct Seg {
@@ -80,37 +156,36 @@ void seg_matches(const View& s, const Seg& g, std::vector<std::pair<int, int>>& 
 }
 
 bool match_math(const View& s, bool with_what_is) {
-  // ^\s*(what is\s+)?\d+\s*[\+\-\*/]\s*\d+\s*\??\s*$
+  // ^\s*(what is\s+)?\d+\s*[\+\-\*/]\s*\d+\s*\??\s*$   (\s and \d in Python's Unicode sense)
   int i = 0;
-  while (i < s.n && is_space(s.at(i))) ++i;
+  while (s.space_at(i)) i = s.next(i);
   if (with_what_is) {
     if (i + 7 > s.n || memcmp(s.p + i, "what is", 7) != 0) return false;
     i += 7;
-    if (i >= s.n || !is_space(s.at(i))) return false;
-    while (i < s.n && is_space(s.at(i))) ++i;
+    if (!s.space_at(i)) return false;
+    while (s.space_at(i)) i = s.next(i);
   }
   int d0 = i;
-  while (i < s.n && is_digit(s.at(i))) ++i;
+  while (s.digit_at(i)) i = s.next(i);
   if (i == d0) return false;
-  while (i < s.n && is_space(s.at(i))) ++i;
+  while (s.space_at(i)) i = s.next(i);
   const unsigned char op = s.at(i);
   if (!(op == '+' || op == '-' || op == '*' || op == '/')) return false;
   ++i;
-  while (i < s.n && is_space(s.at(i))) ++i;
+  while (s.space_at(i)) i = s.next(i);
   d0 = i;
-  while (i < s.n && is_digit(s.at(i))) ++i;
+  while (s.digit_at(i)) i = s.next(i);
   if (i == d0) return false;
-  while (i < s.n && is_space(s.at(i))) ++i;
+  while (s.space_at(i)) i = s.next(i);
   if (i < s.n && s.at(i) == '?') ++i;
-  while (i < s.n && is_space(s.at(i))) ++i;
+  while (s.space_at(i)) i = s.next(i);
   return i == s.n;
 }
 
 bool pat_search(const View& s, const Pat& p) {
   if (p.special == 1) {                          // (?:\b|^)a\*(?:\s|$|\W)
     for (int i = 0; i + 2 <= s.n; ++i)
-      if (s.at(i) == 'a' && s.at(i + 1) == '*' && (i == 0 || !is_word(s.at(i - 1))) &&
-          (i + 2 == s.n || !is_word(s.at(i + 2))))
+      if (s.at(i) == 'a' && s.at(i + 1) == '*' && !s.word_before(i) && !s.word_at(i + 2))
         return true;
     return false;
   }
@@ -230,33 +305,16 @@ bool contains(const View& s, const std::string& m) {
   return false;
 }
 
-void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_heur_params_t& hp,
-                  int32_t* tok, uint8_t* dev, double* conf, int32_t* rule, int32_t* cat) {
+// The ordered rule list (qre:323-364) on the stripped query `q` and its lowered form `ql`.
+void apply_rules(const View& q, const View& ql, bool has_ctx, int64_t ctx_len, const qre_heur_params_t& hp, int64_t t,
+                 uint8_t* dev, double* conf, int32_t* rule, int32_t* cat) {
   const Tables& T = tables();
-  const bool has_ctx = ctx_len > 0;               // `if context` — an empty string is falsy
-  // token estimate over f"{context}\n{query}" (qre:91,96); the ORIGINAL query, not the stripped one
-  const int64_t full_len = has_ctx ? ctx_len + 1 + q_len : q_len;
-  const int64_t t = full_len / 4 > 1 ? full_len / 4 : 1;
-  *tok = static_cast<int32_t>(t > 0x7fffffff ? 0x7fffffff : t);
-  for (int64_t i = 0; i < q_len; ++i)
-    if (static_cast<unsigned char>(q_raw[i]) >= 0x80) { *rule = -1; *cat = -1; *dev = 0; *conf = 0.0; return; }
-  // q = query.strip(); ql = q.lower()
-  int64_t b = 0, e = q_len;
-  while (b < e && is_space(static_cast<unsigned char>(q_raw[b]))) ++b;
-  while (e > b && is_space(static_cast<unsigned char>(q_raw[e - 1]))) --e;
-  View q{q_raw + b, static_cast<int>(e - b)};
-  q.index();
-  std::string low(q.p, q.n);
-  for (char& c : low)
-    if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
-  View ql{low.data(), q.n};
-  ql.index();
   const uint8_t heavy = static_cast<uint8_t>(hp.n_devices - 1), light = 0;
   *cat = -1;
   for (size_t c = 0; c < T.complex_cats.size(); ++c)
     for (const Pat& p : T.complex_cats[c])
       if (pat_search(ql, p)) { *rule = 0; *cat = static_cast<int32_t>(c); *dev = heavy; *conf = 0.92; return; }
-  if (q.n >= hp.long_chars) { *rule = 1; *dev = heavy; *conf = 0.80; return; }
+  if (q.nchars >= hp.long_chars) { *rule = 1; *dev = heavy; *conf = 0.80; return; }
   int qm = 0;
   for (int i = 0; i < q.n; ++i) qm += q.p[i] == '?';
   if (qm >= hp.multi_qmarks) { *rule = 2; *cat = qm; *dev = heavy; *conf = 0.80; return; }
@@ -267,13 +325,13 @@ void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_h
   for (size_t c = 0; c < T.simple_cats.size(); ++c)
     for (const Pat& p : T.simple_cats[c])
       if (pat_search(ql, p)) { *rule = 5; *cat = static_cast<int32_t>(c); *dev = light; *conf = 0.90; return; }
-  int words_n = 0;
+  int words_n = 0;                               // len(low.split())
   for (int i = 0; i < ql.n;) {
-    while (i < ql.n && is_space(ql.at(i))) ++i;
+    while (ql.space_at(i)) i = ql.next(i);
     if (i < ql.n) ++words_n;
-    while (i < ql.n && !is_space(ql.at(i))) ++i;
+    while (i < ql.n && !ql.space_at(i)) i = ql.next(i);
   }
-  if (words_n <= 15 && q.n <= 100) { *rule = 6; *dev = light; *conf = 0.75; return; }
+  if (words_n <= 15 && q.nchars <= 100) { *rule = 6; *dev = light; *conf = 0.75; return; }
   // no rule fired: token router's device, half its confidence (qre:357-364)
   const int thr = hp.token_threshold;
   const int64_t diff = t > thr ? t - thr : thr - t;
@@ -282,6 +340,100 @@ void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_h
   *rule = 7;
   *dev = t > thr ? 1 : 0;
   *conf = c * 0.5;
+}
+
+inline const UniMap* lower_of(uint32_t cp) {
+  int lo = 0, hi = kUniLowerN - 1;
+  while (lo <= hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cp < kUniLower[mid].cp) hi = mid - 1;
+    else if (cp > kUniLower[mid].cp) lo = mid + 1;
+    else return &kUniLower[mid];
+  }
+  return nullptr;
+}
+
+// `low_out` (optional) receives query.lower().strip() as UTF-8 — what the cache's exact-match key hashes.
+void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_heur_params_t& hp,
+                  int32_t* tok, uint8_t* dev, double* conf, int32_t* rule, int32_t* cat, std::string* low_out = nullptr) {
+  const bool has_ctx = ctx_len > 0;               // `if context` — an empty string is falsy
+  bool ascii = true;
+  for (int64_t i = 0; i < q_len && ascii; ++i) ascii = static_cast<unsigned char>(q_raw[i]) < 0x80;
+  auto declined = [&]() { *rule = -1; *cat = -1; *dev = 0; *conf = 0.0; *tok = 1; };
+  std::string low_local;
+  std::string& low = low_out ? *low_out : low_local;
+  low.clear();
+  if (ascii) {
+    // token estimate over f"{context}\n{query}" (qre:91,96); the ORIGINAL query, not the stripped one
+    const int64_t full_len = has_ctx ? ctx_len + 1 + q_len : q_len;
+    const int64_t t = full_len / 4 > 1 ? full_len / 4 : 1;
+    *tok = static_cast<int32_t>(t > 0x7fffffff ? 0x7fffffff : t);
+    // q = query.strip(); ql = q.lower()
+    int64_t b = 0, e = q_len;
+    while (b < e && is_space(static_cast<unsigned char>(q_raw[b]))) ++b;
+    while (e > b && is_space(static_cast<unsigned char>(q_raw[e - 1]))) --e;
+    View q{q_raw + b, static_cast<int>(e - b)};
+    q.nchars = q.n;
+    q.index();
+    low.assign(q.p, static_cast<size_t>(q.n));
+    for (char& c : low)
+      if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
+    View ql{low.data(), q.n};
+    ql.nchars = q.n;
+    ql.index();
+    apply_rules(q, ql, has_ctx, ctx_len, hp, t, dev, conf, rule, cat);
+    return;
+  }
+  // ---- general Unicode text ----
+  std::vector<uint32_t> cps;
+  std::vector<int64_t> at;                       // byte offset of each character (+ the end)
+  for (int64_t i = 0; i < q_len;) {
+    uint32_t cp;
+    at.push_back(i);
+    if (!utf8_next(q_raw, q_len, i, cp) || cp == 0x03A3) { declined(); return; }   // malformed, or final-sigma rule
+    cps.push_back(cp);
+  }
+  at.push_back(q_len);
+  const int64_t n_all = static_cast<int64_t>(cps.size());
+  const int64_t full_len = has_ctx ? ctx_len + 1 + n_all : n_all;                  // len() counts characters
+  const int64_t t = full_len / 4 > 1 ? full_len / 4 : 1;
+  *tok = static_cast<int32_t>(t > 0x7fffffff ? 0x7fffffff : t);
+  int64_t b = 0, e = n_all;
+  while (b < e && (class_of(cps[b]) & kSpace)) ++b;
+  while (e > b && (class_of(cps[e - 1]) & kSpace)) --e;
+  View q{q_raw + at[b], static_cast<int>(at[e] - at[b])};
+  q.nchars = static_cast<int>(e - b);
+  q.index();
+  // `fold` is what the patterns are matched on: the lowered text with the two characters that Python's
+  // re.IGNORECASE treats as equal to an ASCII letter replaced by it (dotless i ~ i, long s ~ s; both are
+  // word characters like the letters they stand for).  `low` stays the true lower() for the cache key.
+  std::string fold;
+  std::vector<uint8_t> cls;
+  int low_chars = 0;
+  auto put = [&](uint32_t cp) {
+    if (low_out) utf8_put(low, cp);
+    const uint32_t m = cp == 0x0131 ? 'i' : (cp == 0x017F ? 's' : cp);
+    const size_t start = fold.size();
+    utf8_put(fold, m);
+    cls.push_back(class_of(m));
+    for (size_t k = start + 1; k < fold.size(); ++k) cls.push_back(kCont);
+    ++low_chars;
+  };
+  for (int64_t i = b; i < e; ++i) {
+    const uint32_t cp = cps[i];
+    if (cp < 0x80) {
+      put(cp >= 'A' && cp <= 'Z' ? cp - 'A' + 'a' : cp);
+    } else if (const UniMap* m = lower_of(cp)) {
+      for (uint32_t k = 0; k < m->len; ++k) put(kUniLowerPool[m->off + k]);
+    } else {
+      put(cp);
+    }
+  }
+  View ql{fold.data(), static_cast<int>(fold.size())};
+  ql.cls = cls.data();
+  ql.nchars = low_chars;
+  ql.index();
+  apply_rules(q, ql, has_ctx, ctx_len, hp, t, dev, conf, rule, cat);
 }
 
 // ---- MD5 (RFC 1321), for the cache's exact-match key: md5("<ctx>||<query lowered, stripped>") ----
@@ -411,17 +563,11 @@ extern "C" QRE_API int qre_host_features_packed(int64_t n, const char* blob, con
       const char* q = blob + offsets[i];
       const int64_t len = offsets[i + 1] - offsets[i];
       classify_one(q, len, context_len ? context_len[i] : 0, *hp, &tok[i], &heur_dev[i], &heur_conf[i],
-                   &heur_rule[i], &heur_cat[i]);
+                   &heur_rule[i], &heur_cat[i], &low);
       if (key_hex == nullptr) continue;
       char* out = key_hex + 32 * i;
       if (heur_rule[i] < 0) { memset(out, 0, 32); continue; }
-      // query.lower().strip() == strip then lower for ASCII
-      int64_t b = 0, e = len;
-      while (b < e && is_space(static_cast<unsigned char>(q[b]))) ++b;
-      while (e > b && is_space(static_cast<unsigned char>(q[e - 1]))) --e;
-      low.assign(q + b, static_cast<size_t>(e - b));
-      for (char& c : low)
-        if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
+      // `low` = query.lower().strip(), left there by the classifier
       const int32_t ci = ctx_index[i];
       const char* parts[3] = {ctx_blob + ctx_offsets[ci], "||", low.data()};
       const int64_t lens[3] = {ctx_offsets[ci + 1] - ctx_offsets[ci], 2, static_cast<int64_t>(low.size())};

@@ -454,7 +454,8 @@ class HeurParams(C.Structure):
 
 def host_features(queries, context_lens, hp: HeurParams, n_threads: int = 0) -> dict:
     """qre_host_features for a list of str: token estimate + heuristic rule per query, computed on
-    C++ threads (no GIL).  rule == -1 marks queries the caller must classify itself (non-ASCII)."""
+    C++ threads (no GIL).  rule == -1 marks the rare query the caller must classify itself
+    (malformed UTF-8, or a capital sigma: str.lower()'s final-sigma rule)."""
     lib = load()
     n = len(queries)
     enc = [q.encode("utf-8") for q in queries]
@@ -477,7 +478,7 @@ def host_features_packed(queries, context_lens, hp: HeurParams, context_keys=Non
     """`host_features` without per-query marshalling: the queries travel as one UTF-8 blob plus
     offsets (qre_host_features_packed).  With `context_keys` (one per query) the result also
     carries `keys`: the cache's exact-match md5 key of every query (None where rule == -1, i.e. a
-    non-ASCII query the caller hashes itself)."""
+    query handed back, which the caller hashes itself)."""
     lib = load()
     n = len(queries)
     if n == 0:

@@ -162,12 +162,34 @@ def main() -> None:
         lines.append("};")
         lines.append(f"static const int {name}N = {len(rs)};")
 
+    lines.append("struct UniMap { uint32_t cp; uint32_t off; uint32_t len; };")
     emit_ranges("kUniSkip", skip)
     emit_ranges("kUniSpace", space)
     emit_ranges("kUniPunct", punct)
     emit_ranges("kUniWhite", white)
     emit_ranges("kUniDecline", decline)
-    lines.append("struct UniMap { uint32_t cp; uint32_t off; uint32_t len; };")
+    # ---- for the heuristic router's regular expressions (qre_host_features.cu): Python `re` classes on str
+    # patterns (\w = isalnum or '_', \d = isdecimal, \s = isspace = kUniWhite) and the full str.lower()
+    # mapping (context-free part; capital sigma is declined there as well)
+    emit_ranges("kUniAlnum", ranges(lambda cp: chr(cp).isalnum()))
+    emit_ranges("kUniDecimal", ranges(lambda cp: chr(cp).isdecimal()))
+    low_entries, low_pool = [], []
+    for cp in range(0x80, 0x110000):
+        if 0xD800 <= cp <= 0xDFFF:
+            continue
+        m = chr(cp).lower()
+        if m != chr(cp):
+            low_entries.append((cp, len(low_pool), len(m)))
+            low_pool.extend(ord(c) for c in m)
+    lines.append("static const UniMap kUniLower[] = {")
+    for i in range(0, len(low_entries), 5):
+        lines.append("  " + " ".join(f"{{0x{c:X}, {o}, {n}}}," for c, o, n in low_entries[i:i + 5]))
+    lines.append("};")
+    lines.append(f"static const int kUniLowerN = {len(low_entries)};")
+    lines.append("static const uint32_t kUniLowerPool[] = {")
+    for i in range(0, len(low_pool), 12):
+        lines.append("  " + " ".join(f"0x{c:X}," for c in low_pool[i:i + 12]))
+    lines.append("  0};")
     lines.append("static const UniMap kUniMap[] = {")
     for i in range(0, len(entries), 5):
         lines.append("  " + " ".join(f"{{0x{c:X}, {o}, {n}}}," for c, o, n in entries[i:i + 5]))

@@ -330,7 +330,7 @@ class HeuristicRouter(BaseRouter):
                        context_keys: Optional[Sequence[str]] = None):
         """What the fused device pass needs from the host for a batch — token counts and the
         heuristic (device, confidence) pairs — as arrays, without building any per-query object
-        (qre_host_features_packed on C++ threads; non-ASCII queries, and every query when a real
+        (qre_host_features_packed on C++ threads; the rare query it hands back, and every query when a real
         tokenizer is installed, go through the Python rules).  With `context_keys` a fourth value is
         returned: the cache's exact-match key of every query (computed in the same C++ pass)."""
         if LITELLM_AVAILABLE:
@@ -351,7 +351,7 @@ class HeuristicRouter(BaseRouter):
 
     def classify_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
         """`classify` for a whole batch on C++ threads (libqre_b200 qre_host_features); the few
-        queries with non-ASCII characters, and every query when a real tokenizer is installed,
+        queries it hands back (capital sigma), and every query when a real tokenizer is installed,
         go through `classify`.  Returns (list of classify() tuples, token counts)."""
         n = len(queries)
         if LITELLM_AVAILABLE:

@@ -254,9 +254,12 @@ QRE_API int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_c
  * UTF-8 bytes of length query_len[i]; context_len[i] is len(context) in characters (<= 0: no
  * context).  Outputs: tok[i]; heur_dev/heur_conf[i]; heur_rule[i] = which rule fired
  * (0 complex pattern, 1 long query, 2 multi-question, 3 code markers, 4 large context,
- * 5 simple pattern, 6 short everyday query, 7 token fallback; -1 = the query has non-ASCII
- * characters and must be classified by the caller's Unicode-aware code); heur_cat[i] = pattern
- * category index for rules 0 / 5 (the '?' count for rule 2). */
+ * 5 simple pattern, 6 short everyday query, 7 token fallback; -1 = handed back to the caller's
+ * own classifier: malformed UTF-8, or a capital sigma, whose lower-casing depends on its neighbours;
+ * every other text, ASCII or not, is classified with Python `re` / `str` semantics for \b, \w, \s,
+ * \d, lower(), strip(), split() and len()); heur_cat[i] = pattern category index for rules 0 / 5
+ * (the '?' count for rule 2).  query_len / context_len: query_len[i] is in BYTES, context_len[i] in
+ * characters. */
 typedef struct {
   int32_t long_chars;            /* heuristic_long_chars          (qre:225) */
   int32_t multi_qmarks;          /* heuristic_multi_qmarks        (qre:226) */

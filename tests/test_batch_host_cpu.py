@@ -101,7 +101,7 @@ def test_packed_features_equal_pointer_form_and_keys_equal_md5():
     from qre_b200 import _cabi
     rs = np.random.Generator(np.random.PCG64(9))
     words = ["implement", "What is", " hello ", "compare", "daily intake", "wéather", "Traceback", "2 + 2 ?",
-             "step by step", "\tdefine  ", "SELECT ;", "vs", "", "ÅNGSTRÖM"]
+             "step by step", "\tdefine  ", "SELECT ;", "vs", "", "ÅNGSTRÖM", "ΣΟΦΙΑ"]
     qs = []
     for i in range(3000):
         k = int(rs.integers(1, 6))
@@ -117,7 +117,7 @@ def test_packed_features_equal_pointer_form_and_keys_equal_md5():
     n_none = 0
     for q, c, key, rule in zip(qs, cks, b["keys"], b["rule"]):
         if rule < 0:
-            assert key is None and any(ord(ch) > 127 for ch in q)
+            assert key is None and "Σ" in q               # only the final-sigma texts are handed back
             n_none += 1
         else:
             assert key == hashlib.md5(f"{c}||{q.lower().strip()}".encode("utf-8")).hexdigest()

@@ -1,6 +1,8 @@
 """CPU: qre_host_features (C++ threads) against HeuristicRouter.classify (Python `re`) on a large
-generated ASCII corpus that stresses every pattern, word-boundary quirk and rule order; and, when
-the reference tree is mounted, against the reference's own HeuristicRouter."""
+generated corpus that stresses every pattern, word-boundary quirk and rule order — ASCII and, for
+the general path, Unicode text (accented neighbours of the keywords, non-ASCII spaces and digits,
+characters whose lower() changes length); and, when the reference tree is mounted, against the
+reference's own HeuristicRouter."""
 import numpy as np
 import pytest
 
@@ -29,7 +31,14 @@ PUNCT = [" ", " ", " ", ", ", ". ", "? ", "! ", "\n", "\t", " - ", "; ", " {", "
 MARKERS = ["def ", "class ", "import ", "Traceback", "Exception", "SELECT ", "FROM ", "JOIN ", "WITH ", "!="]
 
 
-def _corpus(n, seed):
+UNI_WORDCH = ["é", "ß", "ñ", "Ü", "İ", "ı", "中", "文", "й", "Ж", "α", "٣", "K", "ǅ", "ﬁ", "²", "한", "e\u0301"]
+UNI_PUNCT = ["…", "—", "«", "»", "¿", "·", "。", "😀", "\u0301", "€"]
+UNI_SPACE = ["\u00a0", "\u2003", "\u3000", "\u2028", "\x85", "\u1680"]
+UNI_MISC = ["İstanbul", "straße", "naïve", "DÉBUG", "fıx", "Kelvin", "日本語", "привет", "API’s", "ＳＱＬ", "\u200bhi\u200b", "ſql", "ſpark", "eſſay", "hı", "Kubernetes", "dıjkstra"]
+UNI_DIGITS = ["٣", "12", "７", "४२", "9", "²", "½"]
+
+
+def _corpus(n, seed, unicode_mix=False):
     rs = np.random.Generator(np.random.PCG64(seed))
     out = []
     for i in range(n):
@@ -53,7 +62,27 @@ def _corpus(n, seed):
         if rs.random() < 0.02:
             q = ""
         if rs.random() < 0.03:
-            q += " café naïve"            # non-ASCII: must be handed back (rule -1)
+            q += " café naïve"            # non-ASCII: the general path
+        if unicode_mix and rs.random() < 0.5:
+            # glue Unicode word characters, spaces, digits and punctuation onto / between the words
+            bits = q.split(" ")
+            for j in range(len(bits)):
+                u = rs.random()
+                if u < 0.15:
+                    bits[j] = str(rs.choice(UNI_WORDCH)) + bits[j]            # \b must NOT see a boundary here
+                elif u < 0.30:
+                    bits[j] = bits[j] + str(rs.choice(UNI_WORDCH))
+                elif u < 0.40:
+                    bits[j] = bits[j] + str(rs.choice(UNI_PUNCT))             # still a boundary
+                elif u < 0.45:
+                    bits[j] = str(rs.choice(UNI_MISC))
+            q = str(rs.choice(UNI_SPACE + [" "] * 6)).join(bits)
+            if rs.random() < 0.1:
+                q = str(rs.choice(UNI_SPACE)) + q + str(rs.choice(UNI_SPACE))
+        if unicode_mix and rs.random() < 0.03:
+            q = f"{rs.choice(UNI_DIGITS)}{rs.choice(['', ' ', chr(0x3000)])}{rs.choice(list('+-*/'))} {rs.choice(UNI_DIGITS)}{rs.choice(['', '?'])}"
+        if unicode_mix and rs.random() < 0.01:
+            q += " ΣΟΦΙΑ"                 # capital sigma: handed back (final-sigma rule of str.lower)
         ctx_len = int(rs.choice([0, 0, 5, 799, 800, 3199, 3200, 9000]))
         out.append((q, None if ctx_len == 0 else "c" * ctx_len))
     return out
@@ -80,13 +109,49 @@ def test_cpp_features_equal_python_classifier(ci):
         exp = hr.classify(q, c)
         assert f == exp, (q, c and len(c), f, exp)
         assert t == hr._token_fallback.count(q, c)
-        exp_rule.append(-1 if not q.isascii() else prefix[exp[3].split("=")[0].split(" ->")[0]])
+        exp_rule.append(prefix[exp[3].split("=")[0].split(" ->")[0]])
     hp = _cabi.HeurParams(hr.long_text_threshold, hr.multi_question_threshold, hr.code_markers_needed,
                           hr.context_chars_threshold, hr._token_fallback.threshold, 2)
     r = _cabi.host_features(qs, [len(c) if c else 0 for c in cs], hp, n_threads=4)
     assert np.array_equal(r["rule"], np.array(exp_rule, np.int32))
+    assert np.array_equal(r["heur_dev"], np.array([f[0] for f in feats], np.uint8))
+    assert np.array_equal(r["heur_conf"], np.array([f[1] for f in feats], np.float64))
+    assert np.array_equal(r["tok"], np.array(toks, np.int32))
     if ci == 0:      # with the default thresholds the corpus reaches every rule
-        assert set(exp_rule) == {-1, 0, 1, 2, 3, 4, 5, 6, 7}
+        assert set(exp_rule) == {0, 1, 2, 3, 4, 5, 6, 7}
+
+
+@pytest.mark.parametrize("ci", range(len(CFGS)))
+def test_cpp_features_on_unicode_text(ci):
+    """The general path: every keyword with Unicode word characters, punctuation and spaces around it,
+    non-ASCII digits in the tiny-math rule, characters whose lower() changes length (İ), Unicode
+    whitespace in strip() / split() / len().  Rule, device, confidence, token estimate and the cache's
+    exact-match key must equal Python's; only texts with a capital sigma are handed back."""
+    import hashlib
+    _, qre_mod, _ = R.load_modules(None, OracleEngine)
+    hr = qre_mod.HeuristicRouter(CFGS[ci])
+    corpus = _corpus(5000, 40 + ci, unicode_mix=True)
+    qs, cs = [q for q, _ in corpus], [c for _, c in corpus]
+    prefix = {"complex pattern": 0, "long query chars": 1, "multi-question count": 2,
+              "code/debug markers detected": 3, "large context chars": 4, "simple pattern": 5,
+              "short everyday query": 6, "no heuristic match": 7}
+    hp = _cabi.HeurParams(hr.long_text_threshold, hr.multi_question_threshold, hr.code_markers_needed,
+                          hr.context_chars_threshold, hr._token_fallback.threshold, 2)
+    cks = [("default", "ctx-ü")[i % 2] for i in range(len(qs))]
+    r = _cabi.host_features_packed(qs, [len(c) if c else 0 for c in cs], hp, context_keys=cks, n_threads=3)
+    n_uni = n_back = 0
+    for i, (q, c) in enumerate(corpus):
+        if r["rule"][i] < 0:
+            assert "Σ" in q and r["keys"][i] is None, repr(q)
+            n_back += 1
+            continue
+        exp = hr.classify(q, c)
+        got = (int(r["heur_dev"][i]), float(r["heur_conf"][i]), int(r["rule"][i]))
+        assert got == (exp[0], exp[1], prefix[exp[3].split("=")[0].split(" ->")[0]]), (repr(q), got, exp)
+        assert int(r["tok"][i]) == hr._token_fallback.count(q, c), repr(q)
+        assert r["keys"][i] == hashlib.md5(f"{cks[i]}||{q.lower().strip()}".encode("utf-8")).hexdigest(), repr(q)
+        n_uni += not q.isascii()
+    assert n_uni > 1500 and 0 < n_back < 100
 
 
 @pytest.mark.skipif(not ref_harness.available(), reason="reference tree not mounted")
