@@ -9,9 +9,8 @@
 // ASCII queries are matched byte-wise.  Other queries are decoded, stripped and lowered with the
 // full str.lower() table, and every character gets Python `re`'s class on str patterns (\w = isalnum
 // or '_', \s = isspace, \d = isdecimal; tables generated from unicodedata, qre_unicode_tables.inc), so
-// \b, \s, \d, len() and split() mean what they mean in the reference.  Only malformed UTF-8 and texts
-// with a capital sigma (str.lower()'s final-sigma rule looks at the neighbours) are handed back
-// (rule = -1).
+// \b, \s, \d, len() and split() mean what they mean in the reference (str.lower()'s final-sigma rule
+// included).  Only malformed UTF-8 is handed back (rule = -1).
 #include <stdint.h>
 #include <string.h>
 
@@ -390,7 +389,7 @@ void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_h
   for (int64_t i = 0; i < q_len;) {
     uint32_t cp;
     at.push_back(i);
-    if (!utf8_next(q_raw, q_len, i, cp) || cp == 0x03A3) { declined(); return; }   // malformed, or final-sigma rule
+    if (!utf8_next(q_raw, q_len, i, cp)) { declined(); return; }                   // malformed UTF-8
     cps.push_back(cp);
   }
   at.push_back(q_len);
@@ -419,10 +418,29 @@ void classify_one(const char* q_raw, int64_t q_len, int64_t ctx_len, const qre_h
     for (size_t k = start + 1; k < fold.size(); ++k) cls.push_back(kCont);
     ++low_chars;
   };
+  // str.lower()'s one context rule: capital sigma becomes the FINAL form iff a cased character precedes it
+  // and none follows, case-ignorable characters skipped on both sides (looked up over the whole query:
+  // the stripped-off whitespace is neither)
+  auto cased = [](uint32_t c) {
+    return c < 0x80 ? ((c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z')) : uni_in(kUniCased, kUniCasedN, c);
+  };
+  auto ignorable = [](uint32_t c) {
+    return c < 0x80 ? (c == '\'' || c == '.' || c == ':' || c == '^' || c == '`') : uni_in(kUniCaseIgnorable, kUniCaseIgnorableN, c);
+  };
+  auto final_sigma = [&](int64_t i) {
+    int64_t j = i - 1;
+    while (j >= 0 && ignorable(cps[j])) --j;
+    if (j < 0 || !cased(cps[j])) return false;
+    int64_t k = i + 1;
+    while (k < n_all && ignorable(cps[k])) ++k;
+    return k == n_all || !cased(cps[k]);
+  };
   for (int64_t i = b; i < e; ++i) {
     const uint32_t cp = cps[i];
     if (cp < 0x80) {
       put(cp >= 'A' && cp <= 'Z' ? cp - 'A' + 'a' : cp);
+    } else if (cp == 0x03A3) {
+      put(final_sigma(i) ? 0x03C2 : 0x03C3);
     } else if (const UniMap* m = lower_of(cp)) {
       for (uint32_t k = 0; k < m->len; ++k) put(kUniLowerPool[m->off + k]);
     } else {

@@ -454,8 +454,8 @@ class HeurParams(C.Structure):
 
 def host_features(queries, context_lens, hp: HeurParams, n_threads: int = 0) -> dict:
     """qre_host_features for a list of str: token estimate + heuristic rule per query, computed on
-    C++ threads (no GIL).  rule == -1 marks the rare query the caller must classify itself
-    (malformed UTF-8, or a capital sigma: str.lower()'s final-sigma rule)."""
+    C++ threads (no GIL).  rule == -1 marks a query the caller must classify itself
+    (malformed UTF-8: cannot happen for a Python str)."""
     lib = load()
     n = len(queries)
     enc = [q.encode("utf-8") for q in queries]

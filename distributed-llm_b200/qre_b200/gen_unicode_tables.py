@@ -173,6 +173,13 @@ def main() -> None:
     # mapping (context-free part; capital sigma is declined there as well)
     emit_ranges("kUniAlnum", ranges(lambda cp: chr(cp).isalnum()))
     emit_ranges("kUniDecimal", ranges(lambda cp: chr(cp).isdecimal()))
+    # final-sigma rule of str.lower(): capital sigma becomes the final form iff a CASED character precedes it
+    # and none follows, case-IGNORABLE characters skipped on both sides.  CPython does not expose the two
+    # properties; they are read off lower() itself.
+    emit_ranges("kUniCased", ranges(lambda cp: not 0xD800 <= cp <= 0xDFFF and (chr(cp) + "\u03a3").lower()[-1] == "\u03c2"))
+    emit_ranges("kUniCaseIgnorable", ranges(lambda cp: not 0xD800 <= cp <= 0xDFFF
+                                            and (chr(cp) + "\u03a3").lower()[-1] != "\u03c2"
+                                            and ("a" + chr(cp) + "\u03a3").lower()[-1] == "\u03c2"))
     low_entries, low_pool = [], []
     for cp in range(0x80, 0x110000):
         if 0xD800 <= cp <= 0xDFFF:

@@ -351,7 +351,7 @@ class HeuristicRouter(BaseRouter):
 
     def classify_batch(self, queries: Sequence[str], contexts: Sequence[Optional[str]]):
         """`classify` for a whole batch on C++ threads (libqre_b200 qre_host_features); the few
-        queries it hands back (capital sigma), and every query when a real tokenizer is installed,
+        queries it hands back (none for well-formed text), and every query when a real tokenizer is installed,
         go through `classify`.  Returns (list of classify() tuples, token counts)."""
         n = len(queries)
         if LITELLM_AVAILABLE:

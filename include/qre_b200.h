@@ -255,9 +255,8 @@ QRE_API int qre_merge_route_dev(qre_cache_t* h, int m, int n_shards, const qre_c
  * context).  Outputs: tok[i]; heur_dev/heur_conf[i]; heur_rule[i] = which rule fired
  * (0 complex pattern, 1 long query, 2 multi-question, 3 code markers, 4 large context,
  * 5 simple pattern, 6 short everyday query, 7 token fallback; -1 = handed back to the caller's
- * own classifier: malformed UTF-8, or a capital sigma, whose lower-casing depends on its neighbours;
- * every other text, ASCII or not, is classified with Python `re` / `str` semantics for \b, \w, \s,
- * \d, lower(), strip(), split() and len()); heur_cat[i] = pattern category index for rules 0 / 5
+ * own classifier: malformed UTF-8 only; every other text, ASCII or not, is classified with Python `re` /
+ * `str` semantics for \b, \w, \s, \d, lower() incl. its final-sigma rule, strip(), split() and len()); heur_cat[i] = pattern category index for rules 0 / 5
  * (the '?' count for rule 2).  query_len / context_len: query_len[i] is in BYTES, context_len[i] in
  * characters. */
 typedef struct {

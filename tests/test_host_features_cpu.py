@@ -81,8 +81,9 @@ def _corpus(n, seed, unicode_mix=False):
                 q = str(rs.choice(UNI_SPACE)) + q + str(rs.choice(UNI_SPACE))
         if unicode_mix and rs.random() < 0.03:
             q = f"{rs.choice(UNI_DIGITS)}{rs.choice(['', ' ', chr(0x3000)])}{rs.choice(list('+-*/'))} {rs.choice(UNI_DIGITS)}{rs.choice(['', '?'])}"
-        if unicode_mix and rs.random() < 0.01:
-            q += " ΣΟΦΙΑ"                 # capital sigma: handed back (final-sigma rule of str.lower)
+        if unicode_mix and rs.random() < 0.05:
+            # capital sigma: str.lower() picks the final form by looking at the neighbours
+            q += str(rs.choice([" ΣΟΦΙΑ", " ΟΔΥΣΣΕΥΣ", "Σ", " ΑΣ.", " ΑΣ'Α", " Σ Σ", "aΣ", " ΑΣ\u0301", "ΑΣ:", " ΑΣ)Σ", "ΑΣ "]))
         ctx_len = int(rs.choice([0, 0, 5, 799, 800, 3199, 3200, 9000]))
         out.append((q, None if ctx_len == 0 else "c" * ctx_len))
     return out
@@ -125,8 +126,9 @@ def test_cpp_features_equal_python_classifier(ci):
 def test_cpp_features_on_unicode_text(ci):
     """The general path: every keyword with Unicode word characters, punctuation and spaces around it,
     non-ASCII digits in the tiny-math rule, characters whose lower() changes length (İ), Unicode
-    whitespace in strip() / split() / len().  Rule, device, confidence, token estimate and the cache's
-    exact-match key must equal Python's; only texts with a capital sigma are handed back."""
+    whitespace in strip() / split() / len(), capital sigmas in and out of the final position.  Rule,
+    device, confidence, token estimate and the cache's exact-match key must equal Python's for every
+    text; only malformed UTF-8 (not expressible as a str) is handed back."""
     import hashlib
     _, qre_mod, _ = R.load_modules(None, OracleEngine)
     hr = qre_mod.HeuristicRouter(CFGS[ci])
@@ -139,19 +141,28 @@ def test_cpp_features_on_unicode_text(ci):
                           hr.context_chars_threshold, hr._token_fallback.threshold, 2)
     cks = [("default", "ctx-ü")[i % 2] for i in range(len(qs))]
     r = _cabi.host_features_packed(qs, [len(c) if c else 0 for c in cs], hp, context_keys=cks, n_threads=3)
-    n_uni = n_back = 0
+    n_uni = n_sigma = 0
     for i, (q, c) in enumerate(corpus):
-        if r["rule"][i] < 0:
-            assert "Σ" in q and r["keys"][i] is None, repr(q)
-            n_back += 1
-            continue
+        assert r["rule"][i] >= 0, repr(q)
+        n_sigma += "Σ" in q
         exp = hr.classify(q, c)
         got = (int(r["heur_dev"][i]), float(r["heur_conf"][i]), int(r["rule"][i]))
         assert got == (exp[0], exp[1], prefix[exp[3].split("=")[0].split(" ->")[0]]), (repr(q), got, exp)
         assert int(r["tok"][i]) == hr._token_fallback.count(q, c), repr(q)
         assert r["keys"][i] == hashlib.md5(f"{cks[i]}||{q.lower().strip()}".encode("utf-8")).hexdigest(), repr(q)
         n_uni += not q.isascii()
-    assert n_uni > 1500 and 0 < n_back < 100
+    assert n_uni > 1500 and n_sigma > 100
+    # malformed UTF-8 through the raw entry point: handed back
+    import ctypes as C
+    raw = [b"ok text", b"bad \xff\xfe bytes", b"truncated \xe4\xb8", b"overlong \xc0\xaf"]
+    arr = (C.c_char_p * len(raw))(*raw)
+    ql = np.array([len(x) for x in raw], np.int64)
+    out = {k: np.zeros(len(raw), t) for k, t in (("tok", np.int32), ("dev", np.uint8), ("conf", np.float64),
+                                                   ("rule", np.int32), ("cat", np.int32))}
+    rc = _cabi.load().qre_host_features(C.c_int64(len(raw)), arr, _cabi._ptr(ql), None, C.byref(hp), C.c_int(1),
+                                        _cabi._ptr(out["tok"]), _cabi._ptr(out["dev"]), _cabi._ptr(out["conf"]),
+                                        _cabi._ptr(out["rule"]), _cabi._ptr(out["cat"]))
+    assert rc == 0 and out["rule"][0] >= 0 and out["rule"][1:].tolist() == [-1, -1, -1]
 
 
 @pytest.mark.skipif(not ref_harness.available(), reason="reference tree not mounted")
